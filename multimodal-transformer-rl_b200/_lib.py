@@ -1,0 +1,89 @@
+"""ctypes binding of libdtb200.so (the C ABI in include/dtb200.h).  Fails loudly when the library is absent."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libdtb200.so")
+
+_lib = None
+
+
+class DtbError(RuntimeError):
+    pass
+
+
+class GemmEpilogue(C.Structure):
+    _fields_ = [
+        ("bias", C.c_void_p), ("residual", C.c_void_p), ("ldr", C.c_int),
+        ("aux", C.c_void_p), ("ldaux", C.c_int), ("act", C.c_int), ("dact", C.c_int),
+        ("out_bf16", C.c_void_p), ("ldo_b", C.c_int), ("out_f32", C.c_void_p), ("ldo_f", C.c_int),
+        ("out_preact", C.c_void_p), ("partial", C.c_void_p), ("alpha", C.c_float), ("accumulate", C.c_int),
+    ]
+
+
+def load() -> C.CDLL:
+    """Load libdtb200.so; raise if it has not been built (no fallback path exists)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise DtbError(
+            f"{LIB_PATH} not found: build it with `python multimodal-transformer-rl_b200/build.py` "
+            "(the sm_100a CUDA extension is the only implementation; there is no CPU/PyTorch fallback)"
+        )
+    lib = C.CDLL(LIB_PATH)
+    lib.dtb_last_error.restype = C.c_char_p
+    lib.dtb_abi_version.restype = C.c_int
+    _lib = lib
+    return lib
+
+
+def check(rc: int) -> int:
+    if rc < 0:
+        raise DtbError(f"dtb200 error {rc}: {load().dtb_last_error().decode()}")
+    return rc
+
+
+def ptr(t) -> C.c_void_p:
+    """Device pointer of a torch tensor (None -> NULL)."""
+    return C.c_void_p(0 if t is None else t.data_ptr())
+
+
+def stream_ptr() -> C.c_void_p:
+    import torch
+
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def exported_symbols() -> list[str]:
+    """Names declared in include/dtb200.h (parsed) — used by the CPU test that the ABI is complete."""
+    import re
+
+    hdr = os.path.join(os.path.dirname(_HERE), "include", "dtb200.h")
+    txt = open(hdr).read()
+    txt = re.sub(r"/\*.*?\*/", "", txt, flags=re.S)
+    return sorted(set(re.findall(r"\b(dtb_[a-z0-9_]+)\s*\(", txt)))
+
+
+def gemm_bf16(A, B, M, N, K, *, a_mn_major=False, b_mn_major=False, bias=None, residual=None, aux=None, act=0, dact=0,
+              out_bf16=None, out_f32=None, out_preact=None, partial=None, alpha=1.0, accumulate=False, split_k=1, bn=0):
+    """Raw tensor-core GEMM through the C ABI (see dtb_gemm_bf16 in include/dtb200.h)."""
+    ep = GemmEpilogue()
+    ep.bias = ptr(bias).value
+    ep.residual = ptr(residual).value
+    ep.ldr = residual.stride(0) if residual is not None else 0
+    ep.aux = ptr(aux).value
+    ep.ldaux = aux.stride(0) if aux is not None else 0
+    ep.act, ep.dact = act, dact
+    ep.out_bf16 = ptr(out_bf16).value
+    ep.ldo_b = out_bf16.stride(0) if out_bf16 is not None else (out_preact.stride(0) if out_preact is not None else 0)
+    ep.out_f32 = ptr(out_f32).value
+    ep.ldo_f = out_f32.stride(0) if out_f32 is not None else 0
+    ep.out_preact = ptr(out_preact).value
+    ep.partial = ptr(partial).value
+    ep.alpha = alpha
+    ep.accumulate = int(accumulate)
+    check(load().dtb_gemm_bf16(stream_ptr(), ptr(A), C.c_int(A.stride(0)), int(a_mn_major), ptr(B), C.c_int(B.stride(0)),
+                               int(b_mn_major), M, N, K, C.byref(ep), split_k, bn))

@@ -1,0 +1,185 @@
+// Host side of the tcgen05 GEMM: TMA descriptor encoding (driver entry point fetched through
+// cudart so the library has no link-time dependency on libcuda), tile/split heuristics, launch.
+#include "gemm_sm100.cuh"
+#include "kernels.h"
+
+#include <cudaTypedefs.h>
+#include <mutex>
+#include <unordered_map>
+#include <string.h>
+
+namespace dtb {
+
+static PFN_cuTensorMapEncodeTiled_v12000 g_encode = nullptr;
+
+static int get_encode_fn() {
+  if (g_encode) return DTB_OK;
+  void* fn = nullptr;
+  cudaDriverEntryPointQueryResult qres;
+  DTB_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres));
+  DTB_REQUIRE(fn != nullptr && qres == cudaDriverEntryPointSuccess, DTB_ERR_CUDA, "cuTensorMapEncodeTiled entry point unavailable");
+  g_encode = reinterpret_cast<PFN_cuTensorMapEncodeTiled_v12000>(fn);
+  return DTB_OK;
+}
+
+struct TmKey {
+  const void* ptr;
+  uint64_t d0, d1, stride;
+  uint32_t b0, b1;
+  bool operator==(const TmKey& o) const {
+    return ptr == o.ptr && d0 == o.d0 && d1 == o.d1 && stride == o.stride && b0 == o.b0 && b1 == o.b1;
+  }
+};
+struct TmKeyHash {
+  size_t operator()(const TmKey& k) const {
+    size_t h = reinterpret_cast<size_t>(k.ptr);
+    h ^= k.d0 * 0x9E3779B97F4A7C15ull + (h << 6) + (h >> 2);
+    h ^= k.d1 * 0xC2B2AE3D27D4EB4Full + (h << 6) + (h >> 2);
+    h ^= k.stride * 0x165667B19E3779F9ull + (h << 6) + (h >> 2);
+    h ^= ((size_t)k.b0 << 32 | k.b1) + (h << 6) + (h >> 2);
+    return h;
+  }
+};
+static std::unordered_map<TmKey, CUtensorMap, TmKeyHash> g_tm_cache;
+static std::mutex g_tm_mutex;
+
+// 2-D bf16 tensor map: dims {d0 (contiguous), d1}, row stride in elements, box {b0, b1}, 128B swizzle.
+static int make_tmap(CUtensorMap* out, const void* ptr, uint64_t d0, uint64_t d1, uint64_t stride_elems, uint32_t b0, uint32_t b1) {
+  DTB_TRY(get_encode_fn());
+  DTB_REQUIRE((reinterpret_cast<uintptr_t>(ptr) & 15) == 0, DTB_ERR_BAD_ARG, "GEMM operand pointer must be 16-byte aligned");
+  DTB_REQUIRE((stride_elems * 2) % 16 == 0, DTB_ERR_BAD_ARG, "GEMM operand row stride must be a multiple of 8 elements (got %llu)",
+              (unsigned long long)stride_elems);
+  TmKey key{ptr, d0, d1, stride_elems, b0, b1};
+  {
+    std::lock_guard<std::mutex> g(g_tm_mutex);
+    auto it = g_tm_cache.find(key);
+    if (it != g_tm_cache.end()) {
+      *out = it->second;
+      return DTB_OK;
+    }
+  }
+  cuuint64_t gdim[2] = {d0, d1};
+  cuuint64_t gstride[1] = {stride_elems * 2};
+  cuuint32_t box[2] = {b0, b1};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = g_encode(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), gdim, gstride, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  DTB_REQUIRE(r == CUDA_SUCCESS, DTB_ERR_CUDA, "cuTensorMapEncodeTiled failed (%d) dims=(%llu,%llu) stride=%llu box=(%u,%u)", (int)r,
+              (unsigned long long)d0, (unsigned long long)d1, (unsigned long long)stride_elems, b0, b1);
+  {
+    std::lock_guard<std::mutex> g(g_tm_mutex);
+    if (g_tm_cache.size() > 4096) g_tm_cache.clear();
+    g_tm_cache.emplace(key, *out);
+  }
+  return DTB_OK;
+}
+
+static bool g_attr_set = false;
+
+size_t gemm_splitk_workspace_bytes(int M, int N, int K) {
+  // upper bound used by callers that pre-size the workspace: split <= 32
+  (void)K;
+  return (size_t)32 * M * N * sizeof(float);
+}
+
+int gemm_pick_split(int M, int N, int K, int BN) {
+  const int m_tiles = (M + GEMM_BM - 1) / GEMM_BM, n_tiles = (N + BN - 1) / BN;
+  const int kblocks = (K + GEMM_BK - 1) / GEMM_BK;
+  const int tiles = m_tiles * n_tiles;
+  int split = (2 * num_sms() + tiles - 1) / tiles;
+  int max_split = kblocks / 8;
+  if (max_split < 1) max_split = 1;
+  if (split > max_split) split = max_split;
+  if (split > 32) split = 32;
+  if (split < 1) split = 1;
+  return split;
+}
+
+static int pick_bn(int M, int N, int b_mn_major) {
+  const int m_tiles = (M + GEMM_BM - 1) / GEMM_BM;
+  const int cands[4] = {256, 128, 64, 32};
+  int best = -1;
+  for (int i = 0; i < 4; ++i) {
+    int bn = cands[i];
+    if (b_mn_major && bn % 64) continue;
+    if (N % bn) continue;
+    if (best < 0) best = bn;  // largest divisor candidate
+    if (m_tiles * (N / bn) >= num_sms()) return bn;
+    best = bn;  // keep shrinking while the grid is under-filled
+    if (bn == 64) break;  // do not go below 64 just to add CTAs
+  }
+  if (best > 0) return best;
+  // N not divisible by any candidate: predicate the tail
+  return b_mn_major ? 64 : (N >= 64 ? 64 : 32);
+}
+
+int gemm_bf16(cudaStream_t stream, const bf16* A, int lda, int a_mn_major, const bf16* B, int ldb, int b_mn_major, int M, int N, int K,
+              const GemmEpilogue& ep_in, int split_k, int bn_override) {
+  DTB_REQUIRE(M > 0 && N > 0 && K > 0, DTB_ERR_BAD_ARG, "gemm: empty problem %d x %d x %d", M, N, K);
+  DTB_REQUIRE(N % 8 == 0, DTB_ERR_BAD_ARG, "gemm: N (%d) must be a multiple of 8", N);
+  GemmParams p;
+  memset(&p, 0, sizeof(p));
+  p.M = M; p.N = N; p.K = K;
+  p.a_mn_major = a_mn_major; p.b_mn_major = b_mn_major;
+  p.BN = bn_override > 0 ? bn_override : pick_bn(M, N, b_mn_major);
+  DTB_REQUIRE(p.BN % 32 == 0 && p.BN >= 32 && p.BN <= 256 && (!b_mn_major || p.BN % 64 == 0), DTB_ERR_BAD_ARG, "gemm: bad BN %d", p.BN);
+  p.m_tiles = (M + GEMM_BM - 1) / GEMM_BM;
+  p.n_tiles = (N + p.BN - 1) / p.BN;
+  const int kblocks = (K + GEMM_BK - 1) / GEMM_BK;
+  if (split_k < 1) split_k = 1;
+  if (split_k > kblocks) split_k = kblocks;
+  p.kb_per_split = (kblocks + split_k - 1) / split_k;
+  p.split_k = (kblocks + p.kb_per_split - 1) / p.kb_per_split;  // no empty splits
+  p.ep = ep_in;
+  if (p.ep.alpha == 0.f) p.ep.alpha = 1.f;
+  if (p.split_k > 1) DTB_REQUIRE(p.ep.partial != nullptr, DTB_ERR_BAD_ARG, "gemm: split-K needs a partial workspace");
+  if (p.split_k == 1 && p.ep.partial) p.split_k = 1;  // single split still writes partial[0]
+
+  CUtensorMap tmA, tmB;
+  if (!a_mn_major) DTB_TRY(make_tmap(&tmA, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda, GEMM_BK, GEMM_BM));
+  else             DTB_TRY(make_tmap(&tmA, A, (uint64_t)M, (uint64_t)K, (uint64_t)lda, 64, GEMM_BK));
+  if (!b_mn_major) DTB_TRY(make_tmap(&tmB, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, GEMM_BK, (uint32_t)p.BN));
+  else             DTB_TRY(make_tmap(&tmB, B, (uint64_t)N, (uint64_t)K, (uint64_t)ldb, 64, GEMM_BK));
+
+  if (!g_attr_set) {
+    DTB_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_BYTES));
+    g_attr_set = true;
+  }
+  const int total = p.m_tiles * p.n_tiles * p.split_k;
+  const int grid = total < num_sms() ? total : num_sms();
+  gemm_tcgen05_kernel<<<grid, GEMM_THREADS, GEMM_SMEM_BYTES, stream>>>(tmA, tmB, p);
+  DTB_CHECK_LAUNCH();
+  return p.split_k;  // >= 1: number of partial slices written when ep.partial != null
+}
+
+// ---- split-K reduction: out[M, ldo] (+)= sum_s partial[s][M][N] -----------------------------------
+__global__ void splitk_reduce_kernel(const float* __restrict__ partial, int splits, int M, int N, float* __restrict__ out, int ldo,
+                                     int accumulate, float scale) {
+  const size_t n4 = (size_t)M * N / 4;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
+    float4 s = ldg_f4(partial + i * 4);
+    for (int k = 1; k < splits; ++k) {
+      float4 v = ldg_f4(partial + (size_t)k * M * N + i * 4);
+      s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+    }
+    const size_t e = i * 4;
+    const int r = (int)(e / N), c = (int)(e % N);
+    float* o = out + (size_t)r * ldo + c;
+    float4 prev = accumulate ? *reinterpret_cast<float4*>(o) : make_float4(0, 0, 0, 0);
+    *reinterpret_cast<float4*>(o) = make_float4(prev.x + scale * s.x, prev.y + scale * s.y, prev.z + scale * s.z, prev.w + scale * s.w);
+  }
+}
+
+int splitk_reduce(cudaStream_t stream, const float* partial, int splits, int M, int N, float* out, int ldo, int accumulate, float scale) {
+  DTB_REQUIRE(N % 4 == 0 && ldo % 4 == 0, DTB_ERR_BAD_ARG, "splitk_reduce: N and ldo must be multiples of 4");
+  const size_t n4 = (size_t)M * N / 4;
+  int blocks = (int)((n4 + 255) / 256);
+  if (blocks > num_sms() * 8) blocks = num_sms() * 8;
+  if (blocks < 1) blocks = 1;
+  splitk_reduce_kernel<<<blocks, 256, 0, stream>>>(partial, splits, M, N, out, ldo, accumulate, scale);
+  DTB_CHECK_LAUNCH();
+  return DTB_OK;
+}
+
+}  // namespace dtb

@@ -1,0 +1,64 @@
+// Internal host-side launch API shared by the .cu translation units (not part of the C ABI).
+#pragma once
+#include "common.cuh"
+
+namespace dtb {
+
+struct GemmEpilogue {
+  const float* bias;      // [N] or null
+  const float* residual;  // fp32 [M, ldr] or null (added after activation)
+  int ldr;
+  const bf16* aux;        // for dact: saved activation output (relu) or pre-activation (gelu)
+  int ldaux;
+  int act;                // 0 none, 1 relu, 2 gelu_new   (applied after bias)
+  int dact;               // 0 none, 1 relu', 2 gelu_new' (multiplies the accumulator by act'(aux))
+  bf16* out_bf16;         // optional bf16 output [M, ldo_b]
+  int ldo_b;
+  float* out_f32;         // optional fp32 output [M, ldo_f]
+  int ldo_f;
+  bf16* out_preact;       // optional: bias-added pre-activation (bf16, ld = ldo_b) saved for gelu backward
+  float* partial;         // split-K: fp32 partials [split][M][N]; epilogue fields above are then ignored
+  float alpha;            // scale applied to the accumulator first
+};
+
+struct GemmParams {
+  int M, N, K;
+  int BN;            // N tile: 32..256, multiple of 32 (multiple of 64 when B is MN-major)
+  int a_mn_major, b_mn_major;
+  int split_k;       // >= 1
+  int kb_per_split;  // k-blocks (of 64) per split
+  int m_tiles, n_tiles;
+  GemmEpilogue ep;
+};
+
+
+// ---- gemm_host.cu ------------------------------------------------------------------------------
+// Returns the number of split-K slices written (>=1) or a negative error code.
+int gemm_bf16(cudaStream_t stream, const bf16* A, int lda, int a_mn_major, const bf16* B, int ldb, int b_mn_major, int M, int N, int K,
+              const GemmEpilogue& ep, int split_k, int bn_override);
+int gemm_pick_split(int M, int N, int K, int BN);
+int splitk_reduce(cudaStream_t stream, const float* partial, int splits, int M, int N, float* out, int ldo, int accumulate, float scale);
+
+// ---- elementwise.cu ----------------------------------------------------------------------------
+// fp32 [R, C] -> bf16 copy [R, C] and (optional) bf16 transpose [C, R]
+int cast_transpose(cudaStream_t stream, const float* src, int R, int C, bf16* dst, bf16* dst_t);
+int cast_bf16(cudaStream_t stream, const float* src, size_t n, bf16* dst);
+// column sums of a bf16 matrix [M, N] (ld) -> fp32 out[N] (+= if accumulate)
+int colsum_bf16(cudaStream_t stream, const bf16* x, int M, int N, int ld, float* out, int accumulate, float* scratch);
+size_t colsum_scratch_floats(int N);
+
+// ---- layernorm.cu ------------------------------------------------------------------------------
+int ln_fwd(cudaStream_t stream, const float* x, const float* gamma, const float* beta, int M, int H, float eps, bf16* y, float* mean,
+           float* rstd);
+// dx_out = dres + LNbwd(dy); also bf16 copy; dgamma/dbeta accumulated (+=) after internal partial reduce
+int ln_bwd(cudaStream_t stream, const bf16* dy, const float* x, const float* mean, const float* rstd, const float* gamma,
+           const float* dres, int M, int H, float* dx_out, bf16* dx_out_bf16, float* dgamma, float* dbeta, float* scratch);
+size_t ln_bwd_scratch_floats(int H);
+
+// ---- attention.cu ------------------------------------------------------------------------------
+// qkv: bf16 [B, T, 3H] (q | k | v, head h at columns h*d), mask: fp32 [B, K] (T = 3K, token j uses mask[b, j/3]) or null
+int attn_fwd(cudaStream_t stream, const bf16* qkv, const float* mask, int B, int T, int nh, int d, bf16* out, float* lse);
+int attn_bwd(cudaStream_t stream, const bf16* qkv, const float* mask, const bf16* out, const bf16* dout, const float* lse, int B, int T,
+             int nh, int d, bf16* dqkv, float* delta);
+
+}  // namespace dtb
