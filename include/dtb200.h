@@ -69,6 +69,31 @@ typedef struct {
 int dtb_gemm_bf16(void* stream, const void* A, int lda, int a_mn_major, const void* B, int ldb, int b_mn_major, int M, int N, int K,
                   const dtb_gemm_epilogue* ep, int split_k, int bn_override);
 
+/* ---- LayerNorm over the fp32 residual stream (HF:272 ln_1, HF:303 ln_2, HF:450 ln_f, HF:628 embed_ln) -------------
+ * fwd: x fp32 [M,H] -> y bf16 [M,H]; mean/rstd fp32 [M] saved for backward (may be NULL).
+ * bwd: dx = dres + LN'(dy): dx_f32 and/or dx_bf16 outputs; dgamma/dbeta fp32 [H] overwritten.
+ *      scratch: fp32, dtb_layernorm_bwd_scratch_floats(H) elements. */
+int dtb_layernorm_fwd(void* stream, const float* x, const float* gamma, const float* beta, int M, int H, float eps, void* y_bf16,
+                      float* mean, float* rstd);
+size_t dtb_layernorm_bwd_scratch_floats(int H);
+int dtb_layernorm_bwd(void* stream, const void* dy_bf16, const float* x, const float* mean, const float* rstd, const float* gamma,
+                      const float* dres, int M, int H, float* dx_f32, void* dx_bf16, float* dgamma, float* dbeta, float* scratch);
+
+/* ---- fused causal attention with the [B,K] padding mask expanded by index (HF:47-65, 408-414, 631-635) -------------
+ * qkv bf16 [B,T,3H] (q|k|v, head h at h*d), mask fp32 [B,T/3] or NULL; allowed(i,j) = j<=i && mask[b,j/3]>0.
+ * fwd writes out bf16 [B,T,H] and lse fp32 [B,nh,T] (base-2 log-sum-exp of the scaled scores).
+ * bwd writes dqkv bf16 [B,T,3H]; delta fp32 [B,nh,T] is scratch. head_dim d in {32,64,128}. */
+int dtb_attention_fwd(void* stream, const void* qkv, const float* mask, int B, int T, int n_head, int head_dim, void* out, float* lse);
+int dtb_attention_bwd(void* stream, const void* qkv, const float* mask, const void* out, const void* dout, const float* lse, int B,
+                      int T, int n_head, int head_dim, void* dqkv, float* delta);
+
+/* ---- weight staging + bias gradients -----------------------------------------------------------------------------
+ * cast_transpose: fp32 [R,C] -> bf16 [R,C] (dst, may be NULL) and bf16 [C,R] (dst_t, may be NULL).
+ * colsum: out[N] (+)= column sums of bf16 x [M,N] (row stride ld); scratch fp32 dtb_colsum_scratch_floats(N). */
+int dtb_cast_transpose(void* stream, const float* src, int R, int C, void* dst, void* dst_t);
+size_t dtb_colsum_scratch_floats(int N);
+int dtb_colsum_bf16(void* stream, const void* x, int M, int N, int ld, float* out, int accumulate, float* scratch);
+
 #ifdef __cplusplus
 }
 #endif

@@ -87,3 +87,53 @@ def gemm_bf16(A, B, M, N, K, *, a_mn_major=False, b_mn_major=False, bias=None, r
     ep.accumulate = int(accumulate)
     check(load().dtb_gemm_bf16(stream_ptr(), ptr(A), C.c_int(A.stride(0)), int(a_mn_major), ptr(B), C.c_int(B.stride(0)),
                                int(b_mn_major), M, N, K, C.byref(ep), split_k, bn))
+
+
+# ---- thin op wrappers (used by tests and by the host-side model) ------------------------------------------------------
+def _f32p(t):
+    return C.c_void_p(0 if t is None else t.data_ptr())
+
+
+def layernorm_fwd(x, gamma, beta, eps, y, mean=None, rstd=None):
+    M, H = x.shape
+    check(load().dtb_layernorm_fwd(stream_ptr(), ptr(x), ptr(gamma), ptr(beta), M, H, C.c_float(eps), ptr(y), ptr(mean), ptr(rstd)))
+
+
+def layernorm_bwd(dy, x, mean, rstd, gamma, dres, dx_f32, dx_bf16, dgamma, dbeta, scratch=None):
+    import torch
+
+    M, H = x.shape
+    lib = load()
+    lib.dtb_layernorm_bwd_scratch_floats.restype = C.c_size_t
+    if scratch is None:
+        scratch = torch.empty(lib.dtb_layernorm_bwd_scratch_floats(H), device=x.device, dtype=torch.float32)
+    check(lib.dtb_layernorm_bwd(stream_ptr(), ptr(dy), ptr(x), ptr(mean), ptr(rstd), ptr(gamma), ptr(dres), M, H, ptr(dx_f32),
+                                ptr(dx_bf16), ptr(dgamma), ptr(dbeta), ptr(scratch)))
+
+
+def attention_fwd(qkv, mask, n_head, out, lse):
+    B, T, H3 = qkv.shape
+    d = H3 // 3 // n_head
+    check(load().dtb_attention_fwd(stream_ptr(), ptr(qkv), ptr(mask), B, T, n_head, d, ptr(out), ptr(lse)))
+
+
+def attention_bwd(qkv, mask, out, dout, lse, n_head, dqkv, delta):
+    B, T, H3 = qkv.shape
+    d = H3 // 3 // n_head
+    check(load().dtb_attention_bwd(stream_ptr(), ptr(qkv), ptr(mask), ptr(out), ptr(dout), ptr(lse), B, T, n_head, d, ptr(dqkv),
+                                   ptr(delta)))
+
+
+def cast_transpose(src, dst, dst_t):
+    R, Cc = src.shape
+    check(load().dtb_cast_transpose(stream_ptr(), ptr(src), R, Cc, ptr(dst), ptr(dst_t)))
+
+
+def colsum_bf16(x, out, accumulate=False):
+    import torch
+
+    M, N = x.shape
+    lib = load()
+    lib.dtb_colsum_scratch_floats.restype = C.c_size_t
+    scratch = torch.empty(lib.dtb_colsum_scratch_floats(N), device=x.device, dtype=torch.float32)
+    check(lib.dtb_colsum_bf16(stream_ptr(), ptr(x), M, N, x.stride(0), ptr(out), int(accumulate), ptr(scratch)))

@@ -49,4 +49,35 @@ int dtb_gemm_bf16(void* stream, const void* A, int lda, int a_mn_major, const vo
   return rc < 0 ? rc : DTB_OK;
 }
 
+int dtb_layernorm_fwd(void* stream, const float* x, const float* gamma, const float* beta, int M, int H, float eps, void* y, float* mean,
+                      float* rstd) {
+  DTB_REQUIRE(x && gamma && beta && y, DTB_ERR_BAD_ARG, "dtb_layernorm_fwd: null pointer");
+  return ln_fwd((cudaStream_t)stream, x, gamma, beta, M, H, eps, (bf16*)y, mean, rstd);
+}
+size_t dtb_layernorm_bwd_scratch_floats(int H) { return ln_bwd_scratch_floats(H); }
+int dtb_layernorm_bwd(void* stream, const void* dy, const float* x, const float* mean, const float* rstd, const float* gamma,
+                      const float* dres, int M, int H, float* dx_f32, void* dx_bf16, float* dgamma, float* dbeta, float* scratch) {
+  DTB_REQUIRE(dy && x && mean && rstd && gamma && dgamma && dbeta && scratch, DTB_ERR_BAD_ARG, "dtb_layernorm_bwd: null pointer");
+  return ln_bwd((cudaStream_t)stream, (const bf16*)dy, x, mean, rstd, gamma, dres, M, H, dx_f32, (bf16*)dx_bf16, dgamma, dbeta, scratch);
+}
+int dtb_attention_fwd(void* stream, const void* qkv, const float* mask, int B, int T, int n_head, int head_dim, void* out, float* lse) {
+  DTB_REQUIRE(qkv && out && lse, DTB_ERR_BAD_ARG, "dtb_attention_fwd: null pointer");
+  return attn_fwd((cudaStream_t)stream, (const bf16*)qkv, mask, B, T, n_head, head_dim, (bf16*)out, lse);
+}
+int dtb_attention_bwd(void* stream, const void* qkv, const float* mask, const void* out, const void* dout, const float* lse, int B,
+                      int T, int n_head, int head_dim, void* dqkv, float* delta) {
+  DTB_REQUIRE(qkv && out && dout && lse && dqkv && delta, DTB_ERR_BAD_ARG, "dtb_attention_bwd: null pointer");
+  return attn_bwd((cudaStream_t)stream, (const bf16*)qkv, mask, (const bf16*)out, (const bf16*)dout, lse, B, T, n_head, head_dim,
+                  (bf16*)dqkv, delta);
+}
+int dtb_cast_transpose(void* stream, const float* src, int R, int C, void* dst, void* dst_t) {
+  DTB_REQUIRE(src, DTB_ERR_BAD_ARG, "dtb_cast_transpose: null pointer");
+  return cast_transpose((cudaStream_t)stream, src, R, C, (bf16*)dst, (bf16*)dst_t);
+}
+size_t dtb_colsum_scratch_floats(int N) { return colsum_scratch_floats(N); }
+int dtb_colsum_bf16(void* stream, const void* x, int M, int N, int ld, float* out, int accumulate, float* scratch) {
+  DTB_REQUIRE(x && out && scratch, DTB_ERR_BAD_ARG, "dtb_colsum_bf16: null pointer");
+  return colsum_bf16((cudaStream_t)stream, (const bf16*)x, M, N, ld, out, accumulate, scratch);
+}
+
 }  // extern "C"

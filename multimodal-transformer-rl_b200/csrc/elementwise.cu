@@ -1,0 +1,112 @@
+// HBM-bound helpers: fp32 -> bf16 weight casts (with transpose), bias-gradient column sums.
+#include "kernels.h"
+
+namespace dtb {
+
+// ---- cast + transpose: src fp32 [R, C] -> dst bf16 [R, C], dst_t bf16 [C, R] -------------------
+// 32x32 tiles through shared memory so both the read and the two writes are coalesced.
+__global__ void cast_transpose_kernel(const float* __restrict__ src, int R, int C, bf16* __restrict__ dst, bf16* __restrict__ dst_t) {
+  __shared__ float tile[32][33];
+  const int c0 = blockIdx.x * 32, r0 = blockIdx.y * 32;
+  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+    const int r = r0 + i, c = c0 + threadIdx.x;
+    float v = (r < R && c < C) ? src[(size_t)r * C + c] : 0.f;
+    tile[i][threadIdx.x] = v;
+    if (dst && r < R && c < C) dst[(size_t)r * C + c] = __float2bfloat16(v);
+  }
+  __syncthreads();
+  if (dst_t) {
+    for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+      const int c = c0 + i, r = r0 + threadIdx.x;
+      if (r < R && c < C) dst_t[(size_t)c * R + r] = __float2bfloat16(tile[threadIdx.x][i]);
+    }
+  }
+}
+
+int cast_transpose(cudaStream_t stream, const float* src, int R, int C, bf16* dst, bf16* dst_t) {
+  dim3 grid((C + 31) / 32, (R + 31) / 32), block(32, 8);
+  cast_transpose_kernel<<<grid, block, 0, stream>>>(src, R, C, dst, dst_t);
+  DTB_CHECK_LAUNCH();
+  return DTB_OK;
+}
+
+__global__ void cast_bf16_kernel(const float* __restrict__ src, size_t n, bf16* __restrict__ dst) {
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  const size_t n4 = n / 4;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n4; i += stride) {
+    float4 v = ldg_f4(src + 4 * i);
+    *reinterpret_cast<uint2*>(dst + 4 * i) = make_uint2(pack_bf16x2(v.x, v.y), pack_bf16x2(v.z, v.w));
+  }
+  for (size_t i = n4 * 4 + blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += stride) dst[i] = __float2bfloat16(src[i]);
+}
+
+int cast_bf16(cudaStream_t stream, const float* src, size_t n, bf16* dst) {
+  if (n == 0) return DTB_OK;
+  DTB_REQUIRE((reinterpret_cast<uintptr_t>(src) & 15) == 0 && (reinterpret_cast<uintptr_t>(dst) & 7) == 0, DTB_ERR_BAD_ARG,
+              "cast_bf16: misaligned pointers");
+  int blocks = (int)((n / 4 + 255) / 256);
+  if (blocks > num_sms() * 8) blocks = num_sms() * 8;
+  if (blocks < 1) blocks = 1;
+  cast_bf16_kernel<<<blocks, 256, 0, stream>>>(src, n, dst);
+  DTB_CHECK_LAUNCH();
+  return DTB_OK;
+}
+
+// ---- column sums (bias gradients): x bf16 [M, N] -> out fp32 [N] --------------------------------
+// Stage 1: grid (N/64 column groups, row slabs); each thread owns 2 adjacent columns and strides rows,
+//          then the 8 row-lanes of the block are reduced through shared memory -> scratch[slab][N].
+// Stage 2: sum the slabs in index order (deterministic).
+constexpr int CS_SLABS_MAX = 256;
+
+__global__ void colsum_stage1(const bf16* __restrict__ x, int M, int N, int ld, float* __restrict__ scratch) {
+  __shared__ float2 red[8][32];
+  const int col = blockIdx.x * 64 + threadIdx.x * 2;
+  const int slab = blockIdx.y, nslab = gridDim.y;
+  float2 acc = make_float2(0.f, 0.f);
+  if (col < N) {
+    for (int r = slab * 8 + threadIdx.y; r < M; r += nslab * 8) {
+      uint32_t u = __ldg(reinterpret_cast<const uint32_t*>(x + (size_t)r * ld + col));
+      float2 v = unpack_bf16x2(u);
+      acc.x += v.x;
+      acc.y += v.y;
+    }
+  }
+  red[threadIdx.y][threadIdx.x] = acc;
+  __syncthreads();
+  if (threadIdx.y == 0 && col < N) {
+#pragma unroll
+    for (int i = 1; i < 8; ++i) {
+      acc.x += red[i][threadIdx.x].x;
+      acc.y += red[i][threadIdx.x].y;
+    }
+    scratch[(size_t)slab * N + col] = acc.x;
+    scratch[(size_t)slab * N + col + 1] = acc.y;
+  }
+}
+
+__global__ void colsum_stage2(const float* __restrict__ scratch, int nslab, int N, float* __restrict__ out, int accumulate) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= N) return;
+  float s = 0.f;
+  for (int i = 0; i < nslab; ++i) s += scratch[(size_t)i * N + c];
+  out[c] = accumulate ? out[c] + s : s;
+}
+
+size_t colsum_scratch_floats(int N) { return (size_t)CS_SLABS_MAX * N; }
+
+int colsum_bf16(cudaStream_t stream, const bf16* x, int M, int N, int ld, float* out, int accumulate, float* scratch) {
+  DTB_REQUIRE(N % 2 == 0 && ld % 2 == 0, DTB_ERR_BAD_ARG, "colsum: N and ld must be even");
+  const int colgroups = (N + 63) / 64;
+  int nslab = (4 * num_sms() + colgroups - 1) / colgroups;
+  const int max_slab = (M + 63) / 64;
+  if (nslab > max_slab) nslab = max_slab;
+  if (nslab > CS_SLABS_MAX) nslab = CS_SLABS_MAX;
+  if (nslab < 1) nslab = 1;
+  colsum_stage1<<<dim3(colgroups, nslab), dim3(32, 8), 0, stream>>>(x, M, N, ld, scratch);
+  DTB_CHECK_LAUNCH();
+  colsum_stage2<<<(N + 255) / 256, 256, 0, stream>>>(scratch, nslab, N, out, accumulate);
+  DTB_CHECK_LAUNCH();
+  return DTB_OK;
+}
+
+}  // namespace dtb

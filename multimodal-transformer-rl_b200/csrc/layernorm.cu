@@ -1,0 +1,167 @@
+// LayerNorm forward / backward for the fp32 residual stream (HBM-bound; one warp per token row).
+// Replaces nn.LayerNorm at HF:272 (ln_1), HF:303 (ln_2) and its autograd backward.
+//   fwd : x fp32 [M,H] -> y bf16 [M,H] (GEMM operand), mean/rstd fp32 [M] saved for backward
+//   bwd : dx = dres + LN'(dy) written as fp32 (gradient residual stream) and bf16 (next GEMM operand);
+//         dgamma/dbeta via per-block partials reduced in index order (deterministic).
+#include "kernels.h"
+
+namespace dtb {
+
+constexpr int LN_MAX_VEC = 8;  // H <= 8 * 128 = 1024
+
+__global__ void __launch_bounds__(256) ln_fwd_kernel(const float* __restrict__ x, const float* __restrict__ gamma,
+                                                     const float* __restrict__ beta, int M, int H, float eps, bf16* __restrict__ y,
+                                                     float* __restrict__ mean_out, float* __restrict__ rstd_out) {
+  const int lane = threadIdx.x & 31;
+  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= M) return;
+  const float* xr = x + (size_t)row * H;
+  float4 v[LN_MAX_VEC];
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < LN_MAX_VEC; ++i) {
+    const int c = i * 128 + lane * 4;
+    if (c < H) {
+      v[i] = ldg_f4(xr + c);
+      s += v[i].x + v[i].y + v[i].z + v[i].w;
+    }
+  }
+  const float mean = warp_sum(s) / H;
+  float q = 0.f;
+#pragma unroll
+  for (int i = 0; i < LN_MAX_VEC; ++i) {
+    const int c = i * 128 + lane * 4;
+    if (c < H) {
+      const float a = v[i].x - mean, b = v[i].y - mean, cc = v[i].z - mean, d = v[i].w - mean;
+      q += a * a + b * b + cc * cc + d * d;
+    }
+  }
+  const float rstd = rsqrtf(warp_sum(q) / H + eps);
+  if (lane == 0) {
+    if (mean_out) mean_out[row] = mean;
+    if (rstd_out) rstd_out[row] = rstd;
+  }
+  bf16* yr = y + (size_t)row * H;
+#pragma unroll
+  for (int i = 0; i < LN_MAX_VEC; ++i) {
+    const int c = i * 128 + lane * 4;
+    if (c < H) {
+      const float4 g = ldg_f4(gamma + c), b = ldg_f4(beta + c);
+      const float o0 = (v[i].x - mean) * rstd * g.x + b.x, o1 = (v[i].y - mean) * rstd * g.y + b.y;
+      const float o2 = (v[i].z - mean) * rstd * g.z + b.z, o3 = (v[i].w - mean) * rstd * g.w + b.w;
+      *reinterpret_cast<uint2*>(yr + c) = make_uint2(pack_bf16x2(o0, o1), pack_bf16x2(o2, o3));
+    }
+  }
+}
+
+int ln_fwd(cudaStream_t stream, const float* x, const float* gamma, const float* beta, int M, int H, float eps, bf16* y, float* mean,
+           float* rstd) {
+  DTB_REQUIRE(H % 4 == 0 && H <= LN_MAX_VEC * 128, DTB_ERR_UNSUPPORTED, "layernorm: hidden size %d unsupported (multiple of 4, <= 1024)", H);
+  if (M == 0) return DTB_OK;
+  ln_fwd_kernel<<<(M + 7) / 8, 256, 0, stream>>>(x, gamma, beta, M, H, eps, y, mean, rstd);
+  DTB_CHECK_LAUNCH();
+  return DTB_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) ln_bwd_kernel(const bf16* __restrict__ dy, const float* __restrict__ x,
+                                                     const float* __restrict__ mean, const float* __restrict__ rstd,
+                                                     const float* __restrict__ gamma, const float* __restrict__ dres, int M, int H,
+                                                     float* __restrict__ dx_out, bf16* __restrict__ dx_bf16,
+                                                     float* __restrict__ scratch /* [grid][2][H] */) {
+  extern __shared__ float sred[];  // [2][H]
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
+  float4 dg[LN_MAX_VEC], db[LN_MAX_VEC];
+#pragma unroll
+  for (int i = 0; i < LN_MAX_VEC; ++i) {
+    dg[i] = make_float4(0, 0, 0, 0);
+    db[i] = make_float4(0, 0, 0, 0);
+  }
+  for (int row = blockIdx.x * nwarp + warp; row < M; row += gridDim.x * nwarp) {
+    const float mu = mean[row], rs = rstd[row];
+    const float* xr = x + (size_t)row * H;
+    const bf16* dyr = dy + (size_t)row * H;
+    float4 xh[LN_MAX_VEC];
+    uint2 dyp[LN_MAX_VEC];
+    float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int i = 0; i < LN_MAX_VEC; ++i) {
+      const int c = i * 128 + lane * 4;
+      if (c < H) {
+        const float4 xv = ldg_f4(xr + c);
+        const float4 gm = ldg_f4(gamma + c);
+        dyp[i] = __ldg(reinterpret_cast<const uint2*>(dyr + c));
+        const float2 d01 = unpack_bf16x2(dyp[i].x), d23 = unpack_bf16x2(dyp[i].y);
+        xh[i] = make_float4((xv.x - mu) * rs, (xv.y - mu) * rs, (xv.z - mu) * rs, (xv.w - mu) * rs);
+        const float g0 = d01.x * gm.x, g1 = d01.y * gm.y, g2 = d23.x * gm.z, g3 = d23.y * gm.w;
+        s1 += g0 + g1 + g2 + g3;
+        s2 += g0 * xh[i].x + g1 * xh[i].y + g2 * xh[i].z + g3 * xh[i].w;
+        dg[i].x += d01.x * xh[i].x; dg[i].y += d01.y * xh[i].y; dg[i].z += d23.x * xh[i].z; dg[i].w += d23.y * xh[i].w;
+        db[i].x += d01.x; db[i].y += d01.y; db[i].z += d23.x; db[i].w += d23.y;
+      }
+    }
+    const float c1 = warp_sum(s1) / H, c2 = warp_sum(s2) / H;
+#pragma unroll
+    for (int i = 0; i < LN_MAX_VEC; ++i) {
+      const int c = i * 128 + lane * 4;
+      if (c < H) {
+        const float4 gm = ldg_f4(gamma + c);
+        const float2 d01 = unpack_bf16x2(dyp[i].x), d23 = unpack_bf16x2(dyp[i].y);
+        float4 o = make_float4(rs * (d01.x * gm.x - c1 - xh[i].x * c2), rs * (d01.y * gm.y - c1 - xh[i].y * c2),
+                               rs * (d23.x * gm.z - c1 - xh[i].z * c2), rs * (d23.y * gm.w - c1 - xh[i].w * c2));
+        if (dres) {
+          const float4 r = ldg_f4(dres + (size_t)row * H + c);
+          o.x += r.x; o.y += r.y; o.z += r.z; o.w += r.w;
+        }
+        if (dx_out) *reinterpret_cast<float4*>(dx_out + (size_t)row * H + c) = o;
+        if (dx_bf16) *reinterpret_cast<uint2*>(dx_bf16 + (size_t)row * H + c) = make_uint2(pack_bf16x2(o.x, o.y), pack_bf16x2(o.z, o.w));
+      }
+    }
+  }
+  // deterministic cross-warp reduction of the dgamma / dbeta partials
+  for (int i = threadIdx.x; i < 2 * H; i += blockDim.x) sred[i] = 0.f;
+  __syncthreads();
+  for (int w = 0; w < nwarp; ++w) {
+    if (warp == w) {
+#pragma unroll
+      for (int i = 0; i < LN_MAX_VEC; ++i) {
+        const int c = i * 128 + lane * 4;
+        if (c < H) {
+          sred[c] += dg[i].x; sred[c + 1] += dg[i].y; sred[c + 2] += dg[i].z; sred[c + 3] += dg[i].w;
+          sred[H + c] += db[i].x; sred[H + c + 1] += db[i].y; sred[H + c + 2] += db[i].z; sred[H + c + 3] += db[i].w;
+        }
+      }
+    }
+    __syncthreads();
+  }
+  for (int i = threadIdx.x; i < 2 * H; i += blockDim.x) scratch[(size_t)blockIdx.x * 2 * H + i] = sred[i];
+}
+
+__global__ void ln_bwd_finalize(const float* __restrict__ scratch, int nblk, int H, float* __restrict__ dgamma, float* __restrict__ dbeta) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= 2 * H) return;
+  float s = 0.f;
+  for (int b = 0; b < nblk; ++b) s += scratch[(size_t)b * 2 * H + c];
+  if (c < H) dgamma[c] = s;
+  else dbeta[c - H] = s;
+}
+
+static int ln_bwd_blocks(int M) {
+  int b = (M + 7) / 8;
+  const int cap = num_sms() * 4;
+  return b > cap ? cap : (b < 1 ? 1 : b);
+}
+size_t ln_bwd_scratch_floats(int H) { return (size_t)DTB_NUM_SMS_FALLBACK * 8 * 2 * H; }
+
+int ln_bwd(cudaStream_t stream, const bf16* dy, const float* x, const float* mean, const float* rstd, const float* gamma,
+           const float* dres, int M, int H, float* dx_out, bf16* dx_out_bf16, float* dgamma, float* dbeta, float* scratch) {
+  DTB_REQUIRE(H % 4 == 0 && H <= LN_MAX_VEC * 128, DTB_ERR_UNSUPPORTED, "layernorm bwd: hidden size %d unsupported", H);
+  const int blocks = ln_bwd_blocks(M);
+  ln_bwd_kernel<<<blocks, 256, 2 * H * sizeof(float), stream>>>(dy, x, mean, rstd, gamma, dres, M, H, dx_out, dx_out_bf16, scratch);
+  DTB_CHECK_LAUNCH();
+  ln_bwd_finalize<<<(2 * H + 255) / 256, 256, 0, stream>>>(scratch, blocks, H, dgamma, dbeta);
+  DTB_CHECK_LAUNCH();
+  return DTB_OK;
+}
+
+}  // namespace dtb

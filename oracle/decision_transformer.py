@@ -209,7 +209,7 @@ class DecisionTransformer(nn.Module):
                 k2 = "transformer." + k[len("encoder."):]
             else:
                 k2 = k
-            if any(t in k2 for t in (".wte.", ".wpe.", "attn.bias", "attn.masked_bias")):
+            if ".wte." in k2 or ".wpe." in k2 or k2.endswith(".attn.bias") or k2.endswith(".attn.masked_bias"):
                 continue
             out[k2] = v
         missing, unexpected = self.load_state_dict(out, strict=False)
