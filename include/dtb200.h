@@ -94,6 +94,79 @@ int dtb_cast_transpose(void* stream, const float* src, int R, int C, void* dst, 
 size_t dtb_colsum_scratch_floats(int N);
 int dtb_colsum_bf16(void* stream, const void* x, int M, int N, int ld, float* out, int accumulate, float* scratch);
 
+/* ---- fused token embedding (HF:611-628): timestep gather + RTG/state/action projections + interleave + embed_ln -----
+ * x fp32 [B*K*3, H] in token order R_k, s_k, a_k.  Exactly one of states (fp32 [BK, sd], sd <= 64) / state_proj
+ * (fp32 [BK, H], the tensor-core projection of a wide multimodal state, no bias) is given.  pre / mean / rstd / U are the
+ * optional training saves (U = bf16 [BK, P8] packed [rtg | actions | states]). */
+int dtb_embed_fwd(void* stream, const float* states, const float* state_proj, const float* actions, const float* rtg,
+                  const long long* timesteps, const float* table, const float* wR, const float* bR, const float* Ws, const float* bs,
+                  const float* Wa, const float* ba, const float* gamma, const float* beta, int BK, int sd, int ad, int H, int E,
+                  float eps, float* x, float* pre, float* mean, float* rstd, void* U, int P8, int u_states);
+
+/* ---- prediction heads + masked action MSE (HF:650-655; upstream SequenceTrainer.train_step loss) -------------------- */
+int dtb_heads_fwd(void* stream, const void* y_bf16, const float* Wa, const float* ba, const float* Ws, const float* bs,
+                  const float* Wr, const float* br, int BK, int H, int sd, int ad, int action_tanh, float* action_preds,
+                  float* state_preds, float* return_preds);
+size_t dtb_mse_scratch_floats(void);
+/* loss_out[0] = mean((pred-target)^2) over rows with mask > 0, loss_out[1] = #valid rows; d_pred (nullable) = grad_scale * dloss/dpred */
+int dtb_masked_mse(void* stream, const float* pred, const float* target, const float* mask, int BK, int ad, float grad_scale,
+                   float* loss_out, float* d_pred, float* scratch);
+
+/* ---- whole-model Decision Transformer (A1-A10) -----------------------------------------------------------------------
+ * Mirrors DecisionTransformer(state_dim, act_dim, hidden_size, max_length, max_ep_len, action_tanh, n_layer, n_head,
+ * n_inner, activation_function) — HF:510-533 / upstream decision_transformer.py.  Parameters live in ONE flat fp32
+ * buffer owned by the caller (layout from dtb_dt_param_layout, each tensor padded to 8 elements), with a bf16 shadow
+ * of the same layout refreshed by dtb_dt_stage_params after every optimizer step; gradients go to a flat fp32 buffer
+ * of the same layout.  Activations saved for backward live in a caller-owned workspace (dtb_dt_workspace_bytes). */
+typedef struct {
+  int state_dim, act_dim, hidden, n_layer, n_head, n_inner, max_ep_len;
+  int activation;  /* 1 relu, 2 gelu_new */
+  int action_tanh; /* HF:527-529 */
+  float ln_eps;
+} dtb_dt_config;
+
+typedef struct {
+  int B, K;
+  const float* states;          /* fp32 [B,K,sd], or NULL when states_bf16 is given */
+  const void* states_bf16;      /* bf16 [B,K,sd] (sd % 8 == 0): wide multimodal state straight from the encoder towers */
+  const float* actions;         /* fp32 [B,K,ad] */
+  const float* returns_to_go;   /* fp32 [B,K] */
+  const long long* timesteps;   /* int64 [B,K] */
+  const float* attention_mask;  /* fp32 [B,K] (> 0 = valid) or NULL = all valid (HF:606-608) */
+} dtb_dt_batch;
+
+typedef struct dtb_dt dtb_dt;
+
+int dtb_dt_create(const dtb_dt_config* cfg, dtb_dt** out);
+int dtb_dt_destroy(dtb_dt* h);
+/* Number of parameter tensors (9 + 12 * n_layer + 8) in flat order:
+ *  embed_timestep.weight, embed_return.{weight,bias}, embed_state.{weight,bias}, embed_action.{weight,bias}, embed_ln.{weight,bias},
+ *  per layer: ln_1.{w,b}, attn.c_attn.{w,b}, attn.c_proj.{w,b}, ln_2.{w,b}, mlp.c_fc.{w,b}, mlp.c_proj.{w,b},
+ *  ln_f.{w,b}, predict_state.weight, predict_return.weight, predict_action.weight, predict_state.bias, predict_return.bias,
+ *  predict_action.bias */
+int dtb_dt_param_entries(const dtb_dt* h);
+/* Fills offsets[i], numels[i] (element counts, fp32) and returns the padded total element count. */
+long long dtb_dt_param_layout(const dtb_dt* h, long long* offsets, long long* numels);
+size_t dtb_dt_workspace_bytes(const dtb_dt* h, int B, int K);
+/* fp32 master -> bf16 shadow (one pass over the flat buffer). */
+int dtb_dt_stage_params(const dtb_dt* h, void* stream, const float* params, void* params_bf16);
+/* forward (HF:536-657).  state_preds / return_preds may be NULL (the loss never reads them, A8). */
+int dtb_dt_forward(const dtb_dt* h, void* stream, const float* params, const void* params_bf16, const dtb_dt_batch* batch,
+                   void* workspace, size_t workspace_bytes, float* action_preds, float* state_preds, float* return_preds);
+/* masked action MSE on the action_preds of the last forward (kept in the workspace); writes loss_out[2] and the loss
+ * gradient (scaled by grad_scale, e.g. 1/world_size) into the workspace for dtb_dt_backward(d_action_preds = NULL). */
+int dtb_dt_loss(const dtb_dt* h, void* stream, const dtb_dt_batch* batch, const float* action_target, float grad_scale, void* workspace,
+                size_t workspace_bytes, float* loss_out);
+/* backward.  d_action_preds NULL = use the gradient dtb_dt_loss left in the workspace; d_state_preds / d_return_preds may be
+ * NULL (zero).  Overwrites the gradients of the stages it runs.  Stages: 0 = ln_f + heads, 1..L = blocks L-1..0, L+1 = embedding;
+ * [stage_begin, stage_end] inclusive lets a data-parallel host all-reduce finished stages while earlier layers still run.
+ * d_states_bf16 (nullable): bf16 [B,K,sd] gradient w.r.t. a wide state (states_bf16 path) for the encoder towers. */
+int dtb_dt_backward(const dtb_dt* h, void* stream, const float* params, const void* params_bf16, const dtb_dt_batch* batch,
+                    void* workspace, size_t workspace_bytes, const float* d_action_preds, const float* d_state_preds,
+                    const float* d_return_preds, float* grads, void* d_states_bf16, int stage_begin, int stage_end);
+/* [begin, end) element range of the flat gradient buffer written by a backward stage. */
+int dtb_dt_stage_grad_range(const dtb_dt* h, int stage, long long* begin, long long* end);
+
 #ifdef __cplusplus
 }
 #endif

@@ -23,6 +23,40 @@ class GemmEpilogue(C.Structure):
     ]
 
 
+class DtConfig(C.Structure):
+    _fields_ = [("state_dim", C.c_int), ("act_dim", C.c_int), ("hidden", C.c_int), ("n_layer", C.c_int), ("n_head", C.c_int),
+                ("n_inner", C.c_int), ("max_ep_len", C.c_int), ("activation", C.c_int), ("action_tanh", C.c_int), ("ln_eps", C.c_float)]
+
+
+class DtBatch(C.Structure):
+    _fields_ = [("B", C.c_int), ("K", C.c_int), ("states", C.c_void_p), ("states_bf16", C.c_void_p), ("actions", C.c_void_p),
+                ("returns_to_go", C.c_void_p), ("timesteps", C.c_void_p), ("attention_mask", C.c_void_p)]
+
+
+def _declare(lib):
+    """restype / argtypes for the entry points whose defaults (int) would truncate pointers or sizes."""
+    vp, i, f, sz, ll = C.c_void_p, C.c_int, C.c_float, C.c_size_t, C.c_longlong
+    lib.dtb_last_error.restype = C.c_char_p
+    lib.dtb_abi_version.restype = i
+    for name in ("dtb_layernorm_bwd_scratch_floats", "dtb_colsum_scratch_floats", "dtb_mse_scratch_floats"):
+        getattr(lib, name).restype = sz
+    lib.dtb_dt_create.argtypes = [C.POINTER(DtConfig), C.POINTER(vp)]
+    lib.dtb_dt_destroy.argtypes = [vp]
+    lib.dtb_dt_param_entries.argtypes = [vp]
+    lib.dtb_dt_param_layout.argtypes = [vp, C.POINTER(ll), C.POINTER(ll)]
+    lib.dtb_dt_param_layout.restype = ll
+    lib.dtb_dt_workspace_bytes.argtypes = [vp, i, i]
+    lib.dtb_dt_workspace_bytes.restype = sz
+    lib.dtb_dt_stage_params.argtypes = [vp, vp, vp, vp]
+    lib.dtb_dt_forward.argtypes = [vp, vp, vp, vp, C.POINTER(DtBatch), vp, sz, vp, vp, vp]
+    lib.dtb_dt_loss.argtypes = [vp, vp, C.POINTER(DtBatch), vp, f, vp, sz, vp]
+    lib.dtb_dt_backward.argtypes = [vp, vp, vp, vp, C.POINTER(DtBatch), vp, sz, vp, vp, vp, vp, vp, i, i]
+    lib.dtb_dt_stage_grad_range.argtypes = [vp, i, C.POINTER(ll), C.POINTER(ll)]
+    lib.dtb_masked_mse.argtypes = [vp, vp, vp, vp, i, i, f, vp, vp, vp]
+    lib.dtb_heads_fwd.argtypes = [vp] * 8 + [i] * 5 + [vp] * 3
+    lib.dtb_embed_fwd.argtypes = [vp] * 15 + [i] * 5 + [f] + [vp] * 5 + [i, i]
+
+
 def load() -> C.CDLL:
     """Load libdtb200.so; raise if it has not been built (no fallback path exists)."""
     global _lib
@@ -34,8 +68,7 @@ def load() -> C.CDLL:
             "(the sm_100a CUDA extension is the only implementation; there is no CPU/PyTorch fallback)"
         )
     lib = C.CDLL(LIB_PATH)
-    lib.dtb_last_error.restype = C.c_char_p
-    lib.dtb_abi_version.restype = C.c_int
+    _declare(lib)
     _lib = lib
     return lib
 
@@ -137,3 +170,32 @@ def colsum_bf16(x, out, accumulate=False):
     lib.dtb_colsum_scratch_floats.restype = C.c_size_t
     scratch = torch.empty(lib.dtb_colsum_scratch_floats(N), device=x.device, dtype=torch.float32)
     check(lib.dtb_colsum_bf16(stream_ptr(), ptr(x), M, N, x.stride(0), ptr(out), int(accumulate), ptr(scratch)))
+
+
+def embed_fwd(states, state_proj, actions, rtg, timesteps, table, wR, bR, Ws, bs, Wa, ba, gamma, beta, eps, x, pre=None, mean=None,
+              rstd=None, U=None, u_states=True):
+    BK, ad = actions.shape
+    H = table.shape[1]
+    sd = Ws.shape[1]
+    P8 = U.shape[1] if U is not None else 0
+    check(load().dtb_embed_fwd(stream_ptr(), ptr(states), ptr(state_proj), ptr(actions), ptr(rtg), ptr(timesteps), ptr(table), ptr(wR),
+                               ptr(bR), ptr(Ws), ptr(bs), ptr(Wa), ptr(ba), ptr(gamma), ptr(beta), BK, sd, ad, H, table.shape[0],
+                               float(eps), ptr(x), ptr(pre), ptr(mean), ptr(rstd), ptr(U), P8, int(u_states)))
+
+
+def heads_fwd(y, Wa, ba, Ws, bs, Wr, br, action_tanh, action_preds, state_preds=None, return_preds=None):
+    BK, ad = action_preds.shape
+    H = y.shape[1]
+    sd = Ws.shape[0] if Ws is not None else 0
+    check(load().dtb_heads_fwd(stream_ptr(), ptr(y), ptr(Wa), ptr(ba), ptr(Ws), ptr(bs), ptr(Wr), ptr(br), BK, H, sd, ad, int(action_tanh),
+                               ptr(action_preds), ptr(state_preds), ptr(return_preds)))
+
+
+def masked_mse(pred, target, mask, grad_scale, loss_out, d_pred=None):
+    import torch
+
+    BK, ad = pred.shape
+    lib = load()
+    scratch = torch.empty(lib.dtb_mse_scratch_floats(), device=pred.device, dtype=torch.float32)
+    check(lib.dtb_masked_mse(stream_ptr(), ptr(pred), ptr(target), ptr(mask), BK, ad, float(grad_scale), ptr(loss_out), ptr(d_pred),
+                             ptr(scratch)))

@@ -80,4 +80,28 @@ int dtb_colsum_bf16(void* stream, const void* x, int M, int N, int ld, float* ou
   return colsum_bf16((cudaStream_t)stream, (const bf16*)x, M, N, ld, out, accumulate, scratch);
 }
 
+int dtb_embed_fwd(void* stream, const float* states, const float* state_proj, const float* actions, const float* rtg,
+                  const long long* timesteps, const float* table, const float* wR, const float* bR, const float* Ws, const float* bs,
+                  const float* Wa, const float* ba, const float* gamma, const float* beta, int BK, int sd, int ad, int H, int E,
+                  float eps, float* x, float* pre, float* mean, float* rstd, void* U, int P8, int u_states) {
+  DTB_REQUIRE(actions && rtg && timesteps && table && wR && bR && Ws && bs && Wa && ba && gamma && beta && x, DTB_ERR_BAD_ARG,
+              "dtb_embed_fwd: null pointer");
+  return embed_fwd((cudaStream_t)stream, states, state_proj, actions, rtg, timesteps, table, wR, bR, Ws, bs, Wa, ba, gamma, beta, BK, sd,
+                   ad, H, E, eps, x, pre, mean, rstd, (bf16*)U, P8, u_states);
+}
+int dtb_heads_fwd(void* stream, const void* y, const float* Wa, const float* ba, const float* Ws, const float* bs, const float* Wr,
+                  const float* br, int BK, int H, int sd, int ad, int action_tanh, float* action_preds, float* state_preds,
+                  float* return_preds) {
+  DTB_REQUIRE(y && Wa && ba && action_preds, DTB_ERR_BAD_ARG, "dtb_heads_fwd: null pointer");
+  DTB_REQUIRE((!state_preds || (Ws && bs)) && (!return_preds || (Wr && br)), DTB_ERR_BAD_ARG, "dtb_heads_fwd: missing head weights");
+  return heads_fwd((cudaStream_t)stream, (const bf16*)y, Wa, ba, Ws, bs, Wr, br, BK, H, sd, ad, action_tanh, action_preds, state_preds,
+                   return_preds);
+}
+size_t dtb_mse_scratch_floats(void) { return mse_scratch_floats(); }
+int dtb_masked_mse(void* stream, const float* pred, const float* target, const float* mask, int BK, int ad, float grad_scale,
+                   float* loss_out, float* d_pred, float* scratch) {
+  DTB_REQUIRE(pred && target && loss_out && scratch, DTB_ERR_BAD_ARG, "dtb_masked_mse: null pointer");
+  return mse_loss((cudaStream_t)stream, pred, target, mask, BK, ad, grad_scale, loss_out, d_pred, scratch);
+}
+
 }  // extern "C"

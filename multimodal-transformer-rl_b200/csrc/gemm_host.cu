@@ -96,7 +96,7 @@ int gemm_pick_split(int M, int N, int K, int BN) {
   return split;
 }
 
-static int pick_bn(int M, int N, int b_mn_major) {
+int gemm_pick_bn(int M, int N, int b_mn_major) {
   const int m_tiles = (M + GEMM_BM - 1) / GEMM_BM;
   const int cands[4] = {256, 128, 64, 32};
   int best = -1;
@@ -122,7 +122,7 @@ int gemm_bf16(cudaStream_t stream, const bf16* A, int lda, int a_mn_major, const
   memset(&p, 0, sizeof(p));
   p.M = M; p.N = N; p.K = K;
   p.a_mn_major = a_mn_major; p.b_mn_major = b_mn_major;
-  p.BN = bn_override > 0 ? bn_override : pick_bn(M, N, b_mn_major);
+  p.BN = bn_override > 0 ? bn_override : gemm_pick_bn(M, N, b_mn_major);
   DTB_REQUIRE(p.BN % 32 == 0 && p.BN >= 32 && p.BN <= 256 && (!b_mn_major || p.BN % 64 == 0), DTB_ERR_BAD_ARG, "gemm: bad BN %d", p.BN);
   p.m_tiles = (M + GEMM_BM - 1) / GEMM_BM;
   p.n_tiles = (N + p.BN - 1) / p.BN;
@@ -180,6 +180,34 @@ int splitk_reduce(cudaStream_t stream, const float* partial, int splits, int M, 
   splitk_reduce_kernel<<<blocks, 256, 0, stream>>>(partial, splits, M, N, out, ldo, accumulate, scale);
   DTB_CHECK_LAUNCH();
   return DTB_OK;
+}
+
+// Weight gradient dW[Mout, Nout] = A^T B with both operands read in place (MN-major): A memory [Kred][Mout] (lda),
+// B memory [Kred][Nout] (ldb).  Split-K over the token dimension with fp32 partials reduced in index order (deterministic).
+int gemm_wgrad_split(int Mout, int Nout, int Kred, size_t partial_floats) {
+  const int bn = gemm_pick_bn(Mout, Nout, 1);
+  int split = gemm_pick_split(Mout, Nout, Kred, bn);
+  const size_t per = (size_t)Mout * Nout;
+  while (split > 1 && per * split > partial_floats) --split;
+  return split;
+}
+
+int gemm_wgrad(cudaStream_t stream, const bf16* A, int lda, const bf16* B, int ldb, int Mout, int Nout, int Kred, float* out, int ldo,
+               float* partial, size_t partial_floats) {
+  const int split = gemm_wgrad_split(Mout, Nout, Kred, partial_floats);
+  GemmEpilogue ep;
+  memset(&ep, 0, sizeof(ep));
+  ep.alpha = 1.f;
+  if (split <= 1) {
+    ep.out_f32 = out;
+    ep.ldo_f = ldo;
+    const int rc = gemm_bf16(stream, A, lda, 1, B, ldb, 1, Mout, Nout, Kred, ep, 1, 0);
+    return rc < 0 ? rc : DTB_OK;
+  }
+  ep.partial = partial;
+  const int rc = gemm_bf16(stream, A, lda, 1, B, ldb, 1, Mout, Nout, Kred, ep, split, 0);
+  if (rc < 0) return rc;
+  return splitk_reduce(stream, partial, rc, Mout, Nout, out, ldo, 0, 1.f);
 }
 
 }  // namespace dtb

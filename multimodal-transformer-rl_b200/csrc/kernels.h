@@ -37,6 +37,10 @@ struct GemmParams {
 int gemm_bf16(cudaStream_t stream, const bf16* A, int lda, int a_mn_major, const bf16* B, int ldb, int b_mn_major, int M, int N, int K,
               const GemmEpilogue& ep, int split_k, int bn_override);
 int gemm_pick_split(int M, int N, int K, int BN);
+int gemm_pick_bn(int M, int N, int b_mn_major);
+int gemm_wgrad_split(int Mout, int Nout, int Kred, size_t partial_floats);
+int gemm_wgrad(cudaStream_t stream, const bf16* A, int lda, const bf16* B, int ldb, int Mout, int Nout, int Kred, float* out, int ldo,
+               float* partial, size_t partial_floats);
 int splitk_reduce(cudaStream_t stream, const float* partial, int splits, int M, int N, float* out, int ldo, int accumulate, float scale);
 
 // ---- elementwise.cu ----------------------------------------------------------------------------
@@ -60,5 +64,26 @@ size_t ln_bwd_scratch_floats(int H);
 int attn_fwd(cudaStream_t stream, const bf16* qkv, const float* mask, int B, int T, int nh, int d, bf16* out, float* lse);
 int attn_bwd(cudaStream_t stream, const bf16* qkv, const float* mask, const bf16* out, const bf16* dout, const float* lse, int B, int T,
              int nh, int d, bf16* dqkv, float* delta);
+
+// ---- embed.cu ----------------------------------------------------------------------------------
+int embed_fwd(cudaStream_t stream, const float* states, const float* state_proj, const float* actions, const float* rtg,
+              const long long* timesteps, const float* table, const float* wR, const float* bR, const float* Ws, const float* bs,
+              const float* Wa, const float* ba, const float* gamma, const float* beta, int BK, int sd, int ad, int H, int E, float eps,
+              float* x, float* pre, float* mean, float* rstd, bf16* U, int P8, int u_states);
+int embed_te_scatter(cudaStream_t stream, const bf16* d_pre, const long long* timesteps, int BK, int H, int E, float* d_table);
+int embed_unpack(cudaStream_t stream, const float* G, const float* bsum, int H, int sd, int ad, int P8, int u_states, float* dwR,
+                 float* dbR, float* dWs, float* dbs, float* dWa, float* dba);
+
+// ---- heads.cu ----------------------------------------------------------------------------------
+int heads_fwd(cudaStream_t stream, const bf16* y, const float* Wa, const float* ba, const float* Ws, const float* bs, const float* Wr,
+              const float* br, int BK, int H, int sd, int ad, int tanh_act, float* action_preds, float* state_preds,
+              float* return_preds);
+size_t mse_scratch_floats();
+int mse_loss(cudaStream_t stream, const float* pred, const float* target, const float* mask, int BK, int ad, float grad_scale,
+             float* loss_out, float* d_pred, float* scratch);
+int heads_bwd(cudaStream_t stream, const float* d_action, const float* d_state, const float* d_return, const float* action_preds,
+              const float* Wa, const float* Ws, const float* Wr, int BK, int H, int sd, int ad, int tanh_act, int ZA8, int ZS8, bf16* dy,
+              bf16* dzA, bf16* dzS);
+int copy2d(cudaStream_t stream, const float* src, int lds, int R, int C, float* dst, int ldd);
 
 }  // namespace dtb

@@ -1,0 +1,390 @@
+"""Host-side mirror of the reference ``DecisionTransformer`` over the sm_100a kernels.
+
+API kept from the reference (kzl decision-transformer, restated by HF ``modeling_decision_transformer.py:502-666``):
+``DecisionTransformer(state_dim, act_dim, hidden_size, max_length, max_ep_len, action_tanh, **gpt2_kwargs)``,
+``.forward(states, actions, rewards, returns_to_go, timesteps, attention_mask) -> (state_preds, action_preds, return_preds)``,
+``.get_action(states, actions, rewards, returns_to_go, timesteps)``, ``state_dict`` keys of the upstream model
+(``transformer.h.{i}...``; HF's ``encoder.*`` prefix is accepted on load).
+
+All parameters are views into ONE flat fp32 buffer (layout defined by ``dtb_dt_param_layout``) with a bf16 shadow the
+tensor-core GEMMs read and a flat gradient buffer the backward writes — the reference's "flatten all grads"
+data-parallel idiom (``cleanrl/ppo_atari_multigpu.py:345-359``) without the copies.  Compute is only ever done by
+``libdtb200.so``; there is no PyTorch/CPU fallback (calling ``forward`` on a CPU tensor raises).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import warnings
+
+import torch
+import torch.nn as nn
+
+from . import _lib
+
+_ACT = {"relu": 1, "gelu_new": 2, "gelu_tanh": 2, "gelu_pytorch_tanh": 2}
+
+
+def _entry_names(n_layer: int):
+    names = ["embed_timestep.weight", "embed_return.weight", "embed_return.bias", "embed_state.weight", "embed_state.bias",
+             "embed_action.weight", "embed_action.bias", "embed_ln.weight", "embed_ln.bias"]
+    for i in range(n_layer):
+        p = f"transformer.h.{i}."
+        names += [p + "ln_1.weight", p + "ln_1.bias", p + "attn.c_attn.weight", p + "attn.c_attn.bias", p + "attn.c_proj.weight",
+                  p + "attn.c_proj.bias", p + "ln_2.weight", p + "ln_2.bias", p + "mlp.c_fc.weight", p + "mlp.c_fc.bias",
+                  p + "mlp.c_proj.weight", p + "mlp.c_proj.bias"]
+    names += ["transformer.ln_f.weight", "transformer.ln_f.bias", "predict_state.weight", "predict_return.weight",
+              "predict_action.0.weight", "predict_state.bias", "predict_return.bias", "predict_action.0.bias"]
+    return names
+
+
+def _entry_shapes(sd, ad, H, I, E, n_layer):
+    shapes = [(E, H), (H, 1), (H,), (H, sd), (H,), (H, ad), (H,), (H,), (H,)]
+    for _ in range(n_layer):
+        shapes += [(H,), (H,), (H, 3 * H), (3 * H,), (H, H), (H,), (H,), (H,), (H, I), (I,), (I, H), (H,)]
+    shapes += [(H,), (H,), (sd, H), (1, H), (ad, H), (sd,), (1,), (ad,)]
+    return shapes
+
+
+class _Node(nn.Module):
+    """Parameter container used to reproduce the reference's dotted state_dict names."""
+
+
+def _set_nested(root: nn.Module, dotted: str, param: nn.Parameter):
+    parts = dotted.split(".")
+    mod = root
+    for p in parts[:-1]:
+        if p not in mod._modules:
+            mod.add_module(p, _Node())
+        mod = mod._modules[p]
+    mod.register_parameter(parts[-1], param)
+
+
+class DecisionTransformer(nn.Module):
+    def __init__(self, state_dim, act_dim, hidden_size, max_length=None, max_ep_len=4096, action_tanh=True, n_layer=3, n_head=1,
+                 n_inner=None, activation_function="relu", n_positions=1024, resid_pdrop=0.1, attn_pdrop=0.1, embd_pdrop=None,
+                 layer_norm_epsilon=1e-5, device=None, **unused):
+        super().__init__()
+        if activation_function not in _ACT:
+            raise ValueError(f"unsupported activation_function {activation_function!r} (relu | gelu_new)")
+        self.state_dim, self.act_dim, self.hidden_size = int(state_dim), int(act_dim), int(hidden_size)
+        self.max_length, self.max_ep_len, self.action_tanh = max_length, int(max_ep_len), bool(action_tanh)
+        n_inner = int(n_inner) if n_inner is not None else 4 * self.hidden_size
+        self.config = dict(state_dim=self.state_dim, act_dim=self.act_dim, hidden_size=self.hidden_size, max_length=max_length,
+                           max_ep_len=self.max_ep_len, action_tanh=self.action_tanh, n_layer=int(n_layer), n_head=int(n_head),
+                           n_inner=n_inner, activation_function=activation_function, resid_pdrop=resid_pdrop, attn_pdrop=attn_pdrop,
+                           layer_norm_epsilon=layer_norm_epsilon)
+        self._pdrop = max(float(resid_pdrop or 0.0), float(attn_pdrop or 0.0), float(embd_pdrop or 0.0))
+        self._warned_dropout = False
+
+        lib = _lib.load()  # raises when libdtb200.so is missing: there is no other implementation
+        cfg = _lib.DtConfig(self.state_dim, self.act_dim, self.hidden_size, int(n_layer), int(n_head), n_inner, self.max_ep_len,
+                            _ACT[activation_function], int(self.action_tanh), float(layer_norm_epsilon))
+        handle = C.c_void_p()
+        _lib.check(lib.dtb_dt_create(C.byref(cfg), C.byref(handle)))
+        self._h = handle
+        n = lib.dtb_dt_param_entries(self._h)
+        offs, nums = (C.c_longlong * n)(), (C.c_longlong * n)()
+        self._total = int(lib.dtb_dt_param_layout(self._h, offs, nums))
+        self._names = _entry_names(int(n_layer))
+        self._shapes = _entry_shapes(self.state_dim, self.act_dim, self.hidden_size, n_inner, self.max_ep_len, int(n_layer))
+        assert len(self._names) == n == len(self._shapes)
+        self._offsets = [int(o) for o in offs]
+        for shp, num in zip(self._shapes, nums):
+            assert int(torch.Size(shp).numel()) == int(num), (shp, num)
+
+        if device is None:
+            device = "cuda" if torch.cuda.is_available() else "cpu"
+        self._flat = torch.zeros(self._total, dtype=torch.float32, device=device)
+        self._flat_grad = None
+        self._flat_bf16 = None
+        self._staged_version = -1
+        self._ws = {}
+        self._ws_gen = 0
+        self._bind_views(register=True)
+        self.reset_parameters()
+
+    # ---- parameter plumbing --------------------------------------------------------------------------------------
+    def _bind_views(self, register: bool):
+        for name, shp, off in zip(self._names, self._shapes, self._offsets):
+            view = self._flat[off:off + torch.Size(shp).numel()].view(shp)
+            if register:
+                _set_nested(self, name, nn.Parameter(view))
+            else:
+                self.get_parameter(name).data = view
+        self._staged_version = -1
+
+    def _apply(self, fn, recurse=True):
+        # .to()/.cuda() rebuild every Parameter separately; gather them back into one flat buffer afterwards
+        super()._apply(fn, recurse)
+        ref = self.get_parameter(self._names[0])
+        flat = torch.zeros(self._total, dtype=torch.float32, device=ref.device)
+        for name, shp, off in zip(self._names, self._shapes, self._offsets):
+            flat[off:off + torch.Size(shp).numel()].view(shp).copy_(self.get_parameter(name).data.float())
+        self._flat = flat
+        self._flat_grad, self._flat_bf16, self._ws = None, None, {}
+        self._bind_views(register=False)
+        return self
+
+    @torch.no_grad()
+    def reset_parameters(self):
+        """GPT-2 style init (HF:327-341): N(0, 0.02), c_proj scaled by 1/sqrt(2L), LayerNorm (1, 0), zero biases."""
+        L = self.config["n_layer"]
+        for name, p in self.named_parameters():
+            if name.endswith(".bias"):
+                p.zero_()
+            elif "ln_" in name or "embed_ln" in name:
+                p.fill_(1.0)
+            elif name.endswith("c_proj.weight"):
+                p.normal_(0.0, 0.02 / (2 * L) ** 0.5)
+            else:
+                p.normal_(0.0, 0.02)
+
+    def load_state_dict(self, state_dict, strict=True, assign=False):
+        """Accepts upstream (``transformer.*``) and HF (``encoder.*``) keys; wte / wpe / attn.bias buffers are ignored (A1)."""
+        sd = {}
+        for k, v in state_dict.items():
+            k2 = "transformer." + k[len("encoder."):] if k.startswith("encoder.") else k
+            if ".wte." in k2 or ".wpe." in k2 or k2.endswith(".attn.bias") or k2.endswith(".attn.masked_bias"):
+                continue
+            sd[k2] = v
+        out = super().load_state_dict(sd, strict=strict, assign=False)
+        self._staged_version = -1
+        return out
+
+    @property
+    def flat_params(self) -> torch.Tensor:
+        return self._flat
+
+    @property
+    def flat_grads(self) -> torch.Tensor:
+        """Flat fp32 gradient buffer (same layout as flat_params); every ``param.grad`` is a view into it."""
+        if self._flat_grad is None or self._flat_grad.device != self._flat.device:
+            self._flat_grad = torch.zeros_like(self._flat)
+        return self._flat_grad
+
+    def attach_grads(self):
+        g = self.flat_grads
+        for name, shp, off in zip(self._names, self._shapes, self._offsets):
+            p = self.get_parameter(name)
+            view = g[off:off + torch.Size(shp).numel()].view(shp)
+            if p.grad is None or p.grad.data_ptr() != view.data_ptr():
+                p.grad = view
+        return g
+
+    def stage_grad_range(self, stage: int):
+        b, e = C.c_longlong(), C.c_longlong()
+        _lib.check(_lib.load().dtb_dt_stage_grad_range(self._h, stage, C.byref(b), C.byref(e)))
+        return int(b.value), int(e.value)
+
+    @property
+    def n_stages(self) -> int:
+        return self.config["n_layer"] + 2
+
+    # ---- device-side plumbing ------------------------------------------------------------------------------------
+    def _require_cuda(self, t: torch.Tensor):
+        if not t.is_cuda or not self._flat.is_cuda:
+            raise _lib.DtbError("DecisionTransformer runs only on an sm_100a CUDA device through libdtb200.so "
+                                "(no CPU / eager-PyTorch fallback exists); move the model and inputs to cuda")
+
+    def _stage(self):
+        """Refresh the bf16 shadow of the parameters if any of them changed since the last staging."""
+        if self._flat_bf16 is None or self._flat_bf16.device != self._flat.device:
+            self._flat_bf16 = torch.empty(self._total, dtype=torch.bfloat16, device=self._flat.device)
+            self._staged_version = -1
+        if self._staged_version != self._flat._version:
+            _lib.check(_lib.load().dtb_dt_stage_params(self._h, _lib.stream_ptr(), _lib.ptr(self._flat), _lib.ptr(self._flat_bf16)))
+            self._staged_version = self._flat._version
+
+    def restage(self):
+        """Force a refresh of the bf16 shadow (call after writing parameters through an aliasing view torch cannot track)."""
+        self._staged_version = -1
+        self._stage()
+
+    def _workspace(self, B: int, K: int) -> torch.Tensor:
+        key = (B, K)
+        ws = self._ws.get(key)
+        if ws is None:
+            nbytes = int(_lib.load().dtb_dt_workspace_bytes(self._h, B, K))
+            if len(self._ws) > 4:
+                self._ws.clear()
+            ws = torch.empty(nbytes, dtype=torch.uint8, device=self._flat.device)
+            self._ws[key] = ws
+        return ws
+
+    def _make_batch(self, states, actions, returns_to_go, timesteps, attention_mask, states_bf16=None):
+        B, K = actions.shape[0], actions.shape[1]
+        keep = []
+
+        def f32(t):
+            t = t.detach().to(torch.float32).contiguous()
+            keep.append(t)
+            return t
+
+        b = _lib.DtBatch()
+        b.B, b.K = B, K
+        if states_bf16 is not None:
+            sb = states_bf16.detach().contiguous()
+            assert sb.dtype == torch.bfloat16
+            keep.append(sb)
+            b.states_bf16 = sb.data_ptr()
+            b.states = None
+        else:
+            b.states = f32(states).data_ptr()
+            b.states_bf16 = None
+        b.actions = f32(actions).data_ptr()
+        b.returns_to_go = f32(returns_to_go.reshape(B, K)).data_ptr()
+        ts = timesteps.detach().to(torch.long).contiguous()
+        keep.append(ts)
+        b.timesteps = ts.data_ptr()
+        if attention_mask is not None:
+            b.attention_mask = f32(attention_mask.reshape(B, K)).data_ptr()
+        else:
+            b.attention_mask = None
+        return b, keep
+
+    def _check_shapes(self, states, actions, returns_to_go, timesteps, attention_mask):
+        B, K = actions.shape[0], actions.shape[1]
+        if states.shape != (B, K, self.state_dim):
+            raise ValueError(f"states must be [B, K, {self.state_dim}], got {tuple(states.shape)}")
+        if actions.shape[2] != self.act_dim:
+            raise ValueError(f"actions must be [B, K, {self.act_dim}], got {tuple(actions.shape)}")
+        if returns_to_go.numel() != B * K or timesteps.numel() != B * K:
+            raise ValueError("returns_to_go must be [B, K, 1] and timesteps [B, K]")
+        if attention_mask is not None and attention_mask.numel() != B * K:
+            raise ValueError("attention_mask must be [B, K]")
+
+    def _maybe_warn_dropout(self):
+        if self.training and self._pdrop > 0 and not self._warned_dropout:
+            warnings.warn("dtb200: dropout (resid_pdrop/attn_pdrop > 0) is not applied by the sm_100a kernels in this version; "
+                          "the step runs with p = 0 (parity is defined at p = 0)")
+            self._warned_dropout = True
+
+    # ---- reference API -------------------------------------------------------------------------------------------
+    def forward(self, states, actions, rewards, returns_to_go, timesteps, attention_mask=None):
+        """HF:536-657.  ``rewards`` is accepted and ignored, as in the reference (A8)."""
+        self._require_cuda(actions)
+        self._check_shapes(states, actions, returns_to_go, timesteps, attention_mask)
+        self._maybe_warn_dropout()
+        params = [self.get_parameter(n) for n in self._names]
+        wide = self.state_dim > 64 and states.dtype == torch.bfloat16
+        return _DTFunction.apply(self, states, actions, returns_to_go, timesteps, attention_mask, wide, *params)
+
+    @torch.no_grad()
+    def get_action(self, states, actions, rewards, returns_to_go, timesteps, **kwargs):
+        """Upstream evaluation entry point: last-K window, LEFT zero padding, action of the last state token."""
+        self._require_cuda(states)
+        dev = states.device
+        states = states.reshape(1, -1, self.state_dim)
+        actions = actions.reshape(1, -1, self.act_dim)
+        returns_to_go = returns_to_go.reshape(1, -1, 1)
+        timesteps = timesteps.reshape(1, -1)
+        attention_mask = None
+        if self.max_length is not None:
+            K = self.max_length
+            states, actions = states[:, -K:], actions[:, -K:]
+            returns_to_go, timesteps = returns_to_go[:, -K:], timesteps[:, -K:]
+            t = states.shape[1]
+            attention_mask = torch.cat([torch.zeros(K - t, device=dev), torch.ones(t, device=dev)]).reshape(1, -1)
+            states = torch.cat([torch.zeros((1, K - t, self.state_dim), device=dev), states.float()], dim=1)
+            actions = torch.cat([torch.zeros((1, K - t, self.act_dim), device=dev), actions.float()], dim=1)
+            returns_to_go = torch.cat([torch.zeros((1, K - t, 1), device=dev), returns_to_go.float()], dim=1)
+            timesteps = torch.cat([torch.zeros((1, K - t), device=dev, dtype=torch.long), timesteps.long()], dim=1)
+        _, action_preds, _ = self._forward_raw(states, actions, returns_to_go, timesteps, attention_mask, want_all=False)
+        return action_preds[0, -1]
+
+    # ---- raw paths (no autograd graph) ---------------------------------------------------------------------------
+    def _forward_raw(self, states, actions, returns_to_go, timesteps, attention_mask, want_all=True, states_bf16=None):
+        lib = _lib.load()
+        B, K = actions.shape[0], actions.shape[1]
+        self._stage()
+        batch, keep = self._make_batch(states, actions, returns_to_go, timesteps, attention_mask, states_bf16)
+        ws = self._workspace(B, K)
+        dev = self._flat.device
+        ap = torch.empty((B, K, self.act_dim), dtype=torch.float32, device=dev)
+        sp = torch.empty((B, K, self.state_dim), dtype=torch.float32, device=dev) if want_all else None
+        rp = torch.empty((B, K, 1), dtype=torch.float32, device=dev) if want_all else None
+        _lib.check(lib.dtb_dt_forward(self._h, _lib.stream_ptr(), _lib.ptr(self._flat), _lib.ptr(self._flat_bf16), C.byref(batch),
+                                      _lib.ptr(ws), ws.numel(), _lib.ptr(ap), _lib.ptr(sp), _lib.ptr(rp)))
+        self._ws_gen += 1
+        self._last = (batch, keep, ws, self._ws_gen)
+        return sp, ap, rp
+
+    def _backward_raw(self, saved, d_action, d_state, d_return, grads, d_states_bf16=None, stage_begin=0, stage_end=None):
+        lib = _lib.load()
+        batch, keep, ws, gen = saved
+        if gen != self._ws_gen:
+            raise _lib.DtbError("DecisionTransformer.backward: the activation workspace was overwritten by a later forward; "
+                                "run backward before the next forward of the same model and batch shape")
+        if stage_end is None:
+            stage_end = self.n_stages - 1
+
+        def f32(t):
+            if t is None:
+                return None
+            t = t.detach().to(torch.float32).contiguous()
+            keep.append(t)
+            return t
+
+        _lib.check(lib.dtb_dt_backward(self._h, _lib.stream_ptr(), _lib.ptr(self._flat), _lib.ptr(self._flat_bf16), C.byref(batch),
+                                       _lib.ptr(ws), ws.numel(), _lib.ptr(f32(d_action)), _lib.ptr(f32(d_state)), _lib.ptr(f32(d_return)),
+                                       _lib.ptr(grads), _lib.ptr(d_states_bf16), stage_begin, stage_end))
+
+    def loss_and_backward(self, states, actions, returns_to_go, timesteps, attention_mask, action_target=None, grad_scale=1.0,
+                          states_bf16=None, d_states_bf16=None, on_stage_done=None):
+        """Fused training step body: forward + masked action MSE (A10) + backward straight into ``flat_grads``.
+
+        Returns a device tensor ``[loss, n_valid_rows]`` (no host sync).  ``on_stage_done(stage, begin, end)`` is called after each
+        backward stage is enqueued (data-parallel hosts all-reduce ``flat_grads[begin:end]`` there)."""
+        lib = _lib.load()
+        self._require_cuda(actions)
+        self._maybe_warn_dropout()
+        target = (actions if action_target is None else action_target).detach().to(torch.float32).contiguous()
+        self._forward_raw(states, actions, returns_to_go, timesteps, attention_mask, want_all=False, states_bf16=states_bf16)
+        batch, keep, ws, _ = self._last
+        loss = torch.empty(2, dtype=torch.float32, device=self._flat.device)
+        _lib.check(lib.dtb_dt_loss(self._h, _lib.stream_ptr(), C.byref(batch), _lib.ptr(target), float(grad_scale), _lib.ptr(ws), ws.numel(),
+                                   _lib.ptr(loss)))
+        grads = self.attach_grads()
+        if on_stage_done is None:
+            self._backward_raw(self._last, None, None, None, grads, d_states_bf16)
+        else:
+            for s in range(self.n_stages):
+                self._backward_raw(self._last, None, None, None, grads, d_states_bf16, s, s)
+                on_stage_done(s, *self.stage_grad_range(s))
+        return loss
+
+    def __del__(self):
+        try:
+            if getattr(self, "_h", None) is not None and self._h.value:
+                _lib.load().dtb_dt_destroy(self._h)
+                self._h = None
+        except Exception:
+            pass
+
+
+class _DTFunction(torch.autograd.Function):
+    """Generic autograd bridge: ``loss.backward()`` populates every ``param.grad`` exactly as it does for the oracle."""
+
+    @staticmethod
+    def forward(ctx, model, states, actions, returns_to_go, timesteps, attention_mask, wide, *params):
+        sb = states if wide else None
+        sp, ap, rp = model._forward_raw(None if wide else states, actions, returns_to_go, timesteps, attention_mask, want_all=True,
+                                        states_bf16=sb)
+        ctx.model, ctx.saved, ctx.wide = model, model._last, wide
+        ctx.states_need_grad = states.requires_grad
+        ctx.state_shape = states.shape
+        ctx.set_materialize_grads(False)
+        return sp, ap, rp
+
+    @staticmethod
+    def backward(ctx, d_state, d_action, d_return):
+        model = ctx.model
+        if ctx.states_need_grad and not ctx.wide:
+            raise NotImplementedError("gradient w.r.t. fp32 states (state_dim <= 64) is not produced by the sm_100a path")
+        grads = torch.empty_like(model._flat)
+        if d_action is None:  # NULL would mean "use the fused-loss gradient kept in the workspace"
+            d_action = torch.zeros(ctx.state_shape[:2] + (model.act_dim,), dtype=torch.float32, device=grads.device)
+        d_states = torch.empty(ctx.state_shape, dtype=torch.bfloat16, device=grads.device) if (ctx.wide and ctx.states_need_grad) else None
+        model._backward_raw(ctx.saved, d_action, d_state, d_return, grads, d_states)
+        out = [grads[off:off + torch.Size(shp).numel()].view(shp) for shp, off in zip(model._shapes, model._offsets)]
+        return (None, d_states, None, None, None, None, None, *out)
