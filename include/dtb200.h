@@ -133,6 +133,7 @@ typedef struct {
   const float* returns_to_go;   /* fp32 [B,K] */
   const long long* timesteps;   /* int64 [B,K] */
   const float* attention_mask;  /* fp32 [B,K] (> 0 = valid) or NULL = all valid (HF:606-608) */
+  int states_relu;              /* states_bf16 is a ReLU output (encoder towers): d_states is returned already masked by (state > 0) */
 } dtb_dt_batch;
 
 typedef struct dtb_dt dtb_dt;
@@ -166,6 +167,39 @@ int dtb_dt_backward(const dtb_dt* h, void* stream, const float* params, const vo
                     const float* d_return_preds, float* grads, void* d_states_bf16, int stage_begin, int stage_end);
 /* [begin, end) element range of the flat gradient buffer written by a backward stage. */
 int dtb_dt_stage_grad_range(const dtb_dt* h, int stage, long long* begin, long long* end);
+
+/* ---- multimodal state encoder (REF src/agents.py:30-55 conv_factory, :118-119 towers, :133-134 /255, :137-143 fusion) ------
+ * frames fp32 [N, Cv, H, W], audio fp32 [N, Ca, H, W] (N = B*K timesteps, NCHW as the reference's obs tensors) ->
+ * states bf16 [N, state_dim] = [relu(video_fc) | relu(audio_fc)] (fusion 0, 'concat', per-sample dim=1 semantics) or their
+ * sum (fusion 1).  Convolutions = patch gather + tcgen05 GEMM with bias+ReLU epilogue, NHWC bf16 activations.
+ * Flat parameter order (PyTorch layouts, nn.Sequential indices of conv_factory): per tower (video, audio):
+ *   big  : 0.weight [32,C,8,8], 0.bias, 2.weight [64,32,4,4], 2.bias, 4.weight [64,64,3,3], 4.bias, 7.weight [512, 64*h*w], 7.bias
+ *   small: 0.weight [16,C,8,8], 0.bias, 2.weight [32,16,4,4], 2.bias, 5.weight [256, 32*h*w], 5.bias */
+typedef struct {
+  int in_channels, in_h, in_w;
+  int big; /* 1 = conv_factory('big'), 0 = 'small' */
+} dtb_tower_config;
+typedef struct {
+  dtb_tower_config video, audio;
+  int fusion;        /* 0 concat, 1 sum */
+  float input_scale; /* 1/255 in the reference (agents.py:133-134) */
+} dtb_encoder_config;
+typedef struct dtb_encoder dtb_encoder;
+
+int dtb_encoder_create(const dtb_encoder_config* cfg, dtb_encoder** out);
+int dtb_encoder_destroy(dtb_encoder* e);
+int dtb_encoder_state_dim(const dtb_encoder* e);
+int dtb_encoder_param_entries(const dtb_encoder* e);
+long long dtb_encoder_param_layout(const dtb_encoder* e, long long* offsets, long long* numels);
+size_t dtb_encoder_workspace_bytes(const dtb_encoder* e, int N);
+/* fp32 master (PyTorch layouts) -> bf16 staged copy in tensor-core K order (same offsets). */
+int dtb_encoder_stage_params(const dtb_encoder* e, void* stream, const float* params, void* staged_bf16);
+int dtb_encoder_forward(const dtb_encoder* e, void* stream, const float* params, const void* staged_bf16, int N, const float* frames,
+                        const float* audio, void* workspace, size_t workspace_bytes, void* states_bf16);
+/* d_states_bf16 [N, state_dim]; d_states_masked != 0 when it is already multiplied by (states > 0) (dtb_dt_backward does this when
+ * dtb_dt_batch.states_relu is set); otherwise states_bf16 must be given and d_states_bf16 is masked IN PLACE.  Overwrites grads. */
+int dtb_encoder_backward(const dtb_encoder* e, void* stream, const float* params, const void* staged_bf16, int N, const void* states_bf16,
+                         const void* d_states_bf16, int d_states_masked, void* workspace, size_t workspace_bytes, float* grads);
 
 #ifdef __cplusplus
 }

@@ -30,7 +30,15 @@ class DtConfig(C.Structure):
 
 class DtBatch(C.Structure):
     _fields_ = [("B", C.c_int), ("K", C.c_int), ("states", C.c_void_p), ("states_bf16", C.c_void_p), ("actions", C.c_void_p),
-                ("returns_to_go", C.c_void_p), ("timesteps", C.c_void_p), ("attention_mask", C.c_void_p)]
+                ("returns_to_go", C.c_void_p), ("timesteps", C.c_void_p), ("attention_mask", C.c_void_p), ("states_relu", C.c_int)]
+
+
+class TowerConfig(C.Structure):
+    _fields_ = [("in_channels", C.c_int), ("in_h", C.c_int), ("in_w", C.c_int), ("big", C.c_int)]
+
+
+class EncoderConfig(C.Structure):
+    _fields_ = [("video", TowerConfig), ("audio", TowerConfig), ("fusion", C.c_int), ("input_scale", C.c_float)]
 
 
 def _declare(lib):
@@ -52,6 +60,17 @@ def _declare(lib):
     lib.dtb_dt_loss.argtypes = [vp, vp, C.POINTER(DtBatch), vp, f, vp, sz, vp]
     lib.dtb_dt_backward.argtypes = [vp, vp, vp, vp, C.POINTER(DtBatch), vp, sz, vp, vp, vp, vp, vp, i, i]
     lib.dtb_dt_stage_grad_range.argtypes = [vp, i, C.POINTER(ll), C.POINTER(ll)]
+    lib.dtb_encoder_create.argtypes = [C.POINTER(EncoderConfig), C.POINTER(vp)]
+    lib.dtb_encoder_destroy.argtypes = [vp]
+    lib.dtb_encoder_state_dim.argtypes = [vp]
+    lib.dtb_encoder_param_entries.argtypes = [vp]
+    lib.dtb_encoder_param_layout.argtypes = [vp, C.POINTER(ll), C.POINTER(ll)]
+    lib.dtb_encoder_param_layout.restype = ll
+    lib.dtb_encoder_workspace_bytes.argtypes = [vp, i]
+    lib.dtb_encoder_workspace_bytes.restype = sz
+    lib.dtb_encoder_stage_params.argtypes = [vp, vp, vp, vp]
+    lib.dtb_encoder_forward.argtypes = [vp, vp, vp, vp, i, vp, vp, vp, sz, vp]
+    lib.dtb_encoder_backward.argtypes = [vp, vp, vp, vp, i, vp, vp, i, vp, sz, vp]
     lib.dtb_masked_mse.argtypes = [vp, vp, vp, vp, i, i, f, vp, vp, vp]
     lib.dtb_heads_fwd.argtypes = [vp] * 8 + [i] * 5 + [vp] * 3
     lib.dtb_embed_fwd.argtypes = [vp] * 15 + [i] * 5 + [f] + [vp] * 5 + [i, i]

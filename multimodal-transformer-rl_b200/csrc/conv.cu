@@ -1,0 +1,214 @@
+// Convolution data movement for the multimodal state towers (REF src/agents.py:30-55, A11): the convolutions
+// themselves run on the tcgen05 GEMM (rows = output pixels, K = kh*kw*Cin, N = Cout, bias + ReLU in the epilogue,
+// which makes the GEMM output the NHWC activation of the next layer).  This file holds the patch gather / scatter
+// and the weight re-ordering between PyTorch's layouts (NCHW activations, [Cout,Cin,kh,kw] weights, (c,h,w) flatten)
+// and the channels-last layouts the tensor-core path uses.
+//   conv1 : fp32 NCHW input -> bf16 patches [N*ho*wo, Cin*k*k], K order (c,kh,kw) = PyTorch weight order; `scale`
+//           folds the reference's `/ 255.0` input scaling (agents.py:133-134).
+//   conv2+: bf16 NHWC input -> bf16 patches [N*ho*wo, k*k*C], K order (kh,kw,c) (weights staged in the same order).
+//   col2im: gather form (no atomics, deterministic) fused with the ReLU mask of the layer that produced the input.
+#include "kernels.h"
+
+namespace dtb {
+
+// ---- conv1 patches from fp32 NCHW (k = 8, any stride with W % 4 == 0 and stride % 4 == 0) -------------------------
+__global__ void __launch_bounds__(256) im2col_nchw_k8_kernel(const float* __restrict__ x, int N, int C, int H, int W, int stride, int ho,
+                                                             int wo, float scale, bf16* __restrict__ p) {
+  const size_t total = (size_t)N * ho * wo * C * 8;  // one thread per (row, c, kh): 8 contiguous kw
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int kh = (int)(i & 7);
+    size_t r = i >> 3;
+    const int c = (int)(r % C);
+    r /= C;  // row = (n, oh, ow)
+    const int ow = (int)(r % wo);
+    const size_t t = r / wo;
+    const int oh = (int)(t % ho), n = (int)(t / ho);
+    const float* src = x + (((size_t)n * C + c) * H + (oh * stride + kh)) * W + ow * stride;
+    const float4 a = ldg_f4(src), b = ldg_f4(src + 4);
+    uint4 o = make_uint4(pack_bf16x2(a.x * scale, a.y * scale), pack_bf16x2(a.z * scale, a.w * scale), pack_bf16x2(b.x * scale, b.y * scale),
+                         pack_bf16x2(b.z * scale, b.w * scale));
+    *reinterpret_cast<uint4*>(p + r * (size_t)(C * 64) + c * 64 + kh * 8) = o;
+  }
+}
+
+int im2col_nchw_k8(cudaStream_t stream, const float* x, int N, int C, int H, int W, int stride, float scale, bf16* p) {
+  DTB_REQUIRE(W % 4 == 0 && stride % 4 == 0 && H >= 8 && W >= 8, DTB_ERR_UNSUPPORTED,
+              "conv1: needs W %% 4 == 0 and stride %% 4 == 0 (got W=%d stride=%d)", W, stride);
+  DTB_REQUIRE((reinterpret_cast<uintptr_t>(x) & 15) == 0, DTB_ERR_BAD_ARG, "conv1: input must be 16-byte aligned");
+  const int ho = (H - 8) / stride + 1, wo = (W - 8) / stride + 1;
+  const size_t total = (size_t)N * ho * wo * C * 8;
+  if (total == 0) return DTB_OK;
+  size_t blocks = (total + 255) / 256;
+  const size_t cap = (size_t)num_sms() * 16;
+  if (blocks > cap) blocks = cap;
+  im2col_nchw_k8_kernel<<<(unsigned)blocks, 256, 0, stream>>>(x, N, C, H, W, stride, ho, wo, scale, p);
+  DTB_CHECK_LAUNCH();
+  return DTB_OK;
+}
+
+// ---- patches from bf16 NHWC: for a fixed (row, kh) the kw*C elements are contiguous in both source and destination --
+__global__ void __launch_bounds__(256) im2col_nhwc_kernel(const bf16* __restrict__ x, int N, int H, int W, int C, int k, int stride, int ho,
+                                                          int wo, bf16* __restrict__ p) {
+  const int run = k * C / 8;  // 16-byte chunks per (row, kh)
+  const size_t total = (size_t)N * ho * wo * k * run;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int ch = (int)(i % run);
+    size_t r = i / run;
+    const int kh = (int)(r % k);
+    r /= k;
+    const int ow = (int)(r % wo);
+    const size_t t = r / wo;
+    const int oh = (int)(t % ho), n = (int)(t / ho);
+    const bf16* src = x + (((size_t)n * H + (oh * stride + kh)) * W + ow * stride) * C + ch * 8;
+    *reinterpret_cast<uint4*>(p + r * (size_t)(k * k * C) + (size_t)kh * k * C + ch * 8) = ldg_u4(src);
+  }
+}
+
+int im2col_nhwc(cudaStream_t stream, const bf16* x, int N, int H, int W, int C, int k, int stride, bf16* p) {
+  DTB_REQUIRE(C % 8 == 0, DTB_ERR_UNSUPPORTED, "im2col: channels (%d) must be a multiple of 8", C);
+  const int ho = (H - k) / stride + 1, wo = (W - k) / stride + 1;
+  const size_t total = (size_t)N * ho * wo * k * (k * C / 8);
+  if (total == 0) return DTB_OK;
+  size_t blocks = (total + 255) / 256;
+  const size_t cap = (size_t)num_sms() * 16;
+  if (blocks > cap) blocks = cap;
+  im2col_nhwc_kernel<<<(unsigned)blocks, 256, 0, stream>>>(x, N, H, W, C, k, stride, ho, wo, p);
+  DTB_CHECK_LAUNCH();
+  return DTB_OK;
+}
+
+// ---- col2im (gather) + ReLU mask: dz[n,h,w,c] = (y[n,h,w,c] > 0) * sum_{kh,kw valid} dp[(n,(h-kh)/s,(w-kw)/s), (kh,kw,c)] ---------
+__global__ void __launch_bounds__(256) col2im_nhwc_relu_kernel(const bf16* __restrict__ dp, const bf16* __restrict__ y, int N, int H, int W,
+                                                               int C, int k, int stride, int ho, int wo, bf16* __restrict__ dz) {
+  const int cg = C / 8;
+  const size_t total = (size_t)N * H * W * cg;
+  const size_t ldp = (size_t)k * k * C;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int c8 = (int)(i % cg);
+    size_t r = i / cg;
+    const int w = (int)(r % W);
+    const size_t t = r / W;
+    const int h = (int)(t % H), n = (int)(t / H);
+    float acc[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) acc[e] = 0.f;
+    for (int kh = h % stride; kh < k; kh += stride) {
+      const int oh = (h - kh) / stride;
+      if (h - kh < 0 || oh >= ho) continue;
+      for (int kw = w % stride; kw < k; kw += stride) {
+        const int ow = (w - kw) / stride;
+        if (w - kw < 0 || ow >= wo) continue;
+        const uint4 u = ldg_u4(dp + (((size_t)n * ho + oh) * wo + ow) * ldp + ((size_t)kh * k + kw) * C + c8 * 8);
+        const float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y), c = unpack_bf16x2(u.z), d = unpack_bf16x2(u.w);
+        acc[0] += a.x; acc[1] += a.y; acc[2] += b.x; acc[3] += b.y; acc[4] += c.x; acc[5] += c.y; acc[6] += d.x; acc[7] += d.y;
+      }
+    }
+    const uint4 yu = ldg_u4(y + r * C + c8 * 8);
+    const float2 ya = unpack_bf16x2(yu.x), yb = unpack_bf16x2(yu.y), yc = unpack_bf16x2(yu.z), yd = unpack_bf16x2(yu.w);
+    const float m[8] = {ya.x, ya.y, yb.x, yb.y, yc.x, yc.y, yd.x, yd.y};
+#pragma unroll
+    for (int e = 0; e < 8; ++e) acc[e] = m[e] > 0.f ? acc[e] : 0.f;
+    *reinterpret_cast<uint4*>(dz + r * C + c8 * 8) =
+        make_uint4(pack_bf16x2(acc[0], acc[1]), pack_bf16x2(acc[2], acc[3]), pack_bf16x2(acc[4], acc[5]), pack_bf16x2(acc[6], acc[7]));
+  }
+}
+
+int col2im_nhwc_relu(cudaStream_t stream, const bf16* dp, const bf16* y, int N, int H, int W, int C, int k, int stride, bf16* dz) {
+  DTB_REQUIRE(C % 8 == 0, DTB_ERR_UNSUPPORTED, "col2im: channels (%d) must be a multiple of 8", C);
+  const int ho = (H - k) / stride + 1, wo = (W - k) / stride + 1;
+  const size_t total = (size_t)N * H * W * (C / 8);
+  if (total == 0) return DTB_OK;
+  size_t blocks = (total + 255) / 256;
+  const size_t cap = (size_t)num_sms() * 16;
+  if (blocks > cap) blocks = cap;
+  col2im_nhwc_relu_kernel<<<(unsigned)blocks, 256, 0, stream>>>(dp, y, N, H, W, C, k, stride, ho, wo, dz);
+  DTB_CHECK_LAUNCH();
+  return DTB_OK;
+}
+
+// ---- weight re-ordering: src fp32 [O][A][B] <-> [O][B][A] --------------------------------------------------------------
+// stage  : dst bf16 [O][B][A] = src fp32 [O][A][B]      ([Cout][Cin][kh*kw] -> [Cout][kh*kw][Cin];  fc [F][C][h*w] -> [F][h*w][C])
+// unstage: dst fp32 [O][A][B] = src fp32 [O][B][A]      (gradients back to the PyTorch order)
+__global__ void permute_stage_kernel(const float* __restrict__ src, int O, int A, int B, bf16* __restrict__ dst) {
+  const size_t total = (size_t)O * A * B;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int a = (int)(i % A);
+    const size_t r = i / A;
+    const int b = (int)(r % B);
+    const size_t o = r / B;
+    dst[i] = __float2bfloat16(src[(o * A + a) * B + b]);
+  }
+}
+__global__ void permute_unstage_kernel(const float* __restrict__ src, int O, int A, int B, float* __restrict__ dst) {
+  const size_t total = (size_t)O * A * B;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int b = (int)(i % B);
+    const size_t r = i / B;
+    const int a = (int)(r % A);
+    const size_t o = r / A;
+    dst[i] = src[(o * B + b) * A + a];
+  }
+}
+static unsigned perm_blocks(size_t total) {
+  size_t blocks = (total + 255) / 256;
+  const size_t cap = (size_t)num_sms() * 8;
+  return (unsigned)(blocks > cap ? cap : (blocks < 1 ? 1 : blocks));
+}
+int permute_stage(cudaStream_t stream, const float* src, int O, int A, int B, bf16* dst) {
+  permute_stage_kernel<<<perm_blocks((size_t)O * A * B), 256, 0, stream>>>(src, O, A, B, dst);
+  DTB_CHECK_LAUNCH();
+  return DTB_OK;
+}
+int permute_unstage(cudaStream_t stream, const float* src, int O, int A, int B, float* dst) {
+  permute_unstage_kernel<<<perm_blocks((size_t)O * A * B), 256, 0, stream>>>(src, O, A, B, dst);
+  DTB_CHECK_LAUNCH();
+  return DTB_OK;
+}
+
+// out = a + b (bf16), and the ReLU-masked variant used by the 'sum' fusion backward: dz = (y > 0) * dy
+__global__ void add_bf16_kernel(const bf16* __restrict__ a, const bf16* __restrict__ b, size_t n8, bf16* __restrict__ out) {
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n8; i += (size_t)gridDim.x * blockDim.x) {
+    const uint4 ua = ldg_u4(a + i * 8), ub = ldg_u4(b + i * 8);
+    const uint32_t wa[4] = {ua.x, ua.y, ua.z, ua.w}, wb[4] = {ub.x, ub.y, ub.z, ub.w};
+    uint32_t o[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const float2 x = unpack_bf16x2(wa[e]), y = unpack_bf16x2(wb[e]);
+      o[e] = pack_bf16x2(x.x + y.x, x.y + y.y);
+    }
+    *reinterpret_cast<uint4*>(out + i * 8) = make_uint4(o[0], o[1], o[2], o[3]);
+  }
+}
+int add_bf16(cudaStream_t stream, const bf16* a, const bf16* b, size_t n, bf16* out) {
+  DTB_REQUIRE(n % 8 == 0, DTB_ERR_BAD_ARG, "add_bf16: n must be a multiple of 8");
+  if (n == 0) return DTB_OK;
+  add_bf16_kernel<<<perm_blocks(n / 8), 256, 0, stream>>>(a, b, n / 8, out);
+  DTB_CHECK_LAUNCH();
+  return DTB_OK;
+}
+__global__ void relu_mask_bf16_kernel(const bf16* __restrict__ dy, int ldy, const bf16* __restrict__ y, int ld, int rows, int cols8,
+                                      bf16* __restrict__ dz, int ldz) {
+  const size_t total = (size_t)rows * cols8;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i % cols8) * 8;
+    const size_t r = i / cols8;
+    const uint4 ud = ldg_u4(dy + r * ldy + c), uy = ldg_u4(y + r * ld + c);
+    const uint32_t wd[4] = {ud.x, ud.y, ud.z, ud.w}, wy[4] = {uy.x, uy.y, uy.z, uy.w};
+    uint32_t o[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const float2 g = unpack_bf16x2(wd[e]), v = unpack_bf16x2(wy[e]);
+      o[e] = pack_bf16x2(v.x > 0.f ? g.x : 0.f, v.y > 0.f ? g.y : 0.f);
+    }
+    *reinterpret_cast<uint4*>(dz + r * ldz + c) = make_uint4(o[0], o[1], o[2], o[3]);
+  }
+}
+int relu_mask_bf16(cudaStream_t stream, const bf16* dy, int ldy, const bf16* y, int ld, int rows, int cols, bf16* dz, int ldz) {
+  DTB_REQUIRE(cols % 8 == 0 && ldy % 8 == 0 && ld % 8 == 0 && ldz % 8 == 0, DTB_ERR_BAD_ARG, "relu_mask: dims must be multiples of 8");
+  if (rows * cols == 0) return DTB_OK;
+  relu_mask_bf16_kernel<<<perm_blocks((size_t)rows * cols / 8), 256, 0, stream>>>(dy, ldy, y, ld, rows, cols / 8, dz, ldz);
+  DTB_CHECK_LAUNCH();
+  return DTB_OK;
+}
+
+}  // namespace dtb

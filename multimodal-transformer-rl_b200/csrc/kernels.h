@@ -86,4 +86,13 @@ int heads_bwd(cudaStream_t stream, const float* d_action, const float* d_state, 
               bf16* dzA, bf16* dzS);
 int copy2d(cudaStream_t stream, const float* src, int lds, int R, int C, float* dst, int ldd);
 
+// ---- conv.cu -----------------------------------------------------------------------------------
+int im2col_nchw_k8(cudaStream_t stream, const float* x, int N, int C, int H, int W, int stride, float scale, bf16* p);
+int im2col_nhwc(cudaStream_t stream, const bf16* x, int N, int H, int W, int C, int k, int stride, bf16* p);
+int col2im_nhwc_relu(cudaStream_t stream, const bf16* dp, const bf16* y, int N, int H, int W, int C, int k, int stride, bf16* dz);
+int permute_stage(cudaStream_t stream, const float* src, int O, int A, int B, bf16* dst);
+int permute_unstage(cudaStream_t stream, const float* src, int O, int A, int B, float* dst);
+int add_bf16(cudaStream_t stream, const bf16* a, const bf16* b, size_t n, bf16* out);
+int relu_mask_bf16(cudaStream_t stream, const bf16* dy, int ldy, const bf16* y, int ld, int rows, int cols, bf16* dz, int ldz);
+
 }  // namespace dtb

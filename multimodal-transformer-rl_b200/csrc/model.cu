@@ -328,6 +328,11 @@ static int bwd_embed(const dtb_dt* h, cudaStream_t st, const float* P, const voi
       GemmEpilogue ep = ep_zero();
       ep.out_bf16 = d_states;
       ep.ldo_b = sd;
+      if (b->states_relu) {  // the wide state is relu(features): hand the towers dZ directly
+        ep.dact = 1;
+        ep.aux = sb;
+        ep.ldaux = sd;
+      }
       DTB_TRY(gemm_fwd(st, dpre_s, 3 * H, bfp(Pb, h->e(E_WS)), sd, true, BK, sd, H, ep));
     }
   }

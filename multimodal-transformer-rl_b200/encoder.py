@@ -1,0 +1,235 @@
+"""Host-side mirror of the reference's multimodal state encoder (``MinecraftAgent`` towers + fusion, REF src/agents.py:93-143)
+and of the multimodal Decision Transformer built on it (encoder output = state tokens, trained end to end).
+
+``MultimodalStateEncoder(frame_shape, audio_shape, conv_type='big', fusion_type='concat')(frames, audio) -> states[B,K,state_dim]``
+mirrors ``MinecraftAgent(envs, device, conv_type, attn_type=None, fusion_type)``'s ``video_net`` / ``audio_net`` / fusion; the
+parameter names (``video_net.0.weight`` ...) and layouts are the reference's ``conv_factory`` nn.Sequential ones, so a
+reference state_dict loads directly.  Compute runs only in ``libdtb200.so`` (no fallback).
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+import torch.nn as nn
+
+from . import _lib
+from .model import DecisionTransformer, _set_nested
+
+
+def _conv_out(n, k, s):
+    return (n - k) // s + 1
+
+
+def _tower_entries(prefix, conv_type, cin, h, w):
+    if conv_type == "big":
+        specs, feat, fc_idx = [(32, 8, 4), (64, 4, 2), (64, 3, 1)], 512, 7
+    elif conv_type == "small":
+        specs, feat, fc_idx = [(16, 8, 4), (32, 4, 2)], 256, 5
+    else:
+        raise NotImplementedError(conv_type)
+    names, shapes = [], []
+    for i, (cout, k, s) in enumerate(specs):
+        names += [f"{prefix}.{2 * i}.weight", f"{prefix}.{2 * i}.bias"]
+        shapes += [(cout, cin, k, k), (cout,)]
+        cin, h, w = cout, _conv_out(h, k, s), _conv_out(w, k, s)
+    names += [f"{prefix}.{fc_idx}.weight", f"{prefix}.{fc_idx}.bias"]
+    shapes += [(feat, cin * h * w), (feat,)]
+    return names, shapes, feat
+
+
+class MultimodalStateEncoder(nn.Module):
+    def __init__(self, frame_shape=(1, 84, 84), audio_shape=(1, 84, 84), conv_type="big", fusion_type="concat", input_scale=1.0 / 255.0,
+                 device=None):
+        super().__init__()
+        self.frame_shape, self.audio_shape = tuple(int(x) for x in frame_shape), tuple(int(x) for x in audio_shape)
+        self.conv_type, self.fusion_type, self.input_scale = conv_type, fusion_type, float(input_scale)
+        if fusion_type not in ("concat", "sum"):
+            raise NotImplementedError(fusion_type)
+        lib = _lib.load()
+        big = 1 if conv_type == "big" else 0
+        cfg = _lib.EncoderConfig(_lib.TowerConfig(*self.frame_shape, big), _lib.TowerConfig(*self.audio_shape, big),
+                                 0 if fusion_type == "concat" else 1, self.input_scale)
+        h = C.c_void_p()
+        _lib.check(lib.dtb_encoder_create(C.byref(cfg), C.byref(h)))
+        self._h = h
+        self.state_dim = int(lib.dtb_encoder_state_dim(self._h))
+        n = lib.dtb_encoder_param_entries(self._h)
+        offs, nums = (C.c_longlong * n)(), (C.c_longlong * n)()
+        self._total = int(lib.dtb_encoder_param_layout(self._h, offs, nums))
+        vn, vs, self.feature_size = _tower_entries("video_net", conv_type, *self.frame_shape)
+        an, as_, _ = _tower_entries("audio_net", conv_type, *self.audio_shape)
+        self._names, self._shapes = vn + an, vs + as_
+        assert len(self._names) == n
+        self._offsets = [int(o) for o in offs]
+        for shp, num in zip(self._shapes, nums):
+            assert int(torch.Size(shp).numel()) == int(num), (shp, num)
+        if device is None:
+            device = "cuda" if torch.cuda.is_available() else "cpu"
+        self._flat = torch.zeros(self._total, dtype=torch.float32, device=device)
+        self._flat_grad, self._staged, self._staged_version, self._ws = None, None, -1, {}
+        for name, shp, off in zip(self._names, self._shapes, self._offsets):
+            _set_nested(self, name, nn.Parameter(self._flat[off:off + torch.Size(shp).numel()].view(shp)))
+        self.reset_parameters()
+
+    # parameter plumbing shared in spirit with DecisionTransformer (flat buffer + views)
+    def _apply(self, fn, recurse=True):
+        super()._apply(fn, recurse)
+        ref = self.get_parameter(self._names[0])
+        flat = torch.zeros(self._total, dtype=torch.float32, device=ref.device)
+        for name, shp, off in zip(self._names, self._shapes, self._offsets):
+            flat[off:off + torch.Size(shp).numel()].view(shp).copy_(self.get_parameter(name).data.float())
+        self._flat = flat
+        self._flat_grad, self._staged, self._staged_version, self._ws = None, None, -1, {}
+        for name, shp, off in zip(self._names, self._shapes, self._offsets):
+            self.get_parameter(name).data = self._flat[off:off + torch.Size(shp).numel()].view(shp)
+        return self
+
+    @torch.no_grad()
+    def reset_parameters(self):
+        """layer_init of the reference (src/utils.py:146-149): orthogonal(gain sqrt 2) weights, zero biases."""
+        for name, p in self.named_parameters():
+            if name.endswith(".bias"):
+                p.zero_()
+            else:
+                w = torch.empty(p.shape, dtype=torch.float32)
+                torch.nn.init.orthogonal_(w, 2 ** 0.5)
+                p.copy_(w)
+
+    def load_state_dict(self, state_dict, strict=True, assign=False):
+        out = super().load_state_dict(state_dict, strict=strict, assign=False)
+        self._staged_version = -1
+        return out
+
+    @property
+    def flat_params(self):
+        return self._flat
+
+    @property
+    def flat_grads(self):
+        if self._flat_grad is None or self._flat_grad.device != self._flat.device:
+            self._flat_grad = torch.zeros_like(self._flat)
+        return self._flat_grad
+
+    def attach_grads(self):
+        g = self.flat_grads
+        for name, shp, off in zip(self._names, self._shapes, self._offsets):
+            p = self.get_parameter(name)
+            view = g[off:off + torch.Size(shp).numel()].view(shp)
+            if p.grad is None or p.grad.data_ptr() != view.data_ptr():
+                p.grad = view
+        return g
+
+    def _stage(self):
+        if self._staged is None or self._staged.device != self._flat.device:
+            self._staged = torch.zeros(self._total, dtype=torch.bfloat16, device=self._flat.device)
+            self._staged_version = -1
+        if self._staged_version != self._flat._version:
+            _lib.check(_lib.load().dtb_encoder_stage_params(self._h, _lib.stream_ptr(), _lib.ptr(self._flat), _lib.ptr(self._staged)))
+            self._staged_version = self._flat._version
+
+    def _workspace(self, N):
+        ws = self._ws.get(N)
+        if ws is None:
+            if len(self._ws) > 4:
+                self._ws.clear()
+            ws = torch.empty(int(_lib.load().dtb_encoder_workspace_bytes(self._h, N)), dtype=torch.uint8, device=self._flat.device)
+            self._ws[N] = ws
+        return ws
+
+    def _prep(self, frames, audio):
+        if not frames.is_cuda or not self._flat.is_cuda:
+            raise _lib.DtbError("MultimodalStateEncoder runs only on an sm_100a CUDA device through libdtb200.so (no CPU fallback)")
+        B, K = frames.shape[0], frames.shape[1]
+        if tuple(frames.shape[2:]) != self.frame_shape or tuple(audio.shape[2:]) != self.audio_shape or audio.shape[:2] != frames.shape[:2]:
+            raise ValueError(f"expected frames [B,K,{self.frame_shape}] and audio [B,K,{self.audio_shape}], got {tuple(frames.shape)}, "
+                             f"{tuple(audio.shape)}")
+        return B, K, frames.detach().to(torch.float32).contiguous(), audio.detach().to(torch.float32).contiguous()
+
+    def forward_raw(self, frames, audio):
+        """frames [B,K,Cv,H,W], audio [B,K,Ca,H,W] (fp32) -> states bf16 [B,K,state_dim]; keeps what backward_raw needs."""
+        B, K, f, a = self._prep(frames, audio)
+        N = B * K
+        self._stage()
+        ws = self._workspace(N)
+        states = torch.empty((B, K, self.state_dim), dtype=torch.bfloat16, device=self._flat.device)
+        _lib.check(_lib.load().dtb_encoder_forward(self._h, _lib.stream_ptr(), _lib.ptr(self._flat), _lib.ptr(self._staged), N, _lib.ptr(f),
+                                                   _lib.ptr(a), _lib.ptr(ws), ws.numel(), _lib.ptr(states)))
+        self._last = (N, f, a, ws, states)
+        return states
+
+    def backward_raw(self, d_states, masked: bool, grads=None):
+        N, f, a, ws, states = self._last
+        grads = self.attach_grads() if grads is None else grads
+        _lib.check(_lib.load().dtb_encoder_backward(self._h, _lib.stream_ptr(), _lib.ptr(self._flat), _lib.ptr(self._staged), N,
+                                                    _lib.ptr(states), _lib.ptr(d_states), int(masked), _lib.ptr(ws), ws.numel(),
+                                                    _lib.ptr(grads)))
+        return grads
+
+    def forward(self, frames, audio):
+        params = [self.get_parameter(n) for n in self._names]
+        return _EncoderFunction.apply(self, frames, audio, *params)
+
+    def __del__(self):
+        try:
+            if getattr(self, "_h", None) is not None and self._h.value:
+                _lib.load().dtb_encoder_destroy(self._h)
+                self._h = None
+        except Exception:
+            pass
+
+
+class _EncoderFunction(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, enc, frames, audio, *params):
+        states = enc.forward_raw(frames, audio)
+        ctx.enc, ctx.saved = enc, enc._last
+        return states
+
+    @staticmethod
+    def backward(ctx, d_states):
+        enc = ctx.enc
+        if enc._last is not ctx.saved:
+            raise _lib.DtbError("MultimodalStateEncoder.backward: workspace overwritten by a later forward")
+        grads = torch.empty_like(enc._flat)
+        d = d_states.detach().to(torch.bfloat16).contiguous().clone()  # masked in place by the library
+        enc.backward_raw(d, masked=False, grads=grads)
+        out = [grads[off:off + torch.Size(shp).numel()].view(shp) for shp, off in zip(enc._shapes, enc._offsets)]
+        return (None, None, None, *out)
+
+
+class MultimodalDecisionTransformer(nn.Module):
+    """Encoder towers -> state tokens -> DecisionTransformer, trained end to end (configs c2 / c3 / c5 of BASELINE.json)."""
+
+    def __init__(self, encoder: MultimodalStateEncoder, dt: DecisionTransformer):
+        super().__init__()
+        if dt.state_dim != encoder.state_dim:
+            raise ValueError(f"DecisionTransformer.state_dim ({dt.state_dim}) must equal the encoder's ({encoder.state_dim})")
+        self.encoder, self.dt = encoder, dt
+
+    def forward(self, frames, audio, actions, rewards, returns_to_go, timesteps, attention_mask=None):
+        states = self.encoder(frames, audio)
+        return self.dt(states, actions, rewards, returns_to_go, timesteps, attention_mask)
+
+    @torch.no_grad()
+    def get_action(self, frames, audio, actions, rewards, returns_to_go, timesteps, **kwargs):
+        """frames [t,Cv,H,W], audio [t,Ca,H,W]: encode the history, then DecisionTransformer.get_action on the state tokens."""
+        K = self.dt.max_length
+        if K is not None:
+            frames, audio = frames[-K:], audio[-K:]
+        states = self.encoder.forward_raw(frames.unsqueeze(0), audio.unsqueeze(0))[0].float()
+        return self.dt.get_action(states, actions, rewards, returns_to_go, timesteps, **kwargs)
+
+    def loss_and_backward(self, frames, audio, actions, returns_to_go, timesteps, attention_mask, action_target=None, grad_scale=1.0,
+                          on_stage_done=None):
+        """Fused end-to-end training step body: towers -> DT forward -> masked action MSE -> DT backward -> towers backward."""
+        states = self.encoder.forward_raw(frames, audio)
+        d_states = torch.empty_like(states)
+        relu_out = self.encoder.fusion_type == "concat"  # the concatenated state is itself relu(features); a sum is not
+        loss = self.dt.loss_and_backward(None, actions, returns_to_go, timesteps, attention_mask, action_target=action_target,
+                                         grad_scale=grad_scale, states_bf16=states, d_states_bf16=d_states, states_relu=relu_out,
+                                         on_stage_done=on_stage_done)
+        self.encoder.backward_raw(d_states, masked=relu_out)
+        if on_stage_done is not None:
+            on_stage_done("encoder", 0, self.encoder._total)
+        return loss

@@ -211,7 +211,7 @@ class DecisionTransformer(nn.Module):
             self._ws[key] = ws
         return ws
 
-    def _make_batch(self, states, actions, returns_to_go, timesteps, attention_mask, states_bf16=None):
+    def _make_batch(self, states, actions, returns_to_go, timesteps, attention_mask, states_bf16=None, states_relu=False):
         B, K = actions.shape[0], actions.shape[1]
         keep = []
 
@@ -222,6 +222,7 @@ class DecisionTransformer(nn.Module):
 
         b = _lib.DtBatch()
         b.B, b.K = B, K
+        b.states_relu = int(bool(states_relu))
         if states_bf16 is not None:
             sb = states_bf16.detach().contiguous()
             assert sb.dtype == torch.bfloat16
@@ -293,11 +294,11 @@ class DecisionTransformer(nn.Module):
         return action_preds[0, -1]
 
     # ---- raw paths (no autograd graph) ---------------------------------------------------------------------------
-    def _forward_raw(self, states, actions, returns_to_go, timesteps, attention_mask, want_all=True, states_bf16=None):
+    def _forward_raw(self, states, actions, returns_to_go, timesteps, attention_mask, want_all=True, states_bf16=None, states_relu=False):
         lib = _lib.load()
         B, K = actions.shape[0], actions.shape[1]
         self._stage()
-        batch, keep = self._make_batch(states, actions, returns_to_go, timesteps, attention_mask, states_bf16)
+        batch, keep = self._make_batch(states, actions, returns_to_go, timesteps, attention_mask, states_bf16, states_relu)
         ws = self._workspace(B, K)
         dev = self._flat.device
         ap = torch.empty((B, K, self.act_dim), dtype=torch.float32, device=dev)
@@ -330,7 +331,7 @@ class DecisionTransformer(nn.Module):
                                        _lib.ptr(grads), _lib.ptr(d_states_bf16), stage_begin, stage_end))
 
     def loss_and_backward(self, states, actions, returns_to_go, timesteps, attention_mask, action_target=None, grad_scale=1.0,
-                          states_bf16=None, d_states_bf16=None, on_stage_done=None):
+                          states_bf16=None, d_states_bf16=None, states_relu=False, on_stage_done=None):
         """Fused training step body: forward + masked action MSE (A10) + backward straight into ``flat_grads``.
 
         Returns a device tensor ``[loss, n_valid_rows]`` (no host sync).  ``on_stage_done(stage, begin, end)`` is called after each
@@ -339,7 +340,8 @@ class DecisionTransformer(nn.Module):
         self._require_cuda(actions)
         self._maybe_warn_dropout()
         target = (actions if action_target is None else action_target).detach().to(torch.float32).contiguous()
-        self._forward_raw(states, actions, returns_to_go, timesteps, attention_mask, want_all=False, states_bf16=states_bf16)
+        self._forward_raw(states, actions, returns_to_go, timesteps, attention_mask, want_all=False, states_bf16=states_bf16,
+                          states_relu=states_relu)
         batch, keep, ws, _ = self._last
         loss = torch.empty(2, dtype=torch.float32, device=self._flat.device)
         _lib.check(lib.dtb_dt_loss(self._h, _lib.stream_ptr(), C.byref(batch), _lib.ptr(target), float(grad_scale), _lib.ptr(ws), ws.numel(),
@@ -371,7 +373,7 @@ class _DTFunction(torch.autograd.Function):
         sp, ap, rp = model._forward_raw(None if wide else states, actions, returns_to_go, timesteps, attention_mask, want_all=True,
                                         states_bf16=sb)
         ctx.model, ctx.saved, ctx.wide = model, model._last, wide
-        ctx.states_need_grad = states.requires_grad
+        ctx.states_need_grad = bool(ctx.needs_input_grad[1])
         ctx.state_shape = states.shape
         ctx.set_materialize_grads(False)
         return sp, ap, rp
