@@ -1,0 +1,414 @@
+"""Benchmark contract: `python bench.py --gpus N --steps K --warmup W [--impl reference] [--workload c1|c2|c3|c4]`.
+
+Metric (BASELINE.json): Decision-Transformer training tokens/s (forward + masked action MSE + backward; + gradient all-reduce for N>1;
+optimizer excluded) on synthetic trajectories.  Default workload = BASELINE.json configs[1], the Minecraft2d
+multimodal DT (3x64x64 frames + 1x64x64 spectrogram -> two conv towers -> K=30, H=128, 3 layers, batch 64 per GPU): weak scaling.
+One JSON line on rank 0.  `value` = device-resident inputs; `e2e` = through the public Python API / C ABI with pinned HOST buffers,
+host->device copies and the loss read-back inside the timed region.  `--impl reference` times the fp32 PyTorch oracle (for the
+towers numerically the reference's own conv_factory) on the host cores.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+import torch  # noqa: E402
+
+WORKLOADS = {
+    # name: DT config + per-GPU batch + encoder shapes (None = vector states)      — SURVEY.md §8 config table
+    "c1": dict(dt=dict(state_dim=11, act_dim=3, hidden_size=128, n_layer=3, n_head=1, activation_function="relu", action_tanh=True), K=20, B=64,
+               enc=None, label="gym DT hopper-shaped: state_dim=11 act_dim=3 K=20 embed=128 3 layers 1 head batch=64"),
+    "c2": dict(dt=dict(state_dim=1024, act_dim=4, hidden_size=128, n_layer=3, n_head=1, activation_function="relu", action_tanh=False), K=30, B=64,
+               enc=dict(frame_shape=(3, 64, 64), audio_shape=(1, 64, 64)),
+               label="Minecraft2d multimodal DT: 64x64 RGB frame CNN + audio spectrogram encoder, K=30 embed=128 3 layers, batch=64/GPU"),
+    "c3": dict(dt=dict(state_dim=1024, act_dim=18, hidden_size=256, n_layer=6, n_head=8, activation_function="relu", action_tanh=False), K=50, B=64,
+               enc=dict(frame_shape=(3, 64, 64), audio_shape=(2, 64, 64)),
+               label="Skeleton+ stereo-audio DT: 2-channel spectrogram + video encoder, K=50 embed=256 6 layers 8 heads, batch=64/GPU"),
+    "c4": dict(dt=dict(state_dim=11, act_dim=3, hidden_size=768, n_layer=12, n_head=12, activation_function="gelu_new", action_tanh=True), K=200,
+               B=256, enc=None, label="scaled DT: K=200 embed=768 12 layers 12 heads bf16 training batch=256"),
+}
+MAX_EP_LEN = 1000
+
+
+def make_batch(wl, B, seed):
+    """Seeded synthetic trajectories of SURVEY.md §8d, on the host."""
+    from util import make_inputs
+
+    dt = wl["dt"]
+    onehot = not dt["action_tanh"]
+    s, a, r, t, m = make_inputs(B, wl["K"], dt["state_dim"] if wl["enc"] is None else 4, dt["act_dim"], MAX_EP_LEN, seed=seed, onehot_actions=onehot)
+    out = dict(actions=a, rtg=r, timesteps=t, mask=m)
+    if wl["enc"] is None:
+        out["states"] = s
+    else:
+        g = torch.Generator().manual_seed(seed + 99)
+        K = wl["K"]
+        out["frames"] = (torch.randint(0, 256, (B, K, *wl["enc"]["frame_shape"]), generator=g, dtype=torch.uint8).float() / 255.0) * 2 - 1
+        out["audio"] = torch.randn(B, K, *wl["enc"]["audio_shape"], generator=g).clamp_(-1, 1)
+    return out
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+
+    Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.index, self.samples, self._stop, self._t = index, [], threading.Event(), None
+
+    def start(self):
+        def run():
+            while not self._stop.is_set():
+                try:
+                    o = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i", str(self.index)],
+                                       capture_output=True, text=True, timeout=5).stdout.strip()
+                    if o:
+                        self.samples.append([x.strip() for x in o.split(",")])
+                except Exception:
+                    pass
+                self._stop.wait(0.2)
+
+        self._t = threading.Thread(target=run, daemon=True)
+        self._t.start()
+
+    def stop(self):
+        self._stop.set()
+        if self._t:
+            self._t.join(timeout=6)
+        mhz = sorted(int(s[0]) for s in self.samples if s and s[0].isdigit())
+        mx = [int(s[1]) for s in self.samples if len(s) > 1 and s[1].isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({n for s in self.samples for n, v in zip(names, s[2:6]) if v.strip().lower() == "active"})
+        return {"sm_mhz": mhz[len(mhz) // 2] if mhz else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
+                "samples": len(self.samples)}
+
+
+# ------------------------------------------------------------------------------------------------------------------------------
+# our arm
+# ------------------------------------------------------------------------------------------------------------------------------
+def build_ours(wl, dev):
+    from mtrl_b200.encoder import MultimodalDecisionTransformer, MultimodalStateEncoder
+    from mtrl_b200.model import DecisionTransformer
+
+    torch.manual_seed(0)  # shared seed -> identical replicas (ppo_atari_multigpu.py:200); broadcast below makes it strict
+    dt = DecisionTransformer(max_length=wl["K"], max_ep_len=MAX_EP_LEN, resid_pdrop=0.0, attn_pdrop=0.0, device=dev, **wl["dt"])
+    if wl["enc"] is None:
+        return dt, [dt]
+    enc = MultimodalStateEncoder(wl["enc"]["frame_shape"], wl["enc"]["audio_shape"], "big", "concat", 1.0 / 255.0, device=dev)
+    return MultimodalDecisionTransformer(enc, dt), [dt, enc]
+
+
+def make_step(wl, model, parts, dev_in, reducer, grad_scale):
+    """Returns step() -> device tensor [loss, n_valid]: forward + masked action MSE + backward (+ overlapped all-reduce)."""
+    d = dev_in
+    if wl["enc"] is None:
+        dt = parts[0]
+        cb = None if reducer is None else (lambda stage, b, e: reducer.ready(dt.flat_grads, b, e))
+
+        def step():
+            out = model.loss_and_backward(d["states"], d["actions"], d["rtg"], d["timesteps"], d["mask"], grad_scale=grad_scale, on_stage_done=cb)
+            if reducer is not None:
+                reducer.finish()
+            return out
+    else:
+        dt, enc = parts
+        cb = None if reducer is None else (lambda stage, b, e: reducer.ready(enc.flat_grads if stage == "encoder" else dt.flat_grads, b, e))
+
+        def step():
+            out = model.loss_and_backward(d["frames"], d["audio"], d["actions"], d["rtg"], d["timesteps"], d["mask"], grad_scale=grad_scale,
+                                          on_stage_done=cb)
+            if reducer is not None:
+                reducer.finish()
+            return out
+    return step
+
+
+def timed_loop(fn, steps, dev, flush=None, dist_on=False):
+    """K steps, each bracketed by CUDA events on the launching stream; barrier + synchronize on both sides; max over ranks."""
+    import torch.distributed as dist
+
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+    if dist_on:
+        dist.barrier()
+    torch.cuda.synchronize(dev)
+    t0 = time.perf_counter()
+    for i in range(steps):
+        if flush is not None:
+            flush.zero_()
+        ev[i][0].record()
+        fn()
+        ev[i][1].record()
+    torch.cuda.synchronize(dev)
+    wall = time.perf_counter() - t0
+    if dist_on:
+        dist.barrier()
+    if flush is None:  # contiguous region: first start -> last end (includes launch gaps)
+        total_ms = ev[0][0].elapsed_time(ev[-1][1])
+    else:  # flush kernels sit between the per-step brackets and are excluded
+        total_ms = sum(a.elapsed_time(b) for a, b in ev)
+    if dist_on:
+        t = torch.tensor([total_ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        total_ms = float(t.item())
+    return total_ms / steps, wall / steps * 1e3
+
+
+def algorithmic_flops_per_step(wl, B):
+    """fwd+bwd FLOPs of one step: trunk 3 * tokens * L * (8H^2 + 4HI + 2TH) (causal attention counted half),
+    towers 3x forward (conv1 has no dgrad: 2x)."""
+    dt, K = wl["dt"], wl["K"]
+    H, L, T = dt["hidden_size"], dt["n_layer"], 3 * K
+    inner = 4 * H
+    trunk = 3.0 * B * T * L * (8 * H * H + 4 * H * inner + 2 * T * H)
+    towers = 0.0
+    if wl["enc"] is not None:
+        for shape in (wl["enc"]["frame_shape"], wl["enc"]["audio_shape"]):
+            c, h, w = shape
+            specs, f = [(32, 8, 4), (64, 4, 2), (64, 3, 1)], 0.0
+            for i, (co, k, s) in enumerate(specs):
+                h, w = (h - k) // s + 1, (w - k) // s + 1
+                f += (2.0 if i == 0 else 3.0) * 2 * h * w * co * k * k * c
+                c = co
+            f += 3.0 * 2 * c * h * w * 512
+            towers += f * B * K
+        towers += 3.0 * 2 * B * K * dt["state_dim"] * H  # embed_state projection of the wide state
+    return trunk + towers
+
+
+def run_ours(args, wl, rank, world, local_rank):
+    import torch.distributed as dist
+
+    from mtrl_b200 import _lib
+    from mtrl_b200.dp import GradAllReducer, broadcast_parameters, replicas_consistent
+
+    dev = torch.device("cuda", local_rank)
+    torch.cuda.set_device(dev)
+    lib = _lib.load()
+    _lib.check(lib.dtb_check_device())
+    B, K = wl["B"], wl["K"]
+    model, parts = build_ours(wl, dev)
+    broadcast_parameters([p.flat_params for p in parts])
+    host = make_batch(wl, B, seed=1234 + rank)  # per-rank data seeds (ppo_atari_multigpu.py:197-199); weak scaling: B per GPU fixed
+    pinned = {k: v.contiguous().pin_memory() for k, v in host.items()}
+    dev_in = {k: torch.empty_like(v, device=dev) for k, v in pinned.items()}
+    for k in pinned:
+        dev_in[k].copy_(pinned[k], non_blocking=True)
+    reducer = GradAllReducer(bucket_bytes=args.bucket_mb << 20) if world > 1 else None
+    raw_step = make_step(wl, model, parts, dev_in, reducer, 1.0 / world)
+
+    def step():
+        for p in parts:
+            p._staged_version = -1  # fp32 -> bf16 weight staging is part of every timed step
+        return raw_step()
+
+    h2d = sum(v.numel() * v.element_size() for v in pinned.values())
+    for _ in range(max(args.warmup, 3)):
+        out = step()
+    torch.cuda.synchronize(dev)
+    l0 = lib.dtb_launch_count()
+    out = step()
+    torch.cuda.synchronize(dev)
+    launches_per_step = int(lib.dtb_launch_count() - l0)
+
+    fn, graphed = step, False
+    if world == 1 and not args.no_graph:
+        try:
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                gout = step()
+            g.replay()
+            torch.cuda.synchronize(dev)
+            fn, out, graphed = g.replay, gout, True
+        except Exception as e:  # noqa: BLE001
+            print(f"[bench] CUDA graph capture failed ({e}); timing plain launches", file=sys.stderr)
+            torch.cuda.synchronize(dev)
+    # working set per step (inputs + saved activations) vs the 126 MB L2
+    ws_bytes = h2d + sum(sum(w.numel() for w in p._ws.values()) for p in parts)
+    flush = None
+    if ws_bytes < 2 * 126e6 or args.flush_l2:
+        flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    for _ in range(args.warmup):
+        fn()
+    clocks = ClockSampler(local_rank)
+    if rank == 0:
+        clocks.start()
+    ms, wall_ms = timed_loop(fn, args.steps, dev, flush, dist_on=world > 1)
+    tokens = B * 3 * K * world
+    value = tokens / ms * 1e3
+
+    # ---- e2e: pinned host buffers -> H2D -> step -> loss D2H, every step ----
+    loss_host = torch.empty(2, dtype=torch.float32).pin_memory()
+
+    def e2e_step():
+        for k in pinned:
+            dev_in[k].copy_(pinned[k], non_blocking=True)
+        o = fn() if graphed else step()
+        loss_host.copy_(out if graphed else o, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        return float(loss_host[0])
+
+    for _ in range(2):
+        e2e_step()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize(dev)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        loss_val = e2e_step()
+    torch.cuda.synchronize(dev)
+    e2e_ms = (time.perf_counter() - t0) / args.steps * 1e3
+    if world > 1:
+        t = torch.tensor([e2e_ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_ms = float(t.item())
+    clock_info = clocks.stop() if rank == 0 else None
+    consistent = replicas_consistent([p.flat_params for p in parts])
+
+    res = {
+        "metric": "DT train tokens/s (fwd+bwd)", "value": value, "unit": "tokens/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+        "config": {"workload": wl["label"], "name": args.workload, "batch_per_gpu": B, "global_batch": B * world, "seq_len": 3 * K,
+                   "parallelism": f"dp{world}", "cuda_graph": graphed, "dropout": 0.0,
+                   "l2": ("explicit 256 MiB flush between steps" if flush is not None else
+                          f"no flush: per-step working set {ws_bytes / 1e6:.0f} MB > 126 MB L2"),
+                   "timed": "weight staging + forward + masked action MSE + backward" + (" + overlapped NCCL all-reduce" if world > 1 else "")},
+        "e2e": {"value": tokens / e2e_ms * 1e3, "unit": "tokens/s", "ms_per_step": e2e_ms, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 8,
+                "host_format": "fp32 pinned buffers in the reference's layouts"},
+        "gpu_launches": launches_per_step * args.steps, "launches_per_step": launches_per_step,
+        "clocks": clock_info, "loss": loss_val, "wall_ms_per_step": wall_ms,
+        "algorithmic_tflops_per_s": algorithmic_flops_per_step(wl, B * world) / ms / 1e9, "replicas_consistent": consistent,
+    }
+    return res, dict(model=model, parts=parts, dev=dev, dev_in=dev_in, step=step)
+
+
+# ------------------------------------------------------------------------------------------------------------------------------
+# CPU arm: the fp32 oracle on the host cores (cpu_baseline of our line, and the whole `--impl reference` run)
+# ------------------------------------------------------------------------------------------------------------------------------
+def build_oracle(wl):
+    from oracle.decision_transformer import DecisionTransformer as ODT
+    from oracle.encoders import MultimodalDecisionTransformer as OMM
+    from oracle.encoders import MultimodalStateEncoder as OEnc
+
+    torch.manual_seed(0)
+    dt = ODT(max_length=wl["K"], max_ep_len=MAX_EP_LEN, resid_pdrop=0.0, attn_pdrop=0.0, **wl["dt"])
+    if wl["enc"] is None:
+        return dt
+    return OMM(OEnc(wl["enc"]["frame_shape"], wl["enc"]["audio_shape"], "big", "concat", 1.0 / 255.0), dt)
+
+
+def oracle_step(wl, model, b):
+    from oracle.trainer import masked_action_mse
+
+    model.zero_grad(set_to_none=True)
+    if wl["enc"] is None:
+        _, ap, _ = model(b["states"], b["actions"], None, b["rtg"], b["timesteps"], b["mask"])
+    else:
+        _, ap, _ = model(b["frames"], b["audio"], b["actions"], None, b["rtg"], b["timesteps"], b["mask"])
+    loss = masked_action_mse(ap, b["actions"], b["mask"])
+    loss.backward()
+    return float(loss.detach())
+
+
+def run_cpu(wl, steps, warmup, budget_s=20.0):
+    """Times the oracle on all host threads on a bounded sample: the same workload at a reduced batch chosen so that
+    warmup + steps fit in ~budget_s; tokens/s = sample tokens / time (linear in batch)."""
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    model = build_oracle(wl)
+    K = wl["K"]
+    Bs = min(wl["B"], 4)
+    b = make_batch(wl, Bs, seed=1234)
+    t0 = time.perf_counter()
+    oracle_step(wl, model, b)
+    probe = time.perf_counter() - t0  # includes first-call overheads: conservative
+    t0 = time.perf_counter()
+    oracle_step(wl, model, b)
+    probe = min(probe, time.perf_counter() - t0)
+    per_traj = probe / Bs
+    want = budget_s / max(1, steps + warmup) / max(per_traj, 1e-6)
+    Bs = int(max(1, min(wl["B"], want)))
+    b = make_batch(wl, Bs, seed=1234)
+    for _ in range(warmup):
+        oracle_step(wl, model, b)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        loss = oracle_step(wl, model, b)
+    dt_s = (time.perf_counter() - t0) / steps
+    tokens = Bs * 3 * K
+    return {"value": tokens / dt_s, "unit": "tokens/s", "cores": cores, "kind": "port", "ms_per_step": dt_s * 1e3,
+            "sample": f"fp32 PyTorch oracle (towers = reference conv_factory math), fwd+loss+bwd, batch {Bs} of {wl['B']} trajectories x K={K} "
+                      f"({tokens} tokens/step), {steps} steps after {warmup} warm-up, {cores} threads", "loss": loss}
+
+
+def measure_roofline(args, wl, ctx):
+    """Dominant kernel timed alone with CUDA events (filled in once the ncu launch list names it)."""
+    return None
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--batch", type=int, default=0, help="per-GPU batch override (default: the workload's)")
+    ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--flush-l2", action="store_true")
+    ap.add_argument("--bucket-mb", type=int, default=8)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-roofline", action="store_true")
+    args = ap.parse_args()
+    wl = dict(WORKLOADS[args.workload])
+    if args.batch:
+        wl["B"] = args.batch
+    rank, world, local_rank = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
+
+    if args.impl == "reference":
+        if rank != 0:
+            return
+        steps, warmup = min(args.steps, 10), min(args.warmup, 2)
+        r = run_cpu(wl, steps, max(warmup, 1), budget_s=60.0)
+        line = {"impl": "reference", "metric": "DT train tokens/s (fwd+bwd)", "value": r["value"], "unit": "tokens/s", "n_gpus": args.gpus,
+                "steps": steps, "warmup": max(warmup, 1), "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": {"workload": wl["label"], "name": args.workload, "seq_len": 3 * wl["K"], "parallelism": "cpu"},
+                "cpu_baseline": r, "e2e": {"value": r["value"], "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                "gpu_launches": 0,
+                "note": "the reference's own DT source is an un-vendored empty submodule (SURVEY.md F1); this arm is the fp32 PyTorch oracle, "
+                        "whose towers are numerically the reference's conv_factory, on the host cores"}
+        print(json.dumps(line), flush=True)
+        return
+
+    import torch.distributed as dist
+
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    res, ctx = run_ours(args, wl, rank, world, local_rank)
+    if rank == 0:
+        if not args.no_roofline:
+            try:
+                res["roofline"] = measure_roofline(args, wl, ctx)
+            except Exception as e:  # noqa: BLE001
+                res["roofline"] = {"error": str(e)}
+        if world == 1 and not args.no_cpu_baseline:
+            res["cpu_baseline"] = run_cpu(wl, 3, 1, budget_s=20.0)
+        print(json.dumps(res), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

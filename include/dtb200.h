@@ -36,6 +36,8 @@ int dtb_abi_version(void);
 const char* dtb_last_error(void);
 /* 0 iff the current CUDA device is sm_100 (no fallback path exists on other devices). */
 int dtb_check_device(void);
+/* Number of kernels this library has launched in this process (the bench's gpu_launches evidence). */
+long long dtb_launch_count(void);
 
 /* ---- tensor-core GEMM (tcgen05 + TMEM + TMA) --------------------------------------------------
  * D[M,N] = epilogue(A x B^T-style product), bf16 operands, fp32 accumulation.

@@ -46,6 +46,7 @@ def _declare(lib):
     vp, i, f, sz, ll = C.c_void_p, C.c_int, C.c_float, C.c_size_t, C.c_longlong
     lib.dtb_last_error.restype = C.c_char_p
     lib.dtb_abi_version.restype = i
+    lib.dtb_launch_count.restype = ll
     for name in ("dtb_layernorm_bwd_scratch_floats", "dtb_colsum_scratch_floats", "dtb_mse_scratch_floats"):
         getattr(lib, name).restype = sz
     lib.dtb_dt_create.argtypes = [C.POINTER(DtConfig), C.POINTER(vp)]

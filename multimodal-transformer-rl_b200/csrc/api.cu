@@ -16,6 +16,7 @@ extern "C" {
 int dtb_abi_version(void) { return DTB_ABI_VERSION; }
 const char* dtb_last_error(void) { return dtb::last_error(); }
 int dtb_check_device(void) { return dtb::require_sm100(); }
+long long dtb_launch_count(void) { return dtb::launch_count(); }
 
 int dtb_gemm_bf16(void* stream, const void* A, int lda, int a_mn_major, const void* B, int ldb, int b_mn_major, int M, int N, int K,
                   const dtb_gemm_epilogue* e, int split_k, int bn_override) {

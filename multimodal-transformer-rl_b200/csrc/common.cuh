@@ -31,6 +31,7 @@ int cuda_fail(cudaError_t e, const char* what, const char* file, int line);
 
 #define DTB_CHECK_LAUNCH()                                                    \
   do {                                                                        \
+    ::dtb::count_launch();                                                    \
     cudaError_t _e = cudaGetLastError();                                      \
     if (_e != cudaSuccess) return ::dtb::cuda_fail(_e, "kernel launch", __FILE__, __LINE__); \
   } while (0)
@@ -50,6 +51,8 @@ int cuda_fail(cudaError_t e, const char* what, const char* file, int line);
   } while (0)
 
 int num_sms();
+void count_launch();
+long long launch_count();
 
 typedef __nv_bfloat16 bf16;
 typedef __nv_bfloat162 bf162;

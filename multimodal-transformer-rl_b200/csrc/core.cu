@@ -22,6 +22,10 @@ int cuda_fail(cudaError_t e, const char* what, const char* file, int line) {
   return DTB_ERR_CUDA;
 }
 
+static long long g_launches = 0;
+void count_launch() { __atomic_add_fetch(&g_launches, 1, __ATOMIC_RELAXED); }
+long long launch_count() { return __atomic_load_n(&g_launches, __ATOMIC_RELAXED); }
+
 static int g_num_sms = 0;
 int num_sms() {
   if (g_num_sms > 0) return g_num_sms;
