@@ -91,7 +91,7 @@ int dtb_attention_bwd(void* stream, const void* qkv, const float* mask, const vo
 
 /* ---- weight staging + bias gradients -----------------------------------------------------------------------------
  * cast_transpose: fp32 [R,C] -> bf16 [R,C] (dst, may be NULL) and bf16 [C,R] (dst_t, may be NULL).
- * colsum: out[N] (+)= column sums of bf16 x [M,N] (row stride ld); scratch fp32 dtb_colsum_scratch_floats(N). */
+ * colsum: out[N] (+)= column sums of bf16 x [M,N] (row stride ld; N, ld multiples of 8); scratch fp32 dtb_colsum_scratch_floats(N). */
 int dtb_cast_transpose(void* stream, const float* src, int R, int C, void* dst, void* dst_t);
 size_t dtb_colsum_scratch_floats(int N);
 int dtb_colsum_bf16(void* stream, const void* x, int M, int N, int ld, float* out, int accumulate, float* scratch);

@@ -53,58 +53,73 @@ int cast_bf16(cudaStream_t stream, const float* src, size_t n, bf16* dst) {
 }
 
 // ---- column sums (bias gradients): x bf16 [M, N] -> out fp32 [N] --------------------------------
-// Stage 1: grid (N/64 column groups, row slabs); each thread owns 2 adjacent columns and strides rows,
-//          then the 8 row-lanes of the block are reduced through shared memory -> scratch[slab][N].
-// Stage 2: sum the slabs in index order (deterministic).
-constexpr int CS_SLABS_MAX = 256;
+// Stage 1: grid (column groups, row slabs); each thread owns 8 adjacent columns (one 128-bit load per row) and strides rows;
+//          the row-lanes of the block are reduced through shared memory in index order -> scratch[slab][N].
+// Stage 2: 32 columns x 8 row-lanes per block sum the slabs, lanes combined in index order (deterministic).
+constexpr int CS_SLABS_MAX = 64;
 
-__global__ void colsum_stage1(const bf16* __restrict__ x, int M, int N, int ld, float* __restrict__ scratch) {
-  __shared__ float2 red[8][32];
-  const int col = blockIdx.x * 64 + threadIdx.x * 2;
+__global__ void __launch_bounds__(256) colsum_stage1(const bf16* __restrict__ x, int M, int N, int ld, float* __restrict__ scratch) {
+  __shared__ float red[256][9];
+  const int cx = blockDim.x, ry = blockDim.y;
+  const int col = (blockIdx.x * cx + threadIdx.x) * 8;
   const int slab = blockIdx.y, nslab = gridDim.y;
-  float2 acc = make_float2(0.f, 0.f);
+  float acc[8];
+#pragma unroll
+  for (int e = 0; e < 8; ++e) acc[e] = 0.f;
   if (col < N) {
-    for (int r = slab * 8 + threadIdx.y; r < M; r += nslab * 8) {
-      uint32_t u = __ldg(reinterpret_cast<const uint32_t*>(x + (size_t)r * ld + col));
-      float2 v = unpack_bf16x2(u);
-      acc.x += v.x;
-      acc.y += v.y;
+    for (int r = slab * ry + threadIdx.y; r < M; r += nslab * ry) {
+      const uint4 u = ldg_u4(x + (size_t)r * ld + col);
+      const float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y), c = unpack_bf16x2(u.z), d = unpack_bf16x2(u.w);
+      acc[0] += a.x; acc[1] += a.y; acc[2] += b.x; acc[3] += b.y; acc[4] += c.x; acc[5] += c.y; acc[6] += d.x; acc[7] += d.y;
     }
   }
-  red[threadIdx.y][threadIdx.x] = acc;
+  const int tid = threadIdx.y * cx + threadIdx.x;
+#pragma unroll
+  for (int e = 0; e < 8; ++e) red[tid][e] = acc[e];
   __syncthreads();
   if (threadIdx.y == 0 && col < N) {
+    for (int i = 1; i < ry; ++i)
 #pragma unroll
-    for (int i = 1; i < 8; ++i) {
-      acc.x += red[i][threadIdx.x].x;
-      acc.y += red[i][threadIdx.x].y;
-    }
-    scratch[(size_t)slab * N + col] = acc.x;
-    scratch[(size_t)slab * N + col + 1] = acc.y;
+      for (int e = 0; e < 8; ++e) acc[e] += red[i * cx + threadIdx.x][e];
+    float* dst = scratch + (size_t)slab * N + col;
+    *reinterpret_cast<float4*>(dst) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+    *reinterpret_cast<float4*>(dst + 4) = make_float4(acc[4], acc[5], acc[6], acc[7]);
   }
 }
 
-__global__ void colsum_stage2(const float* __restrict__ scratch, int nslab, int N, float* __restrict__ out, int accumulate) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= N) return;
+__global__ void __launch_bounds__(256) colsum_stage2(const float* __restrict__ scratch, int nslab, int N, float* __restrict__ out,
+                                                     int accumulate) {
+  __shared__ float red[8][33];
+  const int c = blockIdx.x * 32 + threadIdx.x;
   float s = 0.f;
-  for (int i = 0; i < nslab; ++i) s += scratch[(size_t)i * N + c];
-  out[c] = accumulate ? out[c] + s : s;
+  if (c < N)
+    for (int i = threadIdx.y; i < nslab; i += 8) s += scratch[(size_t)i * N + c];
+  red[threadIdx.y][threadIdx.x] = s;
+  __syncthreads();
+  if (threadIdx.y == 0 && c < N) {
+    for (int i = 1; i < 8; ++i) s += red[i][threadIdx.x];
+    out[c] = accumulate ? out[c] + s : s;
+  }
 }
 
 size_t colsum_scratch_floats(int N) { return (size_t)CS_SLABS_MAX * N; }
 
 int colsum_bf16(cudaStream_t stream, const bf16* x, int M, int N, int ld, float* out, int accumulate, float* scratch) {
-  DTB_REQUIRE(N % 2 == 0 && ld % 2 == 0, DTB_ERR_BAD_ARG, "colsum: N and ld must be even");
-  const int colgroups = (N + 63) / 64;
-  int nslab = (4 * num_sms() + colgroups - 1) / colgroups;
-  const int max_slab = (M + 63) / 64;
+  DTB_REQUIRE(N % 8 == 0 && ld % 8 == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0, DTB_ERR_BAD_ARG,
+              "colsum: N and ld must be multiples of 8 and x 16-byte aligned (N=%d ld=%d)", N, ld);
+  const int n8 = N / 8;
+  int cx = 4;
+  while (cx < 32 && cx < n8) cx *= 2;
+  const int ry = 256 / cx;
+  const int colgroups = (n8 + cx - 1) / cx;
+  int nslab = (2 * num_sms() + colgroups - 1) / colgroups;
+  const int max_slab = (M + 4 * ry - 1) / (4 * ry);
   if (nslab > max_slab) nslab = max_slab;
   if (nslab > CS_SLABS_MAX) nslab = CS_SLABS_MAX;
   if (nslab < 1) nslab = 1;
-  colsum_stage1<<<dim3(colgroups, nslab), dim3(32, 8), 0, stream>>>(x, M, N, ld, scratch);
+  colsum_stage1<<<dim3(colgroups, nslab), dim3(cx, ry), 0, stream>>>(x, M, N, ld, scratch);
   DTB_CHECK_LAUNCH();
-  colsum_stage2<<<(N + 255) / 256, 256, 0, stream>>>(scratch, nslab, N, out, accumulate);
+  colsum_stage2<<<(N + 31) / 32, dim3(32, 8), 0, stream>>>(scratch, nslab, N, out, accumulate);
   DTB_CHECK_LAUNCH();
   return DTB_OK;
 }

@@ -137,18 +137,26 @@ __global__ void __launch_bounds__(256) ln_bwd_kernel(const bf16* __restrict__ dy
   for (int i = threadIdx.x; i < 2 * H; i += blockDim.x) scratch[(size_t)blockIdx.x * 2 * H + i] = sred[i];
 }
 
-__global__ void ln_bwd_finalize(const float* __restrict__ scratch, int nblk, int H, float* __restrict__ dgamma, float* __restrict__ dbeta) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= 2 * H) return;
+// 32 columns x 8 row-lanes per block; lanes combined in index order (deterministic).
+__global__ void __launch_bounds__(256) ln_bwd_finalize(const float* __restrict__ scratch, int nblk, int H, float* __restrict__ dgamma,
+                                                       float* __restrict__ dbeta) {
+  __shared__ float red[8][33];
+  const int c = blockIdx.x * 32 + threadIdx.x;
   float s = 0.f;
-  for (int b = 0; b < nblk; ++b) s += scratch[(size_t)b * 2 * H + c];
-  if (c < H) dgamma[c] = s;
-  else dbeta[c - H] = s;
+  if (c < 2 * H)
+    for (int b = threadIdx.y; b < nblk; b += 8) s += scratch[(size_t)b * 2 * H + c];
+  red[threadIdx.y][threadIdx.x] = s;
+  __syncthreads();
+  if (threadIdx.y == 0 && c < 2 * H) {
+    for (int i = 1; i < 8; ++i) s += red[i][threadIdx.x];
+    if (c < H) dgamma[c] = s;
+    else dbeta[c - H] = s;
+  }
 }
 
 static int ln_bwd_blocks(int M) {
   int b = (M + 7) / 8;
-  const int cap = num_sms() * 4;
+  const int cap = num_sms() * 2;
   return b > cap ? cap : (b < 1 ? 1 : b);
 }
 size_t ln_bwd_scratch_floats(int H) { return (size_t)DTB_NUM_SMS_FALLBACK * 8 * 2 * H; }
@@ -159,7 +167,7 @@ int ln_bwd(cudaStream_t stream, const bf16* dy, const float* x, const float* mea
   const int blocks = ln_bwd_blocks(M);
   ln_bwd_kernel<<<blocks, 256, 2 * H * sizeof(float), stream>>>(dy, x, mean, rstd, gamma, dres, M, H, dx_out, dx_out_bf16, scratch);
   DTB_CHECK_LAUNCH();
-  ln_bwd_finalize<<<(2 * H + 255) / 256, 256, 0, stream>>>(scratch, blocks, H, dgamma, dbeta);
+  ln_bwd_finalize<<<(2 * H + 31) / 32, dim3(32, 8), 0, stream>>>(scratch, blocks, H, dgamma, dbeta);
   DTB_CHECK_LAUNCH();
   return DTB_OK;
 }
