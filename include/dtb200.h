@@ -199,8 +199,10 @@ int dtb_encoder_stage_params(const dtb_encoder* e, void* stream, const float* pa
 int dtb_encoder_forward(const dtb_encoder* e, void* stream, const float* params, const void* staged_bf16, int N, const float* frames,
                         const float* audio, void* workspace, size_t workspace_bytes, void* states_bf16);
 /* d_states_bf16 [N, state_dim]; d_states_masked != 0 when it is already multiplied by (states > 0) (dtb_dt_backward does this when
- * dtb_dt_batch.states_relu is set); otherwise states_bf16 must be given and d_states_bf16 is masked IN PLACE.  Overwrites grads. */
-int dtb_encoder_backward(const dtb_encoder* e, void* stream, const float* params, const void* staged_bf16, int N, const void* states_bf16,
+ * dtb_dt_batch.states_relu is set); otherwise states_bf16 must be given and d_states_bf16 is masked IN PLACE.  frames / audio are the forward inputs again (the
+ * implicit-GEMM conv1 weight gradient re-gathers its patches from them instead of saving them).  Overwrites grads. */
+int dtb_encoder_backward(const dtb_encoder* e, void* stream, const float* params, const void* staged_bf16, int N, const float* frames,
+                         const float* audio, const void* states_bf16,
                          const void* d_states_bf16, int d_states_masked, void* workspace, size_t workspace_bytes, float* grads);
 
 #ifdef __cplusplus

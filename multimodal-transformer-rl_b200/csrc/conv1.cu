@@ -1,0 +1,305 @@
+// Implicit-GEMM first convolution of the frame / spectrogram towers on tcgen05 (REF src/agents.py:33, :46: Conv2d(C, 32|16, 8, stride=4)).
+// The 8x8xC patches are never written to HBM: producer warps read the fp32 NCHW input (the reference's obs layout), apply the
+// `/255` input scale, convert to bf16 and store straight into the 128B-swizzled shared-memory tile the tensor core reads;
+// K order (c, kh, kw) = PyTorch's weight order, one 64-wide k-block (= one 128-byte swizzle row) per input channel.
+//   forward : Y[rows, cout] = relu(P W^T + b)          P tile = A operand (K-major), weights resident in smem via TMA
+//   wgrad   : dW[cout, 64C] = dZ^T P                   P tile = B operand (MN-major: the very same smem image), dZ^T via TMA,
+//             fp32 accumulators for all C k-blocks stay in TMEM across the CTA's whole row range; per-CTA partials reduced in order.
+// HBM-bound by construction (N = 32): algorithmic bytes = input read once + output written once.
+#include "kernels.h"
+#include <string.h>
+
+namespace dtb {
+
+constexpr int C1_THREADS = 288;  // warps 0-3 patch producers, warps 4-7 epilogue (TMEM quadrant = warp & 3), warp 8 MMA + TMEM alloc
+constexpr int C1_MAXC = 4;
+constexpr int C1_KB_BYTES = 128 * 128;  // one k-block of a 128-row tile
+
+struct Conv1Params {
+  const float* x;
+  int N, C, H, W, stride, ho, wo, cout;
+  long long rows;
+  int tiles, stages;
+  float scale;
+  const float* bias;
+  bf16* y;          // forward output [rows, cout]
+  float* partial;   // wgrad: [grid][cout][64C]
+};
+
+// Gather one patch row (all C k-blocks) into the swizzled tile: row r of k-block c lives at c*16KB + r*128, 16-byte chunk kh at (kh ^ (r & 7)).
+__device__ __forceinline__ void c1_gather_row(const Conv1Params& p, uint8_t* stage, int r, long long m) {
+  const bool valid = m < p.rows;
+  int n = 0, oh = 0, ow = 0;
+  if (valid) {
+    ow = (int)(m % p.wo);
+    const long long t = m / p.wo;
+    oh = (int)(t % p.ho);
+    n = (int)(t / p.ho);
+  }
+  const uint32_t dst0 = smem_u32(stage) + r * 128;
+  for (int c = 0; c < p.C; ++c) {
+    const float* src = p.x + (((size_t)n * p.C + c) * p.H + (size_t)oh * p.stride) * p.W + (size_t)ow * p.stride;
+    float4 a[8], b[8];
+#pragma unroll
+    for (int kh = 0; kh < 8; ++kh) {
+      if (valid) {
+        a[kh] = ldg_f4(src + (size_t)kh * p.W);
+        b[kh] = ldg_f4(src + (size_t)kh * p.W + 4);
+      } else {
+        a[kh] = make_float4(0.f, 0.f, 0.f, 0.f);
+        b[kh] = a[kh];
+      }
+    }
+#pragma unroll
+    for (int kh = 0; kh < 8; ++kh) {
+      const uint32_t addr = dst0 + c * C1_KB_BYTES + ((kh ^ (r & 7)) << 4);
+      const float s = p.scale;
+      asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(pack_bf16x2(a[kh].x * s, a[kh].y * s)),
+                   "r"(pack_bf16x2(a[kh].z * s, a[kh].w * s)), "r"(pack_bf16x2(b[kh].x * s, b[kh].y * s)),
+                   "r"(pack_bf16x2(b[kh].z * s, b[kh].w * s))
+                   : "memory");
+    }
+  }
+}
+
+__global__ void __launch_bounds__(C1_THREADS, 1) conv1_fwd_kernel(const __grid_constant__ CUtensorMap tmW, const Conv1Params p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int wkb = p.cout * 128;  // bytes of one weight k-block
+  uint8_t* smW = smem;                                       // [C][cout rows][128 B]
+  uint8_t* smA = smem + ((p.C * wkb + 1023) & ~1023);        // [stages][C][128 rows][128 B]
+  const int stage_bytes = p.C * C1_KB_BYTES;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smA + (size_t)p.stages * stage_bytes);
+  uint64_t* full_bar = bars;             // [stages] producers -> MMA
+  uint64_t* empty_bar = bars + 4;        // [stages] MMA -> producers
+  uint64_t* tfull_bar = bars + 8;        // [2]
+  uint64_t* tempty_bar = bars + 10;      // [2]
+  uint64_t* w_bar = bars + 12;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 13);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < p.stages; ++s) { mbar_init(&full_bar[s], 128); mbar_init(&empty_bar[s], 1); }
+    for (int s = 0; s < 2; ++s) { mbar_init(&tfull_bar[s], 1); mbar_init(&tempty_bar[s], 4); }
+    mbar_init(w_bar, 1);
+    fence_mbar_init();
+  }
+  if (warp == 8) { tmem_alloc(tmem_slot, 64); tmem_relinquish(); }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp < 4) {
+    // ===== patch producers: thread t owns tile row t =====
+    uint32_t stage = 0, phase = 0;
+    for (int t = blockIdx.x; t < p.tiles; t += gridDim.x) {
+      mbar_wait(&empty_bar[stage], phase ^ 1);
+      c1_gather_row(p, smA + (size_t)stage * stage_bytes, threadIdx.x, (long long)t * 128 + threadIdx.x);
+      fence_proxy_async();  // generic-proxy stores -> visible to the tensor core (async proxy)
+      mbar_arrive(&full_bar[stage]);
+      if (++stage == (uint32_t)p.stages) { stage = 0; phase ^= 1; }
+    }
+  } else if (warp == 8) {
+    if (lane == 0) {
+      tma_prefetch_desc(&tmW);
+      mbar_arrive_expect_tx(w_bar, (uint32_t)(p.C * wkb));
+      for (int c = 0; c < p.C; ++c) tma_load_2d(smW + c * wkb, &tmW, w_bar, c * 64, 0);
+      mbar_wait(w_bar, 0);
+      const uint32_t idesc = make_idesc_bf16(128, p.cout, 0, 0);
+      uint32_t stage = 0, phase = 0, acc = 0, acc_phase = 0;
+      for (int t = blockIdx.x; t < p.tiles; t += gridDim.x) {
+        mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
+        mbar_wait(&full_bar[stage], phase);
+        tc_fence_after();
+        const uint32_t a0 = smem_u32(smA + (size_t)stage * stage_bytes), w0 = smem_u32(smW);
+        for (int c = 0; c < p.C; ++c)
+#pragma unroll
+          for (int kk = 0; kk < 4; ++kk)
+            umma_bf16(tmem_base + acc * 32, make_smem_desc_sw128(a0 + c * C1_KB_BYTES + kk * 32, 16, 1024),
+                      make_smem_desc_sw128(w0 + c * wkb + kk * 32, 16, 1024), idesc, (c > 0 || kk > 0) ? 1u : 0u);
+        umma_commit(&empty_bar[stage]);
+        umma_commit(&tfull_bar[acc]);
+        if (++stage == (uint32_t)p.stages) { stage = 0; phase ^= 1; }
+        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+      }
+    }
+  } else {
+    // ===== epilogue: TMEM -> bias + ReLU -> bf16 NHWC rows =====
+    const int q = warp & 3;
+    uint32_t acc = 0, acc_phase = 0;
+    for (int t = blockIdx.x; t < p.tiles; t += gridDim.x) {
+      const long long row = (long long)t * 128 + q * 32 + lane;
+      mbar_wait(&tfull_bar[acc], acc_phase);
+      tc_fence_after();
+      uint32_t v[32];
+      tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + acc * 32, v);
+      tmem_ld_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tempty_bar[acc]);
+      if (row < p.rows) {
+        bf16* dst = p.y + row * p.cout;
+        for (int j = 0; j < p.cout; j += 8) {
+          float f[8];
+#pragma unroll
+          for (int e = 0; e < 8; ++e) f[e] = fmaxf(__uint_as_float(v[j + e]) + __ldg(p.bias + j + e), 0.f);
+          *reinterpret_cast<uint4*>(dst + j) =
+              make_uint4(pack_bf16x2(f[0], f[1]), pack_bf16x2(f[2], f[3]), pack_bf16x2(f[4], f[5]), pack_bf16x2(f[6], f[7]));
+        }
+      }
+      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 8) { tc_fence_after(); tmem_dealloc(tmem_base, 64); }
+}
+
+// ---- weight gradient: dW[cout, 64C] = sum over patch rows of dZ[row, cout]^T P[row, :] --------------------------------------------
+// A = dZ^T (MN-major: smem lines = patch rows, 64 m-elements per 128-byte line, only the first `cout` are real; the second 64-wide
+// M chunk of the 128-row MMA is a shared all-zero region), B = P (MN-major: the producers' tile image), D[c] = TMEM cols c*64..
+__global__ void __launch_bounds__(C1_THREADS, 1) conv1_wgrad_kernel(const __grid_constant__ CUtensorMap tmZ, const Conv1Params p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int stage_bytes = p.C * C1_KB_BYTES;
+  uint8_t* smP = smem;                                            // [stages][C][128 lines][128 B]
+  uint8_t* smZ = smP + (size_t)p.stages * stage_bytes;            // [stages][128 lines][128 B]
+  uint8_t* smZero = smZ + (size_t)p.stages * C1_KB_BYTES;         // [128 lines][128 B] zeros
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smZero + C1_KB_BYTES);
+  uint64_t* full_bar = bars;         // [stages] 128 producer arrivals + 1 TMA (expect_tx) arrival
+  uint64_t* empty_bar = bars + 4;    // [stages]
+  uint64_t* done_bar = bars + 8;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 9);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int i = threadIdx.x; i < C1_KB_BYTES / 16; i += blockDim.x) reinterpret_cast<uint4*>(smZero)[i] = make_uint4(0, 0, 0, 0);
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < p.stages; ++s) { mbar_init(&full_bar[s], 129); mbar_init(&empty_bar[s], 1); }
+    mbar_init(done_bar, 1);
+    fence_mbar_init();
+  }
+  if (warp == 8) { tmem_alloc(tmem_slot, 256); tmem_relinquish(); }
+  fence_proxy_async();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const int my_tiles = p.tiles > (int)blockIdx.x ? (p.tiles - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
+
+  if (warp < 4) {
+    uint32_t stage = 0, phase = 0;
+    for (int t = blockIdx.x; t < p.tiles; t += gridDim.x) {
+      mbar_wait(&empty_bar[stage], phase ^ 1);
+      if (threadIdx.x == 0) {  // dZ^T tile: box [64 m][128 k] of the (cout, rows) tensor; columns >= cout and rows >= rows arrive as zeros
+        mbar_arrive_expect_tx(&full_bar[stage], C1_KB_BYTES);
+        tma_load_2d(smZ + (size_t)stage * C1_KB_BYTES, &tmZ, &full_bar[stage], 0, t * 128);
+      }
+      c1_gather_row(p, smP + (size_t)stage * stage_bytes, threadIdx.x, (long long)t * 128 + threadIdx.x);
+      fence_proxy_async();
+      mbar_arrive(&full_bar[stage]);
+      if (++stage == (uint32_t)p.stages) { stage = 0; phase ^= 1; }
+    }
+  } else if (warp == 8) {
+    if (lane == 0) {
+      tma_prefetch_desc(&tmZ);
+      const uint32_t idesc = make_idesc_bf16(128, 64, 1, 1);
+      uint32_t stage = 0, phase = 0;
+      const uint32_t zero_addr = smem_u32(smZero);
+      for (int i = 0; i < my_tiles; ++i) {
+        mbar_wait(&full_bar[stage], phase);
+        tc_fence_after();
+        const uint32_t z0 = smem_u32(smZ + (size_t)stage * C1_KB_BYTES), p0 = smem_u32(smP + (size_t)stage * stage_bytes);
+        for (int c = 0; c < p.C; ++c)
+#pragma unroll
+          for (int ks = 0; ks < 8; ++ks)  // 16 patch rows per MMA
+            umma_bf16(tmem_base + c * 64, make_smem_desc_sw128(z0 + ks * 2048, zero_addr - z0, 1024),
+                      make_smem_desc_sw128(p0 + c * C1_KB_BYTES + ks * 2048, 16, 1024), idesc, (i > 0 || ks > 0) ? 1u : 0u);
+        umma_commit(&empty_bar[stage]);
+        if (++stage == (uint32_t)p.stages) { stage = 0; phase ^= 1; }
+      }
+      umma_commit(done_bar);
+    }
+  } else if (warp == 4) {
+    // quadrant 0 holds output rows 0..31 = cout channels
+    mbar_wait(done_bar, 0);
+    tc_fence_after();
+    const int K = 64 * p.C;
+    float* dst = p.partial + ((size_t)blockIdx.x * p.cout + lane) * K;
+    for (int c = 0; c < p.C; ++c)
+      for (int h = 0; h < 2; ++h) {
+        uint32_t v[32];
+        tmem_ld_32x32(tmem_base + c * 64 + h * 32, v);
+        tmem_ld_wait();
+        if (lane < p.cout) {
+#pragma unroll
+          for (int j = 0; j < 32; j += 4)
+            *reinterpret_cast<float4*>(dst + c * 64 + h * 32 + j) =
+                my_tiles > 0 ? make_float4(__uint_as_float(v[j]), __uint_as_float(v[j + 1]), __uint_as_float(v[j + 2]), __uint_as_float(v[j + 3]))
+                             : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+      }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 8) { tc_fence_after(); tmem_dealloc(tmem_base, 256); }
+}
+
+// ---- host ------------------------------------------------------------------------------------------------------------------------
+static int c1_params(Conv1Params& p, const float* x, int N, int C, int H, int W, int stride, float scale, int cout) {
+  DTB_REQUIRE(C >= 1 && C <= C1_MAXC, DTB_ERR_UNSUPPORTED, "conv1 implicit GEMM: in_channels %d unsupported (1..%d)", C, C1_MAXC);
+  DTB_REQUIRE(W % 4 == 0 && stride % 4 == 0 && H >= 8 && W >= 8, DTB_ERR_UNSUPPORTED, "conv1: needs W %% 4 == 0, stride %% 4 == 0");
+  DTB_REQUIRE(cout == 16 || cout == 32, DTB_ERR_UNSUPPORTED, "conv1: out_channels %d unsupported (16, 32)", cout);
+  DTB_REQUIRE((reinterpret_cast<uintptr_t>(x) & 15) == 0, DTB_ERR_BAD_ARG, "conv1: input must be 16-byte aligned");
+  memset(&p, 0, sizeof(p));
+  p.x = x; p.N = N; p.C = C; p.H = H; p.W = W; p.stride = stride; p.cout = cout; p.scale = scale;
+  p.ho = (H - 8) / stride + 1; p.wo = (W - 8) / stride + 1;
+  p.rows = (long long)N * p.ho * p.wo;
+  p.tiles = (int)((p.rows + 127) / 128);
+  return DTB_OK;
+}
+bool conv1_implicit_supported(int C, int W, int stride, int cout) {
+  return C >= 1 && C <= C1_MAXC && W % 4 == 0 && stride % 4 == 0 && (cout == 16 || cout == 32);
+}
+
+int conv1_fwd(cudaStream_t stream, const float* x, int N, int C, int H, int W, int stride, float scale, const bf16* w_staged,
+              const float* bias, int cout, bf16* y) {
+  Conv1Params p;
+  DTB_TRY(c1_params(p, x, N, C, H, W, stride, scale, cout));
+  if (p.rows == 0) return DTB_OK;
+  p.bias = bias; p.y = y;
+  p.stages = C <= 2 ? 4 : 3;
+  if (p.stages * C * C1_KB_BYTES > 192 * 1024) p.stages = 192 * 1024 / (C * C1_KB_BYTES);
+  CUtensorMap tmW;
+  DTB_TRY(make_tmap(&tmW, w_staged, (uint64_t)64 * C, (uint64_t)cout, (uint64_t)64 * C, 64, (uint32_t)cout));
+  const int smem = 1024 + ((C * cout * 128 + 1023) & ~1023) + p.stages * C * C1_KB_BYTES + 256;
+  static bool attr = false;
+  if (!attr) { DTB_CUDA(cudaFuncSetAttribute(conv1_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 225 * 1024)); attr = true; }
+  const int grid = p.tiles < num_sms() ? p.tiles : num_sms();
+  conv1_fwd_kernel<<<grid, C1_THREADS, smem, stream>>>(tmW, p);
+  DTB_CHECK_LAUNCH();
+  return DTB_OK;
+}
+
+size_t conv1_wgrad_partial_floats(int C, int cout) { return (size_t)DTB_NUM_SMS_FALLBACK * cout * 64 * C; }
+
+int conv1_wgrad(cudaStream_t stream, const float* x, int N, int C, int H, int W, int stride, float scale, const bf16* dz, int cout,
+                float* partial, float* dw) {
+  Conv1Params p;
+  DTB_TRY(c1_params(p, x, N, C, H, W, stride, scale, cout));
+  if (p.rows == 0) { DTB_CUDA(cudaMemsetAsync(dw, 0, (size_t)cout * 64 * C * sizeof(float), stream)); return DTB_OK; }
+  p.partial = partial;
+  p.stages = 2;
+  CUtensorMap tmZ;
+  DTB_TRY(make_tmap(&tmZ, dz, (uint64_t)cout, (uint64_t)p.rows, (uint64_t)cout, 64, 128));
+  const int smem = 1024 + p.stages * (C + 1) * C1_KB_BYTES + C1_KB_BYTES + 256;
+  static bool attr = false;
+  if (!attr) { DTB_CUDA(cudaFuncSetAttribute(conv1_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 225 * 1024)); attr = true; }
+  int grid = p.tiles < num_sms() ? p.tiles : num_sms();
+  if (grid > DTB_NUM_SMS_FALLBACK) grid = DTB_NUM_SMS_FALLBACK;
+  conv1_wgrad_kernel<<<grid, C1_THREADS, smem, stream>>>(tmZ, p);
+  DTB_CHECK_LAUNCH();
+  return splitk_reduce(stream, partial, grid, cout, 64 * C, dw, 64 * C, 0, 1.f);
+}
+
+}  // namespace dtb

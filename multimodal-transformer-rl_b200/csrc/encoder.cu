@@ -36,6 +36,7 @@ struct TowerWs {
   bf16* dZ[3];  // gradient w.r.t. pre-activation outputs
   bf16* dP;     // patch-gradient scratch
   float* gstage;  // staged-order weight gradient scratch
+  float* c1_partial;  // implicit conv1 wgrad per-CTA partials
 };
 
 struct EncWs {
@@ -124,12 +125,14 @@ static void carve_ws(const dtb_encoder* e, int N, uint8_t* base, EncWs& w) {
     for (int i = 0; i < t.nconv; ++i) {
       const ConvSpec& cs = t.conv[i];
       const size_t rows = (size_t)N * cs.hout * cs.wout, kc = (size_t)cs.cin * cs.k * cs.k;
-      tw.P[i] = carve<bf16>(p, rows * kc);
+      const bool implicit = i == 0 && conv1_implicit_supported(cs.cin, cs.win, cs.stride, cs.cout);
+      tw.P[i] = implicit ? nullptr : carve<bf16>(p, rows * kc);
+      if (i == 0) tw.c1_partial = implicit ? carve<float>(p, conv1_wgrad_partial_floats(cs.cin, cs.cout)) : nullptr;
       tw.Y[i] = carve<bf16>(p, rows * cs.cout);
       tw.dZ[i] = carve<bf16>(p, rows * cs.cout);
       if (i > 0 && rows * kc > max_dp) max_dp = rows * kc;
       if ((size_t)cs.cout * kc > max_g) max_g = (size_t)cs.cout * kc;
-      need(cs.cout, kc, rows);
+      if (!implicit) need(cs.cout, kc, rows);
       if ((size_t)cs.cout > maxn) maxn = cs.cout;
     }
     need(t.feat, t.flat, N);
@@ -164,6 +167,10 @@ static int tower_forward(const dtb_encoder* e, int ti, cudaStream_t st, const fl
   for (int i = 0; i < t.nconv; ++i) {
     const ConvSpec& cs = t.conv[i];
     const int rows = N * cs.hout * cs.wout, kc = cs.cin * cs.k * cs.k;
+    if (i == 0 && tw.P[0] == nullptr) {  // implicit GEMM: patches gathered inside the kernel, never written to HBM
+      DTB_TRY(conv1_fwd(st, x, N, cs.cin, cs.hin, cs.win, cs.stride, e->c.input_scale, Ps + t.w_off[0], P + t.b_off[0], cs.cout, tw.Y[0]));
+      continue;
+    }
     if (i == 0) DTB_TRY(im2col_nchw_k8(st, x, N, cs.cin, cs.hin, cs.win, cs.stride, e->c.input_scale, tw.P[0]));
     else DTB_TRY(im2col_nhwc(st, tw.Y[i - 1], N, cs.hin, cs.win, cs.cin, cs.k, cs.stride, tw.P[i]));
     GemmEpilogue ep = epz();
@@ -182,8 +189,8 @@ static int tower_forward(const dtb_encoder* e, int ti, cudaStream_t st, const fl
 }
 
 // dF: gradient w.r.t. the tower's feature output, already multiplied by the ReLU mask; bf16 [N, feat] with row stride ldf.
-static int tower_backward(const dtb_encoder* e, int ti, cudaStream_t st, const bf16* Ps, int N, const bf16* dF, int ldf, TowerWs& tw,
-                          EncWs& w, float* G) {
+static int tower_backward(const dtb_encoder* e, int ti, cudaStream_t st, const bf16* Ps, int N, const float* x, const bf16* dF, int ldf,
+                          TowerWs& tw, EncWs& w, float* G) {
   const Tower& t = e->t[ti];
   const int last = t.nconv - 1;
   const ConvSpec& cl = t.conv[last];
@@ -205,7 +212,10 @@ static int tower_backward(const dtb_encoder* e, int ti, cudaStream_t st, const b
   for (int i = last; i >= 0; --i) {
     const ConvSpec& cs = t.conv[i];
     const int rows = N * cs.hout * cs.wout, kc = cs.cin * cs.k * cs.k;
-    if (i == 0) {
+    if (i == 0 && tw.P[0] == nullptr) {
+      DTB_REQUIRE(x != nullptr, DTB_ERR_BAD_ARG, "encoder backward: frames / audio are needed again for the implicit conv1 weight gradient");
+      DTB_TRY(conv1_wgrad(st, x, N, cs.cin, cs.hin, cs.win, cs.stride, e->c.input_scale, tw.dZ[0], cs.cout, tw.c1_partial, G + t.w_off[0]));
+    } else if (i == 0) {
       DTB_TRY(gemm_wgrad(st, tw.dZ[0], cs.cout, tw.P[0], kc, cs.cout, kc, rows, G + t.w_off[0], kc, w.partial, w.partial_floats));
     } else {
       DTB_TRY(gemm_wgrad(st, tw.dZ[i], cs.cout, tw.P[i], kc, cs.cout, kc, rows, tw.gstage, kc, w.partial, w.partial_floats));
@@ -307,7 +317,8 @@ int dtb_encoder_forward(const dtb_encoder* e, void* stream, const float* params,
   return DTB_OK;
 }
 
-int dtb_encoder_backward(const dtb_encoder* e, void* stream, const float* params, const void* staged, int N, const void* states_bf16,
+int dtb_encoder_backward(const dtb_encoder* e, void* stream, const float* params, const void* staged, int N, const float* frames,
+                         const float* audio, const void* states_bf16,
                          const void* d_states_bf16, int d_states_masked, void* workspace, size_t workspace_bytes, float* grads) {
   DTB_REQUIRE(e && params && staged && d_states_bf16 && grads, DTB_ERR_BAD_ARG, "dtb_encoder_backward: null argument");
   cudaStream_t st = (cudaStream_t)stream;
@@ -325,14 +336,14 @@ int dtb_encoder_backward(const dtb_encoder* e, void* stream, const float* params
     bf16* d = const_cast<bf16*>(dS);
     if (!d_states_masked)
       DTB_TRY(relu_mask_bf16(st, dS, e->state_dim, (const bf16*)states_bf16, e->state_dim, N, e->state_dim, d, e->state_dim));
-    DTB_TRY(tower_backward(e, 0, st, Ps, N, d, e->state_dim, w.t[0], w, grads));
-    DTB_TRY(tower_backward(e, 1, st, Ps, N, d + e->t[0].feat, e->state_dim, w.t[1], w, grads));
+    DTB_TRY(tower_backward(e, 0, st, Ps, N, frames, d, e->state_dim, w.t[0], w, grads));
+    DTB_TRY(tower_backward(e, 1, st, Ps, N, audio, d + e->t[0].feat, e->state_dim, w.t[1], w, grads));
   } else {
     // sum: the gradient reaches both towers unchanged; each applies its own ReLU mask
     const int F = e->t[0].feat;
     for (int ti = 0; ti < 2; ++ti) {
       DTB_TRY(relu_mask_bf16(st, dS, F, w.feat[ti], F, N, F, w.dfeat, F));
-      DTB_TRY(tower_backward(e, ti, st, Ps, N, w.dfeat, F, w.t[ti], w, grads));
+      DTB_TRY(tower_backward(e, ti, st, Ps, N, ti == 0 ? frames : audio, w.dfeat, F, w.t[ti], w, grads));
     }
   }
   return DTB_OK;

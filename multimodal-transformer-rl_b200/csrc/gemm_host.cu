@@ -44,7 +44,7 @@ static std::unordered_map<TmKey, CUtensorMap, TmKeyHash> g_tm_cache;
 static std::mutex g_tm_mutex;
 
 // 2-D bf16 tensor map: dims {d0 (contiguous), d1}, row stride in elements, box {b0, b1}, 128B swizzle.
-static int make_tmap(CUtensorMap* out, const void* ptr, uint64_t d0, uint64_t d1, uint64_t stride_elems, uint32_t b0, uint32_t b1) {
+int make_tmap(CUtensorMap* out, const void* ptr, uint64_t d0, uint64_t d1, uint64_t stride_elems, uint32_t b0, uint32_t b1) {
   DTB_TRY(get_encode_fn());
   DTB_REQUIRE((reinterpret_cast<uintptr_t>(ptr) & 15) == 0, DTB_ERR_BAD_ARG, "GEMM operand pointer must be 16-byte aligned");
   DTB_REQUIRE((stride_elems * 2) % 16 == 0, DTB_ERR_BAD_ARG, "GEMM operand row stride must be a multiple of 8 elements (got %llu)",

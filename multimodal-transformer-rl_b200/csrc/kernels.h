@@ -43,6 +43,9 @@ int gemm_wgrad(cudaStream_t stream, const bf16* A, int lda, const bf16* B, int l
                float* partial, size_t partial_floats);
 int splitk_reduce(cudaStream_t stream, const float* partial, int splits, int M, int N, float* out, int ldo, int accumulate, float scale);
 
+// 2-D bf16 tensor map (cached): dims {d0 contiguous, d1}, row stride in elements, box {b0, b1}, 128B swizzle.
+int make_tmap(CUtensorMap* out, const void* ptr, uint64_t d0, uint64_t d1, uint64_t stride_elems, uint32_t b0, uint32_t b1);
+
 // ---- elementwise.cu ----------------------------------------------------------------------------
 // fp32 [R, C] -> bf16 copy [R, C] and (optional) bf16 transpose [C, R]
 int cast_transpose(cudaStream_t stream, const float* src, int R, int C, bf16* dst, bf16* dst_t);
@@ -85,6 +88,14 @@ int heads_bwd(cudaStream_t stream, const float* d_action, const float* d_state, 
               const float* Wa, const float* Ws, const float* Wr, int BK, int H, int sd, int ad, int tanh_act, int ZA8, int ZS8, bf16* dy,
               bf16* dzA, bf16* dzS);
 int copy2d(cudaStream_t stream, const float* src, int lds, int R, int C, float* dst, int ldd);
+
+// ---- conv1.cu (implicit-GEMM first convolution) -------------------------------------------------
+bool conv1_implicit_supported(int C, int W, int stride, int cout);
+int conv1_fwd(cudaStream_t stream, const float* x, int N, int C, int H, int W, int stride, float scale, const bf16* w_staged,
+              const float* bias, int cout, bf16* y);
+size_t conv1_wgrad_partial_floats(int C, int cout);
+int conv1_wgrad(cudaStream_t stream, const float* x, int N, int C, int H, int W, int stride, float scale, const bf16* dz, int cout,
+                float* partial, float* dw);
 
 // ---- conv.cu -----------------------------------------------------------------------------------
 int im2col_nchw_k8(cudaStream_t stream, const float* x, int N, int C, int H, int W, int stride, float scale, bf16* p);

@@ -162,7 +162,7 @@ class MultimodalStateEncoder(nn.Module):
         N, f, a, ws, states = self._last
         grads = self.attach_grads() if grads is None else grads
         _lib.check(_lib.load().dtb_encoder_backward(self._h, _lib.stream_ptr(), _lib.ptr(self._flat), _lib.ptr(self._staged), N,
-                                                    _lib.ptr(states), _lib.ptr(d_states), int(masked), _lib.ptr(ws), ws.numel(),
+                                                    _lib.ptr(f), _lib.ptr(a), _lib.ptr(states), _lib.ptr(d_states), int(masked), _lib.ptr(ws), ws.numel(),
                                                     _lib.ptr(grads)))
         return grads
 
