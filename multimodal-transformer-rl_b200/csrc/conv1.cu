@@ -11,7 +11,9 @@
 
 namespace dtb {
 
-constexpr int C1_THREADS = 288;  // warps 0-3 patch producers, warps 4-7 epilogue (TMEM quadrant = warp & 3), warp 8 MMA + TMEM alloc
+constexpr int C1_PRODUCERS = 384;  // warps 0-11 gather patches: enough 128-bit loads in flight per SM to cover HBM latency
+constexpr int C1_THREADS = C1_PRODUCERS + 160;  // warps 12-15 epilogue (TMEM quadrant = warp & 3), warp 16 MMA + TMEM alloc
+constexpr int C1_EPI_WARP0 = C1_PRODUCERS / 32, C1_MMA_WARP = C1_EPI_WARP0 + 4;
 constexpr int C1_MAXC = 4;
 constexpr int C1_KB_BYTES = 128 * 128;  // one k-block of a 128-row tile
 
@@ -26,37 +28,36 @@ struct Conv1Params {
   float* partial;   // wgrad: [grid][cout][64C]
 };
 
-// Gather one patch row (all C k-blocks) into the swizzled tile: row r of k-block c lives at c*16KB + r*128, 16-byte chunk kh at (kh ^ (r & 7)).
-__device__ __forceinline__ void c1_gather_row(const Conv1Params& p, uint8_t* stage, int r, long long m) {
-  const bool valid = m < p.rows;
-  int n = 0, oh = 0, ow = 0;
-  if (valid) {
-    ow = (int)(m % p.wo);
-    const long long t = m / p.wo;
-    oh = (int)(t % p.ho);
-    n = (int)(t / p.ho);
-  }
-  const uint32_t dst0 = smem_u32(stage) + r * 128;
-  for (int c = 0; c < p.C; ++c) {
-    const float* src = p.x + (((size_t)n * p.C + c) * p.H + (size_t)oh * p.stride) * p.W + (size_t)ow * p.stride;
-    float4 a[8], b[8];
+// Gather a 128-row patch tile (all C k-blocks) into the swizzled image: row r of k-block c lives at c*16KB + r*128, 16-byte chunk kh at
+// (kh ^ (r & 7)).  Work item = (row, channel, half of the 8 kernel rows): 8 independent 128-bit loads, then 4 shared stores.
+__device__ __forceinline__ void c1_gather_tile(const Conv1Params& p, uint8_t* stage, long long m0) {
+  const uint32_t base = smem_u32(stage);
+  for (int item = threadIdx.x; item < 256 * p.C; item += C1_PRODUCERS) {
+    const int r = item & 127, half = (item >> 7) & 1, c = item >> 8;
+    const long long m = m0 + r;
+    float4 a[4], b[4];
+    if (m < p.rows) {
+      const int ow = (int)(m % p.wo);
+      const long long t = m / p.wo;
+      const int oh = (int)(t % p.ho), n = (int)(t / p.ho);
+      const float* src = p.x + (((size_t)n * p.C + c) * p.H + (size_t)oh * p.stride + half * 4) * p.W + (size_t)ow * p.stride;
 #pragma unroll
-    for (int kh = 0; kh < 8; ++kh) {
-      if (valid) {
-        a[kh] = ldg_f4(src + (size_t)kh * p.W);
-        b[kh] = ldg_f4(src + (size_t)kh * p.W + 4);
-      } else {
-        a[kh] = make_float4(0.f, 0.f, 0.f, 0.f);
-        b[kh] = a[kh];
+      for (int k = 0; k < 4; ++k) {
+        a[k] = ldg_f4(src + (size_t)k * p.W);
+        b[k] = ldg_f4(src + (size_t)k * p.W + 4);
       }
-    }
+    } else {
 #pragma unroll
-    for (int kh = 0; kh < 8; ++kh) {
-      const uint32_t addr = dst0 + c * C1_KB_BYTES + ((kh ^ (r & 7)) << 4);
-      const float s = p.scale;
-      asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(pack_bf16x2(a[kh].x * s, a[kh].y * s)),
-                   "r"(pack_bf16x2(a[kh].z * s, a[kh].w * s)), "r"(pack_bf16x2(b[kh].x * s, b[kh].y * s)),
-                   "r"(pack_bf16x2(b[kh].z * s, b[kh].w * s))
+      for (int k = 0; k < 4; ++k) a[k] = b[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    const float s = p.scale;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int kh = half * 4 + k;
+      const uint32_t addr = base + c * C1_KB_BYTES + r * 128 + ((kh ^ (r & 7)) << 4);
+      asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(pack_bf16x2(a[k].x * s, a[k].y * s)),
+                   "r"(pack_bf16x2(a[k].z * s, a[k].w * s)), "r"(pack_bf16x2(b[k].x * s, b[k].y * s)),
+                   "r"(pack_bf16x2(b[k].z * s, b[k].w * s))
                    : "memory");
     }
   }
@@ -79,28 +80,28 @@ __global__ void __launch_bounds__(C1_THREADS, 1) conv1_fwd_kernel(const __grid_c
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (threadIdx.x == 0) {
-    for (int s = 0; s < p.stages; ++s) { mbar_init(&full_bar[s], 128); mbar_init(&empty_bar[s], 1); }
+    for (int s = 0; s < p.stages; ++s) { mbar_init(&full_bar[s], C1_PRODUCERS); mbar_init(&empty_bar[s], 1); }
     for (int s = 0; s < 2; ++s) { mbar_init(&tfull_bar[s], 1); mbar_init(&tempty_bar[s], 4); }
     mbar_init(w_bar, 1);
     fence_mbar_init();
   }
-  if (warp == 8) { tmem_alloc(tmem_slot, 64); tmem_relinquish(); }
+  if (warp == C1_MMA_WARP) { tmem_alloc(tmem_slot, 64); tmem_relinquish(); }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  if (warp < 4) {
-    // ===== patch producers: thread t owns tile row t =====
+  if (warp < C1_EPI_WARP0) {
+    // ===== patch producers =====
     uint32_t stage = 0, phase = 0;
     for (int t = blockIdx.x; t < p.tiles; t += gridDim.x) {
       mbar_wait(&empty_bar[stage], phase ^ 1);
-      c1_gather_row(p, smA + (size_t)stage * stage_bytes, threadIdx.x, (long long)t * 128 + threadIdx.x);
+      c1_gather_tile(p, smA + (size_t)stage * stage_bytes, (long long)t * 128);
       fence_proxy_async();  // generic-proxy stores -> visible to the tensor core (async proxy)
       mbar_arrive(&full_bar[stage]);
       if (++stage == (uint32_t)p.stages) { stage = 0; phase ^= 1; }
     }
-  } else if (warp == 8) {
+  } else if (warp == C1_MMA_WARP) {
     if (lane == 0) {
       tma_prefetch_desc(&tmW);
       mbar_arrive_expect_tx(w_bar, (uint32_t)(p.C * wkb));
@@ -153,7 +154,7 @@ __global__ void __launch_bounds__(C1_THREADS, 1) conv1_fwd_kernel(const __grid_c
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 8) { tc_fence_after(); tmem_dealloc(tmem_base, 64); }
+  if (warp == C1_MMA_WARP) { tc_fence_after(); tmem_dealloc(tmem_base, 64); }
 }
 
 // ---- weight gradient: dW[cout, 64C] = sum over patch rows of dZ[row, cout]^T P[row, :] --------------------------------------------
@@ -175,11 +176,11 @@ __global__ void __launch_bounds__(C1_THREADS, 1) conv1_wgrad_kernel(const __grid
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   for (int i = threadIdx.x; i < C1_KB_BYTES / 16; i += blockDim.x) reinterpret_cast<uint4*>(smZero)[i] = make_uint4(0, 0, 0, 0);
   if (threadIdx.x == 0) {
-    for (int s = 0; s < p.stages; ++s) { mbar_init(&full_bar[s], 129); mbar_init(&empty_bar[s], 1); }
+    for (int s = 0; s < p.stages; ++s) { mbar_init(&full_bar[s], C1_PRODUCERS + 1); mbar_init(&empty_bar[s], 1); }
     mbar_init(done_bar, 1);
     fence_mbar_init();
   }
-  if (warp == 8) { tmem_alloc(tmem_slot, 256); tmem_relinquish(); }
+  if (warp == C1_MMA_WARP) { tmem_alloc(tmem_slot, 256); tmem_relinquish(); }
   fence_proxy_async();
   tc_fence_before();
   __syncthreads();
@@ -187,7 +188,7 @@ __global__ void __launch_bounds__(C1_THREADS, 1) conv1_wgrad_kernel(const __grid
   const uint32_t tmem_base = *tmem_slot;
   const int my_tiles = p.tiles > (int)blockIdx.x ? (p.tiles - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
 
-  if (warp < 4) {
+  if (warp < C1_EPI_WARP0) {
     uint32_t stage = 0, phase = 0;
     for (int t = blockIdx.x; t < p.tiles; t += gridDim.x) {
       mbar_wait(&empty_bar[stage], phase ^ 1);
@@ -195,12 +196,12 @@ __global__ void __launch_bounds__(C1_THREADS, 1) conv1_wgrad_kernel(const __grid
         mbar_arrive_expect_tx(&full_bar[stage], C1_KB_BYTES);
         tma_load_2d(smZ + (size_t)stage * C1_KB_BYTES, &tmZ, &full_bar[stage], 0, t * 128);
       }
-      c1_gather_row(p, smP + (size_t)stage * stage_bytes, threadIdx.x, (long long)t * 128 + threadIdx.x);
+      c1_gather_tile(p, smP + (size_t)stage * stage_bytes, (long long)t * 128);
       fence_proxy_async();
       mbar_arrive(&full_bar[stage]);
       if (++stage == (uint32_t)p.stages) { stage = 0; phase ^= 1; }
     }
-  } else if (warp == 8) {
+  } else if (warp == C1_MMA_WARP) {
     if (lane == 0) {
       tma_prefetch_desc(&tmZ);
       const uint32_t idesc = make_idesc_bf16(128, 64, 1, 1);
@@ -220,7 +221,7 @@ __global__ void __launch_bounds__(C1_THREADS, 1) conv1_wgrad_kernel(const __grid
       }
       umma_commit(done_bar);
     }
-  } else if (warp == 4) {
+  } else if (warp == C1_EPI_WARP0) {
     // quadrant 0 holds output rows 0..31 = cout channels
     mbar_wait(done_bar, 0);
     tc_fence_after();
@@ -242,7 +243,7 @@ __global__ void __launch_bounds__(C1_THREADS, 1) conv1_wgrad_kernel(const __grid
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 8) { tc_fence_after(); tmem_dealloc(tmem_base, 256); }
+  if (warp == C1_MMA_WARP) { tc_fence_after(); tmem_dealloc(tmem_base, 256); }
 }
 
 // ---- host ------------------------------------------------------------------------------------------------------------------------

@@ -56,7 +56,8 @@ int cast_bf16(cudaStream_t stream, const float* src, size_t n, bf16* dst) {
 // Stage 1: grid (column groups, row slabs); each thread owns 8 adjacent columns (one 128-bit load per row) and strides rows;
 //          the row-lanes of the block are reduced through shared memory in index order -> scratch[slab][N].
 // Stage 2: 32 columns x 8 row-lanes per block sum the slabs, lanes combined in index order (deterministic).
-constexpr int CS_SLABS_MAX = 64;
+constexpr int CS_SLABS_MAX = 1024;        // narrow matrices (conv bias grads, N = 32) need many row slabs to fill the GPU
+constexpr int CS_SCRATCH_MIN = 64 * 1024;  // floats
 
 __global__ void __launch_bounds__(256) colsum_stage1(const bf16* __restrict__ x, int M, int N, int ld, float* __restrict__ scratch) {
   __shared__ float red[256][9];
@@ -102,7 +103,7 @@ __global__ void __launch_bounds__(256) colsum_stage2(const float* __restrict__ s
   }
 }
 
-size_t colsum_scratch_floats(int N) { return (size_t)CS_SLABS_MAX * N; }
+size_t colsum_scratch_floats(int N) { return (size_t)64 * N > (size_t)CS_SCRATCH_MIN ? (size_t)64 * N : (size_t)CS_SCRATCH_MIN; }
 
 int colsum_bf16(cudaStream_t stream, const bf16* x, int M, int N, int ld, float* out, int accumulate, float* scratch) {
   DTB_REQUIRE(N % 8 == 0 && ld % 8 == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0, DTB_ERR_BAD_ARG,
@@ -112,10 +113,11 @@ int colsum_bf16(cudaStream_t stream, const bf16* x, int M, int N, int ld, float*
   while (cx < 32 && cx < n8) cx *= 2;
   const int ry = 256 / cx;
   const int colgroups = (n8 + cx - 1) / cx;
-  int nslab = (2 * num_sms() + colgroups - 1) / colgroups;
+  int nslab = (4 * num_sms() + colgroups - 1) / colgroups;
   const int max_slab = (M + 4 * ry - 1) / (4 * ry);
   if (nslab > max_slab) nslab = max_slab;
   if (nslab > CS_SLABS_MAX) nslab = CS_SLABS_MAX;
+  if ((size_t)nslab * N > colsum_scratch_floats(N)) nslab = (int)(colsum_scratch_floats(N) / N);
   if (nslab < 1) nslab = 1;
   colsum_stage1<<<dim3(colgroups, nslab), dim3(cx, ry), 0, stream>>>(x, M, N, ld, scratch);
   DTB_CHECK_LAUNCH();

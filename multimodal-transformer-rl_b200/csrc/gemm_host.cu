@@ -153,31 +153,43 @@ int gemm_bf16(cudaStream_t stream, const bf16* A, int lda, int a_mn_major, const
   return p.split_k;  // >= 1: number of partial slices written when ep.partial != null
 }
 
-// ---- split-K reduction: out[M, ldo] (+)= sum_s partial[s][M][N] -----------------------------------
-__global__ void splitk_reduce_kernel(const float* __restrict__ partial, int splits, int M, int N, float* __restrict__ out, int ldo,
-                                     int accumulate, float scale) {
+// ---- split-K reduction: out[M, ldo] (+)= scale * sum_s partial[s][M][N], slices added in index order (deterministic) -------------
+// 32 float4 columns x 8 split-lanes per block: lane l sums slices l, l+8, ... and the 8 lanes are combined in index order.
+__global__ void __launch_bounds__(256) splitk_reduce_kernel(const float* __restrict__ partial, int splits, int M, int N,
+                                                            float* __restrict__ out, int ldo, int accumulate, float scale) {
+  __shared__ float4 red[8][32];
   const size_t n4 = (size_t)M * N / 4;
-  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
-    float4 s = ldg_f4(partial + i * 4);
-    for (int k = 1; k < splits; ++k) {
-      float4 v = ldg_f4(partial + (size_t)k * M * N + i * 4);
-      s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+  for (size_t base = (size_t)blockIdx.x * 32; base < n4; base += (size_t)gridDim.x * 32) {
+    const size_t i = base + threadIdx.x;
+    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (i < n4)
+      for (int k = threadIdx.y; k < splits; k += 8) {
+        const float4 v = ldg_f4(partial + (size_t)k * M * N + i * 4);
+        s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+      }
+    red[threadIdx.y][threadIdx.x] = s;
+    __syncthreads();
+    if (threadIdx.y == 0 && i < n4) {
+      for (int l = 1; l < 8; ++l) {
+        const float4 v = red[l][threadIdx.x];
+        s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+      }
+      const size_t e = i * 4;
+      float* o = out + (e / N) * (size_t)ldo + (e % N);
+      const float4 prev = accumulate ? *reinterpret_cast<float4*>(o) : make_float4(0.f, 0.f, 0.f, 0.f);
+      *reinterpret_cast<float4*>(o) = make_float4(prev.x + scale * s.x, prev.y + scale * s.y, prev.z + scale * s.z, prev.w + scale * s.w);
     }
-    const size_t e = i * 4;
-    const int r = (int)(e / N), c = (int)(e % N);
-    float* o = out + (size_t)r * ldo + c;
-    float4 prev = accumulate ? *reinterpret_cast<float4*>(o) : make_float4(0, 0, 0, 0);
-    *reinterpret_cast<float4*>(o) = make_float4(prev.x + scale * s.x, prev.y + scale * s.y, prev.z + scale * s.z, prev.w + scale * s.w);
+    __syncthreads();
   }
 }
 
 int splitk_reduce(cudaStream_t stream, const float* partial, int splits, int M, int N, float* out, int ldo, int accumulate, float scale) {
   DTB_REQUIRE(N % 4 == 0 && ldo % 4 == 0, DTB_ERR_BAD_ARG, "splitk_reduce: N and ldo must be multiples of 4");
   const size_t n4 = (size_t)M * N / 4;
-  int blocks = (int)((n4 + 255) / 256);
-  if (blocks > num_sms() * 8) blocks = num_sms() * 8;
+  size_t blocks = (n4 + 31) / 32;
+  if (blocks > (size_t)num_sms() * 8) blocks = (size_t)num_sms() * 8;
   if (blocks < 1) blocks = 1;
-  splitk_reduce_kernel<<<blocks, 256, 0, stream>>>(partial, splits, M, N, out, ldo, accumulate, scale);
+  splitk_reduce_kernel<<<(unsigned)blocks, dim3(32, 8), 0, stream>>>(partial, splits, M, N, out, ldo, accumulate, scale);
   DTB_CHECK_LAUNCH();
   return DTB_OK;
 }
