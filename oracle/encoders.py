@@ -73,8 +73,13 @@ class MultimodalStateEncoder(nn.Module):
 
     def forward(self, frames, audio):
         B, K = frames.shape[:2]
-        v = self.video_net(frames.reshape(B * K, *self.frame_shape) * self.input_scale)  # agents.py:133
-        a = self.audio_net(audio.reshape(B * K, *self.audio_shape) * self.input_scale)  # agents.py:134
+        inv = 1.0 / self.input_scale
+        if abs(inv - round(inv)) < 1e-6:  # the reference DIVIDES (`/ 255.0`, agents.py:133-134): keep the same rounding
+            f, au = frames.reshape(B * K, *self.frame_shape) / float(round(inv)), audio.reshape(B * K, *self.audio_shape) / float(round(inv))
+        else:
+            f, au = frames.reshape(B * K, *self.frame_shape) * self.input_scale, audio.reshape(B * K, *self.audio_shape) * self.input_scale
+        v = self.video_net(f)  # agents.py:133
+        a = self.audio_net(au)  # agents.py:134
         fused = torch.cat([v, a], dim=1) if self.fusion_type == "concat" else v + a  # agents.py:137-143 (dim=1 semantics)
         return fused.reshape(B, K, self.state_dim)
 

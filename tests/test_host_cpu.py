@@ -1,0 +1,144 @@
+"""Host-side logic that needs no GPU: the C-ABI library loads and exports every symbol of include/dtb200.h, parameter layouts match the
+oracle's state_dict, the product refuses to compute on CPU (no fallback), and the data-parallel plumbing works at world_size 2 on gloo."""
+import os
+import subprocess
+import sys
+
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_library_exports_every_declared_symbol():
+    from mtrl_b200 import _lib
+
+    lib = _lib.load()
+    syms = _lib.exported_symbols()
+    assert len(syms) >= 30
+    missing = [s for s in syms if not hasattr(lib, s)]
+    assert not missing, missing
+    assert lib.dtb_abi_version() == 1
+
+
+def test_product_never_imports_the_oracle():
+    pkg = os.path.join(ROOT, "multimodal-transformer-rl_b200")
+    for dp, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                txt = open(os.path.join(dp, f)).read()
+                assert "import oracle" not in txt and "from oracle" not in txt and "/root/reference" not in txt, f
+
+
+@pytest.mark.parametrize("cfg", [dict(state_dim=11, act_dim=3, hidden_size=128, n_layer=3, n_head=1),
+                                 dict(state_dim=1024, act_dim=18, hidden_size=256, n_layer=2, n_head=8, action_tanh=False),
+                                 dict(state_dim=11, act_dim=3, hidden_size=768, n_layer=2, n_head=12, activation_function="gelu_new")])
+def test_dt_layout_and_state_dict_roundtrip(cfg):
+    from mtrl_b200.model import DecisionTransformer
+    from oracle.decision_transformer import DecisionTransformer as Oracle
+
+    o = Oracle(max_length=20, max_ep_len=100, **cfg)
+    m = DecisionTransformer(max_length=20, max_ep_len=100, device="cpu", **cfg)
+    sd_o, sd_m = o.state_dict(), m.state_dict()
+    assert set(sd_o) == set(sd_m)
+    assert all(sd_o[k].shape == sd_m[k].shape for k in sd_o)
+    m.load_state_dict(sd_o)
+    assert all(torch.equal(m.state_dict()[k], sd_o[k]) for k in sd_o)
+    # every parameter is a view into the single flat buffer, 8-element aligned, stages cover it exactly once
+    base = m.flat_params.data_ptr()
+    for n, p in m.named_parameters():
+        off = (p.data_ptr() - base) // 4
+        assert 0 <= off < m._total and off % 8 == 0, n
+    ranges = sorted(m.stage_grad_range(s) for s in range(m.n_stages))
+    assert ranges[0][0] == 0 and ranges[-1][1] == m._total
+    assert all(a[1] == b[0] for a, b in zip(ranges, ranges[1:]))
+    o2 = Oracle(max_length=20, max_ep_len=100, **cfg)
+    o2.load_state_dict(m.state_dict())  # and back
+    # HF-prefixed keys are accepted
+    hf_style = {("encoder." + k[len("transformer."):] if k.startswith("transformer.") else k): v for k, v in sd_o.items()}
+    hf_style["encoder.wpe.weight"] = torch.zeros(4, cfg["hidden_size"])
+    m.load_state_dict(hf_style)
+
+
+def test_encoder_layout_and_state_dict_roundtrip():
+    from mtrl_b200.encoder import MultimodalStateEncoder
+    from oracle.encoders import MultimodalStateEncoder as Oracle
+
+    for args in [((1, 84, 84), (1, 84, 84), "big", "concat"), ((3, 64, 64), (2, 64, 64), "small", "sum")]:
+        o, e = Oracle(*args), MultimodalStateEncoder(*args, device="cpu")
+        assert set(o.state_dict()) == set(e.state_dict()) and o.state_dim == e.state_dim
+        e.load_state_dict(o.state_dict())
+        assert all(torch.equal(e.state_dict()[k], v) for k, v in o.state_dict().items())
+
+
+def test_no_cpu_fallback():
+    from mtrl_b200 import _lib
+    from mtrl_b200.encoder import MultimodalStateEncoder
+    from mtrl_b200.model import DecisionTransformer
+
+    m = DecisionTransformer(11, 3, 128, max_length=5, max_ep_len=50, device="cpu")
+    s, a, r, t = torch.zeros(1, 5, 11), torch.zeros(1, 5, 3), torch.zeros(1, 5, 1), torch.zeros(1, 5, dtype=torch.long)
+    with pytest.raises(_lib.DtbError):
+        m(s, a, None, r, t)
+    with pytest.raises(_lib.DtbError):
+        m.get_action(s[0], a[0], None, r[0], t[0])
+    e = MultimodalStateEncoder((1, 84, 84), (1, 84, 84), device="cpu")
+    with pytest.raises(_lib.DtbError):
+        e(torch.zeros(1, 1, 1, 84, 84), torch.zeros(1, 1, 1, 84, 84))
+
+
+def test_bad_configs_are_rejected():
+    from mtrl_b200 import _lib
+    from mtrl_b200.model import DecisionTransformer
+
+    with pytest.raises(_lib.DtbError):
+        DecisionTransformer(11, 3, 100, n_head=1, device="cpu")  # head_dim 100 unsupported
+    with pytest.raises(ValueError):
+        DecisionTransformer(11, 3, 128, activation_function="swish", device="cpu")
+
+
+def test_shard_batch():
+    from mtrl_b200.dp import shard_batch
+
+    x, y = torch.arange(24).reshape(8, 3), torch.arange(8)
+    parts = [shard_batch([x, y], r, 4) for r in range(4)]
+    assert torch.equal(torch.cat([p[0] for p in parts]), x) and torch.equal(torch.cat([p[1] for p in parts]), y)
+
+
+_DP_SCRIPT = r"""
+import os, sys, torch, torch.distributed as dist
+sys.path.insert(0, sys.argv[1])
+from mtrl_b200.dp import GradAllReducer, broadcast_parameters, replicas_consistent
+dist.init_process_group("gloo")
+rank, world = dist.get_rank(), dist.get_world_size()
+torch.manual_seed(rank)
+params = torch.randn(1000)
+broadcast_parameters([params])
+assert replicas_consistent([params])
+# emulate a staged backward: ranges become ready from the tail downwards; local grads are pre-scaled by 1/world
+g = torch.full((1000,), float(rank + 1)) / world
+red = GradAllReducer(bucket_bytes=4 * 300)
+for b, e in [(800, 1000), (500, 800), (200, 500), (0, 200)]:
+    red.ready(g, b, e)
+red.finish()
+expect = sum(r + 1 for r in range(world)) / world
+assert torch.allclose(g, torch.full((1000,), expect)), g[:4]
+assert 2 <= red.n_collectives <= 4
+params -= 0.1 * g
+assert replicas_consistent([params])
+if rank == 1:
+    params[3] += 1e-3
+assert not replicas_consistent([params])
+dist.destroy_process_group()
+print("ok", rank)
+"""
+
+
+def test_data_parallel_allreduce_world2_gloo(tmp_path):
+    script = tmp_path / "dp_check.py"
+    script.write_text(_DP_SCRIPT)
+    env = dict(os.environ, MASTER_ADDR="127.0.0.1")
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+                        "--master-port", "29731", str(script), ROOT], capture_output=True, text=True, timeout=240, env=env)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert r.stdout.count("ok") == 2

@@ -167,3 +167,26 @@ def test_cpu_tensor_raises(cuda_device):
     s, a, r, t, m = make_inputs(2, K, 11, 3, 1000, seed=1)
     with pytest.raises(_lib.DtbError):
         model(s, a, None, r, t, m)
+
+
+def test_against_committed_golden_fixture(cuda_device):
+    """The CUDA path vs tests/golden/dt_oracle_small.pt (oracle outputs / loss / gradients committed by tests/golden/make_golden.py)."""
+    import os
+
+    from mtrl_b200.model import DecisionTransformer
+
+    fx = torch.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "dt_oracle_small.pt"), weights_only=False)
+    dev = cuda_device
+    m = DecisionTransformer(11, 3, 64, max_length=10, max_ep_len=100, n_layer=2, n_head=2, activation_function="gelu_new", resid_pdrop=0.0,
+                            attn_pdrop=0.0, device=dev)
+    m.load_state_dict(fx["state"])
+    s, a, r, t, mask = (x.to(dev) for x in fx["inputs"])
+    sp, ap, rp = m(s, a, None, r, t, mask)
+    keep = mask > 0
+    for mine, ref in zip((sp, ap, rp), fx["outputs"]):
+        assert rel_err(mine[keep], ref.to(dev)[keep]) <= TOL_ACTION
+    out = m.loss_and_backward(s, a, r, t, mask)
+    torch.cuda.synchronize()
+    assert abs(out[0].item() - fx["loss"].item()) <= TOL_LOSS * abs(fx["loss"].item())
+    for n, g in fx["grads"].items():
+        assert rel_err(m.get_parameter(n).grad, g) <= TOL_GRAD, n

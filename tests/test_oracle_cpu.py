@@ -1,0 +1,157 @@
+"""Pins the oracle (test infrastructure) on CPU: against the committed golden fixtures produced by the REFERENCE's own code
+(tests/golden/make_golden.py: /root/reference/src/agents.py conv_factory / towers / fusion) and by the HuggingFace port of the
+un-vendored decision-transformer submodule, and against the live HF model when transformers is importable."""
+import os
+
+import pytest
+import torch
+
+from util import make_inputs
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def _load(name):
+    return torch.load(os.path.join(GOLD, name), weights_only=False)
+
+
+def _sums(module):
+    return {k: (float(v.double().sum()), float(v.double().abs().sum())) for k, v in module.state_dict().items()}
+
+
+def _same_weights(module, sums):
+    mine = _sums(module)
+    assert mine.keys() == sums.keys()
+    for k in sums:
+        assert mine[k][0] == pytest.approx(sums[k][0], rel=1e-9, abs=1e-9) and mine[k][1] == pytest.approx(sums[k][1], rel=1e-9), k
+
+
+@pytest.mark.parametrize("size", ["big", "small"])
+def test_oracle_towers_equal_reference_conv_factory(size):
+    """oracle conv_factory(size, 1, (84, 84)) == reference agents.conv_factory(size) (agents.py:30-55), `/255` scaling (:133-134), fusion."""
+    from oracle.encoders import MultimodalStateEncoder
+
+    fx = _load(f"encoder_ref_{size}.pt")
+    torch.manual_seed(fx["seed"])
+    enc = MultimodalStateEncoder((1, 84, 84), (1, 84, 84), size, "concat")  # creates video_net then audio_net, like the fixture
+    _same_weights(enc.video_net, fx["video_sums"])
+    _same_weights(enc.audio_net, fx["audio_sums"])
+    x = fx["x"]
+    with torch.no_grad():
+        out = enc(x[:, 0:1].unsqueeze(0), x[:, 1:2].unsqueeze(0))[0]
+        enc.fusion_type, enc.state_dim = "sum", enc.feature_size
+        out_sum = enc(x[:, 0:1].unsqueeze(0), x[:, 1:2].unsqueeze(0))[0]
+    assert torch.equal(out, fx["concat_dim1"])  # bit-exact: same torch ops as the reference
+    assert torch.equal(out_sum, fx["sum"])
+
+
+def test_oracle_fusion_equals_minecraft_agent_at_batch_one():
+    """MinecraftAgent.get_states' dim-0 cat + reshape (agents.py:138,146) equals per-sample [video | audio] at B=1."""
+    from oracle.encoders import MultimodalStateEncoder
+
+    fx = _load("encoder_ref_fusion_b1.pt")
+    torch.manual_seed(fx["seed"])
+    enc = MultimodalStateEncoder((1, 84, 84), (1, 84, 84), "big", "concat")
+    _same_weights(enc.video_net, fx["video_sums"])
+    x = fx["x"]
+    with torch.no_grad():
+        out = enc(x[:, 0:1].unsqueeze(0), x[:, 1:2].unsqueeze(0))
+    assert torch.equal(out.reshape(-1), fx["fused"].reshape(-1))
+
+
+def test_oracle_dt_equals_hf_fixture():
+    from oracle.decision_transformer import DecisionTransformer
+
+    fx = _load("dt_hf_c1.pt")
+    o = DecisionTransformer(11, 3, 64, max_length=10, max_ep_len=100, n_layer=2, n_head=2, activation_function="relu", resid_pdrop=0.0,
+                            attn_pdrop=0.0).eval()
+    o.load_hf_state_dict(fx["state"])
+    s, a, r, t, m = fx["inputs"]
+    with torch.no_grad():
+        outs = o(s, a, None, r, t, m)
+    keep = m > 0
+    for mine, ref in zip(outs, fx["outputs"]):
+        assert (mine[keep] - ref[keep]).abs().max().item() < 2e-5
+
+
+def test_oracle_dt_equals_live_hf():
+    pytest.importorskip("transformers")
+    from oracle.check_vs_hf import check
+
+    for kw in [dict(), dict(act="gelu_new", H=64, nh=4, L=2, K=12), dict(sd=16, ad=4, tanh=False, H=96, nh=3)]:
+        assert check(**kw) < 2e-5
+
+
+def test_oracle_reproduces_its_own_golden():
+    from oracle.decision_transformer import DecisionTransformer
+    from oracle.trainer import masked_action_mse
+
+    fx = _load("dt_oracle_small.pt")
+    o = DecisionTransformer(11, 3, 64, max_length=10, max_ep_len=100, n_layer=2, n_head=2, activation_function="gelu_new", resid_pdrop=0.0,
+                            attn_pdrop=0.0)
+    o.load_state_dict(fx["state"])
+    s, a, r, t, m = fx["inputs"]
+    sp, ap, rp = o(s, a, None, r, t, m)
+    loss = masked_action_mse(ap, a, m)
+    loss.backward()
+    assert torch.allclose(ap, fx["outputs"][1], atol=1e-6) and abs(loss.item() - fx["loss"].item()) < 1e-7
+    for n, p in o.named_parameters():
+        if n in fx["grads"]:
+            assert torch.allclose(p.grad, fx["grads"][n], atol=1e-6, rtol=1e-4), n
+
+
+def test_token_interleave_and_mask_rules():
+    """A2/A3 integer rules of the oracle itself: changing inputs under the mask leaves unmasked predictions untouched (exactly 0)."""
+    from oracle.decision_transformer import DecisionTransformer
+
+    torch.manual_seed(0)
+    o = DecisionTransformer(5, 2, 32, max_length=6, max_ep_len=50, n_layer=1, n_head=1, resid_pdrop=0.0, attn_pdrop=0.0).eval()
+    s, a, r, t, m = make_inputs(4, 6, 5, 2, 50, seed=3)
+    with torch.no_grad():
+        _, ap1, _ = o(s, a, None, r, t, m)
+        s2, a2 = s.clone(), a.clone()
+        s2[m == 0], a2[m == 0] = 9.0, -3.0
+        _, ap2, _ = o(s2, a2, None, r, t, m)
+    assert torch.equal(ap1[m > 0], ap2[m > 0])
+
+
+@pytest.mark.parametrize("t_hist", [1, 5, 6, 11])
+def test_get_action_padding_rules(t_hist):
+    """A9: last-K window, LEFT zero padding, mask [0]*(K-t)+[1]*t, action of the last state token == explicit padded forward."""
+    from oracle.decision_transformer import DecisionTransformer
+
+    torch.manual_seed(1)
+    K = 6
+    o = DecisionTransformer(5, 2, 32, max_length=K, max_ep_len=50, n_layer=2, n_head=2, resid_pdrop=0.0, attn_pdrop=0.0).eval()
+    g = torch.Generator().manual_seed(t_hist)
+    s, a, r, ts = torch.randn(t_hist, 5, generator=g), torch.randn(t_hist, 2, generator=g), torch.rand(t_hist, 1, generator=g), torch.arange(t_hist)
+    got = o.get_action(s, a, None, r, ts)
+    t = min(t_hist, K)
+    pad = K - t
+    S = torch.cat([torch.zeros(pad, 5), s[-K:]])[None]
+    A = torch.cat([torch.zeros(pad, 2), a[-K:]])[None]
+    R = torch.cat([torch.zeros(pad, 1), r[-K:]])[None]
+    T = torch.cat([torch.zeros(pad, dtype=torch.long), ts[-K:]])[None]
+    M = torch.cat([torch.zeros(pad), torch.ones(t)])[None]
+    with torch.no_grad():
+        _, ap, _ = o(S, A, None, R, T, M)
+    assert torch.equal(got, ap[0, -1])
+
+
+def test_train_step_loss_rule():
+    """A10: loss = mean((a_hat - a)^2) over rows with attention_mask > 0; clip 0.25; rtg[:, :-1] when rtg carries K+1 entries."""
+    from oracle.decision_transformer import DecisionTransformer
+    from oracle.trainer import SequenceTrainer, masked_action_mse
+
+    torch.manual_seed(2)
+    o = DecisionTransformer(5, 2, 32, max_length=6, max_ep_len=50, n_layer=1, n_head=1, resid_pdrop=0.0, attn_pdrop=0.0)
+    s, a, r, t, m = make_inputs(4, 6, 5, 2, 50, seed=4)
+    with torch.no_grad():
+        _, ap, _ = o(s, a, None, r, t, m)
+    manual = sum(((ap[b, k] - a[b, k]) ** 2).sum() for b in range(4) for k in range(6) if m[b, k] > 0) / (int((m > 0).sum()) * 2)
+    assert abs(masked_action_mse(ap, a, m).item() - manual.item()) < 1e-6
+    rtg = torch.cat([r, r[:, -1:]], dim=1)
+    tr = SequenceTrainer(o, torch.optim.AdamW(o.parameters(), lr=1e-3), 4, lambda bs: (s, a, None, None, rtg, t, m))
+    l0 = tr.train_step()
+    assert abs(l0 - manual.item()) < 1e-6
+    assert tr.train_step() < l0
