@@ -8,6 +8,7 @@
 // (names video_net.{0,2,4,7}.*, audio_net.* as in the reference's nn.Sequential), so state_dicts round-trip.
 #include "../../include/dtb200.h"
 #include "kernels.h"
+#include "side.h"
 
 #include <new>
 #include <string.h>
@@ -59,6 +60,7 @@ struct dtb_encoder {
   long long total;
   int n_entries;
   std::vector<long long> off, num;
+  mutable dtb::SideStream side;  // weight-gradient branch of the backward
 };
 
 namespace dtb {
@@ -195,10 +197,13 @@ static int tower_backward(const dtb_encoder* e, int ti, cudaStream_t st, const b
   const int last = t.nconv - 1;
   const ConvSpec& cl = t.conv[last];
   const int hw = cl.hout * cl.wout;
+  SideStream& sd = e->side;
+  cudaStream_t ss = sd.pick(st);  // weight / bias gradients: side branch; data gradients stay on the caller's stream
   // ---- FC ----
-  DTB_TRY(gemm_wgrad(st, dF, ldf, tw.Y[last], t.flat, t.feat, t.flat, N, tw.gstage, t.flat, w.partial, w.partial_floats));
-  DTB_TRY(permute_unstage(st, tw.gstage, t.feat, cl.cout, hw, G + t.w_off[3]));  // staged (h,w,c) -> PyTorch flatten (c,h,w)
-  DTB_TRY(colsum_bf16(st, dF, N, t.feat, ldf, G + t.b_off[3], 0, w.cs_scratch));
+  DTB_TRY(sd.fork(st));
+  DTB_TRY(gemm_wgrad(ss, dF, ldf, tw.Y[last], t.flat, t.feat, t.flat, N, tw.gstage, t.flat, w.partial, w.partial_floats));
+  DTB_TRY(permute_unstage(ss, tw.gstage, t.feat, cl.cout, hw, G + t.w_off[3]));  // staged (h,w,c) -> PyTorch flatten (c,h,w)
+  DTB_TRY(colsum_bf16(ss, dF, N, t.feat, ldf, G + t.b_off[3], 0, w.cs_scratch));
   {
     GemmEpilogue ep = epz();
     ep.dact = 1;
@@ -212,16 +217,17 @@ static int tower_backward(const dtb_encoder* e, int ti, cudaStream_t st, const b
   for (int i = last; i >= 0; --i) {
     const ConvSpec& cs = t.conv[i];
     const int rows = N * cs.hout * cs.wout, kc = cs.cin * cs.k * cs.k;
+    DTB_TRY(sd.fork(st));  // dZ[i] is complete on the main stream
     if (i == 0 && tw.P[0] == nullptr) {
       DTB_REQUIRE(x != nullptr, DTB_ERR_BAD_ARG, "encoder backward: frames / audio are needed again for the implicit conv1 weight gradient");
-      DTB_TRY(conv1_wgrad(st, x, N, cs.cin, cs.hin, cs.win, cs.stride, e->c.input_scale, tw.dZ[0], cs.cout, tw.c1_partial, G + t.w_off[0]));
+      DTB_TRY(conv1_wgrad(ss, x, N, cs.cin, cs.hin, cs.win, cs.stride, e->c.input_scale, tw.dZ[0], cs.cout, tw.c1_partial, G + t.w_off[0]));
     } else if (i == 0) {
-      DTB_TRY(gemm_wgrad(st, tw.dZ[0], cs.cout, tw.P[0], kc, cs.cout, kc, rows, G + t.w_off[0], kc, w.partial, w.partial_floats));
+      DTB_TRY(gemm_wgrad(ss, tw.dZ[0], cs.cout, tw.P[0], kc, cs.cout, kc, rows, G + t.w_off[0], kc, w.partial, w.partial_floats));
     } else {
-      DTB_TRY(gemm_wgrad(st, tw.dZ[i], cs.cout, tw.P[i], kc, cs.cout, kc, rows, tw.gstage, kc, w.partial, w.partial_floats));
-      DTB_TRY(permute_unstage(st, tw.gstage, cs.cout, cs.cin, cs.k * cs.k, G + t.w_off[i]));  // (kh,kw,c) -> (c,kh,kw)
+      DTB_TRY(gemm_wgrad(ss, tw.dZ[i], cs.cout, tw.P[i], kc, cs.cout, kc, rows, tw.gstage, kc, w.partial, w.partial_floats));
+      DTB_TRY(permute_unstage(ss, tw.gstage, cs.cout, cs.cin, cs.k * cs.k, G + t.w_off[i]));  // (kh,kw,c) -> (c,kh,kw)
     }
-    DTB_TRY(colsum_bf16(st, tw.dZ[i], rows, cs.cout, cs.cout, G + t.b_off[i], 0, w.cs_scratch));
+    DTB_TRY(colsum_bf16(ss, tw.dZ[i], rows, cs.cout, cs.cout, G + t.b_off[i], 0, w.cs_scratch));
     if (i > 0) {
       GemmEpilogue ep = epz();
       ep.out_bf16 = tw.dP;
@@ -252,7 +258,11 @@ int dtb_encoder_create(const dtb_encoder_config* cfg, dtb_encoder** out) {
   *out = e;
   return DTB_OK;
 }
-int dtb_encoder_destroy(dtb_encoder* e) { delete e; return DTB_OK; }
+int dtb_encoder_destroy(dtb_encoder* e) {
+  if (e) e->side.destroy();
+  delete e;
+  return DTB_OK;
+}
 int dtb_encoder_state_dim(const dtb_encoder* e) { return e ? e->state_dim : DTB_ERR_BAD_ARG; }
 int dtb_encoder_param_entries(const dtb_encoder* e) { return e ? e->n_entries : DTB_ERR_BAD_ARG; }
 long long dtb_encoder_param_layout(const dtb_encoder* e, long long* offsets, long long* numels) {
@@ -304,14 +314,20 @@ int dtb_encoder_forward(const dtb_encoder* e, void* stream, const float* params,
   cudaStream_t st = (cudaStream_t)stream;
   EncWs w;
   DTB_TRY(enc_ws(e, N, workspace, workspace_bytes, w));
+  DTB_TRY(e->side.init());
   const bf16* Ps = (const bf16*)staged;
   bf16* out = (bf16*)states_bf16;
   if (e->c.fusion == 0) {  // concat: each tower's FC epilogue writes its half of [N, state_dim]  (agents.py:137-139, dim=1 semantics)
+    // the two towers are independent: audio runs on the side branch, video on the caller's stream
+    DTB_TRY(e->side.fork(st));
+    DTB_TRY(tower_forward(e, 1, e->side.pick(st), params, Ps, N, audio, w.t[1], out + e->t[0].feat, e->state_dim));
     DTB_TRY(tower_forward(e, 0, st, params, Ps, N, frames, w.t[0], out, e->state_dim));
-    DTB_TRY(tower_forward(e, 1, st, params, Ps, N, audio, w.t[1], out + e->t[0].feat, e->state_dim));
+    DTB_TRY(e->side.join(st));
   } else {  // sum (agents.py:140-141)
+    DTB_TRY(e->side.fork(st));
+    DTB_TRY(tower_forward(e, 1, e->side.pick(st), params, Ps, N, audio, w.t[1], w.feat[1], e->t[1].feat));
     DTB_TRY(tower_forward(e, 0, st, params, Ps, N, frames, w.t[0], w.feat[0], e->t[0].feat));
-    DTB_TRY(tower_forward(e, 1, st, params, Ps, N, audio, w.t[1], w.feat[1], e->t[1].feat));
+    DTB_TRY(e->side.join(st));
     DTB_TRY(add_bf16(st, w.feat[0], w.feat[1], (size_t)N * e->t[0].feat, out));
   }
   return DTB_OK;
@@ -328,6 +344,7 @@ int dtb_encoder_backward(const dtb_encoder* e, void* stream, const float* params
   }
   EncWs w;
   DTB_TRY(enc_ws(e, N, workspace, workspace_bytes, w));
+  DTB_TRY(e->side.init());
   const bf16* Ps = (const bf16*)staged;
   const bf16* dS = (const bf16*)d_states_bf16;
   if (e->c.fusion == 0) {
@@ -344,9 +361,10 @@ int dtb_encoder_backward(const dtb_encoder* e, void* stream, const float* params
     for (int ti = 0; ti < 2; ++ti) {
       DTB_TRY(relu_mask_bf16(st, dS, F, w.feat[ti], F, N, F, w.dfeat, F));
       DTB_TRY(tower_backward(e, ti, st, Ps, N, ti == 0 ? frames : audio, w.dfeat, F, w.t[ti], w, grads));
+      DTB_TRY(e->side.join(st));  // w.dfeat is reused by the next tower
     }
   }
-  return DTB_OK;
+  return e->side.join(st);
 }
 
 }  // extern "C"

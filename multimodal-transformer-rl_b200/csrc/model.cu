@@ -6,6 +6,7 @@
 //   backward: the autograd of the same graph, in reverse, split into stages for data-parallel overlap.
 #include "../../include/dtb200.h"
 #include "kernels.h"
+#include "side.h"
 
 #include <new>
 #include <string.h>
@@ -29,7 +30,7 @@ struct Workspace {
   bf16 *U, *states_b, *yf;
   // backward temporaries
   float *dX, *delta, *G, *bsum, *partial, *cs_scratch, *ln_scratch, *mse_scratch, *tmpf;
-  bf16 *dXb, *tmp_big, *tmp_h, *dzA, *dzS;
+  bf16 *dXb, *dXb2, *tmp_big, *tmp_big2, *tmp_h, *dzA, *dzS;
   size_t partial_floats;
   size_t total;
 };
@@ -44,6 +45,7 @@ struct dtb_dt {
   long long total;
   int sd_small;  // fused fp32 state projection (sd <= 64) vs tensor-core projection of a wide state
   int P8, ZA8, ZS8;
+  mutable dtb::SideStream side;  // weight-gradient branch of the backward
   long long e(int id) const { return off[id]; }
   long long l(int layer, int id) const { return off[E_COUNT + layer * L_COUNT + id]; }
   long long t(int id) const { return off[E_COUNT + c.n_layer * L_COUNT + id]; }
@@ -101,9 +103,9 @@ static void carve_workspace(const dtb_dt* h, int B, int K, uint8_t* base, Worksp
   w.yf = carve<bf16>(p, M * H); w.meanf = carve<float>(p, M); w.rstdf = carve<float>(p, M);
   w.ap = carve<float>(p, BK * ad); w.d_ap = carve<float>(p, BK * ad);
   // backward temporaries
-  w.dX = carve<float>(p, M * H); w.dXb = carve<bf16>(p, M * H);
+  w.dX = carve<float>(p, M * H); w.dXb = carve<bf16>(p, M * H); w.dXb2 = carve<bf16>(p, M * H);
   const size_t big = I > 3 * H ? I : 3 * H;
-  w.tmp_big = carve<bf16>(p, M * big); w.tmp_h = carve<bf16>(p, M * H);
+  w.tmp_big = carve<bf16>(p, M * big); w.tmp_big2 = carve<bf16>(p, M * 3 * H); w.tmp_h = carve<bf16>(p, M * H);
   w.delta = carve<float>(p, (size_t)B * c.n_head * T);
   w.dzA = carve<bf16>(p, BK * h->ZA8); w.dzS = carve<bf16>(p, BK * h->ZS8);
   w.G = carve<float>(p, 3 * H * h->P8); w.bsum = carve<float>(p, 3 * H);
@@ -227,29 +229,32 @@ static int dt_forward(const dtb_dt* h, cudaStream_t st, const float* P, const vo
 
 static int bwd_heads(const dtb_dt* h, cudaStream_t st, const float* P, const dtb_dt_batch* b, Workspace& w, const float* d_action,
                      const float* d_state, const float* d_return, float* G) {
+  SideStream& sd_ = h->side;
   const dtb_dt_config& c = h->c;
   const int L = c.n_layer, H = c.hidden, sd = c.state_dim, ad = c.act_dim;
   const int BK = b->B * b->K, M = BK * 3;
   DTB_TRY(heads_bwd(st, d_action, d_state, d_return, w.ap, P + h->t(T_WPA), P + h->t(T_WPS), P + h->t(T_WPR), BK, H, sd, ad,
                     c.action_tanh, h->ZA8, h->ZS8, w.tmp_h, w.dzA, w.dzS));
+  DTB_TRY(sd_.fork(st));
+  cudaStream_t ss = sd_.pick(st);  // head weight gradients: side branch
   const bf16* y_s = w.yf + H;      // state-token rows, stride 3H
   const bf16* y_a = w.yf + 2 * H;  // action-token rows
   if (d_action) {
-    DTB_TRY(gemm_wgrad(st, w.dzA, h->ZA8, y_s, 3 * H, ad, H, BK, G + h->t(T_WPA), H, w.partial, w.partial_floats));
-    DTB_TRY(colsum_bf16(st, w.dzA, BK, h->ZA8, h->ZA8, G + h->t(T_BPA), 0, w.cs_scratch));
+    DTB_TRY(gemm_wgrad(ss, w.dzA, h->ZA8, y_s, 3 * H, ad, H, BK, G + h->t(T_WPA), H, w.partial, w.partial_floats));
+    DTB_TRY(colsum_bf16(ss, w.dzA, BK, h->ZA8, h->ZA8, G + h->t(T_BPA), 0, w.cs_scratch));
   } else {
-    DTB_CUDA(cudaMemsetAsync(G + h->t(T_WPA), 0, pad8((long long)ad * H) * sizeof(float), st));
-    DTB_CUDA(cudaMemsetAsync(G + h->t(T_BPA), 0, pad8(ad) * sizeof(float), st));
+    DTB_CUDA(cudaMemsetAsync(G + h->t(T_WPA), 0, pad8((long long)ad * H) * sizeof(float), ss));
+    DTB_CUDA(cudaMemsetAsync(G + h->t(T_BPA), 0, pad8(ad) * sizeof(float), ss));
   }
   if (d_state || d_return) {
     // predict_state.weight [sd,H] and predict_return.weight [1,H] are adjacent in the flat layout: one [sd+1, H] product
-    DTB_TRY(gemm_wgrad(st, w.dzS, h->ZS8, y_a, 3 * H, sd + 1, H, BK, G + h->t(T_WPS), H, w.partial, w.partial_floats));
-    DTB_TRY(colsum_bf16(st, w.dzS, BK, h->ZS8, h->ZS8, w.tmpf, 0, w.cs_scratch));
-    DTB_TRY(copy2d(st, w.tmpf, h->ZS8, 1, sd, G + h->t(T_BPS), sd));
-    DTB_TRY(copy2d(st, w.tmpf + sd, h->ZS8, 1, 1, G + h->t(T_BPR), 1));
+    DTB_TRY(gemm_wgrad(ss, w.dzS, h->ZS8, y_a, 3 * H, sd + 1, H, BK, G + h->t(T_WPS), H, w.partial, w.partial_floats));
+    DTB_TRY(colsum_bf16(ss, w.dzS, BK, h->ZS8, h->ZS8, w.tmpf, 0, w.cs_scratch));
+    DTB_TRY(copy2d(ss, w.tmpf, h->ZS8, 1, sd, G + h->t(T_BPS), sd));
+    DTB_TRY(copy2d(ss, w.tmpf + sd, h->ZS8, 1, 1, G + h->t(T_BPR), 1));
   } else {
-    DTB_CUDA(cudaMemsetAsync(G + h->t(T_WPS), 0, (pad8((long long)sd * H) + pad8(H)) * sizeof(float), st));
-    DTB_CUDA(cudaMemsetAsync(G + h->t(T_BPS), 0, (pad8(sd) + pad8(1)) * sizeof(float), st));
+    DTB_CUDA(cudaMemsetAsync(G + h->t(T_WPS), 0, (pad8((long long)sd * H) + pad8(H)) * sizeof(float), ss));
+    DTB_CUDA(cudaMemsetAsync(G + h->t(T_BPS), 0, (pad8(sd) + pad8(1)) * sizeof(float), ss));
   }
   DTB_TRY(ln_bwd(st, w.tmp_h, w.xs[L], w.meanf, w.rstdf, P + h->t(T_LNFW), nullptr, M, H, w.dX, w.dXb, G + h->t(T_LNFW), G + h->t(T_LNFB),
                  w.ln_scratch));
@@ -257,51 +262,63 @@ static int bwd_heads(const dtb_dt* h, cudaStream_t st, const float* P, const dtb
 }
 
 static int bwd_layer(const dtb_dt* h, cudaStream_t st, const float* P, const void* Pb, const dtb_dt_batch* b, Workspace& w, int l,
-                     float* G) {
+                     float* G, bool& attn_marked) {
   const dtb_dt_config& c = h->c;
   const int H = c.hidden, I = c.n_inner, nh = c.n_head, d = H / nh;
   const int B = b->B, BK = B * b->K, M = BK * 3, T = 3 * b->K;
+  SideStream& sd = h->side;
+  cudaStream_t ss = sd.pick(st);
+  // Main stream: the data-gradient chain.  Side stream: weight / bias gradients (they only read).  X / Y ping-pong the bf16 gradient
+  // stream and T1 / T2 hold dfc / dqkv, so the chain never overwrites a buffer the side branch may still be reading without a wait.
+  bf16 *X = w.dXb, *Y = w.dXb2, *T1 = w.tmp_big, *T2 = w.tmp_big2;
   // ---- MLP ----
   {  // dfc = (dX W2^T) * act'(.)
     GemmEpilogue ep = ep_zero();
     ep.dact = c.activation;
     ep.aux = c.activation == 2 ? w.pre[l] : w.fc[l];
     ep.ldaux = I;
-    ep.out_bf16 = w.tmp_big;
+    ep.out_bf16 = T1;
     ep.ldo_b = I;
-    DTB_TRY(gemm_fwd(st, w.dXb, H, bfp(Pb, h->l(l, L_W2)), H, false, M, I, H, ep));
+    DTB_TRY(gemm_fwd(st, X, H, bfp(Pb, h->l(l, L_W2)), H, false, M, I, H, ep));
   }
-  DTB_TRY(gemm_wgrad(st, w.fc[l], I, w.dXb, H, I, H, M, G + h->l(l, L_W2), H, w.partial, w.partial_floats));
-  DTB_TRY(colsum_bf16(st, w.dXb, M, H, H, G + h->l(l, L_B2), 0, w.cs_scratch));
+  DTB_TRY(sd.fork(st));
+  DTB_TRY(gemm_wgrad(ss, w.fc[l], I, X, H, I, H, M, G + h->l(l, L_W2), H, w.partial, w.partial_floats));
+  DTB_TRY(colsum_bf16(ss, X, M, H, H, G + h->l(l, L_B2), 0, w.cs_scratch));
+  DTB_TRY(gemm_wgrad(ss, w.h2[l], H, T1, I, H, I, M, G + h->l(l, L_W1), I, w.partial, w.partial_floats));
+  DTB_TRY(colsum_bf16(ss, T1, M, I, I, G + h->l(l, L_B1), 0, w.cs_scratch));
+  DTB_TRY(sd.mark(sd.ev_a));
   {  // dh2 = dfc W1^T
     GemmEpilogue ep = ep_zero();
     ep.out_bf16 = w.tmp_h;
     ep.ldo_b = H;
-    DTB_TRY(gemm_fwd(st, w.tmp_big, I, bfp(Pb, h->l(l, L_W1)), I, false, M, H, I, ep));
+    DTB_TRY(gemm_fwd(st, T1, I, bfp(Pb, h->l(l, L_W1)), I, false, M, H, I, ep));
   }
-  DTB_TRY(gemm_wgrad(st, w.h2[l], H, w.tmp_big, I, H, I, M, G + h->l(l, L_W1), I, w.partial, w.partial_floats));
-  DTB_TRY(colsum_bf16(st, w.tmp_big, M, I, I, G + h->l(l, L_B1), 0, w.cs_scratch));
-  DTB_TRY(ln_bwd(st, w.tmp_h, w.xmid[l], w.mean2[l], w.rstd2[l], P + h->l(l, L_LN2W), w.dX, M, H, w.dX, w.dXb, G + h->l(l, L_LN2W),
+  if (attn_marked) DTB_TRY(sd.wait(st, sd.ev_b));  // the previous block's attention weight gradients still read Y / T2
+  DTB_TRY(ln_bwd(st, w.tmp_h, w.xmid[l], w.mean2[l], w.rstd2[l], P + h->l(l, L_LN2W), w.dX, M, H, w.dX, Y, G + h->l(l, L_LN2W),
                  G + h->l(l, L_LN2B), w.ln_scratch));
   // ---- attention ----
   {  // do = dX Wo^T
     GemmEpilogue ep = ep_zero();
     ep.out_bf16 = w.tmp_h;
     ep.ldo_b = H;
-    DTB_TRY(gemm_fwd(st, w.dXb, H, bfp(Pb, h->l(l, L_WO)), H, false, M, H, H, ep));
+    DTB_TRY(gemm_fwd(st, Y, H, bfp(Pb, h->l(l, L_WO)), H, false, M, H, H, ep));
   }
-  DTB_TRY(gemm_wgrad(st, w.o[l], H, w.dXb, H, H, H, M, G + h->l(l, L_WO), H, w.partial, w.partial_floats));
-  DTB_TRY(colsum_bf16(st, w.dXb, M, H, H, G + h->l(l, L_BO), 0, w.cs_scratch));
-  DTB_TRY(attn_bwd(st, w.qkv[l], b->attention_mask, w.o[l], w.tmp_h, w.lse[l], B, T, nh, d, w.tmp_big, w.delta));
+  DTB_TRY(attn_bwd(st, w.qkv[l], b->attention_mask, w.o[l], w.tmp_h, w.lse[l], B, T, nh, d, T2, w.delta));
+  DTB_TRY(sd.fork(st));
+  DTB_TRY(gemm_wgrad(ss, w.o[l], H, Y, H, H, H, M, G + h->l(l, L_WO), H, w.partial, w.partial_floats));
+  DTB_TRY(colsum_bf16(ss, Y, M, H, H, G + h->l(l, L_BO), 0, w.cs_scratch));
+  DTB_TRY(gemm_wgrad(ss, w.h1[l], H, T2, 3 * H, H, 3 * H, M, G + h->l(l, L_WQKV), 3 * H, w.partial, w.partial_floats));
+  DTB_TRY(colsum_bf16(ss, T2, M, 3 * H, 3 * H, G + h->l(l, L_BQKV), 0, w.cs_scratch));
+  DTB_TRY(sd.mark(sd.ev_b));
+  attn_marked = sd.on();
   {  // dh1 = dqkv Wqkv^T
     GemmEpilogue ep = ep_zero();
     ep.out_bf16 = w.tmp_h;
     ep.ldo_b = H;
-    DTB_TRY(gemm_fwd(st, w.tmp_big, 3 * H, bfp(Pb, h->l(l, L_WQKV)), 3 * H, false, M, H, 3 * H, ep));
+    DTB_TRY(gemm_fwd(st, T2, 3 * H, bfp(Pb, h->l(l, L_WQKV)), 3 * H, false, M, H, 3 * H, ep));
   }
-  DTB_TRY(gemm_wgrad(st, w.h1[l], H, w.tmp_big, 3 * H, H, 3 * H, M, G + h->l(l, L_WQKV), 3 * H, w.partial, w.partial_floats));
-  DTB_TRY(colsum_bf16(st, w.tmp_big, M, 3 * H, 3 * H, G + h->l(l, L_BQKV), 0, w.cs_scratch));
-  DTB_TRY(ln_bwd(st, w.tmp_h, w.xs[l], w.mean1[l], w.rstd1[l], P + h->l(l, L_LN1W), w.dX, M, H, w.dX, w.dXb, G + h->l(l, L_LN1W),
+  DTB_TRY(sd.wait(st, sd.ev_a));  // the MLP weight gradients read X and T1, which the next two kernels / the next block overwrite
+  DTB_TRY(ln_bwd(st, w.tmp_h, w.xs[l], w.mean1[l], w.rstd1[l], P + h->l(l, L_LN1W), w.dX, M, H, w.dX, X, G + h->l(l, L_LN1W),
                  G + h->l(l, L_LN1B), w.ln_scratch));
   return DTB_OK;
 }
@@ -314,16 +331,19 @@ static int bwd_embed(const dtb_dt* h, cudaStream_t st, const float* P, const voi
   // embed_ln backward: d_pre (bf16, [BK, 3H] view of [M, H]) -> tmp_h
   DTB_TRY(ln_bwd(st, w.dXb, w.pre0, w.mean0, w.rstd0, P + h->e(E_LNW), nullptr, M, H, nullptr, w.tmp_h, G + h->e(E_LNW), G + h->e(E_LNB),
                  w.ln_scratch));
-  DTB_CUDA(cudaMemsetAsync(G + h->e(E_TABLE), 0, (size_t)E * H * sizeof(float), st));
-  DTB_TRY(embed_te_scatter(st, w.tmp_h, b->timesteps, BK, H, E, G + h->e(E_TABLE)));
-  DTB_TRY(gemm_wgrad(st, w.tmp_h, 3 * H, w.U, h->P8, 3 * H, h->P8, BK, w.G, h->P8, w.partial, w.partial_floats));
-  DTB_TRY(colsum_bf16(st, w.tmp_h, BK, 3 * H, 3 * H, w.bsum, 0, w.cs_scratch));
-  DTB_TRY(embed_unpack(st, w.G, w.bsum, H, sd, ad, h->P8, h->sd_small, G + h->e(E_WR), G + h->e(E_BR), G + h->e(E_WS), G + h->e(E_BS),
+  SideStream& sside = h->side;
+  DTB_TRY(sside.fork(st));
+  cudaStream_t ss = sside.pick(st);  // parameter gradients on the side branch; d_states (towers' input) stays on the main chain
+  DTB_CUDA(cudaMemsetAsync(G + h->e(E_TABLE), 0, (size_t)E * H * sizeof(float), ss));
+  DTB_TRY(embed_te_scatter(ss, w.tmp_h, b->timesteps, BK, H, E, G + h->e(E_TABLE)));
+  DTB_TRY(gemm_wgrad(ss, w.tmp_h, 3 * H, w.U, h->P8, 3 * H, h->P8, BK, w.G, h->P8, w.partial, w.partial_floats));
+  DTB_TRY(colsum_bf16(ss, w.tmp_h, BK, 3 * H, 3 * H, w.bsum, 0, w.cs_scratch));
+  DTB_TRY(embed_unpack(ss, w.G, w.bsum, H, sd, ad, h->P8, h->sd_small, G + h->e(E_WR), G + h->e(E_BR), G + h->e(E_WS), G + h->e(E_BS),
                        G + h->e(E_WA), G + h->e(E_BA)));
   if (!h->sd_small) {
     const bf16* dpre_s = w.tmp_h + H;  // state-token rows of d_pre, stride 3H
     const bf16* sb = b->states_bf16 ? reinterpret_cast<const bf16*>(b->states_bf16) : w.states_b;
-    DTB_TRY(gemm_wgrad(st, dpre_s, 3 * H, sb, sd, H, sd, BK, G + h->e(E_WS), sd, w.partial, w.partial_floats));
+    DTB_TRY(gemm_wgrad(ss, dpre_s, 3 * H, sb, sd, H, sd, BK, G + h->e(E_WS), sd, w.partial, w.partial_floats));
     if (d_states) {  // d_states = d_pre_s Ws   (Ws [H, sd] read as MN-major B)
       GemmEpilogue ep = ep_zero();
       ep.out_bf16 = d_states;
@@ -369,6 +389,7 @@ int dtb_dt_create(const dtb_dt_config* cfg, dtb_dt** out) {
 }
 
 int dtb_dt_destroy(dtb_dt* h) {
+  if (h) h->side.destroy();
   delete h;
   return DTB_OK;
 }
@@ -445,12 +466,14 @@ int dtb_dt_backward(const dtb_dt* h, void* stream, const float* params, const vo
     DTB_CUDA(cudaMemsetAsync(grads + lo, 0, (size_t)(hi - lo) * sizeof(float), st));
     return DTB_OK;
   }
+  DTB_TRY(h->side.init());
+  bool attn_marked = false;
   for (int s = stage_begin; s <= stage_end; ++s) {
     if (s == 0) DTB_TRY(bwd_heads(h, st, params, batch, w, d_action_preds ? d_action_preds : w.d_ap, d_state_preds, d_return_preds, grads));
-    else if (s <= L) DTB_TRY(bwd_layer(h, st, params, params_bf16, batch, w, L - s, grads));
+    else if (s <= L) DTB_TRY(bwd_layer(h, st, params, params_bf16, batch, w, L - s, grads, attn_marked));
     else DTB_TRY(bwd_embed(h, st, params, params_bf16, batch, w, grads, (bf16*)d_states_bf16));
   }
-  return DTB_OK;
+  return h->side.join(st);
 }
 
 int dtb_dt_stage_grad_range(const dtb_dt* h, int stage, long long* begin, long long* end) {
