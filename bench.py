@@ -349,9 +349,57 @@ def run_cpu(wl, steps, warmup, budget_s=20.0):
                       f"({tokens} tokens/step), {steps} steps after {warmup} warm-up, {cores} threads", "loss": loss}
 
 
-def measure_roofline(args, wl, ctx):
-    """Dominant kernel timed alone with CUDA events (filled in once the ncu launch list names it)."""
-    return None
+PROF_FAMILIES = [("gemm_tcgen05_kernel", "tensor"), ("conv1_fwd_kernel", "hbm"), ("conv1_wgrad_kernel", "hbm"), ("attn_fwd_kernel", "tensor"),
+                 ("attn_bwd_dq+dkv_kernel", "tensor"), ("ln_fwd_kernel", "hbm"), ("ln_bwd_kernel(+finalize)", "hbm"), ("embed_fwd_kernel", "hbm"),
+                 ("colsum_stage1+2", "hbm"), ("im2col_nhwc_kernel", "hbm"), ("col2im_nhwc_relu_kernel", "hbm")]
+
+
+def measure_roofline(args, wl, ctx, reps=5):
+    """Per-kernel-family durations measured live with CUDA events recorded by the library on the stream each kernel is launched on
+    (plain launches, same process, right after the timed region).  The dominant family (largest share of the step) is reported:
+    achieved = its algorithmic flops (tensor) or bytes (hbm) / its summed launch durations; peak = MEASURED_PEAKS.json."""
+    import ctypes as C
+
+    from mtrl_b200 import _lib
+
+    lib = _lib.load()
+    peaks = {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "source": "fallback (B200_PROFILING.md)"}
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as fh:
+            mp = json.load(fh)
+        peaks = {"hbm_gbs": float(mp["hbm_gbs"]), "bf16_tflops": float(mp["bf16_tflops"]), "source": "measured (MEASURED_PEAKS.json, burst)"}
+    except Exception:
+        pass
+    step = ctx["step"]
+    step()
+    torch.cuda.synchronize()
+    lib.dtb_profile_enable(1)
+    for _ in range(reps):
+        step()
+    torch.cuda.synchronize()
+    fams = []
+    for i, (name, bound) in enumerate(PROF_FAMILIES):
+        ms, work, n = C.c_double(), C.c_double(), C.c_longlong()
+        _lib.check(lib.dtb_profile_report(i, C.byref(ms), C.byref(work), C.byref(n)))
+        if n.value:
+            fams.append(dict(kernel=name, bound=bound, ms_per_step=ms.value / reps, launches_per_step=n.value // reps, work_per_step=work.value / reps))
+    lib.dtb_profile_enable(0)
+    if not fams:
+        return None
+    total = sum(f["ms_per_step"] for f in fams)
+    for f in fams:
+        f["share_of_profiled"] = f["ms_per_step"] / total
+        if f["bound"] == "tensor":
+            f["achieved"], f["unit"], f["peak"] = f["work_per_step"] / f["ms_per_step"] / 1e9, "TFLOP/s", peaks["bf16_tflops"]
+        else:
+            f["achieved"], f["unit"], f["peak"] = f["work_per_step"] / f["ms_per_step"] / 1e6, "GB/s", peaks["hbm_gbs"]
+        f["frac"] = f["achieved"] / f["peak"]
+    top = max(fams, key=lambda f: f["ms_per_step"])
+    return {"kernel": top["kernel"], "bound": top["bound"], "achieved": top["achieved"], "peak": top["peak"], "unit": top["unit"],
+            "frac": top["frac"], "traffic": None, "peak_source": peaks["source"], "launches_per_step": top["launches_per_step"],
+            "avg_launch_us": top["ms_per_step"] / max(1, top["launches_per_step"]) * 1e3,
+            "how": f"CUDA events around every launch of the family on its own stream, {reps} un-graphed steps; algorithmic work per DESIGN.md §3",
+            "families": sorted(fams, key=lambda f: -f["ms_per_step"])}
 
 
 def main():

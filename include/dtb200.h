@@ -38,6 +38,12 @@ const char* dtb_last_error(void);
 int dtb_check_device(void);
 /* Number of kernels this library has launched in this process (the bench's gpu_launches evidence). */
 long long dtb_launch_count(void);
+/* Live per-kernel-family timing for bench.py's roofline: when enabled (and the stream is not being captured) every launch of a
+ * family is bracketed by CUDA events on its own stream.  family: 0 gemm (work = flops), 1 conv1 fwd (bytes), 2 conv1 wgrad (bytes),
+ * 3 attention fwd (flops), 4 attention bwd (flops), 5 LN fwd (bytes), 6 LN bwd (bytes), 7 embed fwd (bytes), 8 colsum (bytes),
+ * 9 im2col (bytes), 10 col2im (bytes).  report() synchronises the events and returns summed milliseconds, algorithmic work, launches. */
+void dtb_profile_enable(int on);
+int dtb_profile_report(int family, double* total_ms, double* work, long long* launches);
 
 /* ---- tensor-core GEMM (tcgen05 + TMEM + TMA) --------------------------------------------------
  * D[M,N] = epilogue(A x B^T-style product), bf16 operands, fp32 accumulation.

@@ -5,6 +5,9 @@
 #include <string.h>
 
 namespace dtb {
+void prof_enable(bool on);
+void prof_reset();
+int prof_report(int family, double* total_ms, double* work, long long* launches);
 const char* last_error();
 int require_sm100();
 }  // namespace dtb
@@ -17,6 +20,10 @@ int dtb_abi_version(void) { return DTB_ABI_VERSION; }
 const char* dtb_last_error(void) { return dtb::last_error(); }
 int dtb_check_device(void) { return dtb::require_sm100(); }
 long long dtb_launch_count(void) { return dtb::launch_count(); }
+void dtb_profile_enable(int on) { dtb::prof_enable(on != 0); if (on) dtb::prof_reset(); }
+int dtb_profile_report(int family, double* total_ms, double* work, long long* launches) {
+  return dtb::prof_report(family, total_ms, work, launches);
+}
 
 int dtb_gemm_bf16(void* stream, const void* A, int lda, int a_mn_major, const void* B, int ldb, int b_mn_major, int M, int N, int K,
                   const dtb_gemm_epilogue* e, int split_k, int bn_override) {

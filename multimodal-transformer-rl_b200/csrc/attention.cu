@@ -144,6 +144,7 @@ static int launch_fwd(cudaStream_t stream, const bf16* qkv, const float* mask, i
   }
   const float scale_log2 = 1.4426950408889634f / sqrtf((float)D);
   dim3 grid((T + 63) / 64, nh, B);
+  ProfScope prof(stream, PF_ATTN_FWD, 2.0 * B * nh * (double)T * T * D);
   attn_fwd_kernel<D><<<grid, 128, smem, stream>>>(qkv, mask, T, nh, T / 3, scale_log2, out, lse);
   DTB_CHECK_LAUNCH();
   return DTB_OK;

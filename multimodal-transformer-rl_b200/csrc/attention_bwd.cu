@@ -269,6 +269,7 @@ static int launch_bwd(cudaStream_t stream, const bf16* qkv, const float* mask, c
   const float scale = 1.f / sqrtf((float)D);
   const float scale_log2 = 1.4426950408889634f * scale;
   dim3 grid((T + 63) / 64, nh, B);
+  ProfScope prof(stream, PF_ATTN_BWD, 5.0 * B * nh * (double)T * T * D);
   attn_bwd_dq_kernel<D><<<grid, 128, smem, stream>>>(qkv, mask, out, dout, lse, T, nh, T / 3, scale, scale_log2, dqkv, delta);
   DTB_CHECK_LAUNCH();
   attn_bwd_dkv_kernel<D><<<grid, 128, smem, stream>>>(qkv, mask, dout, lse, delta, T, nh, T / 3, scale, scale_log2, dqkv);

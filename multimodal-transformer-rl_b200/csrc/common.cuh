@@ -54,6 +54,18 @@ int num_sms();
 void count_launch();
 long long launch_count();
 
+// Optional live profiling (bench.py roofline): CUDA events recorded on the launching stream around each launch of a kernel family.
+enum ProfFamily { PF_GEMM = 0, PF_CONV1_FWD, PF_CONV1_WGRAD, PF_ATTN_FWD, PF_ATTN_BWD, PF_LN_FWD, PF_LN_BWD, PF_EMBED_FWD, PF_COLSUM,
+                  PF_IM2COL, PF_COL2IM, PF_COUNT };
+bool prof_on();
+int prof_begin(cudaStream_t stream, int family, double work);  // returns a slot (or -1)
+void prof_end(cudaStream_t stream, int slot);
+struct ProfScope {
+  cudaStream_t st; int slot;
+  ProfScope(cudaStream_t s, int family, double work) : st(s), slot(prof_on() ? prof_begin(s, family, work) : -1) {}
+  ~ProfScope() { if (slot >= 0) prof_end(st, slot); }
+};
+
 typedef __nv_bfloat16 bf16;
 typedef __nv_bfloat162 bf162;
 

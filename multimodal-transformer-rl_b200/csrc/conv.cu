@@ -72,6 +72,7 @@ int im2col_nhwc(cudaStream_t stream, const bf16* x, int N, int H, int W, int C, 
   size_t blocks = (total + 255) / 256;
   const size_t cap = (size_t)num_sms() * 16;
   if (blocks > cap) blocks = cap;
+  ProfScope prof(stream, PF_IM2COL, 2.0 * N * H * W * C + 2.0 * (double)total * 8);
   im2col_nhwc_kernel<<<(unsigned)blocks, 256, 0, stream>>>(x, N, H, W, C, k, stride, ho, wo, p);
   DTB_CHECK_LAUNCH();
   return DTB_OK;
@@ -121,6 +122,7 @@ int col2im_nhwc_relu(cudaStream_t stream, const bf16* dp, const bf16* y, int N, 
   size_t blocks = (total + 255) / 256;
   const size_t cap = (size_t)num_sms() * 16;
   if (blocks > cap) blocks = cap;
+  ProfScope prof(stream, PF_COL2IM, 4.0 * N * H * W * C + 2.0 * (double)N * ho * wo * k * k * C);
   col2im_nhwc_relu_kernel<<<(unsigned)blocks, 256, 0, stream>>>(dp, y, N, H, W, C, k, stride, ho, wo, dz);
   DTB_CHECK_LAUNCH();
   return DTB_OK;

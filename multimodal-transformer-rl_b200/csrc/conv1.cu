@@ -277,6 +277,7 @@ int conv1_fwd(cudaStream_t stream, const float* x, int N, int C, int H, int W, i
   static bool attr = false;
   if (!attr) { DTB_CUDA(cudaFuncSetAttribute(conv1_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 225 * 1024)); attr = true; }
   const int grid = p.tiles < num_sms() ? p.tiles : num_sms();
+  ProfScope prof(stream, PF_CONV1_FWD, 4.0 * N * C * H * W + 2.0 * (double)p.rows * cout);
   conv1_fwd_kernel<<<grid, C1_THREADS, smem, stream>>>(tmW, p);
   DTB_CHECK_LAUNCH();
   return DTB_OK;
@@ -298,8 +299,11 @@ int conv1_wgrad(cudaStream_t stream, const float* x, int N, int C, int H, int W,
   if (!attr) { DTB_CUDA(cudaFuncSetAttribute(conv1_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 225 * 1024)); attr = true; }
   int grid = p.tiles < num_sms() ? p.tiles : num_sms();
   if (grid > DTB_NUM_SMS_FALLBACK) grid = DTB_NUM_SMS_FALLBACK;
+  ProfScope prof(stream, PF_CONV1_WGRAD, 4.0 * N * C * H * W + 2.0 * (double)p.rows * cout);
   conv1_wgrad_kernel<<<grid, C1_THREADS, smem, stream>>>(tmZ, p);
   DTB_CHECK_LAUNCH();
+  prof.~ProfScope();
+  prof.slot = -1;
   return splitk_reduce(stream, partial, grid, cout, 64 * C, dw, 64 * C, 0, 1.f);
 }
 

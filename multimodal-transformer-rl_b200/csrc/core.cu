@@ -26,6 +26,48 @@ static long long g_launches = 0;
 void count_launch() { __atomic_add_fetch(&g_launches, 1, __ATOMIC_RELAXED); }
 long long launch_count() { return __atomic_load_n(&g_launches, __ATOMIC_RELAXED); }
 
+// ---- live profiling ------------------------------------------------------------------------------------------------
+static bool g_prof = false;
+static const int PROF_SLOTS = 8192;
+static cudaEvent_t g_pe0[PROF_SLOTS], g_pe1[PROF_SLOTS];
+static int g_pfam[PROF_SLOTS];
+static double g_pwork[PROF_SLOTS];
+static int g_pn = 0, g_pcreated = 0;
+bool prof_on() { return g_prof; }
+void prof_enable(bool on) { g_prof = on; }
+void prof_reset() { g_pn = 0; }
+int prof_begin(cudaStream_t stream, int family, double work) {
+  if (g_pn >= PROF_SLOTS) return -1;
+  cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+  if (cudaStreamIsCapturing(stream, &cs) != cudaSuccess || cs != cudaStreamCaptureStatusNone) return -1;
+  const int i = g_pn++;
+  if (i >= g_pcreated) {
+    cudaEventCreate(&g_pe0[i]);
+    cudaEventCreate(&g_pe1[i]);
+    g_pcreated = i + 1;
+  }
+  g_pfam[i] = family;
+  g_pwork[i] = work;
+  cudaEventRecord(g_pe0[i], stream);
+  return i;
+}
+void prof_end(cudaStream_t stream, int slot) { cudaEventRecord(g_pe1[slot], stream); }
+int prof_report(int family, double* total_ms, double* work, long long* launches) {
+  double t = 0, w = 0;
+  long long n = 0;
+  for (int i = 0; i < g_pn; ++i) {
+    if (g_pfam[i] != family) continue;
+    if (cudaEventSynchronize(g_pe1[i]) != cudaSuccess) return DTB_ERR_CUDA;
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, g_pe0[i], g_pe1[i]) != cudaSuccess) return DTB_ERR_CUDA;
+    t += ms; w += g_pwork[i]; ++n;
+  }
+  if (total_ms) *total_ms = t;
+  if (work) *work = w;
+  if (launches) *launches = n;
+  return DTB_OK;
+}
+
 static int g_num_sms = 0;
 int num_sms() {
   if (g_num_sms > 0) return g_num_sms;

@@ -119,6 +119,7 @@ int colsum_bf16(cudaStream_t stream, const bf16* x, int M, int N, int ld, float*
   if (nslab > CS_SLABS_MAX) nslab = CS_SLABS_MAX;
   if ((size_t)nslab * N > colsum_scratch_floats(N)) nslab = (int)(colsum_scratch_floats(N) / N);
   if (nslab < 1) nslab = 1;
+  ProfScope prof(stream, PF_COLSUM, 2.0 * M * N);
   colsum_stage1<<<dim3(colgroups, nslab), dim3(cx, ry), 0, stream>>>(x, M, N, ld, scratch);
   DTB_CHECK_LAUNCH();
   colsum_stage2<<<(N + 31) / 32, dim3(32, 8), 0, stream>>>(scratch, nslab, N, out, accumulate);

@@ -183,6 +183,7 @@ int embed_fwd(cudaStream_t stream, const float* states, const float* state_proj,
   int blocks = (BK + 7) / 8;
   const int cap = num_sms() * 2;
   if (blocks > cap) blocks = cap;
+  ProfScope prof(stream, PF_EMBED_FWD, (pre ? 8.0 : 4.0) * BK * 3 * H + 4.0 * BK * (sd + ad + 3));
   embed_fwd_kernel<<<blocks, 256, smem, stream>>>(a);
   DTB_CHECK_LAUNCH();
   return DTB_OK;

@@ -148,6 +148,7 @@ int gemm_bf16(cudaStream_t stream, const bf16* A, int lda, int a_mn_major, const
   }
   const int total = p.m_tiles * p.n_tiles * p.split_k;
   const int grid = total < num_sms() ? total : num_sms();
+  ProfScope prof(stream, PF_GEMM, 2.0 * M * N * K);
   gemm_tcgen05_kernel<<<grid, GEMM_THREADS, GEMM_SMEM_BYTES, stream>>>(tmA, tmB, p);
   DTB_CHECK_LAUNCH();
   return p.split_k;  // >= 1: number of partial slices written when ep.partial != null

@@ -58,6 +58,7 @@ int ln_fwd(cudaStream_t stream, const float* x, const float* gamma, const float*
            float* rstd) {
   DTB_REQUIRE(H % 4 == 0 && H <= LN_MAX_VEC * 128, DTB_ERR_UNSUPPORTED, "layernorm: hidden size %d unsupported (multiple of 4, <= 1024)", H);
   if (M == 0) return DTB_OK;
+  ProfScope prof(stream, PF_LN_FWD, 6.0 * M * H);
   ln_fwd_kernel<<<(M + 7) / 8, 256, 0, stream>>>(x, gamma, beta, M, H, eps, y, mean, rstd);
   DTB_CHECK_LAUNCH();
   return DTB_OK;
@@ -165,6 +166,7 @@ int ln_bwd(cudaStream_t stream, const bf16* dy, const float* x, const float* mea
            const float* dres, int M, int H, float* dx_out, bf16* dx_out_bf16, float* dgamma, float* dbeta, float* scratch) {
   DTB_REQUIRE(H % 4 == 0 && H <= LN_MAX_VEC * 128, DTB_ERR_UNSUPPORTED, "layernorm bwd: hidden size %d unsupported", H);
   const int blocks = ln_bwd_blocks(M);
+  ProfScope prof(stream, PF_LN_BWD, 16.0 * M * H);
   ln_bwd_kernel<<<blocks, 256, 2 * H * sizeof(float), stream>>>(dy, x, mean, rstd, gamma, dres, M, H, dx_out, dx_out_bf16, scratch);
   DTB_CHECK_LAUNCH();
   ln_bwd_finalize<<<(2 * H + 31) / 32, dim3(32, 8), 0, stream>>>(scratch, blocks, H, dgamma, dbeta);
