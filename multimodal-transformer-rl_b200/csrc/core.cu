@@ -39,7 +39,7 @@ void prof_reset() { g_pn = 0; }
 int prof_begin(cudaStream_t stream, int family, double work) {
   if (g_pn >= PROF_SLOTS) return -1;
   cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
-  if (cudaStreamIsCapturing(stream, &cs) != cudaSuccess || cs != cudaStreamCaptureStatusNone) return -1;
+  if (cudaStreamIsCapturing(stream, &cs) != cudaSuccess) return -1;
   const int i = g_pn++;
   if (i >= g_pcreated) {
     cudaEventCreate(&g_pe0[i]);
@@ -48,10 +48,15 @@ int prof_begin(cudaStream_t stream, int family, double work) {
   }
   g_pfam[i] = family;
   g_pwork[i] = work;
-  cudaEventRecord(g_pe0[i], stream);
+  // inside a stream capture the record becomes an external event-record node: every graph replay re-times the kernel in place
+  cudaEventRecordWithFlags(g_pe0[i], stream, cs == cudaStreamCaptureStatusNone ? cudaEventRecordDefault : cudaEventRecordExternal);
   return i;
 }
-void prof_end(cudaStream_t stream, int slot) { cudaEventRecord(g_pe1[slot], stream); }
+void prof_end(cudaStream_t stream, int slot) {
+  cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+  cudaStreamIsCapturing(stream, &cs);
+  cudaEventRecordWithFlags(g_pe1[slot], stream, cs == cudaStreamCaptureStatusNone ? cudaEventRecordDefault : cudaEventRecordExternal);
+}
 int prof_report(int family, double* total_ms, double* work, long long* launches) {
   double t = 0, w = 0;
   long long n = 0;
