@@ -52,7 +52,9 @@ def make_batch(wl, B, seed):
     else:
         g = torch.Generator().manual_seed(seed + 99)
         K = wl["K"]
-        out["frames"] = (torch.randint(0, 256, (B, K, *wl["enc"]["frame_shape"]), generator=g, dtype=torch.uint8).float() / 255.0) * 2 - 1
+        # uint8 pixels, the format the frames exist in before the reference's decode img * 2 / 255 - 1 (Minecraft.py:333-335); our arm
+        # ships the pixels and decodes in-kernel (bit-identical, tests/test_encoder_gpu.py), the CPU arm decodes on the host
+        out["frames"] = torch.randint(0, 256, (B, K, *wl["enc"]["frame_shape"]), generator=g, dtype=torch.uint8)
         out["audio"] = torch.randn(B, K, *wl["enc"]["audio_shape"], generator=g).clamp_(-1, 1)
     return out
 
@@ -199,38 +201,38 @@ def run_ours(args, wl, rank, world, local_rank):
     broadcast_parameters([p.flat_params for p in parts])
     host = make_batch(wl, B, seed=1234 + rank)  # per-rank data seeds (ppo_atari_multigpu.py:197-199); weak scaling: B per GPU fixed
     pinned = {k: v.contiguous().pin_memory() for k, v in host.items()}
-    dev_in = {k: torch.empty_like(v, device=dev) for k, v in pinned.items()}
-    for k in pinned:
-        dev_in[k].copy_(pinned[k], non_blocking=True)
     reducer = GradAllReducer(bucket_bytes=args.bucket_mb << 20) if world > 1 else None
-    raw_step = make_step(wl, model, parts, dev_in, reducer, 1.0 / world)
 
-    def step():
-        for p in parts:
-            p._staged_version = -1  # fp32 -> bf16 weight staging is part of every timed step
-        return raw_step()
+    def make_step_for(dev_in):
+        raw_step = make_step(wl, model, parts, dev_in, reducer, 1.0 / world)
 
-    h2d = sum(v.numel() * v.element_size() for v in pinned.values())
-    for _ in range(max(args.warmup, 3)):
-        out = step()
-    torch.cuda.synchronize(dev)
+        def step():
+            for p in parts:
+                p._staged_version = -1  # fp32 -> bf16 weight staging is part of every timed step
+            return raw_step()
+
+        return step
+
+    from mtrl_b200.pipeline import HostBatchPipeline
+
+    graphed = world == 1 and not args.no_graph
+    try:
+        pipe = HostBatchPipeline(make_step_for, pinned, dev, use_graph=graphed, warmup=max(args.warmup, 3))
+    except Exception as e:  # noqa: BLE001
+        if not graphed:
+            raise
+        print(f"[bench] CUDA graph capture failed ({e}); timing plain launches", file=sys.stderr)
+        torch.cuda.synchronize(dev)
+        graphed = False
+        pipe = HostBatchPipeline(make_step_for, pinned, dev, use_graph=False, warmup=max(args.warmup, 3))
+    slot = pipe.slots[0]
+    dev_in, step = slot["dev"], slot["step"]
+    h2d = pipe.bytes_per_batch
     l0 = lib.dtb_launch_count()
     out = step()
     torch.cuda.synchronize(dev)
     launches_per_step = int(lib.dtb_launch_count() - l0)
-
-    fn, graphed = step, False
-    if world == 1 and not args.no_graph:
-        try:
-            g = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(g):
-                gout = step()
-            g.replay()
-            torch.cuda.synchronize(dev)
-            fn, out, graphed = g.replay, gout, True
-        except Exception as e:  # noqa: BLE001
-            print(f"[bench] CUDA graph capture failed ({e}); timing plain launches", file=sys.stderr)
-            torch.cuda.synchronize(dev)
+    fn = slot["graph"].replay if graphed else step
     # working set per step (inputs + saved activations) vs the 126 MB L2
     ws_bytes = h2d + sum(sum(w.numel() for w in p._ws.values()) for p in parts)
     flush = None
@@ -245,25 +247,17 @@ def run_ours(args, wl, rank, world, local_rank):
     tokens = B * 3 * K * world
     value = tokens / ms * 1e3
 
-    # ---- e2e: pinned host buffers -> H2D -> step -> loss D2H, every step ----
-    loss_host = torch.empty(2, dtype=torch.float32).pin_memory()
-
-    def e2e_step():
-        for k in pinned:
-            dev_in[k].copy_(pinned[k], non_blocking=True)
-        o = fn() if graphed else step()
-        loss_host.copy_(out if graphed else o, non_blocking=True)
-        torch.cuda.current_stream().synchronize()
-        return float(loss_host[0])
-
-    for _ in range(2):
-        e2e_step()
+    # ---- e2e: pinned host buffers -> H2D (copy stream, double-buffered: batch i+1 copies while step i computes) -> step -> loss D2H + sync,
+    # every step, through the package's own feeder (mtrl_b200.pipeline.HostBatchPipeline) ----
+    pipe.prefetch(pinned)
+    for _ in range(3):
+        pipe.step(pinned)
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize(dev)
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        loss_val = e2e_step()
+        loss_val = pipe.step(pinned)
     torch.cuda.synchronize(dev)
     e2e_ms = (time.perf_counter() - t0) / args.steps * 1e3
     if world > 1:
@@ -282,7 +276,8 @@ def run_ours(args, wl, rank, world, local_rank):
                           f"no flush: per-step working set {ws_bytes / 1e6:.0f} MB > 126 MB L2"),
                    "timed": "weight staging + forward + masked action MSE + backward" + (" + overlapped NCCL all-reduce" if world > 1 else "")},
         "e2e": {"value": tokens / e2e_ms * 1e3, "unit": "tokens/s", "ms_per_step": e2e_ms, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 8,
-                "host_format": "fp32 pinned buffers in the reference's layouts"},
+                "host_format": "pinned host buffers in the reference's layouts (fp32; video frames as uint8 pixels, decoded in-kernel)",
+                "overlap": "H2D of batch i+1 on a copy stream while step i computes (double-buffered device slots)"},
         "gpu_launches": launches_per_step * args.steps, "launches_per_step": launches_per_step,
         "clocks": clock_info, "loss": loss_val, "wall_ms_per_step": wall_ms,
         "algorithmic_tflops_per_s": algorithmic_flops_per_step(wl, B * world) / ms / 1e9, "replicas_consistent": consistent,
@@ -312,7 +307,8 @@ def oracle_step(wl, model, b):
     if wl["enc"] is None:
         _, ap, _ = model(b["states"], b["actions"], None, b["rtg"], b["timesteps"], b["mask"])
     else:
-        _, ap, _ = model(b["frames"], b["audio"], b["actions"], None, b["rtg"], b["timesteps"], b["mask"])
+        frames = b["frames"].float() * 2.0 / 255.0 - 1  # the reference's pixel decode (Minecraft.py:333-335), on the host for the CPU arm
+        _, ap, _ = model(frames, b["audio"], b["actions"], None, b["rtg"], b["timesteps"], b["mask"])
     loss = masked_action_mse(ap, b["actions"], b["mask"])
     loss.backward()
     return float(loss.detach())

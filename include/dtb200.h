@@ -211,6 +211,15 @@ int dtb_encoder_backward(const dtb_encoder* e, void* stream, const float* params
                          const float* audio, const void* states_bf16,
                          const void* d_states_bf16, int d_states_masked, void* workspace, size_t workspace_bytes, float* grads);
 
+/* Same, with the video frames as uint8 pixels [N, Cv, H, W]: the reference's pixel decode `img * 2. / 255. - 1` (fp32,
+ * REF environments/Minecraft/Minecraft.py:333-335) runs inside the implicit-GEMM conv1 gather, bit-identical to passing the decoded
+ * fp32 frames to dtb_encoder_forward / _backward; 4x fewer bytes cross PCIe and HBM.  Needs in_w % 4 == 0 and in_channels <= 4. */
+int dtb_encoder_forward_u8(const dtb_encoder* e, void* stream, const float* params, const void* staged_bf16, int N,
+                           const unsigned char* frames_u8, const float* audio, void* workspace, size_t workspace_bytes, void* states_bf16);
+int dtb_encoder_backward_u8(const dtb_encoder* e, void* stream, const float* params, const void* staged_bf16, int N,
+                            const unsigned char* frames_u8, const float* audio, const void* states_bf16, const void* d_states_bf16,
+                            int d_states_masked, void* workspace, size_t workspace_bytes, float* grads);
+
 #ifdef __cplusplus
 }
 #endif

@@ -19,6 +19,7 @@ constexpr int C1_KB_BYTES = 128 * 128;  // one k-block of a 128-row tile
 
 struct Conv1Params {
   const float* x;
+  const uint8_t* xu8;  // non-null: uint8 pixels, decoded as p*2/255-1 (REF environments/Minecraft/Minecraft.py:333-335), x unused
   int N, C, H, W, stride, ho, wo, cout;
   long long rows;
   int tiles, stages;
@@ -63,6 +64,53 @@ __device__ __forceinline__ void c1_gather_tile(const Conv1Params& p, uint8_t* st
   }
 }
 
+// uint8-pixel variant: the reference's pixel decode (img * 2 / 255 - 1, fp32) and the `/255` input scale are folded into a 256-entry
+// bf16 table built once per CTA with exactly those fp32 operations, so the tile image is bit-identical to the fp32-input path.
+__device__ __forceinline__ void c1_build_lut(uint16_t* lut, float scale) {
+  for (int i = threadIdx.x; i < 256; i += blockDim.x) {
+    const float v = __fsub_rn(__fdiv_rn(__fmul_rn((float)i, 2.f), 255.f), 1.f);
+    const bf16 b = __float2bfloat16_rn(v * scale);
+    lut[i] = *reinterpret_cast<const uint16_t*>(&b);
+  }
+}
+__device__ __forceinline__ void c1_gather_tile_u8(const Conv1Params& p, uint8_t* stage, long long m0, const uint16_t* lut) {
+  const uint32_t base = smem_u32(stage);
+  for (int item = threadIdx.x; item < 256 * p.C; item += C1_PRODUCERS) {
+    const int r = item & 127, half = (item >> 7) & 1, c = item >> 8;
+    const long long m = m0 + r;
+    uint32_t a[4], b[4];
+    if (m < p.rows) {
+      const int ow = (int)(m % p.wo);
+      const long long t = m / p.wo;
+      const int oh = (int)(t % p.ho), n = (int)(t / p.ho);
+      const uint8_t* src = p.xu8 + (((size_t)n * p.C + c) * p.H + (size_t)oh * p.stride + half * 4) * p.W + (size_t)ow * p.stride;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        a[k] = __ldg(reinterpret_cast<const uint32_t*>(src + (size_t)k * p.W));
+        b[k] = __ldg(reinterpret_cast<const uint32_t*>(src + (size_t)k * p.W + 4));
+      }
+    } else {
+#pragma unroll
+      for (int k = 0; k < 4; ++k) a[k] = b[k] = 0u;
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int kh = half * 4 + k;
+      const uint32_t addr = base + c * C1_KB_BYTES + r * 128 + ((kh ^ (r & 7)) << 4);
+      uint32_t w0, w1, w2, w3;
+      if (m < p.rows) {
+        w0 = (uint32_t)lut[a[k] & 255] | ((uint32_t)lut[(a[k] >> 8) & 255] << 16);
+        w1 = (uint32_t)lut[(a[k] >> 16) & 255] | ((uint32_t)lut[a[k] >> 24] << 16);
+        w2 = (uint32_t)lut[b[k] & 255] | ((uint32_t)lut[(b[k] >> 8) & 255] << 16);
+        w3 = (uint32_t)lut[(b[k] >> 16) & 255] | ((uint32_t)lut[b[k] >> 24] << 16);
+      } else {
+        w0 = w1 = w2 = w3 = 0u;
+      }
+      asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(w0), "r"(w1), "r"(w2), "r"(w3) : "memory");
+    }
+  }
+}
+
 __global__ void __launch_bounds__(C1_THREADS, 1) conv1_fwd_kernel(const __grid_constant__ CUtensorMap tmW, const Conv1Params p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -77,6 +125,8 @@ __global__ void __launch_bounds__(C1_THREADS, 1) conv1_fwd_kernel(const __grid_c
   uint64_t* tempty_bar = bars + 10;      // [2]
   uint64_t* w_bar = bars + 12;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 13);
+  uint16_t* lut = reinterpret_cast<uint16_t*>(bars + 14);  // [256] (uint8 input only)
+  if (p.xu8) c1_build_lut(lut, p.scale);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (threadIdx.x == 0) {
@@ -96,7 +146,8 @@ __global__ void __launch_bounds__(C1_THREADS, 1) conv1_fwd_kernel(const __grid_c
     uint32_t stage = 0, phase = 0;
     for (int t = blockIdx.x; t < p.tiles; t += gridDim.x) {
       mbar_wait(&empty_bar[stage], phase ^ 1);
-      c1_gather_tile(p, smA + (size_t)stage * stage_bytes, (long long)t * 128);
+      if (p.xu8) c1_gather_tile_u8(p, smA + (size_t)stage * stage_bytes, (long long)t * 128, lut);
+      else c1_gather_tile(p, smA + (size_t)stage * stage_bytes, (long long)t * 128);
       fence_proxy_async();  // generic-proxy stores -> visible to the tensor core (async proxy)
       mbar_arrive(&full_bar[stage]);
       if (++stage == (uint32_t)p.stages) { stage = 0; phase ^= 1; }
@@ -172,6 +223,8 @@ __global__ void __launch_bounds__(C1_THREADS, 1) conv1_wgrad_kernel(const __grid
   uint64_t* empty_bar = bars + 4;    // [stages]
   uint64_t* done_bar = bars + 8;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 9);
+  uint16_t* lut = reinterpret_cast<uint16_t*>(bars + 10);  // [256] (uint8 input only)
+  if (p.xu8) c1_build_lut(lut, p.scale);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   for (int i = threadIdx.x; i < C1_KB_BYTES / 16; i += blockDim.x) reinterpret_cast<uint4*>(smZero)[i] = make_uint4(0, 0, 0, 0);
@@ -196,7 +249,8 @@ __global__ void __launch_bounds__(C1_THREADS, 1) conv1_wgrad_kernel(const __grid
         mbar_arrive_expect_tx(&full_bar[stage], C1_KB_BYTES);
         tma_load_2d(smZ + (size_t)stage * C1_KB_BYTES, &tmZ, &full_bar[stage], 0, t * 128);
       }
-      c1_gather_tile(p, smP + (size_t)stage * stage_bytes, (long long)t * 128);
+      if (p.xu8) c1_gather_tile_u8(p, smP + (size_t)stage * stage_bytes, (long long)t * 128, lut);
+      else c1_gather_tile(p, smP + (size_t)stage * stage_bytes, (long long)t * 128);
       fence_proxy_async();
       mbar_arrive(&full_bar[stage]);
       if (++stage == (uint32_t)p.stages) { stage = 0; phase ^= 1; }
@@ -247,13 +301,14 @@ __global__ void __launch_bounds__(C1_THREADS, 1) conv1_wgrad_kernel(const __grid
 }
 
 // ---- host ------------------------------------------------------------------------------------------------------------------------
-static int c1_params(Conv1Params& p, const float* x, int N, int C, int H, int W, int stride, float scale, int cout) {
+static int c1_params(Conv1Params& p, const void* xv, int x_u8, int N, int C, int H, int W, int stride, float scale, int cout) {
   DTB_REQUIRE(C >= 1 && C <= C1_MAXC, DTB_ERR_UNSUPPORTED, "conv1 implicit GEMM: in_channels %d unsupported (1..%d)", C, C1_MAXC);
   DTB_REQUIRE(W % 4 == 0 && stride % 4 == 0 && H >= 8 && W >= 8, DTB_ERR_UNSUPPORTED, "conv1: needs W %% 4 == 0, stride %% 4 == 0");
   DTB_REQUIRE(cout == 16 || cout == 32, DTB_ERR_UNSUPPORTED, "conv1: out_channels %d unsupported (16, 32)", cout);
-  DTB_REQUIRE((reinterpret_cast<uintptr_t>(x) & 15) == 0, DTB_ERR_BAD_ARG, "conv1: input must be 16-byte aligned");
+  DTB_REQUIRE((reinterpret_cast<uintptr_t>(xv) & 15) == 0, DTB_ERR_BAD_ARG, "conv1: input must be 16-byte aligned");
   memset(&p, 0, sizeof(p));
-  p.x = x; p.N = N; p.C = C; p.H = H; p.W = W; p.stride = stride; p.cout = cout; p.scale = scale;
+  if (x_u8) p.xu8 = reinterpret_cast<const uint8_t*>(xv); else p.x = reinterpret_cast<const float*>(xv);
+  p.N = N; p.C = C; p.H = H; p.W = W; p.stride = stride; p.cout = cout; p.scale = scale;
   p.ho = (H - 8) / stride + 1; p.wo = (W - 8) / stride + 1;
   p.rows = (long long)N * p.ho * p.wo;
   p.tiles = (int)((p.rows + 127) / 128);
@@ -263,21 +318,21 @@ bool conv1_implicit_supported(int C, int W, int stride, int cout) {
   return C >= 1 && C <= C1_MAXC && W % 4 == 0 && stride % 4 == 0 && (cout == 16 || cout == 32);
 }
 
-int conv1_fwd(cudaStream_t stream, const float* x, int N, int C, int H, int W, int stride, float scale, const bf16* w_staged,
+int conv1_fwd(cudaStream_t stream, const void* x, int x_u8, int N, int C, int H, int W, int stride, float scale, const bf16* w_staged,
               const float* bias, int cout, bf16* y) {
   Conv1Params p;
-  DTB_TRY(c1_params(p, x, N, C, H, W, stride, scale, cout));
+  DTB_TRY(c1_params(p, x, x_u8, N, C, H, W, stride, scale, cout));
   if (p.rows == 0) return DTB_OK;
   p.bias = bias; p.y = y;
   p.stages = C <= 2 ? 4 : 3;
   if (p.stages * C * C1_KB_BYTES > 192 * 1024) p.stages = 192 * 1024 / (C * C1_KB_BYTES);
   CUtensorMap tmW;
   DTB_TRY(make_tmap(&tmW, w_staged, (uint64_t)64 * C, (uint64_t)cout, (uint64_t)64 * C, 64, (uint32_t)cout));
-  const int smem = 1024 + ((C * cout * 128 + 1023) & ~1023) + p.stages * C * C1_KB_BYTES + 256;
+  const int smem = 1024 + ((C * cout * 128 + 1023) & ~1023) + p.stages * C * C1_KB_BYTES + 256 + 512;
   static bool attr = false;
   if (!attr) { DTB_CUDA(cudaFuncSetAttribute(conv1_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 225 * 1024)); attr = true; }
   const int grid = p.tiles < num_sms() ? p.tiles : num_sms();
-  ProfScope prof(stream, PF_CONV1_FWD, 4.0 * N * C * H * W + 2.0 * (double)p.rows * cout);
+  ProfScope prof(stream, PF_CONV1_FWD, (x_u8 ? 1.0 : 4.0) * N * C * H * W + 2.0 * (double)p.rows * cout);
   conv1_fwd_kernel<<<grid, C1_THREADS, smem, stream>>>(tmW, p);
   DTB_CHECK_LAUNCH();
   return DTB_OK;
@@ -285,21 +340,21 @@ int conv1_fwd(cudaStream_t stream, const float* x, int N, int C, int H, int W, i
 
 size_t conv1_wgrad_partial_floats(int C, int cout) { return (size_t)DTB_NUM_SMS_FALLBACK * cout * 64 * C; }
 
-int conv1_wgrad(cudaStream_t stream, const float* x, int N, int C, int H, int W, int stride, float scale, const bf16* dz, int cout,
+int conv1_wgrad(cudaStream_t stream, const void* x, int x_u8, int N, int C, int H, int W, int stride, float scale, const bf16* dz, int cout,
                 float* partial, float* dw) {
   Conv1Params p;
-  DTB_TRY(c1_params(p, x, N, C, H, W, stride, scale, cout));
+  DTB_TRY(c1_params(p, x, x_u8, N, C, H, W, stride, scale, cout));
   if (p.rows == 0) { DTB_CUDA(cudaMemsetAsync(dw, 0, (size_t)cout * 64 * C * sizeof(float), stream)); return DTB_OK; }
   p.partial = partial;
   p.stages = 2;
   CUtensorMap tmZ;
   DTB_TRY(make_tmap(&tmZ, dz, (uint64_t)cout, (uint64_t)p.rows, (uint64_t)cout, 64, 128));
-  const int smem = 1024 + p.stages * (C + 1) * C1_KB_BYTES + C1_KB_BYTES + 256;
+  const int smem = 1024 + p.stages * (C + 1) * C1_KB_BYTES + C1_KB_BYTES + 256 + 512;
   static bool attr = false;
   if (!attr) { DTB_CUDA(cudaFuncSetAttribute(conv1_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 225 * 1024)); attr = true; }
   int grid = p.tiles < num_sms() ? p.tiles : num_sms();
   if (grid > DTB_NUM_SMS_FALLBACK) grid = DTB_NUM_SMS_FALLBACK;
-  ProfScope prof(stream, PF_CONV1_WGRAD, 4.0 * N * C * H * W + 2.0 * (double)p.rows * cout);
+  ProfScope prof(stream, PF_CONV1_WGRAD, (x_u8 ? 1.0 : 4.0) * N * C * H * W + 2.0 * (double)p.rows * cout);
   conv1_wgrad_kernel<<<grid, C1_THREADS, smem, stream>>>(tmZ, p);
   DTB_CHECK_LAUNCH();
   prof.~ProfScope();

@@ -163,17 +163,18 @@ static int gemm_kk(cudaStream_t st, const bf16* A, int lda, const bf16* B, int l
   return rc < 0 ? rc : DTB_OK;
 }
 
-static int tower_forward(const dtb_encoder* e, int ti, cudaStream_t st, const float* P, const bf16* Ps, int N, const float* x, TowerWs& tw,
-                         bf16* out, int ldo) {
+static int tower_forward(const dtb_encoder* e, int ti, cudaStream_t st, const float* P, const bf16* Ps, int N, const void* x, int x_u8,
+                         TowerWs& tw, bf16* out, int ldo) {
   const Tower& t = e->t[ti];
   for (int i = 0; i < t.nconv; ++i) {
     const ConvSpec& cs = t.conv[i];
     const int rows = N * cs.hout * cs.wout, kc = cs.cin * cs.k * cs.k;
     if (i == 0 && tw.P[0] == nullptr) {  // implicit GEMM: patches gathered inside the kernel, never written to HBM
-      DTB_TRY(conv1_fwd(st, x, N, cs.cin, cs.hin, cs.win, cs.stride, e->c.input_scale, Ps + t.w_off[0], P + t.b_off[0], cs.cout, tw.Y[0]));
+      DTB_TRY(conv1_fwd(st, x, x_u8, N, cs.cin, cs.hin, cs.win, cs.stride, e->c.input_scale, Ps + t.w_off[0], P + t.b_off[0], cs.cout, tw.Y[0]));
       continue;
     }
-    if (i == 0) DTB_TRY(im2col_nchw_k8(st, x, N, cs.cin, cs.hin, cs.win, cs.stride, e->c.input_scale, tw.P[0]));
+    if (i == 0) DTB_REQUIRE(!x_u8, DTB_ERR_UNSUPPORTED, "uint8 pixel input needs the implicit-GEMM conv1 (W %% 4 == 0, stride 4, C <= 4)");
+    if (i == 0) DTB_TRY(im2col_nchw_k8(st, reinterpret_cast<const float*>(x), N, cs.cin, cs.hin, cs.win, cs.stride, e->c.input_scale, tw.P[0]));
     else DTB_TRY(im2col_nhwc(st, tw.Y[i - 1], N, cs.hin, cs.win, cs.cin, cs.k, cs.stride, tw.P[i]));
     GemmEpilogue ep = epz();
     ep.bias = P + t.b_off[i];
@@ -191,8 +192,8 @@ static int tower_forward(const dtb_encoder* e, int ti, cudaStream_t st, const fl
 }
 
 // dF: gradient w.r.t. the tower's feature output, already multiplied by the ReLU mask; bf16 [N, feat] with row stride ldf.
-static int tower_backward(const dtb_encoder* e, int ti, cudaStream_t st, const bf16* Ps, int N, const float* x, const bf16* dF, int ldf,
-                          TowerWs& tw, EncWs& w, float* G) {
+static int tower_backward(const dtb_encoder* e, int ti, cudaStream_t st, const bf16* Ps, int N, const void* x, int x_u8, const bf16* dF,
+                          int ldf, TowerWs& tw, EncWs& w, float* G) {
   const Tower& t = e->t[ti];
   const int last = t.nconv - 1;
   const ConvSpec& cl = t.conv[last];
@@ -220,7 +221,7 @@ static int tower_backward(const dtb_encoder* e, int ti, cudaStream_t st, const b
     DTB_TRY(sd.fork(st));  // dZ[i] is complete on the main stream
     if (i == 0 && tw.P[0] == nullptr) {
       DTB_REQUIRE(x != nullptr, DTB_ERR_BAD_ARG, "encoder backward: frames / audio are needed again for the implicit conv1 weight gradient");
-      DTB_TRY(conv1_wgrad(ss, x, N, cs.cin, cs.hin, cs.win, cs.stride, e->c.input_scale, tw.dZ[0], cs.cout, tw.c1_partial, G + t.w_off[0]));
+      DTB_TRY(conv1_wgrad(ss, x, x_u8, N, cs.cin, cs.hin, cs.win, cs.stride, e->c.input_scale, tw.dZ[0], cs.cout, tw.c1_partial, G + t.w_off[0]));
     } else if (i == 0) {
       DTB_TRY(gemm_wgrad(ss, tw.dZ[0], cs.cout, tw.P[0], kc, cs.cout, kc, rows, G + t.w_off[0], kc, w.partial, w.partial_floats));
     } else {
@@ -306,8 +307,8 @@ static int enc_ws(const dtb_encoder* e, int N, void* workspace, size_t bytes, En
   return DTB_OK;
 }
 
-int dtb_encoder_forward(const dtb_encoder* e, void* stream, const float* params, const void* staged, int N, const float* frames,
-                        const float* audio, void* workspace, size_t workspace_bytes, void* states_bf16) {
+static int encoder_forward_impl(const dtb_encoder* e, void* stream, const float* params, const void* staged, int N, const void* frames,
+                                int frames_u8, const float* audio, void* workspace, size_t workspace_bytes, void* states_bf16) {
   DTB_REQUIRE(e && params && staged && frames && audio && states_bf16, DTB_ERR_BAD_ARG, "dtb_encoder_forward: null argument");
   DTB_TRY(require_sm100());
   if (N == 0) return DTB_OK;
@@ -320,22 +321,22 @@ int dtb_encoder_forward(const dtb_encoder* e, void* stream, const float* params,
   if (e->c.fusion == 0) {  // concat: each tower's FC epilogue writes its half of [N, state_dim]  (agents.py:137-139, dim=1 semantics)
     // the two towers are independent: audio runs on the side branch, video on the caller's stream
     DTB_TRY(e->side.fork(st));
-    DTB_TRY(tower_forward(e, 1, e->side.pick(st), params, Ps, N, audio, w.t[1], out + e->t[0].feat, e->state_dim));
-    DTB_TRY(tower_forward(e, 0, st, params, Ps, N, frames, w.t[0], out, e->state_dim));
+    DTB_TRY(tower_forward(e, 1, e->side.pick(st), params, Ps, N, audio, 0, w.t[1], out + e->t[0].feat, e->state_dim));
+    DTB_TRY(tower_forward(e, 0, st, params, Ps, N, frames, frames_u8, w.t[0], out, e->state_dim));
     DTB_TRY(e->side.join(st));
   } else {  // sum (agents.py:140-141)
     DTB_TRY(e->side.fork(st));
-    DTB_TRY(tower_forward(e, 1, e->side.pick(st), params, Ps, N, audio, w.t[1], w.feat[1], e->t[1].feat));
-    DTB_TRY(tower_forward(e, 0, st, params, Ps, N, frames, w.t[0], w.feat[0], e->t[0].feat));
+    DTB_TRY(tower_forward(e, 1, e->side.pick(st), params, Ps, N, audio, 0, w.t[1], w.feat[1], e->t[1].feat));
+    DTB_TRY(tower_forward(e, 0, st, params, Ps, N, frames, frames_u8, w.t[0], w.feat[0], e->t[0].feat));
     DTB_TRY(e->side.join(st));
     DTB_TRY(add_bf16(st, w.feat[0], w.feat[1], (size_t)N * e->t[0].feat, out));
   }
   return DTB_OK;
 }
 
-int dtb_encoder_backward(const dtb_encoder* e, void* stream, const float* params, const void* staged, int N, const float* frames,
-                         const float* audio, const void* states_bf16,
-                         const void* d_states_bf16, int d_states_masked, void* workspace, size_t workspace_bytes, float* grads) {
+static int encoder_backward_impl(const dtb_encoder* e, void* stream, const float* params, const void* staged, int N, const void* frames,
+                                 int frames_u8, const float* audio, const void* states_bf16, const void* d_states_bf16, int d_states_masked,
+                                 void* workspace, size_t workspace_bytes, float* grads) {
   DTB_REQUIRE(e && params && staged && d_states_bf16 && grads, DTB_ERR_BAD_ARG, "dtb_encoder_backward: null argument");
   cudaStream_t st = (cudaStream_t)stream;
   if (N == 0) {
@@ -353,18 +354,39 @@ int dtb_encoder_backward(const dtb_encoder* e, void* stream, const float* params
     bf16* d = const_cast<bf16*>(dS);
     if (!d_states_masked)
       DTB_TRY(relu_mask_bf16(st, dS, e->state_dim, (const bf16*)states_bf16, e->state_dim, N, e->state_dim, d, e->state_dim));
-    DTB_TRY(tower_backward(e, 0, st, Ps, N, frames, d, e->state_dim, w.t[0], w, grads));
-    DTB_TRY(tower_backward(e, 1, st, Ps, N, audio, d + e->t[0].feat, e->state_dim, w.t[1], w, grads));
+    DTB_TRY(tower_backward(e, 0, st, Ps, N, frames, frames_u8, d, e->state_dim, w.t[0], w, grads));
+    DTB_TRY(tower_backward(e, 1, st, Ps, N, audio, 0, d + e->t[0].feat, e->state_dim, w.t[1], w, grads));
   } else {
     // sum: the gradient reaches both towers unchanged; each applies its own ReLU mask
     const int F = e->t[0].feat;
     for (int ti = 0; ti < 2; ++ti) {
       DTB_TRY(relu_mask_bf16(st, dS, F, w.feat[ti], F, N, F, w.dfeat, F));
-      DTB_TRY(tower_backward(e, ti, st, Ps, N, ti == 0 ? frames : audio, w.dfeat, F, w.t[ti], w, grads));
+      DTB_TRY(tower_backward(e, ti, st, Ps, N, ti == 0 ? frames : (const void*)audio, ti == 0 ? frames_u8 : 0, w.dfeat, F, w.t[ti], w, grads));
       DTB_TRY(e->side.join(st));  // w.dfeat is reused by the next tower
     }
   }
   return e->side.join(st);
+}
+
+int dtb_encoder_forward(const dtb_encoder* e, void* stream, const float* params, const void* staged, int N, const float* frames,
+                        const float* audio, void* workspace, size_t workspace_bytes, void* states_bf16) {
+  return encoder_forward_impl(e, stream, params, staged, N, frames, 0, audio, workspace, workspace_bytes, states_bf16);
+}
+int dtb_encoder_forward_u8(const dtb_encoder* e, void* stream, const float* params, const void* staged, int N, const unsigned char* frames_u8,
+                           const float* audio, void* workspace, size_t workspace_bytes, void* states_bf16) {
+  return encoder_forward_impl(e, stream, params, staged, N, frames_u8, 1, audio, workspace, workspace_bytes, states_bf16);
+}
+int dtb_encoder_backward(const dtb_encoder* e, void* stream, const float* params, const void* staged, int N, const float* frames,
+                         const float* audio, const void* states_bf16, const void* d_states_bf16, int d_states_masked, void* workspace,
+                         size_t workspace_bytes, float* grads) {
+  return encoder_backward_impl(e, stream, params, staged, N, frames, 0, audio, states_bf16, d_states_bf16, d_states_masked, workspace,
+                               workspace_bytes, grads);
+}
+int dtb_encoder_backward_u8(const dtb_encoder* e, void* stream, const float* params, const void* staged, int N,
+                            const unsigned char* frames_u8, const float* audio, const void* states_bf16, const void* d_states_bf16,
+                            int d_states_masked, void* workspace, size_t workspace_bytes, float* grads) {
+  return encoder_backward_impl(e, stream, params, staged, N, frames_u8, 1, audio, states_bf16, d_states_bf16, d_states_masked, workspace,
+                               workspace_bytes, grads);
 }
 
 }  // extern "C"

@@ -91,10 +91,10 @@ int copy2d(cudaStream_t stream, const float* src, int lds, int R, int C, float* 
 
 // ---- conv1.cu (implicit-GEMM first convolution) -------------------------------------------------
 bool conv1_implicit_supported(int C, int W, int stride, int cout);
-int conv1_fwd(cudaStream_t stream, const float* x, int N, int C, int H, int W, int stride, float scale, const bf16* w_staged,
+int conv1_fwd(cudaStream_t stream, const void* x, int x_u8, int N, int C, int H, int W, int stride, float scale, const bf16* w_staged,
               const float* bias, int cout, bf16* y);
 size_t conv1_wgrad_partial_floats(int C, int cout);
-int conv1_wgrad(cudaStream_t stream, const float* x, int N, int C, int H, int W, int stride, float scale, const bf16* dz, int cout,
+int conv1_wgrad(cudaStream_t stream, const void* x, int x_u8, int N, int C, int H, int W, int stride, float scale, const bf16* dz, int cout,
                 float* partial, float* dw);
 
 // ---- conv.cu -----------------------------------------------------------------------------------

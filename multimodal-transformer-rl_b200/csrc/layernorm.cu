@@ -65,51 +65,73 @@ int ln_fwd(cudaStream_t stream, const float* x, const float* gamma, const float*
 }
 
 // ---------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) ln_bwd_kernel(const bf16* __restrict__ dy, const float* __restrict__ x,
-                                                     const float* __restrict__ mean, const float* __restrict__ rstd,
-                                                     const float* __restrict__ gamma, const float* __restrict__ dres, int M, int H,
-                                                     float* __restrict__ dx_out, bf16* __restrict__ dx_bf16,
-                                                     float* __restrict__ scratch /* [grid][2][H] */) {
+// One warp per token row, NV = ceil(H / 128) float4 per lane (compile-time so the per-lane arrays are exact).  All of a row's loads
+// (x, dy, dres) are issued before the first reduction so ~10 KB per warp is in flight; two 256-thread CTAs per SM.
+template <int NV>
+__global__ void __launch_bounds__(256, 2) ln_bwd_kernel(const bf16* __restrict__ dy, const float* __restrict__ x,
+                                                        const float* __restrict__ mean, const float* __restrict__ rstd,
+                                                        const float* __restrict__ gamma, const float* __restrict__ dres, int M, int H,
+                                                        float* __restrict__ dx_out, bf16* __restrict__ dx_bf16,
+                                                        float* __restrict__ scratch /* [grid][2][H] */) {
   extern __shared__ float sred[];  // [2][H]
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
-  float4 dg[LN_MAX_VEC], db[LN_MAX_VEC];
+  float4 dg[NV], db[NV];
 #pragma unroll
-  for (int i = 0; i < LN_MAX_VEC; ++i) {
+  for (int i = 0; i < NV; ++i) {
     dg[i] = make_float4(0, 0, 0, 0);
     db[i] = make_float4(0, 0, 0, 0);
   }
-  for (int row = blockIdx.x * nwarp + warp; row < M; row += gridDim.x * nwarp) {
-    const float mu = mean[row], rs = rstd[row];
+  const int row_step = gridDim.x * nwarp;
+  for (int row = blockIdx.x * nwarp + warp; row < M; row += row_step) {
     const float* xr = x + (size_t)row * H;
     const bf16* dyr = dy + (size_t)row * H;
-    float4 xh[LN_MAX_VEC];
-    uint2 dyp[LN_MAX_VEC];
-    float s1 = 0.f, s2 = 0.f;
+    float4 xv[NV];
+    uint2 dyp[NV];
 #pragma unroll
-    for (int i = 0; i < LN_MAX_VEC; ++i) {
+    for (int i = 0; i < NV; ++i) {
       const int c = i * 128 + lane * 4;
       if (c < H) {
-        const float4 xv = ldg_f4(xr + c);
-        const float4 gm = ldg_f4(gamma + c);
+        xv[i] = ldg_f4(xr + c);
         dyp[i] = __ldg(reinterpret_cast<const uint2*>(dyr + c));
+      }
+    }
+    // register-free look-ahead: this row's dres and the warp's next row are pulled into L2 while the reductions run
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int c = i * 128 + lane * 4;
+      if (c < H) {
+        if (dres) prefetch_l2(dres + (size_t)row * H + c);
+        if (row + row_step < M) {
+          prefetch_l2(xr + (size_t)row_step * H + c);
+          if ((lane & 1) == 0) prefetch_l2(dyr + (size_t)row_step * H + c);
+        }
+      }
+    }
+    const float mu = mean[row], rs = rstd[row];
+    float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int c = i * 128 + lane * 4;
+      if (c < H) {
         const float2 d01 = unpack_bf16x2(dyp[i].x), d23 = unpack_bf16x2(dyp[i].y);
-        xh[i] = make_float4((xv.x - mu) * rs, (xv.y - mu) * rs, (xv.z - mu) * rs, (xv.w - mu) * rs);
+        xv[i] = make_float4((xv[i].x - mu) * rs, (xv[i].y - mu) * rs, (xv[i].z - mu) * rs, (xv[i].w - mu) * rs);  // xhat
+        const float4 gm = ldg_f4(gamma + c);
         const float g0 = d01.x * gm.x, g1 = d01.y * gm.y, g2 = d23.x * gm.z, g3 = d23.y * gm.w;
         s1 += g0 + g1 + g2 + g3;
-        s2 += g0 * xh[i].x + g1 * xh[i].y + g2 * xh[i].z + g3 * xh[i].w;
-        dg[i].x += d01.x * xh[i].x; dg[i].y += d01.y * xh[i].y; dg[i].z += d23.x * xh[i].z; dg[i].w += d23.y * xh[i].w;
+        s2 += g0 * xv[i].x + g1 * xv[i].y + g2 * xv[i].z + g3 * xv[i].w;
+        dg[i].x += d01.x * xv[i].x; dg[i].y += d01.y * xv[i].y; dg[i].z += d23.x * xv[i].z; dg[i].w += d23.y * xv[i].w;
         db[i].x += d01.x; db[i].y += d01.y; db[i].z += d23.x; db[i].w += d23.y;
       }
     }
     const float c1 = warp_sum(s1) / H, c2 = warp_sum(s2) / H;
 #pragma unroll
-    for (int i = 0; i < LN_MAX_VEC; ++i) {
+    for (int i = 0; i < NV; ++i) {
       const int c = i * 128 + lane * 4;
       if (c < H) {
-        const float4 gm = ldg_f4(gamma + c);
         const float2 d01 = unpack_bf16x2(dyp[i].x), d23 = unpack_bf16x2(dyp[i].y);
-        float4 o = make_float4(rs * (d01.x * gm.x - c1 - xh[i].x * c2), rs * (d01.y * gm.y - c1 - xh[i].y * c2),
-                               rs * (d23.x * gm.z - c1 - xh[i].z * c2), rs * (d23.y * gm.w - c1 - xh[i].w * c2));
+        const float4 gm = ldg_f4(gamma + c);
+        float4 o = make_float4(rs * (d01.x * gm.x - c1 - xv[i].x * c2), rs * (d01.y * gm.y - c1 - xv[i].y * c2),
+                               rs * (d23.x * gm.z - c1 - xv[i].z * c2), rs * (d23.y * gm.w - c1 - xv[i].w * c2));
         if (dres) {
           const float4 r = ldg_f4(dres + (size_t)row * H + c);
           o.x += r.x; o.y += r.y; o.z += r.z; o.w += r.w;
@@ -125,7 +147,7 @@ __global__ void __launch_bounds__(256) ln_bwd_kernel(const bf16* __restrict__ dy
   for (int w = 0; w < nwarp; ++w) {
     if (warp == w) {
 #pragma unroll
-      for (int i = 0; i < LN_MAX_VEC; ++i) {
+      for (int i = 0; i < NV; ++i) {
         const int c = i * 128 + lane * 4;
         if (c < H) {
           sred[c] += dg[i].x; sred[c + 1] += dg[i].y; sred[c + 2] += dg[i].z; sred[c + 3] += dg[i].w;
@@ -155,9 +177,9 @@ __global__ void __launch_bounds__(256) ln_bwd_finalize(const float* __restrict__
   }
 }
 
-static int ln_bwd_blocks(int M) {
+static int ln_bwd_blocks(int M, int H) {
   int b = (M + 7) / 8;
-  const int cap = num_sms() * 2;
+  const int cap = num_sms() * (H <= 256 ? 8 : 2);  // scratch is sized for 8 x SMs partial rows
   return b > cap ? cap : (b < 1 ? 1 : b);
 }
 size_t ln_bwd_scratch_floats(int H) { return (size_t)DTB_NUM_SMS_FALLBACK * 8 * 2 * H; }
@@ -165,9 +187,17 @@ size_t ln_bwd_scratch_floats(int H) { return (size_t)DTB_NUM_SMS_FALLBACK * 8 * 
 int ln_bwd(cudaStream_t stream, const bf16* dy, const float* x, const float* mean, const float* rstd, const float* gamma,
            const float* dres, int M, int H, float* dx_out, bf16* dx_out_bf16, float* dgamma, float* dbeta, float* scratch) {
   DTB_REQUIRE(H % 4 == 0 && H <= LN_MAX_VEC * 128, DTB_ERR_UNSUPPORTED, "layernorm bwd: hidden size %d unsupported", H);
-  const int blocks = ln_bwd_blocks(M);
+  const int blocks = ln_bwd_blocks(M, H);
+  const int nv = (H + 127) / 128;
+  const size_t sm = 2 * H * sizeof(float);
   ProfScope prof(stream, PF_LN_BWD, 16.0 * M * H);
-  ln_bwd_kernel<<<blocks, 256, 2 * H * sizeof(float), stream>>>(dy, x, mean, rstd, gamma, dres, M, H, dx_out, dx_out_bf16, scratch);
+#define DTB_LN_BWD(NV) ln_bwd_kernel<NV><<<blocks, 256, sm, stream>>>(dy, x, mean, rstd, gamma, dres, M, H, dx_out, dx_out_bf16, scratch)
+  if (nv <= 1) DTB_LN_BWD(1);
+  else if (nv <= 2) DTB_LN_BWD(2);
+  else if (nv <= 4) DTB_LN_BWD(4);
+  else if (nv <= 6) DTB_LN_BWD(6);
+  else DTB_LN_BWD(8);
+#undef DTB_LN_BWD
   DTB_CHECK_LAUNCH();
   ln_bwd_finalize<<<(2 * H + 31) / 32, dim3(32, 8), 0, stream>>>(scratch, blocks, H, dgamma, dbeta);
   DTB_CHECK_LAUNCH();

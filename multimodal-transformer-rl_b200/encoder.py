@@ -144,16 +144,21 @@ class MultimodalStateEncoder(nn.Module):
         if tuple(frames.shape[2:]) != self.frame_shape or tuple(audio.shape[2:]) != self.audio_shape or audio.shape[:2] != frames.shape[:2]:
             raise ValueError(f"expected frames [B,K,{self.frame_shape}] and audio [B,K,{self.audio_shape}], got {tuple(frames.shape)}, "
                              f"{tuple(audio.shape)}")
-        return B, K, frames.detach().to(torch.float32).contiguous(), audio.detach().to(torch.float32).contiguous()
+        # uint8 frames are raw pixels: the library applies the reference's decode (img * 2 / 255 - 1, Minecraft.py:333-335) in-kernel
+        f = frames.detach().contiguous() if frames.dtype == torch.uint8 else frames.detach().to(torch.float32).contiguous()
+        return B, K, f, audio.detach().to(torch.float32).contiguous()
 
     def forward_raw(self, frames, audio):
-        """frames [B,K,Cv,H,W], audio [B,K,Ca,H,W] (fp32) -> states bf16 [B,K,state_dim]; keeps what backward_raw needs."""
+        """frames [B,K,Cv,H,W] (fp32 in the reference's decoded range, or uint8 pixels), audio [B,K,Ca,H,W] (fp32) -> states bf16
+        [B,K,state_dim]; keeps what backward_raw needs."""
         B, K, f, a = self._prep(frames, audio)
         N = B * K
         self._stage()
         ws = self._workspace(N)
         states = torch.empty((B, K, self.state_dim), dtype=torch.bfloat16, device=self._flat.device)
-        _lib.check(_lib.load().dtb_encoder_forward(self._h, _lib.stream_ptr(), _lib.ptr(self._flat), _lib.ptr(self._staged), N, _lib.ptr(f),
+        lib = _lib.load()
+        fwd = lib.dtb_encoder_forward_u8 if f.dtype == torch.uint8 else lib.dtb_encoder_forward
+        _lib.check(fwd(self._h, _lib.stream_ptr(), _lib.ptr(self._flat), _lib.ptr(self._staged), N, _lib.ptr(f),
                                                    _lib.ptr(a), _lib.ptr(ws), ws.numel(), _lib.ptr(states)))
         self._last = (N, f, a, ws, states)
         return states
@@ -161,9 +166,10 @@ class MultimodalStateEncoder(nn.Module):
     def backward_raw(self, d_states, masked: bool, grads=None):
         N, f, a, ws, states = self._last
         grads = self.attach_grads() if grads is None else grads
-        _lib.check(_lib.load().dtb_encoder_backward(self._h, _lib.stream_ptr(), _lib.ptr(self._flat), _lib.ptr(self._staged), N,
-                                                    _lib.ptr(f), _lib.ptr(a), _lib.ptr(states), _lib.ptr(d_states), int(masked), _lib.ptr(ws), ws.numel(),
-                                                    _lib.ptr(grads)))
+        lib = _lib.load()
+        bwd = lib.dtb_encoder_backward_u8 if f.dtype == torch.uint8 else lib.dtb_encoder_backward
+        _lib.check(bwd(self._h, _lib.stream_ptr(), _lib.ptr(self._flat), _lib.ptr(self._staged), N, _lib.ptr(f), _lib.ptr(a), _lib.ptr(states),
+                       _lib.ptr(d_states), int(masked), _lib.ptr(ws), ws.numel(), _lib.ptr(grads)))
         return grads
 
     def forward(self, frames, audio):

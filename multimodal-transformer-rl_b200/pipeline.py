@@ -1,0 +1,77 @@
+"""Double-buffered host -> device feeder for the training step (the caller side of ``train_step``: upstream's ``get_batch`` hands
+numpy/CPU batches to the model every step).
+
+While step *i* runs on the compute stream, step *i+1*'s batch is copied from pinned host memory on a copy stream into the other
+device slot, so the PCIe transfer (c2: 55 MB/step with uint8 frames) hides behind the kernels.  Each slot owns its device tensors
+and, optionally, a CUDA graph of the step captured over them.  ``step()`` returns the step's loss as a Python float (8-byte
+device -> host read + stream sync every step), exactly what ``SequenceTrainer.train_step()`` returns.
+"""
+from __future__ import annotations
+
+from typing import Callable, Dict
+
+import torch
+
+
+class HostBatchPipeline:
+    def __init__(self, make_step: Callable[[Dict[str, torch.Tensor]], Callable[[], torch.Tensor]], example: Dict[str, torch.Tensor],
+                 device: torch.device, use_graph: bool = True, warmup: int = 3):
+        """make_step(device_batch) -> step() returning a device tensor whose element 0 is the loss; `example` fixes shapes/dtypes."""
+        self.device = device
+        self.copy_stream = torch.cuda.Stream(device=device)
+        self.slots = []
+        for _ in range(2):
+            dev = {k: torch.empty(v.shape, dtype=v.dtype, device=device) for k, v in example.items()}
+            self.slots.append(dict(dev=dev, step=make_step(dev), graph=None, out=None, copied=torch.cuda.Event(), consumed=torch.cuda.Event()))
+        self.loss_host = torch.empty(2, dtype=torch.float32).pin_memory()
+        self.bytes_per_batch = sum(v.numel() * v.element_size() for v in example.values())
+        self._cur, self._filled = 0, False
+        # warm-up on real data, then capture one graph per slot
+        for s in self.slots:
+            for k, v in example.items():
+                s["dev"][k].copy_(v, non_blocking=True)
+            for _ in range(warmup):
+                s["out"] = s["step"]()
+        torch.cuda.synchronize(device)
+        if use_graph:
+            for s in self.slots:
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g):
+                    s["out"] = s["step"]()
+                s["graph"] = g
+            torch.cuda.synchronize(device)
+        for s in self.slots:
+            s["consumed"].record(torch.cuda.current_stream(device))
+
+    def prefetch(self, host_batch: Dict[str, torch.Tensor]):
+        """Enqueue the H2D copy of the NEXT batch (pinned host tensors) into the idle slot on the copy stream."""
+        s = self.slots[self._cur if not self._filled else 1 - self._cur]
+        self.copy_stream.wait_event(s["consumed"])  # the step that last read this slot has finished
+        with torch.cuda.stream(self.copy_stream):
+            for k, v in host_batch.items():
+                s["dev"][k].copy_(v, non_blocking=True)
+            s["copied"].record(self.copy_stream)
+        self._filled = True
+
+    def step(self, next_host_batch: Dict[str, torch.Tensor] | None = None) -> float:
+        """Run the step on the batch prefetched last; meanwhile copy `next_host_batch` into the other slot."""
+        if not self._filled:
+            raise RuntimeError("HostBatchPipeline.step() before prefetch()")
+        s = self.slots[self._cur]
+        main = torch.cuda.current_stream(self.device)
+        main.wait_event(s["copied"])
+        if next_host_batch is not None:
+            self.prefetch(next_host_batch)  # overlaps with the kernels enqueued next
+        if s["graph"] is not None:
+            s["graph"].replay()
+            out = s["out"]
+        else:
+            out = s["step"]()
+        s["consumed"].record(main)
+        self.loss_host.copy_(out[:2] if out.numel() >= 2 else out, non_blocking=True)
+        main.synchronize()
+        if next_host_batch is not None:
+            self._cur = 1 - self._cur
+        else:
+            self._filled = False
+        return float(self.loss_host[0])

@@ -131,3 +131,28 @@ def test_multimodal_dt_end_to_end(cuda_device, cfg_name, frame_shape, audio_shap
     for n, p in model.named_parameters():
         if n in fused and p.grad is not None and fused[n].norm() > 0:
             assert rel_err(p.grad, fused[n]) <= 1e-2, n
+
+
+@pytest.mark.parametrize("frame_shape,audio_shape,conv_type", [((3, 64, 64), (1, 64, 64), "big"), ((1, 84, 84), (1, 84, 84), "small")])
+def test_uint8_pixel_frames_bit_exact(frame_shape, audio_shape, conv_type):
+    """uint8 pixels decoded in-kernel (img * 2 / 255 - 1, REF Minecraft.py:333-335) == the same frames decoded on the host to fp32:
+    states and every gradient bit-identical."""
+    dev = torch.device("cuda:0")
+    g = torch.Generator().manual_seed(7)
+    B, K = 3, 5
+    _, enc = _pair(frame_shape, audio_shape, conv_type, "concat", dev)
+    px = torch.randint(0, 256, (B, K, *frame_shape), generator=g, dtype=torch.uint8)
+    px[0, 0].fill_(0); px[0, 1].fill_(255)  # extremes
+    f32 = px.float() * 2.0 / 255.0 - 1  # the reference's own expression
+    audio = _spec(B, K, audio_shape, g)
+    d_states = torch.randn(B, K, enc.state_dim, generator=g).to(torch.bfloat16).to(dev)
+    outs = []
+    for frames in (f32, px):
+        s = enc.forward_raw(frames.to(dev), audio.to(dev)).clone()
+        grads = torch.zeros_like(enc.flat_params)
+        enc.backward_raw(d_states.clone(), masked=False, grads=grads)
+        torch.cuda.synchronize()
+        outs.append((s, grads.clone()))
+    assert torch.equal(outs[0][0], outs[1][0])
+    assert torch.equal(outs[0][1], outs[1][1])
+    assert outs[0][1].abs().sum() > 0
