@@ -153,6 +153,7 @@ static int launch_fwd(cudaStream_t stream, const bf16* qkv, const float* mask, i
 int attn_fwd(cudaStream_t stream, const bf16* qkv, const float* mask, int B, int T, int nh, int d, bf16* out, float* lse) {
   DTB_REQUIRE(T % 3 == 0 || mask == nullptr, DTB_ERR_BAD_ARG, "attention: T (%d) must be 3*K when a [B,K] mask is given", T);
   if (B == 0 || T == 0) return DTB_OK;
+  if (attn_tc_supported(T, d)) return attn_fwd_tc(stream, qkv, mask, B, T, nh, d, out, lse);
   switch (d) {
     case 32: return launch_fwd<32>(stream, qkv, mask, B, T, nh, out, lse);
     case 64: return launch_fwd<64>(stream, qkv, mask, B, T, nh, out, lse);

@@ -1,0 +1,361 @@
+// Causal self-attention with padding mask on tcgen05 tensor cores (head_dim 64) — forward and backward.
+// Replaces eager_attention_forward (HF:47-65) + the materialised [B,1,T,T] mask (HF:408-414, 631-635) and its autograd:
+//   allowed(i, j) = (j <= i) and attention_mask[b, j / 3] > 0        (integer-exact index rule)
+// Same tensors and conventions as the mma.sync kernels in attention.cu / attention_bwd.cu (qkv bf16 [B,T,3H] = q | k | v, head h at
+// h*d; lse in the base-2 domain of s * scale_log2; fully masked rows -> out 0, lse 0; dS = P (dP - delta) / sqrt(d)).
+//
+// Structure (all three kernels): one CTA per (128-row tile, head, batch); TMEM lane = tile row, so each of the 128 softmax threads
+// owns one row and needs no cross-lane reduction.  Warps 0-3 = softmax / epilogue (TMEM lane quadrant = warp), warp 4 = single-thread
+// tcgen05.mma issuer (+ TMEM allocation), warp 5 = TMA producer.  64-wide blocks of the other sequence dimension stream through a
+// 2-stage TMA ring; S (and dP) live in TMEM, P / dS go back to the tensor core through 128B-swizzled shared memory written by the
+// row-owning threads; accumulators (O, dQ, dK, dV) stay in TMEM for the whole CTA.  Two CTAs per SM overlap each other's
+// softmax (MUFU-bound at d = 64) with MMA and TMA.
+#include "kernels.h"
+
+#include <math.h>
+#include <stdlib.h>
+#include <string.h>
+
+namespace dtb {
+
+constexpr int AT_D = 64;
+constexpr int AT_THREADS = 192;
+constexpr int AT_TILE128 = 128 * 128;  // bytes: 128 rows x 128 B (64 bf16)
+constexpr int AT_TILE64 = 64 * 128;    // bytes: 64 rows x 128 B
+constexpr int AT_KV_STAGES = 3;        // TMA ring depth for the streamed 64-row blocks (prefetch distance 2 blocks ~ TMA latency)
+
+struct AttnTcParams {
+  int T, nh, Kmask;
+  float scale, scale_log2;
+  const float* mask;
+  const float* lse_in;
+  const bf16* out_in;   // forward output (backward: delta = rowsum(dO * O))
+  const bf16* dout;
+  bf16* out;
+  float* lse;
+  bf16* dqkv;
+  float* delta;
+};
+
+// key-validity bits of the 64-key block starting at k0: bit l of word c <=> key k0 + 32c + l is in range and not padding
+__device__ __forceinline__ void at_valid_bits(const AttnTcParams& p, int b, int k0, int lane, uint32_t (&bits)[2]) {
+#pragma unroll
+  for (int c = 0; c < 2; ++c) {
+    const int kj = k0 + 32 * c + lane;
+    const bool ok = kj < p.T && (p.mask == nullptr || __ldg(p.mask + (size_t)b * p.Kmask + kj / 3) > 0.f);
+    bits[c] = __ballot_sync(0xffffffffu, ok);
+  }
+}
+
+// the same words for chunks 0..nchunks-1 (32 keys each), written to shared memory once per CTA by all of its warps
+constexpr int AT_MAX_CHUNKS = 128;  // T <= 4096
+__device__ __forceinline__ void at_fill_valid_bits(const AttnTcParams& p, int b, int nchunks, uint32_t* sBits) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarp = blockDim.x >> 5;
+  for (int c = warp; c < nchunks; c += nwarp) {
+    const int kj = 32 * c + lane;
+    const bool ok = kj < p.T && (p.mask == nullptr || __ldg(p.mask + (size_t)b * p.Kmask + kj / 3) > 0.f);
+    const uint32_t w = __ballot_sync(0xffffffffu, ok);
+    if (lane == 0) sBits[c] = w;
+  }
+}
+
+// causal word of a 32-key chunk: bit e set <=> key (chunk_first + e) <= query, given n = query - chunk_first
+__device__ __forceinline__ uint32_t at_causal_word(int n) { return n >= 31 ? 0xffffffffu : (n < 0 ? 0u : ((2u << n) - 1u)); }
+
+// row r of a [rows x 64] bf16 K-major tile (128 B per row, 128B swizzle): 16-byte unit u lives at r*128 + ((u ^ (r & 7)) << 4)
+__device__ __forceinline__ void at_store_row_unit(uint32_t tile_base, int r, int u, uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3) {
+  const uint32_t addr = tile_base + r * 128 + ((u ^ (r & 7)) << 4);
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(w0), "r"(w1), "r"(w2), "r"(w3) : "memory");
+}
+
+// ================================================================================================================================
+// forward
+// ================================================================================================================================
+// smem: Q [128x64] | K[2] [64x64] | V[2] [64x64] | P[2] [128x64]  (all bf16, swizzled)            = 16 + 16 + 16 + 32 KB
+// TMEM (128 columns): S fp32 [128 x 64] at column 0, O fp32 [128 x 64] at column 64
+__global__ void __launch_bounds__(AT_THREADS, 2)
+attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmKV, const AttnTcParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sQ = smem;
+  uint8_t* sK = sQ + AT_TILE128;
+  uint8_t* sV = sK + AT_KV_STAGES * AT_TILE64;
+  uint8_t* sP = sV + AT_KV_STAGES * AT_TILE64;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sP + 2 * AT_TILE128);
+  uint64_t* q_full = bars;          // [1]
+  uint64_t* k_full = bars + 1;      // [4]
+  uint64_t* k_free = bars + 5;      // [4]
+  uint64_t* v_full = bars + 9;      // [4]
+  uint64_t* v_free = bars + 13;     // [4]
+  uint64_t* s_full = bars + 17;     // [1] MMA -> softmax
+  uint64_t* s_free = bars + 18;     // [1] softmax (128) -> MMA
+  uint64_t* p_full = bars + 19;     // [2] softmax (128) -> MMA
+  uint64_t* pv_done = bars + 21;    // [2] MMA -> softmax
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 23);
+  uint32_t* sBits = reinterpret_cast<uint32_t*>(bars + 24);  // [AT_MAX_CHUNKS] key-validity words, 32 keys each
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int qb = gridDim.x - 1 - blockIdx.x;  // heaviest (last) query tiles first
+  const int h = blockIdx.y, b = blockIdx.z;
+  const int q0 = qb * 128;
+  const int T = p.T;
+  int nkb = (q0 + 128) / 64;
+  const int nkb_max = (T + 63) / 64;
+  if (nkb > nkb_max) nkb = nkb_max;
+
+  if (threadIdx.x == 0) {
+    mbar_init(q_full, 1);
+    for (int s = 0; s < AT_KV_STAGES; ++s) {
+      mbar_init(&k_full[s], 1); mbar_init(&k_free[s], 1); mbar_init(&v_full[s], 1); mbar_init(&v_free[s], 1);
+    }
+    for (int s = 0; s < 2; ++s) { mbar_init(&p_full[s], 128); mbar_init(&pv_done[s], 1); }
+    mbar_init(s_full, 1);
+    mbar_init(s_free, 128);
+    fence_mbar_init();
+  }
+  if (warp == 4) { tmem_alloc(tmem_slot, 128); tmem_relinquish(); }
+  at_fill_valid_bits(p, b, 2 * nkb, sBits);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t tS = tmem_base, tO = tmem_base + 64;
+  const int H = p.nh * AT_D;
+
+  if (warp == 5) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      tma_prefetch_desc(&tmQ);
+      tma_prefetch_desc(&tmKV);
+      mbar_arrive_expect_tx(q_full, AT_TILE128);
+      tma_load_3d(sQ, &tmQ, q_full, h * AT_D, q0, b);
+      for (int j = 0; j < nkb; ++j) {
+        const int s = j % AT_KV_STAGES, u = j / AT_KV_STAGES;
+        if (u > 0) mbar_wait(&k_free[s], (u - 1) & 1);
+        mbar_arrive_expect_tx(&k_full[s], AT_TILE64);
+        tma_load_3d(sK + s * AT_TILE64, &tmKV, &k_full[s], H + h * AT_D, j * 64, b);
+        if (u > 0) mbar_wait(&v_free[s], (u - 1) & 1);
+        mbar_arrive_expect_tx(&v_full[s], AT_TILE64);
+        tma_load_3d(sV + s * AT_TILE64, &tmKV, &v_full[s], 2 * H + h * AT_D, j * 64, b);
+      }
+    }
+  } else if (warp == 4) {
+    // ===================== MMA issuer (single thread) =====================
+    if (lane == 0) {
+      const uint32_t idesc_qk = make_idesc_bf16(128, 64, 0, 0);
+      const uint32_t idesc_pv = make_idesc_bf16(128, 64, 0, 1);
+      const uint32_t q_addr = smem_u32(sQ);
+      auto issue_qk = [&](int j) {
+        const int s = j % AT_KV_STAGES;
+        mbar_wait(&k_full[s], (j / AT_KV_STAGES) & 1);
+        if (j > 0) mbar_wait(s_free, (j - 1) & 1);
+        tc_fence_after();
+        const uint32_t k_addr = smem_u32(sK + s * AT_TILE64);
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk)
+          umma_bf16(tS, make_smem_desc_sw128(q_addr + kk * 32, 16, 1024), make_smem_desc_sw128(k_addr + kk * 32, 16, 1024), idesc_qk,
+                    kk > 0 ? 1u : 0u);
+        umma_commit(&k_free[s]);
+        umma_commit(s_full);
+      };
+      mbar_wait(q_full, 0);
+      issue_qk(0);
+      for (int j = 0; j < nkb; ++j) {
+        if (j + 1 < nkb) issue_qk(j + 1);
+        const int s = j % AT_KV_STAGES, pb = j & 1;
+        mbar_wait(&v_full[s], (j / AT_KV_STAGES) & 1);
+        mbar_wait(&p_full[pb], (j >> 1) & 1);
+        tc_fence_after();
+        const uint32_t p_addr = smem_u32(sP + pb * AT_TILE128), v_addr = smem_u32(sV + s * AT_TILE64);
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk)
+          umma_bf16(tO, make_smem_desc_sw128(p_addr + kk * 32, 16, 1024), make_smem_desc_sw128(v_addr + kk * 2048, 8192, 1024), idesc_pv,
+                    (j > 0 || kk > 0) ? 1u : 0u);
+        umma_commit(&v_free[s]);
+        umma_commit(&pv_done[pb]);
+      }
+    }
+  } else {
+    // ===================== softmax: one thread per query row =====================
+    const int r = warp * 32 + lane;
+    const int qi = q0 + r;
+    const uint32_t lane_addr = (uint32_t)(warp * 32) << 16;
+    float m_use = -INFINITY, l = 0.f;
+    for (int j = 0; j < nkb; ++j) {
+      const int k0 = j * 64;
+      const uint32_t bits[2] = {sBits[2 * j], sBits[2 * j + 1]};
+      const bool diag = k0 + 63 > q0;  // some key of the block is beyond some query of the tile
+      // chunk c of this warp is entirely above the diagonal when its first key exceeds the warp's last row
+      const bool act0 = !diag || (k0 <= q0 + warp * 32 + 31), act1 = !diag || (k0 + 32 <= q0 + warp * 32 + 31);
+      mbar_wait(s_full, j & 1);
+      tc_fence_after();
+      uint32_t v0[32], v1[32];
+      if (act0) tmem_ld_32x32(tS + lane_addr, v0);
+      if (act1) tmem_ld_32x32(tS + lane_addr + 32, v1);
+      tmem_ld_wait();
+      tc_fence_before();
+      mbar_arrive(s_free);
+      // ---- mask (branch-free: one allowed-key word per 32-key chunk and row) + row max (raw domain; scale > 0) ----
+      uint32_t m0 = 0u, m1 = 0u;
+      if (act0) m0 = bits[0] & (diag ? at_causal_word(qi - k0) : 0xffffffffu);
+      if (act1) m1 = bits[1] & (diag ? at_causal_word(qi - k0 - 32) : 0xffffffffu);
+      const bool all_open = __all_sync(0xffffffffu, (m0 & m1) == 0xffffffffu);  // warp-uniform fast path: nothing to mask
+      float mxa = -INFINITY, mxb = -INFINITY, mxc = -INFINITY, mxd = -INFINITY;
+      if (!all_open) {
+        if (act0) {
+#pragma unroll
+          for (int e = 0; e < 32; ++e) v0[e] = (m0 & (1u << e)) ? v0[e] : 0xff800000u;  // -inf
+        }
+        if (act1) {
+#pragma unroll
+          for (int e = 0; e < 32; ++e) v1[e] = (m1 & (1u << e)) ? v1[e] : 0xff800000u;
+        }
+      }
+      if (act0) {
+#pragma unroll
+        for (int e = 0; e < 32; e += 4) {
+          mxa = fmaxf(mxa, __uint_as_float(v0[e])); mxb = fmaxf(mxb, __uint_as_float(v0[e + 1]));
+          mxc = fmaxf(mxc, __uint_as_float(v0[e + 2])); mxd = fmaxf(mxd, __uint_as_float(v0[e + 3]));
+        }
+      }
+      if (act1) {
+#pragma unroll
+        for (int e = 0; e < 32; e += 4) {
+          mxa = fmaxf(mxa, __uint_as_float(v1[e])); mxb = fmaxf(mxb, __uint_as_float(v1[e + 1]));
+          mxc = fmaxf(mxc, __uint_as_float(v1[e + 2])); mxd = fmaxf(mxd, __uint_as_float(v1[e + 3]));
+        }
+      }
+      const float mxs = fmaxf(fmaxf(mxa, mxb), fmaxf(mxc, mxd)) * p.scale_log2;
+      // lazy rescale: the running maximum only moves when it grows by more than 8 (p <= 2^8 stays exact enough in bf16 / fp32)
+      float alpha = 1.f;
+      bool moved = false;
+      if (j == 0) {
+        m_use = mxs;
+      } else if (mxs > m_use + 8.f) {
+        alpha = fast_exp2(m_use - mxs);  // m_use = -inf -> 0
+        m_use = mxs;
+        moved = true;
+      }
+      const float nms = m_use == -INFINITY ? 0.f : -m_use;
+      // ---- P = exp2(s * scale_log2 - m), row sum, bf16 pack ----
+      const int s = j & 1;
+      if (j >= 2) mbar_wait(&pv_done[s], ((j - 2) >> 1) & 1);  // P buffer s was last read by PV(j - 2)
+      const uint32_t p_tile = smem_u32(sP + s * AT_TILE128);
+      float rsa = 0.f, rsb = 0.f, rsc = 0.f, rsd = 0.f;
+      if (act0) {
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          float f[8];
+#pragma unroll
+          for (int e = 0; e < 8; ++e) f[e] = fast_exp2(fmaf(__uint_as_float(v0[u * 8 + e]), p.scale_log2, nms));
+          rsa += f[0] + f[4]; rsb += f[1] + f[5]; rsc += f[2] + f[6]; rsd += f[3] + f[7];
+          at_store_row_unit(p_tile, r, u, pack_bf16x2(f[0], f[1]), pack_bf16x2(f[2], f[3]), pack_bf16x2(f[4], f[5]), pack_bf16x2(f[6], f[7]));
+        }
+      } else {
+#pragma unroll
+        for (int u = 0; u < 4; ++u) at_store_row_unit(p_tile, r, u, 0u, 0u, 0u, 0u);
+      }
+      if (act1) {
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          float f[8];
+#pragma unroll
+          for (int e = 0; e < 8; ++e) f[e] = fast_exp2(fmaf(__uint_as_float(v1[u * 8 + e]), p.scale_log2, nms));
+          rsa += f[0] + f[4]; rsb += f[1] + f[5]; rsc += f[2] + f[6]; rsd += f[3] + f[7];
+          at_store_row_unit(p_tile, r, 4 + u, pack_bf16x2(f[0], f[1]), pack_bf16x2(f[2], f[3]), pack_bf16x2(f[4], f[5]), pack_bf16x2(f[6], f[7]));
+        }
+      } else {
+#pragma unroll
+        for (int u = 0; u < 4; ++u) at_store_row_unit(p_tile, r, 4 + u, 0u, 0u, 0u, 0u);
+      }
+      const float rs = (rsa + rsb) + (rsc + rsd);
+      l = l * alpha + rs;
+      // ---- rescale O when some row of this warp moved its maximum (PV(j-1) must have retired) ----
+      if (__any_sync(0xffffffffu, moved)) {
+        mbar_wait(&pv_done[(j - 1) & 1], ((j - 1) >> 1) & 1);
+        tc_fence_after();
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+          uint32_t o[32];
+          tmem_ld_32x32(tO + lane_addr + c * 32, o);
+          tmem_ld_wait();
+#pragma unroll
+          for (int e = 0; e < 32; ++e) o[e] = __float_as_uint(__uint_as_float(o[e]) * alpha);
+          tmem_st_32x32(tO + lane_addr + c * 32, o);
+        }
+        tmem_st_wait();
+      }
+      fence_proxy_async();  // P stores (generic proxy) -> visible to the tensor core
+      tc_fence_before();
+      mbar_arrive(&p_full[s]);
+    }
+    // ---- epilogue: O / l -> bf16, lse ----
+    mbar_wait(&pv_done[(nkb - 1) & 1], ((nkb - 1) >> 1) & 1);
+    tc_fence_after();
+    const float inv = l > 0.f ? 1.f / l : 0.f;
+    bf16* orow = p.out + ((size_t)b * T + qi) * H + h * AT_D;
+#pragma unroll
+    for (int c = 0; c < 2; ++c) {
+      uint32_t o[32];
+      tmem_ld_32x32(tO + lane_addr + c * 32, o);
+      tmem_ld_wait();
+      if (qi < T) {
+#pragma unroll
+        for (int e = 0; e < 32; e += 8)
+          *reinterpret_cast<uint4*>(orow + c * 32 + e) =
+              make_uint4(pack_bf16x2(__uint_as_float(o[e]) * inv, __uint_as_float(o[e + 1]) * inv),
+                         pack_bf16x2(__uint_as_float(o[e + 2]) * inv, __uint_as_float(o[e + 3]) * inv),
+                         pack_bf16x2(__uint_as_float(o[e + 4]) * inv, __uint_as_float(o[e + 5]) * inv),
+                         pack_bf16x2(__uint_as_float(o[e + 6]) * inv, __uint_as_float(o[e + 7]) * inv));
+      }
+    }
+    if (qi < T) p.lse[((size_t)b * p.nh + h) * T + qi] = l > 0.f ? m_use + log2f(l) : 0.f;
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 4) { tc_fence_after(); tmem_dealloc(tmem_base, 128); }
+}
+
+constexpr int AT_FWD_SMEM = 1024 + AT_TILE128 + 2 * AT_KV_STAGES * AT_TILE64 + 2 * AT_TILE128 + 256 + AT_MAX_CHUNKS * 4;
+
+bool attn_tc_supported(int T, int d) {
+  static int legacy = -1;
+  if (legacy < 0) {
+    const char* e = getenv("DTB_ATTN_LEGACY");
+    legacy = (e && e[0] == '1') ? 1 : 0;
+  }
+  return !legacy && d == AT_D && T >= 1 && T <= 32 * AT_MAX_CHUNKS;
+}
+
+static int at_maps(const bf16* qkv, int B, int T, int H, CUtensorMap* tm128, CUtensorMap* tm64) {
+  DTB_TRY(make_tmap3(tm128, qkv, (uint64_t)3 * H, (uint64_t)T, (uint64_t)B, (uint64_t)3 * H, (uint64_t)T * 3 * H, 64, 128));
+  DTB_TRY(make_tmap3(tm64, qkv, (uint64_t)3 * H, (uint64_t)T, (uint64_t)B, (uint64_t)3 * H, (uint64_t)T * 3 * H, 64, 64));
+  return DTB_OK;
+}
+
+int attn_fwd_tc(cudaStream_t stream, const bf16* qkv, const float* mask, int B, int T, int nh, int d, bf16* out, float* lse) {
+  DTB_REQUIRE(d == AT_D, DTB_ERR_UNSUPPORTED, "tcgen05 attention: head_dim %d unsupported (64)", d);
+  DTB_REQUIRE((nh * d) % 8 == 0, DTB_ERR_BAD_ARG, "tcgen05 attention: hidden size must be a multiple of 8");
+  const int H = nh * d;
+  CUtensorMap tmQ, tmKV;
+  DTB_TRY(at_maps(qkv, B, T, H, &tmQ, &tmKV));
+  AttnTcParams p;
+  memset(&p, 0, sizeof(p));
+  p.T = T; p.nh = nh; p.Kmask = T / 3;
+  p.scale = 1.f / sqrtf((float)d);
+  p.scale_log2 = 1.4426950408889634f * p.scale;
+  p.mask = mask; p.out = out; p.lse = lse;
+  static bool attr = false;
+  if (!attr) {
+    DTB_CUDA(cudaFuncSetAttribute(attn_fwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_FWD_SMEM));
+    attr = true;
+  }
+  dim3 grid((T + 127) / 128, nh, B);
+  ProfScope prof(stream, PF_ATTN_FWD, 2.0 * B * nh * (double)T * T * d);
+  attn_fwd_tc_kernel<<<grid, AT_THREADS, AT_FWD_SMEM, stream>>>(tmQ, tmKV, p);
+  DTB_CHECK_LAUNCH();
+  return DTB_OK;
+}
+
+}  // namespace dtb

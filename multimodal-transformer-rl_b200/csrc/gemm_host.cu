@@ -75,6 +75,24 @@ int make_tmap(CUtensorMap* out, const void* ptr, uint64_t d0, uint64_t d1, uint6
   return DTB_OK;
 }
 
+// 3-D bf16 tensor map (uncached: callers keep it for the launch): dims {d0 contiguous, d1, d2}, strides of d1 / d2 in elements,
+// box {b0, b1, 1}, 128B swizzle, out-of-bounds elements read as zero.
+int make_tmap3(CUtensorMap* out, const void* ptr, uint64_t d0, uint64_t d1, uint64_t d2, uint64_t stride1, uint64_t stride2, uint32_t b0,
+               uint32_t b1) {
+  DTB_TRY(get_encode_fn());
+  DTB_REQUIRE((reinterpret_cast<uintptr_t>(ptr) & 15) == 0 && (stride1 * 2) % 16 == 0 && (stride2 * 2) % 16 == 0, DTB_ERR_BAD_ARG,
+              "tensor map: pointer / strides must be 16-byte aligned");
+  cuuint64_t gdim[3] = {d0, d1, d2};
+  cuuint64_t gstride[2] = {stride1 * 2, stride2 * 2};
+  cuuint32_t box[3] = {b0, b1, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = g_encode(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(ptr), gdim, gstride, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  DTB_REQUIRE(r == CUDA_SUCCESS, DTB_ERR_CUDA, "cuTensorMapEncodeTiled(3d) failed (%d)", (int)r);
+  return DTB_OK;
+}
+
 static bool g_attr_set = false;
 
 size_t gemm_splitk_workspace_bytes(int M, int N, int K) {

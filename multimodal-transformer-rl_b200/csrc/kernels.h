@@ -46,6 +46,9 @@ int splitk_reduce(cudaStream_t stream, const float* partial, int splits, int M, 
 // 2-D bf16 tensor map (cached): dims {d0 contiguous, d1}, row stride in elements, box {b0, b1}, 128B swizzle.
 int make_tmap(CUtensorMap* out, const void* ptr, uint64_t d0, uint64_t d1, uint64_t stride_elems, uint32_t b0, uint32_t b1);
 
+int make_tmap3(CUtensorMap* out, const void* ptr, uint64_t d0, uint64_t d1, uint64_t d2, uint64_t stride1, uint64_t stride2, uint32_t b0,
+               uint32_t b1);
+
 // ---- elementwise.cu ----------------------------------------------------------------------------
 // fp32 [R, C] -> bf16 copy [R, C] and (optional) bf16 transpose [C, R]
 int cast_transpose(cudaStream_t stream, const float* src, int R, int C, bf16* dst, bf16* dst_t);
@@ -67,6 +70,12 @@ size_t ln_bwd_scratch_floats(int H);
 int attn_fwd(cudaStream_t stream, const bf16* qkv, const float* mask, int B, int T, int nh, int d, bf16* out, float* lse);
 int attn_bwd(cudaStream_t stream, const bf16* qkv, const float* mask, const bf16* out, const bf16* dout, const float* lse, int B, int T,
              int nh, int d, bf16* dqkv, float* delta);
+
+// ---- attention_tc.cu: tcgen05 / TMEM / TMA flash attention (head_dim 64) ----------------------------
+bool attn_tc_supported(int T, int d);
+int attn_fwd_tc(cudaStream_t stream, const bf16* qkv, const float* mask, int B, int T, int nh, int d, bf16* out, float* lse);
+int attn_bwd_tc(cudaStream_t stream, const bf16* qkv, const float* mask, const bf16* out, const bf16* dout, const float* lse, int B, int T,
+                int nh, int d, bf16* dqkv, float* delta);
 
 // ---- embed.cu ----------------------------------------------------------------------------------
 int embed_fwd(cudaStream_t stream, const float* states, const float* state_proj, const float* actions, const float* rtg,
