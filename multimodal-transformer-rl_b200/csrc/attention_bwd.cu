@@ -281,6 +281,7 @@ int attn_bwd(cudaStream_t stream, const bf16* qkv, const float* mask, const bf16
              int nh, int d, bf16* dqkv, float* delta) {
   DTB_REQUIRE(T % 3 == 0 || mask == nullptr, DTB_ERR_BAD_ARG, "attention bwd: T (%d) must be 3*K when a [B,K] mask is given", T);
   if (B == 0 || T == 0) return DTB_OK;
+  if (attn_tc_supported(T, d)) return attn_bwd_tc(stream, qkv, mask, out, dout, lse, B, T, nh, d, dqkv, delta);
   switch (d) {
     case 32: return launch_bwd<32>(stream, qkv, mask, out, dout, lse, B, T, nh, dqkv, delta);
     case 64: return launch_bwd<64>(stream, qkv, mask, out, dout, lse, B, T, nh, dqkv, delta);

@@ -317,6 +317,413 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
   if (warp == 4) { tc_fence_after(); tmem_dealloc(tmem_base, 128); }
 }
 
+// ================================================================================================================================
+// backward, pass 1: delta = rowsum(dO * O) and dQ = sum_j dS_ij K_j        (one CTA per 128-query tile)
+// ================================================================================================================================
+// smem: Q [128x64] | dO [128x64] | K[3] [64x64] | V[2] [64x64] | dS[2] [128x64]                     = 16 + 16 + 24 + 16 + 32 KB
+// TMEM (256 columns): S at 0, dP at 64, dQ at 128 (fp32 [128 x 64] each)
+constexpr int AT_DQ_KST = 3, AT_DQ_VST = 2;
+
+// one 32-column half of a row: P = exp2(s * scale_log2 - lse), dS = P (dP - delta) / sqrt(d) -> bf16 units u0..u0+3 of the dS tile row
+__device__ __forceinline__ void at_ds_half(const uint32_t (&sv)[32], const uint32_t (&dv)[32], uint32_t word, float scale_log2, float nlse,
+                                           float delta, float scale, uint32_t tile, int r, int u0) {
+#pragma unroll
+  for (int u = 0; u < 4; ++u) {
+    float f[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      const int c = u * 8 + e;
+      float pe = fast_exp2(fmaf(__uint_as_float(sv[c]), scale_log2, nlse));
+      pe = (word & (1u << c)) ? pe : 0.f;
+      f[e] = pe * (__uint_as_float(dv[c]) - delta) * scale;
+    }
+    at_store_row_unit(tile, r, u0 + u, pack_bf16x2(f[0], f[1]), pack_bf16x2(f[2], f[3]), pack_bf16x2(f[4], f[5]), pack_bf16x2(f[6], f[7]));
+  }
+}
+
+__global__ void __launch_bounds__(AT_THREADS, 2)
+attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmKV,
+                      const __grid_constant__ CUtensorMap tmDO, const AttnTcParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sQ = smem;
+  uint8_t* sDO = sQ + AT_TILE128;
+  uint8_t* sK = sDO + AT_TILE128;
+  uint8_t* sV = sK + AT_DQ_KST * AT_TILE64;
+  uint8_t* sDS = sV + AT_DQ_VST * AT_TILE64;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sDS + 2 * AT_TILE128);
+  uint64_t* qdo_full = bars;        // [1]
+  uint64_t* k_full = bars + 1;      // [3]
+  uint64_t* k_free = bars + 4;      // [3]
+  uint64_t* v_full = bars + 7;      // [2]
+  uint64_t* v_free = bars + 9;      // [2]
+  uint64_t* sdp_full = bars + 11;   // [1] MMA -> threads
+  uint64_t* sdp_free = bars + 12;   // [1] threads (128) -> MMA
+  uint64_t* ds_full = bars + 13;    // [2] threads (128) -> MMA
+  uint64_t* ds_done = bars + 15;    // [2] MMA -> threads
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 17);
+  uint32_t* sBits = reinterpret_cast<uint32_t*>(bars + 18);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int qb = gridDim.x - 1 - blockIdx.x;
+  const int h = blockIdx.y, b = blockIdx.z;
+  const int q0 = qb * 128;
+  const int T = p.T;
+  int nkb = (q0 + 128) / 64;
+  const int nkb_max = (T + 63) / 64;
+  if (nkb > nkb_max) nkb = nkb_max;
+
+  if (threadIdx.x == 0) {
+    mbar_init(qdo_full, 1);
+    for (int s = 0; s < AT_DQ_KST; ++s) { mbar_init(&k_full[s], 1); mbar_init(&k_free[s], 1); }
+    for (int s = 0; s < AT_DQ_VST; ++s) { mbar_init(&v_full[s], 1); mbar_init(&v_free[s], 1); }
+    for (int s = 0; s < 2; ++s) { mbar_init(&ds_full[s], 128); mbar_init(&ds_done[s], 1); }
+    mbar_init(sdp_full, 1);
+    mbar_init(sdp_free, 128);
+    fence_mbar_init();
+  }
+  if (warp == 4) { tmem_alloc(tmem_slot, 256); tmem_relinquish(); }
+  at_fill_valid_bits(p, b, 2 * nkb, sBits);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t tS = tmem_base, tDP = tmem_base + 64, tDQ = tmem_base + 128;
+  const int H = p.nh * AT_D;
+
+  if (warp == 5) {
+    if (lane == 0) {
+      tma_prefetch_desc(&tmQ); tma_prefetch_desc(&tmKV); tma_prefetch_desc(&tmDO);
+      mbar_arrive_expect_tx(qdo_full, 2 * AT_TILE128);
+      tma_load_3d(sQ, &tmQ, qdo_full, h * AT_D, q0, b);
+      tma_load_3d(sDO, &tmDO, qdo_full, h * AT_D, q0, b);
+      for (int j = 0; j < nkb; ++j) {
+        const int sk = j % AT_DQ_KST, uk = j / AT_DQ_KST, sv = j % AT_DQ_VST, uv = j / AT_DQ_VST;
+        if (uk > 0) mbar_wait(&k_free[sk], (uk - 1) & 1);
+        mbar_arrive_expect_tx(&k_full[sk], AT_TILE64);
+        tma_load_3d(sK + sk * AT_TILE64, &tmKV, &k_full[sk], H + h * AT_D, j * 64, b);
+        if (uv > 0) mbar_wait(&v_free[sv], (uv - 1) & 1);
+        mbar_arrive_expect_tx(&v_full[sv], AT_TILE64);
+        tma_load_3d(sV + sv * AT_TILE64, &tmKV, &v_full[sv], 2 * H + h * AT_D, j * 64, b);
+      }
+    }
+  } else if (warp == 4) {
+    if (lane == 0) {
+      const uint32_t idesc_kk = make_idesc_bf16(128, 64, 0, 0), idesc_kn = make_idesc_bf16(128, 64, 0, 1);
+      const uint32_t q_addr = smem_u32(sQ), do_addr = smem_u32(sDO);
+      auto issue_sdp = [&](int j) {
+        const int sk = j % AT_DQ_KST, sv = j % AT_DQ_VST;
+        mbar_wait(&k_full[sk], (j / AT_DQ_KST) & 1);
+        mbar_wait(&v_full[sv], (j / AT_DQ_VST) & 1);
+        if (j > 0) mbar_wait(sdp_free, (j - 1) & 1);
+        tc_fence_after();
+        const uint32_t k_addr = smem_u32(sK + sk * AT_TILE64), v_addr = smem_u32(sV + sv * AT_TILE64);
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk)
+          umma_bf16(tS, make_smem_desc_sw128(q_addr + kk * 32, 16, 1024), make_smem_desc_sw128(k_addr + kk * 32, 16, 1024), idesc_kk,
+                    kk > 0 ? 1u : 0u);
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk)
+          umma_bf16(tDP, make_smem_desc_sw128(do_addr + kk * 32, 16, 1024), make_smem_desc_sw128(v_addr + kk * 32, 16, 1024), idesc_kk,
+                    kk > 0 ? 1u : 0u);
+        umma_commit(&v_free[sv]);
+        umma_commit(sdp_full);
+      };
+      mbar_wait(qdo_full, 0);
+      issue_sdp(0);
+      for (int j = 0; j < nkb; ++j) {
+        if (j + 1 < nkb) issue_sdp(j + 1);
+        const int sk = j % AT_DQ_KST, db = j & 1;
+        mbar_wait(&ds_full[db], (j >> 1) & 1);
+        tc_fence_after();
+        const uint32_t ds_addr = smem_u32(sDS + db * AT_TILE128), k_addr = smem_u32(sK + sk * AT_TILE64);
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk)
+          umma_bf16(tDQ, make_smem_desc_sw128(ds_addr + kk * 32, 16, 1024), make_smem_desc_sw128(k_addr + kk * 2048, 8192, 1024), idesc_kn,
+                    (j > 0 || kk > 0) ? 1u : 0u);
+        umma_commit(&k_free[sk]);
+        umma_commit(&ds_done[db]);
+      }
+    }
+  } else {
+    const int r = warp * 32 + lane;
+    const int qi = q0 + r;
+    const uint32_t lane_addr = (uint32_t)(warp * 32) << 16;
+    const size_t row_off = ((size_t)b * p.nh + h) * T;
+    // delta = rowsum(dO * O) for this thread's row, straight from global (128 B each)
+    float delta = 0.f, nlse = 0.f;
+    if (qi < T) {
+      const uint4* orow = reinterpret_cast<const uint4*>(p.out_in + ((size_t)b * T + qi) * H + h * AT_D);
+      const uint4* drow = reinterpret_cast<const uint4*>(p.dout + ((size_t)b * T + qi) * H + h * AT_D);
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const uint4 a = __ldg(orow + u), g = __ldg(drow + u);
+        const uint32_t aw[4] = {a.x, a.y, a.z, a.w}, gw[4] = {g.x, g.y, g.z, g.w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const float2 x = unpack_bf16x2(aw[e]), y = unpack_bf16x2(gw[e]);
+          delta += x.x * y.x + x.y * y.y;
+        }
+      }
+      p.delta[row_off + qi] = delta;
+      nlse = -__ldg(p.lse_in + row_off + qi);
+    }
+    for (int j = 0; j < nkb; ++j) {
+      const int k0 = j * 64;
+      const uint32_t bits[2] = {sBits[2 * j], sBits[2 * j + 1]};
+      const bool diag = k0 + 63 > q0;
+      const bool act0 = !diag || (k0 <= q0 + warp * 32 + 31), act1 = !diag || (k0 + 32 <= q0 + warp * 32 + 31);
+      uint32_t m0 = 0u, m1 = 0u;
+      if (act0) m0 = bits[0] & (diag ? at_causal_word(qi - k0) : 0xffffffffu);
+      if (act1) m1 = bits[1] & (diag ? at_causal_word(qi - k0 - 32) : 0xffffffffu);
+      const int db = j & 1;
+      const uint32_t tile = smem_u32(sDS + db * AT_TILE128);
+      mbar_wait(sdp_full, j & 1);
+      tc_fence_after();
+      if (j >= 2) mbar_wait(&ds_done[db], ((j - 2) >> 1) & 1);  // dS buffer db was last read by the dQ MMAs of block j - 2
+      uint32_t sv[32], dv[32];
+      if (act0) {
+        tmem_ld_32x32(tS + lane_addr, sv);
+        tmem_ld_32x32(tDP + lane_addr, dv);
+        tmem_ld_wait();
+        at_ds_half(sv, dv, m0, p.scale_log2, nlse, delta, p.scale, tile, r, 0);
+      } else {
+#pragma unroll
+        for (int u = 0; u < 4; ++u) at_store_row_unit(tile, r, u, 0u, 0u, 0u, 0u);
+      }
+      if (act1) {
+        tmem_ld_32x32(tS + lane_addr + 32, sv);
+        tmem_ld_32x32(tDP + lane_addr + 32, dv);
+        tmem_ld_wait();
+      }
+      tc_fence_before();
+      mbar_arrive(sdp_free);  // S / dP of this block are in registers: the next block's MMAs may overwrite them
+      if (act1) {
+        at_ds_half(sv, dv, m1, p.scale_log2, nlse, delta, p.scale, tile, r, 4);
+      } else {
+#pragma unroll
+        for (int u = 0; u < 4; ++u) at_store_row_unit(tile, r, 4 + u, 0u, 0u, 0u, 0u);
+      }
+      fence_proxy_async();
+      mbar_arrive(&ds_full[db]);
+    }
+    mbar_wait(&ds_done[(nkb - 1) & 1], ((nkb - 1) >> 1) & 1);
+    tc_fence_after();
+    bf16* grow = p.dqkv + ((size_t)b * T + qi) * 3 * H + h * AT_D;
+#pragma unroll
+    for (int c = 0; c < 2; ++c) {
+      uint32_t o[32];
+      tmem_ld_32x32(tDQ + lane_addr + c * 32, o);
+      tmem_ld_wait();
+      if (qi < T) {
+#pragma unroll
+        for (int e = 0; e < 32; e += 8)
+          *reinterpret_cast<uint4*>(grow + c * 32 + e) =
+              make_uint4(pack_bf16x2(__uint_as_float(o[e]), __uint_as_float(o[e + 1])), pack_bf16x2(__uint_as_float(o[e + 2]), __uint_as_float(o[e + 3])),
+                         pack_bf16x2(__uint_as_float(o[e + 4]), __uint_as_float(o[e + 5])), pack_bf16x2(__uint_as_float(o[e + 6]), __uint_as_float(o[e + 7])));
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 4) { tc_fence_after(); tmem_dealloc(tmem_base, 256); }
+}
+
+// ================================================================================================================================
+// backward, pass 2: dV = P^T dO, dK = dS^T Q        (one CTA per 128-key tile; TMEM lane = key, columns = queries)
+// ================================================================================================================================
+// smem: K [128x64] | V [128x64] | Q[2] [64x64] | dO[2] [64x64] | P^T [128x64] | dS^T [128x64] | lse[Tp] | delta[Tp]
+// TMEM (256 columns): S^T at 0, dP^T at 64, dV at 128, dK at 192
+constexpr int AT_MAX_T_BWD = 1024;
+
+__global__ void __launch_bounds__(AT_THREADS, 2)
+attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmKV, const __grid_constant__ CUtensorMap tmQ64,
+                       const __grid_constant__ CUtensorMap tmDO64, const AttnTcParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sK = smem;
+  uint8_t* sV = sK + AT_TILE128;
+  uint8_t* sQ = sV + AT_TILE128;
+  uint8_t* sDO = sQ + 2 * AT_TILE64;
+  uint8_t* sPT = sDO + 2 * AT_TILE64;
+  uint8_t* sDST = sPT + AT_TILE128;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sDST + AT_TILE128);
+  uint64_t* kv_full = bars;         // [1]
+  uint64_t* qdo_full = bars + 1;    // [2]
+  uint64_t* qdo_free = bars + 3;    // [2]
+  uint64_t* sdp_full = bars + 5;    // [1]
+  uint64_t* sdp_free = bars + 6;    // [1] (128)
+  uint64_t* pds_full = bars + 7;    // [1] (128)
+  uint64_t* pds_done = bars + 8;    // [1]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 9);
+  float* sLse = reinterpret_cast<float*>(bars + 10);
+  float* sDelta = sLse + AT_MAX_T_BWD;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int kb = blockIdx.x, h = blockIdx.y, b = blockIdx.z;  // key tile 0 has the most query blocks: heaviest first
+  const int k0 = kb * 128;
+  const int T = p.T;
+  const int i0 = k0 / 64, nqb = (T + 63) / 64, n = nqb - i0;
+  const size_t row_off = ((size_t)b * p.nh + h) * T;
+
+  if (threadIdx.x == 0) {
+    mbar_init(kv_full, 1);
+    for (int s = 0; s < 2; ++s) { mbar_init(&qdo_full[s], 1); mbar_init(&qdo_free[s], 1); }
+    mbar_init(sdp_full, 1);
+    mbar_init(sdp_free, 128);
+    mbar_init(pds_full, 128);
+    mbar_init(pds_done, 1);
+    fence_mbar_init();
+  }
+  if (warp == 4) { tmem_alloc(tmem_slot, 256); tmem_relinquish(); }
+  for (int t = i0 * 64 + threadIdx.x; t < nqb * 64; t += blockDim.x) {
+    sLse[t] = t < T ? -__ldg(p.lse_in + row_off + t) : 0.f;   // negated: exponent = s * scale_log2 + (-lse)
+    sDelta[t] = t < T ? __ldg(p.delta + row_off + t) : 0.f;
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t tST = tmem_base, tDPT = tmem_base + 64, tDV = tmem_base + 128, tDK = tmem_base + 192;
+  const int H = p.nh * AT_D;
+
+  if (warp == 5) {
+    if (lane == 0) {
+      tma_prefetch_desc(&tmKV); tma_prefetch_desc(&tmQ64); tma_prefetch_desc(&tmDO64);
+      mbar_arrive_expect_tx(kv_full, 2 * AT_TILE128);
+      tma_load_3d(sK, &tmKV, kv_full, H + h * AT_D, k0, b);
+      tma_load_3d(sV, &tmKV, kv_full, 2 * H + h * AT_D, k0, b);
+      for (int t = 0; t < n; ++t) {
+        const int s = t & 1, u = t >> 1;
+        if (u > 0) mbar_wait(&qdo_free[s], (u - 1) & 1);
+        mbar_arrive_expect_tx(&qdo_full[s], 2 * AT_TILE64);
+        tma_load_3d(sQ + s * AT_TILE64, &tmQ64, &qdo_full[s], h * AT_D, (i0 + t) * 64, b);
+        tma_load_3d(sDO + s * AT_TILE64, &tmDO64, &qdo_full[s], h * AT_D, (i0 + t) * 64, b);
+      }
+    }
+  } else if (warp == 4) {
+    if (lane == 0) {
+      const uint32_t idesc_kk = make_idesc_bf16(128, 64, 0, 0), idesc_kn = make_idesc_bf16(128, 64, 0, 1);
+      const uint32_t k_addr = smem_u32(sK), v_addr = smem_u32(sV), pt_addr = smem_u32(sPT), dst_addr = smem_u32(sDST);
+      auto issue_sdp = [&](int t) {
+        const int s = t & 1;
+        mbar_wait(&qdo_full[s], (t >> 1) & 1);
+        if (t > 0) mbar_wait(sdp_free, (t - 1) & 1);
+        tc_fence_after();
+        const uint32_t q_addr = smem_u32(sQ + s * AT_TILE64), do_addr = smem_u32(sDO + s * AT_TILE64);
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk)
+          umma_bf16(tST, make_smem_desc_sw128(k_addr + kk * 32, 16, 1024), make_smem_desc_sw128(q_addr + kk * 32, 16, 1024), idesc_kk,
+                    kk > 0 ? 1u : 0u);
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk)
+          umma_bf16(tDPT, make_smem_desc_sw128(v_addr + kk * 32, 16, 1024), make_smem_desc_sw128(do_addr + kk * 32, 16, 1024), idesc_kk,
+                    kk > 0 ? 1u : 0u);
+        umma_commit(sdp_full);
+      };
+      mbar_wait(kv_full, 0);
+      issue_sdp(0);
+      for (int t = 0; t < n; ++t) {
+        if (t + 1 < n) issue_sdp(t + 1);
+        const int s = t & 1;
+        mbar_wait(pds_full, t & 1);
+        tc_fence_after();
+        const uint32_t q_addr = smem_u32(sQ + s * AT_TILE64), do_addr = smem_u32(sDO + s * AT_TILE64);
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk)
+          umma_bf16(tDV, make_smem_desc_sw128(pt_addr + kk * 32, 16, 1024), make_smem_desc_sw128(do_addr + kk * 2048, 8192, 1024), idesc_kn,
+                    (t > 0 || kk > 0) ? 1u : 0u);
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk)
+          umma_bf16(tDK, make_smem_desc_sw128(dst_addr + kk * 32, 16, 1024), make_smem_desc_sw128(q_addr + kk * 2048, 8192, 1024), idesc_kn,
+                    (t > 0 || kk > 0) ? 1u : 0u);
+        umma_commit(&qdo_free[s]);
+        umma_commit(pds_done);
+      }
+    }
+  } else {
+    const int r = warp * 32 + lane;
+    const int kj = k0 + r;
+    const uint32_t lane_addr = (uint32_t)(warp * 32) << 16;
+    const bool key_ok = kj < T && (p.mask == nullptr || __ldg(p.mask + (size_t)b * p.Kmask + kj / 3) > 0.f);
+    const uint32_t pt_tile = smem_u32(sPT), dst_tile = smem_u32(sDST);
+    for (int t = 0; t < n; ++t) {
+      const int qs = (i0 + t) * 64;  // first query of the block
+      mbar_wait(sdp_full, t & 1);
+      tc_fence_after();
+      if (t > 0) mbar_wait(pds_done, (t - 1) & 1);  // P^T / dS^T were read by the previous block's dV / dK MMAs
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {
+        const int qc = qs + 32 * c;                           // first query of the 32-wide chunk
+        const bool act = qc + 31 >= k0 + warp * 32 && qc < T;  // some (query, key) pair of this warp's rows is on or below the diagonal
+        if (act) {
+          // allowed queries of the chunk for this key: kj <= q < T
+          const int lo = kj - qc, hi = T - qc;
+          uint32_t word = lo <= 0 ? 0xffffffffu : (lo >= 32 ? 0u : ~((1u << lo) - 1u));
+          word &= hi >= 32 ? 0xffffffffu : ((1u << hi) - 1u);
+          if (!key_ok) word = 0u;
+          uint32_t sv[32], dv[32];
+          tmem_ld_32x32(tST + lane_addr + 32 * c, sv);
+          tmem_ld_32x32(tDPT + lane_addr + 32 * c, dv);
+          tmem_ld_wait();
+          if (c == 1) { tc_fence_before(); mbar_arrive(sdp_free); }
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            float pf[8], df[8];
+            const float4 l0 = *reinterpret_cast<const float4*>(sLse + qc + u * 8), l1 = *reinterpret_cast<const float4*>(sLse + qc + u * 8 + 4);
+            const float4 d0 = *reinterpret_cast<const float4*>(sDelta + qc + u * 8), d1 = *reinterpret_cast<const float4*>(sDelta + qc + u * 8 + 4);
+            const float nl[8] = {l0.x, l0.y, l0.z, l0.w, l1.x, l1.y, l1.z, l1.w}, dl[8] = {d0.x, d0.y, d0.z, d0.w, d1.x, d1.y, d1.z, d1.w};
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+              const int col = u * 8 + e;
+              float pe = fast_exp2(fmaf(__uint_as_float(sv[col]), p.scale_log2, nl[e]));
+              pe = (word & (1u << col)) ? pe : 0.f;
+              pf[e] = pe;
+              df[e] = pe * (__uint_as_float(dv[col]) - dl[e]) * p.scale;
+            }
+            at_store_row_unit(pt_tile, r, 4 * c + u, pack_bf16x2(pf[0], pf[1]), pack_bf16x2(pf[2], pf[3]), pack_bf16x2(pf[4], pf[5]),
+                              pack_bf16x2(pf[6], pf[7]));
+            at_store_row_unit(dst_tile, r, 4 * c + u, pack_bf16x2(df[0], df[1]), pack_bf16x2(df[2], df[3]), pack_bf16x2(df[4], df[5]),
+                              pack_bf16x2(df[6], df[7]));
+          }
+        } else {
+          if (c == 1) { tc_fence_before(); mbar_arrive(sdp_free); }
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            at_store_row_unit(pt_tile, r, 4 * c + u, 0u, 0u, 0u, 0u);
+            at_store_row_unit(dst_tile, r, 4 * c + u, 0u, 0u, 0u, 0u);
+          }
+        }
+      }
+      fence_proxy_async();
+      mbar_arrive(pds_full);
+    }
+    mbar_wait(pds_done, (n - 1) & 1);
+    tc_fence_after();
+    bf16* grow = p.dqkv + ((size_t)b * T + kj) * 3 * H + h * AT_D;
+#pragma unroll
+    for (int which = 0; which < 2; ++which) {  // 0: dV -> columns 2H.., 1: dK -> columns H..
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {
+        uint32_t o[32];
+        tmem_ld_32x32((which == 0 ? tDV : tDK) + lane_addr + c * 32, o);
+        tmem_ld_wait();
+        if (kj < T) {
+          bf16* dst = grow + (which == 0 ? 2 * H : H) + c * 32;
+#pragma unroll
+          for (int e = 0; e < 32; e += 8)
+            *reinterpret_cast<uint4*>(dst + e) =
+                make_uint4(pack_bf16x2(__uint_as_float(o[e]), __uint_as_float(o[e + 1])), pack_bf16x2(__uint_as_float(o[e + 2]), __uint_as_float(o[e + 3])),
+                           pack_bf16x2(__uint_as_float(o[e + 4]), __uint_as_float(o[e + 5])), pack_bf16x2(__uint_as_float(o[e + 6]), __uint_as_float(o[e + 7])));
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 4) { tc_fence_after(); tmem_dealloc(tmem_base, 256); }
+}
+
 constexpr int AT_FWD_SMEM = 1024 + AT_TILE128 + 2 * AT_KV_STAGES * AT_TILE64 + 2 * AT_TILE128 + 256 + AT_MAX_CHUNKS * 4;
 
 bool attn_tc_supported(int T, int d) {
@@ -325,7 +732,7 @@ bool attn_tc_supported(int T, int d) {
     const char* e = getenv("DTB_ATTN_LEGACY");
     legacy = (e && e[0] == '1') ? 1 : 0;
   }
-  return !legacy && d == AT_D && T >= 1 && T <= 32 * AT_MAX_CHUNKS;
+  return !legacy && d == AT_D && T >= 1 && T <= AT_MAX_T_BWD;
 }
 
 static int at_maps(const bf16* qkv, int B, int T, int H, CUtensorMap* tm128, CUtensorMap* tm64) {
@@ -354,6 +761,38 @@ int attn_fwd_tc(cudaStream_t stream, const bf16* qkv, const float* mask, int B, 
   dim3 grid((T + 127) / 128, nh, B);
   ProfScope prof(stream, PF_ATTN_FWD, 2.0 * B * nh * (double)T * T * d);
   attn_fwd_tc_kernel<<<grid, AT_THREADS, AT_FWD_SMEM, stream>>>(tmQ, tmKV, p);
+  DTB_CHECK_LAUNCH();
+  return DTB_OK;
+}
+
+constexpr int AT_DQ_SMEM = 1024 + 2 * AT_TILE128 + (AT_DQ_KST + AT_DQ_VST) * AT_TILE64 + 2 * AT_TILE128 + 256 + AT_MAX_CHUNKS * 4;
+constexpr int AT_DKV_SMEM = 1024 + 2 * AT_TILE128 + 4 * AT_TILE64 + 2 * AT_TILE128 + 256 + 2 * AT_MAX_T_BWD * 4;
+
+int attn_bwd_tc(cudaStream_t stream, const bf16* qkv, const float* mask, const bf16* out, const bf16* dout, const float* lse, int B, int T,
+                int nh, int d, bf16* dqkv, float* delta) {
+  DTB_REQUIRE(d == AT_D && T <= AT_MAX_T_BWD, DTB_ERR_UNSUPPORTED, "tcgen05 attention bwd: head_dim %d / T %d unsupported", d, T);
+  const int H = nh * d;
+  CUtensorMap tm128, tm64, tmDO128, tmDO64;
+  DTB_TRY(at_maps(qkv, B, T, H, &tm128, &tm64));
+  DTB_TRY(make_tmap3(&tmDO128, dout, (uint64_t)H, (uint64_t)T, (uint64_t)B, (uint64_t)H, (uint64_t)T * H, 64, 128));
+  DTB_TRY(make_tmap3(&tmDO64, dout, (uint64_t)H, (uint64_t)T, (uint64_t)B, (uint64_t)H, (uint64_t)T * H, 64, 64));
+  AttnTcParams p;
+  memset(&p, 0, sizeof(p));
+  p.T = T; p.nh = nh; p.Kmask = T / 3;
+  p.scale = 1.f / sqrtf((float)d);
+  p.scale_log2 = 1.4426950408889634f * p.scale;
+  p.mask = mask; p.lse_in = lse; p.out_in = out; p.dout = dout; p.dqkv = dqkv; p.delta = delta;
+  static bool attr = false;
+  if (!attr) {
+    DTB_CUDA(cudaFuncSetAttribute(attn_bwd_dq_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_DQ_SMEM));
+    DTB_CUDA(cudaFuncSetAttribute(attn_bwd_dkv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_DKV_SMEM));
+    attr = true;
+  }
+  dim3 grid((T + 127) / 128, nh, B);
+  ProfScope prof(stream, PF_ATTN_BWD, 5.0 * B * nh * (double)T * T * d);
+  attn_bwd_dq_tc_kernel<<<grid, AT_THREADS, AT_DQ_SMEM, stream>>>(tm128, tm64, tmDO128, p);
+  DTB_CHECK_LAUNCH();
+  attn_bwd_dkv_tc_kernel<<<grid, AT_THREADS, AT_DKV_SMEM, stream>>>(tm128, tm64, tmDO64, p);
   DTB_CHECK_LAUNCH();
   return DTB_OK;
 }
