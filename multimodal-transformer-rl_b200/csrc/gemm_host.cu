@@ -7,6 +7,7 @@
 #include <mutex>
 #include <unordered_map>
 #include <string.h>
+#include <stdlib.h>
 
 namespace dtb {
 
@@ -101,17 +102,43 @@ size_t gemm_splitk_workspace_bytes(int M, int N, int K) {
   return (size_t)32 * M * N * sizeof(float);
 }
 
-int gemm_pick_split(int M, int N, int K, int BN) {
-  const int m_tiles = (M + GEMM_BM - 1) / GEMM_BM, n_tiles = (N + BN - 1) / BN;
-  const int kblocks = (K + GEMM_BK - 1) / GEMM_BK;
-  const int tiles = m_tiles * n_tiles;
-  int split = (2 * num_sms() + tiles - 1) / tiles;
+// CTA-pair kernel (256 x 256 tiles, cta_group::2) for problems big enough to fill the 74 SM pairs.
+bool gemm_use_pair(int M, int N, int K) {
+  static int off = -1;
+  if (off < 0) {
+    const char* e = getenv("DTB_GEMM_NO_PAIR");
+    off = (e && e[0] == '1') ? 1 : 0;
+  }
+  if (off) return false;
+  if (M < 512 || N < 256 || N % 128 != 0 || K < 128) return false;
+  const long long tiles = (long long)((M + 255) / 256) * ((N + 255) / 256);
+  const long long kblocks = (K + GEMM_BK - 1) / GEMM_BK;
+  // enough (tile x possible split) work for the 74 pairs
+  return tiles * (kblocks >= 16 ? kblocks / 8 : 1) >= (num_sms() / 2);
+}
+
+// Split-K factor by wave efficiency: work items (tiles x split) should fill whole waves of the `units` concurrent CTAs / pairs.
+static int pick_split_eff(long long tiles, int kblocks, int units) {
   int max_split = kblocks / 8;
   if (max_split < 1) max_split = 1;
-  if (split > max_split) split = max_split;
-  if (split > 32) split = 32;
-  if (split < 1) split = 1;
-  return split;
+  if (max_split > 32) max_split = 32;
+  int best = 1;
+  double best_eff = 0.0;
+  for (int s = 1; s <= max_split; ++s) {
+    const long long items = tiles * s;
+    const long long waves = (items + units - 1) / units;
+    const double eff = (double)items / (double)(waves * units);
+    if (eff > best_eff + 0.02) { best_eff = eff; best = s; }  // prefer the smaller split unless clearly better
+    if (best_eff >= 0.95) break;
+  }
+  return best;
+}
+
+int gemm_pick_split(int M, int N, int K, int BN) {
+  const int kblocks = (K + GEMM_BK - 1) / GEMM_BK;
+  if (gemm_use_pair(M, N, K)) return pick_split_eff((long long)((M + 255) / 256) * ((N + 255) / 256), kblocks, num_sms() / 2);
+  const int m_tiles = (M + GEMM_BM - 1) / GEMM_BM, n_tiles = (N + BN - 1) / BN;
+  return pick_split_eff((long long)m_tiles * n_tiles, kblocks, num_sms());
 }
 
 int gemm_pick_bn(int M, int N, int b_mn_major) {
@@ -140,9 +167,11 @@ int gemm_bf16(cudaStream_t stream, const bf16* A, int lda, int a_mn_major, const
   memset(&p, 0, sizeof(p));
   p.M = M; p.N = N; p.K = K;
   p.a_mn_major = a_mn_major; p.b_mn_major = b_mn_major;
-  p.BN = bn_override > 0 ? bn_override : gemm_pick_bn(M, N, b_mn_major);
+  // bn_override: 0 = automatic; 32..256 = single-CTA kernel with that N tile; 1000 = force the CTA-pair kernel
+  const bool pair = bn_override == 1000 || (bn_override == 0 && gemm_use_pair(M, N, K));
+  p.BN = pair ? GEMM2_BN : (bn_override > 0 ? bn_override : gemm_pick_bn(M, N, b_mn_major));
   DTB_REQUIRE(p.BN % 32 == 0 && p.BN >= 32 && p.BN <= 256 && (!b_mn_major || p.BN % 64 == 0), DTB_ERR_BAD_ARG, "gemm: bad BN %d", p.BN);
-  p.m_tiles = (M + GEMM_BM - 1) / GEMM_BM;
+  p.m_tiles = pair ? (M + 255) / 256 : (M + GEMM_BM - 1) / GEMM_BM;
   p.n_tiles = (N + p.BN - 1) / p.BN;
   const int kblocks = (K + GEMM_BK - 1) / GEMM_BK;
   if (split_k < 1) split_k = 1;
@@ -152,22 +181,28 @@ int gemm_bf16(cudaStream_t stream, const bf16* A, int lda, int a_mn_major, const
   p.ep = ep_in;
   if (p.ep.alpha == 0.f) p.ep.alpha = 1.f;
   if (p.split_k > 1) DTB_REQUIRE(p.ep.partial != nullptr, DTB_ERR_BAD_ARG, "gemm: split-K needs a partial workspace");
-  if (p.split_k == 1 && p.ep.partial) p.split_k = 1;  // single split still writes partial[0]
 
+  const uint32_t b_rows = pair ? 128u : (uint32_t)p.BN;  // a pair CTA stages its own 128-column half of B
   CUtensorMap tmA, tmB;
   if (!a_mn_major) DTB_TRY(make_tmap(&tmA, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda, GEMM_BK, GEMM_BM));
   else             DTB_TRY(make_tmap(&tmA, A, (uint64_t)M, (uint64_t)K, (uint64_t)lda, 64, GEMM_BK));
-  if (!b_mn_major) DTB_TRY(make_tmap(&tmB, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, GEMM_BK, (uint32_t)p.BN));
+  if (!b_mn_major) DTB_TRY(make_tmap(&tmB, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, GEMM_BK, b_rows));
   else             DTB_TRY(make_tmap(&tmB, B, (uint64_t)N, (uint64_t)K, (uint64_t)ldb, 64, GEMM_BK));
 
   if (!g_attr_set) {
     DTB_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_BYTES));
+    DTB_CUDA(cudaFuncSetAttribute(gemm_tcgen05_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM2_SMEM_BYTES));
     g_attr_set = true;
   }
   const int total = p.m_tiles * p.n_tiles * p.split_k;
-  const int grid = total < num_sms() ? total : num_sms();
   ProfScope prof(stream, PF_GEMM, 2.0 * M * N * K);
-  gemm_tcgen05_kernel<<<grid, GEMM_THREADS, GEMM_SMEM_BYTES, stream>>>(tmA, tmB, p);
+  if (pair) {
+    const int npairs = total < num_sms() / 2 ? total : num_sms() / 2;
+    gemm_tcgen05_pair_kernel<<<2 * npairs, GEMM_THREADS, GEMM2_SMEM_BYTES, stream>>>(tmA, tmB, p);
+  } else {
+    const int grid = total < num_sms() ? total : num_sms();
+    gemm_tcgen05_kernel<<<grid, GEMM_THREADS, GEMM_SMEM_BYTES, stream>>>(tmA, tmB, p);
+  }
   DTB_CHECK_LAUNCH();
   return p.split_k;  // >= 1: number of partial slices written when ep.partial != null
 }
@@ -216,7 +251,7 @@ int splitk_reduce(cudaStream_t stream, const float* partial, int splits, int M, 
 // Weight gradient dW[Mout, Nout] = A^T B with both operands read in place (MN-major): A memory [Kred][Mout] (lda),
 // B memory [Kred][Nout] (ldb).  Split-K over the token dimension with fp32 partials reduced in index order (deterministic).
 int gemm_wgrad_split(int Mout, int Nout, int Kred, size_t partial_floats) {
-  const int bn = gemm_pick_bn(Mout, Nout, 1);
+  const int bn = gemm_use_pair(Mout, Nout, Kred) ? GEMM2_BN : gemm_pick_bn(Mout, Nout, 1);
   int split = gemm_pick_split(Mout, Nout, Kred, bn);
   const size_t per = (size_t)Mout * Nout;
   while (split > 1 && per * split > partial_floats) --split;

@@ -24,6 +24,92 @@ constexpr int GEMM_A_STAGE_BYTES = GEMM_BM * GEMM_BK * 2;      // 16 KB
 constexpr int GEMM_B_STAGE_BYTES = GEMM_MAX_BN * GEMM_BK * 2;  // 32 KB
 constexpr int GEMM_SMEM_BYTES = GEMM_STAGES * (GEMM_A_STAGE_BYTES + GEMM_B_STAGE_BYTES) + 1024 /*align*/ + 256 /*barriers*/;
 
+// One 32-column chunk of one accumulator row: bias / activation / act' / residual / stores (or the split-K partial store).
+__device__ __forceinline__ void gemm_epilogue_chunk(const GemmParams& p, const GemmEpilogue& ep, const uint32_t (&v)[32], int row, bool row_ok,
+                                                    int col0, int split) {
+        if (row_ok && col0 < p.N) {
+          const int ncols = min(32, p.N - col0);  // N % 8 == 0 guaranteed by host
+          if (ep.partial) {
+            float* dst = ep.partial + ((size_t)split * p.M + row) * p.N + col0;
+#pragma unroll
+            for (int j = 0; j < 32; j += 4)
+              if (j < ncols)
+                *reinterpret_cast<float4*>(dst + j) = make_float4(__uint_as_float(v[j]), __uint_as_float(v[j + 1]),
+                                                                  __uint_as_float(v[j + 2]), __uint_as_float(v[j + 3]));
+          } else {
+            float f[32];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]) * ep.alpha;
+            if (ep.bias) {
+#pragma unroll
+              for (int j = 0; j < 32; j += 4)
+                if (j < ncols) {
+                  float4 b = ldg_f4(ep.bias + col0 + j);
+                  f[j] += b.x; f[j + 1] += b.y; f[j + 2] += b.z; f[j + 3] += b.w;
+                }
+            }
+            if (ep.out_preact) {
+              bf16* dst = ep.out_preact + (size_t)row * ep.ldo_b + col0;
+#pragma unroll
+              for (int j = 0; j < 32; j += 8)
+                if (j < ncols)
+                  *reinterpret_cast<uint4*>(dst + j) = make_uint4(pack_bf16x2(f[j], f[j + 1]), pack_bf16x2(f[j + 2], f[j + 3]),
+                                                                  pack_bf16x2(f[j + 4], f[j + 5]), pack_bf16x2(f[j + 6], f[j + 7]));
+            }
+            if (ep.act == 1) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
+            } else if (ep.act == 2) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) f[j] = gelu_new_f(f[j]);
+            }
+            if (ep.dact) {
+              const bf16* a = ep.aux + (size_t)row * ep.ldaux + col0;
+#pragma unroll
+              for (int j = 0; j < 32; j += 8)
+                if (j < ncols) {
+                  uint4 u = ldg_u4(a + j);
+                  uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+                  for (int e = 0; e < 4; ++e) {
+                    float2 x = unpack_bf16x2(w[e]);
+                    if (ep.dact == 1) {
+                      f[j + 2 * e] = x.x > 0.f ? f[j + 2 * e] : 0.f;
+                      f[j + 2 * e + 1] = x.y > 0.f ? f[j + 2 * e + 1] : 0.f;
+                    } else {
+                      f[j + 2 * e] *= gelu_new_grad_f(x.x);
+                      f[j + 2 * e + 1] *= gelu_new_grad_f(x.y);
+                    }
+                  }
+                }
+            }
+            if (ep.residual) {
+              const float* r = ep.residual + (size_t)row * ep.ldr + col0;
+#pragma unroll
+              for (int j = 0; j < 32; j += 4)
+                if (j < ncols) {
+                  float4 b = ldg_f4(r + j);
+                  f[j] += b.x; f[j + 1] += b.y; f[j + 2] += b.z; f[j + 3] += b.w;
+                }
+            }
+            if (ep.out_f32) {
+              float* dst = ep.out_f32 + (size_t)row * ep.ldo_f + col0;
+#pragma unroll
+              for (int j = 0; j < 32; j += 4)
+                if (j < ncols) *reinterpret_cast<float4*>(dst + j) = make_float4(f[j], f[j + 1], f[j + 2], f[j + 3]);
+            }
+            if (ep.out_bf16) {
+              bf16* dst = ep.out_bf16 + (size_t)row * ep.ldo_b + col0;
+#pragma unroll
+              for (int j = 0; j < 32; j += 8)
+                if (j < ncols)
+                  *reinterpret_cast<uint4*>(dst + j) = make_uint4(pack_bf16x2(f[j], f[j + 1]), pack_bf16x2(f[j + 2], f[j + 3]),
+                                                                  pack_bf16x2(f[j + 4], f[j + 5]), pack_bf16x2(f[j + 6], f[j + 7]));
+            }
+          }
+        }
+}
+
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmParams p) {
   extern __shared__ uint8_t smem_raw[];
@@ -158,88 +244,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         uint32_t v[32];
         tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + acc * GEMM_MAX_BN + c, v);
         tmem_ld_wait();
-        const int col0 = n0 + c;
-        if (row_ok && col0 < p.N) {
-          const int ncols = min(32, p.N - col0);  // N % 8 == 0 guaranteed by host
-          if (ep.partial) {
-            float* dst = ep.partial + ((size_t)split * p.M + row) * p.N + col0;
-#pragma unroll
-            for (int j = 0; j < 32; j += 4)
-              if (j < ncols)
-                *reinterpret_cast<float4*>(dst + j) = make_float4(__uint_as_float(v[j]), __uint_as_float(v[j + 1]),
-                                                                  __uint_as_float(v[j + 2]), __uint_as_float(v[j + 3]));
-          } else {
-            float f[32];
-#pragma unroll
-            for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]) * ep.alpha;
-            if (ep.bias) {
-#pragma unroll
-              for (int j = 0; j < 32; j += 4)
-                if (j < ncols) {
-                  float4 b = ldg_f4(ep.bias + col0 + j);
-                  f[j] += b.x; f[j + 1] += b.y; f[j + 2] += b.z; f[j + 3] += b.w;
-                }
-            }
-            if (ep.out_preact) {
-              bf16* dst = ep.out_preact + (size_t)row * ep.ldo_b + col0;
-#pragma unroll
-              for (int j = 0; j < 32; j += 8)
-                if (j < ncols)
-                  *reinterpret_cast<uint4*>(dst + j) = make_uint4(pack_bf16x2(f[j], f[j + 1]), pack_bf16x2(f[j + 2], f[j + 3]),
-                                                                  pack_bf16x2(f[j + 4], f[j + 5]), pack_bf16x2(f[j + 6], f[j + 7]));
-            }
-            if (ep.act == 1) {
-#pragma unroll
-              for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
-            } else if (ep.act == 2) {
-#pragma unroll
-              for (int j = 0; j < 32; ++j) f[j] = gelu_new_f(f[j]);
-            }
-            if (ep.dact) {
-              const bf16* a = ep.aux + (size_t)row * ep.ldaux + col0;
-#pragma unroll
-              for (int j = 0; j < 32; j += 8)
-                if (j < ncols) {
-                  uint4 u = ldg_u4(a + j);
-                  uint32_t w[4] = {u.x, u.y, u.z, u.w};
-#pragma unroll
-                  for (int e = 0; e < 4; ++e) {
-                    float2 x = unpack_bf16x2(w[e]);
-                    if (ep.dact == 1) {
-                      f[j + 2 * e] = x.x > 0.f ? f[j + 2 * e] : 0.f;
-                      f[j + 2 * e + 1] = x.y > 0.f ? f[j + 2 * e + 1] : 0.f;
-                    } else {
-                      f[j + 2 * e] *= gelu_new_grad_f(x.x);
-                      f[j + 2 * e + 1] *= gelu_new_grad_f(x.y);
-                    }
-                  }
-                }
-            }
-            if (ep.residual) {
-              const float* r = ep.residual + (size_t)row * ep.ldr + col0;
-#pragma unroll
-              for (int j = 0; j < 32; j += 4)
-                if (j < ncols) {
-                  float4 b = ldg_f4(r + j);
-                  f[j] += b.x; f[j + 1] += b.y; f[j + 2] += b.z; f[j + 3] += b.w;
-                }
-            }
-            if (ep.out_f32) {
-              float* dst = ep.out_f32 + (size_t)row * ep.ldo_f + col0;
-#pragma unroll
-              for (int j = 0; j < 32; j += 4)
-                if (j < ncols) *reinterpret_cast<float4*>(dst + j) = make_float4(f[j], f[j + 1], f[j + 2], f[j + 3]);
-            }
-            if (ep.out_bf16) {
-              bf16* dst = ep.out_bf16 + (size_t)row * ep.ldo_b + col0;
-#pragma unroll
-              for (int j = 0; j < 32; j += 8)
-                if (j < ncols)
-                  *reinterpret_cast<uint4*>(dst + j) = make_uint4(pack_bf16x2(f[j], f[j + 1]), pack_bf16x2(f[j + 2], f[j + 3]),
-                                                                  pack_bf16x2(f[j + 4], f[j + 5]), pack_bf16x2(f[j + 6], f[j + 7]));
-            }
-          }
-        }
+        gemm_epilogue_chunk(p, ep, v, row, row_ok, n0 + c, split);
       }
       tc_fence_before();
       __syncwarp();
@@ -253,6 +258,248 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   if (warp == 2) {
     tc_fence_after();
     tmem_dealloc(tmem_base, 512);
+  }
+}
+
+
+// ================================================================================================================================
+// CTA-pair variant (cta_group::2): two CTAs of a cluster (the two SMs of a TPC) compute one 256 x 256 tile.  Each CTA stages its
+// own 128 rows of A and its own 128-column half of B (32 KB per k-block instead of 48 KB), the leader CTA's single thread issues
+// tcgen05.mma.cta_group::2 (M = 256: rows 0-127 accumulate in the leader's TMEM, rows 128-255 in the peer's), and both tensor cores
+// read both halves of B.  Halves the shared-memory fill per flop, which is what bounds the single-CTA kernel on large GEMMs.
+//   full[s]   : leader only; expect_tx = both CTAs' bytes (the peer's TMA signals the leader's barrier)
+//   empty[s]  : one per CTA, arrived by the leader's tcgen05.commit multicast to both CTAs
+//   tfull[a]  : one per CTA, same multicast commit;   tempty[a] : leader only, 8 arrivals (4 epilogue warps x 2 CTAs, remote for the peer)
+// ================================================================================================================================
+constexpr int GEMM2_STAGES = 6;
+constexpr int GEMM2_BN = 256;
+constexpr int GEMM2_A_BYTES = 128 * GEMM_BK * 2;  // 16 KB
+constexpr int GEMM2_B_BYTES = 128 * GEMM_BK * 2;  // 16 KB: this CTA's half of the 256 columns
+constexpr int GEMM2_SMEM_BYTES = GEMM2_STAGES * (GEMM2_A_BYTES + GEMM2_B_BYTES) + 1024 + 256;
+
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t mapa_rank(uint32_t saddr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(saddr), "r"(rank));
+  return r;
+}
+// TMA load issued by either CTA of the pair; the transaction bytes are credited to the LEADER's mbarrier (peer bit cleared).
+__device__ __forceinline__ void tma_load_2d_pair(void* smem_dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
+          smem_u32(smem_dst)),
+      "l"(reinterpret_cast<uint64_t>(m)), "r"(mapa_rank(smem_u32(bar), 0)), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void umma_bf16_pair(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// arrive (once all prior MMAs of this thread retire) on the barrier at this smem offset in BOTH CTAs of the pair
+__device__ __forceinline__ void umma_commit_pair(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(smem_u32(bar)),
+               "h"((uint16_t)3)
+               : "memory");
+}
+// arrive on the barrier at this smem offset in CTA `rank` of the cluster
+__device__ __forceinline__ void mbar_arrive_cluster(uint64_t* bar, uint32_t rank) {
+  asm volatile(
+      "{\n\t.reg .b32 ra;\n\t"
+      "mapa.shared::cluster.u32 ra, %0, %1;\n\t"
+      "mbarrier.arrive.release.cluster.shared::cluster.b64 _, [ra];\n\t}" ::"r"(smem_u32(bar)),
+      "r"(rank)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_alloc_pair(uint32_t* dst_smem, uint32_t ncols) {
+  asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(dst_smem)), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void tmem_relinquish_pair() {
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc_pair(uint32_t taddr, uint32_t ncols) {
+  asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+// wait with cluster-scope acquire (the barrier is arrived on by the peer CTA's threads / tensor core)
+__device__ __forceinline__ void mbar_wait_cluster(uint64_t* bar, uint32_t parity) {
+  long long t0 = 0;
+  for (;;) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+    if (ok) return;
+    if (t0 == 0) t0 = clock64();
+    else if (clock64() - t0 > 4000000000LL) {
+      printf("dtb200: cluster mbarrier wait timeout (block %d thread %d)\n", blockIdx.x, threadIdx.x);
+      __trap();
+    }
+  }
+}
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
+gemm_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smA = smem;
+  uint8_t* smB = smem + GEMM2_STAGES * GEMM2_A_BYTES;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + GEMM2_STAGES * (GEMM2_A_BYTES + GEMM2_B_BYTES));
+  uint64_t* full_bar = bars;                      // [STAGES]
+  uint64_t* empty_bar = bars + GEMM2_STAGES;      // [STAGES]
+  uint64_t* tfull_bar = bars + 2 * GEMM2_STAGES;  // [2]
+  uint64_t* tempty_bar = tfull_bar + 2;           // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const bool leader = rank == 0;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < GEMM2_STAGES; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&tfull_bar[s], 1);
+      mbar_init(&tempty_bar[s], 8);  // 4 epilogue warps x 2 CTAs
+    }
+    fence_mbar_init();
+  }
+  if (warp == 2) {
+    tmem_alloc_pair(tmem_slot, 512);
+    tmem_relinquish_pair();
+  }
+  tc_fence_before();
+  cluster_sync_all();  // both CTAs' barriers are initialised before any remote arrive / TMA credit
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  // pair tiles: 256 x 256; both CTAs of a pair walk the same tile sequence
+  const int pair = blockIdx.x >> 1, npairs = gridDim.x >> 1;
+  const int total_tiles = p.m_tiles * p.n_tiles * p.split_k;  // m_tiles counts 256-row tiles here
+  const int kblocks_total = (p.K + GEMM_BK - 1) / GEMM_BK;
+  const uint32_t stage_tx = 2u * (GEMM2_A_BYTES + GEMM2_B_BYTES);
+
+  if (warp == 0) {
+    // ===================== TMA producer (one per CTA) =====================
+    if (lane == 0) {
+      uint32_t stage = 0, phase = 0;
+      for (int t = pair; t < total_tiles; t += npairs) {
+        const int split = t / (p.m_tiles * p.n_tiles);
+        const int mn = t - split * (p.m_tiles * p.n_tiles);
+        const int m0 = (mn / p.n_tiles) * 256 + (int)rank * 128;
+        const int n0 = (mn % p.n_tiles) * GEMM2_BN + (int)rank * 128;
+        const int kb0 = split * p.kb_per_split;
+        const int kb1 = min(kb0 + p.kb_per_split, kblocks_total);
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait_cluster(&empty_bar[stage], phase ^ 1);
+          if (leader) mbar_arrive_expect_tx(&full_bar[stage], stage_tx);
+          uint8_t* a_dst = smA + stage * GEMM2_A_BYTES;
+          uint8_t* b_dst = smB + stage * GEMM2_B_BYTES;
+          const int k0 = kb * GEMM_BK;
+          if (!p.a_mn_major) {
+            tma_load_2d_pair(a_dst, &tmA, &full_bar[stage], k0, m0);
+          } else {
+            tma_load_2d_pair(a_dst, &tmA, &full_bar[stage], m0, k0);
+            tma_load_2d_pair(a_dst + GEMM_BK * 128, &tmA, &full_bar[stage], m0 + 64, k0);
+          }
+          if (!p.b_mn_major) {
+            tma_load_2d_pair(b_dst, &tmB, &full_bar[stage], k0, n0);
+          } else {
+            tma_load_2d_pair(b_dst, &tmB, &full_bar[stage], n0, k0);
+            tma_load_2d_pair(b_dst + GEMM_BK * 128, &tmB, &full_bar[stage], n0 + 64, k0);
+          }
+          if (++stage == GEMM2_STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer: the leader CTA's single thread drives both tensor cores =====================
+    if (leader && lane == 0) {
+      const uint32_t idesc = make_idesc_bf16(256, GEMM2_BN, p.a_mn_major, p.b_mn_major);
+      const uint32_t a_lbo = p.a_mn_major ? GEMM_BK * 128 : 16;
+      const uint32_t b_lbo = p.b_mn_major ? GEMM_BK * 128 : 16;
+      const uint32_t a_kstep = p.a_mn_major ? 16 * 128 : 32;
+      const uint32_t b_kstep = p.b_mn_major ? 16 * 128 : 32;
+      uint32_t stage = 0, phase = 0;
+      uint32_t acc = 0, acc_phase = 0;
+      for (int t = pair; t < total_tiles; t += npairs) {
+        const int split = t / (p.m_tiles * p.n_tiles);
+        const int kb0 = split * p.kb_per_split;
+        const int kb1 = min(kb0 + p.kb_per_split, kblocks_total);
+        mbar_wait_cluster(&tempty_bar[acc], acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * GEMM_MAX_BN;
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait_cluster(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t a_addr = smem_u32(smA + stage * GEMM2_A_BYTES);
+          const uint32_t b_addr = smem_u32(smB + stage * GEMM2_B_BYTES);
+#pragma unroll
+          for (int kk = 0; kk < GEMM_BK / 16; ++kk) {
+            const uint64_t adesc = make_smem_desc_sw128(a_addr + kk * a_kstep, a_lbo, 1024);
+            const uint64_t bdesc = make_smem_desc_sw128(b_addr + kk * b_kstep, b_lbo, 1024);
+            umma_bf16_pair(d_tmem, adesc, bdesc, idesc, (kb > kb0 || kk > 0) ? 1u : 0u);
+          }
+          umma_commit_pair(&empty_bar[stage]);
+          if (++stage == GEMM2_STAGES) { stage = 0; phase ^= 1; }
+        }
+        umma_commit_pair(&tfull_bar[acc]);
+        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+      }
+    }
+  } else if (warp >= 4) {
+    // ===================== epilogue: each CTA drains its own 128 rows =====================
+    const int q = warp & 3;
+    const GemmEpilogue& ep = p.ep;
+    uint32_t acc = 0, acc_phase = 0;
+    for (int t = pair; t < total_tiles; t += npairs) {
+      const int split = t / (p.m_tiles * p.n_tiles);
+      const int mn = t - split * (p.m_tiles * p.n_tiles);
+      const int m0 = (mn / p.n_tiles) * 256 + (int)rank * 128;
+      const int n0 = (mn % p.n_tiles) * GEMM2_BN;
+      const int row = m0 + q * 32 + lane;
+      const bool row_ok = row < p.M;
+      mbar_wait_cluster(&tfull_bar[acc], acc_phase);
+      tc_fence_after();
+      for (int c = 0; c < GEMM2_BN; c += 32) {
+        uint32_t v[32];
+        tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + acc * GEMM_MAX_BN + c, v);
+        tmem_ld_wait();
+        gemm_epilogue_chunk(p, ep, v, row, row_ok, n0 + c, split);
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(&tempty_bar[acc], 0);
+      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+    }
+  }
+
+  tc_fence_before();
+  cluster_sync_all();  // neither CTA may exit (or free TMEM) while the other can still touch its smem / barriers / TMEM
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc_pair(tmem_base, 512);
   }
 }
 

@@ -119,3 +119,27 @@ def test_gemm_rejects_bad_args(cuda_device):
     A = _rand((128, 64), cuda_device, 1)
     with pytest.raises(_lib.DtbError):
         _lib.gemm_bf16(A, A, 128, 60, 64, out_f32=torch.empty((128, 60), device=cuda_device))
+
+
+@pytest.mark.parametrize("a_mn,b_mn", [(False, False), (False, True), (True, True), (True, False)])
+@pytest.mark.parametrize("M,N,K,split", [(512, 256, 128, 1), (1000, 768, 320, 1), (2048, 512, 1024, 4), (600, 384, 4096, 7)])
+def test_gemm_cta_pair(cuda_device, a_mn, b_mn, M, N, K, split):
+    """cta_group::2 kernel (bn=1000 forces it): 256 x 256 tiles over two SMs, every operand major, ragged M / N tails, split-K."""
+    from mtrl_b200 import _lib
+
+    A = _rand((K, M) if a_mn else (M, K), cuda_device, 21)
+    B = _rand((K, N) if b_mn else (N, K), cuda_device, 22)
+    ref = (A.float().t() if a_mn else A.float()) @ (B.float() if b_mn else B.float().t())
+    out = torch.full((M, N), float("nan"), device=cuda_device, dtype=torch.float32)
+    if split == 1:
+        bias = torch.randn(N, device=cuda_device)
+        outb = torch.zeros((M, N), device=cuda_device, dtype=torch.bfloat16)
+        _lib.gemm_bf16(A, B, M, N, K, a_mn_major=a_mn, b_mn_major=b_mn, bias=bias, out_f32=out, out_bf16=outb, bn=1000)
+        torch.cuda.synchronize()
+        assert rel_err(out, ref + bias) < 2e-3
+        assert rel_err(outb, ref + bias) < 6e-3
+    else:
+        part = torch.empty((split, M, N), device=cuda_device, dtype=torch.float32)
+        _lib.gemm_bf16(A, B, M, N, K, a_mn_major=a_mn, b_mn_major=b_mn, out_f32=out, partial=part, split_k=split, bn=1000)
+        torch.cuda.synchronize()
+        assert rel_err(out, ref) < 2e-3
