@@ -425,6 +425,54 @@ def measure_roofline(args, wl, ctx, reps=5):
             "families": sorted(fams, key=lambda f: -f["ms_per_step"])}
 
 
+def measure_get_action(wl, ctx, calls=300, warmup=50):
+    """BASELINE.json's second metric: get_action latency at B = 1 with a full K-step history, through the public API
+    (wall clock, one stream sync per call, p50 / p90 / p99 in microseconds)."""
+    model, dev, K = ctx["model"], ctx["dev"], wl["K"]
+    b = make_batch(wl, 1, seed=4321)
+    args = []
+    if wl["enc"] is None:
+        args.append(b["states"][0].to(dev))
+    else:
+        args += [b["frames"][0].to(dev), b["audio"][0].to(dev)]
+    args += [b["actions"][0].to(dev), torch.zeros(K, device=dev), b["rtg"][0].to(dev), b["timesteps"][0].to(dev)]
+    lat = []
+    for i in range(warmup + calls):
+        torch.cuda.synchronize(dev)
+        t0 = time.perf_counter()
+        a = model.get_action(*args)
+        torch.cuda.current_stream(dev).synchronize()
+        if i >= warmup:
+            lat.append((time.perf_counter() - t0) * 1e6)
+    lat.sort()
+    pick = lambda q: lat[min(len(lat) - 1, int(q * len(lat)))]
+    return {"p50_us": pick(0.5), "p90_us": pick(0.9), "p99_us": pick(0.99), "calls": calls, "warmup": warmup, "history": K,
+            "action_dim": int(a.numel()), "how": "wall clock around model.get_action(...) + stream sync, inputs resident on the device"}
+
+
+def other_workloads(args, skip):
+    """Short device-resident runs of the other single-GPU configs of BASELINE.json (each in a fresh subprocess so its workspace is
+    released): tokens/s, algorithmic TFLOP/s and the dominant kernel's roofline line."""
+    out = {}
+    for name in ("c1", "c3", "c4"):
+        if name == skip:
+            continue
+        cmd = [sys.executable, os.path.abspath(__file__), "--workload", name, "--steps", "10" if name == "c4" else "30", "--warmup", "3",
+               "--no-cpu-baseline", "--no-extras"]
+        try:
+            r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+            d = json.loads(r.stdout.strip().splitlines()[-1])
+            rf = d.get("roofline") or {}
+            out[name] = {"workload": d["config"]["workload"], "value": d["value"], "unit": d["unit"], "ms_per_step": d["ms_per_step"],
+                         "e2e": d["e2e"]["value"], "algorithmic_tflops_per_s": d["algorithmic_tflops_per_s"], "launches_per_step": d["launches_per_step"],
+                         "get_action": d.get("get_action"),
+                         "roofline": {k: rf.get(k) for k in ("kernel", "bound", "achieved", "peak", "unit", "frac")},
+                         "families": [{k: f.get(k) for k in ("kernel", "ms_per_step", "achieved", "unit", "frac")} for f in rf.get("families", [])[:6]]}
+        except Exception as e:  # noqa: BLE001
+            out[name] = {"error": str(e)[:200]}
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -438,6 +486,7 @@ def main():
     ap.add_argument("--bucket-mb", type=int, default=8)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-roofline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the other-workload summaries (c1 / c3 / c4) appended to the default line")
     args = ap.parse_args()
     wl = dict(WORKLOADS[args.workload])
     if args.batch:
@@ -467,14 +516,26 @@ def main():
         torch.cuda.set_device(local_rank)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     res, ctx = run_ours(args, wl, rank, world, local_rank)
+    if not args.no_roofline:
+        # every rank runs it (the profiled steps contain the gradient all-reduce at N > 1: a collective on rank 0 alone would hang)
+        try:
+            roof = measure_roofline(args, wl, ctx)
+        except Exception as e:  # noqa: BLE001
+            roof = {"error": str(e)}
+        if rank == 0:
+            res["roofline"] = roof
     if rank == 0:
-        if not args.no_roofline:
+        if world == 1:
             try:
-                res["roofline"] = measure_roofline(args, wl, ctx)
+                res["get_action"] = measure_get_action(wl, ctx)
             except Exception as e:  # noqa: BLE001
-                res["roofline"] = {"error": str(e)}
+                res["get_action"] = {"error": str(e)[:200]}
         if world == 1 and not args.no_cpu_baseline:
             res["cpu_baseline"] = run_cpu(wl, 3, 1, budget_s=20.0)
+        if world == 1 and not args.no_extras:
+            del ctx  # release this workload's device memory before the sub-runs
+            torch.cuda.empty_cache()
+            res["other_workloads"] = other_workloads(args, args.workload)
         print(json.dumps(res), flush=True)
     if world > 1:
         dist.barrier()
