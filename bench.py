@@ -215,7 +215,7 @@ def run_ours(args, wl, rank, world, local_rank):
 
     from mtrl_b200.pipeline import HostBatchPipeline
 
-    graphed = world == 1 and not args.no_graph
+    graphed = not args.no_graph  # NCCL all-reduces on the communication stream are captured into the step's graph too
     try:
         pipe = HostBatchPipeline(make_step_for, pinned, dev, use_graph=graphed, warmup=max(args.warmup, 3))
     except Exception as e:  # noqa: BLE001
