@@ -198,7 +198,7 @@ int gemm_bf16(cudaStream_t stream, const bf16* A, int lda, int a_mn_major, const
   ProfScope prof(stream, PF_GEMM, 2.0 * M * N * K);
   if (pair) {
     const int npairs = total < num_sms() / 2 ? total : num_sms() / 2;
-    gemm_tcgen05_pair_kernel<<<2 * npairs, GEMM_THREADS, GEMM2_SMEM_BYTES, stream>>>(tmA, tmB, p);
+    gemm_tcgen05_pair_kernel<<<2 * npairs, GEMM2_THREADS, GEMM2_SMEM_BYTES, stream>>>(tmA, tmB, p);
   } else {
     const int grid = total < num_sms() ? total : num_sms();
     gemm_tcgen05_kernel<<<grid, GEMM_THREADS, GEMM_SMEM_BYTES, stream>>>(tmA, tmB, p);

@@ -262,6 +262,152 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 }
 
 
+
+// ---- staged epilogue (CTA-pair kernel): every global access of the epilogue is warp-coalesced --------------------------------------
+// A warp owns 32 accumulator rows (TMEM lanes) x 32 columns per chunk, one row per thread.  Row-per-thread global accesses touch 32
+// different 128-byte lines per instruction, which made the epilogue (not the tensor pipe) the bound of the forward / dgrad GEMMs.
+// Here every tile that enters or leaves the thread-owns-a-row layout is transposed through a per-warp shared-memory buffer
+// (32 rows x 36 words: 16-byte aligned rows, conflict-free for 128-bit accesses in both directions), so a load / store instruction
+// covers 4 whole fp32 lines (or 8 half lines of bf16).
+constexpr int EPI_LD = 36;                        // staging row stride in 32-bit words
+constexpr int EPI_WARP_WORDS = 32 * EPI_LD;       // 4608 B per warp
+constexpr int EPI_LDH = 20;                       // bf16 staging: 32 columns = 16 words (+4 pad) per row
+
+__device__ __forceinline__ void sts128(uint32_t* p, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  *reinterpret_cast<uint4*>(p) = make_uint4(a, b, c, d);
+}
+// thread-owns-row fp32 [32] -> staging -> coalesced fp32 global rows
+__device__ __forceinline__ void epi_write_f32(uint32_t* st, int lane, const float (&f)[32], float* dst, int ld, int row0, int M, int col0,
+                                              int ncols) {
+#pragma unroll
+  for (int j = 0; j < 32; j += 4)
+    sts128(st + lane * EPI_LD + j, __float_as_uint(f[j]), __float_as_uint(f[j + 1]), __float_as_uint(f[j + 2]), __float_as_uint(f[j + 3]));
+  __syncwarp();
+  const int cc = 4 * (lane & 7);
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int rr = i * 4 + (lane >> 3);
+    const uint4 v = *reinterpret_cast<const uint4*>(st + rr * EPI_LD + cc);
+    if (row0 + rr < M && cc < ncols) *reinterpret_cast<uint4*>(dst + (size_t)(row0 + rr) * ld + col0 + cc) = v;
+  }
+  __syncwarp();
+}
+// thread-owns-row fp32 [32] -> bf16 -> staging -> coalesced bf16 global rows
+__device__ __forceinline__ void epi_write_bf16(uint32_t* st, int lane, const float (&f)[32], bf16* dst, int ld, int row0, int M, int col0,
+                                               int ncols) {
+#pragma unroll
+  for (int j = 0; j < 32; j += 8)
+    sts128(st + lane * EPI_LDH + j / 2, pack_bf16x2(f[j], f[j + 1]), pack_bf16x2(f[j + 2], f[j + 3]), pack_bf16x2(f[j + 4], f[j + 5]),
+           pack_bf16x2(f[j + 6], f[j + 7]));
+  __syncwarp();
+  const int piece = lane & 3;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int rr = i * 8 + (lane >> 2);
+    const uint4 v = *reinterpret_cast<const uint4*>(st + rr * EPI_LDH + piece * 4);
+    if (row0 + rr < M && piece * 8 < ncols) *reinterpret_cast<uint4*>(dst + (size_t)(row0 + rr) * ld + col0 + piece * 8) = v;
+  }
+  __syncwarp();
+}
+// coalesced global loads of a [32 rows x 32 cols] block, issued early (registers), landed in the thread-owns-row layout later
+struct EpiLoadF32 { uint4 v[8]; };
+struct EpiLoadBf16 { uint4 v[4]; };
+__device__ __forceinline__ void epi_issue_f32(EpiLoadF32& L, int lane, const float* src, int ld, int row0, int M, int col0, int ncols) {
+  const int cc = 4 * (lane & 7);
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int rr = i * 4 + (lane >> 3);
+    L.v[i] = (row0 + rr < M && cc < ncols) ? ldg_u4(src + (size_t)(row0 + rr) * ld + col0 + cc) : make_uint4(0, 0, 0, 0);
+  }
+}
+__device__ __forceinline__ void epi_land_f32(const EpiLoadF32& L, uint32_t* st, int lane, float (&r)[32]) {
+  const int cc = 4 * (lane & 7);
+#pragma unroll
+  for (int i = 0; i < 8; ++i) *reinterpret_cast<uint4*>(st + (i * 4 + (lane >> 3)) * EPI_LD + cc) = L.v[i];
+  __syncwarp();
+#pragma unroll
+  for (int j = 0; j < 32; j += 4) {
+    const uint4 v = *reinterpret_cast<const uint4*>(st + lane * EPI_LD + j);
+    r[j] = __uint_as_float(v.x); r[j + 1] = __uint_as_float(v.y); r[j + 2] = __uint_as_float(v.z); r[j + 3] = __uint_as_float(v.w);
+  }
+  __syncwarp();
+}
+__device__ __forceinline__ void epi_issue_bf16(EpiLoadBf16& L, int lane, const bf16* src, int ld, int row0, int M, int col0, int ncols) {
+  const int piece = lane & 3;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int rr = i * 8 + (lane >> 2);
+    L.v[i] = (row0 + rr < M && piece * 8 < ncols) ? ldg_u4(src + (size_t)(row0 + rr) * ld + col0 + piece * 8) : make_uint4(0, 0, 0, 0);
+  }
+}
+__device__ __forceinline__ void epi_land_bf16(const EpiLoadBf16& L, uint32_t* st, int lane, float (&r)[32]) {
+  const int piece = lane & 3;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) *reinterpret_cast<uint4*>(st + (i * 8 + (lane >> 2)) * EPI_LDH + piece * 4) = L.v[i];
+  __syncwarp();
+#pragma unroll
+  for (int j = 0; j < 32; j += 8) {
+    const uint4 v = *reinterpret_cast<const uint4*>(st + lane * EPI_LDH + j / 2);
+    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const float2 x = unpack_bf16x2(w[e]);
+      r[j + 2 * e] = x.x; r[j + 2 * e + 1] = x.y;
+    }
+  }
+  __syncwarp();
+}
+
+
+// One 32-row x 32-column chunk of a warp, staged: `v` = this thread's accumulator row, row0 = first row of the warp's 32 rows.
+// `bias_lane` = bias[col0 + lane] (loaded early by the caller), `Lr` / `La` = the residual / aux blocks issued early.
+__device__ __forceinline__ void gemm_epilogue_chunk_staged(const GemmParams& p, const GemmEpilogue& ep, const uint32_t (&v)[32], uint32_t* st,
+                                                           int lane, int row0, int col0, int split, float bias_lane, const EpiLoadF32& Lr,
+                                                           const EpiLoadBf16& La) {
+  if (col0 >= p.N) return;  // warp-uniform
+  const int ncols = min(32, p.N - col0);
+  float f[32];
+  if (ep.partial) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
+    epi_write_f32(st, lane, f, ep.partial + (size_t)split * p.M * p.N, p.N, row0, p.M, col0, ncols);
+    return;
+  }
+#pragma unroll
+  for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]) * ep.alpha;
+  if (ep.bias) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) f[j] += __shfl_sync(0xffffffffu, bias_lane, j);
+  }
+  if (ep.out_preact) epi_write_bf16(st, lane, f, ep.out_preact, ep.ldo_b, row0, p.M, col0, ncols);
+  if (ep.act == 1) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
+  } else if (ep.act == 2) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) f[j] = gelu_new_f(f[j]);
+  }
+  if (ep.dact) {
+    float a[32];
+    epi_land_bf16(La, st, lane, a);
+    if (ep.dact == 1) {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) f[j] = a[j] > 0.f ? f[j] : 0.f;
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) f[j] *= gelu_new_grad_f(a[j]);
+    }
+  }
+  if (ep.residual) {
+    float r[32];
+    epi_land_f32(Lr, st, lane, r);
+#pragma unroll
+    for (int j = 0; j < 32; ++j) f[j] += r[j];
+  }
+  if (ep.out_f32) epi_write_f32(st, lane, f, ep.out_f32, ep.ldo_f, row0, p.M, col0, ncols);
+  if (ep.out_bf16) epi_write_bf16(st, lane, f, ep.out_bf16, ep.ldo_b, row0, p.M, col0, ncols);
+}
+
 // ================================================================================================================================
 // CTA-pair variant (cta_group::2): two CTAs of a cluster (the two SMs of a TPC) compute one 256 x 256 tile.  Each CTA stages its
 // own 128 rows of A and its own 128-column half of B (32 KB per k-block instead of 48 KB), the leader CTA's single thread issues
@@ -271,11 +417,13 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 //   empty[s]  : one per CTA, arrived by the leader's tcgen05.commit multicast to both CTAs
 //   tfull[a]  : one per CTA, same multicast commit;   tempty[a] : leader only, 8 arrivals (4 epilogue warps x 2 CTAs, remote for the peer)
 // ================================================================================================================================
-constexpr int GEMM2_STAGES = 6;
+constexpr int GEMM2_STAGES = 5;
 constexpr int GEMM2_BN = 256;
+constexpr int GEMM2_THREADS = 384;  // warp0 TMA, warp1 MMA, warp2 TMEM alloc, warp3 idle, warps 4-11 epilogue (2 per TMEM lane quadrant)
+constexpr int GEMM2_EPI_WARPS = 8;
 constexpr int GEMM2_A_BYTES = 128 * GEMM_BK * 2;  // 16 KB
 constexpr int GEMM2_B_BYTES = 128 * GEMM_BK * 2;  // 16 KB: this CTA's half of the 256 columns
-constexpr int GEMM2_SMEM_BYTES = GEMM2_STAGES * (GEMM2_A_BYTES + GEMM2_B_BYTES) + 1024 + 256;
+constexpr int GEMM2_SMEM_BYTES = GEMM2_STAGES * (GEMM2_A_BYTES + GEMM2_B_BYTES) + 1024 + 256 + GEMM2_EPI_WARPS * EPI_WARP_WORDS * 4;
 
 __device__ __forceinline__ uint32_t cluster_ctarank() {
   uint32_t r;
@@ -352,7 +500,7 @@ __device__ __forceinline__ void mbar_wait_cluster(uint64_t* bar, uint32_t parity
   }
 }
 
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM2_THREADS, 1)
 gemm_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -364,6 +512,7 @@ gemm_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
   uint64_t* tfull_bar = bars + 2 * GEMM2_STAGES;  // [2]
   uint64_t* tempty_bar = tfull_bar + 2;           // [2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+  uint32_t* epi_stage = reinterpret_cast<uint32_t*>(smem + GEMM2_STAGES * (GEMM2_A_BYTES + GEMM2_B_BYTES) + 256);  // [8 warps][32 x 36]
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -381,7 +530,7 @@ gemm_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(&tfull_bar[s], 1);
-      mbar_init(&tempty_bar[s], 8);  // 4 epilogue warps x 2 CTAs
+      mbar_init(&tempty_bar[s], 2 * GEMM2_EPI_WARPS);  // epilogue warps of both CTAs
     }
     fence_mbar_init();
   }
@@ -469,24 +618,40 @@ gemm_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
       }
     }
   } else if (warp >= 4) {
-    // ===================== epilogue: each CTA drains its own 128 rows =====================
-    const int q = warp & 3;
+    // ===================== epilogue: each CTA drains its own 128 rows; two warps per TMEM lane quadrant split the columns ==========
+    const int q = warp & 3, half = (warp - 4) >> 2;
     const GemmEpilogue& ep = p.ep;
+    uint32_t* st = epi_stage + (warp - 4) * EPI_WARP_WORDS;
     uint32_t acc = 0, acc_phase = 0;
     for (int t = pair; t < total_tiles; t += npairs) {
       const int split = t / (p.m_tiles * p.n_tiles);
       const int mn = t - split * (p.m_tiles * p.n_tiles);
       const int m0 = (mn / p.n_tiles) * 256 + (int)rank * 128;
       const int n0 = (mn % p.n_tiles) * GEMM2_BN;
-      const int row = m0 + q * 32 + lane;
-      const bool row_ok = row < p.M;
+      const int row0 = m0 + q * 32;
+      // chunk i of this warp covers columns n0 + 32 * (half + 2 i): the first chunk's operands are fetched before the accumulator is ready
+      EpiLoadF32 Lr;
+      EpiLoadBf16 La;
+      float bias_lane = 0.f;
+      auto prefetch = [&](int col0) {
+        if (ep.partial || col0 >= p.N) return;
+        const int ncols = min(32, p.N - col0);
+        if (ep.bias) bias_lane = lane < ncols ? __ldg(ep.bias + col0 + lane) : 0.f;
+        if (ep.residual) epi_issue_f32(Lr, lane, ep.residual, ep.ldr, row0, p.M, col0, ncols);
+        if (ep.dact) epi_issue_bf16(La, lane, ep.aux, ep.ldaux, row0, p.M, col0, ncols);
+      };
+      prefetch(n0 + 32 * half);
       mbar_wait_cluster(&tfull_bar[acc], acc_phase);
       tc_fence_after();
-      for (int c = 0; c < GEMM2_BN; c += 32) {
+      for (int c = 32 * half; c < GEMM2_BN; c += 64) {
         uint32_t v[32];
         tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + acc * GEMM_MAX_BN + c, v);
         tmem_ld_wait();
-        gemm_epilogue_chunk(p, ep, v, row, row_ok, n0 + c, split);
+        const EpiLoadF32 Lr_cur = Lr;
+        const EpiLoadBf16 La_cur = La;
+        const float bias_cur = bias_lane;
+        if (c + 64 < GEMM2_BN) prefetch(n0 + c + 64);  // next chunk's operands fly while this one is processed
+        gemm_epilogue_chunk_staged(p, ep, v, st, lane, row0, n0 + c, split, bias_cur, Lr_cur, La_cur);
       }
       tc_fence_before();
       __syncwarp();

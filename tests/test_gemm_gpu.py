@@ -37,18 +37,19 @@ def test_gemm_kmajor_plain(cuda_device, M, N, K, bn):
     assert rel_err(outb, ref) < 6e-3
 
 
+@pytest.mark.parametrize("bn", [0, 1000])  # 1000 = CTA-pair kernel with the staged (warp-coalesced) epilogue
 @pytest.mark.parametrize("act", [0, 1, 2])
-def test_gemm_epilogue_bias_act_residual(cuda_device, act):
+def test_gemm_epilogue_bias_act_residual(cuda_device, act, bn):
     from mtrl_b200 import _lib
 
-    M, N, K = 640, 512, 256
+    M, N, K = (640, 512, 256) if bn == 0 else (700, 520, 256)  # ragged M and N tails for the pair kernel
     A = _rand((M, K), cuda_device, 3)
     Bt = _rand((N, K), cuda_device, 4)
     bias = torch.randn(N, device=cuda_device)
     res = torch.randn(M, N, device=cuda_device)
     out = torch.empty((M, N), device=cuda_device, dtype=torch.float32)
     pre = torch.empty((M, N), device=cuda_device, dtype=torch.bfloat16)
-    _lib.gemm_bf16(A, Bt, M, N, K, bias=bias, residual=res, act=act, out_f32=out, out_preact=pre)
+    _lib.gemm_bf16(A, Bt, M, N, K, bias=bias, residual=res, act=act, out_f32=out, out_preact=pre, bn=bn)
     torch.cuda.synchronize()
     z = A.float() @ Bt.float().t() + bias
     y = z if act == 0 else (torch.relu(z) if act == 1 else torch.nn.functional.gelu(z, approximate="tanh"))
@@ -56,17 +57,18 @@ def test_gemm_epilogue_bias_act_residual(cuda_device, act):
     assert rel_err(pre, z) < 6e-3
 
 
+@pytest.mark.parametrize("bn", [0, 1000])
 @pytest.mark.parametrize("dact", [1, 2])
-def test_gemm_dgrad_dact(cuda_device, dact):
+def test_gemm_dgrad_dact(cuda_device, dact, bn):
     """dX = (dY @ W^T) * act'(aux): B = W stored [K_out][N_red] is K-major."""
     from mtrl_b200 import _lib
 
-    M, Nred, Kout = 512, 384, 256
+    M, Nred, Kout = (512, 384, 256) if bn == 0 else (777, 384, 264)
     dY = _rand((M, Nred), cuda_device, 5)
     W = _rand((Kout, Nred), cuda_device, 6)
     aux = _rand((M, Kout), cuda_device, 7)
     out = torch.empty((M, Kout), device=cuda_device, dtype=torch.bfloat16)
-    _lib.gemm_bf16(dY, W, M, Kout, Nred, aux=aux, dact=dact, out_bf16=out)
+    _lib.gemm_bf16(dY, W, M, Kout, Nred, aux=aux, dact=dact, out_bf16=out, bn=bn)
     torch.cuda.synchronize()
     g = dY.float() @ W.float().t()
     if dact == 1:
