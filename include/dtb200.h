@@ -99,6 +99,10 @@ int dtb_attention_bwd(void* stream, const void* qkv, const float* mask, const vo
  * cast_transpose: fp32 [R,C] -> bf16 [R,C] (dst, may be NULL) and bf16 [C,R] (dst_t, may be NULL).
  * colsum: out[N] (+)= column sums of bf16 x [M,N] (row stride ld; N, ld multiples of 8); scratch fp32 dtb_colsum_scratch_floats(N). */
 int dtb_cast_transpose(void* stream, const float* src, int R, int C, void* dst, void* dst_t);
+/* get_action history window (upstream DecisionTransformer.get_action): for each of nseg per-timestep tensors
+ * (row_bytes[s] bytes per timestep, multiples of 4; srcs[s] holds the t most recent timesteps) write K rows to dsts[s]: K - t zero
+ * rows, then the t rows; mask_out[K] = [0]*(K-t) + [1]*t (may be NULL).  One launch; bit-exact copies. */
+int dtb_pad_left(void* stream, int nseg, const void* const* srcs, void* const* dsts, const int* row_bytes, int t, int K, float* mask_out);
 size_t dtb_colsum_scratch_floats(int N);
 int dtb_colsum_bf16(void* stream, const void* x, int M, int N, int ld, float* out, int accumulate, float* scratch);
 

@@ -77,6 +77,7 @@ def _declare(lib):
     lib.dtb_encoder_backward.argtypes = [vp, vp, vp, vp, i, vp, vp, vp, vp, i, vp, sz, vp]
     lib.dtb_encoder_forward_u8.argtypes = lib.dtb_encoder_forward.argtypes
     lib.dtb_encoder_backward_u8.argtypes = lib.dtb_encoder_backward.argtypes
+    lib.dtb_pad_left.argtypes = [vp, i, C.POINTER(vp), C.POINTER(vp), C.POINTER(i), i, i, vp]
     lib.dtb_masked_mse.argtypes = [vp, vp, vp, vp, i, i, f, vp, vp, vp]
     lib.dtb_heads_fwd.argtypes = [vp] * 8 + [i] * 5 + [vp] * 3
     lib.dtb_embed_fwd.argtypes = [vp] * 15 + [i] * 5 + [f] + [vp] * 5 + [i, i]

@@ -82,6 +82,10 @@ int dtb_cast_transpose(void* stream, const float* src, int R, int C, void* dst, 
   DTB_REQUIRE(src, DTB_ERR_BAD_ARG, "dtb_cast_transpose: null pointer");
   return cast_transpose((cudaStream_t)stream, src, R, C, (bf16*)dst, (bf16*)dst_t);
 }
+int dtb_pad_left(void* stream, int nseg, const void* const* srcs, void* const* dsts, const int* row_bytes, int t, int K, float* mask_out) {
+  DTB_REQUIRE(srcs && dsts && row_bytes, DTB_ERR_BAD_ARG, "dtb_pad_left: null argument");
+  return pad_left((cudaStream_t)stream, nseg, srcs, dsts, row_bytes, t, K, mask_out);
+}
 size_t dtb_colsum_scratch_floats(int N) { return colsum_scratch_floats(N); }
 int dtb_colsum_bf16(void* stream, const void* x, int M, int N, int ld, float* out, int accumulate, float* scratch) {
   DTB_REQUIRE(x && out && scratch, DTB_ERR_BAD_ARG, "dtb_colsum_bf16: null pointer");

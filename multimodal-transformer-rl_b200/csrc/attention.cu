@@ -12,6 +12,8 @@ namespace dtb {
 template <int D>
 __global__ void __launch_bounds__(128) attn_fwd_kernel(const bf16* __restrict__ qkv, const float* __restrict__ mask, int T, int nh,
                                                        int Kmask, float scale_log2, bf16* __restrict__ out, float* __restrict__ lse) {
+  pdl_trigger();
+  pdl_wait();
   constexpr int P = D + 8;  // smem row pitch (elements): 16-byte pad keeps ldmatrix conflict-free
   extern __shared__ __align__(16) uint8_t smem_att[];
   bf16* sQ = reinterpret_cast<bf16*>(smem_att);
@@ -145,7 +147,7 @@ static int launch_fwd(cudaStream_t stream, const bf16* qkv, const float* mask, i
   const float scale_log2 = 1.4426950408889634f / sqrtf((float)D);
   dim3 grid((T + 63) / 64, nh, B);
   ProfScope prof(stream, PF_ATTN_FWD, 2.0 * B * nh * (double)T * T * D);
-  attn_fwd_kernel<D><<<grid, 128, smem, stream>>>(qkv, mask, T, nh, T / 3, scale_log2, out, lse);
+  DTB_LAUNCH(attn_fwd_kernel<D>, grid, 128, smem, stream, qkv, mask, T, nh, T / 3, scale_log2, out, lse);
   DTB_CHECK_LAUNCH();
   return DTB_OK;
 }

@@ -13,6 +13,8 @@ __global__ void __launch_bounds__(128) attn_bwd_dq_kernel(const bf16* __restrict
                                                           const bf16* __restrict__ out, const bf16* __restrict__ dout,
                                                           const float* __restrict__ lse, int T, int nh, int Kmask, float scale,
                                                           float scale_log2, bf16* __restrict__ dqkv, float* __restrict__ delta) {
+  pdl_trigger();
+  pdl_wait();
   constexpr int P = D + 8;
   extern __shared__ __align__(16) uint8_t smem_att[];
   bf16* sQ = reinterpret_cast<bf16*>(smem_att);
@@ -137,6 +139,8 @@ __global__ void __launch_bounds__(128) attn_bwd_dkv_kernel(const bf16* __restric
                                                            const bf16* __restrict__ dout, const float* __restrict__ lse,
                                                            const float* __restrict__ delta, int T, int nh, int Kmask, float scale,
                                                            float scale_log2, bf16* __restrict__ dqkv) {
+  pdl_trigger();
+  pdl_wait();
   constexpr int P = D + 8;
   extern __shared__ __align__(16) uint8_t smem_att[];
   bf16* sK = reinterpret_cast<bf16*>(smem_att);
@@ -270,9 +274,9 @@ static int launch_bwd(cudaStream_t stream, const bf16* qkv, const float* mask, c
   const float scale_log2 = 1.4426950408889634f * scale;
   dim3 grid((T + 63) / 64, nh, B);
   ProfScope prof(stream, PF_ATTN_BWD, 5.0 * B * nh * (double)T * T * D);
-  attn_bwd_dq_kernel<D><<<grid, 128, smem, stream>>>(qkv, mask, out, dout, lse, T, nh, T / 3, scale, scale_log2, dqkv, delta);
+  DTB_LAUNCH(attn_bwd_dq_kernel<D>, grid, 128, smem, stream, qkv, mask, out, dout, lse, T, nh, T / 3, scale, scale_log2, dqkv, delta);
   DTB_CHECK_LAUNCH();
-  attn_bwd_dkv_kernel<D><<<grid, 128, smem, stream>>>(qkv, mask, dout, lse, delta, T, nh, T / 3, scale, scale_log2, dqkv);
+  DTB_LAUNCH(attn_bwd_dkv_kernel<D>, grid, 128, smem, stream, qkv, mask, dout, lse, delta, T, nh, T / 3, scale, scale_log2, dqkv);
   DTB_CHECK_LAUNCH();
   return DTB_OK;
 }

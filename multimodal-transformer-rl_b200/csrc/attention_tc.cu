@@ -114,6 +114,8 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
     fence_mbar_init();
   }
   if (warp == 4) { tmem_alloc(tmem_slot, 128); tmem_relinquish(); }
+  pdl_trigger();  // prologue done: the next kernel of the stream may start its own
+  pdl_wait();     // the previous kernel's results are complete and visible from here on
   at_fill_valid_bits(p, b, 2 * nkb, sBits);
   tc_fence_before();
   __syncthreads();
@@ -383,6 +385,8 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
     fence_mbar_init();
   }
   if (warp == 4) { tmem_alloc(tmem_slot, 256); tmem_relinquish(); }
+  pdl_trigger();  // prologue done: the next kernel of the stream may start its own
+  pdl_wait();     // the previous kernel's results are complete and visible from here on
   at_fill_valid_bits(p, b, 2 * nkb, sBits);
   tc_fence_before();
   __syncthreads();
@@ -576,6 +580,8 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmKV, const __grid_co
     fence_mbar_init();
   }
   if (warp == 4) { tmem_alloc(tmem_slot, 256); tmem_relinquish(); }
+  pdl_trigger();  // prologue done: the next kernel of the stream may start its own
+  pdl_wait();     // the previous kernel's results are complete and visible from here on
   for (int t = i0 * 64 + threadIdx.x; t < nqb * 64; t += blockDim.x) {
     sLse[t] = t < T ? -__ldg(p.lse_in + row_off + t) : 0.f;   // negated: exponent = s * scale_log2 + (-lse)
     sDelta[t] = t < T ? __ldg(p.delta + row_off + t) : 0.f;
@@ -760,7 +766,7 @@ int attn_fwd_tc(cudaStream_t stream, const bf16* qkv, const float* mask, int B, 
   }
   dim3 grid((T + 127) / 128, nh, B);
   ProfScope prof(stream, PF_ATTN_FWD, 2.0 * B * nh * (double)T * T * d);
-  attn_fwd_tc_kernel<<<grid, AT_THREADS, AT_FWD_SMEM, stream>>>(tmQ, tmKV, p);
+  DTB_LAUNCH(attn_fwd_tc_kernel, grid, AT_THREADS, AT_FWD_SMEM, stream, tmQ, tmKV, p);
   DTB_CHECK_LAUNCH();
   return DTB_OK;
 }
@@ -790,9 +796,9 @@ int attn_bwd_tc(cudaStream_t stream, const bf16* qkv, const float* mask, const b
   }
   dim3 grid((T + 127) / 128, nh, B);
   ProfScope prof(stream, PF_ATTN_BWD, 5.0 * B * nh * (double)T * T * d);
-  attn_bwd_dq_tc_kernel<<<grid, AT_THREADS, AT_DQ_SMEM, stream>>>(tm128, tm64, tmDO128, p);
+  DTB_LAUNCH(attn_bwd_dq_tc_kernel, grid, AT_THREADS, AT_DQ_SMEM, stream, tm128, tm64, tmDO128, p);
   DTB_CHECK_LAUNCH();
-  attn_bwd_dkv_tc_kernel<<<grid, AT_THREADS, AT_DKV_SMEM, stream>>>(tm128, tm64, tmDO64, p);
+  DTB_LAUNCH(attn_bwd_dkv_tc_kernel, grid, AT_THREADS, AT_DKV_SMEM, stream, tm128, tm64, tmDO64, p);
   DTB_CHECK_LAUNCH();
   return DTB_OK;
 }

@@ -7,6 +7,7 @@
 #include <cuda_bf16.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <string.h>
 #include "../../include/dtb200.h"
 
 #ifndef DTB_NUM_SMS_FALLBACK
@@ -66,6 +67,27 @@ struct ProfScope {
   ~ProfScope() { if (slot >= 0) prof_end(st, slot); }
 };
 
+// ---- kernel launch with programmatic dependent launch (PDL) ------------------------------------------------------------------
+// Every kernel of the library starts with pdl_trigger() + pdl_wait(): launched with the programmatic-stream-serialization attribute,
+// its CTAs may be scheduled (and run their prologue: barrier init, TMEM allocation, descriptor prefetch) while the previous kernel
+// of the stream is still draining; griddepcontrol.wait then blocks until that kernel has completed and its writes are visible.
+// In a captured CUDA graph the edge becomes a programmatic dependency.  DTB_NO_PDL=1 launches without the attribute (plain edges).
+bool pdl_enabled();
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, Args&&... args) {
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+#define DTB_LAUNCH(kernel, grid, block, smem, stream, ...) \
+  (void)::dtb::launch_pdl(kernel, dim3(grid), dim3(block), (size_t)(smem), stream, __VA_ARGS__)
+
 typedef __nv_bfloat16 bf16;
 typedef __nv_bfloat162 bf162;
 
@@ -73,6 +95,10 @@ typedef __nv_bfloat162 bf162;
 // device helpers
 // ----------------------------------------------------------------------------------------------
 #ifdef __CUDACC__
+
+// PDL: let the next kernel of the stream start its prologue / wait for the previous kernel's results (no-ops without the attribute)
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));

@@ -14,6 +14,8 @@ namespace dtb {
 // ---- conv1 patches from fp32 NCHW (k = 8, any stride with W % 4 == 0 and stride % 4 == 0) -------------------------
 __global__ void __launch_bounds__(256) im2col_nchw_k8_kernel(const float* __restrict__ x, int N, int C, int H, int W, int stride, int ho,
                                                              int wo, float scale, bf16* __restrict__ p) {
+  pdl_trigger();
+  pdl_wait();
   const size_t total = (size_t)N * ho * wo * C * 8;  // one thread per (row, c, kh): 8 contiguous kw
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
     const int kh = (int)(i & 7);
@@ -41,7 +43,7 @@ int im2col_nchw_k8(cudaStream_t stream, const float* x, int N, int C, int H, int
   size_t blocks = (total + 255) / 256;
   const size_t cap = (size_t)num_sms() * 16;
   if (blocks > cap) blocks = cap;
-  im2col_nchw_k8_kernel<<<(unsigned)blocks, 256, 0, stream>>>(x, N, C, H, W, stride, ho, wo, scale, p);
+  DTB_LAUNCH(im2col_nchw_k8_kernel, (unsigned)blocks, 256, 0, stream, x, N, C, H, W, stride, ho, wo, scale, p);
   DTB_CHECK_LAUNCH();
   return DTB_OK;
 }
@@ -49,6 +51,8 @@ int im2col_nchw_k8(cudaStream_t stream, const float* x, int N, int C, int H, int
 // ---- patches from bf16 NHWC: for a fixed (row, kh) the kw*C elements are contiguous in both source and destination --
 __global__ void __launch_bounds__(256) im2col_nhwc_kernel(const bf16* __restrict__ x, int N, int H, int W, int C, int k, int stride, int ho,
                                                           int wo, bf16* __restrict__ p) {
+  pdl_trigger();
+  pdl_wait();
   const int run = k * C / 8;  // 16-byte chunks per (row, kh)
   const size_t total = (size_t)N * ho * wo * k * run;
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
@@ -73,7 +77,7 @@ int im2col_nhwc(cudaStream_t stream, const bf16* x, int N, int H, int W, int C, 
   const size_t cap = (size_t)num_sms() * 16;
   if (blocks > cap) blocks = cap;
   ProfScope prof(stream, PF_IM2COL, 2.0 * N * H * W * C + 2.0 * (double)total * 8);
-  im2col_nhwc_kernel<<<(unsigned)blocks, 256, 0, stream>>>(x, N, H, W, C, k, stride, ho, wo, p);
+  DTB_LAUNCH(im2col_nhwc_kernel, (unsigned)blocks, 256, 0, stream, x, N, H, W, C, k, stride, ho, wo, p);
   DTB_CHECK_LAUNCH();
   return DTB_OK;
 }
@@ -81,6 +85,8 @@ int im2col_nhwc(cudaStream_t stream, const bf16* x, int N, int H, int W, int C, 
 // ---- col2im (gather) + ReLU mask: dz[n,h,w,c] = (y[n,h,w,c] > 0) * sum_{kh,kw valid} dp[(n,(h-kh)/s,(w-kw)/s), (kh,kw,c)] ---------
 __global__ void __launch_bounds__(256) col2im_nhwc_relu_kernel(const bf16* __restrict__ dp, const bf16* __restrict__ y, int N, int H, int W,
                                                                int C, int k, int stride, int ho, int wo, bf16* __restrict__ dz) {
+  pdl_trigger();
+  pdl_wait();
   const int cg = C / 8;
   const size_t total = (size_t)N * H * W * cg;
   const size_t ldp = (size_t)k * k * C;
@@ -123,7 +129,7 @@ int col2im_nhwc_relu(cudaStream_t stream, const bf16* dp, const bf16* y, int N, 
   const size_t cap = (size_t)num_sms() * 16;
   if (blocks > cap) blocks = cap;
   ProfScope prof(stream, PF_COL2IM, 4.0 * N * H * W * C + 2.0 * (double)N * ho * wo * k * k * C);
-  col2im_nhwc_relu_kernel<<<(unsigned)blocks, 256, 0, stream>>>(dp, y, N, H, W, C, k, stride, ho, wo, dz);
+  DTB_LAUNCH(col2im_nhwc_relu_kernel, (unsigned)blocks, 256, 0, stream, dp, y, N, H, W, C, k, stride, ho, wo, dz);
   DTB_CHECK_LAUNCH();
   return DTB_OK;
 }
@@ -132,6 +138,8 @@ int col2im_nhwc_relu(cudaStream_t stream, const bf16* dp, const bf16* y, int N, 
 // stage  : dst bf16 [O][B][A] = src fp32 [O][A][B]      ([Cout][Cin][kh*kw] -> [Cout][kh*kw][Cin];  fc [F][C][h*w] -> [F][h*w][C])
 // unstage: dst fp32 [O][A][B] = src fp32 [O][B][A]      (gradients back to the PyTorch order)
 __global__ void permute_stage_kernel(const float* __restrict__ src, int O, int A, int B, bf16* __restrict__ dst) {
+  pdl_trigger();
+  pdl_wait();
   const size_t total = (size_t)O * A * B;
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
     const int a = (int)(i % A);
@@ -142,6 +150,8 @@ __global__ void permute_stage_kernel(const float* __restrict__ src, int O, int A
   }
 }
 __global__ void permute_unstage_kernel(const float* __restrict__ src, int O, int A, int B, float* __restrict__ dst) {
+  pdl_trigger();
+  pdl_wait();
   const size_t total = (size_t)O * A * B;
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
     const int b = (int)(i % B);
@@ -157,18 +167,20 @@ static unsigned perm_blocks(size_t total) {
   return (unsigned)(blocks > cap ? cap : (blocks < 1 ? 1 : blocks));
 }
 int permute_stage(cudaStream_t stream, const float* src, int O, int A, int B, bf16* dst) {
-  permute_stage_kernel<<<perm_blocks((size_t)O * A * B), 256, 0, stream>>>(src, O, A, B, dst);
+  DTB_LAUNCH(permute_stage_kernel, perm_blocks((size_t)O * A * B), 256, 0, stream, src, O, A, B, dst);
   DTB_CHECK_LAUNCH();
   return DTB_OK;
 }
 int permute_unstage(cudaStream_t stream, const float* src, int O, int A, int B, float* dst) {
-  permute_unstage_kernel<<<perm_blocks((size_t)O * A * B), 256, 0, stream>>>(src, O, A, B, dst);
+  DTB_LAUNCH(permute_unstage_kernel, perm_blocks((size_t)O * A * B), 256, 0, stream, src, O, A, B, dst);
   DTB_CHECK_LAUNCH();
   return DTB_OK;
 }
 
 // out = a + b (bf16), and the ReLU-masked variant used by the 'sum' fusion backward: dz = (y > 0) * dy
 __global__ void add_bf16_kernel(const bf16* __restrict__ a, const bf16* __restrict__ b, size_t n8, bf16* __restrict__ out) {
+  pdl_trigger();
+  pdl_wait();
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n8; i += (size_t)gridDim.x * blockDim.x) {
     const uint4 ua = ldg_u4(a + i * 8), ub = ldg_u4(b + i * 8);
     const uint32_t wa[4] = {ua.x, ua.y, ua.z, ua.w}, wb[4] = {ub.x, ub.y, ub.z, ub.w};
@@ -184,12 +196,14 @@ __global__ void add_bf16_kernel(const bf16* __restrict__ a, const bf16* __restri
 int add_bf16(cudaStream_t stream, const bf16* a, const bf16* b, size_t n, bf16* out) {
   DTB_REQUIRE(n % 8 == 0, DTB_ERR_BAD_ARG, "add_bf16: n must be a multiple of 8");
   if (n == 0) return DTB_OK;
-  add_bf16_kernel<<<perm_blocks(n / 8), 256, 0, stream>>>(a, b, n / 8, out);
+  DTB_LAUNCH(add_bf16_kernel, perm_blocks(n / 8), 256, 0, stream, a, b, n / 8, out);
   DTB_CHECK_LAUNCH();
   return DTB_OK;
 }
 __global__ void relu_mask_bf16_kernel(const bf16* __restrict__ dy, int ldy, const bf16* __restrict__ y, int ld, int rows, int cols8,
                                       bf16* __restrict__ dz, int ldz) {
+  pdl_trigger();
+  pdl_wait();
   const size_t total = (size_t)rows * cols8;
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
     const int c = (int)(i % cols8) * 8;
@@ -208,7 +222,7 @@ __global__ void relu_mask_bf16_kernel(const bf16* __restrict__ dy, int ldy, cons
 int relu_mask_bf16(cudaStream_t stream, const bf16* dy, int ldy, const bf16* y, int ld, int rows, int cols, bf16* dz, int ldz) {
   DTB_REQUIRE(cols % 8 == 0 && ldy % 8 == 0 && ld % 8 == 0 && ldz % 8 == 0, DTB_ERR_BAD_ARG, "relu_mask: dims must be multiples of 8");
   if (rows * cols == 0) return DTB_OK;
-  relu_mask_bf16_kernel<<<perm_blocks((size_t)rows * cols / 8), 256, 0, stream>>>(dy, ldy, y, ld, rows, cols / 8, dz, ldz);
+  DTB_LAUNCH(relu_mask_bf16_kernel, perm_blocks((size_t)rows * cols / 8), 256, 0, stream, dy, ldy, y, ld, rows, cols / 8, dz, ldz);
   DTB_CHECK_LAUNCH();
   return DTB_OK;
 }

@@ -140,6 +140,8 @@ __global__ void __launch_bounds__(C1_THREADS, 1) conv1_fwd_kernel(const __grid_c
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_trigger();  // prologue done: the next kernel of the stream may start its own
+  pdl_wait();     // the previous kernel's results are complete and visible from here on
 
   if (warp < C1_EPI_WARP0) {
     // ===== patch producers =====
@@ -239,6 +241,8 @@ __global__ void __launch_bounds__(C1_THREADS, 1) conv1_wgrad_kernel(const __grid
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_trigger();  // prologue done: the next kernel of the stream may start its own
+  pdl_wait();     // the previous kernel's results are complete and visible from here on
   const int my_tiles = p.tiles > (int)blockIdx.x ? (p.tiles - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
 
   if (warp < C1_EPI_WARP0) {
@@ -333,7 +337,7 @@ int conv1_fwd(cudaStream_t stream, const void* x, int x_u8, int N, int C, int H,
   if (!attr) { DTB_CUDA(cudaFuncSetAttribute(conv1_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 225 * 1024)); attr = true; }
   const int grid = p.tiles < num_sms() ? p.tiles : num_sms();
   ProfScope prof(stream, PF_CONV1_FWD, (x_u8 ? 1.0 : 4.0) * N * C * H * W + 2.0 * (double)p.rows * cout);
-  conv1_fwd_kernel<<<grid, C1_THREADS, smem, stream>>>(tmW, p);
+  DTB_LAUNCH(conv1_fwd_kernel, grid, C1_THREADS, smem, stream, tmW, p);
   DTB_CHECK_LAUNCH();
   return DTB_OK;
 }
@@ -355,7 +359,7 @@ int conv1_wgrad(cudaStream_t stream, const void* x, int x_u8, int N, int C, int 
   int grid = p.tiles < num_sms() ? p.tiles : num_sms();
   if (grid > DTB_NUM_SMS_FALLBACK) grid = DTB_NUM_SMS_FALLBACK;
   ProfScope prof(stream, PF_CONV1_WGRAD, (x_u8 ? 1.0 : 4.0) * N * C * H * W + 2.0 * (double)p.rows * cout);
-  conv1_wgrad_kernel<<<grid, C1_THREADS, smem, stream>>>(tmZ, p);
+  DTB_LAUNCH(conv1_wgrad_kernel, grid, C1_THREADS, smem, stream, tmZ, p);
   DTB_CHECK_LAUNCH();
   prof.~ProfScope();
   prof.slot = -1;

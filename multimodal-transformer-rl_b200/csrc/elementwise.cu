@@ -1,11 +1,14 @@
 // HBM-bound helpers: fp32 -> bf16 weight casts (with transpose), bias-gradient column sums.
 #include "kernels.h"
+#include <string.h>
 
 namespace dtb {
 
 // ---- cast + transpose: src fp32 [R, C] -> dst bf16 [R, C], dst_t bf16 [C, R] -------------------
 // 32x32 tiles through shared memory so both the read and the two writes are coalesced.
 __global__ void cast_transpose_kernel(const float* __restrict__ src, int R, int C, bf16* __restrict__ dst, bf16* __restrict__ dst_t) {
+  pdl_trigger();
+  pdl_wait();
   __shared__ float tile[32][33];
   const int c0 = blockIdx.x * 32, r0 = blockIdx.y * 32;
   for (int i = threadIdx.y; i < 32; i += blockDim.y) {
@@ -25,12 +28,14 @@ __global__ void cast_transpose_kernel(const float* __restrict__ src, int R, int 
 
 int cast_transpose(cudaStream_t stream, const float* src, int R, int C, bf16* dst, bf16* dst_t) {
   dim3 grid((C + 31) / 32, (R + 31) / 32), block(32, 8);
-  cast_transpose_kernel<<<grid, block, 0, stream>>>(src, R, C, dst, dst_t);
+  DTB_LAUNCH(cast_transpose_kernel, grid, block, 0, stream, src, R, C, dst, dst_t);
   DTB_CHECK_LAUNCH();
   return DTB_OK;
 }
 
 __global__ void cast_bf16_kernel(const float* __restrict__ src, size_t n, bf16* __restrict__ dst) {
+  pdl_trigger();
+  pdl_wait();
   const size_t stride = (size_t)gridDim.x * blockDim.x;
   const size_t n4 = n / 4;
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n4; i += stride) {
@@ -47,7 +52,7 @@ int cast_bf16(cudaStream_t stream, const float* src, size_t n, bf16* dst) {
   int blocks = (int)((n / 4 + 255) / 256);
   if (blocks > num_sms() * 8) blocks = num_sms() * 8;
   if (blocks < 1) blocks = 1;
-  cast_bf16_kernel<<<blocks, 256, 0, stream>>>(src, n, dst);
+  DTB_LAUNCH(cast_bf16_kernel, blocks, 256, 0, stream, src, n, dst);
   DTB_CHECK_LAUNCH();
   return DTB_OK;
 }
@@ -60,6 +65,8 @@ constexpr int CS_SLABS_MAX = 1024;        // narrow matrices (conv bias grads, N
 constexpr int CS_SCRATCH_MIN = 64 * 1024;  // floats
 
 __global__ void __launch_bounds__(256) colsum_stage1(const bf16* __restrict__ x, int M, int N, int ld, float* __restrict__ scratch) {
+  pdl_trigger();
+  pdl_wait();
   __shared__ float red[256][9];
   const int cx = blockDim.x, ry = blockDim.y;
   const int col = (blockIdx.x * cx + threadIdx.x) * 8;
@@ -90,6 +97,8 @@ __global__ void __launch_bounds__(256) colsum_stage1(const bf16* __restrict__ x,
 
 __global__ void __launch_bounds__(256) colsum_stage2(const float* __restrict__ scratch, int nslab, int N, float* __restrict__ out,
                                                      int accumulate) {
+  pdl_trigger();
+  pdl_wait();
   __shared__ float red[8][33];
   const int c = blockIdx.x * 32 + threadIdx.x;
   float s = 0.f;
@@ -120,9 +129,52 @@ int colsum_bf16(cudaStream_t stream, const bf16* x, int M, int N, int ld, float*
   if ((size_t)nslab * N > colsum_scratch_floats(N)) nslab = (int)(colsum_scratch_floats(N) / N);
   if (nslab < 1) nslab = 1;
   ProfScope prof(stream, PF_COLSUM, 2.0 * M * N);
-  colsum_stage1<<<dim3(colgroups, nslab), dim3(cx, ry), 0, stream>>>(x, M, N, ld, scratch);
+  DTB_LAUNCH(colsum_stage1, dim3(colgroups, nslab), dim3(cx, ry), 0, stream, x, M, N, ld, scratch);
   DTB_CHECK_LAUNCH();
-  colsum_stage2<<<(N + 31) / 32, dim3(32, 8), 0, stream>>>(scratch, nslab, N, out, accumulate);
+  DTB_LAUNCH(colsum_stage2, (N + 31) / 32, dim3(32, 8), 0, stream, scratch, nslab, N, out, accumulate);
+  DTB_CHECK_LAUNCH();
+  return DTB_OK;
+}
+
+// ---- get_action history packing: keep the t most recent rows, LEFT-pad with zeros to K rows, mask = [0]*(K-t)+[1]*t ----
+// One launch for all per-timestep tensors of the call (states / frames / audio / actions / rtg / timesteps): segment s has
+// row_words[s] 32-bit words per timestep; blockIdx.y = segment.  Padding and indexing are integer-exact copies.
+struct PadArgs {
+  const uint32_t* src[8];
+  uint32_t* dst[8];
+  int row_words[8];
+  int t, K;
+  float* mask;
+};
+__global__ void __launch_bounds__(256) pad_left_kernel(const PadArgs a) {
+  pdl_trigger();
+  pdl_wait();
+  const int s = blockIdx.y;
+  const int rw = a.row_words[s];
+  const long long total = (long long)a.K * rw, shift = (long long)(a.K - a.t) * rw;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x)
+    a.dst[s][i] = i >= shift ? a.src[s][i - shift] : 0u;
+  if (s == 0 && blockIdx.x == 0 && a.mask)
+    for (int k = threadIdx.x; k < a.K; k += blockDim.x) a.mask[k] = k >= a.K - a.t ? 1.f : 0.f;
+}
+
+int pad_left(cudaStream_t stream, int nseg, const void* const* srcs, void* const* dsts, const int* row_bytes, int t, int K, float* mask) {
+  DTB_REQUIRE(nseg >= 1 && nseg <= 8 && t >= 0 && t <= K && K >= 1, DTB_ERR_BAD_ARG, "pad_left: bad arguments (nseg=%d t=%d K=%d)", nseg, t, K);
+  PadArgs a;
+  memset(&a, 0, sizeof(a));
+  long long maxw = 1;
+  for (int s = 0; s < nseg; ++s) {
+    DTB_REQUIRE(row_bytes[s] > 0 && row_bytes[s] % 4 == 0 && dsts[s] && (srcs[s] || t == 0), DTB_ERR_BAD_ARG,
+                "pad_left: segment %d needs 4-byte-multiple rows and non-null pointers", s);
+    a.src[s] = reinterpret_cast<const uint32_t*>(srcs[s]);
+    a.dst[s] = reinterpret_cast<uint32_t*>(dsts[s]);
+    a.row_words[s] = row_bytes[s] / 4;
+    if ((long long)K * a.row_words[s] > maxw) maxw = (long long)K * a.row_words[s];
+  }
+  a.t = t; a.K = K; a.mask = mask;
+  long long blocks = (maxw + 255) / 256;
+  if (blocks > 64) blocks = 64;
+  DTB_LAUNCH(pad_left_kernel, dim3((unsigned)blocks, nseg), 256, 0, stream, a);
   DTB_CHECK_LAUNCH();
   return DTB_OK;
 }

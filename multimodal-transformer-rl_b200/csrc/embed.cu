@@ -36,6 +36,8 @@ struct EmbedFwdArgs {
 };
 
 __global__ void __launch_bounds__(256) embed_fwd_kernel(const EmbedFwdArgs a) {
+  pdl_trigger();
+  pdl_wait();
   extern __shared__ __align__(16) float sm_emb[];
   const int H = a.H, sd = a.states ? a.sd : 0, ad = a.ad;
   float* sWs = sm_emb;                 // [sd][H]  (transposed)
@@ -184,7 +186,7 @@ int embed_fwd(cudaStream_t stream, const float* states, const float* state_proj,
   const int cap = num_sms() * 2;
   if (blocks > cap) blocks = cap;
   ProfScope prof(stream, PF_EMBED_FWD, (pre ? 8.0 : 4.0) * BK * 3 * H + 4.0 * BK * (sd + ad + 3));
-  embed_fwd_kernel<<<blocks, 256, smem, stream>>>(a);
+  DTB_LAUNCH(embed_fwd_kernel, blocks, 256, smem, stream, a);
   DTB_CHECK_LAUNCH();
   return DTB_OK;
 }
@@ -194,6 +196,8 @@ int embed_fwd(cudaStream_t stream, const float* states, const float* state_proj,
 // d_table[timesteps[t]] += d_pre_R + d_pre_s + d_pre_a   (fp32 atomics: rows collide across trajectories)
 __global__ void __launch_bounds__(256) embed_te_scatter_kernel(const bf16* __restrict__ d_pre, const long long* __restrict__ timesteps,
                                                                int BK, int H, int E, float* __restrict__ d_table) {
+  pdl_trigger();
+  pdl_wait();
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
   for (int t = blockIdx.x * nwarp + warp; t < BK; t += gridDim.x * nwarp) {
     long long ts = timesteps[t];
@@ -214,7 +218,7 @@ int embed_te_scatter(cudaStream_t stream, const bf16* d_pre, const long long* ti
   if (BK == 0) return DTB_OK;
   int blocks = (BK + 7) / 8;
   if (blocks > num_sms() * 4) blocks = num_sms() * 4;
-  embed_te_scatter_kernel<<<blocks, 256, 0, stream>>>(d_pre, timesteps, BK, H, E, d_table);
+  DTB_LAUNCH(embed_te_scatter_kernel, blocks, 256, 0, stream, d_pre, timesteps, BK, H, E, d_table);
   DTB_CHECK_LAUNCH();
   return DTB_OK;
 }
@@ -224,6 +228,8 @@ int embed_te_scatter(cudaStream_t stream, const bf16* d_pre, const long long* ti
 __global__ void embed_unpack_kernel(const float* __restrict__ G, const float* __restrict__ bsum, int H, int sd, int ad, int P8,
                                     int u_states, float* __restrict__ dwR, float* __restrict__ dbR, float* __restrict__ dWs,
                                     float* __restrict__ dbs, float* __restrict__ dWa, float* __restrict__ dba) {
+  pdl_trigger();
+  pdl_wait();
   const int per_c = 3 + ad + (u_states ? sd : 0);
   const int total = H * per_c;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
@@ -241,7 +247,7 @@ int embed_unpack(cudaStream_t stream, const float* G, const float* bsum, int H, 
   const int total = H * (3 + ad + (u_states ? sd : 0));
   int blocks = (total + 255) / 256;
   if (blocks > num_sms() * 4) blocks = num_sms() * 4;
-  embed_unpack_kernel<<<blocks, 256, 0, stream>>>(G, bsum, H, sd, ad, P8, u_states, dwR, dbR, dWs, dbs, dWa, dba);
+  DTB_LAUNCH(embed_unpack_kernel, blocks, 256, 0, stream, G, bsum, H, sd, ad, P8, u_states, dwR, dbR, dWs, dbs, dWa, dba);
   DTB_CHECK_LAUNCH();
   return DTB_OK;
 }

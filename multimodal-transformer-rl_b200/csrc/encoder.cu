@@ -60,7 +60,8 @@ struct dtb_encoder {
   long long total;
   int n_entries;
   std::vector<long long> off, num;
-  mutable dtb::SideStream side;  // weight-gradient branch of the backward
+  mutable dtb::SideStream side;   // weight-gradient branch of the backward (and the audio tower in forward)
+  mutable dtb::SideStream side2;  // the audio tower's data-gradient chain in backward, concurrent with the video tower's
 };
 
 namespace dtb {
@@ -260,7 +261,7 @@ int dtb_encoder_create(const dtb_encoder_config* cfg, dtb_encoder** out) {
   return DTB_OK;
 }
 int dtb_encoder_destroy(dtb_encoder* e) {
-  if (e) e->side.destroy();
+  if (e) { e->side.destroy(); e->side2.destroy(); }
   delete e;
   return DTB_OK;
 }
@@ -354,8 +355,13 @@ static int encoder_backward_impl(const dtb_encoder* e, void* stream, const float
     bf16* d = const_cast<bf16*>(dS);
     if (!d_states_masked)
       DTB_TRY(relu_mask_bf16(st, dS, e->state_dim, (const bf16*)states_bf16, e->state_dim, N, e->state_dim, d, e->state_dim));
+    // the towers are independent: the audio tower's dgrad chain runs on its own stream next to the video tower's; both feed their
+    // weight gradients to the shared side stream (which serialises the shared split-K / column-sum scratch)
+    DTB_TRY(e->side2.init());
+    DTB_TRY(e->side2.fork(st));
+    DTB_TRY(tower_backward(e, 1, e->side2.pick(st), Ps, N, audio, 0, d + e->t[0].feat, e->state_dim, w.t[1], w, grads));
     DTB_TRY(tower_backward(e, 0, st, Ps, N, frames, frames_u8, d, e->state_dim, w.t[0], w, grads));
-    DTB_TRY(tower_backward(e, 1, st, Ps, N, audio, 0, d + e->t[0].feat, e->state_dim, w.t[1], w, grads));
+    DTB_TRY(e->side2.join(st));
   } else {
     // sum: the gradient reaches both towers unchanged; each applies its own ReLU mask
     const int F = e->t[0].feat;

@@ -198,10 +198,10 @@ int gemm_bf16(cudaStream_t stream, const bf16* A, int lda, int a_mn_major, const
   ProfScope prof(stream, PF_GEMM, 2.0 * M * N * K);
   if (pair) {
     const int npairs = total < num_sms() / 2 ? total : num_sms() / 2;
-    gemm_tcgen05_pair_kernel<<<2 * npairs, GEMM2_THREADS, GEMM2_SMEM_BYTES, stream>>>(tmA, tmB, p);
+    DTB_LAUNCH(gemm_tcgen05_pair_kernel, 2 * npairs, GEMM2_THREADS, GEMM2_SMEM_BYTES, stream, tmA, tmB, p);
   } else {
     const int grid = total < num_sms() ? total : num_sms();
-    gemm_tcgen05_kernel<<<grid, GEMM_THREADS, GEMM_SMEM_BYTES, stream>>>(tmA, tmB, p);
+    DTB_LAUNCH(gemm_tcgen05_kernel, grid, GEMM_THREADS, GEMM_SMEM_BYTES, stream, tmA, tmB, p);
   }
   DTB_CHECK_LAUNCH();
   return p.split_k;  // >= 1: number of partial slices written when ep.partial != null
@@ -211,6 +211,8 @@ int gemm_bf16(cudaStream_t stream, const bf16* A, int lda, int a_mn_major, const
 // 32 float4 columns x 8 split-lanes per block: lane l sums slices l, l+8, ... and the 8 lanes are combined in index order.
 __global__ void __launch_bounds__(256) splitk_reduce_kernel(const float* __restrict__ partial, int splits, int M, int N,
                                                             float* __restrict__ out, int ldo, int accumulate, float scale) {
+  pdl_trigger();
+  pdl_wait();
   __shared__ float4 red[8][32];
   const size_t n4 = (size_t)M * N / 4;
   for (size_t base = (size_t)blockIdx.x * 32; base < n4; base += (size_t)gridDim.x * 32) {
@@ -243,7 +245,7 @@ int splitk_reduce(cudaStream_t stream, const float* partial, int splits, int M, 
   size_t blocks = (n4 + 31) / 32;
   if (blocks > (size_t)num_sms() * 8) blocks = (size_t)num_sms() * 8;
   if (blocks < 1) blocks = 1;
-  splitk_reduce_kernel<<<(unsigned)blocks, dim3(32, 8), 0, stream>>>(partial, splits, M, N, out, ldo, accumulate, scale);
+  DTB_LAUNCH(splitk_reduce_kernel, (unsigned)blocks, dim3(32, 8), 0, stream, partial, splits, M, N, out, ldo, accumulate, scale);
   DTB_CHECK_LAUNCH();
   return DTB_OK;
 }

@@ -150,6 +150,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_trigger();  // prologue done: the next kernel of the stream may start its own
+  pdl_wait();     // the previous kernel's results are complete and visible from here on
 
   const int total_tiles = p.m_tiles * p.n_tiles * p.split_k;
   const int kblocks_total = (p.K + GEMM_BK - 1) / GEMM_BK;
@@ -542,6 +544,8 @@ gemm_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
   cluster_sync_all();  // both CTAs' barriers are initialised before any remote arrive / TMA credit
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_trigger();  // prologue done: the next kernel of the stream may start its own
+  pdl_wait();     // the previous kernel's results are complete and visible from here on
 
   // pair tiles: 256 x 256; both CTAs of a pair walk the same tile sequence
   const int pair = blockIdx.x >> 1, npairs = gridDim.x >> 1;

@@ -50,6 +50,8 @@ __device__ __forceinline__ float dot_row8(const float* __restrict__ w, int H, in
 }
 
 __global__ void __launch_bounds__(256) heads_fwd_kernel(const HeadsFwdArgs a) {
+  pdl_trigger();
+  pdl_wait();
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
   for (int t = blockIdx.x * nwarp + warp; t < a.BK; t += gridDim.x * nwarp) {
     float v[HD_MAX_VEC][8];
@@ -82,7 +84,7 @@ int heads_fwd(cudaStream_t stream, const bf16* y, const float* Wa, const float* 
   HeadsFwdArgs a{y, Wa, ba, Ws, bs, Wr, br, BK, H, sd, ad, tanh_act, action_preds, state_preds, return_preds};
   int blocks = (BK + 7) / 8;
   if (blocks > num_sms() * 8) blocks = num_sms() * 8;
-  heads_fwd_kernel<<<blocks, 256, 0, stream>>>(a);
+  DTB_LAUNCH(heads_fwd_kernel, blocks, 256, 0, stream, a);
   DTB_CHECK_LAUNCH();
   return DTB_OK;
 }
@@ -92,6 +94,8 @@ constexpr int MSE_BLOCKS = 128;
 
 __global__ void __launch_bounds__(256) mse_partial_kernel(const float* __restrict__ pred, const float* __restrict__ target,
                                                           const float* __restrict__ mask, int BK, int ad, float* __restrict__ part) {
+  pdl_trigger();
+  pdl_wait();
   __shared__ float ssum[8], scnt[8];
   float s = 0.f, n = 0.f;
   for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < BK; t += gridDim.x * blockDim.x) {
@@ -120,6 +124,8 @@ __global__ void __launch_bounds__(256) mse_finalize_kernel(const float* __restri
                                                            const float* __restrict__ target, const float* __restrict__ mask, int BK,
                                                            int ad, float grad_scale, float* __restrict__ loss_out,
                                                            float* __restrict__ d_pred) {
+  pdl_trigger();
+  pdl_wait();
   float S = 0.f, N = 0.f;
   for (int i = 0; i < nparts; ++i) { S += part[2 * i]; N += part[2 * i + 1]; }  // every thread: same fixed order
   const float denom = N * ad;
@@ -144,12 +150,12 @@ int mse_loss(cudaStream_t stream, const float* pred, const float* target, const 
   int blocks = (BK + 255) / 256;
   if (blocks > MSE_BLOCKS) blocks = MSE_BLOCKS;
   if (blocks < 1) blocks = 1;
-  mse_partial_kernel<<<blocks, 256, 0, stream>>>(pred, target, mask, BK, ad, scratch);
+  DTB_LAUNCH(mse_partial_kernel, blocks, 256, 0, stream, pred, target, mask, BK, ad, scratch);
   DTB_CHECK_LAUNCH();
   int fblocks = (BK * ad + 255) / 256;
   if (fblocks > num_sms() * 4) fblocks = num_sms() * 4;
   if (fblocks < 1) fblocks = 1;
-  mse_finalize_kernel<<<fblocks, 256, 0, stream>>>(scratch, blocks, pred, target, mask, BK, ad, grad_scale, loss_out, d_pred);
+  DTB_LAUNCH(mse_finalize_kernel, fblocks, 256, 0, stream, scratch, blocks, pred, target, mask, BK, ad, grad_scale, loss_out, d_pred);
   DTB_CHECK_LAUNCH();
   return DTB_OK;
 }
@@ -167,6 +173,8 @@ struct HeadsBwdArgs {
 };
 
 __global__ void __launch_bounds__(256) heads_bwd_kernel(const HeadsBwdArgs a) {
+  pdl_trigger();
+  pdl_wait();
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
   const int H = a.H;
   for (int t = blockIdx.x * nwarp + warp; t < a.BK; t += gridDim.x * nwarp) {
@@ -257,13 +265,15 @@ int heads_bwd(cudaStream_t stream, const float* d_action, const float* d_state, 
   HeadsBwdArgs a{d_action, d_state, d_return, action_preds, Wa, Ws, Wr, BK, H, sd, ad, tanh_act, ZA8, ZS8, dy, dzA, dzS};
   int blocks = (BK + 7) / 8;
   if (blocks > num_sms() * 8) blocks = num_sms() * 8;
-  heads_bwd_kernel<<<blocks, 256, 0, stream>>>(a);
+  DTB_LAUNCH(heads_bwd_kernel, blocks, 256, 0, stream, a);
   DTB_CHECK_LAUNCH();
   return DTB_OK;
 }
 
 // Copy rows/cols out of a padded fp32 matrix: dst[r][c] = src[r * lds + c], r < R, c < C (head weight grads from the padded GEMM result).
 __global__ void copy2d_kernel(const float* __restrict__ src, int lds, int R, int C, float* __restrict__ dst, int ldd) {
+  pdl_trigger();
+  pdl_wait();
   const int total = R * C;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
     const int r = i / C, c = i - r * C;
@@ -274,7 +284,7 @@ int copy2d(cudaStream_t stream, const float* src, int lds, int R, int C, float* 
   if (R * C == 0) return DTB_OK;
   int blocks = (R * C + 255) / 256;
   if (blocks > num_sms() * 4) blocks = num_sms() * 4;
-  copy2d_kernel<<<blocks, 256, 0, stream>>>(src, lds, R, C, dst, ldd);
+  DTB_LAUNCH(copy2d_kernel, blocks, 256, 0, stream, src, lds, R, C, dst, ldd);
   DTB_CHECK_LAUNCH();
   return DTB_OK;
 }

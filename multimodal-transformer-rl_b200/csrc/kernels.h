@@ -57,6 +57,8 @@ int cast_bf16(cudaStream_t stream, const float* src, size_t n, bf16* dst);
 int colsum_bf16(cudaStream_t stream, const bf16* x, int M, int N, int ld, float* out, int accumulate, float* scratch);
 size_t colsum_scratch_floats(int N);
 
+int pad_left(cudaStream_t stream, int nseg, const void* const* srcs, void* const* dsts, const int* row_bytes, int t, int K, float* mask);
+
 // ---- layernorm.cu ------------------------------------------------------------------------------
 int ln_fwd(cudaStream_t stream, const float* x, const float* gamma, const float* beta, int M, int H, float eps, bf16* y, float* mean,
            float* rstd);

@@ -12,6 +12,8 @@ constexpr int LN_MAX_VEC = 8;  // H <= 8 * 128 = 1024
 __global__ void __launch_bounds__(256) ln_fwd_kernel(const float* __restrict__ x, const float* __restrict__ gamma,
                                                      const float* __restrict__ beta, int M, int H, float eps, bf16* __restrict__ y,
                                                      float* __restrict__ mean_out, float* __restrict__ rstd_out) {
+  pdl_trigger();
+  pdl_wait();
   const int lane = threadIdx.x & 31;
   const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (row >= M) return;
@@ -59,7 +61,7 @@ int ln_fwd(cudaStream_t stream, const float* x, const float* gamma, const float*
   DTB_REQUIRE(H % 4 == 0 && H <= LN_MAX_VEC * 128, DTB_ERR_UNSUPPORTED, "layernorm: hidden size %d unsupported (multiple of 4, <= 1024)", H);
   if (M == 0) return DTB_OK;
   ProfScope prof(stream, PF_LN_FWD, 6.0 * M * H);
-  ln_fwd_kernel<<<(M + 7) / 8, 256, 0, stream>>>(x, gamma, beta, M, H, eps, y, mean, rstd);
+  DTB_LAUNCH(ln_fwd_kernel, (M + 7) / 8, 256, 0, stream, x, gamma, beta, M, H, eps, y, mean, rstd);
   DTB_CHECK_LAUNCH();
   return DTB_OK;
 }
@@ -73,6 +75,8 @@ __global__ void __launch_bounds__(256, 2) ln_bwd_kernel(const bf16* __restrict__
                                                         const float* __restrict__ gamma, const float* __restrict__ dres, int M, int H,
                                                         float* __restrict__ dx_out, bf16* __restrict__ dx_bf16,
                                                         float* __restrict__ scratch /* [grid][2][H] */) {
+  pdl_trigger();
+  pdl_wait();
   extern __shared__ float sred[];  // [2][H]
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
   float4 dg[NV], db[NV];
@@ -160,18 +164,20 @@ __global__ void __launch_bounds__(256, 2) ln_bwd_kernel(const bf16* __restrict__
   for (int i = threadIdx.x; i < 2 * H; i += blockDim.x) scratch[(size_t)blockIdx.x * 2 * H + i] = sred[i];
 }
 
-// 32 columns x 8 row-lanes per block; lanes combined in index order (deterministic).
-__global__ void __launch_bounds__(256) ln_bwd_finalize(const float* __restrict__ scratch, int nblk, int H, float* __restrict__ dgamma,
-                                                       float* __restrict__ dbeta) {
-  __shared__ float red[8][33];
+// 32 columns x 32 row-lanes per block (short dependent-load chains: nblk / 32 deep); lanes combined in index order (deterministic).
+__global__ void __launch_bounds__(1024) ln_bwd_finalize(const float* __restrict__ scratch, int nblk, int H, float* __restrict__ dgamma,
+                                                        float* __restrict__ dbeta) {
+  pdl_trigger();
+  pdl_wait();
+  __shared__ float red[32][33];
   const int c = blockIdx.x * 32 + threadIdx.x;
   float s = 0.f;
   if (c < 2 * H)
-    for (int b = threadIdx.y; b < nblk; b += 8) s += scratch[(size_t)b * 2 * H + c];
+    for (int b = threadIdx.y; b < nblk; b += 32) s += scratch[(size_t)b * 2 * H + c];
   red[threadIdx.y][threadIdx.x] = s;
   __syncthreads();
   if (threadIdx.y == 0 && c < 2 * H) {
-    for (int i = 1; i < 8; ++i) s += red[i][threadIdx.x];
+    for (int i = 1; i < 32; ++i) s += red[i][threadIdx.x];
     if (c < H) dgamma[c] = s;
     else dbeta[c - H] = s;
   }
@@ -179,7 +185,7 @@ __global__ void __launch_bounds__(256) ln_bwd_finalize(const float* __restrict__
 
 static int ln_bwd_blocks(int M, int H) {
   int b = (M + 7) / 8;
-  const int cap = num_sms() * (H <= 256 ? 8 : 2);  // scratch is sized for 8 x SMs partial rows
+  const int cap = num_sms() * 2;  // two resident CTAs per SM; scratch is sized for 8 x SMs partial rows
   return b > cap ? cap : (b < 1 ? 1 : b);
 }
 size_t ln_bwd_scratch_floats(int H) { return (size_t)DTB_NUM_SMS_FALLBACK * 8 * 2 * H; }
@@ -191,7 +197,7 @@ int ln_bwd(cudaStream_t stream, const bf16* dy, const float* x, const float* mea
   const int nv = (H + 127) / 128;
   const size_t sm = 2 * H * sizeof(float);
   ProfScope prof(stream, PF_LN_BWD, 16.0 * M * H);
-#define DTB_LN_BWD(NV) ln_bwd_kernel<NV><<<blocks, 256, sm, stream>>>(dy, x, mean, rstd, gamma, dres, M, H, dx_out, dx_out_bf16, scratch)
+#define DTB_LN_BWD(NV) DTB_LAUNCH(ln_bwd_kernel<NV>, blocks, 256, sm, stream, dy, x, mean, rstd, gamma, dres, M, H, dx_out, dx_out_bf16, scratch)
   if (nv <= 1) DTB_LN_BWD(1);
   else if (nv <= 2) DTB_LN_BWD(2);
   else if (nv <= 4) DTB_LN_BWD(4);
@@ -199,7 +205,7 @@ int ln_bwd(cudaStream_t stream, const bf16* dy, const float* x, const float* mea
   else DTB_LN_BWD(8);
 #undef DTB_LN_BWD
   DTB_CHECK_LAUNCH();
-  ln_bwd_finalize<<<(2 * H + 31) / 32, dim3(32, 8), 0, stream>>>(scratch, blocks, H, dgamma, dbeta);
+  DTB_LAUNCH(ln_bwd_finalize, (2 * H + 31) / 32, dim3(32, 32), 0, stream, scratch, blocks, H, dgamma, dbeta);
   DTB_CHECK_LAUNCH();
   return DTB_OK;
 }

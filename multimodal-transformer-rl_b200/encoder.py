@@ -219,12 +219,22 @@ class MultimodalDecisionTransformer(nn.Module):
 
     @torch.no_grad()
     def get_action(self, frames, audio, actions, rewards, returns_to_go, timesteps, **kwargs):
-        """frames [t,Cv,H,W], audio [t,Ca,H,W]: encode the history, then DecisionTransformer.get_action on the state tokens."""
-        K = self.dt.max_length
-        if K is not None:
-            frames, audio = frames[-K:], audio[-K:]
-        states = self.encoder.forward_raw(frames.unsqueeze(0), audio.unsqueeze(0))[0].float()
-        return self.dt.get_action(states, actions, rewards, returns_to_go, timesteps, **kwargs)
+        """frames [t,Cv,H,W] (fp32 or uint8 pixels), audio [t,Ca,H,W]: window + left padding of the raw history in one launch, then one
+        CUDA graph of towers -> state tokens -> B = 1 Decision Transformer forward (model._ActionRunner)."""
+        from .model import _ActionRunner
+
+        dt, K = self.dt, self.dt.max_length
+        if K is None:
+            states = self.encoder.forward_raw(frames.unsqueeze(0), audio.unsqueeze(0))[0].float()
+            return dt.get_action(states, actions, rewards, returns_to_go, timesteps, **kwargs)
+        fdt = torch.uint8 if frames.dtype == torch.uint8 else torch.float32
+        runner = self.__dict__.get("_action_runner")
+        if runner is None or runner.dead(dt) or runner.frames.dtype != fdt:
+            runner = _ActionRunner(dt, self.encoder, fdt)
+            self.__dict__["_action_runner"] = runner
+        hist = [(frames[-K:], runner.frames), (audio[-K:], runner.audio), (actions.reshape(-1, dt.act_dim)[-K:], runner.actions),
+                (returns_to_go.reshape(-1, 1)[-K:], runner.rtg), (timesteps.reshape(-1)[-K:], runner.timesteps)]
+        return runner.run(hist)
 
     def loss_and_backward(self, frames, audio, actions, returns_to_go, timesteps, attention_mask, action_target=None, grad_scale=1.0,
                           on_stage_done=None):

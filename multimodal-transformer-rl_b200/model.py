@@ -272,26 +272,25 @@ class DecisionTransformer(nn.Module):
 
     @torch.no_grad()
     def get_action(self, states, actions, rewards, returns_to_go, timesteps, **kwargs):
-        """Upstream evaluation entry point: last-K window, LEFT zero padding, action of the last state token."""
+        """Upstream evaluation entry point: last-K window, LEFT zero padding, action of the last state token.
+
+        With a fixed window (``max_length``) the call is one ``dtb_pad_left`` launch (window + padding + mask, integer-exact) plus the
+        replay of a CUDA graph of the B = 1 forward over static history buffers (``_ActionRunner``)."""
         self._require_cuda(states)
-        dev = states.device
-        states = states.reshape(1, -1, self.state_dim)
-        actions = actions.reshape(1, -1, self.act_dim)
-        returns_to_go = returns_to_go.reshape(1, -1, 1)
-        timesteps = timesteps.reshape(1, -1)
-        attention_mask = None
-        if self.max_length is not None:
-            K = self.max_length
-            states, actions = states[:, -K:], actions[:, -K:]
-            returns_to_go, timesteps = returns_to_go[:, -K:], timesteps[:, -K:]
-            t = states.shape[1]
-            attention_mask = torch.cat([torch.zeros(K - t, device=dev), torch.ones(t, device=dev)]).reshape(1, -1)
-            states = torch.cat([torch.zeros((1, K - t, self.state_dim), device=dev), states.float()], dim=1)
-            actions = torch.cat([torch.zeros((1, K - t, self.act_dim), device=dev), actions.float()], dim=1)
-            returns_to_go = torch.cat([torch.zeros((1, K - t, 1), device=dev), returns_to_go.float()], dim=1)
-            timesteps = torch.cat([torch.zeros((1, K - t), device=dev, dtype=torch.long), timesteps.long()], dim=1)
-        _, action_preds, _ = self._forward_raw(states, actions, returns_to_go, timesteps, attention_mask, want_all=False)
-        return action_preds[0, -1]
+        if self.max_length is None:
+            states = states.reshape(1, -1, self.state_dim)
+            actions = actions.reshape(1, -1, self.act_dim)
+            _, action_preds, _ = self._forward_raw(states, actions, returns_to_go.reshape(1, -1, 1), timesteps.reshape(1, -1), None,
+                                                   want_all=False)
+            return action_preds[0, -1]
+        K = self.max_length
+        runner = self.__dict__.get("_action_runner")
+        if runner is None or runner.dead(self):
+            runner = _ActionRunner(self, None)
+            self.__dict__["_action_runner"] = runner
+        hist = [(states.reshape(-1, self.state_dim)[-K:], runner.states), (actions.reshape(-1, self.act_dim)[-K:], runner.actions),
+                (returns_to_go.reshape(-1, 1)[-K:], runner.rtg), (timesteps.reshape(-1)[-K:], runner.timesteps)]
+        return runner.run(hist)
 
     # ---- raw paths (no autograd graph) ---------------------------------------------------------------------------
     def _forward_raw(self, states, actions, returns_to_go, timesteps, attention_mask, want_all=True, states_bf16=None, states_relu=False):
@@ -362,6 +361,71 @@ class DecisionTransformer(nn.Module):
                 self._h = None
         except Exception:
             pass
+
+
+class _ActionRunner:
+    """Static K-step history buffers + one CUDA graph of the B = 1 forward (towers included for the multimodal model).
+
+    ``run`` = ``dtb_pad_left`` (the only launch that reads the caller's tensors: keep the last t <= K rows, left-pad with zeros,
+    mask = [0]*(K-t) + [1]*t) + graph replay + a clone of the action row.  Weights are re-staged to bf16 outside the graph whenever
+    the fp32 master changed, so the graph stays valid across optimizer steps."""
+
+    def __init__(self, dt, encoder=None, frames_dtype=None):
+        dev, K = dt._flat.device, dt.max_length
+        self.dt, self.enc, self.K, self.dev = dt, encoder, K, dev
+        self.flat_ptr = dt._flat.data_ptr()
+        self.actions = torch.zeros((1, K, dt.act_dim), dtype=torch.float32, device=dev)
+        self.rtg = torch.zeros((1, K, 1), dtype=torch.float32, device=dev)
+        self.timesteps = torch.zeros((1, K), dtype=torch.long, device=dev)
+        self.mask = torch.zeros((1, K), dtype=torch.float32, device=dev)
+        if encoder is None:
+            self.states = torch.zeros((1, K, dt.state_dim), dtype=torch.float32, device=dev)
+        else:
+            self.frames = torch.zeros((1, K, *encoder.frame_shape), dtype=frames_dtype, device=dev)
+            self.audio = torch.zeros((1, K, *encoder.audio_shape), dtype=torch.float32, device=dev)
+        self.out = torch.zeros(dt.act_dim, dtype=torch.float32, device=dev)
+        self.graph, self._keep = None, None
+
+    def dead(self, dt):
+        return self.flat_ptr != dt._flat.data_ptr()  # the model was moved / re-created: buffers and graph are stale
+
+    def _body(self):
+        dt = self.dt
+        if self.enc is None:
+            _, ap, _ = dt._forward_raw(self.states, self.actions, self.rtg, self.timesteps, self.mask, want_all=False)
+        else:
+            sb = self.enc.forward_raw(self.frames, self.audio)
+            _, ap, _ = dt._forward_raw(None, self.actions, self.rtg, self.timesteps, self.mask, want_all=False, states_bf16=sb)
+        self.out.copy_(ap[0, -1])
+        self._keep = (dt._last, None if self.enc is None else self.enc._last)  # workspaces stay alive as long as the graph does
+
+    def run(self, hist):
+        lib = _lib.load()
+        t = int(hist[0][0].shape[0])
+        n = len(hist)
+        srcs, keep = (C.c_void_p * n)(), []
+        if "_dsts" not in self.__dict__:
+            self._dsts = (C.c_void_p * n)(*[d.data_ptr() for _, d in hist])
+            self._rows = (C.c_int * n)(*[d[0, 0].numel() * d.element_size() for _, d in hist])
+        for i, (src, dst) in enumerate(hist):
+            if src.shape[0] != t:
+                raise ValueError("get_action: states / actions / returns_to_go / timesteps must have the same history length")
+            src = src.detach().to(dst.dtype).contiguous()
+            keep.append(src)
+            srcs[i] = src.data_ptr()
+        self.dt._stage()
+        if self.enc is not None:
+            self.enc._stage()
+        _lib.check(lib.dtb_pad_left(_lib.stream_ptr(), n, srcs, self._dsts, self._rows, t, self.K, _lib.ptr(self.mask)))
+        if self.graph is None:
+            self._body()  # warm-up (lazy allocations, tensor-map cache) outside the capture
+            torch.cuda.current_stream(self.dev).synchronize()
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                self._body()
+            self.graph = g
+        self.graph.replay()
+        return self.out.clone()
 
 
 class _DTFunction(torch.autograd.Function):

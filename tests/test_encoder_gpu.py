@@ -156,3 +156,30 @@ def test_uint8_pixel_frames_bit_exact(frame_shape, audio_shape, conv_type):
     assert torch.equal(outs[0][0], outs[1][0])
     assert torch.equal(outs[0][1], outs[1][1])
     assert outs[0][1].abs().sum() > 0
+
+
+def test_multimodal_get_action(cuda_device):
+    """Raw frame / spectrogram history -> towers -> DT get_action (uint8 pixels and fp32 frames), vs the oracle on the decoded frames."""
+    from mtrl_b200.encoder import MultimodalDecisionTransformer
+    from oracle.encoders import MultimodalDecisionTransformer as OracleMM
+    from util import build_pair
+
+    dev = cuda_device
+    frame_shape, audio_shape = (3, 64, 64), (1, 64, 64)
+    o_enc, enc = _pair(frame_shape, audio_shape, "big", "concat", dev, 1.0)
+    o_dt, dt, K = build_pair("c2", dev)
+    oracle, model = OracleMM(o_enc, o_dt), MultimodalDecisionTransformer(enc, dt)
+    g = torch.Generator().manual_seed(11)
+    for t in (1, 9, K, K + 4):
+        px = torch.randint(0, 256, (t, *frame_shape), generator=g, dtype=torch.uint8)
+        f32 = px.float() * 2.0 / 255.0 - 1
+        audio = _spec(1, t, audio_shape, g)[0] * 0.5
+        a = torch.nn.functional.one_hot(torch.randint(0, 4, (t,), generator=g), 4).float()
+        a[-1] = 0
+        r, ts = torch.rand(t, 1, generator=g) * 3, torch.arange(t)
+        with torch.no_grad():
+            states = oracle.encoder(f32[-K:].unsqueeze(0), audio[-K:].unsqueeze(0))[0]
+            ref = o_dt.get_action(states, a, None, r, ts)
+        for frames in (px, f32):
+            got = model.get_action(frames.to(dev), audio.to(dev), a.to(dev), None, r.to(dev), ts.to(dev))
+            assert rel_err(got, ref) <= 1e-2, (t, frames.dtype)

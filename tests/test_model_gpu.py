@@ -190,3 +190,48 @@ def test_against_committed_golden_fixture(cuda_device):
     assert abs(out[0].item() - fx["loss"].item()) <= TOL_LOSS * abs(fx["loss"].item())
     for n, g in fx["grads"].items():
         assert rel_err(m.get_parameter(n).grad, g) <= TOL_GRAD, n
+
+
+def test_get_action_graph_reuse_and_weight_update(cuda_device):
+    """The cached CUDA graph of get_action must follow (a) a changing history length across calls (episode start -> full window ->
+    sliding window) and (b) in-place weight updates (bf16 staging happens outside the graph)."""
+    oracle, model, K = build_pair("c1", cuda_device, seed=3)
+    dev = cuda_device
+    g = torch.Generator().manual_seed(0)
+    T = K + 6
+    s, a, r, ts = torch.randn(T, 11, generator=g), torch.rand(T, 3, generator=g) * 2 - 1, torch.rand(T, 1, generator=g) * 3, torch.arange(T)
+    for t in (1, 2, K - 1, K, K + 1, T):
+        aa = a[:t].clone(); aa[-1] = 0
+        got = model.get_action(s[:t].to(dev), aa.to(dev), None, r[:t].to(dev), ts[:t].to(dev))
+        ref = oracle.get_action(s[:t], aa, None, r[:t], ts[:t])
+        assert rel_err(got, ref) <= TOL_ACTION, t
+    with torch.no_grad():
+        for (n, p), (_, q) in zip(oracle.named_parameters(), model.named_parameters()):
+            p.mul_(1.05)
+        model.load_state_dict(oracle.state_dict())
+    got = model.get_action(s.to(dev), a.to(dev), None, r.to(dev), ts.to(dev))
+    ref = oracle.get_action(s, a, None, r, ts)
+    assert rel_err(got, ref) <= TOL_ACTION
+
+
+@pytest.mark.parametrize("t,K", [(0, 5), (1, 5), (3, 5), (5, 5), (17, 30)])
+def test_pad_left_bit_exact(cuda_device, t, K):
+    """dtb_pad_left: window + LEFT zero padding + mask, integer-exact for every dtype it moves (fp32, int64, uint8 frames)."""
+    import ctypes as C
+
+    from mtrl_b200 import _lib
+
+    dev = cuda_device
+    srcs = [torch.randn(t, 11, device=dev), torch.arange(t, device=dev, dtype=torch.long) * 7 + 3,
+            torch.randint(0, 256, (t, 3, 8, 8), device=dev, dtype=torch.uint8)]
+    dsts = [torch.full((K, *x.shape[1:]), 77, device=dev, dtype=x.dtype) for x in srcs]
+    mask = torch.full((K,), -1.0, device=dev)
+    n = len(srcs)
+    sp = (C.c_void_p * n)(*[x.data_ptr() for x in srcs])
+    dp = (C.c_void_p * n)(*[x.data_ptr() for x in dsts])
+    rb = (C.c_int * n)(*[x[0].numel() * x.element_size() for x in dsts])
+    _lib.check(_lib.load().dtb_pad_left(_lib.stream_ptr(), n, sp, dp, rb, t, K, _lib.ptr(mask)))
+    torch.cuda.synchronize()
+    for x, d in zip(srcs, dsts):
+        assert torch.equal(d[K - t:], x) and (d[:K - t] == 0).all()
+    assert torch.equal(mask, torch.cat([torch.zeros(K - t), torch.ones(t)]).to(dev))
