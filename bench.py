@@ -486,6 +486,7 @@ def main():
     ap.add_argument("--bucket-mb", type=int, default=8)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-roofline", action="store_true")
+    ap.add_argument("--no-get-action", action="store_true", help="skip the get_action latency measurement (keeps ncu launch lists to the training step)")
     ap.add_argument("--no-extras", action="store_true", help="skip the other-workload summaries (c1 / c3 / c4) appended to the default line")
     args = ap.parse_args()
     wl = dict(WORKLOADS[args.workload])
@@ -525,7 +526,7 @@ def main():
         if rank == 0:
             res["roofline"] = roof
     if rank == 0:
-        if world == 1:
+        if world == 1 and not args.no_get_action:
             try:
                 res["get_action"] = measure_get_action(wl, ctx)
             except Exception as e:  # noqa: BLE001

@@ -44,6 +44,9 @@ long long dtb_launch_count(void);
  * 9 im2col (bytes), 10 col2im (bytes).  report() synchronises the events and returns summed milliseconds, algorithmic work, launches. */
 void dtb_profile_enable(int on);
 int dtb_profile_report(int family, double* total_ms, double* work, long long* launches);
+/* timeline of the last profiled step: number of recorded launches, and launch i's family + [start, end] in ms from the first one */
+int dtb_profile_spans(void);
+int dtb_profile_span(int i, int* family, double* start_ms, double* end_ms);
 
 /* ---- tensor-core GEMM (tcgen05 + TMEM + TMA) --------------------------------------------------
  * D[M,N] = epilogue(A x B^T-style product), bf16 operands, fp32 accumulation.

@@ -49,6 +49,7 @@ def _declare(lib):
     lib.dtb_launch_count.restype = ll
     lib.dtb_profile_enable.argtypes = [i]
     lib.dtb_profile_enable.restype = None
+    lib.dtb_profile_span.argtypes = [i, C.POINTER(i), C.POINTER(C.c_double), C.POINTER(C.c_double)]
     lib.dtb_profile_report.argtypes = [i, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(ll)]
     for name in ("dtb_layernorm_bwd_scratch_floats", "dtb_colsum_scratch_floats", "dtb_mse_scratch_floats"):
         getattr(lib, name).restype = sz

@@ -5,6 +5,8 @@
 #include <string.h>
 
 namespace dtb {
+int prof_span(int i, int* family, double* start_ms, double* end_ms);
+int prof_count();
 void prof_enable(bool on);
 void prof_reset();
 int prof_report(int family, double* total_ms, double* work, long long* launches);
@@ -21,6 +23,8 @@ const char* dtb_last_error(void) { return dtb::last_error(); }
 int dtb_check_device(void) { return dtb::require_sm100(); }
 long long dtb_launch_count(void) { return dtb::launch_count(); }
 void dtb_profile_enable(int on) { dtb::prof_enable(on != 0); if (on) dtb::prof_reset(); }
+int dtb_profile_spans(void) { return dtb::prof_count(); }
+int dtb_profile_span(int i, int* family, double* start_ms, double* end_ms) { return dtb::prof_span(i, family, start_ms, end_ms); }
 int dtb_profile_report(int family, double* total_ms, double* work, long long* launches) {
   return dtb::prof_report(family, total_ms, work, launches);
 }

@@ -33,80 +33,110 @@ struct Conv1Params {
 // (kh ^ (r & 7)).  Work item = (row, channel, half of the 8 kernel rows): 8 independent 128-bit loads, then 4 shared stores.
 __device__ __forceinline__ void c1_gather_tile(const Conv1Params& p, uint8_t* stage, long long m0) {
   const uint32_t base = smem_u32(stage);
-  for (int item = threadIdx.x; item < 256 * p.C; item += C1_PRODUCERS) {
-    const int r = item & 127, half = (item >> 7) & 1, c = item >> 8;
-    const long long m = m0 + r;
-    float4 a[4], b[4];
-    if (m < p.rows) {
-      const int ow = (int)(m % p.wo);
-      const long long t = m / p.wo;
-      const int oh = (int)(t % p.ho), n = (int)(t / p.ho);
-      const float* src = p.x + (((size_t)n * p.C + c) * p.H + (size_t)oh * p.stride + half * 4) * p.W + (size_t)ow * p.stride;
+  constexpr int NB = 2;  // work items per thread whose loads are all issued before the first conversion (16 x 128-bit in flight)
+  const int nitems = 256 * p.C;
+  for (int it0 = threadIdx.x; it0 < nitems; it0 += C1_PRODUCERS * NB) {
+    float4 a[NB][4], b[NB][4];
 #pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        a[k] = ldg_f4(src + (size_t)k * p.W);
-        b[k] = ldg_f4(src + (size_t)k * p.W + 4);
+    for (int j = 0; j < NB; ++j) {
+      const int item = it0 + j * C1_PRODUCERS;
+      const int r = item & 127, half = (item >> 7) & 1, c = item >> 8;
+      const long long m = m0 + r;
+      if (item < nitems && m < p.rows) {
+        const uint32_t mu = (uint32_t)m;  // rows < 2^31 (checked on the host): 32-bit index arithmetic
+        const int ow = (int)(mu % (uint32_t)p.wo);
+        const uint32_t t = mu / (uint32_t)p.wo;
+        const int oh = (int)(t % (uint32_t)p.ho), n = (int)(t / (uint32_t)p.ho);
+        const float* src = p.x + (((size_t)n * p.C + c) * p.H + (size_t)oh * p.stride + half * 4) * p.W + (size_t)ow * p.stride;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          a[j][k] = ldg_f4(src + (size_t)k * p.W);
+          b[j][k] = ldg_f4(src + (size_t)k * p.W + 4);
+        }
+      } else {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) a[j][k] = b[j][k] = make_float4(0.f, 0.f, 0.f, 0.f);
       }
-    } else {
-#pragma unroll
-      for (int k = 0; k < 4; ++k) a[k] = b[k] = make_float4(0.f, 0.f, 0.f, 0.f);
     }
     const float s = p.scale;
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      const int kh = half * 4 + k;
-      const uint32_t addr = base + c * C1_KB_BYTES + r * 128 + ((kh ^ (r & 7)) << 4);
-      asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(pack_bf16x2(a[k].x * s, a[k].y * s)),
-                   "r"(pack_bf16x2(a[k].z * s, a[k].w * s)), "r"(pack_bf16x2(b[k].x * s, b[k].y * s)),
-                   "r"(pack_bf16x2(b[k].z * s, b[k].w * s))
-                   : "memory");
+    for (int j = 0; j < NB; ++j) {
+      const int item = it0 + j * C1_PRODUCERS;
+      if (item >= nitems) break;
+      const int r = item & 127, half = (item >> 7) & 1, c = item >> 8;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int kh = half * 4 + k;
+        const uint32_t addr = base + c * C1_KB_BYTES + r * 128 + ((kh ^ (r & 7)) << 4);
+        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(pack_bf16x2(a[j][k].x * s, a[j][k].y * s)),
+                     "r"(pack_bf16x2(a[j][k].z * s, a[j][k].w * s)), "r"(pack_bf16x2(b[j][k].x * s, b[j][k].y * s)),
+                     "r"(pack_bf16x2(b[j][k].z * s, b[j][k].w * s))
+                     : "memory");
+      }
     }
   }
 }
 
-// uint8-pixel variant: the reference's pixel decode (img * 2 / 255 - 1, fp32) and the `/255` input scale are folded into a 256-entry
-// bf16 table built once per CTA with exactly those fp32 operations, so the tile image is bit-identical to the fp32-input path.
-__device__ __forceinline__ void c1_build_lut(uint16_t* lut, float scale) {
-  for (int i = threadIdx.x; i < 256; i += blockDim.x) {
-    const float v = __fsub_rn(__fdiv_rn(__fmul_rn((float)i, 2.f), 255.f), 1.f);
-    const bf16 b = __float2bfloat16_rn(v * scale);
-    lut[i] = *reinterpret_cast<const uint16_t*>(&b);
-  }
+// uint8-pixel variant: the reference's pixel decode (img * 2 / 255 - 1, fp32) and the `/255` input scale in registers.  The IEEE
+// division n / 255 is reproduced exactly by a reciprocal multiply plus one FMA residual correction (verified for all 256 pixel values:
+// tests/test_encoder_gpu.py::test_uint8_pixel_frames_bit_exact), so the tile image is bit-identical to the fp32-input path.
+__device__ __forceinline__ float c1_decode_px(uint32_t byte, float scale) {
+  const float n = (float)byte * 2.f;  // exact
+  const float r = 1.f / 255.f;
+  float q = __fmul_rn(n, r);
+  const float rem = __fmaf_rn(-q, 255.f, n);
+  q = __fmaf_rn(rem, r, q);  // == n / 255 correctly rounded
+  return __fmul_rn(__fsub_rn(q, 1.f), scale);
 }
-__device__ __forceinline__ void c1_gather_tile_u8(const Conv1Params& p, uint8_t* stage, long long m0, const uint16_t* lut) {
+__device__ __forceinline__ uint32_t c1_decode_pair(uint32_t word, int lo_byte, float scale) {
+  return pack_bf16x2(c1_decode_px((word >> (8 * lo_byte)) & 255u, scale), c1_decode_px((word >> (8 * lo_byte + 8)) & 255u, scale));
+}
+__device__ __forceinline__ void c1_gather_tile_u8(const Conv1Params& p, uint8_t* stage, long long m0) {
   const uint32_t base = smem_u32(stage);
-  for (int item = threadIdx.x; item < 256 * p.C; item += C1_PRODUCERS) {
-    const int r = item & 127, half = (item >> 7) & 1, c = item >> 8;
-    const long long m = m0 + r;
-    uint32_t a[4], b[4];
-    if (m < p.rows) {
-      const int ow = (int)(m % p.wo);
-      const long long t = m / p.wo;
-      const int oh = (int)(t % p.ho), n = (int)(t / p.ho);
-      const uint8_t* src = p.xu8 + (((size_t)n * p.C + c) * p.H + (size_t)oh * p.stride + half * 4) * p.W + (size_t)ow * p.stride;
+  constexpr int NB = 3;  // all of a thread's work items of the tile (C <= 4: at most 3): every load is in flight before the first lookup
+  const int nitems = 256 * p.C;
+  for (int it0 = threadIdx.x; it0 < nitems; it0 += C1_PRODUCERS * NB) {
+    uint32_t a[NB][4], b[NB][4];
+    bool ok[NB];
 #pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        a[k] = __ldg(reinterpret_cast<const uint32_t*>(src + (size_t)k * p.W));
-        b[k] = __ldg(reinterpret_cast<const uint32_t*>(src + (size_t)k * p.W + 4));
+    for (int j = 0; j < NB; ++j) {
+      const int item = it0 + j * C1_PRODUCERS;
+      const int r = item & 127, half = (item >> 7) & 1, c = item >> 8;
+      const long long m = m0 + r;
+      ok[j] = item < nitems && m < p.rows;
+      if (ok[j]) {
+        const uint32_t mu = (uint32_t)m;  // rows < 2^31 (checked on the host): 32-bit index arithmetic
+        const int ow = (int)(mu % (uint32_t)p.wo);
+        const uint32_t t = mu / (uint32_t)p.wo;
+        const int oh = (int)(t % (uint32_t)p.ho), n = (int)(t / (uint32_t)p.ho);
+        const uint8_t* src = p.xu8 + (((size_t)n * p.C + c) * p.H + (size_t)oh * p.stride + half * 4) * p.W + (size_t)ow * p.stride;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          a[j][k] = __ldg(reinterpret_cast<const uint32_t*>(src + (size_t)k * p.W));
+          b[j][k] = __ldg(reinterpret_cast<const uint32_t*>(src + (size_t)k * p.W + 4));
+        }
+      } else {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) a[j][k] = b[j][k] = 0u;
       }
-    } else {
-#pragma unroll
-      for (int k = 0; k < 4; ++k) a[k] = b[k] = 0u;
     }
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      const int kh = half * 4 + k;
-      const uint32_t addr = base + c * C1_KB_BYTES + r * 128 + ((kh ^ (r & 7)) << 4);
-      uint32_t w0, w1, w2, w3;
-      if (m < p.rows) {
-        w0 = (uint32_t)lut[a[k] & 255] | ((uint32_t)lut[(a[k] >> 8) & 255] << 16);
-        w1 = (uint32_t)lut[(a[k] >> 16) & 255] | ((uint32_t)lut[a[k] >> 24] << 16);
-        w2 = (uint32_t)lut[b[k] & 255] | ((uint32_t)lut[(b[k] >> 8) & 255] << 16);
-        w3 = (uint32_t)lut[(b[k] >> 16) & 255] | ((uint32_t)lut[b[k] >> 24] << 16);
-      } else {
-        w0 = w1 = w2 = w3 = 0u;
+    for (int j = 0; j < NB; ++j) {
+      const int item = it0 + j * C1_PRODUCERS;
+      if (item >= nitems) break;
+      const int r = item & 127, half = (item >> 7) & 1, c = item >> 8;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int kh = half * 4 + k;
+        const uint32_t addr = base + c * C1_KB_BYTES + r * 128 + ((kh ^ (r & 7)) << 4);
+        uint32_t w0 = 0u, w1 = 0u, w2 = 0u, w3 = 0u;
+        if (ok[j]) {
+          const uint32_t av = a[j][k], bv = b[j][k];
+          w0 = c1_decode_pair(av, 0, p.scale); w1 = c1_decode_pair(av, 2, p.scale);
+          w2 = c1_decode_pair(bv, 0, p.scale); w3 = c1_decode_pair(bv, 2, p.scale);
+        }
+        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(w0), "r"(w1), "r"(w2), "r"(w3) : "memory");
       }
-      asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(w0), "r"(w1), "r"(w2), "r"(w3) : "memory");
     }
   }
 }
@@ -125,8 +155,6 @@ __global__ void __launch_bounds__(C1_THREADS, 1) conv1_fwd_kernel(const __grid_c
   uint64_t* tempty_bar = bars + 10;      // [2]
   uint64_t* w_bar = bars + 12;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 13);
-  uint16_t* lut = reinterpret_cast<uint16_t*>(bars + 14);  // [256] (uint8 input only)
-  if (p.xu8) c1_build_lut(lut, p.scale);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (threadIdx.x == 0) {
@@ -148,7 +176,7 @@ __global__ void __launch_bounds__(C1_THREADS, 1) conv1_fwd_kernel(const __grid_c
     uint32_t stage = 0, phase = 0;
     for (int t = blockIdx.x; t < p.tiles; t += gridDim.x) {
       mbar_wait(&empty_bar[stage], phase ^ 1);
-      if (p.xu8) c1_gather_tile_u8(p, smA + (size_t)stage * stage_bytes, (long long)t * 128, lut);
+      if (p.xu8) c1_gather_tile_u8(p, smA + (size_t)stage * stage_bytes, (long long)t * 128);
       else c1_gather_tile(p, smA + (size_t)stage * stage_bytes, (long long)t * 128);
       fence_proxy_async();  // generic-proxy stores -> visible to the tensor core (async proxy)
       mbar_arrive(&full_bar[stage]);
@@ -225,8 +253,6 @@ __global__ void __launch_bounds__(C1_THREADS, 1) conv1_wgrad_kernel(const __grid
   uint64_t* empty_bar = bars + 4;    // [stages]
   uint64_t* done_bar = bars + 8;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 9);
-  uint16_t* lut = reinterpret_cast<uint16_t*>(bars + 10);  // [256] (uint8 input only)
-  if (p.xu8) c1_build_lut(lut, p.scale);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   for (int i = threadIdx.x; i < C1_KB_BYTES / 16; i += blockDim.x) reinterpret_cast<uint4*>(smZero)[i] = make_uint4(0, 0, 0, 0);
@@ -253,7 +279,7 @@ __global__ void __launch_bounds__(C1_THREADS, 1) conv1_wgrad_kernel(const __grid
         mbar_arrive_expect_tx(&full_bar[stage], C1_KB_BYTES);
         tma_load_2d(smZ + (size_t)stage * C1_KB_BYTES, &tmZ, &full_bar[stage], 0, t * 128);
       }
-      if (p.xu8) c1_gather_tile_u8(p, smP + (size_t)stage * stage_bytes, (long long)t * 128, lut);
+      if (p.xu8) c1_gather_tile_u8(p, smP + (size_t)stage * stage_bytes, (long long)t * 128);
       else c1_gather_tile(p, smP + (size_t)stage * stage_bytes, (long long)t * 128);
       fence_proxy_async();
       mbar_arrive(&full_bar[stage]);
@@ -315,6 +341,7 @@ static int c1_params(Conv1Params& p, const void* xv, int x_u8, int N, int C, int
   p.N = N; p.C = C; p.H = H; p.W = W; p.stride = stride; p.cout = cout; p.scale = scale;
   p.ho = (H - 8) / stride + 1; p.wo = (W - 8) / stride + 1;
   p.rows = (long long)N * p.ho * p.wo;
+  DTB_REQUIRE(p.rows < (1LL << 31), DTB_ERR_UNSUPPORTED, "conv1: %lld output pixels exceed the 32-bit row index", p.rows);
   p.tiles = (int)((p.rows + 127) / 128);
   return DTB_OK;
 }

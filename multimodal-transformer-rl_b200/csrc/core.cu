@@ -83,6 +83,20 @@ int prof_report(int family, double* total_ms, double* work, long long* launches)
   return DTB_OK;
 }
 
+// span i of the last profiled step: family and [start, end] in ms relative to the first recorded launch (timeline reconstruction)
+int prof_span(int i, int* family, double* start_ms, double* end_ms) {
+  if (i < 0 || i >= g_pn) return DTB_ERR_BAD_ARG;
+  if (cudaEventSynchronize(g_pe1[i]) != cudaSuccess) return DTB_ERR_CUDA;
+  float a = 0.f, b = 0.f;
+  if (cudaEventElapsedTime(&a, g_pe0[0], g_pe0[i]) != cudaSuccess) return DTB_ERR_CUDA;
+  if (cudaEventElapsedTime(&b, g_pe0[0], g_pe1[i]) != cudaSuccess) return DTB_ERR_CUDA;
+  if (family) *family = g_pfam[i];
+  if (start_ms) *start_ms = a;
+  if (end_ms) *end_ms = b;
+  return DTB_OK;
+}
+int prof_count() { return g_pn; }
+
 static int g_num_sms = 0;
 int num_sms() {
   if (g_num_sms > 0) return g_num_sms;

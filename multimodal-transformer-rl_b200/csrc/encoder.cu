@@ -44,9 +44,9 @@ struct EncWs {
   TowerWs t[2];
   bf16* feat[2];   // 'sum' fusion: per-tower features
   bf16* dfeat;     // 'sum' fusion: masked feature gradient
-  float* partial;
+  float* partial[2];     // split-K partials, one buffer per tower (their weight-gradient branches run concurrently)
   size_t partial_floats;
-  float* cs_scratch;
+  float* cs_scratch[2];  // column-sum scratch, one per tower
   size_t total;
 };
 }  // namespace dtb
@@ -62,6 +62,7 @@ struct dtb_encoder {
   std::vector<long long> off, num;
   mutable dtb::SideStream side;   // weight-gradient branch of the backward (and the audio tower in forward)
   mutable dtb::SideStream side2;  // the audio tower's data-gradient chain in backward, concurrent with the video tower's
+  mutable dtb::SideStream side3;  // the audio tower's weight-gradient branch (the video tower's uses `side`)
 };
 
 namespace dtb {
@@ -148,8 +149,10 @@ static void carve_ws(const dtb_encoder* e, int N, uint8_t* base, EncWs& w) {
   w.feat[1] = sum ? carve<bf16>(p, (size_t)N * e->t[1].feat) : nullptr;
   w.dfeat = sum ? carve<bf16>(p, (size_t)N * e->t[0].feat) : nullptr;
   w.partial_floats = pf;
-  w.partial = carve<float>(p, pf);
-  w.cs_scratch = carve<float>(p, colsum_scratch_floats((int)maxn));
+  for (int ti = 0; ti < 2; ++ti) {
+    w.partial[ti] = carve<float>(p, pf);
+    w.cs_scratch[ti] = carve<float>(p, colsum_scratch_floats((int)maxn));
+  }
   w.total = (size_t)(p - base);
 }
 
@@ -194,18 +197,20 @@ static int tower_forward(const dtb_encoder* e, int ti, cudaStream_t st, const fl
 
 // dF: gradient w.r.t. the tower's feature output, already multiplied by the ReLU mask; bf16 [N, feat] with row stride ldf.
 static int tower_backward(const dtb_encoder* e, int ti, cudaStream_t st, const bf16* Ps, int N, const void* x, int x_u8, const bf16* dF,
-                          int ldf, TowerWs& tw, EncWs& w, float* G) {
+                          int ldf, TowerWs& tw, EncWs& w, float* G, SideStream& wside) {
   const Tower& t = e->t[ti];
   const int last = t.nconv - 1;
   const ConvSpec& cl = t.conv[last];
   const int hw = cl.hout * cl.wout;
-  SideStream& sd = e->side;
+  SideStream& sd = wside;
   cudaStream_t ss = sd.pick(st);  // weight / bias gradients: side branch; data gradients stay on the caller's stream
+  float* const partial = w.partial[ti];
+  float* const cs_scratch = w.cs_scratch[ti];
   // ---- FC ----
   DTB_TRY(sd.fork(st));
-  DTB_TRY(gemm_wgrad(ss, dF, ldf, tw.Y[last], t.flat, t.feat, t.flat, N, tw.gstage, t.flat, w.partial, w.partial_floats));
+  DTB_TRY(gemm_wgrad(ss, dF, ldf, tw.Y[last], t.flat, t.feat, t.flat, N, tw.gstage, t.flat, partial, w.partial_floats));
   DTB_TRY(permute_unstage(ss, tw.gstage, t.feat, cl.cout, hw, G + t.w_off[3]));  // staged (h,w,c) -> PyTorch flatten (c,h,w)
-  DTB_TRY(colsum_bf16(ss, dF, N, t.feat, ldf, G + t.b_off[3], 0, w.cs_scratch));
+  DTB_TRY(colsum_bf16(ss, dF, N, t.feat, ldf, G + t.b_off[3], 0, cs_scratch));
   {
     GemmEpilogue ep = epz();
     ep.dact = 1;
@@ -224,12 +229,12 @@ static int tower_backward(const dtb_encoder* e, int ti, cudaStream_t st, const b
       DTB_REQUIRE(x != nullptr, DTB_ERR_BAD_ARG, "encoder backward: frames / audio are needed again for the implicit conv1 weight gradient");
       DTB_TRY(conv1_wgrad(ss, x, x_u8, N, cs.cin, cs.hin, cs.win, cs.stride, e->c.input_scale, tw.dZ[0], cs.cout, tw.c1_partial, G + t.w_off[0]));
     } else if (i == 0) {
-      DTB_TRY(gemm_wgrad(ss, tw.dZ[0], cs.cout, tw.P[0], kc, cs.cout, kc, rows, G + t.w_off[0], kc, w.partial, w.partial_floats));
+      DTB_TRY(gemm_wgrad(ss, tw.dZ[0], cs.cout, tw.P[0], kc, cs.cout, kc, rows, G + t.w_off[0], kc, partial, w.partial_floats));
     } else {
-      DTB_TRY(gemm_wgrad(ss, tw.dZ[i], cs.cout, tw.P[i], kc, cs.cout, kc, rows, tw.gstage, kc, w.partial, w.partial_floats));
+      DTB_TRY(gemm_wgrad(ss, tw.dZ[i], cs.cout, tw.P[i], kc, cs.cout, kc, rows, tw.gstage, kc, partial, w.partial_floats));
       DTB_TRY(permute_unstage(ss, tw.gstage, cs.cout, cs.cin, cs.k * cs.k, G + t.w_off[i]));  // (kh,kw,c) -> (c,kh,kw)
     }
-    DTB_TRY(colsum_bf16(ss, tw.dZ[i], rows, cs.cout, cs.cout, G + t.b_off[i], 0, w.cs_scratch));
+    DTB_TRY(colsum_bf16(ss, tw.dZ[i], rows, cs.cout, cs.cout, G + t.b_off[i], 0, cs_scratch));
     if (i > 0) {
       GemmEpilogue ep = epz();
       ep.out_bf16 = tw.dP;
@@ -261,7 +266,7 @@ int dtb_encoder_create(const dtb_encoder_config* cfg, dtb_encoder** out) {
   return DTB_OK;
 }
 int dtb_encoder_destroy(dtb_encoder* e) {
-  if (e) { e->side.destroy(); e->side2.destroy(); }
+  if (e) { e->side.destroy(); e->side2.destroy(); e->side3.destroy(); }
   delete e;
   return DTB_OK;
 }
@@ -358,16 +363,19 @@ static int encoder_backward_impl(const dtb_encoder* e, void* stream, const float
     // the towers are independent: the audio tower's dgrad chain runs on its own stream next to the video tower's; both feed their
     // weight gradients to the shared side stream (which serialises the shared split-K / column-sum scratch)
     DTB_TRY(e->side2.init());
+    DTB_TRY(e->side3.init());
     DTB_TRY(e->side2.fork(st));
-    DTB_TRY(tower_backward(e, 1, e->side2.pick(st), Ps, N, audio, 0, d + e->t[0].feat, e->state_dim, w.t[1], w, grads));
-    DTB_TRY(tower_backward(e, 0, st, Ps, N, frames, frames_u8, d, e->state_dim, w.t[0], w, grads));
+    DTB_TRY(tower_backward(e, 1, e->side2.pick(st), Ps, N, audio, 0, d + e->t[0].feat, e->state_dim, w.t[1], w, grads, e->side3));
+    DTB_TRY(tower_backward(e, 0, st, Ps, N, frames, frames_u8, d, e->state_dim, w.t[0], w, grads, e->side));
+    DTB_TRY(e->side3.join(e->side2.pick(st)));
     DTB_TRY(e->side2.join(st));
   } else {
     // sum: the gradient reaches both towers unchanged; each applies its own ReLU mask
     const int F = e->t[0].feat;
     for (int ti = 0; ti < 2; ++ti) {
       DTB_TRY(relu_mask_bf16(st, dS, F, w.feat[ti], F, N, F, w.dfeat, F));
-      DTB_TRY(tower_backward(e, ti, st, Ps, N, ti == 0 ? frames : (const void*)audio, ti == 0 ? frames_u8 : 0, w.dfeat, F, w.t[ti], w, grads));
+      DTB_TRY(tower_backward(e, ti, st, Ps, N, ti == 0 ? frames : (const void*)audio, ti == 0 ? frames_u8 : 0, w.dfeat, F, w.t[ti], w, grads,
+                             e->side));
       DTB_TRY(e->side.join(st));  // w.dfeat is reused by the next tower
     }
   }
