@@ -345,7 +345,12 @@ def run_cpu(wl, steps, warmup, budget_s=20.0):
                       f"({tokens} tokens/step), {steps} steps after {warmup} warm-up, {cores} threads", "loss": loss}
 
 
-PROF_FAMILIES = [("gemm_tcgen05_kernel", "tensor"), ("conv1_fwd_kernel", "hbm"), ("conv1_wgrad_kernel", "hbm"), ("attn_fwd_kernel", "tensor"),
+# DRAM bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum, mean over the captured launches) of each workload's dominant
+# kernel, from the committed `ncu --set full` captures (a profiler pass cannot run inside the timed bench)
+NCU_TRAFFIC = {"c2": (20.7e6, "profiles/r01_ncu_gemm_c2_v0.txt (6 launches of the c2 step)"),
+               "c4": (187.4e6, "profiles/r01_ncu_gemm_pair_v1.txt (qkv GEMM at M=38400: 62.6 MB read + 124.8 MB written)")}
+
+PROF_FAMILIES = [("gemm_tcgen05_kernel (+pair)", "tensor"), ("conv1_fwd_kernel", "hbm"), ("conv1_wgrad_kernel", "hbm"), ("attn_fwd_kernel", "tensor"),
                  ("attn_bwd_dq+dkv_kernel", "tensor"), ("ln_fwd_kernel", "hbm"), ("ln_bwd_kernel(+finalize)", "hbm"), ("embed_fwd_kernel", "hbm"),
                  ("colsum_stage1+2", "hbm"), ("im2col_nhwc_kernel", "hbm"), ("col2im_nhwc_relu_kernel", "hbm")]
 
@@ -419,7 +424,8 @@ def measure_roofline(args, wl, ctx, reps=5):
         f["frac"] = f["achieved"] / f["peak"]
     top = max(fams, key=lambda f: f["ms_per_step"])
     return {"kernel": top["kernel"], "bound": top["bound"], "achieved": top["achieved"], "peak": top["peak"], "unit": top["unit"],
-            "frac": top["frac"], "traffic": None, "peak_source": peaks["source"], "launches_per_step": top["launches_per_step"],
+            "frac": top["frac"], "traffic": (NCU_TRAFFIC.get(args.workload, (None, None))[0] if top["kernel"].startswith("gemm") else None),
+            "traffic_source": NCU_TRAFFIC.get(args.workload, (None, None))[1] if top["kernel"].startswith("gemm") else None, "peak_source": peaks["source"], "launches_per_step": top["launches_per_step"],
             "avg_launch_us": top["ms_per_step"] / max(1, top["launches_per_step"]) * 1e3,
             "how": f"CUDA events around every launch of the family on its own stream, {reps} steps, {mode}; algorithmic work per DESIGN.md §3",
             "families": sorted(fams, key=lambda f: -f["ms_per_step"])}
