@@ -155,6 +155,21 @@ typedef struct dtb_dt dtb_dt;
 
 int dtb_dt_create(const dtb_dt_config* cfg, dtb_dt** out);
 int dtb_dt_destroy(dtb_dt* h);
+/* Dropout (nn.Dropout at the three GPT-2 sites of the reference's trunk; HF modeling_gpt2 GPT2Model.drop (embd_pdrop),
+ * GPT2Attention.attn_dropout (attn_pdrop, :60-62 of modeling_decision_transformer eager attention) and resid_dropout / GPT2MLP.dropout
+ * (resid_pdrop, :217-218, :236-237); kzl-style DecisionTransformer passes resid_pdrop = attn_pdrop = dropout, default 0.1).
+ * The masks are counter-based and stateless: keep(site, step, idx) = mix32(key(seed, step, site [, b*nh+h]) + idx) >= p * 2^32, drawn
+ * inside the fused kernels (embed LN epilogue, c_proj GEMM epilogues before the residual add, flash-attention P tiles) and recomputed
+ * by their backward kernels; nothing is stored.  `state` = 3 x uint32 in DEVICE memory {seed_lo, seed_hi, step}, caller-owned and
+ * read at kernel run time, so a captured CUDA graph draws fresh masks on every replay: enqueue dtb_dropout_advance() once per
+ * training step (it increments `step`).  All probabilities 0 (or state NULL) = evaluation mode.  Host-side setting: takes effect for
+ * launches enqueued afterwards (re-capture graphs when it changes). */
+int dtb_dt_set_dropout(dtb_dt* h, float embd_pdrop, float attn_pdrop, float resid_pdrop, const void* state);
+int dtb_dropout_advance(void* stream, void* state);
+/* Test / oracle hook: the keep bits of one site exactly as the kernels draw them at the state's current step.
+ * site: 0 embd, 1 + 3l attention of layer l, 2 + 3l / 3 + 3l the residual dropouts after attn / mlp c_proj of layer l.
+ * groups = 0: elementwise sites, out[i] for i < n (i = row * H + col).  groups = B * n_head: attention, out[g * n + i * T + j], n = T*T. */
+int dtb_dropout_mask(void* stream, const void* state, unsigned site, float p, int groups, long long n, unsigned char* out);
 /* Number of parameter tensors (9 + 12 * n_layer + 8) in flat order:
  *  embed_timestep.weight, embed_return.{weight,bias}, embed_state.{weight,bias}, embed_action.{weight,bias}, embed_ln.{weight,bias},
  *  per layer: ln_1.{w,b}, attn.c_attn.{w,b}, attn.c_proj.{w,b}, ln_2.{w,b}, mlp.c_fc.{w,b}, mlp.c_proj.{w,b},

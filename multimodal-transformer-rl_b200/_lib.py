@@ -79,6 +79,9 @@ def _declare(lib):
     lib.dtb_encoder_forward_u8.argtypes = lib.dtb_encoder_forward.argtypes
     lib.dtb_encoder_backward_u8.argtypes = lib.dtb_encoder_backward.argtypes
     lib.dtb_pad_left.argtypes = [vp, i, C.POINTER(vp), C.POINTER(vp), C.POINTER(i), i, i, vp]
+    lib.dtb_dt_set_dropout.argtypes = [vp, f, f, f, vp]
+    lib.dtb_dropout_advance.argtypes = [vp, vp]
+    lib.dtb_dropout_mask.argtypes = [vp, vp, C.c_uint, f, i, ll, vp]
     lib.dtb_masked_mse.argtypes = [vp, vp, vp, vp, i, i, f, vp, vp, vp]
     lib.dtb_heads_fwd.argtypes = [vp] * 8 + [i] * 5 + [vp] * 3
     lib.dtb_embed_fwd.argtypes = [vp] * 15 + [i] * 5 + [f] + [vp] * 5 + [i, i]

@@ -11,9 +11,11 @@ namespace dtb {
 
 template <int D>
 __global__ void __launch_bounds__(128) attn_fwd_kernel(const bf16* __restrict__ qkv, const float* __restrict__ mask, int T, int nh,
-                                                       int Kmask, float scale_log2, bf16* __restrict__ out, float* __restrict__ lse) {
+                                                       int Kmask, float scale_log2, bf16* __restrict__ out, float* __restrict__ lse,
+                                                       const DropSite drop) {
   pdl_trigger();
   pdl_wait();
+  const uint32_t drop_key = drop.state ? drop_group_key(drop_site_key(drop), blockIdx.z * nh + blockIdx.y) : 0u;
   constexpr int P = D + 8;  // smem row pitch (elements): 16-byte pad keeps ldmatrix conflict-free
   extern __shared__ __align__(16) uint8_t smem_att[];
   bf16* sQ = reinterpret_cast<bf16*>(smem_att);
@@ -91,10 +93,16 @@ __global__ void __launch_bounds__(128) attn_fwd_kernel(const bf16* __restrict__ 
     uint32_t pf[4][4];
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      const float p00 = exp2f(s[j][0] - ms0), p01 = exp2f(s[j][1] - ms0);
-      const float p10 = exp2f(s[j][2] - ms1), p11 = exp2f(s[j][3] - ms1);
+      float p00 = exp2f(s[j][0] - ms0), p01 = exp2f(s[j][1] - ms0);
+      float p10 = exp2f(s[j][2] - ms1), p11 = exp2f(s[j][3] - ms1);
       rs0 += p00 + p01;
       rs1 += p10 + p11;
+      if (drop.state) {  // attn_dropout on the softmax weights: the normaliser keeps the undropped sum (HF:60-62)
+        const uint32_t kj = (uint32_t)(k0 + j * 8 + 2 * t4);
+        const uint32_t i0 = drop_key + (uint32_t)qi0 * (uint32_t)T + kj, i1 = drop_key + (uint32_t)qi1 * (uint32_t)T + kj;
+        p00 = drop_apply(p00, i0, 0u, drop.thr, drop.scale); p01 = drop_apply(p01, i0, 1u, drop.thr, drop.scale);
+        p10 = drop_apply(p10, i1, 0u, drop.thr, drop.scale); p11 = drop_apply(p11, i1, 1u, drop.thr, drop.scale);
+      }
       pf[j >> 1][(j & 1) * 2 + 0] = pack_bf16x2(p00, p01);
       pf[j >> 1][(j & 1) * 2 + 1] = pack_bf16x2(p10, p11);
     }
@@ -137,7 +145,8 @@ __global__ void __launch_bounds__(128) attn_fwd_kernel(const bf16* __restrict__ 
 }
 
 template <int D>
-static int launch_fwd(cudaStream_t stream, const bf16* qkv, const float* mask, int B, int T, int nh, bf16* out, float* lse) {
+static int launch_fwd(cudaStream_t stream, const bf16* qkv, const float* mask, int B, int T, int nh, bf16* out, float* lse,
+                      const DropSite& drop) {
   const int smem = 3 * 64 * (D + 8) * 2 + 64 * 4;
   static bool attr = false;
   if (!attr) {
@@ -147,19 +156,21 @@ static int launch_fwd(cudaStream_t stream, const bf16* qkv, const float* mask, i
   const float scale_log2 = 1.4426950408889634f / sqrtf((float)D);
   dim3 grid((T + 63) / 64, nh, B);
   ProfScope prof(stream, PF_ATTN_FWD, 2.0 * B * nh * (double)T * T * D);
-  DTB_LAUNCH(attn_fwd_kernel<D>, grid, 128, smem, stream, qkv, mask, T, nh, T / 3, scale_log2, out, lse);
+  DTB_LAUNCH(attn_fwd_kernel<D>, grid, 128, smem, stream, qkv, mask, T, nh, T / 3, scale_log2, out, lse, drop);
   DTB_CHECK_LAUNCH();
   return DTB_OK;
 }
 
-int attn_fwd(cudaStream_t stream, const bf16* qkv, const float* mask, int B, int T, int nh, int d, bf16* out, float* lse) {
+int attn_fwd(cudaStream_t stream, const bf16* qkv, const float* mask, int B, int T, int nh, int d, bf16* out, float* lse,
+             const DropSite& drop) {
   DTB_REQUIRE(T % 3 == 0 || mask == nullptr, DTB_ERR_BAD_ARG, "attention: T (%d) must be 3*K when a [B,K] mask is given", T);
+  DTB_REQUIRE(drop.state == nullptr || (double)T * T < 4294967296.0, DTB_ERR_UNSUPPORTED, "attention dropout: T too large");
   if (B == 0 || T == 0) return DTB_OK;
-  if (attn_tc_supported(T, d)) return attn_fwd_tc(stream, qkv, mask, B, T, nh, d, out, lse);
+  if (attn_tc_supported(T, d)) return attn_fwd_tc(stream, qkv, mask, B, T, nh, d, out, lse, drop);
   switch (d) {
-    case 32: return launch_fwd<32>(stream, qkv, mask, B, T, nh, out, lse);
-    case 64: return launch_fwd<64>(stream, qkv, mask, B, T, nh, out, lse);
-    case 128: return launch_fwd<128>(stream, qkv, mask, B, T, nh, out, lse);
+    case 32: return launch_fwd<32>(stream, qkv, mask, B, T, nh, out, lse, drop);
+    case 64: return launch_fwd<64>(stream, qkv, mask, B, T, nh, out, lse, drop);
+    case 128: return launch_fwd<128>(stream, qkv, mask, B, T, nh, out, lse, drop);
     default: set_error("attention: head_dim %d unsupported (32, 64, 128)", d); return DTB_ERR_UNSUPPORTED;
   }
 }

@@ -12,9 +12,11 @@ template <int D>
 __global__ void __launch_bounds__(128) attn_bwd_dq_kernel(const bf16* __restrict__ qkv, const float* __restrict__ mask,
                                                           const bf16* __restrict__ out, const bf16* __restrict__ dout,
                                                           const float* __restrict__ lse, int T, int nh, int Kmask, float scale,
-                                                          float scale_log2, bf16* __restrict__ dqkv, float* __restrict__ delta) {
+                                                          float scale_log2, bf16* __restrict__ dqkv, float* __restrict__ delta,
+                                                          const DropSite drop) {
   pdl_trigger();
   pdl_wait();
+  const uint32_t drop_key = drop.state ? drop_group_key(drop_site_key(drop), blockIdx.z * nh + blockIdx.y) : 0u;
   constexpr int P = D + 8;
   extern __shared__ __align__(16) uint8_t smem_att[];
   bf16* sQ = reinterpret_cast<bf16*>(smem_att);
@@ -108,8 +110,13 @@ __global__ void __launch_bounds__(128) attn_bwd_dq_kernel(const bf16* __restrict
         const bool kv = sValid[kl] > 0.f;
         const float p0 = (kv && kj <= qi0) ? exp2f(s[j][e] * scale_log2 - lse0) : 0.f;
         const float p1 = (kv && kj <= qi1) ? exp2f(s[j][2 + e] * scale_log2 - lse1) : 0.f;
-        ds[e] = p0 * (dp[j][e] - dl0) * scale;
-        ds[2 + e] = p1 * (dp[j][2 + e] - dl1) * scale;
+        float g0 = dp[j][e], g1 = dp[j][2 + e];
+        if (drop.state) {  // dP = D o (dO V^T), D = keep / (1 - p): the bits of the forward pass
+          g0 = drop_apply(g0, drop_key, (uint32_t)qi0 * (uint32_t)T + (uint32_t)kj, drop.thr, drop.scale);
+          g1 = drop_apply(g1, drop_key, (uint32_t)qi1 * (uint32_t)T + (uint32_t)kj, drop.thr, drop.scale);
+        }
+        ds[e] = p0 * (g0 - dl0) * scale;
+        ds[2 + e] = p1 * (g1 - dl1) * scale;
       }
       dsf[j >> 1][(j & 1) * 2 + 0] = pack_bf16x2(ds[0], ds[1]);
       dsf[j >> 1][(j & 1) * 2 + 1] = pack_bf16x2(ds[2], ds[3]);
@@ -138,9 +145,10 @@ template <int D>
 __global__ void __launch_bounds__(128) attn_bwd_dkv_kernel(const bf16* __restrict__ qkv, const float* __restrict__ mask,
                                                            const bf16* __restrict__ dout, const float* __restrict__ lse,
                                                            const float* __restrict__ delta, int T, int nh, int Kmask, float scale,
-                                                           float scale_log2, bf16* __restrict__ dqkv) {
+                                                           float scale_log2, bf16* __restrict__ dqkv, const DropSite drop) {
   pdl_trigger();
   pdl_wait();
+  const uint32_t drop_key = drop.state ? drop_group_key(drop_site_key(drop), blockIdx.z * nh + blockIdx.y) : 0u;
   constexpr int P = D + 8;
   extern __shared__ __align__(16) uint8_t smem_att[];
   bf16* sK = reinterpret_cast<bf16*>(smem_att);
@@ -221,8 +229,20 @@ __global__ void __launch_bounds__(128) attn_bwd_dkv_kernel(const bf16* __restric
         const bool qok = qi < T;
         p[e] = (qok && kv0 && kj0 <= qi) ? exp2f(st[j][e] * scale_log2 - l) : 0.f;
         p[2 + e] = (qok && kv1 && kj1 <= qi) ? exp2f(st[j][2 + e] * scale_log2 - l) : 0.f;
-        ds[e] = p[e] * (dpt[j][e] - dl) * scale;
-        ds[2 + e] = p[2 + e] * (dpt[j][2 + e] - dl) * scale;
+        float g0 = dpt[j][e], g1 = dpt[j][2 + e];
+        if (drop.state) {
+          const uint32_t base_i = drop_key + (uint32_t)qi * (uint32_t)T;
+          const bool k0_keep = drop_keep(base_i, (uint32_t)kj0, drop.thr), k1_keep = drop_keep(base_i, (uint32_t)kj1, drop.thr);
+          g0 = k0_keep ? g0 * drop.scale : 0.f;
+          g1 = k1_keep ? g1 * drop.scale : 0.f;
+          ds[e] = p[e] * (g0 - dl) * scale;
+          ds[2 + e] = p[2 + e] * (g1 - dl) * scale;
+          p[e] = k0_keep ? p[e] * drop.scale : 0.f;          // dV = (P o D)^T dO
+          p[2 + e] = k1_keep ? p[2 + e] * drop.scale : 0.f;
+        } else {
+          ds[e] = p[e] * (g0 - dl) * scale;
+          ds[2 + e] = p[2 + e] * (g1 - dl) * scale;
+        }
       }
       pf[j >> 1][(j & 1) * 2 + 0] = pack_bf16x2(p[0], p[1]);
       pf[j >> 1][(j & 1) * 2 + 1] = pack_bf16x2(p[2], p[3]);
@@ -262,7 +282,7 @@ __global__ void __launch_bounds__(128) attn_bwd_dkv_kernel(const bf16* __restric
 
 template <int D>
 static int launch_bwd(cudaStream_t stream, const bf16* qkv, const float* mask, const bf16* out, const bf16* dout, const float* lse, int B,
-                      int T, int nh, bf16* dqkv, float* delta) {
+                      int T, int nh, bf16* dqkv, float* delta, const DropSite& drop) {
   const int smem = 4 * 64 * (D + 8) * 2 + 3 * 64 * 4;
   static bool attr = false;
   if (!attr) {
@@ -274,22 +294,22 @@ static int launch_bwd(cudaStream_t stream, const bf16* qkv, const float* mask, c
   const float scale_log2 = 1.4426950408889634f * scale;
   dim3 grid((T + 63) / 64, nh, B);
   ProfScope prof(stream, PF_ATTN_BWD, 5.0 * B * nh * (double)T * T * D);
-  DTB_LAUNCH(attn_bwd_dq_kernel<D>, grid, 128, smem, stream, qkv, mask, out, dout, lse, T, nh, T / 3, scale, scale_log2, dqkv, delta);
+  DTB_LAUNCH(attn_bwd_dq_kernel<D>, grid, 128, smem, stream, qkv, mask, out, dout, lse, T, nh, T / 3, scale, scale_log2, dqkv, delta, drop);
   DTB_CHECK_LAUNCH();
-  DTB_LAUNCH(attn_bwd_dkv_kernel<D>, grid, 128, smem, stream, qkv, mask, dout, lse, delta, T, nh, T / 3, scale, scale_log2, dqkv);
+  DTB_LAUNCH(attn_bwd_dkv_kernel<D>, grid, 128, smem, stream, qkv, mask, dout, lse, delta, T, nh, T / 3, scale, scale_log2, dqkv, drop);
   DTB_CHECK_LAUNCH();
   return DTB_OK;
 }
 
 int attn_bwd(cudaStream_t stream, const bf16* qkv, const float* mask, const bf16* out, const bf16* dout, const float* lse, int B, int T,
-             int nh, int d, bf16* dqkv, float* delta) {
+             int nh, int d, bf16* dqkv, float* delta, const DropSite& drop) {
   DTB_REQUIRE(T % 3 == 0 || mask == nullptr, DTB_ERR_BAD_ARG, "attention bwd: T (%d) must be 3*K when a [B,K] mask is given", T);
   if (B == 0 || T == 0) return DTB_OK;
-  if (attn_tc_supported(T, d)) return attn_bwd_tc(stream, qkv, mask, out, dout, lse, B, T, nh, d, dqkv, delta);
+  if (attn_tc_supported(T, d)) return attn_bwd_tc(stream, qkv, mask, out, dout, lse, B, T, nh, d, dqkv, delta, drop);
   switch (d) {
-    case 32: return launch_bwd<32>(stream, qkv, mask, out, dout, lse, B, T, nh, dqkv, delta);
-    case 64: return launch_bwd<64>(stream, qkv, mask, out, dout, lse, B, T, nh, dqkv, delta);
-    case 128: return launch_bwd<128>(stream, qkv, mask, out, dout, lse, B, T, nh, dqkv, delta);
+    case 32: return launch_bwd<32>(stream, qkv, mask, out, dout, lse, B, T, nh, dqkv, delta, drop);
+    case 64: return launch_bwd<64>(stream, qkv, mask, out, dout, lse, B, T, nh, dqkv, delta, drop);
+    case 128: return launch_bwd<128>(stream, qkv, mask, out, dout, lse, B, T, nh, dqkv, delta, drop);
     default: set_error("attention bwd: head_dim %d unsupported (32, 64, 128)", d); return DTB_ERR_UNSUPPORTED;
   }
 }

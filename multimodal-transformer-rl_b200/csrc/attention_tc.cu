@@ -19,7 +19,8 @@
 namespace dtb {
 
 constexpr int AT_D = 64;
-constexpr int AT_THREADS = 192;
+constexpr int AT_THREADS = 192;      // forward: warps 0-3 softmax, 4 MMA, 5 TMA
+constexpr int AT_BWD_THREADS = 320;  // backward: warps 0-7 compute (warp w and w+4 share TMEM lane quadrant w & 3, 32 columns each), 8 MMA, 9 TMA
 constexpr int AT_TILE128 = 128 * 128;  // bytes: 128 rows x 128 B (64 bf16)
 constexpr int AT_TILE64 = 64 * 128;    // bytes: 64 rows x 128 B
 constexpr int AT_KV_STAGES = 3;        // TMA ring depth for the streamed 64-row blocks (prefetch distance 2 blocks ~ TMA latency)
@@ -35,7 +36,13 @@ struct AttnTcParams {
   float* lse;
   bf16* dqkv;
   float* delta;
+  DropSite drop;        // attn_dropout on the softmax weights (group = b * nh + h, idx = i * T + j); state == nullptr: off
 };
+
+// this CTA's dropout key (0 threshold = off: callers branch on it, warp-uniformly)
+__device__ __forceinline__ uint32_t at_drop_key(const AttnTcParams& p, int b, int h) {
+  return p.drop.state ? drop_group_key(drop_site_key(p.drop), (uint32_t)(b * p.nh + h)) : 0u;
+}
 
 // key-validity bits of the 64-key block starting at k0: bit l of word c <=> key k0 + 32c + l is in range and not padding
 __device__ __forceinline__ void at_valid_bits(const AttnTcParams& p, int b, int k0, int lane, uint32_t (&bits)[2]) {
@@ -183,6 +190,8 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
     const int qi = q0 + r;
     const uint32_t lane_addr = (uint32_t)(warp * 32) << 16;
     float m_use = -INFINITY, l = 0.f;
+    const uint32_t dthr = p.drop.state ? p.drop.thr : 0u;
+    const uint32_t drow = at_drop_key(p, b, h) + (uint32_t)qi * (uint32_t)T;
     for (int j = 0; j < nkb; ++j) {
       const int k0 = j * 64;
       const uint32_t bits[2] = {sBits[2 * j], sBits[2 * j + 1]};
@@ -251,6 +260,10 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
 #pragma unroll
           for (int e = 0; e < 8; ++e) f[e] = fast_exp2(fmaf(__uint_as_float(v0[u * 8 + e]), p.scale_log2, nms));
           rsa += f[0] + f[4]; rsb += f[1] + f[5]; rsc += f[2] + f[6]; rsd += f[3] + f[7];
+          if (dthr) {  // dropped weights leave the PV product, not the normaliser; 1 / (1 - p) is applied to O at the end
+#pragma unroll
+            for (int e = 0; e < 8; ++e) f[e] = drop_keep(drow, (uint32_t)(k0 + u * 8 + e), dthr) ? f[e] : 0.f;
+          }
           at_store_row_unit(p_tile, r, u, pack_bf16x2(f[0], f[1]), pack_bf16x2(f[2], f[3]), pack_bf16x2(f[4], f[5]), pack_bf16x2(f[6], f[7]));
         }
       } else {
@@ -264,6 +277,10 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
 #pragma unroll
           for (int e = 0; e < 8; ++e) f[e] = fast_exp2(fmaf(__uint_as_float(v1[u * 8 + e]), p.scale_log2, nms));
           rsa += f[0] + f[4]; rsb += f[1] + f[5]; rsc += f[2] + f[6]; rsd += f[3] + f[7];
+          if (dthr) {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) f[e] = drop_keep(drow, (uint32_t)(k0 + 32 + u * 8 + e), dthr) ? f[e] : 0.f;
+          }
           at_store_row_unit(p_tile, r, 4 + u, pack_bf16x2(f[0], f[1]), pack_bf16x2(f[2], f[3]), pack_bf16x2(f[4], f[5]), pack_bf16x2(f[6], f[7]));
         }
       } else {
@@ -294,7 +311,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
     // ---- epilogue: O / l -> bf16, lse ----
     mbar_wait(&pv_done[(nkb - 1) & 1], ((nkb - 1) >> 1) & 1);
     tc_fence_after();
-    const float inv = l > 0.f ? 1.f / l : 0.f;
+    const float inv = l > 0.f ? (dthr ? p.drop.scale : 1.f) / l : 0.f;
     bf16* orow = p.out + ((size_t)b * T + qi) * H + h * AT_D;
 #pragma unroll
     for (int c = 0; c < 2; ++c) {
@@ -327,8 +344,10 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
 constexpr int AT_DQ_KST = 3, AT_DQ_VST = 2;
 
 // one 32-column half of a row: P = exp2(s * scale_log2 - lse), dS = P (dP - delta) / sqrt(d) -> bf16 units u0..u0+3 of the dS tile row
+// dropout (dthr != 0): dP = D o (dO V^T) with D = keep / (1 - p) recomputed from dbase + column
 __device__ __forceinline__ void at_ds_half(const uint32_t (&sv)[32], const uint32_t (&dv)[32], uint32_t word, float scale_log2, float nlse,
-                                           float delta, float scale, uint32_t tile, int r, int u0) {
+                                           float delta, float scale, uint32_t tile, int r, int u0, uint32_t dbase, uint32_t dthr,
+                                           float dscale) {
 #pragma unroll
   for (int u = 0; u < 4; ++u) {
     float f[8];
@@ -337,13 +356,15 @@ __device__ __forceinline__ void at_ds_half(const uint32_t (&sv)[32], const uint3
       const int c = u * 8 + e;
       float pe = fast_exp2(fmaf(__uint_as_float(sv[c]), scale_log2, nlse));
       pe = (word & (1u << c)) ? pe : 0.f;
-      f[e] = pe * (__uint_as_float(dv[c]) - delta) * scale;
+      float g = __uint_as_float(dv[c]);
+      if (dthr) g = drop_keep(dbase, (uint32_t)c, dthr) ? g * dscale : 0.f;
+      f[e] = pe * (g - delta) * scale;
     }
     at_store_row_unit(tile, r, u0 + u, pack_bf16x2(f[0], f[1]), pack_bf16x2(f[2], f[3]), pack_bf16x2(f[4], f[5]), pack_bf16x2(f[6], f[7]));
   }
 }
 
-__global__ void __launch_bounds__(AT_THREADS, 2)
+__global__ void __launch_bounds__(AT_BWD_THREADS, 2)
 attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmKV,
                       const __grid_constant__ CUtensorMap tmDO, const AttnTcParams p) {
   extern __shared__ uint8_t smem_raw[];
@@ -360,8 +381,8 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
   uint64_t* v_full = bars + 7;      // [2]
   uint64_t* v_free = bars + 9;      // [2]
   uint64_t* sdp_full = bars + 11;   // [1] MMA -> threads
-  uint64_t* sdp_free = bars + 12;   // [1] threads (128) -> MMA
-  uint64_t* ds_full = bars + 13;    // [2] threads (128) -> MMA
+  uint64_t* sdp_free = bars + 12;   // [1] threads (256) -> MMA
+  uint64_t* ds_full = bars + 13;    // [2] threads (256) -> MMA
   uint64_t* ds_done = bars + 15;    // [2] MMA -> threads
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 17);
   uint32_t* sBits = reinterpret_cast<uint32_t*>(bars + 18);
@@ -379,12 +400,12 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
     mbar_init(qdo_full, 1);
     for (int s = 0; s < AT_DQ_KST; ++s) { mbar_init(&k_full[s], 1); mbar_init(&k_free[s], 1); }
     for (int s = 0; s < AT_DQ_VST; ++s) { mbar_init(&v_full[s], 1); mbar_init(&v_free[s], 1); }
-    for (int s = 0; s < 2; ++s) { mbar_init(&ds_full[s], 128); mbar_init(&ds_done[s], 1); }
+    for (int s = 0; s < 2; ++s) { mbar_init(&ds_full[s], 256); mbar_init(&ds_done[s], 1); }
     mbar_init(sdp_full, 1);
-    mbar_init(sdp_free, 128);
+    mbar_init(sdp_free, 256);
     fence_mbar_init();
   }
-  if (warp == 4) { tmem_alloc(tmem_slot, 256); tmem_relinquish(); }
+  if (warp == 8) { tmem_alloc(tmem_slot, 256); tmem_relinquish(); }
   pdl_trigger();  // prologue done: the next kernel of the stream may start its own
   pdl_wait();     // the previous kernel's results are complete and visible from here on
   at_fill_valid_bits(p, b, 2 * nkb, sBits);
@@ -395,7 +416,7 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
   const uint32_t tS = tmem_base, tDP = tmem_base + 64, tDQ = tmem_base + 128;
   const int H = p.nh * AT_D;
 
-  if (warp == 5) {
+  if (warp == 9) {
     if (lane == 0) {
       tma_prefetch_desc(&tmQ); tma_prefetch_desc(&tmKV); tma_prefetch_desc(&tmDO);
       mbar_arrive_expect_tx(qdo_full, 2 * AT_TILE128);
@@ -411,7 +432,7 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
         tma_load_3d(sV + sv * AT_TILE64, &tmKV, &v_full[sv], 2 * H + h * AT_D, j * 64, b);
       }
     }
-  } else if (warp == 4) {
+  } else if (warp == 8) {
     if (lane == 0) {
       const uint32_t idesc_kk = make_idesc_bf16(128, 64, 0, 0), idesc_kn = make_idesc_bf16(128, 64, 0, 1);
       const uint32_t q_addr = smem_u32(sQ), do_addr = smem_u32(sDO);
@@ -450,12 +471,16 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
       }
     }
   } else {
-    const int r = warp * 32 + lane;
+    // warp w (0-7): rows 32 (w & 3) .. +31 (its TMEM lane quadrant), columns 32 (w >> 2) .. +31 of every 64-key block
+    const int qd = warp & 3, half = warp >> 2;
+    const int r = qd * 32 + lane;
     const int qi = q0 + r;
-    const uint32_t lane_addr = (uint32_t)(warp * 32) << 16;
+    const uint32_t lane_addr = ((uint32_t)(qd * 32) << 16) + 32 * half;
     const size_t row_off = ((size_t)b * p.nh + h) * T;
-    // delta = rowsum(dO * O) for this thread's row, straight from global (128 B each)
+    // delta = rowsum(dO * O) for this thread's row, straight from global (128 B each; both warps of a row compute it, one stores it)
     float delta = 0.f, nlse = 0.f;
+    const uint32_t dthr = p.drop.state ? p.drop.thr : 0u;
+    const uint32_t drow = at_drop_key(p, b, h) + (uint32_t)qi * (uint32_t)T;
     if (qi < T) {
       const uint4* orow = reinterpret_cast<const uint4*>(p.out_in + ((size_t)b * T + qi) * H + h * AT_D);
       const uint4* drow = reinterpret_cast<const uint4*>(p.dout + ((size_t)b * T + qi) * H + h * AT_D);
@@ -469,60 +494,48 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
           delta += x.x * y.x + x.y * y.y;
         }
       }
-      p.delta[row_off + qi] = delta;
+      if (half == 0) p.delta[row_off + qi] = delta;
       nlse = -__ldg(p.lse_in + row_off + qi);
     }
     for (int j = 0; j < nkb; ++j) {
-      const int k0 = j * 64;
-      const uint32_t bits[2] = {sBits[2 * j], sBits[2 * j + 1]};
-      const bool diag = k0 + 63 > q0;
-      const bool act0 = !diag || (k0 <= q0 + warp * 32 + 31), act1 = !diag || (k0 + 32 <= q0 + warp * 32 + 31);
-      uint32_t m0 = 0u, m1 = 0u;
-      if (act0) m0 = bits[0] & (diag ? at_causal_word(qi - k0) : 0xffffffffu);
-      if (act1) m1 = bits[1] & (diag ? at_causal_word(qi - k0 - 32) : 0xffffffffu);
+      const int k0 = j * 64 + 32 * half;  // first key of this warp's 32-key chunk
+      const bool diag = j * 64 + 63 > q0;
+      const bool act = !diag || (k0 <= q0 + qd * 32 + 31);
+      uint32_t m = 0u;
+      if (act) m = sBits[2 * j + half] & (diag ? at_causal_word(qi - k0) : 0xffffffffu);
       const int db = j & 1;
       const uint32_t tile = smem_u32(sDS + db * AT_TILE128);
       mbar_wait(sdp_full, j & 1);
       tc_fence_after();
-      if (j >= 2) mbar_wait(&ds_done[db], ((j - 2) >> 1) & 1);  // dS buffer db was last read by the dQ MMAs of block j - 2
       uint32_t sv[32], dv[32];
-      if (act0) {
+      if (act) {
         tmem_ld_32x32(tS + lane_addr, sv);
         tmem_ld_32x32(tDP + lane_addr, dv);
-        tmem_ld_wait();
-        at_ds_half(sv, dv, m0, p.scale_log2, nlse, delta, p.scale, tile, r, 0);
-      } else {
-#pragma unroll
-        for (int u = 0; u < 4; ++u) at_store_row_unit(tile, r, u, 0u, 0u, 0u, 0u);
-      }
-      if (act1) {
-        tmem_ld_32x32(tS + lane_addr + 32, sv);
-        tmem_ld_32x32(tDP + lane_addr + 32, dv);
         tmem_ld_wait();
       }
       tc_fence_before();
       mbar_arrive(sdp_free);  // S / dP of this block are in registers: the next block's MMAs may overwrite them
-      if (act1) {
-        at_ds_half(sv, dv, m1, p.scale_log2, nlse, delta, p.scale, tile, r, 4);
+      if (j >= 2) mbar_wait(&ds_done[db], ((j - 2) >> 1) & 1);  // dS buffer db was last read by the dQ MMAs of block j - 2
+      if (act) {
+        at_ds_half(sv, dv, m, p.scale_log2, nlse, delta, p.scale, tile, r, 4 * half, drow + (uint32_t)k0, dthr, p.drop.scale);
       } else {
 #pragma unroll
-        for (int u = 0; u < 4; ++u) at_store_row_unit(tile, r, 4 + u, 0u, 0u, 0u, 0u);
+        for (int u = 0; u < 4; ++u) at_store_row_unit(tile, r, 4 * half + u, 0u, 0u, 0u, 0u);
       }
       fence_proxy_async();
       mbar_arrive(&ds_full[db]);
     }
     mbar_wait(&ds_done[(nkb - 1) & 1], ((nkb - 1) >> 1) & 1);
     tc_fence_after();
-    bf16* grow = p.dqkv + ((size_t)b * T + qi) * 3 * H + h * AT_D;
-#pragma unroll
-    for (int c = 0; c < 2; ++c) {
+    bf16* grow = p.dqkv + ((size_t)b * T + qi) * 3 * H + h * AT_D + 32 * half;
+    {
       uint32_t o[32];
-      tmem_ld_32x32(tDQ + lane_addr + c * 32, o);
+      tmem_ld_32x32(tDQ + lane_addr, o);
       tmem_ld_wait();
       if (qi < T) {
 #pragma unroll
         for (int e = 0; e < 32; e += 8)
-          *reinterpret_cast<uint4*>(grow + c * 32 + e) =
+          *reinterpret_cast<uint4*>(grow + e) =
               make_uint4(pack_bf16x2(__uint_as_float(o[e]), __uint_as_float(o[e + 1])), pack_bf16x2(__uint_as_float(o[e + 2]), __uint_as_float(o[e + 3])),
                          pack_bf16x2(__uint_as_float(o[e + 4]), __uint_as_float(o[e + 5])), pack_bf16x2(__uint_as_float(o[e + 6]), __uint_as_float(o[e + 7])));
       }
@@ -530,7 +543,7 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 4) { tc_fence_after(); tmem_dealloc(tmem_base, 256); }
+  if (warp == 8) { tc_fence_after(); tmem_dealloc(tmem_base, 256); }
 }
 
 // ================================================================================================================================
@@ -540,7 +553,7 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
 // TMEM (256 columns): S^T at 0, dP^T at 64, dV at 128, dK at 192
 constexpr int AT_MAX_T_BWD = 1024;
 
-__global__ void __launch_bounds__(AT_THREADS, 2)
+__global__ void __launch_bounds__(AT_BWD_THREADS, 2)
 attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmKV, const __grid_constant__ CUtensorMap tmQ64,
                        const __grid_constant__ CUtensorMap tmDO64, const AttnTcParams p) {
   extern __shared__ uint8_t smem_raw[];
@@ -556,8 +569,8 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmKV, const __grid_co
   uint64_t* qdo_full = bars + 1;    // [2]
   uint64_t* qdo_free = bars + 3;    // [2]
   uint64_t* sdp_full = bars + 5;    // [1]
-  uint64_t* sdp_free = bars + 6;    // [1] (128)
-  uint64_t* pds_full = bars + 7;    // [1] (128)
+  uint64_t* sdp_free = bars + 6;    // [1] (256)
+  uint64_t* pds_full = bars + 7;    // [1] (256)
   uint64_t* pds_done = bars + 8;    // [1]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 9);
   float* sLse = reinterpret_cast<float*>(bars + 10);
@@ -574,12 +587,12 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmKV, const __grid_co
     mbar_init(kv_full, 1);
     for (int s = 0; s < 2; ++s) { mbar_init(&qdo_full[s], 1); mbar_init(&qdo_free[s], 1); }
     mbar_init(sdp_full, 1);
-    mbar_init(sdp_free, 128);
-    mbar_init(pds_full, 128);
+    mbar_init(sdp_free, 256);
+    mbar_init(pds_full, 256);
     mbar_init(pds_done, 1);
     fence_mbar_init();
   }
-  if (warp == 4) { tmem_alloc(tmem_slot, 256); tmem_relinquish(); }
+  if (warp == 8) { tmem_alloc(tmem_slot, 256); tmem_relinquish(); }
   pdl_trigger();  // prologue done: the next kernel of the stream may start its own
   pdl_wait();     // the previous kernel's results are complete and visible from here on
   for (int t = i0 * 64 + threadIdx.x; t < nqb * 64; t += blockDim.x) {
@@ -593,7 +606,7 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmKV, const __grid_co
   const uint32_t tST = tmem_base, tDPT = tmem_base + 64, tDV = tmem_base + 128, tDK = tmem_base + 192;
   const int H = p.nh * AT_D;
 
-  if (warp == 5) {
+  if (warp == 9) {
     if (lane == 0) {
       tma_prefetch_desc(&tmKV); tma_prefetch_desc(&tmQ64); tma_prefetch_desc(&tmDO64);
       mbar_arrive_expect_tx(kv_full, 2 * AT_TILE128);
@@ -607,7 +620,7 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmKV, const __grid_co
         tma_load_3d(sDO + s * AT_TILE64, &tmDO64, &qdo_full[s], h * AT_D, (i0 + t) * 64, b);
       }
     }
-  } else if (warp == 4) {
+  } else if (warp == 8) {
     if (lane == 0) {
       const uint32_t idesc_kk = make_idesc_bf16(128, 64, 0, 0), idesc_kn = make_idesc_bf16(128, 64, 0, 1);
       const uint32_t k_addr = smem_u32(sK), v_addr = smem_u32(sV), pt_addr = smem_u32(sPT), dst_addr = smem_u32(sDST);
@@ -648,57 +661,65 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmKV, const __grid_co
       }
     }
   } else {
-    const int r = warp * 32 + lane;
+    // warp w (0-7): keys 32 (w & 3) .. +31 (its TMEM lane quadrant), queries 32 (w >> 2) .. +31 of every 64-query block
+    const int qd = warp & 3, half = warp >> 2;
+    const int r = qd * 32 + lane;
     const int kj = k0 + r;
-    const uint32_t lane_addr = (uint32_t)(warp * 32) << 16;
+    const uint32_t lane_addr = ((uint32_t)(qd * 32) << 16) + 32 * half;
     const bool key_ok = kj < T && (p.mask == nullptr || __ldg(p.mask + (size_t)b * p.Kmask + kj / 3) > 0.f);
+    const uint32_t dthr = p.drop.state ? p.drop.thr : 0u;
+    const uint32_t dcol = at_drop_key(p, b, h) + (uint32_t)kj;
     const uint32_t pt_tile = smem_u32(sPT), dst_tile = smem_u32(sDST);
     for (int t = 0; t < n; ++t) {
-      const int qs = (i0 + t) * 64;  // first query of the block
+      const int qc = (i0 + t) * 64 + 32 * half;             // first query of this warp's 32-wide chunk
+      const bool act = qc + 31 >= k0 + qd * 32 && qc < T;   // some (query, key) pair of this warp's rows is on or below the diagonal
       mbar_wait(sdp_full, t & 1);
       tc_fence_after();
+      uint32_t sv[32], dv[32];
+      if (act) {
+        tmem_ld_32x32(tST + lane_addr, sv);
+        tmem_ld_32x32(tDPT + lane_addr, dv);
+        tmem_ld_wait();
+      }
+      tc_fence_before();
+      mbar_arrive(sdp_free);
       if (t > 0) mbar_wait(pds_done, (t - 1) & 1);  // P^T / dS^T were read by the previous block's dV / dK MMAs
+      if (act) {
+        // allowed queries of the chunk for this key: kj <= q < T
+        const int lo = kj - qc, hi = T - qc;
+        uint32_t word = lo <= 0 ? 0xffffffffu : (lo >= 32 ? 0u : ~((1u << lo) - 1u));
+        word &= hi >= 32 ? 0xffffffffu : ((1u << hi) - 1u);
+        if (!key_ok) word = 0u;
 #pragma unroll
-      for (int c = 0; c < 2; ++c) {
-        const int qc = qs + 32 * c;                           // first query of the 32-wide chunk
-        const bool act = qc + 31 >= k0 + warp * 32 && qc < T;  // some (query, key) pair of this warp's rows is on or below the diagonal
-        if (act) {
-          // allowed queries of the chunk for this key: kj <= q < T
-          const int lo = kj - qc, hi = T - qc;
-          uint32_t word = lo <= 0 ? 0xffffffffu : (lo >= 32 ? 0u : ~((1u << lo) - 1u));
-          word &= hi >= 32 ? 0xffffffffu : ((1u << hi) - 1u);
-          if (!key_ok) word = 0u;
-          uint32_t sv[32], dv[32];
-          tmem_ld_32x32(tST + lane_addr + 32 * c, sv);
-          tmem_ld_32x32(tDPT + lane_addr + 32 * c, dv);
-          tmem_ld_wait();
-          if (c == 1) { tc_fence_before(); mbar_arrive(sdp_free); }
+        for (int u = 0; u < 4; ++u) {
+          float pf[8], df[8];
+          const float4 l0 = *reinterpret_cast<const float4*>(sLse + qc + u * 8), l1 = *reinterpret_cast<const float4*>(sLse + qc + u * 8 + 4);
+          const float4 d0 = *reinterpret_cast<const float4*>(sDelta + qc + u * 8), d1 = *reinterpret_cast<const float4*>(sDelta + qc + u * 8 + 4);
+          const float nl[8] = {l0.x, l0.y, l0.z, l0.w, l1.x, l1.y, l1.z, l1.w}, dl[8] = {d0.x, d0.y, d0.z, d0.w, d1.x, d1.y, d1.z, d1.w};
 #pragma unroll
-          for (int u = 0; u < 4; ++u) {
-            float pf[8], df[8];
-            const float4 l0 = *reinterpret_cast<const float4*>(sLse + qc + u * 8), l1 = *reinterpret_cast<const float4*>(sLse + qc + u * 8 + 4);
-            const float4 d0 = *reinterpret_cast<const float4*>(sDelta + qc + u * 8), d1 = *reinterpret_cast<const float4*>(sDelta + qc + u * 8 + 4);
-            const float nl[8] = {l0.x, l0.y, l0.z, l0.w, l1.x, l1.y, l1.z, l1.w}, dl[8] = {d0.x, d0.y, d0.z, d0.w, d1.x, d1.y, d1.z, d1.w};
-#pragma unroll
-            for (int e = 0; e < 8; ++e) {
-              const int col = u * 8 + e;
-              float pe = fast_exp2(fmaf(__uint_as_float(sv[col]), p.scale_log2, nl[e]));
-              pe = (word & (1u << col)) ? pe : 0.f;
-              pf[e] = pe;
-              df[e] = pe * (__uint_as_float(dv[col]) - dl[e]) * p.scale;
+          for (int e = 0; e < 8; ++e) {
+            const int col = u * 8 + e;
+            float pe = fast_exp2(fmaf(__uint_as_float(sv[col]), p.scale_log2, nl[e]));
+            pe = (word & (1u << col)) ? pe : 0.f;
+            float g = __uint_as_float(dv[col]);
+            bool keep = true;
+            if (dthr) {  // bit of (query qc + col, key kj); dV's 1 / (1 - p) is applied once in the epilogue
+              keep = drop_keep(dcol, (uint32_t)(qc + col) * (uint32_t)T, dthr);
+              g = keep ? g * p.drop.scale : 0.f;
             }
-            at_store_row_unit(pt_tile, r, 4 * c + u, pack_bf16x2(pf[0], pf[1]), pack_bf16x2(pf[2], pf[3]), pack_bf16x2(pf[4], pf[5]),
-                              pack_bf16x2(pf[6], pf[7]));
-            at_store_row_unit(dst_tile, r, 4 * c + u, pack_bf16x2(df[0], df[1]), pack_bf16x2(df[2], df[3]), pack_bf16x2(df[4], df[5]),
-                              pack_bf16x2(df[6], df[7]));
+            pf[e] = keep ? pe : 0.f;
+            df[e] = pe * (g - dl[e]) * p.scale;
           }
-        } else {
-          if (c == 1) { tc_fence_before(); mbar_arrive(sdp_free); }
+          at_store_row_unit(pt_tile, r, 4 * half + u, pack_bf16x2(pf[0], pf[1]), pack_bf16x2(pf[2], pf[3]), pack_bf16x2(pf[4], pf[5]),
+                            pack_bf16x2(pf[6], pf[7]));
+          at_store_row_unit(dst_tile, r, 4 * half + u, pack_bf16x2(df[0], df[1]), pack_bf16x2(df[2], df[3]), pack_bf16x2(df[4], df[5]),
+                            pack_bf16x2(df[6], df[7]));
+        }
+      } else {
 #pragma unroll
-          for (int u = 0; u < 4; ++u) {
-            at_store_row_unit(pt_tile, r, 4 * c + u, 0u, 0u, 0u, 0u);
-            at_store_row_unit(dst_tile, r, 4 * c + u, 0u, 0u, 0u, 0u);
-          }
+        for (int u = 0; u < 4; ++u) {
+          at_store_row_unit(pt_tile, r, 4 * half + u, 0u, 0u, 0u, 0u);
+          at_store_row_unit(dst_tile, r, 4 * half + u, 0u, 0u, 0u, 0u);
         }
       }
       fence_proxy_async();
@@ -706,28 +727,29 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmKV, const __grid_co
     }
     mbar_wait(pds_done, (n - 1) & 1);
     tc_fence_after();
-    bf16* grow = p.dqkv + ((size_t)b * T + kj) * 3 * H + h * AT_D;
+    bf16* grow = p.dqkv + ((size_t)b * T + kj) * 3 * H + h * AT_D + 32 * half;
 #pragma unroll
     for (int which = 0; which < 2; ++which) {  // 0: dV -> columns 2H.., 1: dK -> columns H..
+      uint32_t o[32];
+      tmem_ld_32x32((which == 0 ? tDV : tDK) + lane_addr, o);
+      tmem_ld_wait();
+      if (which == 0 && dthr) {
 #pragma unroll
-      for (int c = 0; c < 2; ++c) {
-        uint32_t o[32];
-        tmem_ld_32x32((which == 0 ? tDV : tDK) + lane_addr + c * 32, o);
-        tmem_ld_wait();
-        if (kj < T) {
-          bf16* dst = grow + (which == 0 ? 2 * H : H) + c * 32;
+        for (int e = 0; e < 32; ++e) o[e] = __float_as_uint(__uint_as_float(o[e]) * p.drop.scale);
+      }
+      if (kj < T) {
+        bf16* dst = grow + (which == 0 ? 2 * H : H);
 #pragma unroll
-          for (int e = 0; e < 32; e += 8)
-            *reinterpret_cast<uint4*>(dst + e) =
-                make_uint4(pack_bf16x2(__uint_as_float(o[e]), __uint_as_float(o[e + 1])), pack_bf16x2(__uint_as_float(o[e + 2]), __uint_as_float(o[e + 3])),
-                           pack_bf16x2(__uint_as_float(o[e + 4]), __uint_as_float(o[e + 5])), pack_bf16x2(__uint_as_float(o[e + 6]), __uint_as_float(o[e + 7])));
-        }
+        for (int e = 0; e < 32; e += 8)
+          *reinterpret_cast<uint4*>(dst + e) =
+              make_uint4(pack_bf16x2(__uint_as_float(o[e]), __uint_as_float(o[e + 1])), pack_bf16x2(__uint_as_float(o[e + 2]), __uint_as_float(o[e + 3])),
+                         pack_bf16x2(__uint_as_float(o[e + 4]), __uint_as_float(o[e + 5])), pack_bf16x2(__uint_as_float(o[e + 6]), __uint_as_float(o[e + 7])));
       }
     }
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 4) { tc_fence_after(); tmem_dealloc(tmem_base, 256); }
+  if (warp == 8) { tc_fence_after(); tmem_dealloc(tmem_base, 256); }
 }
 
 constexpr int AT_FWD_SMEM = 1024 + AT_TILE128 + 2 * AT_KV_STAGES * AT_TILE64 + 2 * AT_TILE128 + 256 + AT_MAX_CHUNKS * 4;
@@ -747,7 +769,8 @@ static int at_maps(const bf16* qkv, int B, int T, int H, CUtensorMap* tm128, CUt
   return DTB_OK;
 }
 
-int attn_fwd_tc(cudaStream_t stream, const bf16* qkv, const float* mask, int B, int T, int nh, int d, bf16* out, float* lse) {
+int attn_fwd_tc(cudaStream_t stream, const bf16* qkv, const float* mask, int B, int T, int nh, int d, bf16* out, float* lse,
+                const DropSite& drop) {
   DTB_REQUIRE(d == AT_D, DTB_ERR_UNSUPPORTED, "tcgen05 attention: head_dim %d unsupported (64)", d);
   DTB_REQUIRE((nh * d) % 8 == 0, DTB_ERR_BAD_ARG, "tcgen05 attention: hidden size must be a multiple of 8");
   const int H = nh * d;
@@ -758,7 +781,7 @@ int attn_fwd_tc(cudaStream_t stream, const bf16* qkv, const float* mask, int B, 
   p.T = T; p.nh = nh; p.Kmask = T / 3;
   p.scale = 1.f / sqrtf((float)d);
   p.scale_log2 = 1.4426950408889634f * p.scale;
-  p.mask = mask; p.out = out; p.lse = lse;
+  p.mask = mask; p.out = out; p.lse = lse; p.drop = drop;
   static bool attr = false;
   if (!attr) {
     DTB_CUDA(cudaFuncSetAttribute(attn_fwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_FWD_SMEM));
@@ -775,7 +798,7 @@ constexpr int AT_DQ_SMEM = 1024 + 2 * AT_TILE128 + (AT_DQ_KST + AT_DQ_VST) * AT_
 constexpr int AT_DKV_SMEM = 1024 + 2 * AT_TILE128 + 4 * AT_TILE64 + 2 * AT_TILE128 + 256 + 2 * AT_MAX_T_BWD * 4;
 
 int attn_bwd_tc(cudaStream_t stream, const bf16* qkv, const float* mask, const bf16* out, const bf16* dout, const float* lse, int B, int T,
-                int nh, int d, bf16* dqkv, float* delta) {
+                int nh, int d, bf16* dqkv, float* delta, const DropSite& drop) {
   DTB_REQUIRE(d == AT_D && T <= AT_MAX_T_BWD, DTB_ERR_UNSUPPORTED, "tcgen05 attention bwd: head_dim %d / T %d unsupported", d, T);
   const int H = nh * d;
   CUtensorMap tm128, tm64, tmDO128, tmDO64;
@@ -787,7 +810,7 @@ int attn_bwd_tc(cudaStream_t stream, const bf16* qkv, const float* mask, const b
   p.T = T; p.nh = nh; p.Kmask = T / 3;
   p.scale = 1.f / sqrtf((float)d);
   p.scale_log2 = 1.4426950408889634f * p.scale;
-  p.mask = mask; p.lse_in = lse; p.out_in = out; p.dout = dout; p.dqkv = dqkv; p.delta = delta;
+  p.mask = mask; p.lse_in = lse; p.out_in = out; p.dout = dout; p.dqkv = dqkv; p.delta = delta; p.drop = drop;
   static bool attr = false;
   if (!attr) {
     DTB_CUDA(cudaFuncSetAttribute(attn_bwd_dq_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_DQ_SMEM));
@@ -796,9 +819,9 @@ int attn_bwd_tc(cudaStream_t stream, const bf16* qkv, const float* mask, const b
   }
   dim3 grid((T + 127) / 128, nh, B);
   ProfScope prof(stream, PF_ATTN_BWD, 5.0 * B * nh * (double)T * T * d);
-  DTB_LAUNCH(attn_bwd_dq_tc_kernel, grid, AT_THREADS, AT_DQ_SMEM, stream, tm128, tm64, tmDO128, p);
+  DTB_LAUNCH(attn_bwd_dq_tc_kernel, grid, AT_BWD_THREADS, AT_DQ_SMEM, stream, tm128, tm64, tmDO128, p);
   DTB_CHECK_LAUNCH();
-  DTB_LAUNCH(attn_bwd_dkv_tc_kernel, grid, AT_THREADS, AT_DKV_SMEM, stream, tm128, tm64, tmDO64, p);
+  DTB_LAUNCH(attn_bwd_dkv_tc_kernel, grid, AT_BWD_THREADS, AT_DKV_SMEM, stream, tm128, tm64, tmDO64, p);
   DTB_CHECK_LAUNCH();
   return DTB_OK;
 }

@@ -263,6 +263,46 @@ __device__ __forceinline__ float fast_exp2(float x) {
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
+// ---- dropout (counter-based, stateless) ----------------------------------------------------------------------------------------
+// keep(site, step, group, idx) = mix32(key + idx) >= thr, thr = p * 2^32; key = f(seed, step, site[, group]).  The generator state
+// {seed_lo, seed_hi, step} lives in device memory so that a captured CUDA graph draws a fresh mask on every replay (a 1-thread
+// kernel advances `step`); forward and backward kernels of a site recompute the same bits, nothing is stored.  mix32 is the
+// "lowbias32" integer finaliser (two multiply / xor-shift rounds, full avalanche).  Replaces nn.Dropout at the reference's three
+// GPT-2 sites (HF modeling_gpt2: embd drop, attn_dropout on the softmax weights, resid_dropout after both c_proj).
+struct DropSite {
+  const uint32_t* state;  // device {seed_lo, seed_hi, step}; nullptr = dropout off
+  uint32_t site;          // 0 embd, 1 + 3l attn, 2 + 3l resid (attn c_proj), 3 + 3l resid (mlp c_proj)
+  uint32_t thr;           // drop iff mix32(key + idx) < thr
+  float scale;            // 1 / (1 - p)
+};
+__host__ __device__ __forceinline__ uint32_t drop_mix(uint32_t x) {
+  x ^= x >> 16; x *= 0x7feb352dU; x ^= x >> 15; x *= 0x846ca68bU; x ^= x >> 16;
+  return x;
+}
+__host__ __device__ __forceinline__ uint32_t drop_key_from(uint32_t s0, uint32_t s1, uint32_t step, uint32_t site) {
+  return drop_mix(drop_mix(s0 ^ (site * 0x9E3779B9U)) + drop_mix(s1 + step * 0x85EBCA6BU + 0x165667B1U));
+}
+__device__ __forceinline__ uint32_t drop_site_key(const DropSite& d) {
+  return drop_key_from(__ldg(d.state), __ldg(d.state + 1), __ldg(d.state + 2), d.site);
+}
+__host__ __device__ __forceinline__ uint32_t drop_group_key(uint32_t key, uint32_t group) { return drop_mix(key ^ (group * 0xC2B2AE35U + 0x27D4EB2FU)); }
+__host__ __device__ __forceinline__ bool drop_keep(uint32_t key, uint32_t idx, uint32_t thr) { return drop_mix(key + idx) >= thr; }
+__host__ __device__ __forceinline__ float drop_apply(float v, uint32_t key, uint32_t idx, uint32_t thr, float scale) {
+  return drop_mix(key + idx) >= thr ? v * scale : 0.f;
+}
+static inline DropSite drop_none() { DropSite d; d.state = nullptr; d.site = 0; d.thr = 0; d.scale = 1.f; return d; }
+static inline DropSite drop_make(const void* state, uint32_t site, float p) {
+  DropSite d = drop_none();
+  if (state && p > 0.f) {
+    double t = (double)p * 4294967296.0;
+    d.state = reinterpret_cast<const uint32_t*>(state);
+    d.site = site;
+    d.thr = t >= 4294967295.0 ? 4294967295u : (uint32_t)t;
+    d.scale = (float)(1.0 / (1.0 - (double)d.thr / 4294967296.0));
+  }
+  return d;
+}
+
 // Shared-memory matrix descriptor for tcgen05.mma, 128-byte swizzle (SM100 descriptor version 1).
 // K-major : rows of 128 B (64 bf16 along K), 8-row swizzle atoms 1024 B apart (SBO); LBO unused.
 // MN-major: rows of 128 B (64 bf16 along M/N) indexed by k; 8-k atoms 1024 B apart (SBO);

@@ -179,4 +179,34 @@ int pad_left(cudaStream_t stream, int nseg, const void* const* srcs, void* const
   return DTB_OK;
 }
 
+// ---- dropout plumbing ------------------------------------------------------------------------------------------------------
+__global__ void dropout_advance_kernel(uint32_t* state) {
+  pdl_trigger();
+  pdl_wait();
+  if (threadIdx.x == 0 && blockIdx.x == 0) state[2] += 1u;
+}
+int dropout_advance(cudaStream_t stream, void* state) {
+  DTB_REQUIRE(state != nullptr, DTB_ERR_BAD_ARG, "dropout_advance: null state");
+  DTB_LAUNCH(dropout_advance_kernel, 1, 32, 0, stream, reinterpret_cast<uint32_t*>(state));
+  DTB_CHECK_LAUNCH();
+  return DTB_OK;
+}
+// keep bits of one site exactly as the fused kernels draw them: out[g * n + i] = keep(site, step, g, i)   (tests / oracle masks)
+__global__ void __launch_bounds__(256) dropout_mask_kernel(const DropSite d, int groups, long long n, uint8_t* __restrict__ out) {
+  const uint32_t key0 = drop_site_key(d);
+  const long long total = (groups > 0 ? (long long)groups : 1LL) * n;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const long long g = i / n, e = i - g * n;
+    const uint32_t key = groups > 0 ? drop_group_key(key0, (uint32_t)g) : key0;
+    out[i] = drop_keep(key, (uint32_t)e, d.thr) ? 1 : 0;
+  }
+}
+int dropout_mask(cudaStream_t stream, const DropSite& d, int groups, long long n, uint8_t* out) {
+  DTB_REQUIRE(d.state && out && n >= 0 && groups >= 0, DTB_ERR_BAD_ARG, "dropout_mask: bad arguments");
+  if (n == 0) return DTB_OK;
+  dropout_mask_kernel<<<num_sms() * 4, 256, 0, stream>>>(d, groups, n, out);
+  DTB_CHECK_LAUNCH();
+  return DTB_OK;
+}
+
 }  // namespace dtb

@@ -33,12 +33,14 @@ struct EmbedFwdArgs {
   bf16* U;       // [BK, P8] or null
   int P8;
   int u_states;  // 1: U also carries the states (small-state path)
+  DropSite drop; // embd dropout on the LayerNorm output (GPT2Model.drop; idx = row * H + col)
 };
 
 __global__ void __launch_bounds__(256) embed_fwd_kernel(const EmbedFwdArgs a) {
   pdl_trigger();
   pdl_wait();
   extern __shared__ __align__(16) float sm_emb[];
+  const uint32_t drop_key = a.drop.state ? drop_site_key(a.drop) : 0u;
   const int H = a.H, sd = a.states ? a.sd : 0, ad = a.ad;
   float* sWs = sm_emb;                 // [sd][H]  (transposed)
   float* sWa = sWs + (size_t)sd * H;   // [ad][H]
@@ -157,6 +159,11 @@ __global__ void __launch_bounds__(256) embed_fwd_kernel(const EmbedFwdArgs a) {
           o.y = (v[i].y - mean) * rstd * g.y + b.y;
           o.z = (v[i].z - mean) * rstd * g.z + b.z;
           o.w = (v[i].w - mean) * rstd * g.w + b.w;
+          if (a.drop.state) {
+            const uint32_t k = drop_key + (uint32_t)row * (uint32_t)H + (uint32_t)c;
+            o.x = drop_apply(o.x, k, 0u, a.drop.thr, a.drop.scale); o.y = drop_apply(o.y, k, 1u, a.drop.thr, a.drop.scale);
+            o.z = drop_apply(o.z, k, 2u, a.drop.thr, a.drop.scale); o.w = drop_apply(o.w, k, 3u, a.drop.thr, a.drop.scale);
+          }
           *reinterpret_cast<float4*>(a.x + row * H + c) = o;
         }
       }
@@ -167,14 +174,14 @@ __global__ void __launch_bounds__(256) embed_fwd_kernel(const EmbedFwdArgs a) {
 int embed_fwd(cudaStream_t stream, const float* states, const float* state_proj, const float* actions, const float* rtg,
               const long long* timesteps, const float* table, const float* wR, const float* bR, const float* Ws, const float* bs,
               const float* Wa, const float* ba, const float* gamma, const float* beta, int BK, int sd, int ad, int H, int E, float eps,
-              float* x, float* pre, float* mean, float* rstd, bf16* U, int P8, int u_states) {
+              float* x, float* pre, float* mean, float* rstd, bf16* U, int P8, int u_states, const DropSite& drop) {
   DTB_REQUIRE(H % 4 == 0 && H <= EMB_MAX_VEC * 128, DTB_ERR_UNSUPPORTED, "embed: hidden size %d unsupported (multiple of 4, <= 1024)", H);
   DTB_REQUIRE(ad >= 1 && ad <= 64, DTB_ERR_UNSUPPORTED, "embed: act_dim %d unsupported (1..64)", ad);
   DTB_REQUIRE((states != nullptr) != (state_proj != nullptr), DTB_ERR_BAD_ARG, "embed: exactly one of states / state_proj must be given");
   DTB_REQUIRE(states == nullptr || sd <= 64, DTB_ERR_UNSUPPORTED, "embed: fused state projection needs state_dim <= 64 (got %d)", sd);
   if (BK == 0) return DTB_OK;
   EmbedFwdArgs a{states, state_proj, actions, rtg, timesteps, table, wR, bR, Ws, bs, Wa, ba, gamma, beta,
-                 BK, sd, ad, H, E, eps, x, pre, mean, rstd, U, P8, u_states};
+                 BK, sd, ad, H, E, eps, x, pre, mean, rstd, U, P8, u_states, drop};
   const size_t smem = ((size_t)(states ? sd : 0) + ad + 6) * H * sizeof(float);
   DTB_REQUIRE(smem <= 200 * 1024, DTB_ERR_UNSUPPORTED, "embed: (state_dim + act_dim + 6) * hidden too large for shared memory");
   static bool attr_set = false;

@@ -83,6 +83,11 @@ __device__ __forceinline__ void gemm_epilogue_chunk(const GemmParams& p, const G
                   }
                 }
             }
+            if (ep.drop.state) {  // resid_dropout(c_proj(.)) before the residual add (HF modeling_gpt2 :217-218, :236-237)
+              const uint32_t key = drop_site_key(ep.drop) + (uint32_t)row * (uint32_t)p.N + (uint32_t)col0;
+#pragma unroll
+              for (int j = 0; j < 32; ++j) f[j] = drop_apply(f[j], key, (uint32_t)j, ep.drop.thr, ep.drop.scale);
+            }
             if (ep.residual) {
               const float* r = ep.residual + (size_t)row * ep.ldr + col0;
 #pragma unroll
@@ -399,6 +404,11 @@ __device__ __forceinline__ void gemm_epilogue_chunk_staged(const GemmParams& p, 
 #pragma unroll
       for (int j = 0; j < 32; ++j) f[j] *= gelu_new_grad_f(a[j]);
     }
+  }
+  if (ep.drop.state) {  // same bits as gemm_epilogue_chunk: idx = row * N + col
+    const uint32_t key = drop_site_key(ep.drop) + (uint32_t)(row0 + lane) * (uint32_t)p.N + (uint32_t)col0;
+#pragma unroll
+    for (int j = 0; j < 32; ++j) f[j] = drop_apply(f[j], key, (uint32_t)j, ep.drop.thr, ep.drop.scale);
   }
   if (ep.residual) {
     float r[32];

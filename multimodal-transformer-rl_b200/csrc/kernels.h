@@ -19,6 +19,7 @@ struct GemmEpilogue {
   bf16* out_preact;       // optional: bias-added pre-activation (bf16, ld = ldo_b) saved for gelu backward
   float* partial;         // split-K: fp32 partials [split][M][N]; epilogue fields above are then ignored
   float alpha;            // scale applied to the accumulator first
+  DropSite drop;          // dropout of (acc + bias [act]) before the residual add; element index = row * N + col
 };
 
 struct GemmParams {
@@ -57,6 +58,10 @@ int cast_bf16(cudaStream_t stream, const float* src, size_t n, bf16* dst);
 int colsum_bf16(cudaStream_t stream, const bf16* x, int M, int N, int ld, float* out, int accumulate, float* scratch);
 size_t colsum_scratch_floats(int N);
 
+// dropout plumbing: advance the device-resident step counter; export keep bits for the tests (groups = 0: no group folding)
+int dropout_advance(cudaStream_t stream, void* state);
+int dropout_mask(cudaStream_t stream, const DropSite& d, int groups, long long n, uint8_t* out);
+
 int pad_left(cudaStream_t stream, int nseg, const void* const* srcs, void* const* dsts, const int* row_bytes, int t, int K, float* mask);
 
 // ---- layernorm.cu ------------------------------------------------------------------------------
@@ -64,26 +69,29 @@ int ln_fwd(cudaStream_t stream, const float* x, const float* gamma, const float*
            float* rstd);
 // dx_out = dres + LNbwd(dy); also bf16 copy; dgamma/dbeta accumulated (+=) after internal partial reduce
 int ln_bwd(cudaStream_t stream, const bf16* dy, const float* x, const float* mean, const float* rstd, const float* gamma,
-           const float* dres, int M, int H, float* dx_out, bf16* dx_out_bf16, float* dgamma, float* dbeta, float* scratch);
+           const float* dres, int M, int H, float* dx_out, bf16* dx_out_bf16, float* dgamma, float* dbeta, float* scratch,
+           const DropSite& drop_bf16 = drop_none());  // dropout mask of the consumer site applied to the bf16 copy only (idx = row * H + col)
 size_t ln_bwd_scratch_floats(int H);
 
 // ---- attention.cu ------------------------------------------------------------------------------
 // qkv: bf16 [B, T, 3H] (q | k | v, head h at columns h*d), mask: fp32 [B, K] (T = 3K, token j uses mask[b, j/3]) or null
-int attn_fwd(cudaStream_t stream, const bf16* qkv, const float* mask, int B, int T, int nh, int d, bf16* out, float* lse);
+int attn_fwd(cudaStream_t stream, const bf16* qkv, const float* mask, int B, int T, int nh, int d, bf16* out, float* lse,
+             const DropSite& drop = drop_none());  // dropout on the softmax weights: group = b * nh + h, idx = i * T + j
 int attn_bwd(cudaStream_t stream, const bf16* qkv, const float* mask, const bf16* out, const bf16* dout, const float* lse, int B, int T,
-             int nh, int d, bf16* dqkv, float* delta);
+             int nh, int d, bf16* dqkv, float* delta, const DropSite& drop = drop_none());
 
 // ---- attention_tc.cu: tcgen05 / TMEM / TMA flash attention (head_dim 64) ----------------------------
 bool attn_tc_supported(int T, int d);
-int attn_fwd_tc(cudaStream_t stream, const bf16* qkv, const float* mask, int B, int T, int nh, int d, bf16* out, float* lse);
+int attn_fwd_tc(cudaStream_t stream, const bf16* qkv, const float* mask, int B, int T, int nh, int d, bf16* out, float* lse,
+                const DropSite& drop);
 int attn_bwd_tc(cudaStream_t stream, const bf16* qkv, const float* mask, const bf16* out, const bf16* dout, const float* lse, int B, int T,
-                int nh, int d, bf16* dqkv, float* delta);
+                int nh, int d, bf16* dqkv, float* delta, const DropSite& drop);
 
 // ---- embed.cu ----------------------------------------------------------------------------------
 int embed_fwd(cudaStream_t stream, const float* states, const float* state_proj, const float* actions, const float* rtg,
               const long long* timesteps, const float* table, const float* wR, const float* bR, const float* Ws, const float* bs,
               const float* Wa, const float* ba, const float* gamma, const float* beta, int BK, int sd, int ad, int H, int E, float eps,
-              float* x, float* pre, float* mean, float* rstd, bf16* U, int P8, int u_states);
+              float* x, float* pre, float* mean, float* rstd, bf16* U, int P8, int u_states, const DropSite& drop = drop_none());
 int embed_te_scatter(cudaStream_t stream, const bf16* d_pre, const long long* timesteps, int BK, int H, int E, float* d_table);
 int embed_unpack(cudaStream_t stream, const float* G, const float* bsum, int H, int sd, int ad, int P8, int u_states, float* dwR,
                  float* dbR, float* dWs, float* dbs, float* dWa, float* dba);

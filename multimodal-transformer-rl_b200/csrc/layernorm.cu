@@ -74,9 +74,10 @@ __global__ void __launch_bounds__(256, 2) ln_bwd_kernel(const bf16* __restrict__
                                                         const float* __restrict__ mean, const float* __restrict__ rstd,
                                                         const float* __restrict__ gamma, const float* __restrict__ dres, int M, int H,
                                                         float* __restrict__ dx_out, bf16* __restrict__ dx_bf16,
-                                                        float* __restrict__ scratch /* [grid][2][H] */) {
+                                                        float* __restrict__ scratch /* [grid][2][H] */, const DropSite drop) {
   pdl_trigger();
   pdl_wait();
+  const uint32_t drop_key = drop.state ? drop_site_key(drop) : 0u;
   extern __shared__ float sred[];  // [2][H]
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
   float4 dg[NV], db[NV];
@@ -141,7 +142,14 @@ __global__ void __launch_bounds__(256, 2) ln_bwd_kernel(const bf16* __restrict__
           o.x += r.x; o.y += r.y; o.z += r.z; o.w += r.w;
         }
         if (dx_out) *reinterpret_cast<float4*>(dx_out + (size_t)row * H + c) = o;
-        if (dx_bf16) *reinterpret_cast<uint2*>(dx_bf16 + (size_t)row * H + c) = make_uint2(pack_bf16x2(o.x, o.y), pack_bf16x2(o.z, o.w));
+        if (dx_bf16) {
+          if (drop.state) {  // the bf16 copy feeds the c_proj backward of a dropout site: d(drop(y)) = mask * scale * d
+            const uint32_t k = drop_key + (uint32_t)row * (uint32_t)H + (uint32_t)c;
+            o.x = drop_apply(o.x, k, 0u, drop.thr, drop.scale); o.y = drop_apply(o.y, k, 1u, drop.thr, drop.scale);
+            o.z = drop_apply(o.z, k, 2u, drop.thr, drop.scale); o.w = drop_apply(o.w, k, 3u, drop.thr, drop.scale);
+          }
+          *reinterpret_cast<uint2*>(dx_bf16 + (size_t)row * H + c) = make_uint2(pack_bf16x2(o.x, o.y), pack_bf16x2(o.z, o.w));
+        }
       }
     }
   }
@@ -191,13 +199,14 @@ static int ln_bwd_blocks(int M, int H) {
 size_t ln_bwd_scratch_floats(int H) { return (size_t)DTB_NUM_SMS_FALLBACK * 8 * 2 * H; }
 
 int ln_bwd(cudaStream_t stream, const bf16* dy, const float* x, const float* mean, const float* rstd, const float* gamma,
-           const float* dres, int M, int H, float* dx_out, bf16* dx_out_bf16, float* dgamma, float* dbeta, float* scratch) {
+           const float* dres, int M, int H, float* dx_out, bf16* dx_out_bf16, float* dgamma, float* dbeta, float* scratch,
+           const DropSite& drop) {
   DTB_REQUIRE(H % 4 == 0 && H <= LN_MAX_VEC * 128, DTB_ERR_UNSUPPORTED, "layernorm bwd: hidden size %d unsupported", H);
   const int blocks = ln_bwd_blocks(M, H);
   const int nv = (H + 127) / 128;
   const size_t sm = 2 * H * sizeof(float);
   ProfScope prof(stream, PF_LN_BWD, 16.0 * M * H);
-#define DTB_LN_BWD(NV) DTB_LAUNCH(ln_bwd_kernel<NV>, blocks, 256, sm, stream, dy, x, mean, rstd, gamma, dres, M, H, dx_out, dx_out_bf16, scratch)
+#define DTB_LN_BWD(NV) DTB_LAUNCH(ln_bwd_kernel<NV>, blocks, 256, sm, stream, dy, x, mean, rstd, gamma, dres, M, H, dx_out, dx_out_bf16, scratch, drop)
   if (nv <= 1) DTB_LN_BWD(1);
   else if (nv <= 2) DTB_LN_BWD(2);
   else if (nv <= 4) DTB_LN_BWD(4);

@@ -46,6 +46,12 @@ struct dtb_dt {
   int sd_small;  // fused fp32 state projection (sd <= 64) vs tensor-core projection of a wide state
   int P8, ZA8, ZS8;
   mutable dtb::SideStream side;  // weight-gradient branch of the backward
+  // dropout (training mode): probabilities of the three GPT-2 sites and the device-resident generator state {seed_lo, seed_hi, step}
+  float p_embd = 0.f, p_attn = 0.f, p_resid = 0.f;
+  const void* drop_state = nullptr;
+  dtb::DropSite drop_embd() const { return dtb::drop_make(drop_state, 0u, p_embd); }
+  dtb::DropSite drop_attn(int l) const { return dtb::drop_make(drop_state, 1u + 3u * (uint32_t)l, p_attn); }
+  dtb::DropSite drop_resid(int l, int which) const { return dtb::drop_make(drop_state, 2u + (uint32_t)which + 3u * (uint32_t)l, p_resid); }
   long long e(int id) const { return off[id]; }
   long long l(int layer, int id) const { return off[E_COUNT + layer * L_COUNT + id]; }
   long long t(int id) const { return off[E_COUNT + c.n_layer * L_COUNT + id]; }
@@ -178,7 +184,7 @@ static int dt_forward(const dtb_dt* h, cudaStream_t st, const float* P, const vo
   }
   DTB_TRY(embed_fwd(st, states_f, sproj, b->actions, b->returns_to_go, b->timesteps, P + h->e(E_TABLE), P + h->e(E_WR), P + h->e(E_BR),
                     P + h->e(E_WS), P + h->e(E_BS), P + h->e(E_WA), P + h->e(E_BA), P + h->e(E_LNW), P + h->e(E_LNB), BK, sd, ad, H,
-                    c.max_ep_len, c.ln_eps, w.xs[0], w.pre0, w.mean0, w.rstd0, w.U, h->P8, h->sd_small));
+                    c.max_ep_len, c.ln_eps, w.xs[0], w.pre0, w.mean0, w.rstd0, w.U, h->P8, h->sd_small, h->drop_embd()));
   // ---- GPT-2 blocks (A4-A6) ----
   for (int l = 0; l < L; ++l) {
     DTB_TRY(ln_fwd(st, w.xs[l], P + h->l(l, L_LN1W), P + h->l(l, L_LN1B), M, H, c.ln_eps, w.h1[l], w.mean1[l], w.rstd1[l]));
@@ -189,7 +195,7 @@ static int dt_forward(const dtb_dt* h, cudaStream_t st, const float* P, const vo
       ep.ldo_b = 3 * H;
       DTB_TRY(gemm_fwd(st, w.h1[l], H, bfp(Pb, h->l(l, L_WQKV)), 3 * H, true, M, 3 * H, H, ep));
     }
-    DTB_TRY(attn_fwd(st, w.qkv[l], b->attention_mask, B, T, nh, d, w.o[l], w.lse[l]));
+    DTB_TRY(attn_fwd(st, w.qkv[l], b->attention_mask, B, T, nh, d, w.o[l], w.lse[l], h->drop_attn(l)));
     {
       GemmEpilogue ep = ep_zero();
       ep.bias = P + h->l(l, L_BO);
@@ -197,6 +203,7 @@ static int dt_forward(const dtb_dt* h, cudaStream_t st, const float* P, const vo
       ep.ldr = H;
       ep.out_f32 = w.xmid[l];
       ep.ldo_f = H;
+      ep.drop = h->drop_resid(l, 0);
       DTB_TRY(gemm_fwd(st, w.o[l], H, bfp(Pb, h->l(l, L_WO)), H, true, M, H, H, ep));
     }
     DTB_TRY(ln_fwd(st, w.xmid[l], P + h->l(l, L_LN2W), P + h->l(l, L_LN2B), M, H, c.ln_eps, w.h2[l], w.mean2[l], w.rstd2[l]));
@@ -216,6 +223,7 @@ static int dt_forward(const dtb_dt* h, cudaStream_t st, const float* P, const vo
       ep.ldr = H;
       ep.out_f32 = w.xs[l + 1];
       ep.ldo_f = H;
+      ep.drop = h->drop_resid(l, 1);
       DTB_TRY(gemm_fwd(st, w.fc[l], I, bfp(Pb, h->l(l, L_W2)), H, true, M, H, I, ep));
     }
   }
@@ -256,8 +264,9 @@ static int bwd_heads(const dtb_dt* h, cudaStream_t st, const float* P, const dtb
     DTB_CUDA(cudaMemsetAsync(G + h->t(T_WPS), 0, (pad8((long long)sd * H) + pad8(H)) * sizeof(float), ss));
     DTB_CUDA(cudaMemsetAsync(G + h->t(T_BPS), 0, (pad8(sd) + pad8(1)) * sizeof(float), ss));
   }
+  // the bf16 copy of every residual-stream gradient carries the dropout mask of the c_proj site that consumes it next
   DTB_TRY(ln_bwd(st, w.tmp_h, w.xs[L], w.meanf, w.rstdf, P + h->t(T_LNFW), nullptr, M, H, w.dX, w.dXb, G + h->t(T_LNFW), G + h->t(T_LNFB),
-                 w.ln_scratch));
+                 w.ln_scratch, h->drop_resid(L - 1, 1)));
   return DTB_OK;
 }
 
@@ -295,7 +304,7 @@ static int bwd_layer(const dtb_dt* h, cudaStream_t st, const float* P, const voi
   }
   if (attn_marked) DTB_TRY(sd.wait(st, sd.ev_b));  // the previous block's attention weight gradients still read Y / T2
   DTB_TRY(ln_bwd(st, w.tmp_h, w.xmid[l], w.mean2[l], w.rstd2[l], P + h->l(l, L_LN2W), w.dX, M, H, w.dX, Y, G + h->l(l, L_LN2W),
-                 G + h->l(l, L_LN2B), w.ln_scratch));
+                 G + h->l(l, L_LN2B), w.ln_scratch, h->drop_resid(l, 0)));
   // ---- attention ----
   {  // do = dX Wo^T
     GemmEpilogue ep = ep_zero();
@@ -303,7 +312,7 @@ static int bwd_layer(const dtb_dt* h, cudaStream_t st, const float* P, const voi
     ep.ldo_b = H;
     DTB_TRY(gemm_fwd(st, Y, H, bfp(Pb, h->l(l, L_WO)), H, false, M, H, H, ep));
   }
-  DTB_TRY(attn_bwd(st, w.qkv[l], b->attention_mask, w.o[l], w.tmp_h, w.lse[l], B, T, nh, d, T2, w.delta));
+  DTB_TRY(attn_bwd(st, w.qkv[l], b->attention_mask, w.o[l], w.tmp_h, w.lse[l], B, T, nh, d, T2, w.delta, h->drop_attn(l)));
   DTB_TRY(sd.fork(st));
   DTB_TRY(gemm_wgrad(ss, w.o[l], H, Y, H, H, H, M, G + h->l(l, L_WO), H, w.partial, w.partial_floats));
   DTB_TRY(colsum_bf16(ss, Y, M, H, H, G + h->l(l, L_BO), 0, w.cs_scratch));
@@ -319,7 +328,7 @@ static int bwd_layer(const dtb_dt* h, cudaStream_t st, const float* P, const voi
   }
   DTB_TRY(sd.wait(st, sd.ev_a));  // the MLP weight gradients read X and T1, which the next two kernels / the next block overwrite
   DTB_TRY(ln_bwd(st, w.tmp_h, w.xs[l], w.mean1[l], w.rstd1[l], P + h->l(l, L_LN1W), w.dX, M, H, w.dX, X, G + h->l(l, L_LN1W),
-                 G + h->l(l, L_LN1B), w.ln_scratch));
+                 G + h->l(l, L_LN1B), w.ln_scratch, l > 0 ? h->drop_resid(l - 1, 1) : h->drop_embd()));
   return DTB_OK;
 }
 
@@ -392,6 +401,24 @@ int dtb_dt_destroy(dtb_dt* h) {
   if (h) h->side.destroy();
   delete h;
   return DTB_OK;
+}
+
+int dtb_dt_set_dropout(dtb_dt* h, float embd_pdrop, float attn_pdrop, float resid_pdrop, const void* state) {
+  DTB_REQUIRE(h != nullptr, DTB_ERR_BAD_ARG, "dtb_dt_set_dropout: null handle");
+  DTB_REQUIRE(embd_pdrop >= 0.f && embd_pdrop < 1.f && attn_pdrop >= 0.f && attn_pdrop < 1.f && resid_pdrop >= 0.f && resid_pdrop < 1.f,
+              DTB_ERR_BAD_ARG, "dtb_dt_set_dropout: probabilities must be in [0, 1)");
+  const bool any = embd_pdrop > 0.f || attn_pdrop > 0.f || resid_pdrop > 0.f;
+  DTB_REQUIRE(!any || state != nullptr, DTB_ERR_BAD_ARG, "dtb_dt_set_dropout: a device state buffer is required when a probability is > 0");
+  h->p_embd = embd_pdrop; h->p_attn = attn_pdrop; h->p_resid = resid_pdrop;
+  h->drop_state = any ? state : nullptr;
+  return DTB_OK;
+}
+
+int dtb_dropout_advance(void* stream, void* state) { return dropout_advance((cudaStream_t)stream, state); }
+
+int dtb_dropout_mask(void* stream, const void* state, unsigned site, float p, int groups, long long n, unsigned char* out) {
+  DTB_REQUIRE(state && p > 0.f && p < 1.f, DTB_ERR_BAD_ARG, "dtb_dropout_mask: state and 0 < p < 1 required");
+  return dropout_mask((cudaStream_t)stream, drop_make(state, site, p), groups, n, out);
 }
 
 int dtb_dt_param_entries(const dtb_dt* h) { return h ? h->n_entries : DTB_ERR_BAD_ARG; }

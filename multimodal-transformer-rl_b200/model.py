@@ -73,8 +73,11 @@ class DecisionTransformer(nn.Module):
                            max_ep_len=self.max_ep_len, action_tanh=self.action_tanh, n_layer=int(n_layer), n_head=int(n_head),
                            n_inner=n_inner, activation_function=activation_function, resid_pdrop=resid_pdrop, attn_pdrop=attn_pdrop,
                            layer_norm_epsilon=layer_norm_epsilon)
-        self._pdrop = max(float(resid_pdrop or 0.0), float(attn_pdrop or 0.0), float(embd_pdrop or 0.0))
-        self._warned_dropout = False
+        # nn.Dropout sites of the trunk (GPT2Model.drop / attn_dropout / resid_dropout); embd_pdrop follows resid_pdrop when not given
+        self._p_resid, self._p_attn = float(resid_pdrop or 0.0), float(attn_pdrop or 0.0)
+        self._p_embd = self._p_resid if embd_pdrop is None else float(embd_pdrop)
+        self._drop_state = None       # device int32 [3] = {seed_lo, seed_hi, step}, read by the kernels at run time
+        self._drop_applied = None     # (p_embd, p_attn, p_resid, state ptr) last handed to the library
 
         lib = _lib.load()  # raises when libdtb200.so is missing: there is no other implementation
         cfg = _lib.DtConfig(self.state_dim, self.act_dim, self.hidden_size, int(n_layer), int(n_head), n_inner, self.max_ep_len,
@@ -254,18 +257,45 @@ class DecisionTransformer(nn.Module):
         if attention_mask is not None and attention_mask.numel() != B * K:
             raise ValueError("attention_mask must be [B, K]")
 
-    def _maybe_warn_dropout(self):
-        if self.training and self._pdrop > 0 and not self._warned_dropout:
-            warnings.warn("dtb200: dropout (resid_pdrop/attn_pdrop > 0) is not applied by the sm_100a kernels in this version; "
-                          "the step runs with p = 0 (parity is defined at p = 0)")
-            self._warned_dropout = True
+    # ---- dropout --------------------------------------------------------------------------------------------------
+    def set_dropout_seed(self, seed: int, step: int = 0):
+        """(Re)seed the in-kernel dropout generator.  Replicas of a data-parallel job pass different seeds (independent masks)."""
+        seed = int(seed) & 0xFFFFFFFFFFFFFFFF
+        vals = [seed & 0xFFFFFFFF, seed >> 32, int(step) & 0xFFFFFFFF]
+        vals = [v - (1 << 32) if v >= (1 << 31) else v for v in vals]
+        t = torch.tensor(vals, dtype=torch.int32)
+        if self._drop_state is None or self._drop_state.device != self._flat.device:
+            self._drop_state = t.to(self._flat.device)
+        else:
+            self._drop_state.copy_(t)  # in place: captured graphs keep reading the same buffer
+
+    def dropout_active(self) -> bool:
+        return bool(self.training and max(self._p_embd, self._p_attn, self._p_resid) > 0.0)
+
+    def _sync_dropout(self) -> bool:
+        """Hand the current mode (train: the three probabilities, eval: off) to the library; True when dropout is on."""
+        on = self.dropout_active()
+        if on and (self._drop_state is None or self._drop_state.device != self._flat.device):
+            self.set_dropout_seed(torch.initial_seed())
+        want = (self._p_embd, self._p_attn, self._p_resid, self._drop_state.data_ptr()) if on else (0.0, 0.0, 0.0, 0)
+        if want != self._drop_applied:
+            _lib.check(_lib.load().dtb_dt_set_dropout(self._h, want[0], want[1], want[2], want[3] or None))
+            self._drop_applied = want
+        return on
+
+    def dropout_keep_mask(self, site: int, p: float, n: int, groups: int = 0) -> torch.Tensor:
+        """Keep bits (uint8) of one dropout site at the generator's CURRENT step, exactly as the kernels draw them (tests / oracle)."""
+        total = n * max(groups, 1)
+        out = torch.empty(total, dtype=torch.uint8, device=self._flat.device)
+        _lib.check(_lib.load().dtb_dropout_mask(_lib.stream_ptr(), _lib.ptr(self._drop_state), int(site), float(p), int(groups), int(n),
+                                                _lib.ptr(out)))
+        return out
 
     # ---- reference API -------------------------------------------------------------------------------------------
     def forward(self, states, actions, rewards, returns_to_go, timesteps, attention_mask=None):
         """HF:536-657.  ``rewards`` is accepted and ignored, as in the reference (A8)."""
         self._require_cuda(actions)
         self._check_shapes(states, actions, returns_to_go, timesteps, attention_mask)
-        self._maybe_warn_dropout()
         params = [self.get_parameter(n) for n in self._names]
         wide = self.state_dim > 64 and states.dtype == torch.bfloat16
         return _DTFunction.apply(self, states, actions, returns_to_go, timesteps, attention_mask, wide, *params)
@@ -297,6 +327,8 @@ class DecisionTransformer(nn.Module):
         lib = _lib.load()
         B, K = actions.shape[0], actions.shape[1]
         self._stage()
+        if self._sync_dropout():  # training mode with p > 0: one fresh set of masks per forward (its backward re-draws the same bits)
+            _lib.check(lib.dtb_dropout_advance(_lib.stream_ptr(), _lib.ptr(self._drop_state)))
         batch, keep = self._make_batch(states, actions, returns_to_go, timesteps, attention_mask, states_bf16, states_relu)
         ws = self._workspace(B, K)
         dev = self._flat.device
@@ -337,7 +369,6 @@ class DecisionTransformer(nn.Module):
         backward stage is enqueued (data-parallel hosts all-reduce ``flat_grads[begin:end]`` there)."""
         lib = _lib.load()
         self._require_cuda(actions)
-        self._maybe_warn_dropout()
         target = (actions if action_target is None else action_target).detach().to(torch.float32).contiguous()
         self._forward_raw(states, actions, returns_to_go, timesteps, attention_mask, want_all=False, states_bf16=states_bf16,
                           states_relu=states_relu)
@@ -385,9 +416,11 @@ class _ActionRunner:
             self.audio = torch.zeros((1, K, *encoder.audio_shape), dtype=torch.float32, device=dev)
         self.out = torch.zeros(dt.act_dim, dtype=torch.float32, device=dev)
         self.graph, self._keep = None, None
+        self.drop_mode = dt.dropout_active()
 
     def dead(self, dt):
-        return self.flat_ptr != dt._flat.data_ptr()  # the model was moved / re-created: buffers and graph are stale
+        # the model was moved / re-created, or train() / eval() changed the dropout mode: buffers and graph are stale
+        return self.flat_ptr != dt._flat.data_ptr() or self.drop_mode != dt.dropout_active()
 
     def _body(self):
         dt = self.dt

@@ -48,6 +48,28 @@ def _act(name: str):
     raise ValueError(f"unsupported activation_function {name!r} (relu | gelu_new)")
 
 
+class MaskedDropout(nn.Dropout):
+    """nn.Dropout, except that a test may pin the keep mask (`keep`: bool tensor shaped like the input) so that this oracle and the
+    CUDA path drop the SAME elements: y = x * keep / (1 - p).  Without a pinned mask it is plain nn.Dropout (torch's generator)."""
+
+    keep = None
+
+    def forward(self, x):
+        if self.keep is None or not self.training or self.p == 0.0:
+            return super().forward(x)
+        return x * self.keep.to(x.dtype).view(x.shape) / (1.0 - self.p)
+
+
+def set_dropout_masks(model, embd=None, attn=None, resid_attn=None, resid_mlp=None):
+    """Pin the keep masks of a DecisionTransformer oracle: `embd` [B,T,H]; per-layer lists `attn` [B,nh,T,T], `resid_*` [B,T,H]."""
+    tr = model.transformer
+    tr.drop.keep = embd
+    for l, blk in enumerate(tr.h):
+        blk.attn.attn_dropout.keep = None if attn is None else attn[l]
+        blk.attn.resid_dropout.keep = None if resid_attn is None else resid_attn[l]
+        blk.mlp.dropout.keep = None if resid_mlp is None else resid_mlp[l]
+
+
 class Attention(nn.Module):
     def __init__(self, hidden: int, n_head: int, attn_pdrop: float, resid_pdrop: float):
         super().__init__()
@@ -55,8 +77,8 @@ class Attention(nn.Module):
         self.n_head, self.head_dim = n_head, hidden // n_head
         self.c_attn = Conv1D(3 * hidden, hidden)
         self.c_proj = Conv1D(hidden, hidden)
-        self.attn_dropout = nn.Dropout(attn_pdrop)
-        self.resid_dropout = nn.Dropout(resid_pdrop)
+        self.attn_dropout = MaskedDropout(attn_pdrop)
+        self.resid_dropout = MaskedDropout(resid_pdrop)
 
     def forward(self, x, allowed):  # allowed: bool [B, 1, T, T]
         B, T, H = x.shape
@@ -78,7 +100,7 @@ class MLP(nn.Module):
         self.c_fc = Conv1D(inner, hidden)
         self.c_proj = Conv1D(hidden, inner)
         self.act = _act(act)
-        self.dropout = nn.Dropout(resid_pdrop)
+        self.dropout = MaskedDropout(resid_pdrop)
 
     def forward(self, x):
         return self.dropout(self.c_proj(self.act(self.c_fc(x))))  # HF:233-238
@@ -103,7 +125,7 @@ class GPT2Trunk(nn.Module):
 
     def __init__(self, hidden, n_layer, n_head, inner, act, attn_pdrop, resid_pdrop, embd_pdrop, eps):
         super().__init__()
-        self.drop = nn.Dropout(embd_pdrop)
+        self.drop = MaskedDropout(embd_pdrop)
         self.h = nn.ModuleList([Block(hidden, n_head, inner, act, attn_pdrop, resid_pdrop, eps) for _ in range(n_layer)])
         self.ln_f = nn.LayerNorm(hidden, eps=eps)
 

@@ -45,7 +45,7 @@ CONFIGS = {
 }
 
 
-def build_pair(name, device, max_ep_len=1000, seed=0):
+def build_pair(name, device, max_ep_len=1000, seed=0, pdrop=0.0):
     """(oracle on CPU, drop-in on `device`) with identical weights."""
     from mtrl_b200.model import DecisionTransformer
     from oracle.decision_transformer import DecisionTransformer as Oracle
@@ -53,7 +53,7 @@ def build_pair(name, device, max_ep_len=1000, seed=0):
     cfg = dict(CONFIGS[name])
     K = cfg.pop("K")
     torch.manual_seed(seed)
-    oracle = Oracle(max_length=K, max_ep_len=max_ep_len, resid_pdrop=0.0, attn_pdrop=0.0, **cfg)
+    oracle = Oracle(max_length=K, max_ep_len=max_ep_len, resid_pdrop=pdrop, attn_pdrop=pdrop, **cfg)
     # non-trivial LayerNorm / bias values so every gradient path is exercised
     with torch.no_grad():
         for n, p in oracle.named_parameters():
@@ -61,7 +61,7 @@ def build_pair(name, device, max_ep_len=1000, seed=0):
                 p.normal_(0, 0.02)
             elif "ln_" in n or "embed_ln" in n:
                 p.add_(torch.randn_like(p) * 0.05)
-    model = DecisionTransformer(max_length=K, max_ep_len=max_ep_len, resid_pdrop=0.0, attn_pdrop=0.0, device=device, **cfg)
+    model = DecisionTransformer(max_length=K, max_ep_len=max_ep_len, resid_pdrop=pdrop, attn_pdrop=pdrop, device=device, **cfg)
     model.load_state_dict(oracle.state_dict())
     return oracle, model, K
 
