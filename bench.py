@@ -97,12 +97,14 @@ class ClockSampler:
 # ------------------------------------------------------------------------------------------------------------------------------
 # our arm
 # ------------------------------------------------------------------------------------------------------------------------------
-def build_ours(wl, dev):
+def build_ours(wl, dev, pdrop=0.0, rank=0):
     from mtrl_b200.encoder import MultimodalDecisionTransformer, MultimodalStateEncoder
     from mtrl_b200.model import DecisionTransformer
 
     torch.manual_seed(0)  # shared seed -> identical replicas (ppo_atari_multigpu.py:200); broadcast below makes it strict
-    dt = DecisionTransformer(max_length=wl["K"], max_ep_len=MAX_EP_LEN, resid_pdrop=0.0, attn_pdrop=0.0, device=dev, **wl["dt"])
+    dt = DecisionTransformer(max_length=wl["K"], max_ep_len=MAX_EP_LEN, resid_pdrop=pdrop, attn_pdrop=pdrop, device=dev, **wl["dt"])
+    dt.train()  # training mode: dropout (upstream default 0.1) is drawn inside the kernels, fresh masks on every step / graph replay
+    dt.set_dropout_seed(1000 + rank)  # independent masks per replica
     if wl["enc"] is None:
         return dt, [dt]
     enc = MultimodalStateEncoder(wl["enc"]["frame_shape"], wl["enc"]["audio_shape"], "big", "concat", 1.0 / 255.0, device=dev)
@@ -197,7 +199,7 @@ def run_ours(args, wl, rank, world, local_rank):
     lib = _lib.load()
     _lib.check(lib.dtb_check_device())
     B, K = wl["B"], wl["K"]
-    model, parts = build_ours(wl, dev)
+    model, parts = build_ours(wl, dev, args.dropout, rank)
     broadcast_parameters([p.flat_params for p in parts])
     host = make_batch(wl, B, seed=1234 + rank)  # per-rank data seeds (ppo_atari_multigpu.py:197-199); weak scaling: B per GPU fixed
     pinned = {k: v.contiguous().pin_memory() for k, v in host.items()}
@@ -271,7 +273,7 @@ def run_ours(args, wl, rank, world, local_rank):
         "metric": "DT train tokens/s (fwd+bwd)", "value": value, "unit": "tokens/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
         "config": {"workload": wl["label"], "name": args.workload, "batch_per_gpu": B, "global_batch": B * world, "seq_len": 3 * K,
-                   "parallelism": f"dp{world}", "cuda_graph": graphed, "dropout": 0.0,
+                   "parallelism": f"dp{world}", "cuda_graph": graphed, "dropout": args.dropout,
                    "l2": ("explicit 256 MiB flush between steps" if flush is not None else
                           f"no flush: per-step working set {ws_bytes / 1e6:.0f} MB > 126 MB L2"),
                    "timed": "weight staging + forward + masked action MSE + backward" + (" + overlapped NCCL all-reduce" if world > 1 else "")},
@@ -288,13 +290,13 @@ def run_ours(args, wl, rank, world, local_rank):
 # ------------------------------------------------------------------------------------------------------------------------------
 # CPU arm: the fp32 oracle on the host cores (cpu_baseline of our line, and the whole `--impl reference` run)
 # ------------------------------------------------------------------------------------------------------------------------------
-def build_oracle(wl):
+def build_oracle(wl, pdrop=0.0):
     from oracle.decision_transformer import DecisionTransformer as ODT
     from oracle.encoders import MultimodalDecisionTransformer as OMM
     from oracle.encoders import MultimodalStateEncoder as OEnc
 
     torch.manual_seed(0)
-    dt = ODT(max_length=wl["K"], max_ep_len=MAX_EP_LEN, resid_pdrop=0.0, attn_pdrop=0.0, **wl["dt"])
+    dt = ODT(max_length=wl["K"], max_ep_len=MAX_EP_LEN, resid_pdrop=pdrop, attn_pdrop=pdrop, **wl["dt"])
     if wl["enc"] is None:
         return dt
     return OMM(OEnc(wl["enc"]["frame_shape"], wl["enc"]["audio_shape"], "big", "concat", 1.0 / 255.0), dt)
@@ -314,12 +316,13 @@ def oracle_step(wl, model, b):
     return float(loss.detach())
 
 
-def run_cpu(wl, steps, warmup, budget_s=20.0):
+def run_cpu(wl, steps, warmup, budget_s=20.0, pdrop=0.0):
     """Times the oracle on all host threads on a bounded sample: the same workload at a reduced batch chosen so that
     warmup + steps fit in ~budget_s; tokens/s = sample tokens / time (linear in batch)."""
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
-    model = build_oracle(wl)
+    model = build_oracle(wl, pdrop)
+    model.train()  # nn.Dropout(p) active, as in the reference's train_step
     K = wl["K"]
     Bs = min(wl["B"], 4)
     b = make_batch(wl, Bs, seed=1234)
@@ -342,7 +345,7 @@ def run_cpu(wl, steps, warmup, budget_s=20.0):
     tokens = Bs * 3 * K
     return {"value": tokens / dt_s, "unit": "tokens/s", "cores": cores, "kind": "port", "ms_per_step": dt_s * 1e3,
             "sample": f"fp32 PyTorch oracle (towers = reference conv_factory math), fwd+loss+bwd, batch {Bs} of {wl['B']} trajectories x K={K} "
-                      f"({tokens} tokens/step), {steps} steps after {warmup} warm-up, {cores} threads", "loss": loss}
+                      f"({tokens} tokens/step), dropout {pdrop}, {steps} steps after {warmup} warm-up, {cores} threads", "loss": loss}
 
 
 # DRAM bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum, mean over the captured launches) of each workload's dominant
@@ -352,7 +355,8 @@ NCU_TRAFFIC = {"c2": (20.7e6, "profiles/r01_ncu_gemm_c2_v0.txt (6 launches of th
 
 PROF_FAMILIES = [("gemm_tcgen05_kernel (+pair)", "tensor"), ("conv1_fwd_kernel", "hbm"), ("conv1_wgrad_kernel", "hbm"), ("attn_fwd_kernel", "tensor"),
                  ("attn_bwd_dq+dkv_kernel", "tensor"), ("ln_fwd_kernel", "hbm"), ("ln_bwd_kernel(+finalize)", "hbm"), ("embed_fwd_kernel", "hbm"),
-                 ("colsum_stage1+2", "hbm"), ("im2col_nhwc_kernel", "hbm"), ("col2im_nhwc_relu_kernel", "hbm")]
+                 ("colsum_stage1+2", "hbm"), ("im2col_nhwc_kernel", "hbm"), ("col2im_nhwc_relu_kernel", "hbm"),
+                 ("gemm_tcgen05_kernel, HBM-bound shapes (flops < 216 x bytes)", "hbm")]
 
 
 def measure_roofline(args, wl, ctx, reps=5):
@@ -435,6 +439,7 @@ def measure_get_action(wl, ctx, calls=300, warmup=50):
     """BASELINE.json's second metric: get_action latency at B = 1 with a full K-step history, through the public API
     (wall clock, one stream sync per call, p50 / p90 / p99 in microseconds)."""
     model, dev, K = ctx["model"], ctx["dev"], wl["K"]
+    model.eval()  # evaluation rollouts run without dropout (upstream evaluate_episode_rtg: model.eval())
     b = make_batch(wl, 1, seed=4321)
     args = []
     if wl["enc"] is None:
@@ -453,23 +458,27 @@ def measure_get_action(wl, ctx, calls=300, warmup=50):
     lat.sort()
     pick = lambda q: lat[min(len(lat) - 1, int(q * len(lat)))]
     return {"p50_us": pick(0.5), "p90_us": pick(0.9), "p99_us": pick(0.99), "calls": calls, "warmup": warmup, "history": K,
-            "action_dim": int(a.numel()), "how": "wall clock around model.get_action(...) + stream sync, inputs resident on the device"}
+            "action_dim": int(a.numel()), "how": "wall clock around model.get_action(...) + stream sync, inputs resident on the device, model.eval()"}
 
 
 def other_workloads(args, skip):
     """Short device-resident runs of the other single-GPU configs of BASELINE.json (each in a fresh subprocess so its workspace is
     released): tokens/s, algorithmic TFLOP/s and the dominant kernel's roofline line."""
     out = {}
-    for name in ("c1", "c3", "c4"):
-        if name == skip:
-            continue
+    runs = [(n, n, args.dropout) for n in ("c1", "c3", "c4") if n != skip]
+    if args.dropout > 0:
+        runs += [(f"{n}_dropout0", n, 0.0) for n in (skip, "c4") if n]  # the same steps with dropout off (parity mode)
+    for key, name, pdrop in runs:
         cmd = [sys.executable, os.path.abspath(__file__), "--workload", name, "--steps", "10" if name == "c4" else "30", "--warmup", "3",
-               "--no-cpu-baseline", "--no-extras"]
+               "--no-cpu-baseline", "--no-extras", "--dropout", str(pdrop)]
+        if key != name:
+            cmd += ["--no-get-action"]
+        name = key
         try:
             r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
             d = json.loads(r.stdout.strip().splitlines()[-1])
             rf = d.get("roofline") or {}
-            out[name] = {"workload": d["config"]["workload"], "value": d["value"], "unit": d["unit"], "ms_per_step": d["ms_per_step"],
+            out[name] = {"workload": d["config"]["workload"], "dropout": d["config"].get("dropout"), "value": d["value"], "unit": d["unit"], "ms_per_step": d["ms_per_step"],
                          "e2e": d["e2e"]["value"], "algorithmic_tflops_per_s": d["algorithmic_tflops_per_s"], "launches_per_step": d["launches_per_step"],
                          "get_action": d.get("get_action"),
                          "roofline": {k: rf.get(k) for k in ("kernel", "bound", "achieved", "peak", "unit", "frac")},
@@ -493,6 +502,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-roofline", action="store_true")
     ap.add_argument("--no-get-action", action="store_true", help="skip the get_action latency measurement (keeps ncu launch lists to the training step)")
+    ap.add_argument("--dropout", type=float, default=0.1, help="resid/attn/embd dropout of the training step (upstream default 0.1)")
     ap.add_argument("--no-extras", action="store_true", help="skip the other-workload summaries (c1 / c3 / c4) appended to the default line")
     args = ap.parse_args()
     wl = dict(WORKLOADS[args.workload])
@@ -504,11 +514,11 @@ def main():
         if rank != 0:
             return
         steps, warmup = min(args.steps, 10), min(args.warmup, 2)
-        r = run_cpu(wl, steps, max(warmup, 1), budget_s=60.0)
+        r = run_cpu(wl, steps, max(warmup, 1), budget_s=60.0, pdrop=args.dropout)
         line = {"impl": "reference", "metric": "DT train tokens/s (fwd+bwd)", "value": r["value"], "unit": "tokens/s", "n_gpus": args.gpus,
                 "steps": steps, "warmup": max(warmup, 1), "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak",
                 "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-                "config": {"workload": wl["label"], "name": args.workload, "seq_len": 3 * wl["K"], "parallelism": "cpu"},
+                "config": {"workload": wl["label"], "name": args.workload, "seq_len": 3 * wl["K"], "parallelism": "cpu", "dropout": args.dropout},
                 "cpu_baseline": r, "e2e": {"value": r["value"], "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                 "gpu_launches": 0,
                 "note": "the reference's own DT source is an un-vendored empty submodule (SURVEY.md F1); this arm is the fp32 PyTorch oracle, "
@@ -538,7 +548,7 @@ def main():
             except Exception as e:  # noqa: BLE001
                 res["get_action"] = {"error": str(e)[:200]}
         if world == 1 and not args.no_cpu_baseline:
-            res["cpu_baseline"] = run_cpu(wl, 3, 1, budget_s=20.0)
+            res["cpu_baseline"] = run_cpu(wl, 3, 1, budget_s=20.0, pdrop=args.dropout)
         if world == 1 and not args.no_extras:
             del ctx  # release this workload's device memory before the sub-runs
             torch.cuda.empty_cache()

@@ -97,6 +97,12 @@ int dtb_layernorm_bwd(void* stream, const void* dy_bf16, const float* x, const f
 int dtb_attention_fwd(void* stream, const void* qkv, const float* mask, int B, int T, int n_head, int head_dim, void* out, float* lse);
 int dtb_attention_bwd(void* stream, const void* qkv, const float* mask, const void* out, const void* dout, const float* lse, int B,
                       int T, int n_head, int head_dim, void* dqkv, float* delta);
+/* The same kernels with attn_dropout on the softmax weights (HF eager attention :60-62): keep bits of `site` drawn from the device
+ * generator state (see dtb_dt_set_dropout); the backward re-draws the bits of the forward.  p = 0 or drop_state NULL = no dropout. */
+int dtb_attention_fwd_dropout(void* stream, const void* qkv, const float* mask, int B, int T, int n_head, int head_dim, void* out,
+                              float* lse, const void* drop_state, unsigned site, float p);
+int dtb_attention_bwd_dropout(void* stream, const void* qkv, const float* mask, const void* out, const void* dout, const float* lse, int B,
+                              int T, int n_head, int head_dim, void* dqkv, float* delta, const void* drop_state, unsigned site, float p);
 
 /* ---- weight staging + bias gradients -----------------------------------------------------------------------------
  * cast_transpose: fp32 [R,C] -> bf16 [R,C] (dst, may be NULL) and bf16 [C,R] (dst_t, may be NULL).

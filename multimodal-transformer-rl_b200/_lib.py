@@ -80,6 +80,8 @@ def _declare(lib):
     lib.dtb_encoder_backward_u8.argtypes = lib.dtb_encoder_backward.argtypes
     lib.dtb_pad_left.argtypes = [vp, i, C.POINTER(vp), C.POINTER(vp), C.POINTER(i), i, i, vp]
     lib.dtb_dt_set_dropout.argtypes = [vp, f, f, f, vp]
+    lib.dtb_attention_fwd_dropout.argtypes = [vp, vp, vp, i, i, i, i, vp, vp, vp, C.c_uint, f]
+    lib.dtb_attention_bwd_dropout.argtypes = [vp, vp, vp, vp, vp, vp, i, i, i, i, vp, vp, vp, C.c_uint, f]
     lib.dtb_dropout_advance.argtypes = [vp, vp]
     lib.dtb_dropout_mask.argtypes = [vp, vp, C.c_uint, f, i, ll, vp]
     lib.dtb_masked_mse.argtypes = [vp, vp, vp, vp, i, i, f, vp, vp, vp]
@@ -174,15 +176,23 @@ def layernorm_bwd(dy, x, mean, rstd, gamma, dres, dx_f32, dx_bf16, dgamma, dbeta
                                 ptr(dx_bf16), ptr(dgamma), ptr(dbeta), ptr(scratch)))
 
 
-def attention_fwd(qkv, mask, n_head, out, lse):
+def attention_fwd(qkv, mask, n_head, out, lse, drop_state=None, site=0, p=0.0):
     B, T, H3 = qkv.shape
     d = H3 // 3 // n_head
+    if drop_state is not None and p > 0:
+        check(load().dtb_attention_fwd_dropout(stream_ptr(), ptr(qkv), ptr(mask), B, T, n_head, d, ptr(out), ptr(lse), ptr(drop_state),
+                                               int(site), float(p)))
+        return
     check(load().dtb_attention_fwd(stream_ptr(), ptr(qkv), ptr(mask), B, T, n_head, d, ptr(out), ptr(lse)))
 
 
-def attention_bwd(qkv, mask, out, dout, lse, n_head, dqkv, delta):
+def attention_bwd(qkv, mask, out, dout, lse, n_head, dqkv, delta, drop_state=None, site=0, p=0.0):
     B, T, H3 = qkv.shape
     d = H3 // 3 // n_head
+    if drop_state is not None and p > 0:
+        check(load().dtb_attention_bwd_dropout(stream_ptr(), ptr(qkv), ptr(mask), ptr(out), ptr(dout), ptr(lse), B, T, n_head, d,
+                                               ptr(dqkv), ptr(delta), ptr(drop_state), int(site), float(p)))
+        return
     check(load().dtb_attention_bwd(stream_ptr(), ptr(qkv), ptr(mask), ptr(out), ptr(dout), ptr(lse), B, T, n_head, d, ptr(dqkv),
                                    ptr(delta)))
 

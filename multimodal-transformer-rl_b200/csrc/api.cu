@@ -82,6 +82,19 @@ int dtb_attention_bwd(void* stream, const void* qkv, const float* mask, const vo
   return attn_bwd((cudaStream_t)stream, (const bf16*)qkv, mask, (const bf16*)out, (const bf16*)dout, lse, B, T, n_head, head_dim,
                   (bf16*)dqkv, delta);
 }
+int dtb_attention_fwd_dropout(void* stream, const void* qkv, const float* mask, int B, int T, int n_head, int head_dim, void* out,
+                              float* lse, const void* drop_state, unsigned site, float p) {
+  DTB_REQUIRE(qkv && out && lse, DTB_ERR_BAD_ARG, "dtb_attention_fwd_dropout: null pointer");
+  DTB_REQUIRE(p >= 0.f && p < 1.f, DTB_ERR_BAD_ARG, "dtb_attention_fwd_dropout: p must be in [0, 1)");
+  return attn_fwd((cudaStream_t)stream, (const bf16*)qkv, mask, B, T, n_head, head_dim, (bf16*)out, lse, drop_make(drop_state, site, p));
+}
+int dtb_attention_bwd_dropout(void* stream, const void* qkv, const float* mask, const void* out, const void* dout, const float* lse, int B,
+                              int T, int n_head, int head_dim, void* dqkv, float* delta, const void* drop_state, unsigned site, float p) {
+  DTB_REQUIRE(qkv && out && dout && lse && dqkv && delta, DTB_ERR_BAD_ARG, "dtb_attention_bwd_dropout: null pointer");
+  DTB_REQUIRE(p >= 0.f && p < 1.f, DTB_ERR_BAD_ARG, "dtb_attention_bwd_dropout: p must be in [0, 1)");
+  return attn_bwd((cudaStream_t)stream, (const bf16*)qkv, mask, (const bf16*)out, (const bf16*)dout, lse, B, T, n_head, head_dim,
+                  (bf16*)dqkv, delta, drop_make(drop_state, site, p));
+}
 int dtb_cast_transpose(void* stream, const float* src, int R, int C, void* dst, void* dst_t) {
   DTB_REQUIRE(src, DTB_ERR_BAD_ARG, "dtb_cast_transpose: null pointer");
   return cast_transpose((cudaStream_t)stream, src, R, C, (bf16*)dst, (bf16*)dst_t);

@@ -20,7 +20,7 @@ namespace dtb {
 
 constexpr int AT_D = 64;
 constexpr int AT_THREADS = 192;      // forward: warps 0-3 softmax, 4 MMA, 5 TMA
-constexpr int AT_BWD_THREADS = 320;  // backward: warps 0-7 compute (warp w and w+4 share TMEM lane quadrant w & 3, 32 columns each), 8 MMA, 9 TMA
+// backward: CW compute warps (4 or 8; warps w and w + 4 share TMEM lane quadrant w & 3), then one MMA warp and one TMA warp
 constexpr int AT_TILE128 = 128 * 128;  // bytes: 128 rows x 128 B (64 bf16)
 constexpr int AT_TILE64 = 64 * 128;    // bytes: 64 rows x 128 B
 constexpr int AT_KV_STAGES = 3;        // TMA ring depth for the streamed 64-row blocks (prefetch distance 2 blocks ~ TMA latency)
@@ -80,6 +80,7 @@ __device__ __forceinline__ void at_store_row_unit(uint32_t tile_base, int r, int
 // ================================================================================================================================
 // smem: Q [128x64] | K[2] [64x64] | V[2] [64x64] | P[2] [128x64]  (all bf16, swizzled)            = 16 + 16 + 16 + 32 KB
 // TMEM (128 columns): S fp32 [128 x 64] at column 0, O fp32 [128 x 64] at column 64
+template <bool DROP>  // DROP = false compiles every dropout branch away (dthr is a constant 0)
 __global__ void __launch_bounds__(AT_THREADS, 2)
 attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmKV, const AttnTcParams p) {
   extern __shared__ uint8_t smem_raw[];
@@ -190,8 +191,8 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
     const int qi = q0 + r;
     const uint32_t lane_addr = (uint32_t)(warp * 32) << 16;
     float m_use = -INFINITY, l = 0.f;
-    const uint32_t dthr = p.drop.state ? p.drop.thr : 0u;
-    const uint32_t drow = at_drop_key(p, b, h) + (uint32_t)qi * (uint32_t)T;
+    const uint32_t dthr = DROP ? p.drop.thr : 0u;
+    const uint32_t drow = DROP ? at_drop_key(p, b, h) + (uint32_t)qi * (uint32_t)T : 0u;
     for (int j = 0; j < nkb; ++j) {
       const int k0 = j * 64;
       const uint32_t bits[2] = {sBits[2 * j], sBits[2 * j + 1]};
@@ -364,7 +365,8 @@ __device__ __forceinline__ void at_ds_half(const uint32_t (&sv)[32], const uint3
   }
 }
 
-__global__ void __launch_bounds__(AT_BWD_THREADS, 2)
+template <bool DROP, int CW>  // DROP = false compiles every dropout branch away; CW = compute warps (4: both halves per thread, 8: one)
+__global__ void __launch_bounds__(32 * (CW + 2), 2)
 attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmKV,
                       const __grid_constant__ CUtensorMap tmDO, const AttnTcParams p) {
   extern __shared__ uint8_t smem_raw[];
@@ -400,12 +402,12 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
     mbar_init(qdo_full, 1);
     for (int s = 0; s < AT_DQ_KST; ++s) { mbar_init(&k_full[s], 1); mbar_init(&k_free[s], 1); }
     for (int s = 0; s < AT_DQ_VST; ++s) { mbar_init(&v_full[s], 1); mbar_init(&v_free[s], 1); }
-    for (int s = 0; s < 2; ++s) { mbar_init(&ds_full[s], 256); mbar_init(&ds_done[s], 1); }
+    for (int s = 0; s < 2; ++s) { mbar_init(&ds_full[s], 32 * CW); mbar_init(&ds_done[s], 1); }
     mbar_init(sdp_full, 1);
-    mbar_init(sdp_free, 256);
+    mbar_init(sdp_free, 32 * CW);
     fence_mbar_init();
   }
-  if (warp == 8) { tmem_alloc(tmem_slot, 256); tmem_relinquish(); }
+  if (warp == CW) { tmem_alloc(tmem_slot, 256); tmem_relinquish(); }
   pdl_trigger();  // prologue done: the next kernel of the stream may start its own
   pdl_wait();     // the previous kernel's results are complete and visible from here on
   at_fill_valid_bits(p, b, 2 * nkb, sBits);
@@ -416,7 +418,7 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
   const uint32_t tS = tmem_base, tDP = tmem_base + 64, tDQ = tmem_base + 128;
   const int H = p.nh * AT_D;
 
-  if (warp == 9) {
+  if (warp == CW + 1) {
     if (lane == 0) {
       tma_prefetch_desc(&tmQ); tma_prefetch_desc(&tmKV); tma_prefetch_desc(&tmDO);
       mbar_arrive_expect_tx(qdo_full, 2 * AT_TILE128);
@@ -432,7 +434,7 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
         tma_load_3d(sV + sv * AT_TILE64, &tmKV, &v_full[sv], 2 * H + h * AT_D, j * 64, b);
       }
     }
-  } else if (warp == 8) {
+  } else if (warp == CW) {
     if (lane == 0) {
       const uint32_t idesc_kk = make_idesc_bf16(128, 64, 0, 0), idesc_kn = make_idesc_bf16(128, 64, 0, 1);
       const uint32_t q_addr = smem_u32(sQ), do_addr = smem_u32(sDO);
@@ -471,22 +473,23 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
       }
     }
   } else {
-    // warp w (0-7): rows 32 (w & 3) .. +31 (its TMEM lane quadrant), columns 32 (w >> 2) .. +31 of every 64-key block
-    const int qd = warp & 3, half = warp >> 2;
+    // compute warps: TMEM lane quadrant qd = w & 3 (rows 32 qd .. +31, one per thread).  CW = 8: warp w owns the 32-column half w >> 2 of
+    // every 64-key block; CW = 4: every thread walks both halves.
+    const int qd = warp & 3, h_lo = CW == 8 ? (warp >> 2) : 0, h_hi = CW == 8 ? h_lo + 1 : 2;
     const int r = qd * 32 + lane;
     const int qi = q0 + r;
-    const uint32_t lane_addr = ((uint32_t)(qd * 32) << 16) + 32 * half;
+    const uint32_t lane_base = (uint32_t)(qd * 32) << 16;
     const size_t row_off = ((size_t)b * p.nh + h) * T;
-    // delta = rowsum(dO * O) for this thread's row, straight from global (128 B each; both warps of a row compute it, one stores it)
+    // delta = rowsum(dO * O) for this thread's row, straight from global (128 B each)
     float delta = 0.f, nlse = 0.f;
-    const uint32_t dthr = p.drop.state ? p.drop.thr : 0u;
-    const uint32_t drow = at_drop_key(p, b, h) + (uint32_t)qi * (uint32_t)T;
+    const uint32_t dthr = DROP ? p.drop.thr : 0u;
+    const uint32_t drow = DROP ? at_drop_key(p, b, h) + (uint32_t)qi * (uint32_t)T : 0u;
     if (qi < T) {
       const uint4* orow = reinterpret_cast<const uint4*>(p.out_in + ((size_t)b * T + qi) * H + h * AT_D);
-      const uint4* drow = reinterpret_cast<const uint4*>(p.dout + ((size_t)b * T + qi) * H + h * AT_D);
+      const uint4* drow_g = reinterpret_cast<const uint4*>(p.dout + ((size_t)b * T + qi) * H + h * AT_D);
 #pragma unroll
       for (int u = 0; u < 8; ++u) {
-        const uint4 a = __ldg(orow + u), g = __ldg(drow + u);
+        const uint4 a = __ldg(orow + u), g = __ldg(drow_g + u);
         const uint32_t aw[4] = {a.x, a.y, a.z, a.w}, gw[4] = {g.x, g.y, g.z, g.w};
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
@@ -494,43 +497,49 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
           delta += x.x * y.x + x.y * y.y;
         }
       }
-      if (half == 0) p.delta[row_off + qi] = delta;
+      if (h_lo == 0) p.delta[row_off + qi] = delta;
       nlse = -__ldg(p.lse_in + row_off + qi);
     }
     for (int j = 0; j < nkb; ++j) {
-      const int k0 = j * 64 + 32 * half;  // first key of this warp's 32-key chunk
       const bool diag = j * 64 + 63 > q0;
-      const bool act = !diag || (k0 <= q0 + qd * 32 + 31);
-      uint32_t m = 0u;
-      if (act) m = sBits[2 * j + half] & (diag ? at_causal_word(qi - k0) : 0xffffffffu);
       const int db = j & 1;
       const uint32_t tile = smem_u32(sDS + db * AT_TILE128);
       mbar_wait(sdp_full, j & 1);
       tc_fence_after();
-      uint32_t sv[32], dv[32];
-      if (act) {
-        tmem_ld_32x32(tS + lane_addr, sv);
-        tmem_ld_32x32(tDP + lane_addr, dv);
-        tmem_ld_wait();
-      }
-      tc_fence_before();
-      mbar_arrive(sdp_free);  // S / dP of this block are in registers: the next block's MMAs may overwrite them
-      if (j >= 2) mbar_wait(&ds_done[db], ((j - 2) >> 1) & 1);  // dS buffer db was last read by the dQ MMAs of block j - 2
-      if (act) {
-        at_ds_half(sv, dv, m, p.scale_log2, nlse, delta, p.scale, tile, r, 4 * half, drow + (uint32_t)k0, dthr, p.drop.scale);
-      } else {
 #pragma unroll
-        for (int u = 0; u < 4; ++u) at_store_row_unit(tile, r, 4 * half + u, 0u, 0u, 0u, 0u);
+      for (int half = h_lo; half < h_hi; ++half) {
+        const int k0 = j * 64 + 32 * half;  // first key of the 32-key chunk
+        const bool act = !diag || (k0 <= q0 + qd * 32 + 31);
+        uint32_t m = 0u;
+        if (act) m = sBits[2 * j + half] & (diag ? at_causal_word(qi - k0) : 0xffffffffu);
+        uint32_t sv[32], dv[32];
+        if (act) {
+          tmem_ld_32x32(tS + lane_base + 32 * half, sv);
+          tmem_ld_32x32(tDP + lane_base + 32 * half, dv);
+          tmem_ld_wait();
+        }
+        if (half == h_hi - 1) {  // S / dP of this block are in registers: the next block's MMAs may overwrite them
+          tc_fence_before();
+          mbar_arrive(sdp_free);
+        }
+        if (half == h_lo && j >= 2) mbar_wait(&ds_done[db], ((j - 2) >> 1) & 1);  // dS buffer db was last read by the dQ MMAs of block j - 2
+        if (act) {
+          at_ds_half(sv, dv, m, p.scale_log2, nlse, delta, p.scale, tile, r, 4 * half, drow + (uint32_t)k0, dthr, p.drop.scale);
+        } else {
+#pragma unroll
+          for (int u = 0; u < 4; ++u) at_store_row_unit(tile, r, 4 * half + u, 0u, 0u, 0u, 0u);
+        }
       }
       fence_proxy_async();
       mbar_arrive(&ds_full[db]);
     }
     mbar_wait(&ds_done[(nkb - 1) & 1], ((nkb - 1) >> 1) & 1);
     tc_fence_after();
-    bf16* grow = p.dqkv + ((size_t)b * T + qi) * 3 * H + h * AT_D + 32 * half;
-    {
+#pragma unroll
+    for (int half = h_lo; half < h_hi; ++half) {
+      bf16* grow = p.dqkv + ((size_t)b * T + qi) * 3 * H + h * AT_D + 32 * half;
       uint32_t o[32];
-      tmem_ld_32x32(tDQ + lane_addr, o);
+      tmem_ld_32x32(tDQ + lane_base + 32 * half, o);
       tmem_ld_wait();
       if (qi < T) {
 #pragma unroll
@@ -543,7 +552,7 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 8) { tc_fence_after(); tmem_dealloc(tmem_base, 256); }
+  if (warp == CW) { tc_fence_after(); tmem_dealloc(tmem_base, 256); }
 }
 
 // ================================================================================================================================
@@ -553,7 +562,8 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
 // TMEM (256 columns): S^T at 0, dP^T at 64, dV at 128, dK at 192
 constexpr int AT_MAX_T_BWD = 1024;
 
-__global__ void __launch_bounds__(AT_BWD_THREADS, 2)
+template <bool DROP, int CW>
+__global__ void __launch_bounds__(32 * (CW + 2), 2)
 attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmKV, const __grid_constant__ CUtensorMap tmQ64,
                        const __grid_constant__ CUtensorMap tmDO64, const AttnTcParams p) {
   extern __shared__ uint8_t smem_raw[];
@@ -587,12 +597,12 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmKV, const __grid_co
     mbar_init(kv_full, 1);
     for (int s = 0; s < 2; ++s) { mbar_init(&qdo_full[s], 1); mbar_init(&qdo_free[s], 1); }
     mbar_init(sdp_full, 1);
-    mbar_init(sdp_free, 256);
-    mbar_init(pds_full, 256);
+    mbar_init(sdp_free, 32 * CW);
+    mbar_init(pds_full, 32 * CW);
     mbar_init(pds_done, 1);
     fence_mbar_init();
   }
-  if (warp == 8) { tmem_alloc(tmem_slot, 256); tmem_relinquish(); }
+  if (warp == CW) { tmem_alloc(tmem_slot, 256); tmem_relinquish(); }
   pdl_trigger();  // prologue done: the next kernel of the stream may start its own
   pdl_wait();     // the previous kernel's results are complete and visible from here on
   for (int t = i0 * 64 + threadIdx.x; t < nqb * 64; t += blockDim.x) {
@@ -606,7 +616,7 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmKV, const __grid_co
   const uint32_t tST = tmem_base, tDPT = tmem_base + 64, tDV = tmem_base + 128, tDK = tmem_base + 192;
   const int H = p.nh * AT_D;
 
-  if (warp == 9) {
+  if (warp == CW + 1) {
     if (lane == 0) {
       tma_prefetch_desc(&tmKV); tma_prefetch_desc(&tmQ64); tma_prefetch_desc(&tmDO64);
       mbar_arrive_expect_tx(kv_full, 2 * AT_TILE128);
@@ -620,7 +630,7 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmKV, const __grid_co
         tma_load_3d(sDO + s * AT_TILE64, &tmDO64, &qdo_full[s], h * AT_D, (i0 + t) * 64, b);
       }
     }
-  } else if (warp == 8) {
+  } else if (warp == CW) {
     if (lane == 0) {
       const uint32_t idesc_kk = make_idesc_bf16(128, 64, 0, 0), idesc_kn = make_idesc_bf16(128, 64, 0, 1);
       const uint32_t k_addr = smem_u32(sK), v_addr = smem_u32(sV), pt_addr = smem_u32(sPT), dst_addr = smem_u32(sDST);
@@ -661,65 +671,71 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmKV, const __grid_co
       }
     }
   } else {
-    // warp w (0-7): keys 32 (w & 3) .. +31 (its TMEM lane quadrant), queries 32 (w >> 2) .. +31 of every 64-query block
-    const int qd = warp & 3, half = warp >> 2;
+    // compute warps: TMEM lane quadrant qd = w & 3 (keys 32 qd .. +31, one per thread); CW = 8: warp w owns the 32-query half w >> 2 of
+    // every 64-query block, CW = 4: every thread walks both halves
+    const int qd = warp & 3, h_lo = CW == 8 ? (warp >> 2) : 0, h_hi = CW == 8 ? h_lo + 1 : 2;
     const int r = qd * 32 + lane;
     const int kj = k0 + r;
-    const uint32_t lane_addr = ((uint32_t)(qd * 32) << 16) + 32 * half;
+    const uint32_t lane_base = (uint32_t)(qd * 32) << 16;
     const bool key_ok = kj < T && (p.mask == nullptr || __ldg(p.mask + (size_t)b * p.Kmask + kj / 3) > 0.f);
-    const uint32_t dthr = p.drop.state ? p.drop.thr : 0u;
-    const uint32_t dcol = at_drop_key(p, b, h) + (uint32_t)kj;
+    const uint32_t dthr = DROP ? p.drop.thr : 0u;
+    const uint32_t dcol = DROP ? at_drop_key(p, b, h) + (uint32_t)kj : 0u;
     const uint32_t pt_tile = smem_u32(sPT), dst_tile = smem_u32(sDST);
     for (int t = 0; t < n; ++t) {
-      const int qc = (i0 + t) * 64 + 32 * half;             // first query of this warp's 32-wide chunk
-      const bool act = qc + 31 >= k0 + qd * 32 && qc < T;   // some (query, key) pair of this warp's rows is on or below the diagonal
       mbar_wait(sdp_full, t & 1);
       tc_fence_after();
-      uint32_t sv[32], dv[32];
-      if (act) {
-        tmem_ld_32x32(tST + lane_addr, sv);
-        tmem_ld_32x32(tDPT + lane_addr, dv);
-        tmem_ld_wait();
-      }
-      tc_fence_before();
-      mbar_arrive(sdp_free);
-      if (t > 0) mbar_wait(pds_done, (t - 1) & 1);  // P^T / dS^T were read by the previous block's dV / dK MMAs
-      if (act) {
-        // allowed queries of the chunk for this key: kj <= q < T
-        const int lo = kj - qc, hi = T - qc;
-        uint32_t word = lo <= 0 ? 0xffffffffu : (lo >= 32 ? 0u : ~((1u << lo) - 1u));
-        word &= hi >= 32 ? 0xffffffffu : ((1u << hi) - 1u);
-        if (!key_ok) word = 0u;
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
-          float pf[8], df[8];
-          const float4 l0 = *reinterpret_cast<const float4*>(sLse + qc + u * 8), l1 = *reinterpret_cast<const float4*>(sLse + qc + u * 8 + 4);
-          const float4 d0 = *reinterpret_cast<const float4*>(sDelta + qc + u * 8), d1 = *reinterpret_cast<const float4*>(sDelta + qc + u * 8 + 4);
-          const float nl[8] = {l0.x, l0.y, l0.z, l0.w, l1.x, l1.y, l1.z, l1.w}, dl[8] = {d0.x, d0.y, d0.z, d0.w, d1.x, d1.y, d1.z, d1.w};
-#pragma unroll
-          for (int e = 0; e < 8; ++e) {
-            const int col = u * 8 + e;
-            float pe = fast_exp2(fmaf(__uint_as_float(sv[col]), p.scale_log2, nl[e]));
-            pe = (word & (1u << col)) ? pe : 0.f;
-            float g = __uint_as_float(dv[col]);
-            bool keep = true;
-            if (dthr) {  // bit of (query qc + col, key kj); dV's 1 / (1 - p) is applied once in the epilogue
-              keep = drop_keep(dcol, (uint32_t)(qc + col) * (uint32_t)T, dthr);
-              g = keep ? g * p.drop.scale : 0.f;
-            }
-            pf[e] = keep ? pe : 0.f;
-            df[e] = pe * (g - dl[e]) * p.scale;
-          }
-          at_store_row_unit(pt_tile, r, 4 * half + u, pack_bf16x2(pf[0], pf[1]), pack_bf16x2(pf[2], pf[3]), pack_bf16x2(pf[4], pf[5]),
-                            pack_bf16x2(pf[6], pf[7]));
-          at_store_row_unit(dst_tile, r, 4 * half + u, pack_bf16x2(df[0], df[1]), pack_bf16x2(df[2], df[3]), pack_bf16x2(df[4], df[5]),
-                            pack_bf16x2(df[6], df[7]));
+      for (int half = h_lo; half < h_hi; ++half) {
+        const int qc = (i0 + t) * 64 + 32 * half;             // first query of the 32-wide chunk
+        const bool act = qc + 31 >= k0 + qd * 32 && qc < T;   // some (query, key) pair of this warp's rows is on or below the diagonal
+        uint32_t sv[32], dv[32];
+        if (act) {
+          tmem_ld_32x32(tST + lane_base + 32 * half, sv);
+          tmem_ld_32x32(tDPT + lane_base + 32 * half, dv);
+          tmem_ld_wait();
         }
-      } else {
+        if (half == h_hi - 1) {
+          tc_fence_before();
+          mbar_arrive(sdp_free);
+        }
+        if (half == h_lo && t > 0) mbar_wait(pds_done, (t - 1) & 1);  // P^T / dS^T were read by the previous block's dV / dK MMAs
+        if (act) {
+          // allowed queries of the chunk for this key: kj <= q < T
+          const int lo = kj - qc, hi = T - qc;
+          uint32_t word = lo <= 0 ? 0xffffffffu : (lo >= 32 ? 0u : ~((1u << lo) - 1u));
+          word &= hi >= 32 ? 0xffffffffu : ((1u << hi) - 1u);
+          if (!key_ok) word = 0u;
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
-          at_store_row_unit(pt_tile, r, 4 * half + u, 0u, 0u, 0u, 0u);
-          at_store_row_unit(dst_tile, r, 4 * half + u, 0u, 0u, 0u, 0u);
+          for (int u = 0; u < 4; ++u) {
+            float pf[8], df[8];
+            const float4 l0 = *reinterpret_cast<const float4*>(sLse + qc + u * 8), l1 = *reinterpret_cast<const float4*>(sLse + qc + u * 8 + 4);
+            const float4 d0 = *reinterpret_cast<const float4*>(sDelta + qc + u * 8), d1 = *reinterpret_cast<const float4*>(sDelta + qc + u * 8 + 4);
+            const float nl[8] = {l0.x, l0.y, l0.z, l0.w, l1.x, l1.y, l1.z, l1.w}, dl[8] = {d0.x, d0.y, d0.z, d0.w, d1.x, d1.y, d1.z, d1.w};
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+              const int col = u * 8 + e;
+              float pe = fast_exp2(fmaf(__uint_as_float(sv[col]), p.scale_log2, nl[e]));
+              pe = (word & (1u << col)) ? pe : 0.f;
+              float g = __uint_as_float(dv[col]);
+              bool keep = true;
+              if (dthr) {  // bit of (query qc + col, key kj); dV's 1 / (1 - p) is applied once in the epilogue
+                keep = drop_keep(dcol, (uint32_t)(qc + col) * (uint32_t)T, dthr);
+                g = keep ? g * p.drop.scale : 0.f;
+              }
+              pf[e] = keep ? pe : 0.f;
+              df[e] = pe * (g - dl[e]) * p.scale;
+            }
+            at_store_row_unit(pt_tile, r, 4 * half + u, pack_bf16x2(pf[0], pf[1]), pack_bf16x2(pf[2], pf[3]), pack_bf16x2(pf[4], pf[5]),
+                              pack_bf16x2(pf[6], pf[7]));
+            at_store_row_unit(dst_tile, r, 4 * half + u, pack_bf16x2(df[0], df[1]), pack_bf16x2(df[2], df[3]), pack_bf16x2(df[4], df[5]),
+                              pack_bf16x2(df[6], df[7]));
+          }
+        } else {
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            at_store_row_unit(pt_tile, r, 4 * half + u, 0u, 0u, 0u, 0u);
+            at_store_row_unit(dst_tile, r, 4 * half + u, 0u, 0u, 0u, 0u);
+          }
         }
       }
       fence_proxy_async();
@@ -727,29 +743,31 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmKV, const __grid_co
     }
     mbar_wait(pds_done, (n - 1) & 1);
     tc_fence_after();
-    bf16* grow = p.dqkv + ((size_t)b * T + kj) * 3 * H + h * AT_D + 32 * half;
 #pragma unroll
     for (int which = 0; which < 2; ++which) {  // 0: dV -> columns 2H.., 1: dK -> columns H..
-      uint32_t o[32];
-      tmem_ld_32x32((which == 0 ? tDV : tDK) + lane_addr, o);
-      tmem_ld_wait();
-      if (which == 0 && dthr) {
 #pragma unroll
-        for (int e = 0; e < 32; ++e) o[e] = __float_as_uint(__uint_as_float(o[e]) * p.drop.scale);
-      }
-      if (kj < T) {
-        bf16* dst = grow + (which == 0 ? 2 * H : H);
+      for (int half = h_lo; half < h_hi; ++half) {
+        uint32_t o[32];
+        tmem_ld_32x32((which == 0 ? tDV : tDK) + lane_base + 32 * half, o);
+        tmem_ld_wait();
+        if (which == 0 && dthr) {
 #pragma unroll
-        for (int e = 0; e < 32; e += 8)
-          *reinterpret_cast<uint4*>(dst + e) =
-              make_uint4(pack_bf16x2(__uint_as_float(o[e]), __uint_as_float(o[e + 1])), pack_bf16x2(__uint_as_float(o[e + 2]), __uint_as_float(o[e + 3])),
-                         pack_bf16x2(__uint_as_float(o[e + 4]), __uint_as_float(o[e + 5])), pack_bf16x2(__uint_as_float(o[e + 6]), __uint_as_float(o[e + 7])));
+          for (int e = 0; e < 32; ++e) o[e] = __float_as_uint(__uint_as_float(o[e]) * p.drop.scale);
+        }
+        if (kj < T) {
+          bf16* dst = p.dqkv + ((size_t)b * T + kj) * 3 * H + h * AT_D + 32 * half + (which == 0 ? 2 * H : H);
+#pragma unroll
+          for (int e = 0; e < 32; e += 8)
+            *reinterpret_cast<uint4*>(dst + e) =
+                make_uint4(pack_bf16x2(__uint_as_float(o[e]), __uint_as_float(o[e + 1])), pack_bf16x2(__uint_as_float(o[e + 2]), __uint_as_float(o[e + 3])),
+                           pack_bf16x2(__uint_as_float(o[e + 4]), __uint_as_float(o[e + 5])), pack_bf16x2(__uint_as_float(o[e + 6]), __uint_as_float(o[e + 7])));
+        }
       }
     }
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 8) { tc_fence_after(); tmem_dealloc(tmem_base, 256); }
+  if (warp == CW) { tc_fence_after(); tmem_dealloc(tmem_base, 256); }
 }
 
 constexpr int AT_FWD_SMEM = 1024 + AT_TILE128 + 2 * AT_KV_STAGES * AT_TILE64 + 2 * AT_TILE128 + 256 + AT_MAX_CHUNKS * 4;
@@ -784,18 +802,42 @@ int attn_fwd_tc(cudaStream_t stream, const bf16* qkv, const float* mask, int B, 
   p.mask = mask; p.out = out; p.lse = lse; p.drop = drop;
   static bool attr = false;
   if (!attr) {
-    DTB_CUDA(cudaFuncSetAttribute(attn_fwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_FWD_SMEM));
+    DTB_CUDA(cudaFuncSetAttribute(attn_fwd_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_FWD_SMEM));
+    DTB_CUDA(cudaFuncSetAttribute(attn_fwd_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_FWD_SMEM));
     attr = true;
   }
   dim3 grid((T + 127) / 128, nh, B);
   ProfScope prof(stream, PF_ATTN_FWD, 2.0 * B * nh * (double)T * T * d);
-  DTB_LAUNCH(attn_fwd_tc_kernel, grid, AT_THREADS, AT_FWD_SMEM, stream, tmQ, tmKV, p);
+  if (drop.state) DTB_LAUNCH(attn_fwd_tc_kernel<true>, grid, AT_THREADS, AT_FWD_SMEM, stream, tmQ, tmKV, p);
+  else DTB_LAUNCH(attn_fwd_tc_kernel<false>, grid, AT_THREADS, AT_FWD_SMEM, stream, tmQ, tmKV, p);
   DTB_CHECK_LAUNCH();
   return DTB_OK;
 }
 
 constexpr int AT_DQ_SMEM = 1024 + 2 * AT_TILE128 + (AT_DQ_KST + AT_DQ_VST) * AT_TILE64 + 2 * AT_TILE128 + 256 + AT_MAX_CHUNKS * 4;
 constexpr int AT_DKV_SMEM = 1024 + 2 * AT_TILE128 + 4 * AT_TILE64 + 2 * AT_TILE128 + 256 + 2 * AT_MAX_T_BWD * 4;
+
+template <bool DROP, int CW>
+static void at_bwd_attrs() {
+  cudaFuncSetAttribute(attn_bwd_dq_tc_kernel<DROP, CW>, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_DQ_SMEM);
+  cudaFuncSetAttribute(attn_bwd_dkv_tc_kernel<DROP, CW>, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_DKV_SMEM);
+}
+template <bool DROP, int CW>
+static void at_bwd_launch(dim3 grid, cudaStream_t stream, const CUtensorMap& tm128, const CUtensorMap& tm64, const CUtensorMap& tmDO128,
+                          const CUtensorMap& tmDO64, const AttnTcParams& p) {
+  DTB_LAUNCH((attn_bwd_dq_tc_kernel<DROP, CW>), grid, 32 * (CW + 2), AT_DQ_SMEM, stream, tm128, tm64, tmDO128, p);
+  DTB_LAUNCH((attn_bwd_dkv_tc_kernel<DROP, CW>), grid, 32 * (CW + 2), AT_DKV_SMEM, stream, tm128, tm64, tmDO64, p);
+}
+// compute warps of the backward kernels: 4 (each thread walks both 32-column halves) or 8 (one half per warp); env DTB_ATTN_BWD_WARPS
+static int at_bwd_warps(bool dropout) {
+  static int forced = -1;
+  if (forced < 0) {
+    const char* e = getenv("DTB_ATTN_BWD_WARPS");
+    forced = e ? atoi(e) : 0;
+  }
+  if (forced == 4 || forced == 8) return forced;
+  return dropout ? 8 : 4;
+}
 
 int attn_bwd_tc(cudaStream_t stream, const bf16* qkv, const float* mask, const bf16* out, const bf16* dout, const float* lse, int B, int T,
                 int nh, int d, bf16* dqkv, float* delta, const DropSite& drop) {
@@ -813,15 +855,14 @@ int attn_bwd_tc(cudaStream_t stream, const bf16* qkv, const float* mask, const b
   p.mask = mask; p.lse_in = lse; p.out_in = out; p.dout = dout; p.dqkv = dqkv; p.delta = delta; p.drop = drop;
   static bool attr = false;
   if (!attr) {
-    DTB_CUDA(cudaFuncSetAttribute(attn_bwd_dq_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_DQ_SMEM));
-    DTB_CUDA(cudaFuncSetAttribute(attn_bwd_dkv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_DKV_SMEM));
+    at_bwd_attrs<false, 4>(); at_bwd_attrs<true, 4>(); at_bwd_attrs<false, 8>(); at_bwd_attrs<true, 8>();
     attr = true;
   }
   dim3 grid((T + 127) / 128, nh, B);
   ProfScope prof(stream, PF_ATTN_BWD, 5.0 * B * nh * (double)T * T * d);
-  DTB_LAUNCH(attn_bwd_dq_tc_kernel, grid, AT_BWD_THREADS, AT_DQ_SMEM, stream, tm128, tm64, tmDO128, p);
-  DTB_CHECK_LAUNCH();
-  DTB_LAUNCH(attn_bwd_dkv_tc_kernel, grid, AT_BWD_THREADS, AT_DKV_SMEM, stream, tm128, tm64, tmDO64, p);
+  const bool w8 = at_bwd_warps(drop.state != nullptr) == 8;
+  if (drop.state) { if (w8) at_bwd_launch<true, 8>(grid, stream, tm128, tm64, tmDO128, tmDO64, p); else at_bwd_launch<true, 4>(grid, stream, tm128, tm64, tmDO128, tmDO64, p); }
+  else            { if (w8) at_bwd_launch<false, 8>(grid, stream, tm128, tm64, tmDO128, tmDO64, p); else at_bwd_launch<false, 4>(grid, stream, tm128, tm64, tmDO128, tmDO64, p); }
   DTB_CHECK_LAUNCH();
   return DTB_OK;
 }

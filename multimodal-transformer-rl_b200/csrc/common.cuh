@@ -57,7 +57,7 @@ long long launch_count();
 
 // Optional live profiling (bench.py roofline): CUDA events recorded on the launching stream around each launch of a kernel family.
 enum ProfFamily { PF_GEMM = 0, PF_CONV1_FWD, PF_CONV1_WGRAD, PF_ATTN_FWD, PF_ATTN_BWD, PF_LN_FWD, PF_LN_BWD, PF_EMBED_FWD, PF_COLSUM,
-                  PF_IM2COL, PF_COL2IM, PF_COUNT };
+                  PF_IM2COL, PF_COL2IM, PF_GEMM_MEM /* GEMM shapes below the machine balance: work = algorithmic bytes */, PF_COUNT };
 bool prof_on();
 int prof_begin(cudaStream_t stream, int family, double work);  // returns a slot (or -1)
 void prof_end(cudaStream_t stream, int slot);
@@ -264,7 +264,7 @@ __device__ __forceinline__ float fast_exp2(float x) {
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
 // ---- dropout (counter-based, stateless) ----------------------------------------------------------------------------------------
-// keep(site, step, group, idx) = mix32(key + idx) >= thr, thr = p * 2^32; key = f(seed, step, site[, group]).  The generator state
+// keep(site, step, group, idx) = bits32(key + idx) >= thr, thr = p * 2^32; key = f(seed, step, site[, group]).  The generator state
 // {seed_lo, seed_hi, step} lives in device memory so that a captured CUDA graph draws a fresh mask on every replay (a 1-thread
 // kernel advances `step`); forward and backward kernels of a site recompute the same bits, nothing is stored.  mix32 is the
 // "lowbias32" integer finaliser (two multiply / xor-shift rounds, full avalanche).  Replaces nn.Dropout at the reference's three
@@ -286,9 +286,15 @@ __device__ __forceinline__ uint32_t drop_site_key(const DropSite& d) {
   return drop_key_from(__ldg(d.state), __ldg(d.state + 1), __ldg(d.state + 2), d.site);
 }
 __host__ __device__ __forceinline__ uint32_t drop_group_key(uint32_t key, uint32_t group) { return drop_mix(key ^ (group * 0xC2B2AE35U + 0x27D4EB2FU)); }
-__host__ __device__ __forceinline__ bool drop_keep(uint32_t key, uint32_t idx, uint32_t thr) { return drop_mix(key + idx) >= thr; }
+// per-element draw: the same finaliser without its last xor-shift (it only repairs the low bits; the threshold compare is decided
+// by the high ones — lag / stride autocorrelation measured identical to the full finaliser)
+__host__ __device__ __forceinline__ uint32_t drop_bits(uint32_t x) {
+  x ^= x >> 16; x *= 0x7feb352dU; x ^= x >> 15; x *= 0x846ca68bU;
+  return x;
+}
+__host__ __device__ __forceinline__ bool drop_keep(uint32_t key, uint32_t idx, uint32_t thr) { return drop_bits(key + idx) >= thr; }
 __host__ __device__ __forceinline__ float drop_apply(float v, uint32_t key, uint32_t idx, uint32_t thr, float scale) {
-  return drop_mix(key + idx) >= thr ? v * scale : 0.f;
+  return drop_bits(key + idx) >= thr ? v * scale : 0.f;
 }
 static inline DropSite drop_none() { DropSite d; d.state = nullptr; d.site = 0; d.thr = 0; d.scale = 1.f; return d; }
 static inline DropSite drop_make(const void* state, uint32_t site, float p) {

@@ -195,7 +195,15 @@ int gemm_bf16(cudaStream_t stream, const bf16* A, int lda, int a_mn_major, const
     g_attr_set = true;
   }
   const int total = p.m_tiles * p.n_tiles * p.split_k;
-  ProfScope prof(stream, PF_GEMM, 2.0 * M * N * K);
+  // roofline family: a shape whose arithmetic intensity is below the machine balance (1 397 TFLOP/s / 6 457 GB/s = 216 flop/B,
+  // MEASURED_PEAKS.json) is HBM-bound; its work is counted in algorithmic bytes (operands once + every epilogue stream once)
+  const double flops = 2.0 * M * N * K, mn = (double)M * N;
+  const double bytes = 2.0 * ((double)M * K + (double)K * N) +
+                       (p.ep.partial ? 4.0 * mn * p.split_k
+                                   : mn * ((p.ep.out_bf16 ? 2.0 : 0.0) + (p.ep.out_f32 ? 4.0 : 0.0) + (p.ep.out_preact ? 2.0 : 0.0) +
+                                           (p.ep.residual ? 4.0 : 0.0) + (p.ep.dact ? 2.0 : 0.0)));
+  const bool mem_bound = flops < 216.0 * bytes;
+  ProfScope prof(stream, mem_bound ? PF_GEMM_MEM : PF_GEMM, mem_bound ? bytes : flops);
   if (pair) {
     const int npairs = total < num_sms() / 2 ? total : num_sms() / 2;
     DTB_LAUNCH(gemm_tcgen05_pair_kernel, 2 * npairs, GEMM2_THREADS, GEMM2_SMEM_BYTES, stream, tmA, tmB, p);

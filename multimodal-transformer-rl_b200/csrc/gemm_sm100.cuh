@@ -22,7 +22,8 @@ constexpr int GEMM_MAX_BN = 256;
 constexpr int GEMM_THREADS = 256;  // warp0 TMA, warp1 MMA, warp2 TMEM alloc, warp3 idle, warps4-7 epilogue
 constexpr int GEMM_A_STAGE_BYTES = GEMM_BM * GEMM_BK * 2;      // 16 KB
 constexpr int GEMM_B_STAGE_BYTES = GEMM_MAX_BN * GEMM_BK * 2;  // 32 KB
-constexpr int GEMM_SMEM_BYTES = GEMM_STAGES * (GEMM_A_STAGE_BYTES + GEMM_B_STAGE_BYTES) + 1024 /*align*/ + 256 /*barriers*/;
+constexpr int GEMM_EPI_STAGE_BYTES = 4 * 32 * 36 * 4;  // 4 epilogue warps x [32 rows x 36 words] transpose staging (EPI_WARP_WORDS)
+constexpr int GEMM_SMEM_BYTES = GEMM_STAGES * (GEMM_A_STAGE_BYTES + GEMM_B_STAGE_BYTES) + 1024 /*align*/ + 256 /*barriers*/ + GEMM_EPI_STAGE_BYTES;
 
 // One 32-column chunk of one accumulator row: bias / activation / act' / residual / stores (or the split-K partial store).
 __device__ __forceinline__ void gemm_epilogue_chunk(const GemmParams& p, const GemmEpilogue& ep, const uint32_t (&v)[32], int row, bool row_ok,
@@ -115,162 +116,7 @@ __device__ __forceinline__ void gemm_epilogue_chunk(const GemmParams& p, const G
         }
 }
 
-__global__ void __launch_bounds__(GEMM_THREADS, 1)
-gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmParams p) {
-  extern __shared__ uint8_t smem_raw[];
-  // 1024-byte alignment is required by the 128B swizzle atoms.
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* smA = smem;
-  uint8_t* smB = smem + GEMM_STAGES * GEMM_A_STAGE_BYTES;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + GEMM_STAGES * (GEMM_A_STAGE_BYTES + GEMM_B_STAGE_BYTES));
-  uint64_t* full_bar = bars;                     // [STAGES]  TMA -> MMA
-  uint64_t* empty_bar = bars + GEMM_STAGES;      // [STAGES]  MMA -> TMA
-  uint64_t* tfull_bar = bars + 2 * GEMM_STAGES;  // [2]       MMA -> epilogue
-  uint64_t* tempty_bar = tfull_bar + 2;          // [2]       epilogue -> MMA
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
-
-  const int warp = threadIdx.x >> 5;
-  const int lane = threadIdx.x & 31;
-
-  if (warp == 0 && lane == 0) {
-    tma_prefetch_desc(&tmA);
-    tma_prefetch_desc(&tmB);
-  }
-  if (warp == 1 && lane == 0) {
-    for (int s = 0; s < GEMM_STAGES; ++s) {
-      mbar_init(&full_bar[s], 1);
-      mbar_init(&empty_bar[s], 1);
-    }
-    for (int s = 0; s < 2; ++s) {
-      mbar_init(&tfull_bar[s], 1);
-      mbar_init(&tempty_bar[s], 4);  // one arrive per epilogue warp
-    }
-    fence_mbar_init();
-  }
-  if (warp == 2) {
-    tmem_alloc(tmem_slot, 512);
-    tmem_relinquish();
-  }
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  const uint32_t tmem_base = *tmem_slot;
-  pdl_trigger();  // prologue done: the next kernel of the stream may start its own
-  pdl_wait();     // the previous kernel's results are complete and visible from here on
-
-  const int total_tiles = p.m_tiles * p.n_tiles * p.split_k;
-  const int kblocks_total = (p.K + GEMM_BK - 1) / GEMM_BK;
-  const int BN = p.BN;
-  const uint32_t a_bytes = GEMM_A_STAGE_BYTES;
-  const uint32_t b_bytes = (uint32_t)BN * GEMM_BK * 2;
-
-  if (warp == 0) {
-    // ===================== TMA producer =====================
-    if (lane == 0) {
-      uint32_t stage = 0, phase = 0;
-      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
-        const int split = t / (p.m_tiles * p.n_tiles);
-        const int mn = t - split * (p.m_tiles * p.n_tiles);
-        const int m0 = (mn / p.n_tiles) * GEMM_BM;
-        const int n0 = (mn % p.n_tiles) * BN;
-        const int kb0 = split * p.kb_per_split;
-        const int kb1 = min(kb0 + p.kb_per_split, kblocks_total);
-        for (int kb = kb0; kb < kb1; ++kb) {
-          mbar_wait(&empty_bar[stage], phase ^ 1);
-          mbar_arrive_expect_tx(&full_bar[stage], a_bytes + b_bytes);
-          uint8_t* a_dst = smA + stage * GEMM_A_STAGE_BYTES;
-          uint8_t* b_dst = smB + stage * GEMM_B_STAGE_BYTES;
-          const int k0 = kb * GEMM_BK;
-          if (!p.a_mn_major) {
-            tma_load_2d(a_dst, &tmA, &full_bar[stage], k0, m0);  // box [64 k][128 m]
-          } else {
-            tma_load_2d(a_dst, &tmA, &full_bar[stage], m0, k0);  // box [64 m][64 k] x2
-            tma_load_2d(a_dst + GEMM_BK * 128, &tmA, &full_bar[stage], m0 + 64, k0);
-          }
-          if (!p.b_mn_major) {
-            tma_load_2d(b_dst, &tmB, &full_bar[stage], k0, n0);  // box [64 k][BN n]
-          } else {
-            for (int j = 0; j < BN / 64; ++j)
-              tma_load_2d(b_dst + j * (GEMM_BK * 128), &tmB, &full_bar[stage], n0 + 64 * j, k0);
-          }
-          if (++stage == GEMM_STAGES) { stage = 0; phase ^= 1; }
-        }
-      }
-    }
-  } else if (warp == 1) {
-    // ===================== MMA issuer (single thread) =====================
-    if (lane == 0) {
-      const uint32_t idesc = make_idesc_bf16(GEMM_BM, BN, p.a_mn_major, p.b_mn_major);
-      // descriptor constants per major
-      const uint32_t a_lbo = p.a_mn_major ? GEMM_BK * 128 : 16;
-      const uint32_t b_lbo = p.b_mn_major ? GEMM_BK * 128 : 16;
-      const uint32_t a_kstep = p.a_mn_major ? 16 * 128 : 32;  // bytes per UMMA_K=16 step
-      const uint32_t b_kstep = p.b_mn_major ? 16 * 128 : 32;
-      uint32_t stage = 0, phase = 0;
-      uint32_t acc = 0, acc_phase = 0;
-      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
-        const int split = t / (p.m_tiles * p.n_tiles);
-        const int kb0 = split * p.kb_per_split;
-        const int kb1 = min(kb0 + p.kb_per_split, kblocks_total);
-        mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
-        tc_fence_after();
-        const uint32_t d_tmem = tmem_base + acc * GEMM_MAX_BN;
-        for (int kb = kb0; kb < kb1; ++kb) {
-          mbar_wait(&full_bar[stage], phase);
-          tc_fence_after();
-          const uint32_t a_addr = smem_u32(smA + stage * GEMM_A_STAGE_BYTES);
-          const uint32_t b_addr = smem_u32(smB + stage * GEMM_B_STAGE_BYTES);
-#pragma unroll
-          for (int kk = 0; kk < GEMM_BK / 16; ++kk) {
-            const uint64_t adesc = make_smem_desc_sw128(a_addr + kk * a_kstep, a_lbo, 1024);
-            const uint64_t bdesc = make_smem_desc_sw128(b_addr + kk * b_kstep, b_lbo, 1024);
-            umma_bf16(d_tmem, adesc, bdesc, idesc, (kb > kb0 || kk > 0) ? 1u : 0u);
-          }
-          umma_commit(&empty_bar[stage]);  // frees the smem slot when these MMAs retire
-          if (++stage == GEMM_STAGES) { stage = 0; phase ^= 1; }
-        }
-        umma_commit(&tfull_bar[acc]);  // accumulator ready for the epilogue
-        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
-      }
-    }
-  } else if (warp >= 4) {
-    // ===================== epilogue: TMEM -> registers -> global =====================
-    const int q = warp & 3;  // TMEM lane quadrant accessible to this warp
-    const GemmEpilogue& ep = p.ep;
-    uint32_t acc = 0, acc_phase = 0;
-    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
-      const int split = t / (p.m_tiles * p.n_tiles);
-      const int mn = t - split * (p.m_tiles * p.n_tiles);
-      const int m0 = (mn / p.n_tiles) * GEMM_BM;
-      const int n0 = (mn % p.n_tiles) * BN;
-      const int row = m0 + q * 32 + lane;
-      const bool row_ok = row < p.M;
-      mbar_wait(&tfull_bar[acc], acc_phase);
-      tc_fence_after();
-      for (int c = 0; c < BN; c += 32) {
-        uint32_t v[32];
-        tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + acc * GEMM_MAX_BN + c, v);
-        tmem_ld_wait();
-        gemm_epilogue_chunk(p, ep, v, row, row_ok, n0 + c, split);
-      }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&tempty_bar[acc]);
-      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
-    }
-  }
-
-  tc_fence_before();
-  __syncthreads();
-  if (warp == 2) {
-    tc_fence_after();
-    tmem_dealloc(tmem_base, 512);
-  }
-}
-
-
-
-// ---- staged epilogue (CTA-pair kernel): every global access of the epilogue is warp-coalesced --------------------------------------
+// ---- staged epilogue (both kernels): every global access of the epilogue is warp-coalesced --------------------------------------
 // A warp owns 32 accumulator rows (TMEM lanes) x 32 columns per chunk, one row per thread.  Row-per-thread global accesses touch 32
 // different 128-byte lines per instruction, which made the epilogue (not the tensor pipe) the bound of the forward / dgrad GEMMs.
 // Here every tile that enters or leaves the thread-owns-a-row layout is transposed through a per-warp shared-memory buffer
@@ -419,6 +265,177 @@ __device__ __forceinline__ void gemm_epilogue_chunk_staged(const GemmParams& p, 
   if (ep.out_f32) epi_write_f32(st, lane, f, ep.out_f32, ep.ldo_f, row0, p.M, col0, ncols);
   if (ep.out_bf16) epi_write_bf16(st, lane, f, ep.out_bf16, ep.ldo_b, row0, p.M, col0, ncols);
 }
+
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  // 1024-byte alignment is required by the 128B swizzle atoms.
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smA = smem;
+  uint8_t* smB = smem + GEMM_STAGES * GEMM_A_STAGE_BYTES;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + GEMM_STAGES * (GEMM_A_STAGE_BYTES + GEMM_B_STAGE_BYTES));
+  uint64_t* full_bar = bars;                     // [STAGES]  TMA -> MMA
+  uint64_t* empty_bar = bars + GEMM_STAGES;      // [STAGES]  MMA -> TMA
+  uint64_t* tfull_bar = bars + 2 * GEMM_STAGES;  // [2]       MMA -> epilogue
+  uint64_t* tempty_bar = tfull_bar + 2;          // [2]       epilogue -> MMA
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < GEMM_STAGES; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&tfull_bar[s], 1);
+      mbar_init(&tempty_bar[s], 4);  // one arrive per epilogue warp
+    }
+    fence_mbar_init();
+  }
+  if (warp == 2) {
+    tmem_alloc(tmem_slot, 512);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  pdl_trigger();  // prologue done: the next kernel of the stream may start its own
+  pdl_wait();     // the previous kernel's results are complete and visible from here on
+
+  const int total_tiles = p.m_tiles * p.n_tiles * p.split_k;
+  const int kblocks_total = (p.K + GEMM_BK - 1) / GEMM_BK;
+  const int BN = p.BN;
+  const uint32_t a_bytes = GEMM_A_STAGE_BYTES;
+  const uint32_t b_bytes = (uint32_t)BN * GEMM_BK * 2;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      uint32_t stage = 0, phase = 0;
+      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+        const int split = t / (p.m_tiles * p.n_tiles);
+        const int mn = t - split * (p.m_tiles * p.n_tiles);
+        const int m0 = (mn / p.n_tiles) * GEMM_BM;
+        const int n0 = (mn % p.n_tiles) * BN;
+        const int kb0 = split * p.kb_per_split;
+        const int kb1 = min(kb0 + p.kb_per_split, kblocks_total);
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          mbar_arrive_expect_tx(&full_bar[stage], a_bytes + b_bytes);
+          uint8_t* a_dst = smA + stage * GEMM_A_STAGE_BYTES;
+          uint8_t* b_dst = smB + stage * GEMM_B_STAGE_BYTES;
+          const int k0 = kb * GEMM_BK;
+          if (!p.a_mn_major) {
+            tma_load_2d(a_dst, &tmA, &full_bar[stage], k0, m0);  // box [64 k][128 m]
+          } else {
+            tma_load_2d(a_dst, &tmA, &full_bar[stage], m0, k0);  // box [64 m][64 k] x2
+            tma_load_2d(a_dst + GEMM_BK * 128, &tmA, &full_bar[stage], m0 + 64, k0);
+          }
+          if (!p.b_mn_major) {
+            tma_load_2d(b_dst, &tmB, &full_bar[stage], k0, n0);  // box [64 k][BN n]
+          } else {
+            for (int j = 0; j < BN / 64; ++j)
+              tma_load_2d(b_dst + j * (GEMM_BK * 128), &tmB, &full_bar[stage], n0 + 64 * j, k0);
+          }
+          if (++stage == GEMM_STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer (single thread) =====================
+    if (lane == 0) {
+      const uint32_t idesc = make_idesc_bf16(GEMM_BM, BN, p.a_mn_major, p.b_mn_major);
+      // descriptor constants per major
+      const uint32_t a_lbo = p.a_mn_major ? GEMM_BK * 128 : 16;
+      const uint32_t b_lbo = p.b_mn_major ? GEMM_BK * 128 : 16;
+      const uint32_t a_kstep = p.a_mn_major ? 16 * 128 : 32;  // bytes per UMMA_K=16 step
+      const uint32_t b_kstep = p.b_mn_major ? 16 * 128 : 32;
+      uint32_t stage = 0, phase = 0;
+      uint32_t acc = 0, acc_phase = 0;
+      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+        const int split = t / (p.m_tiles * p.n_tiles);
+        const int kb0 = split * p.kb_per_split;
+        const int kb1 = min(kb0 + p.kb_per_split, kblocks_total);
+        mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * GEMM_MAX_BN;
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t a_addr = smem_u32(smA + stage * GEMM_A_STAGE_BYTES);
+          const uint32_t b_addr = smem_u32(smB + stage * GEMM_B_STAGE_BYTES);
+#pragma unroll
+          for (int kk = 0; kk < GEMM_BK / 16; ++kk) {
+            const uint64_t adesc = make_smem_desc_sw128(a_addr + kk * a_kstep, a_lbo, 1024);
+            const uint64_t bdesc = make_smem_desc_sw128(b_addr + kk * b_kstep, b_lbo, 1024);
+            umma_bf16(d_tmem, adesc, bdesc, idesc, (kb > kb0 || kk > 0) ? 1u : 0u);
+          }
+          umma_commit(&empty_bar[stage]);  // frees the smem slot when these MMAs retire
+          if (++stage == GEMM_STAGES) { stage = 0; phase ^= 1; }
+        }
+        umma_commit(&tfull_bar[acc]);  // accumulator ready for the epilogue
+        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+      }
+    }
+  } else if (warp >= 4) {
+    // ===================== epilogue: TMEM -> registers -> global =====================
+    const int q = warp & 3;  // TMEM lane quadrant accessible to this warp
+    const GemmEpilogue& ep = p.ep;
+    uint32_t* st = reinterpret_cast<uint32_t*>(smem + GEMM_STAGES * (GEMM_A_STAGE_BYTES + GEMM_B_STAGE_BYTES) + 256) + q * EPI_WARP_WORDS;
+    uint32_t acc = 0, acc_phase = 0;
+    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+      const int split = t / (p.m_tiles * p.n_tiles);
+      const int mn = t - split * (p.m_tiles * p.n_tiles);
+      const int m0 = (mn / p.n_tiles) * GEMM_BM;
+      const int n0 = (mn % p.n_tiles) * BN;
+      const int row0 = m0 + q * 32;
+      // the first chunk's bias / residual / aux blocks are fetched (coalesced) before the accumulator is ready
+      EpiLoadF32 Lr;
+      EpiLoadBf16 La;
+      float bias_lane = 0.f;
+      auto prefetch = [&](int col0) {
+        if (ep.partial || col0 >= p.N) return;
+        const int ncols = min(32, p.N - col0);
+        if (ep.bias) bias_lane = lane < ncols ? __ldg(ep.bias + col0 + lane) : 0.f;
+        if (ep.residual) epi_issue_f32(Lr, lane, ep.residual, ep.ldr, row0, p.M, col0, ncols);
+        if (ep.dact) epi_issue_bf16(La, lane, ep.aux, ep.ldaux, row0, p.M, col0, ncols);
+      };
+      prefetch(n0);
+      mbar_wait(&tfull_bar[acc], acc_phase);
+      tc_fence_after();
+      for (int c = 0; c < BN; c += 32) {
+        uint32_t v[32];
+        tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + acc * GEMM_MAX_BN + c, v);
+        tmem_ld_wait();
+        const EpiLoadF32 Lr_cur = Lr;
+        const EpiLoadBf16 La_cur = La;
+        const float bias_cur = bias_lane;
+        if (c + 32 < BN) prefetch(n0 + c + 32);  // next chunk's operands fly while this one is processed
+        gemm_epilogue_chunk_staged(p, ep, v, st, lane, row0, n0 + c, split, bias_cur, Lr_cur, La_cur);
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tempty_bar[acc]);
+      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 512);
+  }
+}
+
+
 
 // ================================================================================================================================
 // CTA-pair variant (cta_group::2): two CTAs of a cluster (the two SMs of a TPC) compute one 256 x 256 tile.  Each CTA stages its

@@ -70,6 +70,10 @@ def attn_suite(B, K, nh, d):
     timeit(f"attn_fwd B={B} T={T} nh={nh} d={d}", lambda: _lib.attention_fwd(qkv, mask, nh, out, lse), flops=fl)
     dout, dqkv, delta = bf(B, T, H), torch.empty(B, T, 3 * H, device=dev, dtype=torch.bfloat16), torch.empty(B, nh, T, device=dev)
     timeit(f"attn_bwd B={B} T={T} nh={nh} d={d}", lambda: _lib.attention_bwd(qkv, mask, out, dout, lse, nh, dqkv, delta), flops=2.5 * fl)
+    st = torch.tensor([1, 2, 3], dtype=torch.int32, device=dev)  # dropout generator state {seed_lo, seed_hi, step}
+    timeit(f"attn_fwd p=0.1 B={B} T={T} nh={nh} d={d}", lambda: _lib.attention_fwd(qkv, mask, nh, out, lse, st, 1, 0.1), flops=fl)
+    timeit(f"attn_bwd p=0.1 B={B} T={T} nh={nh} d={d}", lambda: _lib.attention_bwd(qkv, mask, out, dout, lse, nh, dqkv, delta, st, 1, 0.1),
+           flops=2.5 * fl)
 
 
 if __name__ == "__main__":
