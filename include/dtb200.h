@@ -161,6 +161,31 @@ typedef struct dtb_dt dtb_dt;
 
 int dtb_dt_create(const dtb_dt_config* cfg, dtb_dt** out);
 int dtb_dt_destroy(dtb_dt* h);
+/* ---- fused gradient clipping + AdamW (trainer tail) -------------------------------------------------
+ * Replaces, after loss.backward() in the reference's SequenceTrainer.train_step():
+ *     torch.nn.utils.clip_grad_norm_(model.parameters(), .25); optimizer.step()        (torch.optim.AdamW(lr, weight_decay))
+ * over the flat fp32 parameter / gradient buffers of up to 8 modules (one global norm across all of them, as clip_grad_norm_ over
+ * model.parameters()).  Three launches, no host synchronisation: the step count (and optionally the learning rate, for schedulers
+ * inside a CUDA graph) live in device memory.  When `params_bf16` is given the bf16 shadow the GEMMs read is rewritten in the same pass.
+ * scratch: dtb_adamw_scratch_floats() floats; after the call scratch[3] = the global gradient norm before clipping, scratch[0] = the
+ * clip coefficient applied. */
+typedef struct {
+  float* params;       /* fp32 master parameters [n] */
+  float* grads;        /* fp32 gradients [n] (scaled in place by the clip coefficient when write_clipped_grads != 0) */
+  float* exp_avg;      /* Adam first moment [n] */
+  float* exp_avg_sq;   /* Adam second moment [n] */
+  void* params_bf16;   /* optional bf16 shadow [n] */
+  long long n;
+} dtb_adamw_segment;
+typedef struct {
+  double lr, beta1, beta2, eps, weight_decay; /* doubles: torch forms 1 - beta, lr / (1 - beta1^t), ... in Python doubles */
+  double max_norm;            /* <= 0: no clipping */
+  const float* lr_dev;        /* optional device scalar overriding lr */
+  int write_clipped_grads;
+} dtb_adamw_hparams;
+size_t dtb_adamw_scratch_floats(void);
+int dtb_clip_adamw_step(void* stream, int nseg, const dtb_adamw_segment* segs, const dtb_adamw_hparams* hp, int* step_dev, float* scratch);
+
 /* Dropout (nn.Dropout at the three GPT-2 sites of the reference's trunk; HF modeling_gpt2 GPT2Model.drop (embd_pdrop),
  * GPT2Attention.attn_dropout (attn_pdrop, :60-62 of modeling_decision_transformer eager attention) and resid_dropout / GPT2MLP.dropout
  * (resid_pdrop, :217-218, :236-237); kzl-style DecisionTransformer passes resid_pdrop = attn_pdrop = dropout, default 0.1).

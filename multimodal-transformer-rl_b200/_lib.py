@@ -33,6 +33,16 @@ class DtBatch(C.Structure):
                 ("returns_to_go", C.c_void_p), ("timesteps", C.c_void_p), ("attention_mask", C.c_void_p), ("states_relu", C.c_int)]
 
 
+class AdamwSegment(C.Structure):
+    _fields_ = [("params", C.c_void_p), ("grads", C.c_void_p), ("exp_avg", C.c_void_p), ("exp_avg_sq", C.c_void_p),
+                ("params_bf16", C.c_void_p), ("n", C.c_longlong)]
+
+
+class AdamwHparams(C.Structure):
+    _fields_ = [("lr", C.c_double), ("beta1", C.c_double), ("beta2", C.c_double), ("eps", C.c_double), ("weight_decay", C.c_double),
+                ("max_norm", C.c_double), ("lr_dev", C.c_void_p), ("write_clipped_grads", C.c_int)]
+
+
 class TowerConfig(C.Structure):
     _fields_ = [("in_channels", C.c_int), ("in_h", C.c_int), ("in_w", C.c_int), ("big", C.c_int)]
 
@@ -80,6 +90,8 @@ def _declare(lib):
     lib.dtb_encoder_backward_u8.argtypes = lib.dtb_encoder_backward.argtypes
     lib.dtb_pad_left.argtypes = [vp, i, C.POINTER(vp), C.POINTER(vp), C.POINTER(i), i, i, vp]
     lib.dtb_dt_set_dropout.argtypes = [vp, f, f, f, vp]
+    lib.dtb_adamw_scratch_floats.restype = sz
+    lib.dtb_clip_adamw_step.argtypes = [vp, i, C.POINTER(AdamwSegment), C.POINTER(AdamwHparams), vp, vp]
     lib.dtb_attention_fwd_dropout.argtypes = [vp, vp, vp, i, i, i, i, vp, vp, vp, C.c_uint, f]
     lib.dtb_attention_bwd_dropout.argtypes = [vp, vp, vp, vp, vp, vp, i, i, i, i, vp, vp, vp, C.c_uint, f]
     lib.dtb_dropout_advance.argtypes = [vp, vp]

@@ -95,6 +95,11 @@ int dtb_attention_bwd_dropout(void* stream, const void* qkv, const float* mask, 
   return attn_bwd((cudaStream_t)stream, (const bf16*)qkv, mask, (const bf16*)out, (const bf16*)dout, lse, B, T, n_head, head_dim,
                   (bf16*)dqkv, delta, drop_make(drop_state, site, p));
 }
+size_t dtb_adamw_scratch_floats(void) { return adamw_scratch_floats(); }
+int dtb_clip_adamw_step(void* stream, int nseg, const dtb_adamw_segment* segs, const dtb_adamw_hparams* hp, int* step_dev, float* scratch) {
+  DTB_TRY(require_sm100());
+  return clip_adamw_step((cudaStream_t)stream, nseg, segs, hp, step_dev, scratch);
+}
 int dtb_cast_transpose(void* stream, const float* src, int R, int C, void* dst, void* dst_t) {
   DTB_REQUIRE(src, DTB_ERR_BAD_ARG, "dtb_cast_transpose: null pointer");
   return cast_transpose((cudaStream_t)stream, src, R, C, (bf16*)dst, (bf16*)dst_t);

@@ -64,6 +64,10 @@ int dropout_mask(cudaStream_t stream, const DropSite& d, int groups, long long n
 
 int pad_left(cudaStream_t stream, int nseg, const void* const* srcs, void* const* dsts, const int* row_bytes, int t, int K, float* mask);
 
+// ---- optim.cu ------------------------------------------------------------------------------------
+size_t adamw_scratch_floats();
+int clip_adamw_step(cudaStream_t stream, int nseg, const dtb_adamw_segment* segs, const dtb_adamw_hparams* hp, int* step_dev, float* scratch);
+
 // ---- layernorm.cu ------------------------------------------------------------------------------
 int ln_fwd(cudaStream_t stream, const float* x, const float* gamma, const float* beta, int M, int H, float eps, bf16* y, float* mean,
            float* rstd);

@@ -4,7 +4,8 @@
 With ``loss_fn=None`` (the upstream loss: mean squared action error over rows with ``attention_mask > 0``) the step is the
 fused one: forward + loss + backward run inside ``libdtb200.so`` and write gradients straight into the model's flat
 gradient buffer; a custom ``loss_fn(s_hat, a_hat, r_hat, s, a, r)`` goes through the generic autograd bridge instead.
-Gradient clipping (0.25) and the optimizer are the caller's torch objects, as upstream.
+Gradient clipping (0.25) and the optimizer are the caller's torch objects, as upstream — or ``mtrl_b200.optim.FusedClipAdamW``, which
+does both on the flat buffers in three launches (then ``clip_grad_norm_`` is not called separately; its threshold is ``grad_clip``).
 """
 from __future__ import annotations
 
@@ -17,6 +18,11 @@ class SequenceTrainer:
         self.loss_fn, self.scheduler, self.grad_clip = loss_fn, scheduler, grad_clip
         self.eval_fns = [] if eval_fns is None else eval_fns
         self.diagnostics = {}
+        from .optim import FusedClipAdamW
+
+        self._fused_opt = isinstance(optimizer, FusedClipAdamW)
+        if self._fused_opt:
+            optimizer.max_norm = grad_clip
 
     def loss_and_backward(self, batch):
         """forward + masked action MSE + backward (what the tokens/s metric times; optimizer excluded).  Returns a device scalar."""
@@ -39,7 +45,8 @@ class SequenceTrainer:
     def train_step(self):
         batch = self.get_batch(self.batch_size)
         loss = self.loss_and_backward(batch)
-        torch.nn.utils.clip_grad_norm_(self.model.parameters(), self.grad_clip)
+        if not self._fused_opt:
+            torch.nn.utils.clip_grad_norm_(self.model.parameters(), self.grad_clip)
         self.optimizer.step()
         if self.scheduler is not None:
             self.scheduler.step()

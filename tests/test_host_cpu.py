@@ -142,3 +142,36 @@ def test_data_parallel_allreduce_world2_gloo(tmp_path):
                         "--master-port", "29731", str(script), ROOT], capture_output=True, text=True, timeout=240, env=env)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
     assert r.stdout.count("ok") == 2
+
+
+def test_no_global_access_is_hoisted_above_the_pdl_wait():
+    """Every kernel launched with programmatic dependent launch starts while its predecessor may still be running and must not touch
+    global memory before `griddepcontrol.wait` (SASS: ACQBULK).  nvcc is free to hoist `const __restrict__` / __ldg loads above the
+    asm statement (it did, in opt_adamw_kernel: LDG.E.CONSTANT of the step scalars before ACQBULK -> stale clip coefficient), so the
+    compiled SASS of every kernel that contains the wait is scanned: only shared-memory traffic may precede it."""
+    import glob
+    import re
+    import shutil
+    import subprocess
+
+    cuobjdump = shutil.which("cuobjdump") or "/usr/local/cuda/bin/cuobjdump"
+    if not os.path.exists(cuobjdump):
+        pytest.skip("cuobjdump not available")
+    objs = sorted(glob.glob(os.path.join(ROOT, "multimodal-transformer-rl_b200", "build", "*.o")))
+    if not objs:
+        pytest.skip("library objects not built (run __graft_entry__.build())")
+    offenders, checked = [], 0
+    for obj in objs:
+        sass = subprocess.run([cuobjdump, "-sass", obj], capture_output=True, text=True, check=True).stdout
+        for body in re.split(r"Function : ", sass)[1:]:
+            name = body.split()[0]
+            if "ACQBULK" not in body:
+                continue  # launched without the PDL attribute (plain stream order)
+            checked += 1
+            before = body.split("ACQBULK")[0]
+            ops = re.findall(r"\*/\s+(?:@!?U?P\d+\s+)?([A-Z][A-Z0-9_.]*)", before)
+            bad = [o for o in ops if o.startswith(("LDG", "STG", "ATOMG", "RED", "LDTM", "UTMALDG", "UBLKCP"))]
+            if bad:
+                offenders.append((os.path.basename(obj), name[:60], bad))
+    assert checked >= 20, checked
+    assert not offenders, offenders
