@@ -269,6 +269,39 @@ def run_ours(args, wl, rank, world, local_rank):
     clock_info = clocks.stop() if rank == 0 else None
     consistent = replicas_consistent([p.flat_params for p in parts])
 
+    # ---- extra (not the headline metric, which excludes the optimizer as BASELINE.json's does): the full train_step() body, i.e. the same
+    # step followed by the fused clip_grad_norm_(0.25) + AdamW over the flat buffers (mtrl_b200.optim.FusedClipAdamW), in one graph ----
+    with_opt = None
+    if not args.no_optimizer_extra:
+        try:
+            from mtrl_b200.optim import FusedClipAdamW
+
+            opt = FusedClipAdamW(parts, lr=1e-4, weight_decay=1e-4, max_norm=0.25)
+            raw = make_step(wl, model, parts, dev_in, reducer, 1.0 / world)  # no forced re-staging: the optimizer rewrites the bf16 shadow
+
+            def full_step():
+                out_ = raw()
+                opt.step()
+                return out_
+
+            for _ in range(3):
+                full_step()
+            torch.cuda.synchronize(dev)
+            fn2 = full_step
+            if graphed:
+                g2 = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g2):
+                    full_step()
+                fn2 = g2.replay
+            for _ in range(3):
+                fn2()
+            ms2, _ = timed_loop(fn2, args.steps, dev, flush, dist_on=world > 1)
+            with_opt = {"ms_per_step": ms2, "value": tokens / ms2 * 1e3, "unit": "tokens/s", "optimizer_steps": opt.step_count,
+                        "what": "fwd + loss + bwd + fused clip_grad_norm_(0.25) + AdamW (3 extra launches), same graph",
+                        "replicas_consistent": replicas_consistent([p.flat_params for p in parts])}
+        except Exception as e:  # noqa: BLE001
+            with_opt = {"error": str(e)[:200]}
+
     res = {
         "metric": "DT train tokens/s (fwd+bwd)", "value": value, "unit": "tokens/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
@@ -283,6 +316,7 @@ def run_ours(args, wl, rank, world, local_rank):
         "gpu_launches": launches_per_step * args.steps, "launches_per_step": launches_per_step,
         "clocks": clock_info, "loss": loss_val, "wall_ms_per_step": wall_ms,
         "algorithmic_tflops_per_s": algorithmic_flops_per_step(wl, B * world) / ms / 1e9, "replicas_consistent": consistent,
+        "train_step_with_optimizer": with_opt,
     }
     return res, dict(model=model, parts=parts, dev=dev, dev_in=dev_in, step=step, world=world)
 
@@ -503,6 +537,7 @@ def main():
     ap.add_argument("--no-roofline", action="store_true")
     ap.add_argument("--no-get-action", action="store_true", help="skip the get_action latency measurement (keeps ncu launch lists to the training step)")
     ap.add_argument("--dropout", type=float, default=0.1, help="resid/attn/embd dropout of the training step (upstream default 0.1)")
+    ap.add_argument("--no-optimizer-extra", action="store_true", help="skip the extra timing of the step + fused clip/AdamW")
     ap.add_argument("--no-extras", action="store_true", help="skip the other-workload summaries (c1 / c3 / c4) appended to the default line")
     args = ap.parse_args()
     wl = dict(WORKLOADS[args.workload])
