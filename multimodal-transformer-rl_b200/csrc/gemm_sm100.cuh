@@ -511,14 +511,16 @@ __device__ __forceinline__ void tmem_relinquish_pair() {
 __device__ __forceinline__ void tmem_dealloc_pair(uint32_t taddr, uint32_t ncols) {
   asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
 }
-// wait with cluster-scope acquire (the barrier is arrived on by the peer CTA's threads / tensor core)
+// wait on a barrier that the peer CTA's threads / tensor core / TMA arrive on.  Default (.acquire.cta) scope on purpose: what these
+// barriers order is TMEM and async-proxy smem traffic, never generic global memory; `.acquire.cluster` compiled to a CCTL.IVALL (whole-L1
+// invalidate) after every successful wait, i.e. per k-block in the producer / MMA loops and per tile in the epilogue warps.
 __device__ __forceinline__ void mbar_wait_cluster(uint64_t* bar, uint32_t parity) {
   long long t0 = 0;
   for (;;) {
     uint32_t ok;
     asm volatile(
         "{\n\t.reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
         "selp.u32 %0, 1, 0, p;\n\t}"
         : "=r"(ok)
         : "r"(smem_u32(bar)), "r"(parity)
