@@ -384,8 +384,8 @@ def run_cpu(wl, steps, warmup, budget_s=20.0, pdrop=0.0):
 
 # DRAM bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum, mean over the captured launches) of each workload's dominant
 # kernel, from the committed `ncu --set full` captures (a profiler pass cannot run inside the timed bench)
-NCU_TRAFFIC = {"c2": (20.7e6, "profiles/r01_ncu_gemm_c2_v0.txt (6 launches of the c2 step)"),
-               "c4": (187.4e6, "profiles/r01_ncu_gemm_pair_v1.txt (qkv GEMM at M=38400: 62.6 MB read + 124.8 MB written)")}
+NCU_TRAFFIC = {"c2": (12.87e6, "profiles/r01_ncu_gemm_c2_v2.txt (all 59 single-CTA GEMM launches of one c2 step: 759.6 MB DRAM read + write)"),
+               "c4": (186.2e6, "profiles/r01_ncu_gemm_pair_v2.txt (qkv GEMM at M=38400: 62.6 MB read + 123.6 MB written; tensor pipe 64 % active)")}
 
 PROF_FAMILIES = [("gemm_tcgen05_kernel (+pair)", "tensor"), ("conv1_fwd_kernel", "hbm"), ("conv1_wgrad_kernel", "hbm"), ("attn_fwd_kernel", "tensor"),
                  ("attn_bwd_dq+dkv_kernel", "tensor"), ("ln_fwd_kernel", "hbm"), ("ln_bwd_kernel(+finalize)", "hbm"), ("embed_fwd_kernel", "hbm"),
