@@ -101,6 +101,10 @@ int im2col_nhwc(cudaStream_t stream, const bf16* x, int N, int H, int W, int C, 
 }
 
 // ---- col2im (gather) + ReLU mask: dz[n,h,w,c] = (y[n,h,w,c] > 0) * sum_{kh,kw valid} dp[(n,(h-kh)/s,(w-kw)/s), (kh,kw,c)] ---------
+// TK = ceil(k / stride) candidate taps per axis (kh = h % s + a s, kw = w % s + b s): the reference's layers are (k, s) = (4, 2) and
+// (3, 1), i.e. TK = 2 and 3.  All TK^2 loads of a thread are issued first (predicated, independent) and summed afterwards: the previous
+// data-dependent tap loops kept one 16-byte load in flight per thread and reached 18 % of the HBM roofline.  TK = 0: generic loops.
+template <int TK>
 __global__ void __launch_bounds__(256) col2im_nhwc_relu_kernel(const bf16* __restrict__ dp, const bf16* __restrict__ y, int N, int H, int W,
                                                                int C, int k, int stride, int ho, int wo, bf16* __restrict__ dz) {
   pdl_trigger();
@@ -117,15 +121,36 @@ __global__ void __launch_bounds__(256) col2im_nhwc_relu_kernel(const bf16* __res
     float acc[8];
 #pragma unroll
     for (int e = 0; e < 8; ++e) acc[e] = 0.f;
-    for (int kh = h % stride; kh < k; kh += stride) {
-      const int oh = (h - kh) / stride;
-      if (h - kh < 0 || oh >= ho) continue;
-      for (int kw = w % stride; kw < k; kw += stride) {
-        const int ow = (w - kw) / stride;
-        if (w - kw < 0 || ow >= wo) continue;
-        const uint4 u = ldg_u4(dp + (((size_t)n * ho + oh) * wo + ow) * ldp + ((size_t)kh * k + kw) * C + c8 * 8);
-        const float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y), c = unpack_bf16x2(u.z), d = unpack_bf16x2(u.w);
+    if (TK > 0) {
+      uint4 u[TK > 0 ? TK * TK : 1];
+      const int kh0 = h % stride, kw0 = w % stride;
+#pragma unroll
+      for (int a = 0; a < TK; ++a) {
+        const int kh = kh0 + a * stride, oh = (h - kh) / stride;
+        const bool okh = kh < k && h - kh >= 0 && oh < ho;
+#pragma unroll
+        for (int b = 0; b < TK; ++b) {
+          const int kw = kw0 + b * stride, ow = (w - kw) / stride;
+          const bool ok = okh && kw < k && w - kw >= 0 && ow < wo;
+          u[a * TK + b] = ok ? ldg_u4(dp + (((size_t)n * ho + oh) * wo + ow) * ldp + ((size_t)kh * k + kw) * C + c8 * 8) : make_uint4(0, 0, 0, 0);
+        }
+      }
+#pragma unroll
+      for (int q = 0; q < TK * TK; ++q) {  // same (kh-major, kw-minor) summation order as the generic loops: bit-identical
+        const float2 a = unpack_bf16x2(u[q].x), b = unpack_bf16x2(u[q].y), c = unpack_bf16x2(u[q].z), d = unpack_bf16x2(u[q].w);
         acc[0] += a.x; acc[1] += a.y; acc[2] += b.x; acc[3] += b.y; acc[4] += c.x; acc[5] += c.y; acc[6] += d.x; acc[7] += d.y;
+      }
+    } else {
+      for (int kh = h % stride; kh < k; kh += stride) {
+        const int oh = (h - kh) / stride;
+        if (h - kh < 0 || oh >= ho) continue;
+        for (int kw = w % stride; kw < k; kw += stride) {
+          const int ow = (w - kw) / stride;
+          if (w - kw < 0 || ow >= wo) continue;
+          const uint4 u = ldg_u4(dp + (((size_t)n * ho + oh) * wo + ow) * ldp + ((size_t)kh * k + kw) * C + c8 * 8);
+          const float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y), c = unpack_bf16x2(u.z), d = unpack_bf16x2(u.w);
+          acc[0] += a.x; acc[1] += a.y; acc[2] += b.x; acc[3] += b.y; acc[4] += c.x; acc[5] += c.y; acc[6] += d.x; acc[7] += d.y;
+        }
       }
     }
     const float2 ya = unpack_bf16x2(yu.x), yb = unpack_bf16x2(yu.y), yc = unpack_bf16x2(yu.z), yd = unpack_bf16x2(yu.w);
@@ -147,7 +172,10 @@ int col2im_nhwc_relu(cudaStream_t stream, const bf16* dp, const bf16* y, int N, 
   const size_t cap = (size_t)num_sms() * 8;
   if (blocks > cap) blocks = cap;
   ProfScope prof(stream, PF_COL2IM, 4.0 * N * H * W * C + 2.0 * (double)N * ho * wo * k * k * C);
-  DTB_LAUNCH(col2im_nhwc_relu_kernel, (unsigned)blocks, 256, 0, stream, dp, y, N, H, W, C, k, stride, ho, wo, dz);
+  const int tk = (k + stride - 1) / stride;
+  if (tk == 2) DTB_LAUNCH(col2im_nhwc_relu_kernel<2>, (unsigned)blocks, 256, 0, stream, dp, y, N, H, W, C, k, stride, ho, wo, dz);
+  else if (tk == 3) DTB_LAUNCH(col2im_nhwc_relu_kernel<3>, (unsigned)blocks, 256, 0, stream, dp, y, N, H, W, C, k, stride, ho, wo, dz);
+  else DTB_LAUNCH(col2im_nhwc_relu_kernel<0>, (unsigned)blocks, 256, 0, stream, dp, y, N, H, W, C, k, stride, ho, wo, dz);
   DTB_CHECK_LAUNCH();
   return DTB_OK;
 }
