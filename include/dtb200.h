@@ -182,6 +182,7 @@ typedef struct {
   double max_norm;            /* <= 0: no clipping */
   const float* lr_dev;        /* optional device scalar overriding lr */
   int write_clipped_grads;
+  int warmup_steps;           /* > 0: linear warm-up, lr * min(t / warmup_steps, 1) at the t-th step (upstream's LambdaLR), on the device */
 } dtb_adamw_hparams;
 size_t dtb_adamw_scratch_floats(void);
 int dtb_clip_adamw_step(void* stream, int nseg, const dtb_adamw_segment* segs, const dtb_adamw_hparams* hp, int* step_dev, float* scratch);

@@ -40,7 +40,7 @@ class AdamwSegment(C.Structure):
 
 class AdamwHparams(C.Structure):
     _fields_ = [("lr", C.c_double), ("beta1", C.c_double), ("beta2", C.c_double), ("eps", C.c_double), ("weight_decay", C.c_double),
-                ("max_norm", C.c_double), ("lr_dev", C.c_void_p), ("write_clipped_grads", C.c_int)]
+                ("max_norm", C.c_double), ("lr_dev", C.c_void_p), ("write_clipped_grads", C.c_int), ("warmup_steps", C.c_int)]
 
 
 class TowerConfig(C.Structure):

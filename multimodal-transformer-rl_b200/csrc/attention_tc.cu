@@ -27,6 +27,7 @@ constexpr int AT_KV_STAGES = 3;        // TMA ring depth for the streamed 64-row
 
 struct AttnTcParams {
   int T, nh, Kmask;
+  int ntile_b;          // batch size (forward: the persistent tile list spans query blocks x heads x batch)
   float scale, scale_log2;
   const float* mask;
   const float* lse_in;
@@ -78,8 +79,12 @@ __device__ __forceinline__ void at_store_row_unit(uint32_t tile_base, int r, int
 // ================================================================================================================================
 // forward
 // ================================================================================================================================
-// smem: Q [128x64] | K[2] [64x64] | V[2] [64x64] | P[2] [128x64]  (all bf16, swizzled)            = 16 + 16 + 16 + 32 KB
-// TMEM (128 columns): S fp32 [128 x 64] at column 0, O fp32 [128 x 64] at column 64
+// smem: Q [128x64] | K[3] [64x64] | V[3] [64x64] | P[2] [128x64]  (all bf16, swizzled)            = 16 + 24 + 24 + 32 KB
+// TMEM (256 columns allocated): S fp32 [128 x 64] at column 0, O fp32 [128 x 64] double-buffered at columns 64 / 128
+// Persistent over tiles: a CTA walks tiles blockIdx.x, + gridDim.x, ... (heaviest query blocks first).  All three roles keep the
+// same running block counter g, so the K/V ring, the S hand-shake and the P buffers run straight through tile boundaries: the next
+// tile's Q / K / V loads and its first S = Q K^T are in flight while the softmax threads still normalise and store the current tile's O
+// (which is why O is double-buffered in TMEM).  With gridDim.x = number of tiles it degenerates to one tile per CTA.
 template <bool DROP>  // DROP = false compiles every dropout branch away (dthr is a constant 0)
 __global__ void __launch_bounds__(AT_THREADS, 2)
 attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmKV, const AttnTcParams p) {
@@ -99,37 +104,37 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
   uint64_t* s_free = bars + 18;     // [1] softmax (128) -> MMA
   uint64_t* p_full = bars + 19;     // [2] softmax (128) -> MMA
   uint64_t* pv_done = bars + 21;    // [2] MMA -> softmax
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 23);
-  uint32_t* sBits = reinterpret_cast<uint32_t*>(bars + 24);  // [AT_MAX_CHUNKS] key-validity words, 32 keys each
+  uint64_t* q_free = bars + 23;     // [1] MMA (last S MMA of a tile retired) -> TMA
+  uint64_t* o_free = bars + 24;     // [2] softmax (128: O buffer read out) -> MMA
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 26);
+  uint32_t* sBits = reinterpret_cast<uint32_t*>(bars + 27);  // [AT_MAX_CHUNKS] key-validity words, 32 keys each
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int qb = gridDim.x - 1 - blockIdx.x;  // heaviest (last) query tiles first
-  const int h = blockIdx.y, b = blockIdx.z;
-  const int q0 = qb * 128;
   const int T = p.T;
-  int nkb = (q0 + 128) / 64;
-  const int nkb_max = (T + 63) / 64;
-  if (nkb > nkb_max) nkb = nkb_max;
+  const int nkb_max = (T + 63) / 64, ntq = (T + 127) / 128, nhb = p.nh * p.ntile_b, ntiles = ntq * nhb;
+  // tile t -> (query block, head, batch): query blocks descend with t, so every CTA's list starts with the heaviest tiles
+  auto tile_qb = [&](int t) { return ntq - 1 - t / nhb; };
+  auto tile_nkb = [&](int t) { const int n = (tile_qb(t) * 128 + 128) / 64; return n < nkb_max ? n : nkb_max; };
 
   if (threadIdx.x == 0) {
     mbar_init(q_full, 1);
     for (int s = 0; s < AT_KV_STAGES; ++s) {
       mbar_init(&k_full[s], 1); mbar_init(&k_free[s], 1); mbar_init(&v_full[s], 1); mbar_init(&v_free[s], 1);
     }
-    for (int s = 0; s < 2; ++s) { mbar_init(&p_full[s], 128); mbar_init(&pv_done[s], 1); }
+    for (int s = 0; s < 2; ++s) { mbar_init(&p_full[s], 128); mbar_init(&pv_done[s], 1); mbar_init(&o_free[s], 128); }
     mbar_init(s_full, 1);
     mbar_init(s_free, 128);
+    mbar_init(q_free, 1);
     fence_mbar_init();
   }
-  if (warp == 4) { tmem_alloc(tmem_slot, 128); tmem_relinquish(); }
+  if (warp == 4) { tmem_alloc(tmem_slot, 256); tmem_relinquish(); }
   pdl_trigger();  // prologue done: the next kernel of the stream may start its own
   pdl_wait();     // the previous kernel's results are complete and visible from here on
-  at_fill_valid_bits(p, b, 2 * nkb, sBits);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  const uint32_t tS = tmem_base, tO = tmem_base + 64;
+  const uint32_t tS = tmem_base, tO0 = tmem_base + 64;
   const int H = p.nh * AT_D;
 
   if (warp == 5) {
@@ -137,16 +142,21 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
     if (lane == 0) {
       tma_prefetch_desc(&tmQ);
       tma_prefetch_desc(&tmKV);
-      mbar_arrive_expect_tx(q_full, AT_TILE128);
-      tma_load_3d(sQ, &tmQ, q_full, h * AT_D, q0, b);
-      for (int j = 0; j < nkb; ++j) {
-        const int s = j % AT_KV_STAGES, u = j / AT_KV_STAGES;
-        if (u > 0) mbar_wait(&k_free[s], (u - 1) & 1);
-        mbar_arrive_expect_tx(&k_full[s], AT_TILE64);
-        tma_load_3d(sK + s * AT_TILE64, &tmKV, &k_full[s], H + h * AT_D, j * 64, b);
-        if (u > 0) mbar_wait(&v_free[s], (u - 1) & 1);
-        mbar_arrive_expect_tx(&v_full[s], AT_TILE64);
-        tma_load_3d(sV + s * AT_TILE64, &tmKV, &v_full[s], 2 * H + h * AT_D, j * 64, b);
+      int g = 0, tl = 0;
+      for (int t = blockIdx.x; t < ntiles; t += gridDim.x, ++tl) {
+        const int hb = t % nhb, h = hb % p.nh, b = hb / p.nh, q0 = tile_qb(t) * 128, nkb = tile_nkb(t);
+        if (tl > 0) mbar_wait(q_free, (tl - 1) & 1);  // the previous tile's last S MMA has read Q
+        mbar_arrive_expect_tx(q_full, AT_TILE128);
+        tma_load_3d(sQ, &tmQ, q_full, h * AT_D, q0, b);
+        for (int j = 0; j < nkb; ++j, ++g) {
+          const int s = g % AT_KV_STAGES, u = g / AT_KV_STAGES;
+          if (u > 0) mbar_wait(&k_free[s], (u - 1) & 1);
+          mbar_arrive_expect_tx(&k_full[s], AT_TILE64);
+          tma_load_3d(sK + s * AT_TILE64, &tmKV, &k_full[s], H + h * AT_D, j * 64, b);
+          if (u > 0) mbar_wait(&v_free[s], (u - 1) & 1);
+          mbar_arrive_expect_tx(&v_full[s], AT_TILE64);
+          tma_load_3d(sV + s * AT_TILE64, &tmKV, &v_full[s], 2 * H + h * AT_D, j * 64, b);
+        }
       }
     }
   } else if (warp == 4) {
@@ -155,10 +165,11 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
       const uint32_t idesc_qk = make_idesc_bf16(128, 64, 0, 0);
       const uint32_t idesc_pv = make_idesc_bf16(128, 64, 0, 1);
       const uint32_t q_addr = smem_u32(sQ);
-      auto issue_qk = [&](int j) {
-        const int s = j % AT_KV_STAGES;
-        mbar_wait(&k_full[s], (j / AT_KV_STAGES) & 1);
-        if (j > 0) mbar_wait(s_free, (j - 1) & 1);
+      // S(g) = Q K_g^T; `last` = last block of its tile: its retirement frees the Q buffer for the next tile's load
+      auto issue_qk = [&](int g, bool last) {
+        const int s = g % AT_KV_STAGES;
+        mbar_wait(&k_full[s], (g / AT_KV_STAGES) & 1);
+        if (g > 0) mbar_wait(s_free, (g - 1) & 1);
         tc_fence_after();
         const uint32_t k_addr = smem_u32(sK + s * AT_TILE64);
 #pragma unroll
@@ -166,40 +177,68 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
           umma_bf16(tS, make_smem_desc_sw128(q_addr + kk * 32, 16, 1024), make_smem_desc_sw128(k_addr + kk * 32, 16, 1024), idesc_qk,
                     kk > 0 ? 1u : 0u);
         umma_commit(&k_free[s]);
+        if (last) umma_commit(q_free);
         umma_commit(s_full);
       };
-      mbar_wait(q_full, 0);
-      issue_qk(0);
-      for (int j = 0; j < nkb; ++j) {
-        if (j + 1 < nkb) issue_qk(j + 1);
-        const int s = j % AT_KV_STAGES, pb = j & 1;
-        mbar_wait(&v_full[s], (j / AT_KV_STAGES) & 1);
-        mbar_wait(&p_full[pb], (j >> 1) & 1);
-        tc_fence_after();
-        const uint32_t p_addr = smem_u32(sP + pb * AT_TILE128), v_addr = smem_u32(sV + s * AT_TILE64);
+      int g = 0, tl = 0;
+      if (blockIdx.x < ntiles) {
+        mbar_wait(q_full, 0);
+        issue_qk(0, tile_nkb(blockIdx.x) == 1);
+      }
+      for (int t = blockIdx.x; t < ntiles; t += gridDim.x, ++tl) {
+        const int nkb = tile_nkb(t), tn = t + gridDim.x;
+        const uint32_t tO = tO0 + 64 * (tl & 1);
+        for (int j = 0; j < nkb; ++j, ++g) {
+          // look-ahead S: the next block of this tile, or (crossing the tile boundary) the first block of the CTA's next tile
+          if (j + 1 < nkb) {
+            issue_qk(g + 1, j + 2 == nkb);
+          } else if (tn < ntiles) {
+            mbar_wait(q_full, (tl + 1) & 1);
+            issue_qk(g + 1, tile_nkb(tn) == 1);
+          }
+          const int s = g % AT_KV_STAGES, pb = g & 1;
+          mbar_wait(&v_full[s], (g / AT_KV_STAGES) & 1);
+          mbar_wait(&p_full[pb], (g >> 1) & 1);
+          if (j == 0 && tl >= 2) mbar_wait(&o_free[tl & 1], ((tl - 2) >> 1) & 1);  // this O buffer was read out (tile tl - 2)
+          tc_fence_after();
+          const uint32_t p_addr = smem_u32(sP + pb * AT_TILE128), v_addr = smem_u32(sV + s * AT_TILE64);
 #pragma unroll
-        for (int kk = 0; kk < 4; ++kk)
-          umma_bf16(tO, make_smem_desc_sw128(p_addr + kk * 32, 16, 1024), make_smem_desc_sw128(v_addr + kk * 2048, 8192, 1024), idesc_pv,
-                    (j > 0 || kk > 0) ? 1u : 0u);
-        umma_commit(&v_free[s]);
-        umma_commit(&pv_done[pb]);
+          for (int kk = 0; kk < 4; ++kk)
+            umma_bf16(tO, make_smem_desc_sw128(p_addr + kk * 32, 16, 1024), make_smem_desc_sw128(v_addr + kk * 2048, 8192, 1024), idesc_pv,
+                      (j > 0 || kk > 0) ? 1u : 0u);
+          umma_commit(&v_free[s]);
+          umma_commit(&pv_done[pb]);
+        }
       }
     }
   } else {
     // ===================== softmax: one thread per query row =====================
     const int r = warp * 32 + lane;
-    const int qi = q0 + r;
     const uint32_t lane_addr = (uint32_t)(warp * 32) << 16;
-    float m_use = -INFINITY, l = 0.f;
     const uint32_t dthr = DROP ? p.drop.thr : 0u;
+    int g = 0, tl = 0;
+    for (int t = blockIdx.x; t < ntiles; t += gridDim.x, ++tl) {
+    const int hb = t % nhb, h = hb % p.nh, b = hb / p.nh, q0 = tile_qb(t) * 128, nkb = tile_nkb(t);
+    const int qi = q0 + r;
+    const uint32_t tO = tO0 + 64 * (tl & 1);
     const uint32_t drow = DROP ? at_drop_key(p, b, h) + (uint32_t)qi * (uint32_t)T : 0u;
-    for (int j = 0; j < nkb; ++j) {
+    // key-validity words of this tile's batch row (the four softmax warps only: named barrier 1)
+    asm volatile("bar.sync 1, 128;" ::: "memory");
+    for (int c = warp; c < 2 * nkb; c += 4) {
+      const int kj = 32 * c + lane;
+      const bool ok = kj < T && (p.mask == nullptr || __ldg(p.mask + (size_t)b * p.Kmask + kj / 3) > 0.f);
+      const uint32_t w = __ballot_sync(0xffffffffu, ok);
+      if (lane == 0) sBits[c] = w;
+    }
+    asm volatile("bar.sync 1, 128;" ::: "memory");
+    float m_use = -INFINITY, l = 0.f;
+    for (int j = 0; j < nkb; ++j, ++g) {
       const int k0 = j * 64;
       const uint32_t bits[2] = {sBits[2 * j], sBits[2 * j + 1]};
       const bool diag = k0 + 63 > q0;  // some key of the block is beyond some query of the tile
       // chunk c of this warp is entirely above the diagonal when its first key exceeds the warp's last row
       const bool act0 = !diag || (k0 <= q0 + warp * 32 + 31), act1 = !diag || (k0 + 32 <= q0 + warp * 32 + 31);
-      mbar_wait(s_full, j & 1);
+      mbar_wait(s_full, g & 1);
       tc_fence_after();
       uint32_t v0[32], v1[32];
       if (act0) tmem_ld_32x32(tS + lane_addr, v0);
@@ -250,8 +289,8 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
       }
       const float nms = m_use == -INFINITY ? 0.f : -m_use;
       // ---- P = exp2(s * scale_log2 - m), row sum, bf16 pack ----
-      const int s = j & 1;
-      if (j >= 2) mbar_wait(&pv_done[s], ((j - 2) >> 1) & 1);  // P buffer s was last read by PV(j - 2)
+      const int s = g & 1;
+      if (g >= 2) mbar_wait(&pv_done[s], ((g - 2) >> 1) & 1);  // P buffer s was last read by PV(g - 2) (possibly the previous tile's)
       const uint32_t p_tile = smem_u32(sP + s * AT_TILE128);
       float rsa = 0.f, rsb = 0.f, rsc = 0.f, rsd = 0.f;
       if (act0) {
@@ -292,7 +331,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
       l = l * alpha + rs;
       // ---- rescale O when some row of this warp moved its maximum (PV(j-1) must have retired) ----
       if (__any_sync(0xffffffffu, moved)) {
-        mbar_wait(&pv_done[(j - 1) & 1], ((j - 1) >> 1) & 1);
+        mbar_wait(&pv_done[(g - 1) & 1], ((g - 1) >> 1) & 1);  // moved implies j > 0: PV(g - 1) belongs to this tile
         tc_fence_after();
 #pragma unroll
         for (int c = 0; c < 2; ++c) {
@@ -310,7 +349,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
       mbar_arrive(&p_full[s]);
     }
     // ---- epilogue: O / l -> bf16, lse ----
-    mbar_wait(&pv_done[(nkb - 1) & 1], ((nkb - 1) >> 1) & 1);
+    mbar_wait(&pv_done[(g - 1) & 1], ((g - 1) >> 1) & 1);
     tc_fence_after();
     const float inv = l > 0.f ? (dthr ? p.drop.scale : 1.f) / l : 0.f;
     bf16* orow = p.out + ((size_t)b * T + qi) * H + h * AT_D;
@@ -330,11 +369,14 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
       }
     }
     if (qi < T) p.lse[((size_t)b * p.nh + h) * T + qi] = l > 0.f ? m_use + log2f(l) : 0.f;
+    tc_fence_before();
+    mbar_arrive(&o_free[tl & 1]);  // this thread's rows of the O buffer are in registers / stored: tile tl + 2 may overwrite them
+    }  // tile loop
   }
 
   tc_fence_before();
   __syncthreads();
-  if (warp == 4) { tc_fence_after(); tmem_dealloc(tmem_base, 128); }
+  if (warp == 4) { tc_fence_after(); tmem_dealloc(tmem_base, 256); }
 }
 
 // ================================================================================================================================
@@ -806,7 +848,17 @@ int attn_fwd_tc(cudaStream_t stream, const bf16* qkv, const float* mask, int B, 
     DTB_CUDA(cudaFuncSetAttribute(attn_fwd_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_FWD_SMEM));
     attr = true;
   }
-  dim3 grid((T + 127) / 128, nh, B);
+  p.ntile_b = B;
+  // persistent: two CTAs per SM (registers / 256 TMEM columns each) walk the tile list; DTB_ATTN_PERSIST=0 -> one tile per CTA
+  static int persist = -1;
+  if (persist < 0) {
+    const char* e = getenv("DTB_ATTN_PERSIST");
+    persist = (e && e[0] == '0') ? 0 : 1;
+  }
+  const long long ntiles = (long long)((T + 127) / 128) * nh * B;
+  DTB_REQUIRE(ntiles < (1LL << 31), DTB_ERR_UNSUPPORTED, "tcgen05 attention: too many tiles");
+  const long long cap = persist ? 2LL * num_sms() : ntiles;
+  dim3 grid((unsigned)(ntiles < cap ? ntiles : cap));
   ProfScope prof(stream, PF_ATTN_FWD, 2.0 * B * nh * (double)T * T * d);
   if (drop.state) DTB_LAUNCH(attn_fwd_tc_kernel<true>, grid, AT_THREADS, AT_FWD_SMEM, stream, tmQ, tmKV, p);
   else DTB_LAUNCH(attn_fwd_tc_kernel<false>, grid, AT_THREADS, AT_FWD_SMEM, stream, tmQ, tmKV, p);

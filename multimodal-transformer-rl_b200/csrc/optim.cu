@@ -54,7 +54,7 @@ __global__ void __launch_bounds__(256) opt_sumsq_kernel(const OptSegs s, float* 
 // one block: global norm (partials combined in index order, in double), clip coefficient, step count and the per-step scalars.
 // torch evaluates those scalars in Python doubles before they meet fp32 tensors; the same is done here (hyper-parameters are doubles).
 __global__ void opt_prepare_kernel(float* __restrict__ scratch, int nparts, double max_norm, double beta1, double beta2, double lr,
-                                   double weight_decay, const float* __restrict__ lr_dev, int* __restrict__ step_dev) {
+                                   double weight_decay, int warmup_steps, const float* __restrict__ lr_dev, int* __restrict__ step_dev) {
   pdl_trigger();
   pdl_wait();
   if (threadIdx.x != 0) return;
@@ -69,6 +69,8 @@ __global__ void opt_prepare_kernel(float* __restrict__ scratch, int nparts, doub
   const int t = *step_dev + 1;
   *step_dev = t;
   if (lr_dev) lr = (double)*lr_dev;
+  // upstream scheduler: LambdaLR(optimizer, lambda steps: min((steps + 1) / warmup_steps, 1)) -> at the t-th optimizer step lr * min(t / warmup, 1)
+  if (warmup_steps > 0 && t < warmup_steps) lr *= (double)t / (double)warmup_steps;
   scratch[0] = clip;
   scratch[1] = (float)(lr / (1.0 - pow(beta1, (double)t)));   // step_size = lr / bias_correction1
   scratch[2] = (float)sqrt(1.0 - pow(beta2, (double)t));      // bias_correction2_sqrt
@@ -154,7 +156,7 @@ int clip_adamw_step(cudaStream_t stream, int nseg, const dtb_adamw_segment* segs
   DTB_LAUNCH(opt_sumsq_kernel, dim3(OPT_BLOCKS_PER_SEG, nseg), 256, 0, stream, s, scratch);
   DTB_CHECK_LAUNCH();
   DTB_LAUNCH(opt_prepare_kernel, 1, 32, 0, stream, scratch, nseg * OPT_BLOCKS_PER_SEG, hp->max_norm, hp->beta1, hp->beta2, hp->lr,
-             hp->weight_decay, hp->lr_dev, step_dev);
+             hp->weight_decay, hp->warmup_steps, hp->lr_dev, step_dev);
   DTB_CHECK_LAUNCH();
   OptScalars c;
   c.b2 = (float)hp->beta2; c.omb1 = (float)(1.0 - hp->beta1); c.omb2 = (float)(1.0 - hp->beta2); c.eps = (float)hp->eps;

@@ -19,7 +19,7 @@ from . import _lib
 
 
 class FusedClipAdamW:
-    def __init__(self, modules, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=1e-2, max_norm=0.25, write_clipped_grads=True):
+    def __init__(self, modules, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=1e-2, max_norm=0.25, write_clipped_grads=True, warmup_steps=0):
         self.modules = list(modules) if isinstance(modules, (list, tuple)) else [modules]
         if not 1 <= len(self.modules) <= 8:
             raise ValueError("FusedClipAdamW takes 1..8 modules")
@@ -28,6 +28,7 @@ class FusedClipAdamW:
                 raise TypeError("FusedClipAdamW needs modules with flat_params / flat_grads (DecisionTransformer, MultimodalStateEncoder)")
         self.lr, self.betas, self.eps, self.weight_decay, self.max_norm = float(lr), (float(betas[0]), float(betas[1])), float(eps), float(weight_decay), max_norm
         self.write_clipped_grads = bool(write_clipped_grads)
+        self.warmup_steps = int(warmup_steps)  # > 0: upstream's LambdaLR warm-up, evaluated on the device from the step count
         self.lr_tensor = None  # optional device scalar read at kernel run time (learning-rate schedules inside a CUDA graph)
         self.param_groups = [{"lr": self.lr}]  # scheduler-style access: step() reads param_groups[0]["lr"]
         self._state = None
@@ -92,7 +93,8 @@ class FusedClipAdamW:
             segs[i].n = p.numel()
         hp = _lib.AdamwHparams(float(self.param_groups[0]["lr"]), self.betas[0], self.betas[1], self.eps, self.weight_decay,
                                float(self.max_norm) if self.max_norm else 0.0,
-                               self.lr_tensor.data_ptr() if self.lr_tensor is not None else None, int(self.write_clipped_grads))
+                               self.lr_tensor.data_ptr() if self.lr_tensor is not None else None, int(self.write_clipped_grads),
+                               self.warmup_steps)
         _lib.check(lib.dtb_clip_adamw_step(_lib.stream_ptr(), n, segs, C.byref(hp), _lib.ptr(st["step"]), _lib.ptr(st["scratch"])))
         for i, mod in enumerate(self.modules):
             # the library wrote the fp32 master behind torch's back: shadows it rewrote are current, the others must be re-staged

@@ -41,6 +41,27 @@ def test_fused_clip_adamw_matches_torch(cuda_device, max_norm):
     assert opt.step_count == 4
 
 
+def test_device_side_lr_warmup_matches_lambdalr(cuda_device):
+    """warmup_steps: lr * min(t / warmup, 1) from the device step count == upstream's LambdaLR(min((steps + 1) / warmup, 1))."""
+    from mtrl_b200.optim import FusedClipAdamW
+
+    _, model, _ = build_pair("c1", cuda_device)
+    opt = FusedClipAdamW(model, lr=1e-3, weight_decay=1e-4, max_norm=0.25, warmup_steps=3)
+    rp = torch.nn.Parameter(model.flat_params.detach().clone())
+    ref_opt = torch.optim.AdamW([rp], lr=1e-3, weight_decay=1e-4)
+    sched = torch.optim.lr_scheduler.LambdaLR(ref_opt, lambda steps: min((steps + 1) / 3, 1))
+    g = torch.Generator(device="cpu").manual_seed(5)
+    for _ in range(5):
+        grad = (torch.randn(model.flat_params.numel(), generator=g) * 1e-3).to(cuda_device)
+        model.flat_grads.copy_(grad)
+        rp.grad = grad.clone()
+        torch.nn.utils.clip_grad_norm_([rp], 0.25)
+        ref_opt.step()
+        sched.step()
+        opt.step()
+        torch.testing.assert_close(model.flat_params, rp.data, rtol=2e-6, atol=2e-9)
+
+
 def test_train_step_with_fused_optimizer_tracks_oracle_trainer(cuda_device):
     """3 train_step()s: sm_100a model + FusedClipAdamW vs the fp32 oracle + clip_grad_norm_ + torch.optim.AdamW on the same batches."""
     from mtrl_b200.optim import FusedClipAdamW
