@@ -187,6 +187,33 @@ typedef struct {
 size_t dtb_adamw_scratch_floats(void);
 int dtb_clip_adamw_step(void* stream, int nseg, const dtb_adamw_segment* segs, const dtb_adamw_hparams* hp, int* step_dev, float* scratch);
 
+/* ---- GPU-side get_batch ------------------------------------------------------------------------------
+ * Replaces upstream experiment.py get_batch() after the (trajectory, start) pairs are sampled on the host: window slice of at most K
+ * steps, LEFT padding to K (states 0 — then normalised like every other row —, actions -10, rewards 0, dones 2, timesteps 0, mask 0),
+ * `(s - mean) / std` and `rtg / scale` evaluated in double and rounded to fp32 exactly as numpy's promotions do, timesteps clamped to
+ * max_ep_len - 1, returns-to-go with K + 1 entries (0 past the end of the trajectory).  The store is flat per-timestep rows in device
+ * memory; `rtg_suffix` holds upstream's discount_cumsum(rewards, gamma = 1) per trajectory (computed once by the host loader).
+ * Raw fields (frames, spectrograms: any 16-byte-multiple row) are copied with zero padding. */
+typedef struct {
+  const float* obs; int state_dim; const double* state_mean; const double* state_std; /* obs may be NULL when only raw fields are used */
+  const float* act; int act_dim;
+  const float* rew; const float* done; const double* rtg_suffix;                    /* [N_total] each; suffix sums in double (exact for fp32 data) */
+  const long long* traj_offset;                                                      /* [n_traj + 1] first timestep of each trajectory */
+  int n_raw; const void* raw_src[4]; int raw_row_bytes[4];
+} dtb_traj_store;
+typedef struct {
+  float* states;         /* [B, K, state_dim] or NULL */
+  float* actions;        /* [B, K, act_dim] or NULL */
+  float* rewards;        /* [B, K] or NULL */
+  long long* dones;      /* [B, K] or NULL */
+  float* rtg;            /* [B, K + 1] or NULL */
+  long long* timesteps;  /* [B, K] or NULL */
+  float* mask;           /* [B, K] or NULL */
+  void* raw_dst[4];      /* [B, K, row_bytes] per raw field */
+} dtb_batch_out;
+int dtb_get_batch(void* stream, const dtb_traj_store* store, const long long* traj_idx, const long long* start, int B, int K,
+                  int max_ep_len, double scale, const dtb_batch_out* out);
+
 /* Dropout (nn.Dropout at the three GPT-2 sites of the reference's trunk; HF modeling_gpt2 GPT2Model.drop (embd_pdrop),
  * GPT2Attention.attn_dropout (attn_pdrop, :60-62 of modeling_decision_transformer eager attention) and resid_dropout / GPT2MLP.dropout
  * (resid_pdrop, :217-218, :236-237); kzl-style DecisionTransformer passes resid_pdrop = attn_pdrop = dropout, default 0.1).

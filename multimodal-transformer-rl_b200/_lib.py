@@ -43,6 +43,17 @@ class AdamwHparams(C.Structure):
                 ("max_norm", C.c_double), ("lr_dev", C.c_void_p), ("write_clipped_grads", C.c_int), ("warmup_steps", C.c_int)]
 
 
+class TrajStore(C.Structure):
+    _fields_ = [("obs", C.c_void_p), ("state_dim", C.c_int), ("state_mean", C.c_void_p), ("state_std", C.c_void_p), ("act", C.c_void_p),
+                ("act_dim", C.c_int), ("rew", C.c_void_p), ("done", C.c_void_p), ("rtg_suffix", C.c_void_p), ("traj_offset", C.c_void_p),
+                ("n_raw", C.c_int), ("raw_src", C.c_void_p * 4), ("raw_row_bytes", C.c_int * 4)]
+
+
+class BatchOut(C.Structure):
+    _fields_ = [("states", C.c_void_p), ("actions", C.c_void_p), ("rewards", C.c_void_p), ("dones", C.c_void_p), ("rtg", C.c_void_p),
+                ("timesteps", C.c_void_p), ("mask", C.c_void_p), ("raw_dst", C.c_void_p * 4)]
+
+
 class TowerConfig(C.Structure):
     _fields_ = [("in_channels", C.c_int), ("in_h", C.c_int), ("in_w", C.c_int), ("big", C.c_int)]
 
@@ -90,6 +101,7 @@ def _declare(lib):
     lib.dtb_encoder_backward_u8.argtypes = lib.dtb_encoder_backward.argtypes
     lib.dtb_pad_left.argtypes = [vp, i, C.POINTER(vp), C.POINTER(vp), C.POINTER(i), i, i, vp]
     lib.dtb_dt_set_dropout.argtypes = [vp, f, f, f, vp]
+    lib.dtb_get_batch.argtypes = [vp, C.POINTER(TrajStore), vp, vp, i, i, i, C.c_double, C.POINTER(BatchOut)]
     lib.dtb_adamw_scratch_floats.restype = sz
     lib.dtb_clip_adamw_step.argtypes = [vp, i, C.POINTER(AdamwSegment), C.POINTER(AdamwHparams), vp, vp]
     lib.dtb_attention_fwd_dropout.argtypes = [vp, vp, vp, i, i, i, i, vp, vp, vp, C.c_uint, f]

@@ -95,6 +95,11 @@ int dtb_attention_bwd_dropout(void* stream, const void* qkv, const float* mask, 
   return attn_bwd((cudaStream_t)stream, (const bf16*)qkv, mask, (const bf16*)out, (const bf16*)dout, lse, B, T, n_head, head_dim,
                   (bf16*)dqkv, delta, drop_make(drop_state, site, p));
 }
+int dtb_get_batch(void* stream, const dtb_traj_store* store, const long long* traj_idx, const long long* start, int B, int K, int max_ep_len,
+                  double scale, const dtb_batch_out* out) {
+  DTB_TRY(require_sm100());
+  return get_batch((cudaStream_t)stream, store, traj_idx, start, B, K, max_ep_len, scale, out);
+}
 size_t dtb_adamw_scratch_floats(void) { return adamw_scratch_floats(); }
 int dtb_clip_adamw_step(void* stream, int nseg, const dtb_adamw_segment* segs, const dtb_adamw_hparams* hp, int* step_dev, float* scratch) {
   DTB_TRY(require_sm100());

@@ -64,6 +64,10 @@ int dropout_mask(cudaStream_t stream, const DropSite& d, int groups, long long n
 
 int pad_left(cudaStream_t stream, int nseg, const void* const* srcs, void* const* dsts, const int* row_bytes, int t, int K, float* mask);
 
+// ---- get_batch.cu --------------------------------------------------------------------------------
+int get_batch(cudaStream_t stream, const dtb_traj_store* st, const long long* traj_idx, const long long* start, int B, int K, int max_ep_len,
+              double scale, const dtb_batch_out* out);
+
 // ---- optim.cu ------------------------------------------------------------------------------------
 size_t adamw_scratch_floats();
 int clip_adamw_step(cudaStream_t stream, int nseg, const dtb_adamw_segment* segs, const dtb_adamw_hparams* hp, int* step_dev, float* scratch);
