@@ -112,8 +112,10 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int T = p.T;
   const int nkb_max = (T + 63) / 64, ntq = (T + 127) / 128, nhb = p.nh * p.ntile_b, ntiles = ntq * nhb;
-  // tile t -> (query block, head, batch): query blocks descend with t, so every CTA's list starts with the heaviest tiles
-  auto tile_qb = [&](int t) { return ntq - 1 - t / nhb; };
+  // tile t -> (head-batch pair t / ntq, query block descending within it): the tiles of one (b, h) — which share K / V — are adjacent
+  // in the list, i.e. run at the same time on neighbouring CTAs (L2 reuse: DRAM reads 349 -> 177 MB vs a block-major order), while each
+  // CTA's own list (stride gridDim.x) still cycles through light and heavy query blocks
+  auto tile_qb = [&](int t) { return ntq - 1 - t % ntq; };
   auto tile_nkb = [&](int t) { const int n = (tile_qb(t) * 128 + 128) / 64; return n < nkb_max ? n : nkb_max; };
 
   if (threadIdx.x == 0) {
@@ -144,7 +146,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
       tma_prefetch_desc(&tmKV);
       int g = 0, tl = 0;
       for (int t = blockIdx.x; t < ntiles; t += gridDim.x, ++tl) {
-        const int hb = t % nhb, h = hb % p.nh, b = hb / p.nh, q0 = tile_qb(t) * 128, nkb = tile_nkb(t);
+        const int hb = t / ntq, h = hb % p.nh, b = hb / p.nh, q0 = tile_qb(t) * 128, nkb = tile_nkb(t);
         if (tl > 0) mbar_wait(q_free, (tl - 1) & 1);  // the previous tile's last S MMA has read Q
         mbar_arrive_expect_tx(q_full, AT_TILE128);
         tma_load_3d(sQ, &tmQ, q_full, h * AT_D, q0, b);
@@ -218,7 +220,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
     const uint32_t dthr = DROP ? p.drop.thr : 0u;
     int g = 0, tl = 0;
     for (int t = blockIdx.x; t < ntiles; t += gridDim.x, ++tl) {
-    const int hb = t % nhb, h = hb % p.nh, b = hb / p.nh, q0 = tile_qb(t) * 128, nkb = tile_nkb(t);
+    const int hb = t / ntq, h = hb % p.nh, b = hb / p.nh, q0 = tile_qb(t) * 128, nkb = tile_nkb(t);
     const int qi = q0 + r;
     const uint32_t tO = tO0 + 64 * (tl & 1);
     const uint32_t drow = DROP ? at_drop_key(p, b, h) + (uint32_t)qi * (uint32_t)T : 0u;
