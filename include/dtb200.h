@@ -301,6 +301,36 @@ int dtb_encoder_backward_u8(const dtb_encoder* e, void* stream, const float* par
                             const unsigned char* frames_u8, const float* audio, const void* states_bf16, const void* d_states_bf16,
                             int d_states_masked, void* workspace, size_t workspace_bytes, float* grads);
 
+/* ---- modality attention over the two tower features (REF src/agents.py:58-75 CaslAttention, :78-90 NewAttention; the call site
+ * is agents.py:135-136 between the towers and the fusion) ---------------------------------------------------------------------
+ *   type 0 'casl': z = tanh(video_fc(v) + audio_fc(a) + state_fc(h)) [32];   type 1 'new': z = tanh(fc([v | a | h])) [128]
+ *   w = softmax(attention(z)) [2];  v' = w[0] v, a' = w[1] a;  states = [v' | a'] (fusion 0) or v' + a' (fusion 1, agents.py:137-143)
+ * feat_bf16 [N, 2*feat] = [relu(video_fc) | relu(audio_fc)] as dtb_encoder_forward (fusion 0) writes it; hidden fp32 [N, 128] = the
+ * recurrent state the reference's LSTM agent feeds in (lstm_state[0]); NULL = zeros (the Decision Transformer has no such state).
+ * Stateless: the config is passed to every call; the workspace of the forward must be handed unchanged to the backward.
+ * Flat fp32 parameter order (PyTorch layouts, module order of the reference classes):
+ *   casl: audio_fc.{weight [32,feat], bias}, video_fc.{weight [32,feat], bias}, state_fc.{weight [32,128], bias}, attention.{weight [2,32], bias}
+ *   new : fc.{weight [128, 2*feat+128], bias}, attention.{weight [2,128], bias} */
+typedef struct {
+  int type;   /* 0 casl, 1 new */
+  int feat;   /* per-tower feature size: 512 ('big') or 256 ('small') */
+  int fusion; /* 0 concat, 1 sum */
+} dtb_modal_attn_config;
+int dtb_modal_attn_param_entries(const dtb_modal_attn_config* cfg);
+long long dtb_modal_attn_param_layout(const dtb_modal_attn_config* cfg, long long* offsets, long long* numels);
+int dtb_modal_attn_state_dim(const dtb_modal_attn_config* cfg);
+size_t dtb_modal_attn_workspace_bytes(const dtb_modal_attn_config* cfg, int N);
+/* states_bf16 [N, state_dim]; attn_weights fp32 [N, 2] (nullable). */
+int dtb_modal_attn_forward(const dtb_modal_attn_config* cfg, void* stream, const float* params, int N, const void* feat_bf16,
+                           const float* hidden, void* workspace, size_t workspace_bytes, void* states_bf16, float* attn_weights);
+/* d_states_bf16 [N, state_dim] -> d_feat_bf16 [N, 2*feat], already multiplied by the towers' ReLU mask (feat > 0): hand it to
+ * dtb_encoder_backward with d_states_masked = 1.  Overwrites grads (flat, same layout as params); has_hidden = whether the forward
+ * was given a hidden state (its weight columns get a zero gradient otherwise).  No gradient flows into hidden (the reference detaches
+ * the LSTM state between steps). */
+int dtb_modal_attn_backward(const dtb_modal_attn_config* cfg, void* stream, const float* params, int N, const void* feat_bf16,
+                            int has_hidden, const void* d_states_bf16, void* workspace, size_t workspace_bytes, void* d_feat_bf16,
+                            float* grads);
+
 #ifdef __cplusplus
 }
 #endif

@@ -62,6 +62,10 @@ class EncoderConfig(C.Structure):
     _fields_ = [("video", TowerConfig), ("audio", TowerConfig), ("fusion", C.c_int), ("input_scale", C.c_float)]
 
 
+class ModalAttnConfig(C.Structure):
+    _fields_ = [("type", C.c_int), ("feat", C.c_int), ("fusion", C.c_int)]
+
+
 def _declare(lib):
     """restype / argtypes for the entry points whose defaults (int) would truncate pointers or sizes."""
     vp, i, f, sz, ll = C.c_void_p, C.c_int, C.c_float, C.c_size_t, C.c_longlong
@@ -99,6 +103,15 @@ def _declare(lib):
     lib.dtb_encoder_backward.argtypes = [vp, vp, vp, vp, i, vp, vp, vp, vp, i, vp, sz, vp]
     lib.dtb_encoder_forward_u8.argtypes = lib.dtb_encoder_forward.argtypes
     lib.dtb_encoder_backward_u8.argtypes = lib.dtb_encoder_backward.argtypes
+    macp = C.POINTER(ModalAttnConfig)
+    lib.dtb_modal_attn_param_entries.argtypes = [macp]
+    lib.dtb_modal_attn_param_layout.argtypes = [macp, C.POINTER(ll), C.POINTER(ll)]
+    lib.dtb_modal_attn_param_layout.restype = ll
+    lib.dtb_modal_attn_state_dim.argtypes = [macp]
+    lib.dtb_modal_attn_workspace_bytes.argtypes = [macp, i]
+    lib.dtb_modal_attn_workspace_bytes.restype = sz
+    lib.dtb_modal_attn_forward.argtypes = [macp, vp, vp, i, vp, vp, vp, sz, vp, vp]
+    lib.dtb_modal_attn_backward.argtypes = [macp, vp, vp, i, vp, i, vp, vp, sz, vp, vp]
     lib.dtb_pad_left.argtypes = [vp, i, C.POINTER(vp), C.POINTER(vp), C.POINTER(i), i, i, vp]
     lib.dtb_dt_set_dropout.argtypes = [vp, f, f, f, vp]
     lib.dtb_get_batch.argtypes = [vp, C.POINTER(TrajStore), vp, vp, i, i, i, C.c_double, C.POINTER(BatchOut)]

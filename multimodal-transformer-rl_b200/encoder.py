@@ -40,16 +40,20 @@ def _tower_entries(prefix, conv_type, cin, h, w):
 
 class MultimodalStateEncoder(nn.Module):
     def __init__(self, frame_shape=(1, 84, 84), audio_shape=(1, 84, 84), conv_type="big", fusion_type="concat", input_scale=1.0 / 255.0,
-                 device=None):
+                 device=None, attn_type=None):
         super().__init__()
         self.frame_shape, self.audio_shape = tuple(int(x) for x in frame_shape), tuple(int(x) for x in audio_shape)
         self.conv_type, self.fusion_type, self.input_scale = conv_type, fusion_type, float(input_scale)
         if fusion_type not in ("concat", "sum"):
             raise NotImplementedError(fusion_type)
+        if attn_type not in (None, "", "casl", "new"):
+            raise NotImplementedError(attn_type)  # as MinecraftAgent.__init__ (agents.py:108-114)
+        self.attn_type = attn_type or None
         lib = _lib.load()
         big = 1 if conv_type == "big" else 0
+        # with modality attention the towers always write [video | audio] side by side; the attention op does the fusion
         cfg = _lib.EncoderConfig(_lib.TowerConfig(*self.frame_shape, big), _lib.TowerConfig(*self.audio_shape, big),
-                                 0 if fusion_type == "concat" else 1, self.input_scale)
+                                 0 if (fusion_type == "concat" or self.attn_type) else 1, self.input_scale)
         h = C.c_void_p()
         _lib.check(lib.dtb_encoder_create(C.byref(cfg), C.byref(h)))
         self._h = h
@@ -64,6 +68,26 @@ class MultimodalStateEncoder(nn.Module):
         self._offsets = [int(o) for o in offs]
         for shp, num in zip(self._shapes, nums):
             assert int(torch.Size(shp).numel()) == int(num), (shp, num)
+        self._tower_total, self._acfg, self._attn_ws, self.attn_weights = self._total, None, {}, None
+        if self.attn_type:  # attn.* parameters (reference names, agents.py:58-90) appended to the same flat buffer
+            F = self.feature_size
+            self._acfg = _lib.ModalAttnConfig(0 if self.attn_type == "casl" else 1, F, 0 if fusion_type == "concat" else 1)
+            na = _lib.check(lib.dtb_modal_attn_param_entries(C.byref(self._acfg)))
+            aoffs, anums = (C.c_longlong * na)(), (C.c_longlong * na)()
+            atotal = int(lib.dtb_modal_attn_param_layout(C.byref(self._acfg), aoffs, anums))
+            if self.attn_type == "casl":
+                anames = ["attn.audio_fc", "attn.video_fc", "attn.state_fc", "attn.attention"]
+                ashapes = [(32, F), (32,), (32, F), (32,), (32, 128), (32,), (2, 32), (2,)]
+            else:
+                anames = ["attn.fc", "attn.attention"]
+                ashapes = [(128, 2 * F + 128), (128,), (2, 128), (2,)]
+            self._names = self._names + [f"{m}.{k}" for m in anames for k in ("weight", "bias")]
+            self._shapes = self._shapes + ashapes
+            self._offsets = self._offsets + [self._tower_total + int(o) for o in aoffs]
+            for shp, num in zip(ashapes, anums):
+                assert int(torch.Size(shp).numel()) == int(num), (shp, num)
+            self._total = self._tower_total + atotal
+            self.state_dim = int(lib.dtb_modal_attn_state_dim(C.byref(self._acfg)))
         if device is None:
             device = "cuda" if torch.cuda.is_available() else "cpu"
         self._flat = torch.zeros(self._total, dtype=torch.float32, device=device)
@@ -81,6 +105,7 @@ class MultimodalStateEncoder(nn.Module):
             flat[off:off + torch.Size(shp).numel()].view(shp).copy_(self.get_parameter(name).data.float())
         self._flat = flat
         self._flat_grad, self._staged, self._staged_version, self._ws = None, None, -1, {}
+        self._attn_ws = {}
         for name, shp, off in zip(self._names, self._shapes, self._offsets):
             self.get_parameter(name).data = self._flat[off:off + torch.Size(shp).numel()].view(shp)
         return self
@@ -89,7 +114,15 @@ class MultimodalStateEncoder(nn.Module):
     def reset_parameters(self):
         """layer_init of the reference (src/utils.py:146-149): orthogonal(gain sqrt 2) weights, zero biases."""
         for name, p in self.named_parameters():
-            if name.endswith(".bias"):
+            if name.startswith("attn."):  # plain nn.Linear default init in the reference (agents.py:61-64, 81-82)
+                if name.endswith(".weight"):
+                    w = torch.empty(p.shape, dtype=torch.float32)
+                    torch.nn.init.kaiming_uniform_(w, a=5 ** 0.5)
+                    p.copy_(w)
+                else:
+                    fan_in = self.get_parameter(name[:-4] + "weight").shape[1]
+                    p.copy_(torch.empty(p.shape).uniform_(-1.0 / fan_in ** 0.5, 1.0 / fan_in ** 0.5))
+            elif name.endswith(".bias"):
                 p.zero_()
             else:
                 w = torch.empty(p.shape, dtype=torch.float32)
@@ -148,9 +181,34 @@ class MultimodalStateEncoder(nn.Module):
         f = frames.detach().contiguous() if frames.dtype == torch.uint8 else frames.detach().to(torch.float32).contiguous()
         return B, K, f, audio.detach().to(torch.float32).contiguous()
 
-    def forward_raw(self, frames, audio):
+    def _attn_workspace(self, N):
+        ws = self._attn_ws.get(N)
+        if ws is None:
+            if len(self._attn_ws) > 4:
+                self._attn_ws.clear()
+            nbytes = int(_lib.load().dtb_modal_attn_workspace_bytes(C.byref(self._acfg), N))
+            ws = (torch.empty(nbytes, dtype=torch.uint8, device=self._flat.device),
+                  torch.empty((N, 2 * self.feature_size), dtype=torch.bfloat16, device=self._flat.device),   # tower features
+                  torch.empty((N, 2 * self.feature_size), dtype=torch.bfloat16, device=self._flat.device),   # their gradient
+                  torch.empty((N, 2), dtype=torch.float32, device=self._flat.device))                        # attention weights
+            self._attn_ws[N] = ws
+        return ws
+
+    def _hidden(self, hidden, N):
+        """hidden: None (the Decision Transformer has no recurrent state: zeros), [N,128], [1,N,128] (casl's lstm_state[0]) or one
+        row [1,128] / [1,1,128] repeated over the samples (NewAttention, agents.py:85)."""
+        if hidden is None:
+            return None
+        h = hidden.detach().to(device=self._flat.device, dtype=torch.float32).reshape(-1, 128)
+        if h.shape[0] == 1 and N > 1:
+            h = h.expand(N, 128)
+        if h.shape[0] != N:
+            raise ValueError(f"hidden must have 1 or {N} rows of 128, got {tuple(hidden.shape)}")
+        return h.contiguous()
+
+    def forward_raw(self, frames, audio, hidden=None):
         """frames [B,K,Cv,H,W] (fp32 in the reference's decoded range, or uint8 pixels), audio [B,K,Ca,H,W] (fp32) -> states bf16
-        [B,K,state_dim]; keeps what backward_raw needs."""
+        [B,K,state_dim]; keeps what backward_raw needs.  hidden: recurrent state for the modality attention (attn_type only)."""
         B, K, f, a = self._prep(frames, audio)
         N = B * K
         self._stage()
@@ -158,23 +216,43 @@ class MultimodalStateEncoder(nn.Module):
         states = torch.empty((B, K, self.state_dim), dtype=torch.bfloat16, device=self._flat.device)
         lib = _lib.load()
         fwd = lib.dtb_encoder_forward_u8 if f.dtype == torch.uint8 else lib.dtb_encoder_forward
+        if not self.attn_type:
+            if hidden is not None:
+                raise ValueError("hidden is only used by the modality attention (attn_type='casl' | 'new')")
+            _lib.check(fwd(self._h, _lib.stream_ptr(), _lib.ptr(self._flat), _lib.ptr(self._staged), N, _lib.ptr(f),
+                           _lib.ptr(a), _lib.ptr(ws), ws.numel(), _lib.ptr(states)))
+            self._last = (N, f, a, ws, states)
+            return states
+        aws, feat, _, weights = self._attn_workspace(N)
+        h = self._hidden(hidden, N)
         _lib.check(fwd(self._h, _lib.stream_ptr(), _lib.ptr(self._flat), _lib.ptr(self._staged), N, _lib.ptr(f),
-                                                   _lib.ptr(a), _lib.ptr(ws), ws.numel(), _lib.ptr(states)))
-        self._last = (N, f, a, ws, states)
+                       _lib.ptr(a), _lib.ptr(ws), ws.numel(), _lib.ptr(feat)))
+        _lib.check(lib.dtb_modal_attn_forward(C.byref(self._acfg), _lib.stream_ptr(), _lib.ptr(self._flat[self._tower_total:]), N,
+                                              _lib.ptr(feat), _lib.ptr(h), _lib.ptr(aws), aws.numel(), _lib.ptr(states), _lib.ptr(weights)))
+        self.attn_weights = weights.view(B, K, 2)
+        self._last = (N, f, a, ws, states, h is not None)
         return states
 
     def backward_raw(self, d_states, masked: bool, grads=None):
-        N, f, a, ws, states = self._last
+        N, f, a, ws, states = self._last[:5]
         grads = self.attach_grads() if grads is None else grads
         lib = _lib.load()
         bwd = lib.dtb_encoder_backward_u8 if f.dtype == torch.uint8 else lib.dtb_encoder_backward
+        if self.attn_type:
+            # attention backward -> gradient of the tower features, already ReLU-masked; a d_states masked by (states > 0) is fine
+            # too: states > 0 exactly where the features are (the weights are positive), and masked entries only meet zero features
+            aws, feat, dfeat, _ = self._attn_workspace(N)
+            _lib.check(lib.dtb_modal_attn_backward(C.byref(self._acfg), _lib.stream_ptr(), _lib.ptr(self._flat[self._tower_total:]), N,
+                                                   _lib.ptr(feat), int(self._last[5]), _lib.ptr(d_states), _lib.ptr(aws), aws.numel(),
+                                                   _lib.ptr(dfeat), _lib.ptr(grads[self._tower_total:])))
+            states, d_states, masked = feat, dfeat, True
         _lib.check(bwd(self._h, _lib.stream_ptr(), _lib.ptr(self._flat), _lib.ptr(self._staged), N, _lib.ptr(f), _lib.ptr(a), _lib.ptr(states),
                        _lib.ptr(d_states), int(masked), _lib.ptr(ws), ws.numel(), _lib.ptr(grads)))
         return grads
 
-    def forward(self, frames, audio):
+    def forward(self, frames, audio, hidden=None):
         params = [self.get_parameter(n) for n in self._names]
-        return _EncoderFunction.apply(self, frames, audio, *params)
+        return _EncoderFunction.apply(self, frames, audio, hidden, *params)
 
     def __del__(self):
         try:
@@ -187,8 +265,8 @@ class MultimodalStateEncoder(nn.Module):
 
 class _EncoderFunction(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, enc, frames, audio, *params):
-        states = enc.forward_raw(frames, audio)
+    def forward(ctx, enc, frames, audio, hidden, *params):
+        states = enc.forward_raw(frames, audio, hidden)
         ctx.enc, ctx.saved = enc, enc._last
         return states
 
@@ -201,7 +279,7 @@ class _EncoderFunction(torch.autograd.Function):
         d = d_states.detach().to(torch.bfloat16).contiguous().clone()  # masked in place by the library
         enc.backward_raw(d, masked=False, grads=grads)
         out = [grads[off:off + torch.Size(shp).numel()].view(shp) for shp, off in zip(enc._shapes, enc._offsets)]
-        return (None, None, None, *out)
+        return (None, None, None, None, *out)
 
 
 class MultimodalDecisionTransformer(nn.Module):
@@ -241,7 +319,8 @@ class MultimodalDecisionTransformer(nn.Module):
         """Fused end-to-end training step body: towers -> DT forward -> masked action MSE -> DT backward -> towers backward."""
         states = self.encoder.forward_raw(frames, audio)
         d_states = torch.empty_like(states)
-        relu_out = self.encoder.fusion_type == "concat"  # the concatenated state is itself relu(features); a sum is not
+        # the concatenated state is itself relu(features) (scaled by positive attention weights, if any); a sum is not
+        relu_out = self.encoder.fusion_type == "concat"
         loss = self.dt.loss_and_backward(None, actions, returns_to_go, timesteps, attention_mask, action_target=action_target,
                                          grad_scale=grad_scale, states_bf16=states, d_states_bf16=d_states, states_relu=relu_out,
                                          on_stage_done=on_stage_done)

@@ -2,6 +2,7 @@
 
   encoder_ref_{big,small}.pt : the REFERENCE's own conv_factory / two towers / fusion (imported from /root/reference/src/agents.py
                                with stub modules for its absent deps) on seeded inputs -> pins oracle/encoders.py
+  modal_attn_ref.pt          : the REFERENCE's CaslAttention / NewAttention on seeded features -> pins the oracle's restatement
   dt_hf_c1.pt                : HuggingFace DecisionTransformerModel (wpe zeroed = upstream semantics) on seeded inputs -> pins
                                oracle/decision_transformer.py
   dt_oracle_small.pt         : oracle forward / loss / gradient norms on a tiny config -> fixture the GPU path is compared with
@@ -61,6 +62,23 @@ def fusion_b1_fixture(agents):
     return {"seed": 3, "x": x, "video_sums": checksums(ag.video_net), "audio_sums": checksums(ag.audio_net), "fused": fused}
 
 
+def modal_attn_fixture(agents):
+    """The REFERENCE's CaslAttention / NewAttention (agents.py:58-90) on seeded features -> pins oracle/encoders.py's restatement.
+    casl takes lstm_state[0] of shape [1, N, 128] (per-sample rows); new repeats ONE row [1, 1, 128] over the samples."""
+    out = {}
+    g = torch.Generator().manual_seed(21)
+    for name, cls, F in [("casl", agents.CaslAttention, 512), ("new", agents.NewAttention, 256)]:
+        torch.manual_seed(13)
+        m = cls(F, torch.device("cpu"))
+        n = 6
+        v, a = torch.relu(torch.randn(n, F, generator=g)), torch.relu(torch.randn(n, F, generator=g))
+        h = torch.randn(1, n if name == "casl" else 1, 128, generator=g)
+        with torch.no_grad():
+            v2, a2, w = m(v, a, (h, torch.zeros_like(h)))
+        out[name] = {"state": m.state_dict(), "v": v, "a": a, "h": h, "v_out": v2, "a_out": a2, "w": w}
+    return out
+
+
 def hf_fixture():
     from transformers import DecisionTransformerConfig, DecisionTransformerModel
     from util import make_inputs
@@ -98,6 +116,7 @@ if __name__ == "__main__":
     torch.save(encoder_fixture(agents, "big"), os.path.join(HERE, "encoder_ref_big.pt"))
     torch.save(encoder_fixture(agents, "small"), os.path.join(HERE, "encoder_ref_small.pt"))
     torch.save(fusion_b1_fixture(agents), os.path.join(HERE, "encoder_ref_fusion_b1.pt"))
+    torch.save(modal_attn_fixture(agents), os.path.join(HERE, "modal_attn_ref.pt"))
     torch.save(hf_fixture(), os.path.join(HERE, "dt_hf_c1.pt"))
     torch.save(oracle_small_fixture(), os.path.join(HERE, "dt_oracle_small.pt"))
     for f in sorted(os.listdir(HERE)):

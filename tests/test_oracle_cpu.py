@@ -155,3 +155,34 @@ def test_train_step_loss_rule():
     l0 = tr.train_step()
     assert abs(l0 - manual.item()) < 1e-6
     assert tr.train_step() < l0
+
+
+@pytest.mark.parametrize("kind,F", [("casl", 512), ("new", 256)])
+def test_oracle_modal_attention_equals_reference_classes(kind, F):
+    """oracle CaslAttention / NewAttention == the REFERENCE's classes (agents.py:58-90) on the committed fixture: bit-exact."""
+    from oracle.encoders import CaslAttention, NewAttention
+
+    d = torch.load(os.path.join(GOLD, "modal_attn_ref.pt"))[kind]
+    m = (CaslAttention if kind == "casl" else NewAttention)(F)
+    assert list(m.state_dict().keys()) == list(d["state"].keys())  # same module names and order as the reference
+    m.load_state_dict(d["state"])
+    with torch.no_grad():
+        v2, a2, w = m(d["v"], d["a"], d["h"][0])
+    assert torch.equal(v2, d["v_out"]) and torch.equal(a2, d["a_out"]) and torch.equal(w, d["w"])
+    # no hidden state (the Decision Transformer case) == an all-zero hidden state
+    with torch.no_grad():
+        w0 = m(d["v"], d["a"], None)[2]
+        wz = m(d["v"], d["a"], torch.zeros(d["v"].shape[0], 128))[2]
+    assert torch.equal(w0, wz)
+
+
+def test_oracle_encoder_with_attention_param_names():
+    """attn.* parameter names follow MinecraftAgent (self.attn = CaslAttention / NewAttention, agents.py:110-113)."""
+    from oracle.encoders import MultimodalStateEncoder
+
+    e = MultimodalStateEncoder((1, 84, 84), (1, 84, 84), "small", "sum", attn_type="casl")
+    names = [n for n, _ in e.named_parameters() if n.startswith("attn.")]
+    assert names == [f"attn.{m}.{k}" for m in ("audio_fc", "video_fc", "state_fc", "attention") for k in ("weight", "bias")]
+    x = torch.rand(2, 3, 1, 84, 84)
+    s = e(x, x)
+    assert s.shape == (2, 3, 256) and e.attn_weights.shape == (6, 2)
