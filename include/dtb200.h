@@ -331,6 +331,29 @@ int dtb_modal_attn_backward(const dtb_modal_attn_config* cfg, void* stream, cons
                             int has_hidden, const void* d_states_bf16, void* workspace, size_t workspace_bytes, void* d_feat_bf16,
                             float* grads);
 
+/* ---- audio front-end: wav -> MFCC image (REF environments/Minecraft/Minecraft.py:226-245 `_get_mfcc` / `_wav_to_mfcc`; the same code in
+ * environments/Doorpuzzle/Doorpuzzle.py:264-282) -------------------------------------------------------------------------------------
+ * cepstra = python_speech_features.mfcc(signal, samplerate) with its release-0.6 defaults (25 ms frames every 10 ms, rectangular
+ * window, pre-emphasis 0.97, FFT = next power of two, 26 mel filters, log, DCT-II ortho -> 13, lifter 22, c0 = log frame energy),
+ * computed in double like the reference; image = Pillow `Image.fromarray(cepstra.T).resize((out_w, out_h), BICUBIC)` (float32, bit-exact)
+ * followed by the reference's float32 min-max normalisation to [-1, 1].
+ * signal: int16 PCM (is_i16 = 1, as scipy.io.wavfile returns it) or float32, n_clips rows of n_samples (row stride clip_stride).  The
+ * reference hands scipy's [n, channels] array of a stereo file straight to python_speech_features, whose pre-emphasis then acts per
+ * channel and whose numpy.append flattens the result: pass the interleaved samples (n_samples = n * channels) and `channels` (the
+ * pre-emphasis lag); framing then runs over the interleaved stream exactly as in the reference. */
+long long dtb_mfcc_num_frames(long long n_samples, int samplerate);
+/* nfft and the 28 filter-bank edge bins the kernel uses for this sample rate (test hook). */
+int dtb_mfcc_filterbank_bins(int samplerate, int* nfft, int* bins);
+size_t dtb_mfcc_workspace_bytes(int n_clips, long long n_samples, int samplerate, int out_w);
+/* cepstra: double [n_clips, num_frames, 13] */
+int dtb_mfcc_cepstra(void* stream, const void* signal, int is_i16, int channels, int n_clips, long long n_samples, long long clip_stride, int samplerate,
+                     double* cepstra);
+/* scratch: float [n_clips, 13, out_w]; image: float [n_clips, out_h, out_w] */
+int dtb_mfcc_resize_normalize(void* stream, const double* cepstra, int n_clips, long long numframes, int out_w, int out_h, float* scratch,
+                              float* image);
+int dtb_wav_to_mfcc_image(void* stream, const void* signal, int is_i16, int channels, int n_clips, long long n_samples, long long clip_stride,
+                          int samplerate, int out_w, int out_h, void* workspace, size_t workspace_bytes, float* image);
+
 #ifdef __cplusplus
 }
 #endif

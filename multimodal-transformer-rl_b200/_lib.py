@@ -112,6 +112,14 @@ def _declare(lib):
     lib.dtb_modal_attn_workspace_bytes.restype = sz
     lib.dtb_modal_attn_forward.argtypes = [macp, vp, vp, i, vp, vp, vp, sz, vp, vp]
     lib.dtb_modal_attn_backward.argtypes = [macp, vp, vp, i, vp, i, vp, vp, sz, vp, vp]
+    lib.dtb_mfcc_num_frames.argtypes = [ll, i]
+    lib.dtb_mfcc_num_frames.restype = ll
+    lib.dtb_mfcc_filterbank_bins.argtypes = [i, C.POINTER(i), C.POINTER(i)]
+    lib.dtb_mfcc_workspace_bytes.argtypes = [i, ll, i, i]
+    lib.dtb_mfcc_workspace_bytes.restype = sz
+    lib.dtb_mfcc_cepstra.argtypes = [vp, vp, i, i, i, ll, ll, i, vp]
+    lib.dtb_mfcc_resize_normalize.argtypes = [vp, vp, i, ll, i, i, vp, vp]
+    lib.dtb_wav_to_mfcc_image.argtypes = [vp, vp, i, i, i, ll, ll, i, i, i, vp, sz, vp]
     lib.dtb_pad_left.argtypes = [vp, i, C.POINTER(vp), C.POINTER(vp), C.POINTER(i), i, i, vp]
     lib.dtb_dt_set_dropout.argtypes = [vp, f, f, f, vp]
     lib.dtb_get_batch.argtypes = [vp, C.POINTER(TrajStore), vp, vp, i, i, i, C.c_double, C.POINTER(BatchOut)]

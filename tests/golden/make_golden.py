@@ -3,6 +3,7 @@
   encoder_ref_{big,small}.pt : the REFERENCE's own conv_factory / two towers / fusion (imported from /root/reference/src/agents.py
                                with stub modules for its absent deps) on seeded inputs -> pins oracle/encoders.py
   modal_attn_ref.pt          : the REFERENCE's CaslAttention / NewAttention on seeded features -> pins the oracle's restatement
+  mfcc_ref.npz               : 1 s excerpt of the reference's asset target_good.wav + the oracle's MFCC cepstra / image of it
   dt_hf_c1.pt                : HuggingFace DecisionTransformerModel (wpe zeroed = upstream semantics) on seeded inputs -> pins
                                oracle/decision_transformer.py
   dt_oracle_small.pt         : oracle forward / loss / gradient norms on a tiny config -> fixture the GPU path is compared with
@@ -79,6 +80,18 @@ def modal_attn_fixture(agents):
     return out
 
 
+def mfcc_fixture():
+    """1 s of the reference's stereo asset target_good.wav (24 kHz int16) -> oracle cepstra and image (oracle/mfcc.py)."""
+    import numpy as np
+    import scipy.io.wavfile as wav
+
+    from oracle import mfcc as O
+
+    sr, a = wav.read("/root/reference/environments/Minecraft/assets/target_good.wav")
+    a = np.ascontiguousarray(a[24000:48000])
+    return {"samplerate": np.int64(sr), "wav": a, "cepstra": O.psf_mfcc(a, sr), "image": O.wav_to_mfcc(sr, a)}
+
+
 def hf_fixture():
     from transformers import DecisionTransformerConfig, DecisionTransformerModel
     from util import make_inputs
@@ -117,6 +130,8 @@ if __name__ == "__main__":
     torch.save(encoder_fixture(agents, "small"), os.path.join(HERE, "encoder_ref_small.pt"))
     torch.save(fusion_b1_fixture(agents), os.path.join(HERE, "encoder_ref_fusion_b1.pt"))
     torch.save(modal_attn_fixture(agents), os.path.join(HERE, "modal_attn_ref.pt"))
+    import numpy as np
+    np.savez_compressed(os.path.join(HERE, "mfcc_ref.npz"), **mfcc_fixture())
     torch.save(hf_fixture(), os.path.join(HERE, "dt_hf_c1.pt"))
     torch.save(oracle_small_fixture(), os.path.join(HERE, "dt_oracle_small.pt"))
     for f in sorted(os.listdir(HERE)):

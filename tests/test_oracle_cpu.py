@@ -186,3 +186,52 @@ def test_oracle_encoder_with_attention_param_names():
     x = torch.rand(2, 3, 1, 84, 84)
     s = e(x, x)
     assert s.shape == (2, 3, 256) and e.attn_weights.shape == (6, 2)
+
+
+def test_oracle_mfcc_restatement_properties():
+    """oracle/mfcc.py restates python_speech_features 0.6 (absent from this image: parity unpinned for the cepstra).  What can be
+    checked without it: the pieces it delegates to numpy / scipy are called the same way, and its documented invariants hold."""
+    import numpy as np
+    from scipy.fftpack import dct
+
+    from oracle import mfcc as O
+
+    sr, n = 16000, 4000
+    rng = np.random.default_rng(0)
+    t = np.arange(n) / sr
+    x = np.round(5000 * np.sin(2 * np.pi * 1000 * t) + 300 * rng.standard_normal(n)).astype(np.int16)
+    assert O.calculate_nfft(sr, 0.025) == 512 and O.calculate_nfft(44100, 0.025) == 2048 and O.calculate_nfft(24000, 0.025) == 1024
+    assert O.frame_geometry(n, sr) == (400, 160, 1 + int(np.ceil((n - 400) / 160)))
+    assert O.round_half_up(1102.5) == 1103 and O.round_half_up(2.5) == 3  # not banker's rounding
+    fb = O.get_filterbanks(26, 512, sr)
+    assert fb.shape == (26, 257) and fb.min() >= 0 and fb.max() <= 1.0
+    c = O.psf_mfcc(x, sr)
+    assert c.shape == (O.frame_geometry(n, sr)[2], 13) and c.dtype == np.float64
+    # c0 is the log frame energy of the pre-emphasised frame (appendEnergy=True); Parseval ties it to the time domain
+    y = np.append(x[0], x[1:] - 0.97 * x[:-1])
+    # (the one-sided spectrum holds half of the energy, up to the DC / Nyquist bins)
+    assert c[3, 0] == pytest.approx(np.log(np.sum(y[480:880] ** 2) / 2), abs=1e-2)
+    # the DCT it delegates to: ortho DCT-II of a constant vector has only the DC term
+    d = dct(np.ones((1, 26)), type=2, axis=1, norm="ortho")
+    assert d[0, 0] == pytest.approx(np.sqrt(26)) and np.abs(d[0, 1:]).max() < 1e-12
+    # a 1 kHz tone: the strongest filter contains the tone's bin
+    b = O.filterbank_bins(26, 512, sr)
+    pspec = np.abs(np.fft.rfft(y[480:880], 512)) ** 2 / 512
+    j = int(np.argmax(pspec @ fb.T))
+    assert b[j] <= 1000 * 513 / sr <= b[j + 2]
+    # stereo input: pre-emphasis per channel, then numpy.append flattens to interleaved samples (as inside the reference's call)
+    st = np.stack([x, x[::-1]], axis=1).astype(np.float64)
+    pre = np.concatenate([st[:1], st[1:] - 0.97 * st[:-1]]).reshape(-1)
+    assert np.array_equal(O.psf_mfcc(st, sr), O.psf_mfcc(pre, sr, preemph=0.0))
+    img = O.wav_to_mfcc(sr, x)
+    assert img.shape == (84, 84) and img.dtype == np.float32 and img.min() == -1.0 and img.max() == 1.0
+
+
+def test_oracle_mfcc_reproduces_committed_golden():
+    import numpy as np
+
+    from oracle import mfcc as O
+
+    d = np.load(os.path.join(GOLD, "mfcc_ref.npz"))
+    assert np.array_equal(O.psf_mfcc(d["wav"], int(d["samplerate"])), d["cepstra"])
+    assert np.array_equal(O.wav_to_mfcc(int(d["samplerate"]), d["wav"]), d["image"])
