@@ -345,9 +345,11 @@ long long dtb_mfcc_num_frames(long long n_samples, int samplerate);
 /* nfft and the 28 filter-bank edge bins the kernel uses for this sample rate (test hook). */
 int dtb_mfcc_filterbank_bins(int samplerate, int* nfft, int* bins);
 size_t dtb_mfcc_workspace_bytes(int n_clips, long long n_samples, int samplerate, int out_w);
-/* cepstra: double [n_clips, num_frames, 13] */
+/* cepstra: double [n_clips, num_frames, 13]; tables: caller scratch of dtb_mfcc_table_doubles(samplerate) doubles (FFT twiddles + the
+ * DCT / lifter matrix, written by a small kernel at the start of the call and read by every frame's CTA). */
+size_t dtb_mfcc_table_doubles(int samplerate);
 int dtb_mfcc_cepstra(void* stream, const void* signal, int is_i16, int channels, int n_clips, long long n_samples, long long clip_stride, int samplerate,
-                     double* cepstra);
+                     double* tables, double* cepstra);
 /* scratch: float [n_clips, 13, out_w]; image: float [n_clips, out_h, out_w] */
 int dtb_mfcc_resize_normalize(void* stream, const double* cepstra, int n_clips, long long numframes, int out_w, int out_h, float* scratch,
                               float* image);

@@ -117,7 +117,9 @@ def _declare(lib):
     lib.dtb_mfcc_filterbank_bins.argtypes = [i, C.POINTER(i), C.POINTER(i)]
     lib.dtb_mfcc_workspace_bytes.argtypes = [i, ll, i, i]
     lib.dtb_mfcc_workspace_bytes.restype = sz
-    lib.dtb_mfcc_cepstra.argtypes = [vp, vp, i, i, i, ll, ll, i, vp]
+    lib.dtb_mfcc_cepstra.argtypes = [vp, vp, i, i, i, ll, ll, i, vp, vp]
+    lib.dtb_mfcc_table_doubles.argtypes = [i]
+    lib.dtb_mfcc_table_doubles.restype = sz
     lib.dtb_mfcc_resize_normalize.argtypes = [vp, vp, i, ll, i, i, vp, vp]
     lib.dtb_wav_to_mfcc_image.argtypes = [vp, vp, i, i, i, ll, ll, i, i, i, vp, sz, vp]
     lib.dtb_pad_left.argtypes = [vp, i, C.POINTER(vp), C.POINTER(vp), C.POINTER(i), i, i, vp]

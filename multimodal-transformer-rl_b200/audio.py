@@ -38,8 +38,10 @@ def mfcc(signal, samplerate, device="cuda"):
     n = sig.numel()
     frames = mfcc_num_frames(n, samplerate)
     out = torch.empty((frames, 13), dtype=torch.float64, device=dev)
-    _lib.check(_lib.load().dtb_mfcc_cepstra(_lib.stream_ptr(), _lib.ptr(sig), int(sig.dtype == torch.int16), channels, 1, n, n,
-                                            int(samplerate), _lib.ptr(out)))
+    lib = _lib.load()
+    tables = torch.empty(int(lib.dtb_mfcc_table_doubles(int(samplerate))), dtype=torch.float64, device=dev)
+    _lib.check(lib.dtb_mfcc_cepstra(_lib.stream_ptr(), _lib.ptr(sig), int(sig.dtype == torch.int16), channels, 1, n, n, int(samplerate),
+                                    _lib.ptr(tables), _lib.ptr(out)))
     return out
 
 

@@ -61,18 +61,61 @@ __device__ __forceinline__ double warp_sum_d(double v) {
   return v;
 }
 
-// One CTA per (clip, frame).  smem: re[nfft], im[nfft], twiddle cos/sin [nfft / 2] (doubles), then pspec reuses re[].
+// One CTA per (clip, frame).  The real frame of n = nfft samples is packed into m = n / 2 complex points z[i] = y[2i] + i y[2i+1];
+// an m-point FFT (radix-4 passes in registers: two butterfly stages per shared-memory round trip, one radix-2 pass first when log2 m
+// is odd) and the split X[k] = E[k] + e^{-2 pi i k / n} O[k] give the one-sided spectrum.  smem (doubles): zr[m + 1], zi[m + 1],
+// twiddle table e^{-2 pi i k / n} for k < m (the m-point twiddles are its even entries); the power spectrum overwrites zr in place.
+// Tables shared by every frame of a launch (one small kernel per call, kept in the caller's workspace): the twiddles e^{-2 pi i k / n},
+// k < n / 2 (cos, -sin) and the 13 x 26 DCT-II matrix with scipy's 'ortho' scaling and the lifter folded in.
+constexpr int DCT_TABLE = NCEP * NFILT;
+// Layout: [0, m) cos, [m, 2m) -sin, [2m, 2m + 338) DCT, then the mel weights of every bin: up[i] = rising weight of the filter whose
+// rising edge [bin[j], bin[j+1]) holds bin i, dn[i] = the falling weight of filter j - 1 over the same segment (base.get_filterbanks).
+__global__ void __launch_bounds__(256) mfcc_tables_kernel(int n, MfccGeom g, double* __restrict__ tab) {
+  pdl_trigger();
+  pdl_wait();
+  const int m = n >> 1;
+  const int tid = blockIdx.x * blockDim.x + threadIdx.x, nth = gridDim.x * blockDim.x;
+  for (int k = tid; k < m; k += nth) {
+    double sn, cs;
+    sincospi(2.0 * (double)k / (double)n, &sn, &cs);
+    tab[k] = cs;
+    tab[m + k] = -sn;
+  }
+  for (int i = tid; i < DCT_TABLE; i += nth) {
+    const int k = i / NFILT, f = i % NFILT;
+    double v = cospi((double)k * (double)(2 * f + 1) / (double)(2 * NFILT));
+    v *= 2.0 * (k == 0 ? sqrt(1.0 / (4.0 * NFILT)) : sqrt(1.0 / (2.0 * NFILT)));  // scipy.fftpack.dct(type=2, norm='ortho')
+    v *= 1.0 + (CEPLIFTER / 2.0) * sinpi((double)k / CEPLIFTER);                  // base.lifter, L = 22
+    tab[2 * m + i] = v;
+  }
+  double* up = tab + 2 * m + DCT_TABLE;
+  double* dn = up + (m + 1);
+  for (int i = tid; i <= m; i += nth) {
+    double u = 0.0, d = 0.0;
+    for (int j = 0; j <= NFILT; ++j) {
+      const int b0 = g.bin[j], b1 = g.bin[j + 1];
+      if (i >= b0 && i < b1) {
+        u = (double)(i - b0) / (double)(b1 - b0);
+        d = (double)(b1 - i) / (double)(b1 - b0);
+      }
+    }
+    up[i] = u;
+    dn[i] = d;
+  }
+}
+
 template <bool I16>
 __global__ void __launch_bounds__(FFT_THREADS) mfcc_frame_kernel(const void* __restrict__ signal_, long long n_samples, long long clip_stride,
-                                                                 int lag, MfccGeom g, double* __restrict__ cep) {
+                                                                 int lag, MfccGeom g, const double* __restrict__ tab,
+                                                                 double* __restrict__ cep) {
   pdl_trigger();
   pdl_wait();
   extern __shared__ double sm[];
-  const int n = g.nfft, half = n >> 1;
-  double* re = sm;
-  double* im = sm + n;
-  double* tc = sm + 2 * n;
-  double* ts = tc + half;
+  const int n = g.nfft, m = n >> 1, lm = g.log2n - 1;
+  double* zr = sm;
+  double* zi = sm + (m + 1);
+  double* tc = sm + 2 * (m + 1);
+  double* ts = tc + m;
   __shared__ double red[FFT_THREADS / 32];
   __shared__ double fb[NFILT];
   __shared__ double energy_s;
@@ -80,16 +123,10 @@ __global__ void __launch_bounds__(FFT_THREADS) mfcc_frame_kernel(const void* __r
   const long long clip = blockIdx.x / g.numframes, frame = blockIdx.x % g.numframes;
   const long long start = frame * g.frame_step;
 
-  // twiddles e^{-2 pi i k / n}
-  for (int k = tid; k < half; k += FFT_THREADS) {
-    double s, c;
-    sincospi(2.0 * (double)k / (double)n, &s, &c);
-    tc[k] = c;
-    ts[k] = -s;
-  }
-  // pre-emphasised frame, bit-reversed order.  sigproc.preemphasis: append(x[0], x[1:] - 0.97 x[:-1]) acts per channel ROW of an
-  // [n, channels] array and is then flattened: in interleaved samples y[p] = x[p] - 0.97 x[p - lag] (p >= lag), y[p] = x[p] (p < lag),
-  // lag = channels.  Zero padding is appended AFTER the pre-emphasis.
+  for (int k = tid; k < 2 * m; k += FFT_THREADS) tc[k] = tab[k];  // e^{-2 pi i k / n}: cos in tc[0..m), -sin in ts[0..m)
+  // pre-emphasised frame.  sigproc.preemphasis: append(x[0], x[1:] - 0.97 x[:-1]) acts per channel ROW of an [n, channels] array and
+  // is then flattened: in interleaved samples y[p] = x[p] - 0.97 x[p - lag] (p >= lag), y[p] = x[p] (p < lag), lag = channels.
+  // Zero padding is appended AFTER the pre-emphasis.  Sample 2i goes to Re z[i], 2i+1 to Im z[i], z stored in bit-reversed order.
   for (int i = tid; i < n; i += FFT_THREADS) {
     double v = 0.0;
     const long long p = start + i;
@@ -106,34 +143,66 @@ __global__ void __launch_bounds__(FFT_THREADS) mfcc_frame_kernel(const void* __r
       }
       v = p >= lag ? x0 - PREEMPH * x1 : x0;
     }
-    const int r = (int)(__brev((unsigned)i) >> (32 - g.log2n));
-    re[r] = v;
-    im[r] = 0.0;
+    const int r = (int)(__brev((unsigned)(i >> 1)) >> (32 - lm));
+    if (i & 1) zi[r] = v; else zr[r] = v;
   }
   __syncthreads();
-  // radix-2 decimation-in-time butterflies
-  for (int s = 0; s < g.log2n; ++s) {
-    const int h = 1 << s, tstride = half >> s;
-    for (int t = tid; t < half; t += FFT_THREADS) {
-      const int j = t & (h - 1), i0 = ((t >> s) << (s + 1)) + j, i1 = i0 + h;
-      const double wr = tc[j * tstride], wi = ts[j * tstride];
-      const double xr = re[i1], xi = im[i1];
-      const double pr = xr * wr - xi * wi, pi = xr * wi + xi * wr;
-      const double ur = re[i0], ui = im[i0];
-      re[i0] = ur + pr; im[i0] = ui + pi;
-      re[i1] = ur - pr; im[i1] = ui - pi;
+  int s0 = 0;
+  if (lm & 1) {  // radix-2 pass (stage 0: twiddle 1)
+    for (int t = tid; t < (m >> 1); t += FFT_THREADS) {
+      const int i0 = 2 * t, i1 = i0 + 1;
+      const double ar = zr[i0], ai = zi[i0], br = zr[i1], bi = zi[i1];
+      zr[i0] = ar + br; zi[i0] = ai + bi;
+      zr[i1] = ar - br; zi[i1] = ai - bi;
+    }
+    __syncthreads();
+    s0 = 1;
+  }
+  for (int s = s0; s < lm; s += 2) {  // radix-4 pass = stages s and s + 1 (half sizes h and 2h)
+    const int h = 1 << s;
+    const int st1 = 2 * (m >> (s + 1)), st2 = 2 * (m >> (s + 2));  // table strides of W_{2h} and W_{4h} (table = W_n, W_m = W_n^2)
+    for (int q = tid; q < (m >> 2); q += FFT_THREADS) {
+      const int j = q & (h - 1), i0 = ((q >> s) << (s + 2)) + j, i1 = i0 + h, i2 = i1 + h, i3 = i2 + h;
+      const double w1r = tc[j * st1], w1i = ts[j * st1];
+      const double w2r = tc[j * st2], w2i = ts[j * st2];
+      const double w3r = tc[(j + h) * st2], w3i = ts[(j + h) * st2];
+      const double x0r = zr[i0], x0i = zi[i0], x1r = zr[i1], x1i = zi[i1], x2r = zr[i2], x2i = zi[i2], x3r = zr[i3], x3i = zi[i3];
+      double tr = x1r * w1r - x1i * w1i, ti = x1r * w1i + x1i * w1r;
+      const double a0r = x0r + tr, a0i = x0i + ti, a1r = x0r - tr, a1i = x0i - ti;
+      tr = x3r * w1r - x3i * w1i; ti = x3r * w1i + x3i * w1r;
+      const double a2r = x2r + tr, a2i = x2i + ti, a3r = x2r - tr, a3i = x2i - ti;
+      tr = a2r * w2r - a2i * w2i; ti = a2r * w2i + a2i * w2r;
+      zr[i0] = a0r + tr; zi[i0] = a0i + ti;
+      zr[i2] = a0r - tr; zi[i2] = a0i - ti;
+      tr = a3r * w3r - a3i * w3i; ti = a3r * w3i + a3i * w3r;
+      zr[i1] = a1r + tr; zi[i1] = a1i + ti;
+      zr[i3] = a1r - tr; zi[i3] = a1i - ti;
     }
     __syncthreads();
   }
-  // power spectrum (sigproc.powspec: |rfft|^2 / nfft) over bins 0..n/2, kept in tc[0..half] (half + 1 <= 2 * half doubles of tc + ts)
-  double* ps = tc;
+  // split + power spectrum (sigproc.powspec: |rfft|^2 / nfft) for bins 0..m, pair (k, m - k) per thread, written over zr (ps[m] in zr[m])
+  double* ps = zr;
   double e = 0.0;
-  __syncthreads();
-  for (int k = tid; k <= half; k += FFT_THREADS) {
-    const double a = re[k], b = im[k];
-    const double p = (a * a + b * b) / (double)n;
-    ps[k] = p;
-    e += p;
+  const double inv_n = 1.0 / (double)n;
+  for (int k = tid; k <= (m >> 1); k += FFT_THREADS) {
+    const int k2 = (m - k) & (m - 1);
+    const double ar = zr[k], ai = zi[k], br = zr[k2], bi = -zi[k2];  // A = Z[k], B = conj(Z[m - k])
+    const double er = 0.5 * (ar + br), ei = 0.5 * (ai + bi);
+    const double dr = 0.5 * (ar - br), di = 0.5 * (ai - bi);  // O = -i (A - B) / 2 = (di, -dr)
+    const double orr = di, oi = -dr;
+    const double c = tc[k], sn = ts[k];  // (cos, -sin) of 2 pi k / n
+    // X[k] = E + W O
+    const double xr = er + (orr * c - oi * sn), xi = ei + (orr * sn + oi * c);
+    // X[m - k]: E' = conj(E), O' = conj(O), W' = (-c, sn)  [e^{-2 pi i (m - k) / n} = -conj(W)]
+    const double yr = er + (orr * (-c) - (-oi) * sn), yi = -ei + (orr * sn + (-oi) * (-c));
+    const double p0 = (xr * xr + xi * xi) * inv_n, p1 = (yr * yr + yi * yi) * inv_n;  // n is a power of two: same as dividing
+    if (k == 0) {  // X[0] and X[m] both come from Z[0]
+      ps[0] = p0; ps[m] = p1; e += p0 + p1;
+    } else if (k == k2) {
+      ps[k] = p0; e += p0;
+    } else {
+      ps[k] = p0; ps[m - k] = p1; e += p0 + p1;
+    }
   }
   e = warp_sum_d(e);
   if (lane == 0) red[wid] = e;
@@ -143,27 +212,24 @@ __global__ void __launch_bounds__(FFT_THREADS) mfcc_frame_kernel(const void* __r
     for (int i = 0; i < FFT_THREADS / 32; ++i) s += red[i];
     energy_s = s == 0.0 ? F64_EPS : s;
   }
-  // mel filterbank: filter j rises over [bin[j], bin[j+1]) and falls over [bin[j+1], bin[j+2])
+  // mel filterbank: filter j rises over [bin[j], bin[j+1]) and falls over [bin[j+1], bin[j+2]) (weights from the table)
+  const double* mel_up = tab + 2 * m + DCT_TABLE;
+  const double* mel_dn = mel_up + (m + 1);
   for (int j = wid; j < NFILT; j += FFT_THREADS / 32) {
     const int b0 = g.bin[j], b1 = g.bin[j + 1], b2 = g.bin[j + 2];
     double acc = 0.0;
-    for (int i = b0 + lane; i < b2; i += 32) {
-      const double wgt = i < b1 ? (double)(i - b0) / (double)(b1 - b0) : (double)(b2 - i) / (double)(b2 - b1);
-      acc += ps[i] * wgt;
-    }
+    for (int i = b0 + lane; i < b2; i += 32) acc += ps[i] * (i < b1 ? mel_up[i] : mel_dn[i]);
     acc = warp_sum_d(acc);
     if (lane == 0) fb[j] = log(acc == 0.0 ? F64_EPS : acc);
   }
   __syncthreads();
-  // DCT-II, norm='ortho' (scipy.fftpack.dct), first 13 coefficients; lifter 1 + 11 sin(pi k / 22); c0 := log(energy)
-  if (tid < NCEP) {
-    const int k = tid;
-    double s = 0.0;
-    for (int m = 0; m < NFILT; ++m) s += fb[m] * cospi((double)k * (double)(2 * m + 1) / (double)(2 * NFILT));
-    s *= 2.0 * (k == 0 ? sqrt(1.0 / (4.0 * NFILT)) : sqrt(1.0 / (2.0 * NFILT)));
-    s *= 1.0 + (CEPLIFTER / 2.0) * sinpi((double)k / CEPLIFTER);
+  // DCT-II, norm='ortho' (scipy.fftpack.dct), first 13 coefficients, lifter 1 + 11 sin(pi k / 22) (both in the table); c0 := log(energy)
+  const double* dct = tab + 2 * m;
+  for (int k = wid; k < NCEP; k += FFT_THREADS / 32) {
+    double s = lane < NFILT ? fb[lane] * dct[k * NFILT + lane] : 0.0;
+    s = warp_sum_d(s);
     if (k == 0) s = log(energy_s);
-    cep[(clip * g.numframes + frame) * NCEP + k] = s;
+    if (lane == 0) cep[(clip * g.numframes + frame) * NCEP + k] = s;
   }
 }
 
@@ -204,49 +270,88 @@ __device__ __forceinline__ double axis_coeff(const ResampleAxis& ax, double cent
   return ww != 0.0 ? __ddiv_rn(w, ww) : w;
 }
 
-// One CTA per clip.  cep [frames, 13] (double) is the transposed source image: pixel (row y = cepstral index, column x = frame) as float32.
-__global__ void __launch_bounds__(512) mfcc_image_kernel(const double* __restrict__ cep, long long numframes, int W, int H,
-                                                         float* __restrict__ tmp_all, float* __restrict__ image_all) {
+// Horizontal pass (ImagingResampleHorizontal_32bpc), one warp per output column.  cep [frames, 13] (double) is the transposed
+// source image: pixel (row y = cepstral index, column x = frame) as float32.  Pillow sums the weights and then the 13 rows' products
+// sequentially in tap order; double addition is not associative, so those chains stay sequential here (every lane carries the same
+// running sum), while what feeds them — the bicubic weights, their division by the normaliser, the pixel loads — is spread over the
+// 32 lanes: lanes evaluate 32 taps at a time, lanes 0..12 each own one image row.
+__global__ void __launch_bounds__(256) mfcc_resample_h_kernel(const double* __restrict__ cep, long long numframes, int W,
+                                                              float* __restrict__ tmp_all) {
+  pdl_trigger();
+  pdl_wait();
+  __shared__ float pix[8][32 * NCEP];
+  const int lane = threadIdx.x & 31;
+  const int xx = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (xx >= W) return;
+  const double* src = cep + (size_t)blockIdx.y * numframes * NCEP;
+  float* tmp = tmp_all + (size_t)blockIdx.y * NCEP * W;  // [13, W]
+  if (numframes == (long long)W) {  // Pillow skips the pass when the width is unchanged
+    if (lane < NCEP) tmp[lane * W + xx] = (float)src[(size_t)xx * NCEP + lane];
+    return;
+  }
+  const ResampleAxis ax = make_axis((int)numframes, W);
+  const double center = __dmul_rn(__dadd_rn((double)xx, 0.5), ax.scale);
+  int xmin = (int)__dadd_rn(__dsub_rn(center, ax.support), 0.5);
+  if (xmin < 0) xmin = 0;
+  int xmax = (int)__dadd_rn(__dadd_rn(center, ax.support), 0.5);
+  if (xmax > ax.in_size) xmax = ax.in_size;
+  const int cnt = xmax - xmin;
+  double ww = 0.0;
+  for (int base = 0; base < cnt; base += 32) {
+    const int x = base + lane;
+    const double w = x < cnt ? bicubic_filter(__dmul_rn(__dadd_rn(__dsub_rn((double)(x + xmin), center), 0.5), ax.ss)) : 0.0;
+    const int m = min(32, cnt - base);
+    for (int l = 0; l < m; ++l) ww = __dadd_rn(ww, __shfl_sync(0xffffffffu, w, l));
+  }
+  double ss = 0.0;
+  float* px = pix[threadIdx.x >> 5];
+  for (int base = 0; base < cnt; base += 32) {
+    const int x = base + lane;
+    double k = x < cnt ? bicubic_filter(__dmul_rn(__dadd_rn(__dsub_rn((double)(x + xmin), center), 0.5), ax.ss)) : 0.0;
+    if (ww != 0.0) k = __ddiv_rn(k, ww);
+    const int m = min(32, cnt - base);
+    // the chunk's m x 13 source pixels are contiguous: one coalesced sweep into shared memory (as the float32 image Pillow sees)
+    for (int i = lane; i < m * NCEP; i += 32) px[i] = (float)src[(size_t)(xmin + base) * NCEP + i];
+    __syncwarp();
+    for (int l = 0; l < m; ++l) {
+      const double kk = __shfl_sync(0xffffffffu, k, l);
+      if (lane < NCEP) ss = __dadd_rn(ss, __dmul_rn((double)px[l * NCEP + lane], kk));
+    }
+    __syncwarp();
+  }
+  if (lane < NCEP) tmp[lane * W + xx] = (float)ss;
+}
+
+// Vertical pass + min-max normalisation, one CTA per clip.
+__global__ void __launch_bounds__(512) mfcc_image_kernel(int W, int H, const float* __restrict__ tmp_all, float* __restrict__ image_all) {
   pdl_trigger();
   pdl_wait();
   __shared__ float smin[16], smax[16];
-  const double* src = cep + (size_t)blockIdx.x * numframes * NCEP;
-  float* tmp = tmp_all + (size_t)blockIdx.x * NCEP * W;   // [13, W] after the horizontal pass
-  float* img = image_all + (size_t)blockIdx.x * H * W;    // [H, W]
+  extern __shared__ double vk[];  // [H][13] normalised weights of each output row, then ymin / count as ints
+  int* vb = reinterpret_cast<int*>(vk + (size_t)H * NCEP);
+  const float* tmp = tmp_all + (size_t)blockIdx.x * NCEP * W;   // [13, W] after the horizontal pass
+  float* img = image_all + (size_t)blockIdx.x * H * W;          // [H, W]
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-  const bool need_h = numframes != (long long)W, need_v = H != NCEP;
-  // horizontal pass (ImagingResampleHorizontal_32bpc)
-  {
-    const ResampleAxis ax = make_axis((int)numframes, W);
-    for (int o = tid; o < NCEP * W; o += blockDim.x) {
-      const int yy = o / W, xx = o % W;
-      float r;
-      if (need_h) {
-        double center, ww; int xmin, cnt;
-        axis_bounds(ax, xx, center, xmin, cnt, ww);
-        double ss = 0.0;
-        for (int x = 0; x < cnt; ++x)
-          ss = __dadd_rn(ss, __dmul_rn((double)(float)src[(size_t)(x + xmin) * NCEP + yy], axis_coeff(ax, center, xmin, x, ww)));
-        r = (float)ss;
-      } else {
-        r = (float)src[(size_t)xx * NCEP + yy];
-      }
-      tmp[o] = r;
-    }
-  }
-  __syncthreads();
+  const bool need_v = H != NCEP;
   // vertical pass (ImagingResampleVertical_32bpc) + running min / max
   float mn = INFINITY, mx = -INFINITY;
   {
     const ResampleAxis ax = make_axis(NCEP, H);
+    if (need_v)
+      for (int yy = tid; yy < H; yy += blockDim.x) {  // precompute_coeffs of the vertical axis: at most 13 taps (the source has 13 rows)
+        double center, ww; int ymin, cnt;
+        axis_bounds(ax, yy, center, ymin, cnt, ww);
+        for (int y = 0; y < cnt; ++y) vk[yy * NCEP + y] = axis_coeff(ax, center, ymin, y, ww);
+        vb[2 * yy] = ymin; vb[2 * yy + 1] = cnt;
+      }
+    __syncthreads();
     for (int o = tid; o < H * W; o += blockDim.x) {
       const int yy = o / W, xx = o % W;
       float r;
       if (need_v) {
-        double center, ww; int ymin, cnt;
-        axis_bounds(ax, yy, center, ymin, cnt, ww);
+        const int ymin = vb[2 * yy], cnt = vb[2 * yy + 1];
         double ss = 0.0;
-        for (int y = 0; y < cnt; ++y) ss = __dadd_rn(ss, __dmul_rn((double)tmp[(y + ymin) * W + xx], axis_coeff(ax, center, ymin, y, ww)));
+        for (int y = 0; y < cnt; ++y) ss = __dadd_rn(ss, __dmul_rn((double)tmp[(y + ymin) * W + xx], vk[yy * NCEP + y]));
         r = (float)ss;
       } else {
         r = tmp[o];
@@ -271,20 +376,26 @@ __global__ void __launch_bounds__(512) mfcc_image_kernel(const double* __restric
     img[o] = __fsub_rn(__fmul_rn(__fdiv_rn(__fsub_rn(img[o], mn), range), 2.0f), 1.0f);
 }
 
+inline size_t table_doubles(int nfft) { return (size_t)nfft + DCT_TABLE + 2 * ((size_t)nfft / 2 + 1); }
+
 int launch_cepstra(cudaStream_t st, const void* signal, int is_i16, int channels, int n_clips, long long n_samples, long long clip_stride,
-                   const MfccGeom& g, double* cep) {
+                   const MfccGeom& g, double* tab, double* cep) {
   DTB_REQUIRE(channels >= 1 && channels <= 8, DTB_ERR_BAD_ARG, "mfcc: channels must be 1..8");
   const long long blocks = (long long)n_clips * g.numframes;
   DTB_REQUIRE(blocks <= 0x7fffffffLL, DTB_ERR_UNSUPPORTED, "mfcc: too many frames in one launch");
-  const size_t smem = (size_t)3 * g.nfft * sizeof(double);
+  const size_t smem = (size_t)(2 * g.nfft + 2) * sizeof(double);
   static bool attr_set = false;
   if (!attr_set) {
-    DTB_CUDA(cudaFuncSetAttribute(mfcc_frame_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 3 * MAX_NFFT * (int)sizeof(double)));
-    DTB_CUDA(cudaFuncSetAttribute(mfcc_frame_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 3 * MAX_NFFT * (int)sizeof(double)));
+    DTB_CUDA(cudaFuncSetAttribute(mfcc_frame_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (2 * MAX_NFFT + 2) * (int)sizeof(double)));
+    DTB_CUDA(cudaFuncSetAttribute(mfcc_frame_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (2 * MAX_NFFT + 2) * (int)sizeof(double)));
     attr_set = true;
   }
-  if (is_i16) DTB_LAUNCH(mfcc_frame_kernel<true>, (unsigned)blocks, FFT_THREADS, smem, st, signal, n_samples, clip_stride, channels, g, cep);
-  else DTB_LAUNCH(mfcc_frame_kernel<false>, (unsigned)blocks, FFT_THREADS, smem, st, signal, n_samples, clip_stride, channels, g, cep);
+  DTB_LAUNCH(mfcc_tables_kernel, 8, 256, 0, st, g.nfft, g, tab);
+  DTB_CHECK_LAUNCH();
+  if (is_i16)
+    DTB_LAUNCH(mfcc_frame_kernel<true>, (unsigned)blocks, FFT_THREADS, smem, st, signal, n_samples, clip_stride, channels, g, (const double*)tab, cep);
+  else
+    DTB_LAUNCH(mfcc_frame_kernel<false>, (unsigned)blocks, FFT_THREADS, smem, st, signal, n_samples, clip_stride, channels, g, (const double*)tab, cep);
   DTB_CHECK_LAUNCH();
   return DTB_OK;
 }
@@ -310,18 +421,24 @@ int dtb_mfcc_filterbank_bins(int samplerate, int* nfft, int* bins) {
   if (bins) for (int i = 0; i < NFILT + 2; ++i) bins[i] = g.bin[i];
   return DTB_OK;
 }
+size_t dtb_mfcc_table_doubles(int samplerate) {
+  MfccGeom g;
+  if (make_geom(1, samplerate, g) != DTB_OK) return 0;
+  return table_doubles(g.nfft);
+}
 size_t dtb_mfcc_workspace_bytes(int n_clips, long long n_samples, int samplerate, int out_w) {
   MfccGeom g;
   if (n_clips < 1 || out_w < 1 || make_geom(n_samples, samplerate, g) != DTB_OK) return 0;
-  return al256((size_t)n_clips * g.numframes * NCEP * sizeof(double)) + al256((size_t)n_clips * NCEP * out_w * sizeof(float)) + 256;
+  return al256(table_doubles(g.nfft) * sizeof(double)) + al256((size_t)n_clips * g.numframes * NCEP * sizeof(double)) +
+         al256((size_t)n_clips * NCEP * out_w * sizeof(float)) + 256;
 }
 int dtb_mfcc_cepstra(void* stream, const void* signal, int is_i16, int channels, int n_clips, long long n_samples, long long clip_stride, int samplerate,
-                     double* cepstra) {
-  DTB_REQUIRE(signal && cepstra && n_clips >= 1, DTB_ERR_BAD_ARG, "dtb_mfcc_cepstra: null argument");
+                     double* tables, double* cepstra) {
+  DTB_REQUIRE(signal && cepstra && tables && n_clips >= 1, DTB_ERR_BAD_ARG, "dtb_mfcc_cepstra: null argument");
   DTB_TRY(require_sm100());
   MfccGeom g;
   DTB_TRY(make_geom(n_samples, samplerate, g));
-  return launch_cepstra((cudaStream_t)stream, signal, is_i16, channels, n_clips, n_samples, clip_stride, g, cepstra);
+  return launch_cepstra((cudaStream_t)stream, signal, is_i16, channels, n_clips, n_samples, clip_stride, g, tables, cepstra);
 }
 int dtb_mfcc_resize_normalize(void* stream, const double* cepstra, int n_clips, long long numframes, int out_w, int out_h, float* scratch,
                               float* image) {
@@ -329,7 +446,16 @@ int dtb_mfcc_resize_normalize(void* stream, const double* cepstra, int n_clips, 
               "dtb_mfcc_resize_normalize: bad argument");
   DTB_REQUIRE(numframes <= 0x7fffffffLL / NCEP, DTB_ERR_UNSUPPORTED, "mfcc: clip too long");
   DTB_TRY(require_sm100());
-  DTB_LAUNCH(mfcc_image_kernel, n_clips, 512, 0, (cudaStream_t)stream, cepstra, numframes, out_w, out_h, scratch, image);
+  DTB_LAUNCH(mfcc_resample_h_kernel, dim3((out_w + 7) / 8, n_clips), 256, 0, (cudaStream_t)stream, cepstra, numframes, out_w, scratch);
+  DTB_CHECK_LAUNCH();
+  const size_t vsmem = (size_t)out_h * NCEP * sizeof(double) + (size_t)out_h * 2 * sizeof(int);
+  DTB_REQUIRE(vsmem <= 200 * 1024, DTB_ERR_UNSUPPORTED, "mfcc: out_h %d too large", out_h);
+  static size_t vsmem_set = 48 * 1024;
+  if (vsmem > vsmem_set) {
+    DTB_CUDA(cudaFuncSetAttribute(mfcc_image_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    vsmem_set = 200 * 1024;
+  }
+  DTB_LAUNCH(mfcc_image_kernel, n_clips, 512, vsmem, (cudaStream_t)stream, out_w, out_h, (const float*)scratch, image);
   DTB_CHECK_LAUNCH();
   return DTB_OK;
 }
@@ -340,12 +466,15 @@ int dtb_wav_to_mfcc_image(void* stream, const void* signal, int is_i16, int chan
   MfccGeom g;
   DTB_TRY(make_geom(n_samples, samplerate, g));
   uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(workspace) + 255) & ~uintptr_t(255));
+  const size_t tab_bytes = al256(table_doubles(g.nfft) * sizeof(double));
   const size_t cep_bytes = al256((size_t)n_clips * g.numframes * NCEP * sizeof(double));
-  const size_t need = (size_t)(base - reinterpret_cast<uint8_t*>(workspace)) + cep_bytes + al256((size_t)n_clips * NCEP * out_w * sizeof(float));
+  const size_t need = (size_t)(base - reinterpret_cast<uint8_t*>(workspace)) + tab_bytes + cep_bytes +
+                      al256((size_t)n_clips * NCEP * out_w * sizeof(float));
   DTB_REQUIRE(need <= workspace_bytes, DTB_ERR_WORKSPACE, "mfcc: workspace too small (%zu bytes given, %zu needed)", workspace_bytes, need);
-  double* cep = reinterpret_cast<double*>(base);
-  float* scratch = reinterpret_cast<float*>(base + cep_bytes);
-  DTB_TRY(launch_cepstra((cudaStream_t)stream, signal, is_i16, channels, n_clips, n_samples, clip_stride, g, cep));
+  double* tab = reinterpret_cast<double*>(base);
+  double* cep = reinterpret_cast<double*>(base + tab_bytes);
+  float* scratch = reinterpret_cast<float*>(base + tab_bytes + cep_bytes);
+  DTB_TRY(launch_cepstra((cudaStream_t)stream, signal, is_i16, channels, n_clips, n_samples, clip_stride, g, tab, cep));
   return dtb_mfcc_resize_normalize(stream, cep, n_clips, g.numframes, out_w, out_h, scratch, image);
 }
 
