@@ -65,30 +65,59 @@ __device__ __forceinline__ double warp_sum_d(double v) {
 // an m-point FFT (radix-4 passes in registers: two butterfly stages per shared-memory round trip, one radix-2 pass first when log2 m
 // is odd) and the split X[k] = E[k] + e^{-2 pi i k / n} O[k] give the one-sided spectrum.  smem (doubles): zr[m + 1], zi[m + 1],
 // twiddle table e^{-2 pi i k / n} for k < m (the m-point twiddles are its even entries); the power spectrum overwrites zr in place.
+// Bank conflicts (ncu v1: 64 % of the shared wavefronts): zr / zi are padded by one double per 16 (PD) and, while the half size of a
+// pass is < 16, lanes run over butterfly groups instead of over j, which makes every pass conflict-free; the frame is first staged in
+// natural order (padded by one double per 128, PS) in the twiddle area and then gathered in bit-reversed order, so neither the
+// global loads nor the shared stores of the load phase are scattered.
+__device__ __forceinline__ int PD(int i) { return i + (i >> 4); }
+__device__ __forceinline__ int PS(int i) { return i + (i >> 7); }
 // Tables shared by every frame of a launch (one small kernel per call, kept in the caller's workspace): the twiddles e^{-2 pi i k / n},
 // k < n / 2 (cos, -sin) and the 13 x 26 DCT-II matrix with scipy's 'ortho' scaling and the lifter folded in.
 constexpr int DCT_TABLE = NCEP * NFILT;
+// Twiddle table length (complex entries) for an n-point real frame, m = n / 2: [0, m / 2] the split factors e^{-2 pi i k / n}, then per
+// radix-4 pass (half size h) 3h entries laid out contiguously so that lanes running over j read consecutive doubles (ncu v2: the strided
+// reads tc[j * stride] of a single shared table were 4- to 32-way bank conflicts): W_{2h}^j (j < h), then W_{4h}^j (j < 2h).
+__host__ __device__ inline int tw_len(int n) {
+  const int m = n >> 1;
+  int lm = 0;
+  while ((1 << lm) < m) ++lm;
+  int len = m / 2 + 1;
+  for (int s = lm & 1; s < lm; s += 2) len += 3 << s;
+  return len;
+}
 // Layout: [0, m) cos, [m, 2m) -sin, [2m, 2m + 338) DCT, then the mel weights of every bin: up[i] = rising weight of the filter whose
 // rising edge [bin[j], bin[j+1]) holds bin i, dn[i] = the falling weight of filter j - 1 over the same segment (base.get_filterbanks).
 __global__ void __launch_bounds__(256) mfcc_tables_kernel(int n, MfccGeom g, double* __restrict__ tab) {
   pdl_trigger();
   pdl_wait();
-  const int m = n >> 1;
+  const int m = n >> 1, lt = tw_len(n), lm = g.log2n - 1;
   const int tid = blockIdx.x * blockDim.x + threadIdx.x, nth = gridDim.x * blockDim.x;
-  for (int k = tid; k < m; k += nth) {
+  for (int k = tid; k <= m / 2; k += nth) {
     double sn, cs;
     sincospi(2.0 * (double)k / (double)n, &sn, &cs);
     tab[k] = cs;
-    tab[m + k] = -sn;
+    tab[lt + k] = -sn;
+  }
+  int off = m / 2 + 1;
+  for (int s = lm & 1; s < lm; s += 2) {
+    const int h = 1 << s;
+    for (int t = tid; t < 3 * h; t += nth) {
+      double sn, cs;
+      if (t < h) sincospi((double)t / (double)h, &sn, &cs);             // W_{2h}^t = e^{-2 pi i t / (2h)}
+      else sincospi((double)(t - h) / (double)(2 * h), &sn, &cs);       // W_{4h}^{t-h}
+      tab[off + t] = cs;
+      tab[lt + off + t] = -sn;
+    }
+    off += 3 * h;
   }
   for (int i = tid; i < DCT_TABLE; i += nth) {
     const int k = i / NFILT, f = i % NFILT;
     double v = cospi((double)k * (double)(2 * f + 1) / (double)(2 * NFILT));
     v *= 2.0 * (k == 0 ? sqrt(1.0 / (4.0 * NFILT)) : sqrt(1.0 / (2.0 * NFILT)));  // scipy.fftpack.dct(type=2, norm='ortho')
     v *= 1.0 + (CEPLIFTER / 2.0) * sinpi((double)k / CEPLIFTER);                  // base.lifter, L = 22
-    tab[2 * m + i] = v;
+    tab[2 * lt + i] = v;
   }
-  double* up = tab + 2 * m + DCT_TABLE;
+  double* up = tab + 2 * lt + DCT_TABLE;
   double* dn = up + (m + 1);
   for (int i = tid; i <= m; i += nth) {
     double u = 0.0, d = 0.0;
@@ -112,10 +141,12 @@ __global__ void __launch_bounds__(FFT_THREADS) mfcc_frame_kernel(const void* __r
   pdl_wait();
   extern __shared__ double sm[];
   const int n = g.nfft, m = n >> 1, lm = g.log2n - 1;
+  const int zlen = m + (m >> 4) + 1, lt = tw_len(n);
   double* zr = sm;
-  double* zi = sm + (m + 1);
-  double* tc = sm + 2 * (m + 1);
-  double* ts = tc + m;
+  double* zi = sm + zlen;
+  double* tc = sm + 2 * zlen;  // 3m + 2 doubles: staging area of the frame first (n + n / 128 + 1), then the twiddles (cos | -sin)
+  double* ts = tc + lt;
+  double* stage = tc;
   __shared__ double red[FFT_THREADS / 32];
   __shared__ double fb[NFILT];
   __shared__ double energy_s;
@@ -123,7 +154,6 @@ __global__ void __launch_bounds__(FFT_THREADS) mfcc_frame_kernel(const void* __r
   const long long clip = blockIdx.x / g.numframes, frame = blockIdx.x % g.numframes;
   const long long start = frame * g.frame_step;
 
-  for (int k = tid; k < 2 * m; k += FFT_THREADS) tc[k] = tab[k];  // e^{-2 pi i k / n}: cos in tc[0..m), -sin in ts[0..m)
   // pre-emphasised frame.  sigproc.preemphasis: append(x[0], x[1:] - 0.97 x[:-1]) acts per channel ROW of an [n, channels] array and
   // is then flattened: in interleaved samples y[p] = x[p] - 0.97 x[p - lag] (p >= lag), y[p] = x[p] (p < lag), lag = channels.
   // Zero padding is appended AFTER the pre-emphasis.  Sample 2i goes to Re z[i], 2i+1 to Im z[i], z stored in bit-reversed order.
@@ -143,14 +173,21 @@ __global__ void __launch_bounds__(FFT_THREADS) mfcc_frame_kernel(const void* __r
       }
       v = p >= lag ? x0 - PREEMPH * x1 : x0;
     }
-    const int r = (int)(__brev((unsigned)(i >> 1)) >> (32 - lm));
-    if (i & 1) zi[r] = v; else zr[r] = v;
+    stage[PS(i)] = v;
   }
+  __syncthreads();
+  for (int r = tid; r < m; r += FFT_THREADS) {
+    const int i = (int)(__brev((unsigned)r) >> (32 - lm));
+    zr[PD(r)] = stage[PS(2 * i)];
+    zi[PD(r)] = stage[PS(2 * i + 1)];
+  }
+  __syncthreads();
+  for (int k = tid; k < 2 * lt; k += FFT_THREADS) tc[k] = tab[k];  // cos in tc[0..lt), -sin in ts[0..lt)
   __syncthreads();
   int s0 = 0;
   if (lm & 1) {  // radix-2 pass (stage 0: twiddle 1)
     for (int t = tid; t < (m >> 1); t += FFT_THREADS) {
-      const int i0 = 2 * t, i1 = i0 + 1;
+      const int i0 = PD(2 * t), i1 = PD(2 * t + 1);
       const double ar = zr[i0], ai = zi[i0], br = zr[i1], bi = zi[i1];
       zr[i0] = ar + br; zi[i0] = ai + bi;
       zr[i1] = ar - br; zi[i1] = ai - bi;
@@ -158,14 +195,18 @@ __global__ void __launch_bounds__(FFT_THREADS) mfcc_frame_kernel(const void* __r
     __syncthreads();
     s0 = 1;
   }
-  for (int s = s0; s < lm; s += 2) {  // radix-4 pass = stages s and s + 1 (half sizes h and 2h)
+  int poff = m / 2 + 1;
+  for (int s = s0; s < lm; poff += 3 << s, s += 2) {  // radix-4 pass = stages s and s + 1 (half sizes h and 2h)
     const int h = 1 << s;
-    const int st1 = 2 * (m >> (s + 1)), st2 = 2 * (m >> (s + 2));  // table strides of W_{2h} and W_{4h} (table = W_n, W_m = W_n^2)
+    const int groups = m >> (s + 2);
     for (int q = tid; q < (m >> 2); q += FFT_THREADS) {
-      const int j = q & (h - 1), i0 = ((q >> s) << (s + 2)) + j, i1 = i0 + h, i2 = i1 + h, i3 = i2 + h;
-      const double w1r = tc[j * st1], w1i = ts[j * st1];
-      const double w2r = tc[j * st2], w2i = ts[j * st2];
-      const double w3r = tc[(j + h) * st2], w3i = ts[(j + h) * st2];
+      // h >= 16: lanes over j (16 consecutive doubles); h < 16: lanes over groups (stride 4h doubles, spread over the banks by PD)
+      const int j = h >= 16 ? (q & (h - 1)) : (q >> (lm - s - 2)), blk = h >= 16 ? (q >> s) : (q & (groups - 1));
+      const int b0 = (blk << (s + 2)) + j;
+      const int i0 = PD(b0), i1 = PD(b0 + h), i2 = PD(b0 + 2 * h), i3 = PD(b0 + 3 * h);
+      const double w1r = tc[poff + j], w1i = ts[poff + j];                  // W_{2h}^j
+      const double w2r = tc[poff + h + j], w2i = ts[poff + h + j];          // W_{4h}^j
+      const double w3r = tc[poff + 2 * h + j], w3i = ts[poff + 2 * h + j];  // W_{4h}^{j+h}
       const double x0r = zr[i0], x0i = zi[i0], x1r = zr[i1], x1i = zi[i1], x2r = zr[i2], x2i = zi[i2], x3r = zr[i3], x3i = zi[i3];
       double tr = x1r * w1r - x1i * w1i, ti = x1r * w1i + x1i * w1r;
       const double a0r = x0r + tr, a0i = x0i + ti, a1r = x0r - tr, a1i = x0i - ti;
@@ -186,7 +227,7 @@ __global__ void __launch_bounds__(FFT_THREADS) mfcc_frame_kernel(const void* __r
   const double inv_n = 1.0 / (double)n;
   for (int k = tid; k <= (m >> 1); k += FFT_THREADS) {
     const int k2 = (m - k) & (m - 1);
-    const double ar = zr[k], ai = zi[k], br = zr[k2], bi = -zi[k2];  // A = Z[k], B = conj(Z[m - k])
+    const double ar = zr[PD(k)], ai = zi[PD(k)], br = zr[PD(k2)], bi = -zi[PD(k2)];  // A = Z[k], B = conj(Z[m - k])
     const double er = 0.5 * (ar + br), ei = 0.5 * (ai + bi);
     const double dr = 0.5 * (ar - br), di = 0.5 * (ai - bi);  // O = -i (A - B) / 2 = (di, -dr)
     const double orr = di, oi = -dr;
@@ -197,11 +238,11 @@ __global__ void __launch_bounds__(FFT_THREADS) mfcc_frame_kernel(const void* __r
     const double yr = er + (orr * (-c) - (-oi) * sn), yi = -ei + (orr * sn + (-oi) * (-c));
     const double p0 = (xr * xr + xi * xi) * inv_n, p1 = (yr * yr + yi * yi) * inv_n;  // n is a power of two: same as dividing
     if (k == 0) {  // X[0] and X[m] both come from Z[0]
-      ps[0] = p0; ps[m] = p1; e += p0 + p1;
+      ps[0] = p0; ps[PD(m)] = p1; e += p0 + p1;
     } else if (k == k2) {
-      ps[k] = p0; e += p0;
+      ps[PD(k)] = p0; e += p0;
     } else {
-      ps[k] = p0; ps[m - k] = p1; e += p0 + p1;
+      ps[PD(k)] = p0; ps[PD(m - k)] = p1; e += p0 + p1;
     }
   }
   e = warp_sum_d(e);
@@ -213,18 +254,18 @@ __global__ void __launch_bounds__(FFT_THREADS) mfcc_frame_kernel(const void* __r
     energy_s = s == 0.0 ? F64_EPS : s;
   }
   // mel filterbank: filter j rises over [bin[j], bin[j+1]) and falls over [bin[j+1], bin[j+2]) (weights from the table)
-  const double* mel_up = tab + 2 * m + DCT_TABLE;
+  const double* mel_up = tab + 2 * lt + DCT_TABLE;
   const double* mel_dn = mel_up + (m + 1);
   for (int j = wid; j < NFILT; j += FFT_THREADS / 32) {
     const int b0 = g.bin[j], b1 = g.bin[j + 1], b2 = g.bin[j + 2];
     double acc = 0.0;
-    for (int i = b0 + lane; i < b2; i += 32) acc += ps[i] * (i < b1 ? mel_up[i] : mel_dn[i]);
+    for (int i = b0 + lane; i < b2; i += 32) acc += ps[PD(i)] * (i < b1 ? mel_up[i] : mel_dn[i]);
     acc = warp_sum_d(acc);
     if (lane == 0) fb[j] = log(acc == 0.0 ? F64_EPS : acc);
   }
   __syncthreads();
   // DCT-II, norm='ortho' (scipy.fftpack.dct), first 13 coefficients, lifter 1 + 11 sin(pi k / 22) (both in the table); c0 := log(energy)
-  const double* dct = tab + 2 * m;
+  const double* dct = tab + 2 * lt;
   for (int k = wid; k < NCEP; k += FFT_THREADS / 32) {
     double s = lane < NFILT ? fb[lane] * dct[k * NFILT + lane] : 0.0;
     s = warp_sum_d(s);
@@ -376,18 +417,23 @@ __global__ void __launch_bounds__(512) mfcc_image_kernel(int W, int H, const flo
     img[o] = __fsub_rn(__fmul_rn(__fdiv_rn(__fsub_rn(img[o], mn), range), 2.0f), 1.0f);
 }
 
-inline size_t table_doubles(int nfft) { return (size_t)nfft + DCT_TABLE + 2 * ((size_t)nfft / 2 + 1); }
+inline size_t frame_smem_doubles(int nfft) {  // zr, zi (m + m / 16 + 1 each) + staging / twiddle area (n + n / 128 + 1)
+  const size_t m = (size_t)nfft / 2;
+  const size_t stage = (size_t)nfft + (size_t)nfft / 128 + 1, tw = 2 * (size_t)tw_len(nfft);
+  return 2 * (m + m / 16 + 1) + (stage > tw ? stage : tw);
+}
+inline size_t table_doubles(int nfft) { return 2 * (size_t)tw_len(nfft) + DCT_TABLE + 2 * ((size_t)nfft / 2 + 1); }
 
 int launch_cepstra(cudaStream_t st, const void* signal, int is_i16, int channels, int n_clips, long long n_samples, long long clip_stride,
                    const MfccGeom& g, double* tab, double* cep) {
   DTB_REQUIRE(channels >= 1 && channels <= 8, DTB_ERR_BAD_ARG, "mfcc: channels must be 1..8");
   const long long blocks = (long long)n_clips * g.numframes;
   DTB_REQUIRE(blocks <= 0x7fffffffLL, DTB_ERR_UNSUPPORTED, "mfcc: too many frames in one launch");
-  const size_t smem = (size_t)(2 * g.nfft + 2) * sizeof(double);
+  const size_t smem = frame_smem_doubles(g.nfft) * sizeof(double);
   static bool attr_set = false;
   if (!attr_set) {
-    DTB_CUDA(cudaFuncSetAttribute(mfcc_frame_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (2 * MAX_NFFT + 2) * (int)sizeof(double)));
-    DTB_CUDA(cudaFuncSetAttribute(mfcc_frame_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (2 * MAX_NFFT + 2) * (int)sizeof(double)));
+    DTB_CUDA(cudaFuncSetAttribute(mfcc_frame_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(frame_smem_doubles(MAX_NFFT) * sizeof(double))));
+    DTB_CUDA(cudaFuncSetAttribute(mfcc_frame_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(frame_smem_doubles(MAX_NFFT) * sizeof(double))));
     attr_set = true;
   }
   DTB_LAUNCH(mfcc_tables_kernel, 8, 256, 0, st, g.nfft, g, tab);
