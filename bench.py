@@ -522,6 +522,21 @@ def other_workloads(args, skip):
     return out
 
 
+def next_rows():
+    """SURVEY.md §8(f) rows built beside the headline path, timed by their own tools (fresh subprocess each): the modality-attention op
+    (N4, agents.py:58-90) at the c2 sample count and the wav -> MFCC-image front-end (N3, Minecraft.py:226-245) with its numpy / Pillow
+    oracle timed on the host beside it."""
+    out = {}
+    root = os.path.dirname(os.path.abspath(__file__))
+    for key, tool in (("modality_attention", "modal_attn_bench.py"), ("mfcc_front_end", "mfcc_bench.py")):
+        try:
+            r = subprocess.run([sys.executable, os.path.join(root, "tools", tool)], capture_output=True, text=True, timeout=300)
+            out[key] = json.loads(r.stdout.strip().splitlines()[-1])
+        except Exception as e:  # noqa: BLE001
+            out[key] = {"error": str(e)[:200]}
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -588,6 +603,7 @@ def main():
             del ctx  # release this workload's device memory before the sub-runs
             torch.cuda.empty_cache()
             res["other_workloads"] = other_workloads(args, args.workload)
+            res["next_rows"] = next_rows()
         print(json.dumps(res), flush=True)
     if world > 1:
         dist.barrier()
