@@ -97,6 +97,9 @@ class ClockSampler:
 # ------------------------------------------------------------------------------------------------------------------------------
 # our arm
 # ------------------------------------------------------------------------------------------------------------------------------
+ATTN_TYPE = None  # --attn-type: modality attention between the towers and the fusion (agents.py:135-136); None = the reference default
+
+
 def build_ours(wl, dev, pdrop=0.0, rank=0):
     from mtrl_b200.encoder import MultimodalDecisionTransformer, MultimodalStateEncoder
     from mtrl_b200.model import DecisionTransformer
@@ -107,7 +110,7 @@ def build_ours(wl, dev, pdrop=0.0, rank=0):
     dt.set_dropout_seed(1000 + rank)  # independent masks per replica
     if wl["enc"] is None:
         return dt, [dt]
-    enc = MultimodalStateEncoder(wl["enc"]["frame_shape"], wl["enc"]["audio_shape"], "big", "concat", 1.0 / 255.0, device=dev)
+    enc = MultimodalStateEncoder(wl["enc"]["frame_shape"], wl["enc"]["audio_shape"], "big", "concat", 1.0 / 255.0, device=dev, attn_type=ATTN_TYPE)
     return MultimodalDecisionTransformer(enc, dt), [dt, enc]
 
 
@@ -306,7 +309,7 @@ def run_ours(args, wl, rank, world, local_rank):
         "metric": "DT train tokens/s (fwd+bwd)", "value": value, "unit": "tokens/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
         "config": {"workload": wl["label"], "name": args.workload, "batch_per_gpu": B, "global_batch": B * world, "seq_len": 3 * K,
-                   "parallelism": f"dp{world}", "cuda_graph": graphed, "dropout": args.dropout,
+                   "parallelism": f"dp{world}", "cuda_graph": graphed, "dropout": args.dropout, "attn_type": ATTN_TYPE,
                    "l2": ("explicit 256 MiB flush between steps" if flush is not None else
                           f"no flush: per-step working set {ws_bytes / 1e6:.0f} MB > 126 MB L2"),
                    "timed": "weight staging + forward + masked action MSE + backward" + (" + overlapped NCCL all-reduce" if world > 1 else "")},
@@ -333,7 +336,7 @@ def build_oracle(wl, pdrop=0.0):
     dt = ODT(max_length=wl["K"], max_ep_len=MAX_EP_LEN, resid_pdrop=pdrop, attn_pdrop=pdrop, **wl["dt"])
     if wl["enc"] is None:
         return dt
-    return OMM(OEnc(wl["enc"]["frame_shape"], wl["enc"]["audio_shape"], "big", "concat", 1.0 / 255.0), dt)
+    return OMM(OEnc(wl["enc"]["frame_shape"], wl["enc"]["audio_shape"], "big", "concat", 1.0 / 255.0, attn_type=ATTN_TYPE), dt)
 
 
 def oracle_step(wl, model, b):
@@ -500,12 +503,16 @@ def other_workloads(args, skip):
     released): tokens/s, algorithmic TFLOP/s and the dominant kernel's roofline line."""
     out = {}
     runs = [(n, n, args.dropout) for n in ("c1", "c3", "c4") if n != skip]
+    attn_runs = {"c2_attn_casl": "casl", "c2_attn_new": "new"}  # the headline workload with the reference's --attn-type options
+    runs += [(k, "c2", args.dropout) for k in attn_runs]
     if args.dropout > 0:
         runs += [(f"{n}_dropout0", n, 0.0) for n in (skip, "c4") if n]  # the same steps with dropout off (parity mode)
     for key, name, pdrop in runs:
         cmd = [sys.executable, os.path.abspath(__file__), "--workload", name, "--steps", "10" if name == "c4" else "30", "--warmup", "3",
                "--no-cpu-baseline", "--no-extras", "--dropout", str(pdrop)]
-        if key != name:
+        if key in attn_runs:
+            cmd += ["--attn-type", attn_runs[key]]
+        elif key != name:
             cmd += ["--no-get-action"]
         name = key
         try:
@@ -553,8 +560,11 @@ def main():
     ap.add_argument("--no-get-action", action="store_true", help="skip the get_action latency measurement (keeps ncu launch lists to the training step)")
     ap.add_argument("--dropout", type=float, default=0.1, help="resid/attn/embd dropout of the training step (upstream default 0.1)")
     ap.add_argument("--no-optimizer-extra", action="store_true", help="skip the extra timing of the step + fused clip/AdamW")
+    ap.add_argument("--attn-type", default=None, choices=["casl", "new"], help="modality attention of the encoders (reference --attn-type, src/utils.py:115); multimodal workloads only")
     ap.add_argument("--no-extras", action="store_true", help="skip the other-workload summaries (c1 / c3 / c4) appended to the default line")
     args = ap.parse_args()
+    global ATTN_TYPE
+    ATTN_TYPE = args.attn_type
     wl = dict(WORKLOADS[args.workload])
     if args.batch:
         wl["B"] = args.batch
