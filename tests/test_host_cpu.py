@@ -175,3 +175,59 @@ def test_no_global_access_is_hoisted_above_the_pdl_wait():
                 offenders.append((os.path.basename(obj), name[:60], bad))
     assert checked >= 20, checked
     assert not offenders, offenders
+
+
+def test_modal_attention_host_layout_and_no_fallback():
+    """attn.* parameters carry the reference's names / shapes (agents.py:61-64, 81-82), a reference-style state_dict round-trips, the
+    C layout functions agree with them, and nothing computes without the GPU."""
+    import ctypes as C
+
+    from mtrl_b200 import _lib
+    from mtrl_b200.encoder import MultimodalStateEncoder
+    from oracle.encoders import MultimodalStateEncoder as OracleEncoder
+
+    lib = _lib.load()
+    for attn, conv, fusion, sd in [("casl", "big", "concat", 1024), ("new", "small", "sum", 256)]:
+        e = MultimodalStateEncoder((1, 84, 84), (1, 84, 84), conv, fusion, device="cpu", attn_type=attn)
+        o = OracleEncoder((1, 84, 84), (1, 84, 84), conv, fusion, attn_type=attn)
+        assert e.state_dim == sd
+        assert {k: tuple(v.shape) for k, v in e.state_dict().items()} == {k: tuple(v.shape) for k, v in o.state_dict().items()}
+        e.load_state_dict(o.state_dict())
+        for k, v in o.state_dict().items():
+            assert torch.equal(e.state_dict()[k], v), k
+        # every parameter is a view into the one flat buffer the optimizer / all-reduce see
+        base = e.flat_params.data_ptr()
+        for _, p in e.named_parameters():
+            assert base <= p.data_ptr() < base + e.flat_params.numel() * 4
+        with pytest.raises(_lib.DtbError):
+            e(torch.zeros(1, 1, 1, 84, 84), torch.zeros(1, 1, 1, 84, 84))
+    with pytest.raises(NotImplementedError):
+        MultimodalStateEncoder((1, 84, 84), (1, 84, 84), device="cpu", attn_type="other")  # as MinecraftAgent.__init__ (agents.py:114)
+    bad = _lib.ModalAttnConfig(2, 512, 0)
+    assert lib.dtb_modal_attn_param_entries(C.byref(bad)) < 0 and b"type" in lib.dtb_last_error()
+    bad = _lib.ModalAttnConfig(0, 100, 0)
+    assert lib.dtb_modal_attn_workspace_bytes(C.byref(bad), 8) == 0
+
+
+def test_mfcc_host_geometry_and_no_fallback():
+    """Frame count / FFT size / filter-bank bins come from host code in the library (no GPU needed) and must equal the oracle's for the
+    reference's two asset sample rates; compute entry points refuse to run without the device."""
+    import ctypes as C
+
+    from mtrl_b200 import _lib, audio
+    from oracle import mfcc as O
+
+    lib = _lib.load()
+    for sr, n in [(44100, 768764), (24000, 2 * 118203)]:  # noise.wav; target_good.wav (stereo, interleaved)
+        assert lib.dtb_mfcc_num_frames(n, sr) == O.frame_geometry(n, sr)[2]
+        nfft, bins = C.c_int(), (C.c_int * 28)()
+        _lib.check(lib.dtb_mfcc_filterbank_bins(sr, C.byref(nfft), bins))
+        assert nfft.value == O.calculate_nfft(sr, 0.025)
+        assert list(bins) == [int(b) for b in O.filterbank_bins(26, nfft.value, sr)]
+        assert lib.dtb_mfcc_workspace_bytes(1, n, sr, 84) > 13 * 8 * O.frame_geometry(n, sr)[2]
+    assert lib.dtb_mfcc_num_frames(1000, 500) < 0  # unsupported sample rate: error code, not a crash
+    assert lib.dtb_mfcc_num_frames(1000, 400000) < 0  # FFT would exceed the shared-memory kernel's 4096 points
+    with pytest.raises(_lib.DtbError):
+        audio.wav_to_mfcc(16000, torch.zeros(16000, dtype=torch.int16), device="cpu")
+    with pytest.raises(_lib.DtbError):
+        audio.resize_normalize(torch.zeros(50, 13, dtype=torch.float64))
