@@ -310,9 +310,8 @@ class MultimodalDecisionTransformer(nn.Module):
         if runner is None or runner.dead(dt) or runner.frames.dtype != fdt:
             runner = _ActionRunner(dt, self.encoder, fdt)
             self.__dict__["_action_runner"] = runner
-        hist = [(frames[-K:], runner.frames), (audio[-K:], runner.audio), (actions.reshape(-1, dt.act_dim)[-K:], runner.actions),
-                (returns_to_go.reshape(-1, 1)[-K:], runner.rtg), (timesteps.reshape(-1)[-K:], runner.timesteps)]
-        return runner.run(hist)
+        return runner.run([(frames, runner.frames), (audio, runner.audio), (actions, runner.actions), (returns_to_go, runner.rtg),
+                           (timesteps, runner.timesteps)])
 
     def loss_and_backward(self, frames, audio, actions, returns_to_go, timesteps, attention_mask, action_target=None, grad_scale=1.0,
                           on_stage_done=None):

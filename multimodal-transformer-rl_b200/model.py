@@ -318,9 +318,7 @@ class DecisionTransformer(nn.Module):
         if runner is None or runner.dead(self):
             runner = _ActionRunner(self, None)
             self.__dict__["_action_runner"] = runner
-        hist = [(states.reshape(-1, self.state_dim)[-K:], runner.states), (actions.reshape(-1, self.act_dim)[-K:], runner.actions),
-                (returns_to_go.reshape(-1, 1)[-K:], runner.rtg), (timesteps.reshape(-1)[-K:], runner.timesteps)]
-        return runner.run(hist)
+        return runner.run([(states, runner.states), (actions, runner.actions), (returns_to_go, runner.rtg), (timesteps, runner.timesteps)])
 
     # ---- raw paths (no autograd graph) ---------------------------------------------------------------------------
     def _forward_raw(self, states, actions, returns_to_go, timesteps, attention_mask, want_all=True, states_bf16=None, states_relu=False):
@@ -433,19 +431,27 @@ class _ActionRunner:
         self._keep = (dt._last, None if self.enc is None else self.enc._last)  # workspaces stay alive as long as the graph does
 
     def run(self, hist):
+        """hist: [(source tensor with one row per timestep of the WHOLE history, static destination buffer)].  The last-K window is taken
+        by pointer offset (no slicing / reshaping on the host: every torch view costs microseconds on a 200 us call)."""
         lib = _lib.load()
-        t = int(hist[0][0].shape[0])
         n = len(hist)
-        srcs, keep = (C.c_void_p * n)(), []
         if "_dsts" not in self.__dict__:
             self._dsts = (C.c_void_p * n)(*[d.data_ptr() for _, d in hist])
+            self._row_elems = [d[0, 0].numel() for _, d in hist]
             self._rows = (C.c_int * n)(*[d[0, 0].numel() * d.element_size() for _, d in hist])
+            self._srcs = (C.c_void_p * n)()
+        srcs, keep, t = self._srcs, [], -1
         for i, (src, dst) in enumerate(hist):
-            if src.shape[0] != t:
+            if src.dtype != dst.dtype or not src.is_contiguous() or src.requires_grad:
+                src = src.detach().to(dst.dtype).contiguous()
+                keep.append(src)
+            rows = src.numel() // self._row_elems[i]
+            if t < 0:
+                t = rows
+            elif rows != t:
                 raise ValueError("get_action: states / actions / returns_to_go / timesteps must have the same history length")
-            src = src.detach().to(dst.dtype).contiguous()
-            keep.append(src)
-            srcs[i] = src.data_ptr()
+            srcs[i] = src.data_ptr() + (max(0, rows - self.K) * self._rows[i])
+        t = min(t, self.K)
         self.dt._stage()
         if self.enc is not None:
             self.enc._stage()
