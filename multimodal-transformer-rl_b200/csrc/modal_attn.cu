@@ -142,10 +142,11 @@ __global__ void __launch_bounds__(256) ma_stage_kernel(const float* __restrict__
 }
 
 // ---- forward tail: one warp per sample -------------------------------------------------------------------------------------------
+// `pre` and `z_out` may be the same buffer (each element is read, then written, by the same thread): no __restrict__ on those two.
 template <int J>
-__global__ void __launch_bounds__(256) ma_fwd_kernel(const float* __restrict__ pre, const float* __restrict__ Wat,
+__global__ void __launch_bounds__(256) ma_fwd_kernel(const float* pre, const float* __restrict__ Wat,
                                                       const float* __restrict__ bat, const bf16* __restrict__ feat, int N, int F,
-                                                      int fusion, float* __restrict__ z_out, float* __restrict__ w_ws,
+                                                      int fusion, float* z_out, float* __restrict__ w_ws,
                                                       float* __restrict__ w_out, bf16* __restrict__ states) {
   pdl_trigger();
   pdl_wait();

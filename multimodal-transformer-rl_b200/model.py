@@ -412,7 +412,6 @@ class _ActionRunner:
         else:
             self.frames = torch.zeros((1, K, *encoder.frame_shape), dtype=frames_dtype, device=dev)
             self.audio = torch.zeros((1, K, *encoder.audio_shape), dtype=torch.float32, device=dev)
-        self.out = torch.zeros(dt.act_dim, dtype=torch.float32, device=dev)
         self.graph, self._keep = None, None
         self.drop_mode = dt.dropout_active()
 
@@ -427,7 +426,7 @@ class _ActionRunner:
         else:
             sb = self.enc.forward_raw(self.frames, self.audio)
             _, ap, _ = dt._forward_raw(None, self.actions, self.rtg, self.timesteps, self.mask, want_all=False, states_bf16=sb)
-        self.out.copy_(ap[0, -1])
+        self.ap_last = ap[0, -1]  # allocated from the graph's private pool during capture: stays valid (and is rewritten) on every replay
         self._keep = (dt._last, None if self.enc is None else self.enc._last)  # workspaces stay alive as long as the graph does
 
     def run(self, hist):
@@ -464,7 +463,7 @@ class _ActionRunner:
                 self._body()
             self.graph = g
         self.graph.replay()
-        return self.out.clone()
+        return self.ap_last.clone()  # the caller's copy: the static buffer is overwritten by the next call
 
 
 class _DTFunction(torch.autograd.Function):
