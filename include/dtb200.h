@@ -345,16 +345,19 @@ long long dtb_mfcc_num_frames(long long n_samples, int samplerate);
 /* nfft and the 28 filter-bank edge bins the kernel uses for this sample rate (test hook). */
 int dtb_mfcc_filterbank_bins(int samplerate, int* nfft, int* bins);
 size_t dtb_mfcc_workspace_bytes(int n_clips, long long n_samples, int samplerate, int out_w);
-/* cepstra: double [n_clips, num_frames, 13]; tables: caller scratch of dtb_mfcc_table_doubles(samplerate) doubles (FFT twiddles + the
- * DCT / lifter matrix, written by a small kernel at the start of the call and read by every frame's CTA). */
+/* tables: dtb_mfcc_table_doubles(samplerate) doubles in device memory holding the FFT twiddles (per radix-4 pass), the DCT x lifter
+ * matrix and the mel weights of every bin for that sample rate; built once by dtb_mfcc_build_tables and reusable by every later call. */
 size_t dtb_mfcc_table_doubles(int samplerate);
+int dtb_mfcc_build_tables(void* stream, int samplerate, double* tables);
+/* cepstra: double [n_clips, num_frames, 13] */
 int dtb_mfcc_cepstra(void* stream, const void* signal, int is_i16, int channels, int n_clips, long long n_samples, long long clip_stride, int samplerate,
-                     double* tables, double* cepstra);
+                     const double* tables, double* cepstra);
 /* scratch: float [n_clips, 13, out_w]; image: float [n_clips, out_h, out_w] */
 int dtb_mfcc_resize_normalize(void* stream, const double* cepstra, int n_clips, long long numframes, int out_w, int out_h, float* scratch,
                               float* image);
 int dtb_wav_to_mfcc_image(void* stream, const void* signal, int is_i16, int channels, int n_clips, long long n_samples, long long clip_stride,
-                          int samplerate, int out_w, int out_h, void* workspace, size_t workspace_bytes, float* image);
+                          int samplerate, int out_w, int out_h, void* workspace, size_t workspace_bytes, const double* tables /* NULL: built into the workspace */,
+                          float* image);
 
 #ifdef __cplusplus
 }

@@ -121,7 +121,8 @@ def _declare(lib):
     lib.dtb_mfcc_table_doubles.argtypes = [i]
     lib.dtb_mfcc_table_doubles.restype = sz
     lib.dtb_mfcc_resize_normalize.argtypes = [vp, vp, i, ll, i, i, vp, vp]
-    lib.dtb_wav_to_mfcc_image.argtypes = [vp, vp, i, i, i, ll, ll, i, i, i, vp, sz, vp]
+    lib.dtb_wav_to_mfcc_image.argtypes = [vp, vp, i, i, i, ll, ll, i, i, i, vp, sz, vp, vp]
+    lib.dtb_mfcc_build_tables.argtypes = [vp, i, vp]
     lib.dtb_pad_left.argtypes = [vp, i, C.POINTER(vp), C.POINTER(vp), C.POINTER(i), i, i, vp]
     lib.dtb_dt_set_dropout.argtypes = [vp, f, f, f, vp]
     lib.dtb_get_batch.argtypes = [vp, C.POINTER(TrajStore), vp, vp, i, i, i, C.c_double, C.POINTER(BatchOut)]

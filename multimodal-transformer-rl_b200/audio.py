@@ -15,6 +15,24 @@ import torch
 from . import _lib
 
 
+_TABLES = {}
+
+
+def _tables(samplerate, dev):
+    """Per (device, sample rate) tables of the frame kernel (twiddles, DCT x lifter, mel weights): built once, reused by every call."""
+    key = (dev.index if dev.index is not None else torch.cuda.current_device(), int(samplerate))
+    t = _TABLES.get(key)
+    if t is None:
+        lib = _lib.load()
+        n = int(lib.dtb_mfcc_table_doubles(int(samplerate)))
+        if n == 0:
+            raise _lib.DtbError(f"mfcc: unsupported sample rate {samplerate}")
+        t = torch.empty(n, dtype=torch.float64, device=dev)
+        _lib.check(lib.dtb_mfcc_build_tables(_lib.stream_ptr(), int(samplerate), _lib.ptr(t)))
+        _TABLES[key] = t
+    return t
+
+
 def _as_device_signal(wav, device):
     t = torch.as_tensor(wav)
     if t.dtype not in (torch.int16, torch.float32):
@@ -39,7 +57,7 @@ def mfcc(signal, samplerate, device="cuda"):
     frames = mfcc_num_frames(n, samplerate)
     out = torch.empty((frames, 13), dtype=torch.float64, device=dev)
     lib = _lib.load()
-    tables = torch.empty(int(lib.dtb_mfcc_table_doubles(int(samplerate))), dtype=torch.float64, device=dev)
+    tables = _tables(samplerate, sig.device)
     _lib.check(lib.dtb_mfcc_cepstra(_lib.stream_ptr(), _lib.ptr(sig), int(sig.dtype == torch.int16), channels, 1, n, n, int(samplerate),
                                     _lib.ptr(tables), _lib.ptr(out)))
     return out
@@ -90,5 +108,6 @@ def _wav_batch(samplerate, sig, size, channels=1):
     ws = torch.empty(int(lib.dtb_mfcc_workspace_bytes(clips, n, int(samplerate), W)), dtype=torch.uint8, device=sig.device)
     img = torch.empty((clips, H, W), dtype=torch.float32, device=sig.device)
     _lib.check(lib.dtb_wav_to_mfcc_image(_lib.stream_ptr(), _lib.ptr(sig), int(sig.dtype == torch.int16), channels, clips, n, sig.stride(0),
-                                         int(samplerate), W, H, _lib.ptr(ws), ws.numel(), _lib.ptr(img)))
+                                         int(samplerate), W, H, _lib.ptr(ws), ws.numel(), _lib.ptr(_tables(samplerate, sig.device)),
+                                         _lib.ptr(img)))
     return img

@@ -425,7 +425,7 @@ inline size_t frame_smem_doubles(int nfft) {  // zr, zi (m + m / 16 + 1 each) + 
 inline size_t table_doubles(int nfft) { return 2 * (size_t)tw_len(nfft) + DCT_TABLE + 2 * ((size_t)nfft / 2 + 1); }
 
 int launch_cepstra(cudaStream_t st, const void* signal, int is_i16, int channels, int n_clips, long long n_samples, long long clip_stride,
-                   const MfccGeom& g, double* tab, double* cep) {
+                   const MfccGeom& g, const double* tab, double* cep) {
   DTB_REQUIRE(channels >= 1 && channels <= 8, DTB_ERR_BAD_ARG, "mfcc: channels must be 1..8");
   const long long blocks = (long long)n_clips * g.numframes;
   DTB_REQUIRE(blocks <= 0x7fffffffLL, DTB_ERR_UNSUPPORTED, "mfcc: too many frames in one launch");
@@ -436,12 +436,10 @@ int launch_cepstra(cudaStream_t st, const void* signal, int is_i16, int channels
     DTB_CUDA(cudaFuncSetAttribute(mfcc_frame_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(frame_smem_doubles(MAX_NFFT) * sizeof(double))));
     attr_set = true;
   }
-  DTB_LAUNCH(mfcc_tables_kernel, 8, 256, 0, st, g.nfft, g, tab);
-  DTB_CHECK_LAUNCH();
   if (is_i16)
-    DTB_LAUNCH(mfcc_frame_kernel<true>, (unsigned)blocks, FFT_THREADS, smem, st, signal, n_samples, clip_stride, channels, g, (const double*)tab, cep);
+    DTB_LAUNCH(mfcc_frame_kernel<true>, (unsigned)blocks, FFT_THREADS, smem, st, signal, n_samples, clip_stride, channels, g, tab, cep);
   else
-    DTB_LAUNCH(mfcc_frame_kernel<false>, (unsigned)blocks, FFT_THREADS, smem, st, signal, n_samples, clip_stride, channels, g, (const double*)tab, cep);
+    DTB_LAUNCH(mfcc_frame_kernel<false>, (unsigned)blocks, FFT_THREADS, smem, st, signal, n_samples, clip_stride, channels, g, tab, cep);
   DTB_CHECK_LAUNCH();
   return DTB_OK;
 }
@@ -478,8 +476,17 @@ size_t dtb_mfcc_workspace_bytes(int n_clips, long long n_samples, int samplerate
   return al256(table_doubles(g.nfft) * sizeof(double)) + al256((size_t)n_clips * g.numframes * NCEP * sizeof(double)) +
          al256((size_t)n_clips * NCEP * out_w * sizeof(float)) + 256;
 }
+int dtb_mfcc_build_tables(void* stream, int samplerate, double* tables) {
+  DTB_REQUIRE(tables != nullptr, DTB_ERR_BAD_ARG, "dtb_mfcc_build_tables: null argument");
+  DTB_TRY(require_sm100());
+  MfccGeom g;
+  DTB_TRY(make_geom(1, samplerate, g));
+  DTB_LAUNCH(mfcc_tables_kernel, 8, 256, 0, (cudaStream_t)stream, g.nfft, g, tables);
+  DTB_CHECK_LAUNCH();
+  return DTB_OK;
+}
 int dtb_mfcc_cepstra(void* stream, const void* signal, int is_i16, int channels, int n_clips, long long n_samples, long long clip_stride, int samplerate,
-                     double* tables, double* cepstra) {
+                     const double* tables, double* cepstra) {
   DTB_REQUIRE(signal && cepstra && tables && n_clips >= 1, DTB_ERR_BAD_ARG, "dtb_mfcc_cepstra: null argument");
   DTB_TRY(require_sm100());
   MfccGeom g;
@@ -506,7 +513,7 @@ int dtb_mfcc_resize_normalize(void* stream, const double* cepstra, int n_clips, 
   return DTB_OK;
 }
 int dtb_wav_to_mfcc_image(void* stream, const void* signal, int is_i16, int channels, int n_clips, long long n_samples, long long clip_stride,
-                          int samplerate, int out_w, int out_h, void* workspace, size_t workspace_bytes, float* image) {
+                          int samplerate, int out_w, int out_h, void* workspace, size_t workspace_bytes, const double* tables, float* image) {
   DTB_REQUIRE(signal && workspace && image && n_clips >= 1 && out_w >= 1 && out_h >= 1, DTB_ERR_BAD_ARG, "dtb_wav_to_mfcc_image: bad argument");
   DTB_TRY(require_sm100());
   MfccGeom g;
@@ -517,7 +524,11 @@ int dtb_wav_to_mfcc_image(void* stream, const void* signal, int is_i16, int chan
   const size_t need = (size_t)(base - reinterpret_cast<uint8_t*>(workspace)) + tab_bytes + cep_bytes +
                       al256((size_t)n_clips * NCEP * out_w * sizeof(float));
   DTB_REQUIRE(need <= workspace_bytes, DTB_ERR_WORKSPACE, "mfcc: workspace too small (%zu bytes given, %zu needed)", workspace_bytes, need);
-  double* tab = reinterpret_cast<double*>(base);
+  const double* tab = tables;
+  if (!tab) {  // no cached tables: build them into the workspace first
+    DTB_TRY(dtb_mfcc_build_tables(stream, samplerate, reinterpret_cast<double*>(base)));
+    tab = reinterpret_cast<const double*>(base);
+  }
   double* cep = reinterpret_cast<double*>(base + tab_bytes);
   float* scratch = reinterpret_cast<float*>(base + tab_bytes + cep_bytes);
   DTB_TRY(launch_cepstra((cudaStream_t)stream, signal, is_i16, channels, n_clips, n_samples, clip_stride, g, tab, cep));
