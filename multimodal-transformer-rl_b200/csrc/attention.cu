@@ -29,7 +29,17 @@ __global__ void __launch_bounds__(128) attn_fwd_kernel(const bf16* __restrict__ 
   const int q0 = qb * 64;
   const bf16* base = qkv + (size_t)b * T * ld + h * D;
 
+  // Q and the first key / value tile are fetched in one sweep (one L2 round trip instead of two before the first MMA)
+  auto load_kv = [&](int k0) {
+    load_tile<D>(sK, base + H, ld, k0, T);
+    load_tile<D>(sV, base + 2 * H, ld, k0, T);
+    if (threadIdx.x < 64) {
+      const int kj = k0 + threadIdx.x;
+      sValid[threadIdx.x] = (kj < T && (mask == nullptr || mask[(size_t)b * Kmask + kj / 3] > 0.f)) ? 1.f : 0.f;
+    }
+  };
   load_tile<D>(sQ, base, ld, q0, T);
+  load_kv(0);
   __syncthreads();
   uint32_t qf[D / 16][4];
 #pragma unroll
@@ -43,14 +53,11 @@ __global__ void __launch_bounds__(128) attn_fwd_kernel(const bf16* __restrict__ 
 
   for (int kb = 0; kb <= qb; ++kb) {
     const int k0 = kb * 64;
-    __syncthreads();  // previous tile fully consumed
-    load_tile<D>(sK, base + H, ld, k0, T);
-    load_tile<D>(sV, base + 2 * H, ld, k0, T);
-    if (threadIdx.x < 64) {
-      const int kj = k0 + threadIdx.x;
-      sValid[threadIdx.x] = (kj < T && (mask == nullptr || mask[(size_t)b * Kmask + kj / 3] > 0.f)) ? 1.f : 0.f;
+    if (kb > 0) {
+      __syncthreads();  // previous tile fully consumed
+      load_kv(k0);
+      __syncthreads();
     }
-    __syncthreads();
 
     float s[8][4];
 #pragma unroll
