@@ -45,6 +45,27 @@ def main():
         host.append((t1 - t0) * 1e6)
         tot.append((t2 - t0) * 1e6)
     tot.sort(); host.sort()
+    # per-kernel-family time INSIDE the graph (the library's event nodes, as bench.py's roofline pass uses them): a second runner captured
+    # with profiling on; the events add a few microseconds per launch, so read shares
+    import ctypes as C
+
+    from mtrl_b200 import _lib
+
+    lib = _lib.load()
+    lib.dtb_profile_enable(1)
+    model.__dict__.pop("_action_runner", None)
+    for _ in range(3):
+        model.get_action(*args)
+        torch.cuda.synchronize()
+    fam = {}
+    for i, (fname, _) in enumerate(bench.PROF_FAMILIES):
+        ms, work, n = C.c_double(), C.c_double(), C.c_longlong()
+        _lib.check(lib.dtb_profile_report(i, C.byref(ms), C.byref(work), C.byref(n)))
+        if n.value:
+            fam[fname.split(",")[0]] = (round(ms.value * 1e3 / 3, 1), n.value // 3)
+    lib.dtb_profile_enable(0)
+    model.__dict__.pop("_action_runner", None)
+    print(f"{name}: in-graph family times (us per call, launches): {fam}")
     print(f"{name}: graph GPU time {gpu_us:.1f} us (back-to-back replays), call wall p50 {tot[100]:.1f} us, host part (until get_action returns) p50 {host[100]:.1f} us")
 
 
