@@ -15,8 +15,11 @@ import torch
 
 class HostBatchPipeline:
     def __init__(self, make_step: Callable[[Dict[str, torch.Tensor]], Callable[[], torch.Tensor]], example: Dict[str, torch.Tensor],
-                 device: torch.device, use_graph: bool = True, warmup: int = 3):
-        """make_step(device_batch) -> step() returning a device tensor whose element 0 is the loss; `example` fixes shapes/dtypes."""
+                 device: torch.device, use_graph: bool = True, warmup: int = 3, deferred_loss: bool = False):
+        """make_step(device_batch) -> step() returning a device tensor whose element 0 is the loss; `example` fixes shapes/dtypes.
+        deferred_loss: ``step()`` returns the loss of the PREVIOUS step (nan on the first call; ``flush()`` returns the last one): every
+        step's loss is still copied to the host, but the host no longer waits for step i before enqueueing step i + 1, so the GPU never
+        idles for a host round trip.  Default False = upstream ``train_step()`` semantics (the step's own loss, one sync per step)."""
         self.device = device
         self.copy_stream = torch.cuda.Stream(device=device)
         self.slots = []
@@ -24,6 +27,10 @@ class HostBatchPipeline:
             dev = {k: torch.empty(v.shape, dtype=v.dtype, device=device) for k, v in example.items()}
             self.slots.append(dict(dev=dev, step=make_step(dev), graph=None, out=None, copied=torch.cuda.Event(), consumed=torch.cuda.Event()))
         self.loss_host = torch.empty(2, dtype=torch.float32).pin_memory()
+        self.deferred_loss = bool(deferred_loss)
+        self._loss_hosts = [torch.empty(2, dtype=torch.float32).pin_memory() for _ in range(2)]
+        self._loss_events = [torch.cuda.Event() for _ in range(2)]
+        self._pending, self._parity = None, 0
         self.bytes_per_batch = sum(v.numel() * v.element_size() for v in example.values())
         self._cur, self._filled = 0, False
         # warm-up on real data, then capture one graph per slot
@@ -68,10 +75,28 @@ class HostBatchPipeline:
         else:
             out = s["step"]()
         s["consumed"].record(main)
-        self.loss_host.copy_(out[:2] if out.numel() >= 2 else out, non_blocking=True)
-        main.synchronize()
         if next_host_batch is not None:
             self._cur = 1 - self._cur
         else:
             self._filled = False
-        return float(self.loss_host[0])
+        if not self.deferred_loss:
+            self.loss_host.copy_(out[:2] if out.numel() >= 2 else out, non_blocking=True)
+            main.synchronize()
+            return float(self.loss_host[0])
+        buf, ev = self._loss_hosts[self._parity], self._loss_events[self._parity]
+        buf.copy_(out[:2] if out.numel() >= 2 else out, non_blocking=True)
+        ev.record(main)
+        prev, self._pending, self._parity = self._pending, (buf, ev), 1 - self._parity
+        if prev is None:
+            return float("nan")
+        prev[1].synchronize()  # the PREVIOUS step's loss: normally long finished, while this step is already running
+        return float(prev[0][0])
+
+    def flush(self) -> float:
+        """deferred_loss mode: wait for and return the loss of the last step enqueued."""
+        if self._pending is None:
+            return float("nan")
+        buf, ev = self._pending
+        self._pending = None
+        ev.synchronize()
+        return float(buf[0])
