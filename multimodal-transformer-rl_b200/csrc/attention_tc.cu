@@ -1,4 +1,4 @@
-// Causal self-attention with padding mask on tcgen05 tensor cores (head_dim 64) — forward and backward.
+// Causal self-attention with padding mask on tcgen05 tensor cores (head_dim 32 / 64 / 128) — forward and backward.
 // Replaces eager_attention_forward (HF:47-65) + the materialised [B,1,T,T] mask (HF:408-414, 631-635) and its autograd:
 //   allowed(i, j) = (j <= i) and attention_mask[b, j / 3] > 0        (integer-exact index rule)
 // Same tensors and conventions as the mma.sync kernels in attention.cu / attention_bwd.cu (qkv bf16 [B,T,3H] = q | k | v, head h at
@@ -18,7 +18,22 @@
 
 namespace dtb {
 
-constexpr int AT_D = 64;
+// Per-head_dim geometry.  Row tiles are stored as CH chunks of [rows x 64 bf16] (one 128-byte swizzle row per tile row and chunk), each
+// filled by its own TMA box.  D = 128: two chunks; a contraction over head_dim takes KS = 8 UMMA k-steps (4 per chunk) and the head_dim-wide
+// accumulators (O, dQ, dK, dV) are NO = 128 TMEM columns (MN-major B operand = the two chunks, LBO = chunk stride).  D = 32: the boxes stay
+// 64 columns wide (the upper half is the next head / the next of q|k|v / zero fill beyond the tensor: never used as a contraction index,
+// and as an output column it lands in accumulator columns 32..63 that are never read), contractions take KS = 2 k-steps, OC = 1 output chunk.
+template <int D>
+struct AtCfg {
+  static_assert(D == 32 || D == 64 || D == 128, "head_dim 32 / 64 / 128");
+  static constexpr int CH = D == 128 ? 2 : 1;
+  static constexpr int KS = D / 16;
+  static constexpr int NO = D == 128 ? 128 : 64;
+  static constexpr int OC = D / 32;
+  static constexpr int T128 = CH * 128 * 128;  // bytes of a 128-row tile
+  static constexpr int T64 = CH * 64 * 128;    // bytes of a 64-row tile
+  static constexpr int CTAS = D == 128 ? 1 : 2;  // CTAs per SM (shared memory / TMEM columns)
+};
 constexpr int AT_THREADS = 192;      // forward: warps 0-3 softmax, 4 MMA, 5 TMA
 // backward: CW compute warps (4 or 8; warps w and w + 4 share TMEM lane quadrant w & 3), then one MMA warp and one TMA warp
 constexpr int AT_TILE128 = 128 * 128;  // bytes: 128 rows x 128 B (64 bf16)
@@ -85,15 +100,17 @@ __device__ __forceinline__ void at_store_row_unit(uint32_t tile_base, int r, int
 // same running block counter g, so the K/V ring, the S hand-shake and the P buffers run straight through tile boundaries: the next
 // tile's Q / K / V loads and its first S = Q K^T are in flight while the softmax threads still normalise and store the current tile's O
 // (which is why O is double-buffered in TMEM).  With gridDim.x = number of tiles it degenerates to one tile per CTA.
-template <bool DROP>  // DROP = false compiles every dropout branch away (dthr is a constant 0)
-__global__ void __launch_bounds__(AT_THREADS, 2)
+template <int D, bool DROP>  // DROP = false compiles every dropout branch away (dthr is a constant 0)
+__global__ void __launch_bounds__(AT_THREADS, AtCfg<D>::CTAS)
 attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmKV, const AttnTcParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  using Cfg = AtCfg<D>;
+  constexpr int T128 = Cfg::T128, T64 = Cfg::T64, KS = Cfg::KS, NO = Cfg::NO;
   uint8_t* sQ = smem;
-  uint8_t* sK = sQ + AT_TILE128;
-  uint8_t* sV = sK + AT_KV_STAGES * AT_TILE64;
-  uint8_t* sP = sV + AT_KV_STAGES * AT_TILE64;
+  uint8_t* sK = sQ + T128;
+  uint8_t* sV = sK + AT_KV_STAGES * T64;
+  uint8_t* sP = sV + AT_KV_STAGES * T64;
   uint64_t* bars = reinterpret_cast<uint64_t*>(sP + 2 * AT_TILE128);
   uint64_t* q_full = bars;          // [1]
   uint64_t* k_full = bars + 1;      // [4]
@@ -129,7 +146,8 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
     mbar_init(q_free, 1);
     fence_mbar_init();
   }
-  if (warp == 4) { tmem_alloc(tmem_slot, 256); tmem_relinquish(); }
+  constexpr uint32_t TMEM_COLS = 64 + 2 * NO <= 256 ? 256 : 512;
+  if (warp == 4) { tmem_alloc(tmem_slot, TMEM_COLS); tmem_relinquish(); }
   pdl_trigger();  // prologue done: the next kernel of the stream may start its own
   pdl_wait();     // the previous kernel's results are complete and visible from here on
   tc_fence_before();
@@ -137,7 +155,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   const uint32_t tS = tmem_base, tO0 = tmem_base + 64;
-  const int H = p.nh * AT_D;
+  const int H = p.nh * D;
 
   if (warp == 5) {
     // ===================== TMA producer =====================
@@ -148,16 +166,19 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
       for (int t = blockIdx.x; t < ntiles; t += gridDim.x, ++tl) {
         const int hb = t / ntq, h = hb % p.nh, b = hb / p.nh, q0 = tile_qb(t) * 128, nkb = tile_nkb(t);
         if (tl > 0) mbar_wait(q_free, (tl - 1) & 1);  // the previous tile's last S MMA has read Q
-        mbar_arrive_expect_tx(q_full, AT_TILE128);
-        tma_load_3d(sQ, &tmQ, q_full, h * AT_D, q0, b);
+        mbar_arrive_expect_tx(q_full, T128);
+#pragma unroll
+        for (int c = 0; c < Cfg::CH; ++c) tma_load_3d(sQ + c * AT_TILE128, &tmQ, q_full, h * D + 64 * c, q0, b);
         for (int j = 0; j < nkb; ++j, ++g) {
           const int s = g % AT_KV_STAGES, u = g / AT_KV_STAGES;
           if (u > 0) mbar_wait(&k_free[s], (u - 1) & 1);
-          mbar_arrive_expect_tx(&k_full[s], AT_TILE64);
-          tma_load_3d(sK + s * AT_TILE64, &tmKV, &k_full[s], H + h * AT_D, j * 64, b);
+          mbar_arrive_expect_tx(&k_full[s], T64);
+#pragma unroll
+          for (int c = 0; c < Cfg::CH; ++c) tma_load_3d(sK + s * T64 + c * AT_TILE64, &tmKV, &k_full[s], H + h * D + 64 * c, j * 64, b);
           if (u > 0) mbar_wait(&v_free[s], (u - 1) & 1);
-          mbar_arrive_expect_tx(&v_full[s], AT_TILE64);
-          tma_load_3d(sV + s * AT_TILE64, &tmKV, &v_full[s], 2 * H + h * AT_D, j * 64, b);
+          mbar_arrive_expect_tx(&v_full[s], T64);
+#pragma unroll
+          for (int c = 0; c < Cfg::CH; ++c) tma_load_3d(sV + s * T64 + c * AT_TILE64, &tmKV, &v_full[s], 2 * H + h * D + 64 * c, j * 64, b);
         }
       }
     }
@@ -165,7 +186,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
     // ===================== MMA issuer (single thread) =====================
     if (lane == 0) {
       const uint32_t idesc_qk = make_idesc_bf16(128, 64, 0, 0);
-      const uint32_t idesc_pv = make_idesc_bf16(128, 64, 0, 1);
+      const uint32_t idesc_pv = make_idesc_bf16(128, NO, 0, 1);
       const uint32_t q_addr = smem_u32(sQ);
       // S(g) = Q K_g^T; `last` = last block of its tile: its retirement frees the Q buffer for the next tile's load
       auto issue_qk = [&](int g, bool last) {
@@ -173,11 +194,11 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
         mbar_wait(&k_full[s], (g / AT_KV_STAGES) & 1);
         if (g > 0) mbar_wait(s_free, (g - 1) & 1);
         tc_fence_after();
-        const uint32_t k_addr = smem_u32(sK + s * AT_TILE64);
+        const uint32_t k_addr = smem_u32(sK + s * T64);
 #pragma unroll
-        for (int kk = 0; kk < 4; ++kk)
-          umma_bf16(tS, make_smem_desc_sw128(q_addr + kk * 32, 16, 1024), make_smem_desc_sw128(k_addr + kk * 32, 16, 1024), idesc_qk,
-                    kk > 0 ? 1u : 0u);
+        for (int kk = 0; kk < KS; ++kk)  // contraction over head_dim: 4 k-steps per 64-column chunk
+          umma_bf16(tS, make_smem_desc_sw128(q_addr + (kk >> 2) * AT_TILE128 + (kk & 3) * 32, 16, 1024),
+                    make_smem_desc_sw128(k_addr + (kk >> 2) * AT_TILE64 + (kk & 3) * 32, 16, 1024), idesc_qk, kk > 0 ? 1u : 0u);
         umma_commit(&k_free[s]);
         if (last) umma_commit(q_free);
         umma_commit(s_full);
@@ -189,7 +210,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
       }
       for (int t = blockIdx.x; t < ntiles; t += gridDim.x, ++tl) {
         const int nkb = tile_nkb(t), tn = t + gridDim.x;
-        const uint32_t tO = tO0 + 64 * (tl & 1);
+        const uint32_t tO = tO0 + NO * (tl & 1);
         for (int j = 0; j < nkb; ++j, ++g) {
           // look-ahead S: the next block of this tile, or (crossing the tile boundary) the first block of the CTA's next tile
           if (j + 1 < nkb) {
@@ -203,10 +224,10 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
           mbar_wait(&p_full[pb], (g >> 1) & 1);
           if (j == 0 && tl >= 2) mbar_wait(&o_free[tl & 1], ((tl - 2) >> 1) & 1);  // this O buffer was read out (tile tl - 2)
           tc_fence_after();
-          const uint32_t p_addr = smem_u32(sP + pb * AT_TILE128), v_addr = smem_u32(sV + s * AT_TILE64);
+          const uint32_t p_addr = smem_u32(sP + pb * AT_TILE128), v_addr = smem_u32(sV + s * T64);
 #pragma unroll
-          for (int kk = 0; kk < 4; ++kk)
-            umma_bf16(tO, make_smem_desc_sw128(p_addr + kk * 32, 16, 1024), make_smem_desc_sw128(v_addr + kk * 2048, 8192, 1024), idesc_pv,
+          for (int kk = 0; kk < 4; ++kk)  // contraction over the 64 keys; V is the MN-major B operand (N = NO: LBO = chunk stride)
+            umma_bf16(tO, make_smem_desc_sw128(p_addr + kk * 32, 16, 1024), make_smem_desc_sw128(v_addr + kk * 2048, AT_TILE64, 1024), idesc_pv,
                       (j > 0 || kk > 0) ? 1u : 0u);
           umma_commit(&v_free[s]);
           umma_commit(&pv_done[pb]);
@@ -222,7 +243,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
     for (int t = blockIdx.x; t < ntiles; t += gridDim.x, ++tl) {
     const int hb = t / ntq, h = hb % p.nh, b = hb / p.nh, q0 = tile_qb(t) * 128, nkb = tile_nkb(t);
     const int qi = q0 + r;
-    const uint32_t tO = tO0 + 64 * (tl & 1);
+    const uint32_t tO = tO0 + NO * (tl & 1);
     const uint32_t drow = DROP ? at_drop_key(p, b, h) + (uint32_t)qi * (uint32_t)T : 0u;
     // key-validity words of this tile's batch row (the four softmax warps only: named barrier 1)
     asm volatile("bar.sync 1, 128;" ::: "memory");
@@ -336,7 +357,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
         mbar_wait(&pv_done[(g - 1) & 1], ((g - 1) >> 1) & 1);  // moved implies j > 0: PV(g - 1) belongs to this tile
         tc_fence_after();
 #pragma unroll
-        for (int c = 0; c < 2; ++c) {
+        for (int c = 0; c < Cfg::OC; ++c) {
           uint32_t o[32];
           tmem_ld_32x32(tO + lane_addr + c * 32, o);
           tmem_ld_wait();
@@ -354,9 +375,9 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
     mbar_wait(&pv_done[(g - 1) & 1], ((g - 1) >> 1) & 1);
     tc_fence_after();
     const float inv = l > 0.f ? (dthr ? p.drop.scale : 1.f) / l : 0.f;
-    bf16* orow = p.out + ((size_t)b * T + qi) * H + h * AT_D;
+    bf16* orow = p.out + ((size_t)b * T + qi) * H + h * D;
 #pragma unroll
-    for (int c = 0; c < 2; ++c) {
+    for (int c = 0; c < Cfg::OC; ++c) {
       uint32_t o[32];
       tmem_ld_32x32(tO + lane_addr + c * 32, o);
       tmem_ld_wait();
@@ -378,7 +399,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
 
   tc_fence_before();
   __syncthreads();
-  if (warp == 4) { tc_fence_after(); tmem_dealloc(tmem_base, 256); }
+  if (warp == 4) { tc_fence_after(); tmem_dealloc(tmem_base, TMEM_COLS); }
 }
 
 // ================================================================================================================================
@@ -409,17 +430,19 @@ __device__ __forceinline__ void at_ds_half(const uint32_t (&sv)[32], const uint3
   }
 }
 
-template <bool DROP, int CW>  // DROP = false compiles every dropout branch away; CW = compute warps (4: both halves per thread, 8: one)
-__global__ void __launch_bounds__(32 * (CW + 2), 2)
+template <int D, bool DROP, int CW>  // DROP = false compiles every dropout branch away; CW = compute warps (4: both halves per thread, 8: one)
+__global__ void __launch_bounds__(32 * (CW + 2), AtCfg<D>::CTAS)
 attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmKV,
                       const __grid_constant__ CUtensorMap tmDO, const AttnTcParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  using Cfg = AtCfg<D>;
+  constexpr int T128 = Cfg::T128, T64 = Cfg::T64, KS = Cfg::KS, NO = Cfg::NO;
   uint8_t* sQ = smem;
-  uint8_t* sDO = sQ + AT_TILE128;
-  uint8_t* sK = sDO + AT_TILE128;
-  uint8_t* sV = sK + AT_DQ_KST * AT_TILE64;
-  uint8_t* sDS = sV + AT_DQ_VST * AT_TILE64;
+  uint8_t* sDO = sQ + T128;
+  uint8_t* sK = sDO + T128;
+  uint8_t* sV = sK + AT_DQ_KST * T64;
+  uint8_t* sDS = sV + AT_DQ_VST * T64;
   uint64_t* bars = reinterpret_cast<uint64_t*>(sDS + 2 * AT_TILE128);
   uint64_t* qdo_full = bars;        // [1]
   uint64_t* k_full = bars + 1;      // [3]
@@ -459,28 +482,33 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  const uint32_t tS = tmem_base, tDP = tmem_base + 64, tDQ = tmem_base + 128;
-  const int H = p.nh * AT_D;
+  const uint32_t tS = tmem_base, tDP = tmem_base + 64, tDQ = tmem_base + 128;  // 128 + NO <= 256 columns
+  const int H = p.nh * D;
 
   if (warp == CW + 1) {
     if (lane == 0) {
       tma_prefetch_desc(&tmQ); tma_prefetch_desc(&tmKV); tma_prefetch_desc(&tmDO);
-      mbar_arrive_expect_tx(qdo_full, 2 * AT_TILE128);
-      tma_load_3d(sQ, &tmQ, qdo_full, h * AT_D, q0, b);
-      tma_load_3d(sDO, &tmDO, qdo_full, h * AT_D, q0, b);
+      mbar_arrive_expect_tx(qdo_full, 2 * T128);
+#pragma unroll
+      for (int c = 0; c < Cfg::CH; ++c) {
+        tma_load_3d(sQ + c * AT_TILE128, &tmQ, qdo_full, h * D + 64 * c, q0, b);
+        tma_load_3d(sDO + c * AT_TILE128, &tmDO, qdo_full, h * D + 64 * c, q0, b);
+      }
       for (int j = 0; j < nkb; ++j) {
         const int sk = j % AT_DQ_KST, uk = j / AT_DQ_KST, sv = j % AT_DQ_VST, uv = j / AT_DQ_VST;
         if (uk > 0) mbar_wait(&k_free[sk], (uk - 1) & 1);
-        mbar_arrive_expect_tx(&k_full[sk], AT_TILE64);
-        tma_load_3d(sK + sk * AT_TILE64, &tmKV, &k_full[sk], H + h * AT_D, j * 64, b);
+        mbar_arrive_expect_tx(&k_full[sk], T64);
+#pragma unroll
+        for (int c = 0; c < Cfg::CH; ++c) tma_load_3d(sK + sk * T64 + c * AT_TILE64, &tmKV, &k_full[sk], H + h * D + 64 * c, j * 64, b);
         if (uv > 0) mbar_wait(&v_free[sv], (uv - 1) & 1);
-        mbar_arrive_expect_tx(&v_full[sv], AT_TILE64);
-        tma_load_3d(sV + sv * AT_TILE64, &tmKV, &v_full[sv], 2 * H + h * AT_D, j * 64, b);
+        mbar_arrive_expect_tx(&v_full[sv], T64);
+#pragma unroll
+        for (int c = 0; c < Cfg::CH; ++c) tma_load_3d(sV + sv * T64 + c * AT_TILE64, &tmKV, &v_full[sv], 2 * H + h * D + 64 * c, j * 64, b);
       }
     }
   } else if (warp == CW) {
     if (lane == 0) {
-      const uint32_t idesc_kk = make_idesc_bf16(128, 64, 0, 0), idesc_kn = make_idesc_bf16(128, 64, 0, 1);
+      const uint32_t idesc_kk = make_idesc_bf16(128, 64, 0, 0), idesc_kn = make_idesc_bf16(128, NO, 0, 1);
       const uint32_t q_addr = smem_u32(sQ), do_addr = smem_u32(sDO);
       auto issue_sdp = [&](int j) {
         const int sk = j % AT_DQ_KST, sv = j % AT_DQ_VST;
@@ -488,15 +516,15 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
         mbar_wait(&v_full[sv], (j / AT_DQ_VST) & 1);
         if (j > 0) mbar_wait(sdp_free, (j - 1) & 1);
         tc_fence_after();
-        const uint32_t k_addr = smem_u32(sK + sk * AT_TILE64), v_addr = smem_u32(sV + sv * AT_TILE64);
+        const uint32_t k_addr = smem_u32(sK + sk * T64), v_addr = smem_u32(sV + sv * T64);
 #pragma unroll
-        for (int kk = 0; kk < 4; ++kk)
-          umma_bf16(tS, make_smem_desc_sw128(q_addr + kk * 32, 16, 1024), make_smem_desc_sw128(k_addr + kk * 32, 16, 1024), idesc_kk,
-                    kk > 0 ? 1u : 0u);
+        for (int kk = 0; kk < KS; ++kk)
+          umma_bf16(tS, make_smem_desc_sw128(q_addr + (kk >> 2) * AT_TILE128 + (kk & 3) * 32, 16, 1024),
+                    make_smem_desc_sw128(k_addr + (kk >> 2) * AT_TILE64 + (kk & 3) * 32, 16, 1024), idesc_kk, kk > 0 ? 1u : 0u);
 #pragma unroll
-        for (int kk = 0; kk < 4; ++kk)
-          umma_bf16(tDP, make_smem_desc_sw128(do_addr + kk * 32, 16, 1024), make_smem_desc_sw128(v_addr + kk * 32, 16, 1024), idesc_kk,
-                    kk > 0 ? 1u : 0u);
+        for (int kk = 0; kk < KS; ++kk)
+          umma_bf16(tDP, make_smem_desc_sw128(do_addr + (kk >> 2) * AT_TILE128 + (kk & 3) * 32, 16, 1024),
+                    make_smem_desc_sw128(v_addr + (kk >> 2) * AT_TILE64 + (kk & 3) * 32, 16, 1024), idesc_kk, kk > 0 ? 1u : 0u);
         umma_commit(&v_free[sv]);
         umma_commit(sdp_full);
       };
@@ -507,10 +535,10 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
         const int sk = j % AT_DQ_KST, db = j & 1;
         mbar_wait(&ds_full[db], (j >> 1) & 1);
         tc_fence_after();
-        const uint32_t ds_addr = smem_u32(sDS + db * AT_TILE128), k_addr = smem_u32(sK + sk * AT_TILE64);
+        const uint32_t ds_addr = smem_u32(sDS + db * AT_TILE128), k_addr = smem_u32(sK + sk * T64);
 #pragma unroll
         for (int kk = 0; kk < 4; ++kk)
-          umma_bf16(tDQ, make_smem_desc_sw128(ds_addr + kk * 32, 16, 1024), make_smem_desc_sw128(k_addr + kk * 2048, 8192, 1024), idesc_kn,
+          umma_bf16(tDQ, make_smem_desc_sw128(ds_addr + kk * 32, 16, 1024), make_smem_desc_sw128(k_addr + kk * 2048, AT_TILE64, 1024), idesc_kn,
                     (j > 0 || kk > 0) ? 1u : 0u);
         umma_commit(&k_free[sk]);
         umma_commit(&ds_done[db]);
@@ -529,10 +557,10 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
     const uint32_t dthr = DROP ? p.drop.thr : 0u;
     const uint32_t drow = DROP ? at_drop_key(p, b, h) + (uint32_t)qi * (uint32_t)T : 0u;
     if (qi < T) {
-      const uint4* orow = reinterpret_cast<const uint4*>(p.out_in + ((size_t)b * T + qi) * H + h * AT_D);
-      const uint4* drow_g = reinterpret_cast<const uint4*>(p.dout + ((size_t)b * T + qi) * H + h * AT_D);
+      const uint4* orow = reinterpret_cast<const uint4*>(p.out_in + ((size_t)b * T + qi) * H + h * D);
+      const uint4* drow_g = reinterpret_cast<const uint4*>(p.dout + ((size_t)b * T + qi) * H + h * D);
 #pragma unroll
-      for (int u = 0; u < 8; ++u) {
+      for (int u = 0; u < D / 8; ++u) {
         const uint4 a = __ldg(orow + u), g = __ldg(drow_g + u);
         const uint32_t aw[4] = {a.x, a.y, a.z, a.w}, gw[4] = {g.x, g.y, g.z, g.w};
 #pragma unroll
@@ -579,9 +607,10 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
     }
     mbar_wait(&ds_done[(nkb - 1) & 1], ((nkb - 1) >> 1) & 1);
     tc_fence_after();
+    // dQ read-out: 32-column chunks of the head; CW = 8: the two warps of a lane quadrant take alternate chunks
 #pragma unroll
-    for (int half = h_lo; half < h_hi; ++half) {
-      bf16* grow = p.dqkv + ((size_t)b * T + qi) * 3 * H + h * AT_D + 32 * half;
+    for (int half = h_lo; half < Cfg::OC; half += (CW == 8 ? 2 : 1)) {
+      bf16* grow = p.dqkv + ((size_t)b * T + qi) * 3 * H + h * D + 32 * half;
       uint32_t o[32];
       tmem_ld_32x32(tDQ + lane_base + 32 * half, o);
       tmem_ld_wait();
@@ -606,17 +635,19 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
 // TMEM (256 columns): S^T at 0, dP^T at 64, dV at 128, dK at 192
 constexpr int AT_MAX_T_BWD = 1024;
 
-template <bool DROP, int CW>
-__global__ void __launch_bounds__(32 * (CW + 2), 2)
+template <int D, bool DROP, int CW>
+__global__ void __launch_bounds__(32 * (CW + 2), AtCfg<D>::CTAS)
 attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmKV, const __grid_constant__ CUtensorMap tmQ64,
                        const __grid_constant__ CUtensorMap tmDO64, const AttnTcParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  using Cfg = AtCfg<D>;
+  constexpr int T128 = Cfg::T128, T64 = Cfg::T64, KS = Cfg::KS, NO = Cfg::NO;
   uint8_t* sK = smem;
-  uint8_t* sV = sK + AT_TILE128;
-  uint8_t* sQ = sV + AT_TILE128;
-  uint8_t* sDO = sQ + 2 * AT_TILE64;
-  uint8_t* sPT = sDO + 2 * AT_TILE64;
+  uint8_t* sV = sK + T128;
+  uint8_t* sQ = sV + T128;
+  uint8_t* sDO = sQ + 2 * T64;
+  uint8_t* sPT = sDO + 2 * T64;
   uint8_t* sDST = sPT + AT_TILE128;
   uint64_t* bars = reinterpret_cast<uint64_t*>(sDST + AT_TILE128);
   uint64_t* kv_full = bars;         // [1]
@@ -646,7 +677,8 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmKV, const __grid_co
     mbar_init(pds_done, 1);
     fence_mbar_init();
   }
-  if (warp == CW) { tmem_alloc(tmem_slot, 256); tmem_relinquish(); }
+  constexpr uint32_t TMEM_COLS = 128 + 2 * NO <= 256 ? 256 : 512;
+  if (warp == CW) { tmem_alloc(tmem_slot, TMEM_COLS); tmem_relinquish(); }
   pdl_trigger();  // prologue done: the next kernel of the stream may start its own
   pdl_wait();     // the previous kernel's results are complete and visible from here on
   for (int t = i0 * 64 + threadIdx.x; t < nqb * 64; t += blockDim.x) {
@@ -657,41 +689,47 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmKV, const __grid_co
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  const uint32_t tST = tmem_base, tDPT = tmem_base + 64, tDV = tmem_base + 128, tDK = tmem_base + 192;
-  const int H = p.nh * AT_D;
+  const uint32_t tST = tmem_base, tDPT = tmem_base + 64, tDV = tmem_base + 128, tDK = tmem_base + 128 + NO;
+  const int H = p.nh * D;
 
   if (warp == CW + 1) {
     if (lane == 0) {
       tma_prefetch_desc(&tmKV); tma_prefetch_desc(&tmQ64); tma_prefetch_desc(&tmDO64);
-      mbar_arrive_expect_tx(kv_full, 2 * AT_TILE128);
-      tma_load_3d(sK, &tmKV, kv_full, H + h * AT_D, k0, b);
-      tma_load_3d(sV, &tmKV, kv_full, 2 * H + h * AT_D, k0, b);
+      mbar_arrive_expect_tx(kv_full, 2 * T128);
+#pragma unroll
+      for (int c = 0; c < Cfg::CH; ++c) {
+        tma_load_3d(sK + c * AT_TILE128, &tmKV, kv_full, H + h * D + 64 * c, k0, b);
+        tma_load_3d(sV + c * AT_TILE128, &tmKV, kv_full, 2 * H + h * D + 64 * c, k0, b);
+      }
       for (int t = 0; t < n; ++t) {
         const int s = t & 1, u = t >> 1;
         if (u > 0) mbar_wait(&qdo_free[s], (u - 1) & 1);
-        mbar_arrive_expect_tx(&qdo_full[s], 2 * AT_TILE64);
-        tma_load_3d(sQ + s * AT_TILE64, &tmQ64, &qdo_full[s], h * AT_D, (i0 + t) * 64, b);
-        tma_load_3d(sDO + s * AT_TILE64, &tmDO64, &qdo_full[s], h * AT_D, (i0 + t) * 64, b);
+        mbar_arrive_expect_tx(&qdo_full[s], 2 * T64);
+#pragma unroll
+        for (int c = 0; c < Cfg::CH; ++c) {
+          tma_load_3d(sQ + s * T64 + c * AT_TILE64, &tmQ64, &qdo_full[s], h * D + 64 * c, (i0 + t) * 64, b);
+          tma_load_3d(sDO + s * T64 + c * AT_TILE64, &tmDO64, &qdo_full[s], h * D + 64 * c, (i0 + t) * 64, b);
+        }
       }
     }
   } else if (warp == CW) {
     if (lane == 0) {
-      const uint32_t idesc_kk = make_idesc_bf16(128, 64, 0, 0), idesc_kn = make_idesc_bf16(128, 64, 0, 1);
+      const uint32_t idesc_kk = make_idesc_bf16(128, 64, 0, 0), idesc_kn = make_idesc_bf16(128, NO, 0, 1);
       const uint32_t k_addr = smem_u32(sK), v_addr = smem_u32(sV), pt_addr = smem_u32(sPT), dst_addr = smem_u32(sDST);
       auto issue_sdp = [&](int t) {
         const int s = t & 1;
         mbar_wait(&qdo_full[s], (t >> 1) & 1);
         if (t > 0) mbar_wait(sdp_free, (t - 1) & 1);
         tc_fence_after();
-        const uint32_t q_addr = smem_u32(sQ + s * AT_TILE64), do_addr = smem_u32(sDO + s * AT_TILE64);
+        const uint32_t q_addr = smem_u32(sQ + s * T64), do_addr = smem_u32(sDO + s * T64);
 #pragma unroll
-        for (int kk = 0; kk < 4; ++kk)
-          umma_bf16(tST, make_smem_desc_sw128(k_addr + kk * 32, 16, 1024), make_smem_desc_sw128(q_addr + kk * 32, 16, 1024), idesc_kk,
-                    kk > 0 ? 1u : 0u);
+        for (int kk = 0; kk < KS; ++kk)
+          umma_bf16(tST, make_smem_desc_sw128(k_addr + (kk >> 2) * AT_TILE128 + (kk & 3) * 32, 16, 1024),
+                    make_smem_desc_sw128(q_addr + (kk >> 2) * AT_TILE64 + (kk & 3) * 32, 16, 1024), idesc_kk, kk > 0 ? 1u : 0u);
 #pragma unroll
-        for (int kk = 0; kk < 4; ++kk)
-          umma_bf16(tDPT, make_smem_desc_sw128(v_addr + kk * 32, 16, 1024), make_smem_desc_sw128(do_addr + kk * 32, 16, 1024), idesc_kk,
-                    kk > 0 ? 1u : 0u);
+        for (int kk = 0; kk < KS; ++kk)
+          umma_bf16(tDPT, make_smem_desc_sw128(v_addr + (kk >> 2) * AT_TILE128 + (kk & 3) * 32, 16, 1024),
+                    make_smem_desc_sw128(do_addr + (kk >> 2) * AT_TILE64 + (kk & 3) * 32, 16, 1024), idesc_kk, kk > 0 ? 1u : 0u);
         umma_commit(sdp_full);
       };
       mbar_wait(kv_full, 0);
@@ -701,14 +739,14 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmKV, const __grid_co
         const int s = t & 1;
         mbar_wait(pds_full, t & 1);
         tc_fence_after();
-        const uint32_t q_addr = smem_u32(sQ + s * AT_TILE64), do_addr = smem_u32(sDO + s * AT_TILE64);
+        const uint32_t q_addr = smem_u32(sQ + s * T64), do_addr = smem_u32(sDO + s * T64);
 #pragma unroll
         for (int kk = 0; kk < 4; ++kk)
-          umma_bf16(tDV, make_smem_desc_sw128(pt_addr + kk * 32, 16, 1024), make_smem_desc_sw128(do_addr + kk * 2048, 8192, 1024), idesc_kn,
+          umma_bf16(tDV, make_smem_desc_sw128(pt_addr + kk * 32, 16, 1024), make_smem_desc_sw128(do_addr + kk * 2048, AT_TILE64, 1024), idesc_kn,
                     (t > 0 || kk > 0) ? 1u : 0u);
 #pragma unroll
         for (int kk = 0; kk < 4; ++kk)
-          umma_bf16(tDK, make_smem_desc_sw128(dst_addr + kk * 32, 16, 1024), make_smem_desc_sw128(q_addr + kk * 2048, 8192, 1024), idesc_kn,
+          umma_bf16(tDK, make_smem_desc_sw128(dst_addr + kk * 32, 16, 1024), make_smem_desc_sw128(q_addr + kk * 2048, AT_TILE64, 1024), idesc_kn,
                     (t > 0 || kk > 0) ? 1u : 0u);
         umma_commit(&qdo_free[s]);
         umma_commit(pds_done);
@@ -790,7 +828,7 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmKV, const __grid_co
 #pragma unroll
     for (int which = 0; which < 2; ++which) {  // 0: dV -> columns 2H.., 1: dK -> columns H..
 #pragma unroll
-      for (int half = h_lo; half < h_hi; ++half) {
+      for (int half = h_lo; half < Cfg::OC; half += (CW == 8 ? 2 : 1)) {  // 32-column chunks of the head (CW = 8: alternate chunks per warp)
         uint32_t o[32];
         tmem_ld_32x32((which == 0 ? tDV : tDK) + lane_base + 32 * half, o);
         tmem_ld_wait();
@@ -799,7 +837,7 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmKV, const __grid_co
           for (int e = 0; e < 32; ++e) o[e] = __float_as_uint(__uint_as_float(o[e]) * p.drop.scale);
         }
         if (kj < T) {
-          bf16* dst = p.dqkv + ((size_t)b * T + kj) * 3 * H + h * AT_D + 32 * half + (which == 0 ? 2 * H : H);
+          bf16* dst = p.dqkv + ((size_t)b * T + kj) * 3 * H + h * D + 32 * half + (which == 0 ? 2 * H : H);
 #pragma unroll
           for (int e = 0; e < 32; e += 8)
             *reinterpret_cast<uint4*>(dst + e) =
@@ -811,10 +849,14 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmKV, const __grid_co
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == CW) { tc_fence_after(); tmem_dealloc(tmem_base, 256); }
+  if (warp == CW) { tc_fence_after(); tmem_dealloc(tmem_base, TMEM_COLS); }
 }
 
-constexpr int AT_FWD_SMEM = 1024 + AT_TILE128 + 2 * AT_KV_STAGES * AT_TILE64 + 2 * AT_TILE128 + 256 + AT_MAX_CHUNKS * 4;
+template <int D> constexpr int at_fwd_smem() { return 1024 + AtCfg<D>::T128 + 2 * AT_KV_STAGES * AtCfg<D>::T64 + 2 * AT_TILE128 + 256 + AT_MAX_CHUNKS * 4; }
+template <int D> constexpr int at_dq_smem() {
+  return 1024 + 2 * AtCfg<D>::T128 + (AT_DQ_KST + AT_DQ_VST) * AtCfg<D>::T64 + 2 * AT_TILE128 + 256 + AT_MAX_CHUNKS * 4;
+}
+template <int D> constexpr int at_dkv_smem() { return 1024 + 2 * AtCfg<D>::T128 + 4 * AtCfg<D>::T64 + 2 * AT_TILE128 + 256 + 2 * AT_MAX_T_BWD * 4; }
 
 bool attn_tc_supported(int T, int d) {
   static int legacy = -1;
@@ -822,65 +864,80 @@ bool attn_tc_supported(int T, int d) {
     const char* e = getenv("DTB_ATTN_LEGACY");
     legacy = (e && e[0] == '1') ? 1 : 0;
   }
-  return !legacy && d == AT_D && T >= 1 && T <= AT_MAX_T_BWD;
+  return !legacy && (d == 32 || d == 64 || d == 128) && T >= 1 && T <= AT_MAX_T_BWD;
 }
 
-static int at_maps(const bf16* qkv, int B, int T, int H, CUtensorMap* tm128, CUtensorMap* tm64) {
-  DTB_TRY(make_tmap3(tm128, qkv, (uint64_t)3 * H, (uint64_t)T, (uint64_t)B, (uint64_t)3 * H, (uint64_t)T * 3 * H, 64, 128));
-  DTB_TRY(make_tmap3(tm64, qkv, (uint64_t)3 * H, (uint64_t)T, (uint64_t)B, (uint64_t)3 * H, (uint64_t)T * 3 * H, 64, 64));
+// 64-column boxes of 128 / 64 rows over a [B, T, cols] bf16 tensor (columns beyond `cols` read as zeros: the d = 32 boxes of the last head)
+static int at_maps(const bf16* x, int B, int T, int cols, CUtensorMap* tm128, CUtensorMap* tm64) {
+  DTB_TRY(make_tmap3(tm128, x, (uint64_t)cols, (uint64_t)T, (uint64_t)B, (uint64_t)cols, (uint64_t)T * cols, 64, 128));
+  DTB_TRY(make_tmap3(tm64, x, (uint64_t)cols, (uint64_t)T, (uint64_t)B, (uint64_t)cols, (uint64_t)T * cols, 64, 64));
+  return DTB_OK;
+}
+
+template <int D>
+static int at_fwd_launch(cudaStream_t stream, const CUtensorMap& tmQ, const CUtensorMap& tmKV, const AttnTcParams& p, long long ntiles,
+                         bool drop) {
+  static bool attr = false;
+  if (!attr) {
+    DTB_CUDA(cudaFuncSetAttribute(attn_fwd_tc_kernel<D, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, at_fwd_smem<D>()));
+    DTB_CUDA(cudaFuncSetAttribute(attn_fwd_tc_kernel<D, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, at_fwd_smem<D>()));
+    attr = true;
+  }
+  // persistent: AtCfg::CTAS CTAs per SM (shared memory / TMEM columns each) walk the tile list; DTB_ATTN_PERSIST=0 -> one tile per CTA
+  static int persist = -1;
+  if (persist < 0) {
+    const char* e = getenv("DTB_ATTN_PERSIST");
+    persist = (e && e[0] == '0') ? 0 : 1;
+  }
+  const long long cap = persist ? (long long)AtCfg<D>::CTAS * num_sms() : ntiles;
+  dim3 grid((unsigned)(ntiles < cap ? ntiles : cap));
+  if (drop) DTB_LAUNCH((attn_fwd_tc_kernel<D, true>), grid, AT_THREADS, at_fwd_smem<D>(), stream, tmQ, tmKV, p);
+  else DTB_LAUNCH((attn_fwd_tc_kernel<D, false>), grid, AT_THREADS, at_fwd_smem<D>(), stream, tmQ, tmKV, p);
   return DTB_OK;
 }
 
 int attn_fwd_tc(cudaStream_t stream, const bf16* qkv, const float* mask, int B, int T, int nh, int d, bf16* out, float* lse,
                 const DropSite& drop) {
-  DTB_REQUIRE(d == AT_D, DTB_ERR_UNSUPPORTED, "tcgen05 attention: head_dim %d unsupported (64)", d);
+  DTB_REQUIRE(d == 32 || d == 64 || d == 128, DTB_ERR_UNSUPPORTED, "tcgen05 attention: head_dim %d unsupported (32, 64, 128)", d);
   DTB_REQUIRE((nh * d) % 8 == 0, DTB_ERR_BAD_ARG, "tcgen05 attention: hidden size must be a multiple of 8");
   const int H = nh * d;
   CUtensorMap tmQ, tmKV;
-  DTB_TRY(at_maps(qkv, B, T, H, &tmQ, &tmKV));
+  DTB_TRY(at_maps(qkv, B, T, 3 * H, &tmQ, &tmKV));
   AttnTcParams p;
   memset(&p, 0, sizeof(p));
   p.T = T; p.nh = nh; p.Kmask = T / 3;
   p.scale = 1.f / sqrtf((float)d);
   p.scale_log2 = 1.4426950408889634f * p.scale;
   p.mask = mask; p.out = out; p.lse = lse; p.drop = drop;
-  static bool attr = false;
-  if (!attr) {
-    DTB_CUDA(cudaFuncSetAttribute(attn_fwd_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_FWD_SMEM));
-    DTB_CUDA(cudaFuncSetAttribute(attn_fwd_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_FWD_SMEM));
-    attr = true;
-  }
   p.ntile_b = B;
-  // persistent: two CTAs per SM (registers / 256 TMEM columns each) walk the tile list; DTB_ATTN_PERSIST=0 -> one tile per CTA
-  static int persist = -1;
-  if (persist < 0) {
-    const char* e = getenv("DTB_ATTN_PERSIST");
-    persist = (e && e[0] == '0') ? 0 : 1;
-  }
   const long long ntiles = (long long)((T + 127) / 128) * nh * B;
   DTB_REQUIRE(ntiles < (1LL << 31), DTB_ERR_UNSUPPORTED, "tcgen05 attention: too many tiles");
-  const long long cap = persist ? 2LL * num_sms() : ntiles;
-  dim3 grid((unsigned)(ntiles < cap ? ntiles : cap));
   ProfScope prof(stream, PF_ATTN_FWD, 2.0 * B * nh * (double)T * T * d);
-  if (drop.state) DTB_LAUNCH(attn_fwd_tc_kernel<true>, grid, AT_THREADS, AT_FWD_SMEM, stream, tmQ, tmKV, p);
-  else DTB_LAUNCH(attn_fwd_tc_kernel<false>, grid, AT_THREADS, AT_FWD_SMEM, stream, tmQ, tmKV, p);
+  const bool dr = drop.state != nullptr;
+  if (d == 32) DTB_TRY(at_fwd_launch<32>(stream, tmQ, tmKV, p, ntiles, dr));
+  else if (d == 64) DTB_TRY(at_fwd_launch<64>(stream, tmQ, tmKV, p, ntiles, dr));
+  else DTB_TRY(at_fwd_launch<128>(stream, tmQ, tmKV, p, ntiles, dr));
   DTB_CHECK_LAUNCH();
   return DTB_OK;
 }
 
-constexpr int AT_DQ_SMEM = 1024 + 2 * AT_TILE128 + (AT_DQ_KST + AT_DQ_VST) * AT_TILE64 + 2 * AT_TILE128 + 256 + AT_MAX_CHUNKS * 4;
-constexpr int AT_DKV_SMEM = 1024 + 2 * AT_TILE128 + 4 * AT_TILE64 + 2 * AT_TILE128 + 256 + 2 * AT_MAX_T_BWD * 4;
-
-template <bool DROP, int CW>
-static void at_bwd_attrs() {
-  cudaFuncSetAttribute(attn_bwd_dq_tc_kernel<DROP, CW>, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_DQ_SMEM);
-  cudaFuncSetAttribute(attn_bwd_dkv_tc_kernel<DROP, CW>, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_DKV_SMEM);
-}
-template <bool DROP, int CW>
+template <int D, bool DROP, int CW>
 static void at_bwd_launch(dim3 grid, cudaStream_t stream, const CUtensorMap& tm128, const CUtensorMap& tm64, const CUtensorMap& tmDO128,
                           const CUtensorMap& tmDO64, const AttnTcParams& p) {
-  DTB_LAUNCH((attn_bwd_dq_tc_kernel<DROP, CW>), grid, 32 * (CW + 2), AT_DQ_SMEM, stream, tm128, tm64, tmDO128, p);
-  DTB_LAUNCH((attn_bwd_dkv_tc_kernel<DROP, CW>), grid, 32 * (CW + 2), AT_DKV_SMEM, stream, tm128, tm64, tmDO64, p);
+  static bool attr = false;
+  if (!attr) {
+    cudaFuncSetAttribute(attn_bwd_dq_tc_kernel<D, DROP, CW>, cudaFuncAttributeMaxDynamicSharedMemorySize, at_dq_smem<D>());
+    cudaFuncSetAttribute(attn_bwd_dkv_tc_kernel<D, DROP, CW>, cudaFuncAttributeMaxDynamicSharedMemorySize, at_dkv_smem<D>());
+    attr = true;
+  }
+  DTB_LAUNCH((attn_bwd_dq_tc_kernel<D, DROP, CW>), grid, 32 * (CW + 2), at_dq_smem<D>(), stream, tm128, tm64, tmDO128, p);
+  DTB_LAUNCH((attn_bwd_dkv_tc_kernel<D, DROP, CW>), grid, 32 * (CW + 2), at_dkv_smem<D>(), stream, tm128, tm64, tmDO64, p);
+}
+template <int D>
+static void at_bwd_dispatch(bool drop, bool w8, dim3 grid, cudaStream_t stream, const CUtensorMap& tm128, const CUtensorMap& tm64,
+                            const CUtensorMap& tmDO128, const CUtensorMap& tmDO64, const AttnTcParams& p) {
+  if (drop) { if (w8) at_bwd_launch<D, true, 8>(grid, stream, tm128, tm64, tmDO128, tmDO64, p); else at_bwd_launch<D, true, 4>(grid, stream, tm128, tm64, tmDO128, tmDO64, p); }
+  else      { if (w8) at_bwd_launch<D, false, 8>(grid, stream, tm128, tm64, tmDO128, tmDO64, p); else at_bwd_launch<D, false, 4>(grid, stream, tm128, tm64, tmDO128, tmDO64, p); }
 }
 // compute warps of the backward kernels: 4 (each thread walks both 32-column halves) or 8 (one half per warp); env DTB_ATTN_BWD_WARPS
 static int at_bwd_warps(bool dropout) {
@@ -895,28 +952,23 @@ static int at_bwd_warps(bool dropout) {
 
 int attn_bwd_tc(cudaStream_t stream, const bf16* qkv, const float* mask, const bf16* out, const bf16* dout, const float* lse, int B, int T,
                 int nh, int d, bf16* dqkv, float* delta, const DropSite& drop) {
-  DTB_REQUIRE(d == AT_D && T <= AT_MAX_T_BWD, DTB_ERR_UNSUPPORTED, "tcgen05 attention bwd: head_dim %d / T %d unsupported", d, T);
+  DTB_REQUIRE((d == 32 || d == 64 || d == 128) && T <= AT_MAX_T_BWD, DTB_ERR_UNSUPPORTED, "tcgen05 attention bwd: head_dim %d / T %d unsupported", d, T);
   const int H = nh * d;
   CUtensorMap tm128, tm64, tmDO128, tmDO64;
-  DTB_TRY(at_maps(qkv, B, T, H, &tm128, &tm64));
-  DTB_TRY(make_tmap3(&tmDO128, dout, (uint64_t)H, (uint64_t)T, (uint64_t)B, (uint64_t)H, (uint64_t)T * H, 64, 128));
-  DTB_TRY(make_tmap3(&tmDO64, dout, (uint64_t)H, (uint64_t)T, (uint64_t)B, (uint64_t)H, (uint64_t)T * H, 64, 64));
+  DTB_TRY(at_maps(qkv, B, T, 3 * H, &tm128, &tm64));
+  DTB_TRY(at_maps(dout, B, T, H, &tmDO128, &tmDO64));
   AttnTcParams p;
   memset(&p, 0, sizeof(p));
   p.T = T; p.nh = nh; p.Kmask = T / 3;
   p.scale = 1.f / sqrtf((float)d);
   p.scale_log2 = 1.4426950408889634f * p.scale;
   p.mask = mask; p.lse_in = lse; p.out_in = out; p.dout = dout; p.dqkv = dqkv; p.delta = delta; p.drop = drop;
-  static bool attr = false;
-  if (!attr) {
-    at_bwd_attrs<false, 4>(); at_bwd_attrs<true, 4>(); at_bwd_attrs<false, 8>(); at_bwd_attrs<true, 8>();
-    attr = true;
-  }
   dim3 grid((T + 127) / 128, nh, B);
   ProfScope prof(stream, PF_ATTN_BWD, 5.0 * B * nh * (double)T * T * d);
-  const bool w8 = at_bwd_warps(drop.state != nullptr) == 8;
-  if (drop.state) { if (w8) at_bwd_launch<true, 8>(grid, stream, tm128, tm64, tmDO128, tmDO64, p); else at_bwd_launch<true, 4>(grid, stream, tm128, tm64, tmDO128, tmDO64, p); }
-  else            { if (w8) at_bwd_launch<false, 8>(grid, stream, tm128, tm64, tmDO128, tmDO64, p); else at_bwd_launch<false, 4>(grid, stream, tm128, tm64, tmDO128, tmDO64, p); }
+  const bool dr = drop.state != nullptr, w8 = at_bwd_warps(dr) == 8;
+  if (d == 32) at_bwd_dispatch<32>(dr, w8, grid, stream, tm128, tm64, tmDO128, tmDO64, p);
+  else if (d == 64) at_bwd_dispatch<64>(dr, w8, grid, stream, tm128, tm64, tmDO128, tmDO64, p);
+  else at_bwd_dispatch<128>(dr, w8, grid, stream, tm128, tm64, tmDO128, tmDO64, p);
   DTB_CHECK_LAUNCH();
   return DTB_OK;
 }
