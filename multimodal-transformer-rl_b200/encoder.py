@@ -94,7 +94,12 @@ class MultimodalStateEncoder(nn.Module):
         self._flat_grad, self._staged, self._staged_version, self._ws = None, None, -1, {}
         for name, shp, off in zip(self._names, self._shapes, self._offsets):
             _set_nested(self, name, nn.Parameter(self._flat[off:off + torch.Size(shp).numel()].view(shp)))
+        self._plist = [self.get_parameter(n) for n in self._names]
         self.reset_parameters()
+
+    def _version_now(self) -> int:
+        """Staleness stamp of the fp32 master: flat buffer + every Parameter (see DecisionTransformer._version_now)."""
+        return self._flat._version + sum(p._version for p in self._plist)
 
     # parameter plumbing shared in spirit with DecisionTransformer (flat buffer + views)
     def _apply(self, fn, recurse=True):
@@ -157,9 +162,10 @@ class MultimodalStateEncoder(nn.Module):
         if self._staged is None or self._staged.device != self._flat.device:
             self._staged = torch.zeros(self._total, dtype=torch.bfloat16, device=self._flat.device)
             self._staged_version = -1
-        if self._staged_version != self._flat._version:
+        ver = self._version_now()
+        if self._staged_version != ver:
             _lib.check(_lib.load().dtb_encoder_stage_params(self._h, _lib.stream_ptr(), _lib.ptr(self._flat), _lib.ptr(self._staged)))
-            self._staged_version = self._flat._version
+            self._staged_version = ver
 
     def _workspace(self, N):
         ws = self._ws.get(N)

@@ -114,7 +114,14 @@ class DecisionTransformer(nn.Module):
                 _set_nested(self, name, nn.Parameter(view))
             else:
                 self.get_parameter(name).data = view
+        self._plist = [self.get_parameter(n) for n in self._names]
         self._staged_version = -1
+
+    def _version_now(self) -> int:
+        """Staleness stamp of the fp32 master.  After ``.to()`` / ``.cuda()`` torch rebinds every Parameter with ``param.data = view``,
+        which gives each of them its own version counter: an in-place update through a Parameter (``torch.optim.AdamW``) then no longer
+        bumps ``_flat._version``, so the stamp is the sum over the flat buffer AND every Parameter (all counters only ever grow)."""
+        return self._flat._version + sum(p._version for p in self._plist)
 
     def _apply(self, fn, recurse=True):
         # .to()/.cuda() rebuild every Parameter separately; gather them back into one flat buffer afterwards
@@ -130,17 +137,32 @@ class DecisionTransformer(nn.Module):
 
     @torch.no_grad()
     def reset_parameters(self):
-        """GPT-2 style init (HF:327-341): N(0, 0.02), c_proj scaled by 1/sqrt(2L), LayerNorm (1, 0), zero biases."""
+        """Initialisation of the upstream model the reference names (kzl decision-transformer): only the GPT-2 trunk (``transformer.*``)
+        gets the GPT-2 init (HF modeling_gpt2 ``_init_weights``: N(0, 0.02), c_proj scaled by 1/sqrt(2L), LayerNorm (1, 0), zero biases);
+        the embedding / prediction layers outside it keep torch's defaults — ``nn.Linear`` kaiming-uniform(a=sqrt 5) weights and
+        U(-1/sqrt(fan_in), 1/sqrt(fan_in)) biases, ``nn.Embedding`` N(0, 1), ``nn.LayerNorm`` (1, 0)."""
         L = self.config["n_layer"]
         for name, p in self.named_parameters():
-            if name.endswith(".bias"):
-                p.zero_()
-            elif "ln_" in name or "embed_ln" in name:
-                p.fill_(1.0)
-            elif name.endswith("c_proj.weight"):
-                p.normal_(0.0, 0.02 / (2 * L) ** 0.5)
+            if name.startswith("transformer."):
+                if name.endswith(".bias"):
+                    p.zero_()
+                elif ".ln_" in name:
+                    p.fill_(1.0)
+                elif name.endswith("c_proj.weight"):
+                    p.normal_(0.0, 0.02 / (2 * L) ** 0.5)
+                else:
+                    p.normal_(0.0, 0.02)
+            elif name == "embed_timestep.weight":
+                p.normal_(0.0, 1.0)
+            elif name.startswith("embed_ln."):
+                p.fill_(1.0) if name.endswith("weight") else p.zero_()
+            elif name.endswith(".weight"):
+                w = torch.empty(p.shape, dtype=torch.float32)
+                nn.init.kaiming_uniform_(w, a=5 ** 0.5)
+                p.copy_(w)
             else:
-                p.normal_(0.0, 0.02)
+                fan_in = self.get_parameter(name[:-4] + "weight").shape[1]
+                p.copy_(torch.empty(p.shape).uniform_(-1.0 / fan_in ** 0.5, 1.0 / fan_in ** 0.5))
 
     def load_state_dict(self, state_dict, strict=True, assign=False):
         """Accepts upstream (``transformer.*``) and HF (``encoder.*``) keys; wte / wpe / attn.bias buffers are ignored (A1)."""
@@ -194,9 +216,10 @@ class DecisionTransformer(nn.Module):
         if self._flat_bf16 is None or self._flat_bf16.device != self._flat.device:
             self._flat_bf16 = torch.empty(self._total, dtype=torch.bfloat16, device=self._flat.device)
             self._staged_version = -1
-        if self._staged_version != self._flat._version:
+        ver = self._version_now()
+        if self._staged_version != ver:
             _lib.check(_lib.load().dtb_dt_stage_params(self._h, _lib.stream_ptr(), _lib.ptr(self._flat), _lib.ptr(self._flat_bf16)))
-            self._staged_version = self._flat._version
+            self._staged_version = ver
 
     def restage(self):
         """Force a refresh of the bf16 shadow (call after writing parameters through an aliasing view torch cannot track)."""

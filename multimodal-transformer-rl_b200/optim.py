@@ -63,7 +63,24 @@ class FusedClipAdamW:
         return self._ensure_state()["scratch"][3]
 
     def zero_grad(self, set_to_none: bool = False):
-        """The fused backward overwrites the flat gradient buffers on every step; nothing to clear."""
+        """Point every ``param.grad`` at its view of the module's flat gradient buffer and clear the buffer.
+
+        The fused ``loss_and_backward`` overwrites the flat buffers and needs none of this; the autograd bridge (``model(...)`` +
+        ``loss.backward()``, ``SequenceTrainer(loss_fn=...)``) ACCUMULATES into ``param.grad``: with the views attached and zeroed here
+        the gradients land exactly where ``step()`` reads them.  ``set_to_none`` is ignored on purpose (a ``None`` grad would make
+        autograd install tensors outside the flat buffer)."""
+        for mod in self.modules:
+            mod.attach_grads().zero_()
+
+    def _check_grads_alias(self):
+        """step() reads only ``mod.flat_grads``: a ``param.grad`` that lives elsewhere (autograd installed it because it was None) would
+        be silently ignored — refuse instead."""
+        for mod in self.modules:
+            base = mod.flat_grads.data_ptr()
+            for p, off in zip(mod._plist, mod._offsets):
+                if p.grad is not None and p.grad.data_ptr() != base + 4 * off:
+                    raise RuntimeError("FusedClipAdamW.step(): a param.grad does not alias the module's flat gradient buffer; call "
+                                       "optimizer.zero_grad() (or module.attach_grads()) before loss.backward()")
 
     def state_dict(self):
         st = self._ensure_state()
@@ -82,6 +99,7 @@ class FusedClipAdamW:
     def step(self):
         lib = _lib.load()
         st = self._ensure_state()
+        self._check_grads_alias()
         n = len(self.modules)
         segs = (_lib.AdamwSegment * n)()
         for i, mod in enumerate(self.modules):
@@ -98,4 +116,4 @@ class FusedClipAdamW:
         _lib.check(lib.dtb_clip_adamw_step(_lib.stream_ptr(), n, segs, C.byref(hp), _lib.ptr(st["step"]), _lib.ptr(st["scratch"])))
         for i, mod in enumerate(self.modules):
             # the library wrote the fp32 master behind torch's back: shadows it rewrote are current, the others must be re-staged
-            mod._staged_version = mod.flat_params._version if segs[i].params_bf16 else -1
+            mod._staged_version = mod._version_now() if segs[i].params_bf16 else -1

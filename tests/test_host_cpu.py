@@ -231,3 +231,60 @@ def test_mfcc_host_geometry_and_no_fallback():
         audio.wav_to_mfcc(16000, torch.zeros(16000, dtype=torch.int16), device="cpu")
     with pytest.raises(_lib.DtbError):
         audio.resize_normalize(torch.zeros(50, 13, dtype=torch.float64))
+
+
+def test_parameter_updates_after_to_are_seen_by_the_staleness_stamp():
+    """``model.to(dev)`` rebinds every Parameter with ``param.data = view`` (own version counters), so an in-place
+    update through the Parameters (torch.optim.AdamW) no longer bumps ``_flat._version``; the bf16 re-staging must still notice it."""
+    from mtrl_b200.encoder import MultimodalStateEncoder
+    from mtrl_b200.model import DecisionTransformer
+
+    dt = DecisionTransformer(11, 3, 64, max_length=5, max_ep_len=50, n_layer=1, n_head=1, device="cpu")
+    enc = MultimodalStateEncoder((1, 36, 36), (1, 36, 36), "small", "concat", device="cpu")
+    for mod in (dt, enc):
+        mod = mod.to("cpu")
+        before_flat, before = mod._flat.clone(), mod._version_now()
+        opt = torch.optim.AdamW(mod.parameters(), lr=1e-2)
+        for p in mod.parameters():
+            p.grad = torch.ones_like(p)
+        opt.step()
+        assert not torch.equal(mod._flat, before_flat)  # the fp32 master did change (the views alias the new flat buffer)
+        assert mod._version_now() != before              # ... and the stamp that drives the bf16 re-staging sees it
+        # every Parameter is still a view of the flat buffer
+        assert all(p.data_ptr() == mod._flat.data_ptr() + 4 * off for p, off in zip(mod._plist, mod._offsets))
+
+
+def test_fused_optimizer_zero_grad_attaches_and_clears_flat_views():
+    """ADVICE r1 (medium): zero_grad() must leave every param.grad as a zeroed view of flat_grads (autograd then accumulates where step() reads);
+    a grad living elsewhere is refused by step()."""
+    from mtrl_b200.model import DecisionTransformer
+    from mtrl_b200.optim import FusedClipAdamW
+
+    dt = DecisionTransformer(11, 3, 64, max_length=5, max_ep_len=50, n_layer=1, n_head=1, device="cpu")
+    opt = FusedClipAdamW([dt])
+    dt.flat_grads.fill_(3.0)
+    opt.zero_grad()
+    assert float(dt.flat_grads.abs().sum()) == 0.0
+    for p, off in zip(dt._plist, dt._offsets):
+        assert p.grad is not None and p.grad.data_ptr() == dt.flat_grads.data_ptr() + 4 * off
+    opt._check_grads_alias()
+    dt._plist[3].grad = torch.zeros_like(dt._plist[3])  # what autograd does when .grad was None
+    with pytest.raises(RuntimeError):
+        opt._check_grads_alias()
+
+
+def test_reset_parameters_follows_upstream_init_split():
+    """GPT-2 init only inside ``transformer.*``; embeddings / heads keep torch's nn.Linear / nn.Embedding defaults."""
+    from mtrl_b200.model import DecisionTransformer
+
+    torch.manual_seed(0)
+    dt = DecisionTransformer(11, 3, 128, max_length=5, max_ep_len=500, n_layer=2, n_head=1, device="cpu")
+    sd = dt.state_dict()
+    assert abs(float(sd["embed_timestep.weight"].std()) - 1.0) < 0.05                      # nn.Embedding: N(0, 1)
+    bound = 1.0 / 11 ** 0.5
+    assert float(sd["embed_state.weight"].abs().max()) <= bound + 1e-6                     # kaiming_uniform(a = sqrt 5): U(+-1/sqrt(fan_in))
+    assert float(sd["embed_state.bias"].abs().max()) <= bound + 1e-6 and float(sd["embed_state.bias"].abs().sum()) > 0
+    assert abs(float(sd["transformer.h.0.attn.c_attn.weight"].std()) - 0.02) < 2e-3        # GPT-2: N(0, 0.02)
+    assert abs(float(sd["transformer.h.1.mlp.c_proj.weight"].std()) - 0.02 / 2.0) < 2e-3   # scaled by 1 / sqrt(2 L)
+    assert float(sd["transformer.h.0.mlp.c_fc.bias"].abs().sum()) == 0.0
+    assert torch.equal(sd["embed_ln.weight"], torch.ones(128)) and torch.equal(sd["transformer.ln_f.weight"], torch.ones(128))

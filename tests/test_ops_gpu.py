@@ -70,7 +70,8 @@ def _attn_ref(qkv, mask, nh):
 
 @pytest.mark.parametrize("B,K,nh,d,pad", [(4, 20, 1, 128, True), (3, 30, 1, 128, False), (2, 50, 8, 32, True), (2, 200, 12, 64, True),
                                           (5, 7, 2, 64, True), (3, 64, 4, 64, True), (2, 43, 2, 64, False), (1, 1, 1, 64, False),
-                                          (2, 86, 3, 64, True)])
+                                          (2, 86, 3, 64, True), (2, 100, 2, 128, True), (1, 43, 1, 128, False), (2, 150, 3, 32, True),
+                                          (3, 1, 2, 32, False), (2, 60, 1, 32, True), (1, 300, 2, 128, True)])
 def test_attention_fwd_bwd(cuda_device, B, K, nh, d, pad):
     from mtrl_b200 import _lib
 

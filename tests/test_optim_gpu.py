@@ -94,3 +94,57 @@ def test_train_step_with_fused_optimizer_tracks_oracle_trainer(cuda_device):
         worst = max(worst, e)
         assert e <= 0.1, (n, e)
     print("worst parameter rel-diff after 3 fused steps:", worst)
+
+
+def test_to_device_then_torch_adamw_restages_the_bf16_shadow(cuda_device):
+    """the canonical upstream flow ``model = model.to(device)``; ``torch.optim.AdamW(model.parameters())``; step — the
+    kernels must see the updated weights (bf16 shadow re-staged, forward output changes)."""
+    from mtrl_b200.model import DecisionTransformer
+
+    torch.manual_seed(0)
+    model = DecisionTransformer(11, 3, 128, max_length=20, max_ep_len=1000, n_layer=2, n_head=1, resid_pdrop=0.0, attn_pdrop=0.0, device="cpu")
+    model = model.to(cuda_device)
+    model.eval()
+    s, a, r, t, m = (x.to(cuda_device) for x in make_inputs(4, 20, 11, 3, 1000, seed=2))
+    _, ap0, _ = model(s, a, None, r, t, m)
+    shadow0 = model._flat_bf16.clone()
+    opt = torch.optim.AdamW(model.parameters(), lr=1e-2)
+    loss = (model(s, a, None, r, t, m)[1] ** 2).mean()
+    loss.backward()
+    opt.step()
+    _, ap1, _ = model(s, a, None, r, t, m)
+    torch.cuda.synchronize()
+    assert not torch.equal(model._flat_bf16, shadow0)
+    assert not torch.equal(ap0, ap1)
+    assert torch.equal(model._flat_bf16, model._flat.to(torch.bfloat16))
+
+
+def test_loss_fn_path_with_fused_optimizer_tracks_torch_optimizer(cuda_device):
+    """SequenceTrainer(loss_fn=...) + FusedClipAdamW — autograd must accumulate into the flat views the optimizer reads,
+    cleared every step (same loss trajectory as clip_grad_norm_ + torch.optim.AdamW on an identical model)."""
+    from mtrl_b200.optim import FusedClipAdamW
+    from mtrl_b200.trainer import SequenceTrainer
+    from util import rel_err
+
+    dev = cuda_device
+    _, m_fused, K = build_pair("c1", dev, seed=21)
+    _, m_torch, _ = build_pair("c1", dev, seed=21)
+    batches = [make_inputs(16, K, 11, 3, 1000, seed=300 + i) for i in range(5)]
+
+    def mk():
+        it = iter(batches)
+
+        def get_batch(bs):
+            s, a, r, t, m = next(it)
+            rtg = torch.cat([r, r[:, -1:]], dim=1)
+            z = torch.zeros(s.shape[0], K, 1)
+            return tuple(x.to(dev) for x in (s, a, z, z, rtg, t, m))
+        return get_batch
+
+    loss_fn = lambda s_hat, a_hat, r_hat, s, a, r: torch.mean((a_hat - a) ** 2)  # noqa: E731
+    tr_f = SequenceTrainer(m_fused, FusedClipAdamW([m_fused], lr=1e-3, weight_decay=1e-4), 16, mk(), loss_fn=loss_fn)
+    tr_t = SequenceTrainer(m_torch, torch.optim.AdamW(m_torch.parameters(), lr=1e-3, weight_decay=1e-4), 16, mk(), loss_fn=loss_fn)
+    for i in range(5):
+        lf, lt = tr_f.train_step(), tr_t.train_step()
+        assert abs(lf - lt) <= 2e-3 * abs(lt), (i, lf, lt)
+    assert rel_err(m_fused.flat_params, m_torch.flat_params) < 1e-4
