@@ -79,6 +79,12 @@ typedef struct {
 
 int dtb_gemm_bf16(void* stream, const void* A, int lda, int a_mn_major, const void* B, int ldb, int b_mn_major, int M, int N, int K,
                   const dtb_gemm_epilogue* ep, int split_k, int bn_override);
+/* GEMM with LayerNorm fused behind the epilogue (replaces c_proj + residual add + the next nn.LayerNorm: HF:217-218 + :303, HF:236-237 +
+ * :272 / :450): out_f32 (if given) receives the fp32 rows v = epilogue(acc); ln_out bf16 [M, ld_ln] = (v - mean) * rstd * gamma + beta;
+ * mean / rstd fp32 [M] (may be NULL).  Needs N <= 256, N % 64 == 0 (one CTA owns whole rows), no split-K. */
+int dtb_gemm_bf16_ln(void* stream, const void* A, int lda, int a_mn_major, const void* B, int ldb, int b_mn_major, int M, int N, int K,
+                     const dtb_gemm_epilogue* ep, const float* ln_gamma, const float* ln_beta, float ln_eps, void* ln_out_bf16, int ld_ln,
+                     float* ln_mean, float* ln_rstd);
 
 /* ---- LayerNorm over the fp32 residual stream (HF:272 ln_1, HF:303 ln_2, HF:450 ln_f, HF:628 embed_ln) -------------
  * fwd: x fp32 [M,H] -> y bf16 [M,H]; mean/rstd fp32 [M] saved for backward (may be NULL).
@@ -89,6 +95,11 @@ int dtb_layernorm_fwd(void* stream, const float* x, const float* gamma, const fl
 size_t dtb_layernorm_bwd_scratch_floats(int H);
 int dtb_layernorm_bwd(void* stream, const void* dy_bf16, const float* x, const float* mean, const float* rstd, const float* gamma,
                       const float* dres, int M, int H, float* dx_f32, void* dx_bf16, float* dgamma, float* dbeta, float* scratch);
+/* Same, plus dcolsum fp32 [H] = column sums of the dx values handed on as dx_bf16 (before bf16 rounding): the bias gradient of the
+ * Linear / Conv1D whose output gradient dx is (HF:217 attn.c_proj, HF:236 mlp.c_proj), reduced inside the same launch. */
+int dtb_layernorm_bwd_colsum(void* stream, const void* dy_bf16, const float* x, const float* mean, const float* rstd, const float* gamma,
+                             const float* dres, int M, int H, float* dx_f32, void* dx_bf16, float* dgamma, float* dbeta, float* dcolsum,
+                             float* scratch);
 
 /* ---- fused causal attention with the [B,K] padding mask expanded by index (HF:47-65, 408-414, 631-635) -------------
  * qkv bf16 [B,T,3H] (q|k|v, head h at h*d), mask fp32 [B,T/3] or NULL; allowed(i,j) = j<=i && mask[b,j/3]>0.

@@ -202,6 +202,20 @@ def gemm_bf16(A, B, M, N, K, *, a_mn_major=False, b_mn_major=False, bias=None, r
                                int(b_mn_major), M, N, K, C.byref(ep), split_k, bn))
 
 
+def gemm_bf16_ln(A, B, M, N, K, gamma, beta, eps, ln_out, *, b_mn_major=False, bias=None, residual=None, out_f32=None, mean=None, rstd=None):
+    """GEMM + bias + residual + fused LayerNorm epilogue (dtb_gemm_bf16_ln)."""
+    ep = GemmEpilogue()
+    ep.bias = ptr(bias).value
+    ep.residual = ptr(residual).value
+    ep.ldr = residual.stride(0) if residual is not None else 0
+    ep.out_f32 = ptr(out_f32).value
+    ep.ldo_f = out_f32.stride(0) if out_f32 is not None else 0
+    ep.alpha = 1.0
+    check(load().dtb_gemm_bf16_ln(stream_ptr(), ptr(A), C.c_int(A.stride(0)), 0, ptr(B), C.c_int(B.stride(0)), int(b_mn_major), M, N, K,
+                                  C.byref(ep), ptr(gamma), ptr(beta), C.c_float(eps), ptr(ln_out), C.c_int(ln_out.stride(0)), ptr(mean),
+                                  ptr(rstd)))
+
+
 # ---- thin op wrappers (used by tests and by the host-side model) ------------------------------------------------------
 def _f32p(t):
     return C.c_void_p(0 if t is None else t.data_ptr())
@@ -212,7 +226,7 @@ def layernorm_fwd(x, gamma, beta, eps, y, mean=None, rstd=None):
     check(load().dtb_layernorm_fwd(stream_ptr(), ptr(x), ptr(gamma), ptr(beta), M, H, C.c_float(eps), ptr(y), ptr(mean), ptr(rstd)))
 
 
-def layernorm_bwd(dy, x, mean, rstd, gamma, dres, dx_f32, dx_bf16, dgamma, dbeta, scratch=None):
+def layernorm_bwd(dy, x, mean, rstd, gamma, dres, dx_f32, dx_bf16, dgamma, dbeta, scratch=None, dcolsum=None):
     import torch
 
     M, H = x.shape
@@ -220,6 +234,10 @@ def layernorm_bwd(dy, x, mean, rstd, gamma, dres, dx_f32, dx_bf16, dgamma, dbeta
     lib.dtb_layernorm_bwd_scratch_floats.restype = C.c_size_t
     if scratch is None:
         scratch = torch.empty(lib.dtb_layernorm_bwd_scratch_floats(H), device=x.device, dtype=torch.float32)
+    if dcolsum is not None:
+        check(lib.dtb_layernorm_bwd_colsum(stream_ptr(), ptr(dy), ptr(x), ptr(mean), ptr(rstd), ptr(gamma), ptr(dres), M, H, ptr(dx_f32),
+                                           ptr(dx_bf16), ptr(dgamma), ptr(dbeta), ptr(dcolsum), ptr(scratch)))
+        return
     check(lib.dtb_layernorm_bwd(stream_ptr(), ptr(dy), ptr(x), ptr(mean), ptr(rstd), ptr(gamma), ptr(dres), M, H, ptr(dx_f32),
                                 ptr(dx_bf16), ptr(dgamma), ptr(dbeta), ptr(scratch)))
 

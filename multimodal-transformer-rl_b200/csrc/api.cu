@@ -41,8 +41,12 @@ int dtb_gemm_bf16(void* stream, const void* A, int lda, int a_mn_major, const vo
   if (split) {
     DTB_REQUIRE(e->partial && e->out_f32, DTB_ERR_BAD_ARG, "dtb_gemm_bf16: split-K needs partial and out_f32");
     ep.partial = e->partial;
+    if (!e->accumulate && ep.alpha == 1.f) {  // plain store: the last-arriving CTA of every tile reduces the slices inside the GEMM
+      ep.sk_out = e->out_f32;
+      ep.sk_ldo = e->ldo_f;
+    }
     int rc = gemm_bf16(st, (const bf16*)A, lda, a_mn_major, (const bf16*)B, ldb, b_mn_major, M, N, K, ep, split_k, bn_override);
-    if (rc < 0) return rc;
+    if (rc <= 0) return rc;
     return splitk_reduce(st, e->partial, rc, M, N, e->out_f32, e->ldo_f, e->accumulate, ep.alpha);
   }
   ep.bias = e->bias;
@@ -61,6 +65,30 @@ int dtb_gemm_bf16(void* stream, const void* A, int lda, int a_mn_major, const vo
   return rc < 0 ? rc : DTB_OK;
 }
 
+int dtb_gemm_bf16_ln(void* stream, const void* A, int lda, int a_mn_major, const void* B, int ldb, int b_mn_major, int M, int N, int K,
+                     const dtb_gemm_epilogue* e, const float* ln_gamma, const float* ln_beta, float ln_eps, void* ln_out_bf16, int ld_ln,
+                     float* ln_mean, float* ln_rstd) {
+  DTB_REQUIRE(A && B && e && ln_gamma && ln_beta && ln_out_bf16, DTB_ERR_BAD_ARG, "dtb_gemm_bf16_ln: null operand");
+  DTB_REQUIRE(N <= 256 && N % 64 == 0, DTB_ERR_UNSUPPORTED, "dtb_gemm_bf16_ln: N = %d unsupported (multiple of 64, <= 256)", N);
+  DTB_TRY(require_sm100());
+  GemmEpilogue ep;
+  memset(&ep, 0, sizeof(ep));
+  ep.alpha = e->alpha == 0.f ? 1.f : e->alpha;
+  ep.bias = e->bias;
+  ep.residual = e->residual;
+  ep.ldr = e->ldr;
+  ep.aux = (const bf16*)e->aux;
+  ep.ldaux = e->ldaux;
+  ep.act = e->act;
+  ep.dact = e->dact;
+  ep.out_f32 = e->out_f32;
+  ep.ldo_f = e->ldo_f;
+  ep.ln_gamma = ln_gamma; ep.ln_beta = ln_beta; ep.ln_eps = ln_eps;
+  ep.ln_out = (bf16*)ln_out_bf16; ep.ld_ln = ld_ln; ep.ln_mean = ln_mean; ep.ln_rstd = ln_rstd;
+  int rc = gemm_bf16(static_cast<cudaStream_t>(stream), (const bf16*)A, lda, a_mn_major, (const bf16*)B, ldb, b_mn_major, M, N, K, ep, 1, N);
+  return rc < 0 ? rc : DTB_OK;
+}
+
 int dtb_layernorm_fwd(void* stream, const float* x, const float* gamma, const float* beta, int M, int H, float eps, void* y, float* mean,
                       float* rstd) {
   DTB_REQUIRE(x && gamma && beta && y, DTB_ERR_BAD_ARG, "dtb_layernorm_fwd: null pointer");
@@ -71,6 +99,13 @@ int dtb_layernorm_bwd(void* stream, const void* dy, const float* x, const float*
                       const float* dres, int M, int H, float* dx_f32, void* dx_bf16, float* dgamma, float* dbeta, float* scratch) {
   DTB_REQUIRE(dy && x && mean && rstd && gamma && dgamma && dbeta && scratch, DTB_ERR_BAD_ARG, "dtb_layernorm_bwd: null pointer");
   return ln_bwd((cudaStream_t)stream, (const bf16*)dy, x, mean, rstd, gamma, dres, M, H, dx_f32, (bf16*)dx_bf16, dgamma, dbeta, scratch);
+}
+int dtb_layernorm_bwd_colsum(void* stream, const void* dy, const float* x, const float* mean, const float* rstd, const float* gamma,
+                             const float* dres, int M, int H, float* dx_f32, void* dx_bf16, float* dgamma, float* dbeta, float* dcolsum,
+                             float* scratch) {
+  DTB_REQUIRE(dy && x && mean && rstd && gamma && dgamma && dbeta && dcolsum && scratch, DTB_ERR_BAD_ARG, "dtb_layernorm_bwd_colsum: null pointer");
+  return ln_bwd((cudaStream_t)stream, (const bf16*)dy, x, mean, rstd, gamma, dres, M, H, dx_f32, (bf16*)dx_bf16, dgamma, dbeta, scratch,
+                drop_none(), dcolsum);
 }
 int dtb_attention_fwd(void* stream, const void* qkv, const float* mask, int B, int T, int n_head, int head_dim, void* out, float* lse) {
   DTB_REQUIRE(qkv && out && lse, DTB_ERR_BAD_ARG, "dtb_attention_fwd: null pointer");

@@ -34,6 +34,10 @@ struct EmbedFwdArgs {
   int P8;
   int u_states;  // 1: U also carries the states (small-state path)
   DropSite drop; // embd dropout on the LayerNorm output (GPT2Model.drop; idx = row * H + col)
+  // optional: ln_1 of the first block fused behind embed_ln + dropout (the warp still holds the row): h1 = LN(x) in bf16 + its statistics
+  const float* ln1_gamma; const float* ln1_beta;
+  bf16* h1;
+  float* mean1; float* rstd1;
 };
 
 __global__ void __launch_bounds__(256) embed_fwd_kernel(const EmbedFwdArgs a) {
@@ -165,6 +169,40 @@ __global__ void __launch_bounds__(256) embed_fwd_kernel(const EmbedFwdArgs a) {
             o.z = drop_apply(o.z, k, 2u, a.drop.thr, a.drop.scale); o.w = drop_apply(o.w, k, 3u, a.drop.thr, a.drop.scale);
           }
           *reinterpret_cast<float4*>(a.x + row * H + c) = o;
+          v[i] = o;
+        }
+      }
+      if (a.h1) {  // ln_1 of block 0 (HF:272) on the row just produced: same two-pass statistics as ln_fwd_kernel
+        float s2 = 0.f;
+#pragma unroll
+        for (int i = 0; i < EMB_MAX_VEC; ++i) {
+          const int c = i * 128 + lane * 4;
+          if (c < H) s2 += v[i].x + v[i].y + v[i].z + v[i].w;
+        }
+        const float m2 = warp_sum(s2) / H;
+        float q2 = 0.f;
+#pragma unroll
+        for (int i = 0; i < EMB_MAX_VEC; ++i) {
+          const int c = i * 128 + lane * 4;
+          if (c < H) {
+            const float d0 = v[i].x - m2, d1 = v[i].y - m2, d2 = v[i].z - m2, d3 = v[i].w - m2;
+            q2 += d0 * d0 + d1 * d1 + d2 * d2 + d3 * d3;
+          }
+        }
+        const float r2 = rsqrtf(warp_sum(q2) / H + a.eps);
+        if (lane == 0) {
+          if (a.mean1) a.mean1[row] = m2;
+          if (a.rstd1) a.rstd1[row] = r2;
+        }
+#pragma unroll
+        for (int i = 0; i < EMB_MAX_VEC; ++i) {
+          const int c = i * 128 + lane * 4;
+          if (c < H) {
+            const float4 g = ldg_f4(a.ln1_gamma + c), b = ldg_f4(a.ln1_beta + c);
+            *reinterpret_cast<uint2*>(a.h1 + row * H + c) =
+                make_uint2(pack_bf16x2((v[i].x - m2) * r2 * g.x + b.x, (v[i].y - m2) * r2 * g.y + b.y),
+                           pack_bf16x2((v[i].z - m2) * r2 * g.z + b.z, (v[i].w - m2) * r2 * g.w + b.w));
+          }
         }
       }
     }
@@ -174,14 +212,15 @@ __global__ void __launch_bounds__(256) embed_fwd_kernel(const EmbedFwdArgs a) {
 int embed_fwd(cudaStream_t stream, const float* states, const float* state_proj, const float* actions, const float* rtg,
               const long long* timesteps, const float* table, const float* wR, const float* bR, const float* Ws, const float* bs,
               const float* Wa, const float* ba, const float* gamma, const float* beta, int BK, int sd, int ad, int H, int E, float eps,
-              float* x, float* pre, float* mean, float* rstd, bf16* U, int P8, int u_states, const DropSite& drop) {
+              float* x, float* pre, float* mean, float* rstd, bf16* U, int P8, int u_states, const DropSite& drop, const float* ln1_gamma,
+              const float* ln1_beta, bf16* h1, float* mean1, float* rstd1) {
   DTB_REQUIRE(H % 4 == 0 && H <= EMB_MAX_VEC * 128, DTB_ERR_UNSUPPORTED, "embed: hidden size %d unsupported (multiple of 4, <= 1024)", H);
   DTB_REQUIRE(ad >= 1 && ad <= 64, DTB_ERR_UNSUPPORTED, "embed: act_dim %d unsupported (1..64)", ad);
   DTB_REQUIRE((states != nullptr) != (state_proj != nullptr), DTB_ERR_BAD_ARG, "embed: exactly one of states / state_proj must be given");
   DTB_REQUIRE(states == nullptr || sd <= 64, DTB_ERR_UNSUPPORTED, "embed: fused state projection needs state_dim <= 64 (got %d)", sd);
   if (BK == 0) return DTB_OK;
   EmbedFwdArgs a{states, state_proj, actions, rtg, timesteps, table, wR, bR, Ws, bs, Wa, ba, gamma, beta,
-                 BK, sd, ad, H, E, eps, x, pre, mean, rstd, U, P8, u_states, drop};
+                 BK, sd, ad, H, E, eps, x, pre, mean, rstd, U, P8, u_states, drop, ln1_gamma, ln1_beta, h1, mean1, rstd1};
   const size_t smem = ((size_t)(states ? sd : 0) + ad + 6) * H * sizeof(float);
   DTB_REQUIRE(smem <= 200 * 1024, DTB_ERR_UNSUPPORTED, "embed: (state_dim + act_dim + 6) * hidden too large for shared memory");
   static bool attr_set = false;
@@ -200,31 +239,60 @@ int embed_fwd(cudaStream_t stream, const float* states, const float* state_proj,
 
 // ---- backward pieces -----------------------------------------------------------------------------------------------
 // d_pre: bf16 [BK, 3H] (row t = timestep, columns R | s | a) = gradient w.r.t. the pre-LN embeddings (from ln_bwd).
-// d_table[timesteps[t]] += d_pre_R + d_pre_s + d_pre_a   (fp32 atomics: rows collide across trajectories)
+// d_table[e] = sum over the timesteps t with timesteps[t] == e, in ascending t, of d_pre_R + d_pre_s + d_pre_a.
+// One warp per table row: it scans the timestep vector (32 indices per coalesced load, matches found by ballot) and adds the matching
+// rows in index order — no atomics, so the embedding gradient is bit-reproducible run to run (SURVEY.md §8b "Determinism"), and every
+// table row is written exactly once (rows nobody gathered get zeros: no memset pass).
+constexpr int TE_MAX_PAIRS = 16;  // H <= 1024: 16 bf16 pairs per lane
 __global__ void __launch_bounds__(256) embed_te_scatter_kernel(const bf16* __restrict__ d_pre, const long long* __restrict__ timesteps,
                                                                int BK, int H, int E, float* __restrict__ d_table) {
   pdl_trigger();
   pdl_wait();
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
-  for (int t = blockIdx.x * nwarp + warp; t < BK; t += gridDim.x * nwarp) {
-    long long ts = timesteps[t];
-    ts = ts < 0 ? 0 : (ts >= E ? E - 1 : ts);
-    const bf16* p = d_pre + (size_t)t * 3 * H;
-    float* dst = d_table + (size_t)ts * H;
-    for (int c = lane * 2; c < H; c += 64) {
-      const float2 r = unpack_bf16x2(*reinterpret_cast<const uint32_t*>(p + c));
-      const float2 s = unpack_bf16x2(*reinterpret_cast<const uint32_t*>(p + H + c));
-      const float2 a = unpack_bf16x2(*reinterpret_cast<const uint32_t*>(p + 2 * H + c));
-      atomicAdd(dst + c, r.x + s.x + a.x);
-      atomicAdd(dst + c + 1, r.y + s.y + a.y);
+  for (int e = blockIdx.x * nwarp + warp; e < E; e += gridDim.x * nwarp) {
+    float2 acc[TE_MAX_PAIRS];
+#pragma unroll
+    for (int i = 0; i < TE_MAX_PAIRS; ++i) acc[i] = make_float2(0.f, 0.f);
+    for (int t0 = 0; t0 < BK; t0 += 32) {
+      long long ts = -1;
+      if (t0 + lane < BK) {
+        ts = timesteps[t0 + lane];
+        ts = ts < 0 ? 0 : (ts >= E ? E - 1 : ts);  // same clamp as the forward gather
+      }
+      unsigned int m = __ballot_sync(0xffffffffu, ts == (long long)e);
+      while (m) {
+        const int j = __ffs(m) - 1;
+        m &= m - 1;
+        const bf16* p = d_pre + (size_t)(t0 + j) * 3 * H;
+#pragma unroll
+        for (int i = 0; i < TE_MAX_PAIRS; ++i) {
+          const int c = i * 64 + lane * 2;
+          if (c < H) {
+            const float2 r = unpack_bf16x2(__ldg(reinterpret_cast<const uint32_t*>(p + c)));
+            const float2 s = unpack_bf16x2(__ldg(reinterpret_cast<const uint32_t*>(p + H + c)));
+            const float2 a = unpack_bf16x2(__ldg(reinterpret_cast<const uint32_t*>(p + 2 * H + c)));
+            acc[i].x += r.x + s.x + a.x;
+            acc[i].y += r.y + s.y + a.y;
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < TE_MAX_PAIRS; ++i) {
+      const int c = i * 64 + lane * 2;
+      if (c < H) *reinterpret_cast<float2*>(d_table + (size_t)e * H + c) = acc[i];
     }
   }
 }
 
 int embed_te_scatter(cudaStream_t stream, const bf16* d_pre, const long long* timesteps, int BK, int H, int E, float* d_table) {
-  if (BK == 0) return DTB_OK;
-  int blocks = (BK + 7) / 8;
-  if (blocks > num_sms() * 4) blocks = num_sms() * 4;
+  DTB_REQUIRE(H % 2 == 0 && H <= 64 * TE_MAX_PAIRS, DTB_ERR_UNSUPPORTED, "embed_te_scatter: hidden size %d unsupported", H);
+  if (BK == 0) {
+    DTB_CUDA(cudaMemsetAsync(d_table, 0, (size_t)E * H * sizeof(float), stream));
+    return DTB_OK;
+  }
+  int blocks = (E + 7) / 8;
+  if (blocks > num_sms() * 8) blocks = num_sms() * 8;
   DTB_LAUNCH(embed_te_scatter_kernel, blocks, 256, 0, stream, d_pre, timesteps, BK, H, E, d_table);
   DTB_CHECK_LAUNCH();
   return DTB_OK;

@@ -96,6 +96,35 @@ int make_tmap3(CUtensorMap* out, const void* ptr, uint64_t d0, uint64_t d1, uint
 
 static bool g_attr_set = false;
 
+// Ticket counters of the in-kernel split-K reduction (gemm_splitk_finish).  Zero at load, and every kernel leaves the counters it used
+// at zero.  Launches take consecutive slices of the ring, so GEMMs that run concurrently on different streams (data-gradient chain,
+// weight-gradient side streams of the trunk and of both towers) never share a counter; a slice is reused only SK_RING / (counters per
+// launch) launches later.
+constexpr unsigned int SK_RING = 1u << 18;
+__device__ unsigned int g_sk_counters[SK_RING];
+static unsigned int* g_sk_base = nullptr;
+static unsigned int g_sk_cursor = 0;
+static std::mutex g_sk_mutex;
+
+int ticket_counters_take(unsigned int need, unsigned int** out) {
+  *out = nullptr;
+  if (need == 0 || need > SK_RING / 8) return DTB_OK;  // too many tiles: the caller falls back to the separate reduction kernel
+  std::lock_guard<std::mutex> g(g_sk_mutex);
+  if (!g_sk_base) DTB_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&g_sk_base), g_sk_counters));
+  if (g_sk_cursor + need > SK_RING) g_sk_cursor = 0;
+  *out = g_sk_base + g_sk_cursor;
+  g_sk_cursor += need;
+  return DTB_OK;
+}
+static bool sk_inkernel_enabled() {
+  static int off = -1;
+  if (off < 0) {
+    const char* e = getenv("DTB_SPLITK_SEPARATE");
+    off = (e && e[0] == '1') ? 1 : 0;
+  }
+  return !off;
+}
+
 size_t gemm_splitk_workspace_bytes(int M, int N, int K) {
   // upper bound used by callers that pre-size the workspace: split <= 32
   (void)K;
@@ -181,6 +210,19 @@ int gemm_bf16(cudaStream_t stream, const bf16* A, int lda, int a_mn_major, const
   p.ep = ep_in;
   if (p.ep.alpha == 0.f) p.ep.alpha = 1.f;
   if (p.split_k > 1) DTB_REQUIRE(p.ep.partial != nullptr, DTB_ERR_BAD_ARG, "gemm: split-K needs a partial workspace");
+  if (p.ep.ln_out) {
+    DTB_REQUIRE(!pair && p.BN == N && N % 32 == 0 && N <= GEMM_MAX_BN && p.split_k == 1 && !p.ep.partial && p.ep.ln_gamma && p.ep.ln_beta,
+                DTB_ERR_BAD_ARG, "gemm: fused LayerNorm needs the single-CTA kernel with BN == N (N %% 32 == 0, <= 256) and no split-K");
+    DTB_REQUIRE(p.ep.ld_ln % 8 == 0 && (reinterpret_cast<uintptr_t>(p.ep.ln_out) & 15) == 0, DTB_ERR_BAD_ARG, "gemm: ln_out must be 16-byte aligned rows");
+  }
+  if (p.ep.sk_out) {  // in-kernel reduction requested: one counter per (tile, epilogue warp)
+    p.ep.sk_counters = nullptr;
+    if (p.ep.partial && p.split_k > 1 && sk_inkernel_enabled() && p.ep.sk_ldo % 4 == 0 && (reinterpret_cast<uintptr_t>(p.ep.sk_out) & 15) == 0) {
+      const unsigned int need = (unsigned int)(p.m_tiles * p.n_tiles) * (pair ? 2u * GEMM2_EPI_WARPS : 4u);
+      DTB_TRY(ticket_counters_take(need, &p.ep.sk_counters));
+    }
+    if (!p.ep.sk_counters) p.ep.sk_out = nullptr;
+  }
 
   const uint32_t b_rows = pair ? 128u : (uint32_t)p.BN;  // a pair CTA stages its own 128-column half of B
   CUtensorMap tmA, tmB;
@@ -212,7 +254,8 @@ int gemm_bf16(cudaStream_t stream, const bf16* A, int lda, int a_mn_major, const
     DTB_LAUNCH(gemm_tcgen05_kernel, grid, GEMM_THREADS, GEMM_SMEM_BYTES, stream, tmA, tmB, p);
   }
   DTB_CHECK_LAUNCH();
-  return p.split_k;  // >= 1: number of partial slices written when ep.partial != null
+  // > 0: number of partial slices the caller still has to reduce; 0: split-K partials were reduced inside the kernel into ep.sk_out
+  return (p.ep.partial && p.ep.sk_counters) ? 0 : p.split_k;
 }
 
 // ---- split-K reduction: out[M, ldo] (+)= scale * sum_s partial[s][M][N], slices added in index order (deterministic) -------------
@@ -281,8 +324,10 @@ int gemm_wgrad(cudaStream_t stream, const bf16* A, int lda, const bf16* B, int l
     return rc < 0 ? rc : DTB_OK;
   }
   ep.partial = partial;
+  ep.sk_out = out;  // reduced by the last-arriving CTA of every tile inside the GEMM (no separate reduction launch)
+  ep.sk_ldo = ldo;
   const int rc = gemm_bf16(stream, A, lda, 1, B, ldb, 1, Mout, Nout, Kred, ep, split, 0);
-  if (rc < 0) return rc;
+  if (rc <= 0) return rc;
   return splitk_reduce(stream, partial, rc, Mout, Nout, out, ldo, 0, 1.f);
 }
 

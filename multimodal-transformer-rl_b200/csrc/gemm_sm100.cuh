@@ -216,10 +216,9 @@ __device__ __forceinline__ void epi_land_bf16(const EpiLoadBf16& L, uint32_t* st
 // `bias_lane` = bias[col0 + lane] (loaded early by the caller), `Lr` / `La` = the residual / aux blocks issued early.
 __device__ __forceinline__ void gemm_epilogue_chunk_staged(const GemmParams& p, const GemmEpilogue& ep, const uint32_t (&v)[32], uint32_t* st,
                                                            int lane, int row0, int col0, int split, float bias_lane, const EpiLoadF32& Lr,
-                                                           const EpiLoadBf16& La) {
+                                                           const EpiLoadBf16& La, float (&f)[32]) {
   if (col0 >= p.N) return;  // warp-uniform
   const int ncols = min(32, p.N - col0);
-  float f[32];
   if (ep.partial) {
 #pragma unroll
     for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
@@ -264,6 +263,42 @@ __device__ __forceinline__ void gemm_epilogue_chunk_staged(const GemmParams& p, 
   }
   if (ep.out_f32) epi_write_f32(st, lane, f, ep.out_f32, ep.ldo_f, row0, p.M, col0, ncols);
   if (ep.out_bf16) epi_write_bf16(st, lane, f, ep.out_bf16, ep.ldo_b, row0, p.M, col0, ncols);
+}
+
+// Split-K, last arrival reduces: called by one epilogue warp after it stored its partial rows [row0, row0 + 32) x the column chunks
+// c = c_begin, c_begin + c_step, ... of the tile at n0.  The warp that takes the last of the split_k tickets of its counter sums the
+// slices in index order (the same order for whichever CTA happens to be last: deterministic) and writes sk_out; it leaves the counter
+// at zero for the next launch.  Slices are read with ld.global.cg (L2): the other CTAs' stores were fenced before their tickets.
+__device__ __forceinline__ void gemm_splitk_finish(const GemmParams& p, const GemmEpilogue& ep, unsigned int* counter, int lane, int row0,
+                                                   int n0, int c_begin, int c_step, int c_end) {
+  __threadfence();
+  __syncwarp();
+  unsigned int ticket = 0;
+  if (lane == 0) ticket = atomicAdd(counter, 1u);
+  ticket = __shfl_sync(0xffffffffu, ticket, 0);
+  if (ticket != (unsigned int)p.split_k - 1u) return;  // warp-uniform
+  __threadfence();
+  const size_t slice = (size_t)p.M * p.N;
+  const int cc = 4 * (lane & 7);
+  for (int c = c_begin; c < c_end; c += c_step) {
+    const int col0 = n0 + c;
+    if (col0 >= p.N) break;
+    const int ncols = min(32, p.N - col0);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int row = row0 + i * 4 + (lane >> 3);
+      if (row < p.M && cc < ncols) {
+        const float* src = ep.partial + (size_t)row * p.N + col0 + cc;
+        float4 s = __ldcg(reinterpret_cast<const float4*>(src));
+        for (int k = 1; k < p.split_k; ++k) {
+          const float4 t = __ldcg(reinterpret_cast<const float4*>(src + (size_t)k * slice));
+          s.x += t.x; s.y += t.y; s.z += t.z; s.w += t.w;
+        }
+        *reinterpret_cast<float4*>(ep.sk_out + (size_t)row * ep.sk_ldo + col0 + cc) = s;
+      }
+    }
+  }
+  if (lane == 0) *counter = 0u;
 }
 
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
@@ -410,16 +445,54 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       prefetch(n0);
       mbar_wait(&tfull_bar[acc], acc_phase);
       tc_fence_after();
+      const uint32_t t_acc = tmem_base + ((uint32_t)(q * 32) << 16) + acc * GEMM_MAX_BN;
+      float rsum = 0.f;
       for (int c = 0; c < BN; c += 32) {
         uint32_t v[32];
-        tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + acc * GEMM_MAX_BN + c, v);
+        tmem_ld_32x32(t_acc + c, v);
         tmem_ld_wait();
         const EpiLoadF32 Lr_cur = Lr;
         const EpiLoadBf16 La_cur = La;
         const float bias_cur = bias_lane;
         if (c + 32 < BN) prefetch(n0 + c + 32);  // next chunk's operands fly while this one is processed
-        gemm_epilogue_chunk_staged(p, ep, v, st, lane, row0, n0 + c, split, bias_cur, Lr_cur, La_cur);
+        float f[32];
+        gemm_epilogue_chunk_staged(p, ep, v, st, lane, row0, n0 + c, split, bias_cur, Lr_cur, La_cur, f);
+        if (ep.ln_out) {  // fused LayerNorm, pass 1: the finished fp32 row values go back into the accumulator columns; row sum
+#pragma unroll
+          for (int j = 0; j < 32; ++j) { rsum += f[j]; v[j] = __float_as_uint(f[j]); }
+          tmem_st_32x32(t_acc + c, v);
+        }
       }
+      if (ep.ln_out) {  // host guarantees BN == N, N % 32 == 0, one n-tile, no split-K: this thread owns the whole row
+        tmem_st_wait();
+        const float inv_n = 1.f / (float)p.N;
+        const float mean = rsum * inv_n;
+        float q2 = 0.f;
+        for (int c = 0; c < BN; c += 32) {  // pass 2: centred sum of squares (two-pass variance, as nn.LayerNorm computes it)
+          uint32_t v[32];
+          tmem_ld_32x32(t_acc + c, v);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 32; ++j) { const float d = __uint_as_float(v[j]) - mean; q2 = fmaf(d, d, q2); }
+        }
+        const float rstd = rsqrtf(q2 * inv_n + ep.ln_eps);
+        for (int c = 0; c < BN; c += 32) {  // pass 3: normalise, scale / shift, coalesced bf16 rows
+          uint32_t v[32];
+          tmem_ld_32x32(t_acc + c, v);
+          tmem_ld_wait();
+          const float g_lane = __ldg(ep.ln_gamma + c + lane), b_lane = __ldg(ep.ln_beta + c + lane);
+          float y[32];
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            y[j] = fmaf((__uint_as_float(v[j]) - mean) * rstd, __shfl_sync(0xffffffffu, g_lane, j), __shfl_sync(0xffffffffu, b_lane, j));
+          epi_write_bf16(st, lane, y, ep.ln_out, ep.ld_ln, row0, p.M, c, 32);
+        }
+        if (row0 + lane < p.M) {
+          if (ep.ln_mean) ep.ln_mean[row0 + lane] = mean;
+          if (ep.ln_rstd) ep.ln_rstd[row0 + lane] = rstd;
+        }
+      }
+      if (ep.partial && ep.sk_counters) gemm_splitk_finish(p, ep, ep.sk_counters + (size_t)mn * 4 + q, lane, row0, n0, 0, 32, BN);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&tempty_bar[acc]);
@@ -687,8 +760,11 @@ gemm_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
         const EpiLoadBf16 La_cur = La;
         const float bias_cur = bias_lane;
         if (c + 64 < GEMM2_BN) prefetch(n0 + c + 64);  // next chunk's operands fly while this one is processed
-        gemm_epilogue_chunk_staged(p, ep, v, st, lane, row0, n0 + c, split, bias_cur, Lr_cur, La_cur);
+        float f[32];
+        gemm_epilogue_chunk_staged(p, ep, v, st, lane, row0, n0 + c, split, bias_cur, Lr_cur, La_cur, f);
       }
+      if (ep.partial && ep.sk_counters)
+        gemm_splitk_finish(p, ep, ep.sk_counters + ((size_t)mn * 2 + rank) * GEMM2_EPI_WARPS + (warp - 4), lane, row0, n0, 32 * half, 64, GEMM2_BN);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive_cluster(&tempty_bar[acc], 0);

@@ -20,6 +20,21 @@ struct GemmEpilogue {
   float* partial;         // split-K: fp32 partials [split][M][N]; epilogue fields above are then ignored
   float alpha;            // scale applied to the accumulator first
   DropSite drop;          // dropout of (acc + bias [act]) before the residual add; element index = row * N + col
+  // Fused LayerNorm of the finished output rows (single-CTA kernel with BN == N <= 256, N % 32 == 0: a CTA owns whole rows, TMEM lane =
+  // row): ln_out[row] = (v - mean) * rstd * ln_gamma + ln_beta in bf16, v = the fp32 value written to out_f32 (bias / dropout / residual
+  // applied); mean / rstd are saved for ln_bwd.  Replaces the standalone ln_fwd launch after every c_proj (HF:272, :303, :450).
+  const float* ln_gamma;
+  const float* ln_beta;
+  bf16* ln_out;
+  int ld_ln;
+  float* ln_mean;
+  float* ln_rstd;
+  float ln_eps;
+  // Split-K reduced inside the kernel: every epilogue warp takes a ticket on its (tile, row block) counter after storing its partial
+  // rows; the last of the split_k arrivals sums the slices in index order (deterministic) and writes sk_out.  Counters return to zero.
+  unsigned int* sk_counters;
+  float* sk_out;
+  int sk_ldo;
 };
 
 struct GemmParams {
@@ -42,6 +57,9 @@ int gemm_pick_bn(int M, int N, int b_mn_major);
 int gemm_wgrad_split(int Mout, int Nout, int Kred, size_t partial_floats);
 int gemm_wgrad(cudaStream_t stream, const bf16* A, int lda, const bf16* B, int ldb, int Mout, int Nout, int Kred, float* out, int ldo,
                float* partial, size_t partial_floats);
+// `need` zero-initialised device counters for a "last arrival finishes the reduction" kernel (self-resetting; a slice of a ring, so
+// kernels running concurrently on different streams never share one).  *out = nullptr when the request is too large.
+int ticket_counters_take(unsigned int need, unsigned int** out);
 int splitk_reduce(cudaStream_t stream, const float* partial, int splits, int M, int N, float* out, int ldo, int accumulate, float scale);
 
 // 2-D bf16 tensor map (cached): dims {d0 contiguous, d1}, row stride in elements, box {b0, b1}, 128B swizzle.
@@ -78,7 +96,8 @@ int ln_fwd(cudaStream_t stream, const float* x, const float* gamma, const float*
 // dx_out = dres + LNbwd(dy); also bf16 copy; dgamma/dbeta accumulated (+=) after internal partial reduce
 int ln_bwd(cudaStream_t stream, const bf16* dy, const float* x, const float* mean, const float* rstd, const float* gamma,
            const float* dres, int M, int H, float* dx_out, bf16* dx_out_bf16, float* dgamma, float* dbeta, float* scratch,
-           const DropSite& drop_bf16 = drop_none());  // dropout mask of the consumer site applied to the bf16 copy only (idx = row * H + col)
+           const DropSite& drop_bf16 = drop_none(),  // dropout mask of the consumer site applied to the bf16 copy only (idx = row * H + col)
+           float* dcolsum = nullptr);                // optional [H]: column sums of the (masked) bf16-copy values = bias gradient of the Linear that produced this row
 size_t ln_bwd_scratch_floats(int H);
 
 // ---- attention.cu ------------------------------------------------------------------------------
@@ -99,7 +118,9 @@ int attn_bwd_tc(cudaStream_t stream, const bf16* qkv, const float* mask, const b
 int embed_fwd(cudaStream_t stream, const float* states, const float* state_proj, const float* actions, const float* rtg,
               const long long* timesteps, const float* table, const float* wR, const float* bR, const float* Ws, const float* bs,
               const float* Wa, const float* ba, const float* gamma, const float* beta, int BK, int sd, int ad, int H, int E, float eps,
-              float* x, float* pre, float* mean, float* rstd, bf16* U, int P8, int u_states, const DropSite& drop = drop_none());
+              float* x, float* pre, float* mean, float* rstd, bf16* U, int P8, int u_states, const DropSite& drop = drop_none(),
+              const float* ln1_gamma = nullptr, const float* ln1_beta = nullptr, bf16* h1 = nullptr, float* mean1 = nullptr,
+              float* rstd1 = nullptr);
 int embed_te_scatter(cudaStream_t stream, const bf16* d_pre, const long long* timesteps, int BK, int H, int E, float* d_table);
 int embed_unpack(cudaStream_t stream, const float* G, const float* bsum, int H, int sd, int ad, int P8, int u_states, float* dwR,
                  float* dbR, float* dWs, float* dbs, float* dWa, float* dba);

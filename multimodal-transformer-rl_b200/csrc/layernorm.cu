@@ -69,22 +69,30 @@ int ln_fwd(cudaStream_t stream, const float* x, const float* gamma, const float*
 // ---------------------------------------------------------------------------------------------------
 // One warp per token row, NV = ceil(H / 128) float4 per lane (compile-time so the per-lane arrays are exact).  All of a row's loads
 // (x, dy, dres) are issued before the first reduction so ~10 KB per warp is in flight; two 256-thread CTAs per SM.
-template <int NV>
-__global__ void __launch_bounds__(256, 2) ln_bwd_kernel(const bf16* __restrict__ dy, const float* __restrict__ x,
+// Column reductions (dgamma, dbeta and — CS — the column sums of the bf16 output, i.e. the bias gradient of the c_proj whose output
+// gradient this is) leave the kernel as per-block partials; the block that takes the last ticket sums them in block order
+// (deterministic) and writes the results: one launch, no separate finalize kernel.
+template <int NV, bool CS>
+__global__ void __launch_bounds__(256, (NV > 4 && CS) ? 1 : 2) ln_bwd_kernel(const bf16* __restrict__ dy, const float* __restrict__ x,
                                                         const float* __restrict__ mean, const float* __restrict__ rstd,
                                                         const float* __restrict__ gamma, const float* __restrict__ dres, int M, int H,
                                                         float* __restrict__ dx_out, bf16* __restrict__ dx_bf16,
-                                                        float* __restrict__ scratch /* [grid][2][H] */, const DropSite drop) {
+                                                        float* __restrict__ scratch /* [grid][NF][H] */, unsigned int* __restrict__ counter,
+                                                        float* __restrict__ dgamma, float* __restrict__ dbeta, float* __restrict__ dcolsum,
+                                                        const DropSite drop) {
   pdl_trigger();
   pdl_wait();
+  constexpr int NF = CS ? 3 : 2;
   const uint32_t drop_key = drop.state ? drop_site_key(drop) : 0u;
-  extern __shared__ float sred[];  // [2][H]
+  extern __shared__ float sred[];  // [NF][H]
+  __shared__ unsigned int s_last;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
-  float4 dg[NV], db[NV];
+  float4 dg[NV], db[NV], dc[CS ? NV : 1];
 #pragma unroll
   for (int i = 0; i < NV; ++i) {
     dg[i] = make_float4(0, 0, 0, 0);
     db[i] = make_float4(0, 0, 0, 0);
+    if (CS) dc[i] = make_float4(0, 0, 0, 0);
   }
   const int row_step = gridDim.x * nwarp;
   for (int row = blockIdx.x * nwarp + warp; row < M; row += row_step) {
@@ -142,19 +150,20 @@ __global__ void __launch_bounds__(256, 2) ln_bwd_kernel(const bf16* __restrict__
           o.x += r.x; o.y += r.y; o.z += r.z; o.w += r.w;
         }
         if (dx_out) *reinterpret_cast<float4*>(dx_out + (size_t)row * H + c) = o;
-        if (dx_bf16) {
+        if (dx_bf16 || CS) {
           if (drop.state) {  // the bf16 copy feeds the c_proj backward of a dropout site: d(drop(y)) = mask * scale * d
             const uint32_t k = drop_key + (uint32_t)row * (uint32_t)H + (uint32_t)c;
             o.x = drop_apply(o.x, k, 0u, drop.thr, drop.scale); o.y = drop_apply(o.y, k, 1u, drop.thr, drop.scale);
             o.z = drop_apply(o.z, k, 2u, drop.thr, drop.scale); o.w = drop_apply(o.w, k, 3u, drop.thr, drop.scale);
           }
-          *reinterpret_cast<uint2*>(dx_bf16 + (size_t)row * H + c) = make_uint2(pack_bf16x2(o.x, o.y), pack_bf16x2(o.z, o.w));
+          if (dx_bf16) *reinterpret_cast<uint2*>(dx_bf16 + (size_t)row * H + c) = make_uint2(pack_bf16x2(o.x, o.y), pack_bf16x2(o.z, o.w));
+          if (CS) { dc[i].x += o.x; dc[i].y += o.y; dc[i].z += o.z; dc[i].w += o.w; }
         }
       }
     }
   }
-  // deterministic cross-warp reduction of the dgamma / dbeta partials
-  for (int i = threadIdx.x; i < 2 * H; i += blockDim.x) sred[i] = 0.f;
+  // deterministic cross-warp reduction of the column partials
+  for (int i = threadIdx.x; i < NF * H; i += blockDim.x) sred[i] = 0.f;
   __syncthreads();
   for (int w = 0; w < nwarp; ++w) {
     if (warp == w) {
@@ -164,57 +173,73 @@ __global__ void __launch_bounds__(256, 2) ln_bwd_kernel(const bf16* __restrict__
         if (c < H) {
           sred[c] += dg[i].x; sred[c + 1] += dg[i].y; sred[c + 2] += dg[i].z; sred[c + 3] += dg[i].w;
           sred[H + c] += db[i].x; sred[H + c + 1] += db[i].y; sred[H + c + 2] += db[i].z; sred[H + c + 3] += db[i].w;
+          if (CS) { sred[2 * H + c] += dc[i].x; sred[2 * H + c + 1] += dc[i].y; sred[2 * H + c + 2] += dc[i].z; sred[2 * H + c + 3] += dc[i].w; }
         }
       }
     }
     __syncthreads();
   }
-  for (int i = threadIdx.x; i < 2 * H; i += blockDim.x) scratch[(size_t)blockIdx.x * 2 * H + i] = sred[i];
-}
-
-// 32 columns x 32 row-lanes per block (short dependent-load chains: nblk / 32 deep); lanes combined in index order (deterministic).
-__global__ void __launch_bounds__(1024) ln_bwd_finalize(const float* __restrict__ scratch, int nblk, int H, float* __restrict__ dgamma,
-                                                        float* __restrict__ dbeta) {
-  pdl_trigger();
-  pdl_wait();
-  __shared__ float red[32][33];
-  const int c = blockIdx.x * 32 + threadIdx.x;
-  float s = 0.f;
-  if (c < 2 * H)
-    for (int b = threadIdx.y; b < nblk; b += 32) s += scratch[(size_t)b * 2 * H + c];
-  red[threadIdx.y][threadIdx.x] = s;
+  const int nblk = gridDim.x;
+  for (int i = threadIdx.x; i < NF * H; i += blockDim.x) scratch[(size_t)blockIdx.x * NF * H + i] = sred[i];
+  // last block: sum the per-block partials in block order.  8 row-lanes x 32 columns per pass; lanes combined in index order.
+  __threadfence();
   __syncthreads();
-  if (threadIdx.y == 0 && c < 2 * H) {
-    for (int i = 1; i < 32; ++i) s += red[i][threadIdx.x];
-    if (c < H) dgamma[c] = s;
-    else dbeta[c - H] = s;
+  if (threadIdx.x == 0) s_last = atomicAdd(counter, 1u) == (unsigned int)nblk - 1u ? 1u : 0u;
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  float* red = sred;  // reuse: [8][33]  (NF * H >= 2 * 64 floats ... sized by the host to at least 8 * 33)
+  for (int base = 0; base < NF * H; base += 32) {
+    const int c = base + lane;
+    float s = 0.f;
+    if (c < NF * H)
+      for (int b = warp; b < nblk; b += nwarp) s += __ldcg(scratch + (size_t)b * NF * H + c);
+    __syncthreads();
+    red[warp * 33 + lane] = s;
+    __syncthreads();
+    if (warp == 0 && c < NF * H) {
+      for (int i = 1; i < nwarp; ++i) s += red[i * 33 + lane];
+      if (c < H) dgamma[c] = s;
+      else if (c < 2 * H) dbeta[c - H] = s;
+      else dcolsum[c - 2 * H] = s;
+    }
   }
+  if (threadIdx.x == 0) *counter = 0u;
 }
 
-static int ln_bwd_blocks(int M, int H) {
-  int b = (M + 7) / 8;
-  const int cap = num_sms() * 2;  // two resident CTAs per SM; scratch is sized for 8 x SMs partial rows
+static int ln_bwd_blocks(int M, int occ) {
+  int b = (M + 31) / 32;  // at least 4 rows per warp: fewer partial rows for the last block to sum
+  const int cap = num_sms() * occ;  // resident CTAs per SM; scratch is sized for 8 x SMs partial rows
   return b > cap ? cap : (b < 1 ? 1 : b);
 }
-size_t ln_bwd_scratch_floats(int H) { return (size_t)DTB_NUM_SMS_FALLBACK * 8 * 2 * H; }
+size_t ln_bwd_scratch_floats(int H) { return (size_t)DTB_NUM_SMS_FALLBACK * 8 * 3 * H; }
 
 int ln_bwd(cudaStream_t stream, const bf16* dy, const float* x, const float* mean, const float* rstd, const float* gamma,
            const float* dres, int M, int H, float* dx_out, bf16* dx_out_bf16, float* dgamma, float* dbeta, float* scratch,
-           const DropSite& drop) {
+           const DropSite& drop, float* dcolsum) {
   DTB_REQUIRE(H % 4 == 0 && H <= LN_MAX_VEC * 128, DTB_ERR_UNSUPPORTED, "layernorm bwd: hidden size %d unsupported", H);
-  const int blocks = ln_bwd_blocks(M, H);
   const int nv = (H + 127) / 128;
-  const size_t sm = 2 * H * sizeof(float);
+  const int nf = dcolsum ? 3 : 2;
+  const int blocks = ln_bwd_blocks(M, (nv > 4 && dcolsum) ? 1 : 2);
+  size_t sm = (size_t)nf * H * sizeof(float);
+  if (sm < 8 * 33 * sizeof(float)) sm = 8 * 33 * sizeof(float);
+  unsigned int* counter = nullptr;
+  DTB_TRY(ticket_counters_take(1, &counter));
+  DTB_REQUIRE(counter != nullptr, DTB_ERR_CUDA, "layernorm bwd: no ticket counter");
   ProfScope prof(stream, PF_LN_BWD, 16.0 * M * H);
-#define DTB_LN_BWD(NV) DTB_LAUNCH(ln_bwd_kernel<NV>, blocks, 256, sm, stream, dy, x, mean, rstd, gamma, dres, M, H, dx_out, dx_out_bf16, scratch, drop)
+#define DTB_LN_BWD(NV)                                                                                                                  \
+  do {                                                                                                                                  \
+    if (dcolsum) DTB_LAUNCH((ln_bwd_kernel<NV, true>), blocks, 256, sm, stream, dy, x, mean, rstd, gamma, dres, M, H, dx_out, dx_out_bf16, \
+                            scratch, counter, dgamma, dbeta, dcolsum, drop);                                                            \
+    else DTB_LAUNCH((ln_bwd_kernel<NV, false>), blocks, 256, sm, stream, dy, x, mean, rstd, gamma, dres, M, H, dx_out, dx_out_bf16,       \
+                    scratch, counter, dgamma, dbeta, dcolsum, drop);                                                                    \
+  } while (0)
   if (nv <= 1) DTB_LN_BWD(1);
   else if (nv <= 2) DTB_LN_BWD(2);
   else if (nv <= 4) DTB_LN_BWD(4);
   else if (nv <= 6) DTB_LN_BWD(6);
   else DTB_LN_BWD(8);
 #undef DTB_LN_BWD
-  DTB_CHECK_LAUNCH();
-  DTB_LAUNCH(ln_bwd_finalize, (2 * H + 31) / 32, dim3(32, 32), 0, stream, scratch, blocks, H, dgamma, dbeta);
   DTB_CHECK_LAUNCH();
   return DTB_OK;
 }

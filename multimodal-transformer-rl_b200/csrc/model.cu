@@ -9,6 +9,7 @@
 #include "side.h"
 
 #include <new>
+#include <stdlib.h>
 #include <string.h>
 #include <vector>
 
@@ -148,9 +149,21 @@ static inline const bf16* bfp(const void* params_bf16, long long off) { return r
 
 // D = A[M,K] x W, epilogue options; W in place.  conv1d: W is [K_in][N_out] (MN-major B); linear: W is [N_out][K_in] (K-major B).
 static int gemm_fwd(cudaStream_t st, const bf16* A, int lda, const bf16* W, int ldw, bool w_mn_major, int M, int N, int K,
-                    const GemmEpilogue& ep) {
-  const int rc = gemm_bf16(st, A, lda, 0, W, ldw, w_mn_major ? 1 : 0, M, N, K, ep, 1, 0);
+                    const GemmEpilogue& ep, int bn_override = 0) {
+  const int rc = gemm_bf16(st, A, lda, 0, W, ldw, w_mn_major ? 1 : 0, M, N, K, ep, 1, bn_override);
   return rc < 0 ? rc : DTB_OK;
+}
+// LayerNorm in the c_proj epilogue: the CTA must own whole rows (BN == H).  DTB_LN_SEPARATE=1 keeps the standalone ln_fwd launches.
+static bool dt_ln_fused(int H) {
+  static int off = -1;
+  if (off < 0) {
+    const char* e = getenv("DTB_LN_SEPARATE");
+    off = (e && e[0] == '1') ? 1 : 0;
+  }
+  return !off && H <= 256 && H % 64 == 0;  // BN == H must also be a legal MN-major B tile (multiple of 64)
+}
+static void ep_set_ln(GemmEpilogue& ep, const float* gamma, const float* beta, bf16* out, int ld, float* mean, float* rstd, float eps) {
+  ep.ln_gamma = gamma; ep.ln_beta = beta; ep.ln_out = out; ep.ld_ln = ld; ep.ln_mean = mean; ep.ln_rstd = rstd; ep.ln_eps = eps;
 }
 static GemmEpilogue ep_zero() {
   GemmEpilogue ep;
@@ -184,10 +197,13 @@ static int dt_forward(const dtb_dt* h, cudaStream_t st, const float* P, const vo
   }
   DTB_TRY(embed_fwd(st, states_f, sproj, b->actions, b->returns_to_go, b->timesteps, P + h->e(E_TABLE), P + h->e(E_WR), P + h->e(E_BR),
                     P + h->e(E_WS), P + h->e(E_BS), P + h->e(E_WA), P + h->e(E_BA), P + h->e(E_LNW), P + h->e(E_LNB), BK, sd, ad, H,
-                    c.max_ep_len, c.ln_eps, w.xs[0], w.pre0, w.mean0, w.rstd0, w.U, h->P8, h->sd_small, h->drop_embd()));
+                    c.max_ep_len, c.ln_eps, w.xs[0], w.pre0, w.mean0, w.rstd0, w.U, h->P8, h->sd_small, h->drop_embd(),
+                    P + h->l(0, L_LN1W), P + h->l(0, L_LN1B), w.h1[0], w.mean1[0], w.rstd1[0]));  // + ln_1 of block 0 in the same pass
+  // Every other LayerNorm of the forward (ln_2, the next block's ln_1, ln_f) runs in the epilogue of the c_proj GEMM that produces its
+  // input row (north star (2): "LayerNorm/GELU/residual fused into GEMM epilogues") when a CTA can own whole rows: H <= 256, H % 32 == 0.
+  const bool ln_fused = dt_ln_fused(H);
   // ---- GPT-2 blocks (A4-A6) ----
   for (int l = 0; l < L; ++l) {
-    DTB_TRY(ln_fwd(st, w.xs[l], P + h->l(l, L_LN1W), P + h->l(l, L_LN1B), M, H, c.ln_eps, w.h1[l], w.mean1[l], w.rstd1[l]));
     {
       GemmEpilogue ep = ep_zero();
       ep.bias = P + h->l(l, L_BQKV);
@@ -204,9 +220,10 @@ static int dt_forward(const dtb_dt* h, cudaStream_t st, const float* P, const vo
       ep.out_f32 = w.xmid[l];
       ep.ldo_f = H;
       ep.drop = h->drop_resid(l, 0);
-      DTB_TRY(gemm_fwd(st, w.o[l], H, bfp(Pb, h->l(l, L_WO)), H, true, M, H, H, ep));
+      if (ln_fused) ep_set_ln(ep, P + h->l(l, L_LN2W), P + h->l(l, L_LN2B), w.h2[l], H, w.mean2[l], w.rstd2[l], c.ln_eps);
+      DTB_TRY(gemm_fwd(st, w.o[l], H, bfp(Pb, h->l(l, L_WO)), H, true, M, H, H, ep, ln_fused ? H : 0));
     }
-    DTB_TRY(ln_fwd(st, w.xmid[l], P + h->l(l, L_LN2W), P + h->l(l, L_LN2B), M, H, c.ln_eps, w.h2[l], w.mean2[l], w.rstd2[l]));
+    if (!ln_fused) DTB_TRY(ln_fwd(st, w.xmid[l], P + h->l(l, L_LN2W), P + h->l(l, L_LN2B), M, H, c.ln_eps, w.h2[l], w.mean2[l], w.rstd2[l]));
     {
       GemmEpilogue ep = ep_zero();
       ep.bias = P + h->l(l, L_B1);
@@ -224,11 +241,16 @@ static int dt_forward(const dtb_dt* h, cudaStream_t st, const float* P, const vo
       ep.out_f32 = w.xs[l + 1];
       ep.ldo_f = H;
       ep.drop = h->drop_resid(l, 1);
-      DTB_TRY(gemm_fwd(st, w.fc[l], I, bfp(Pb, h->l(l, L_W2)), H, true, M, H, I, ep));
+      // the LayerNorm that reads this block's output: the next block's ln_1, or ln_f after the last block
+      const float* g = l + 1 < L ? P + h->l(l + 1, L_LN1W) : P + h->t(T_LNFW);
+      const float* be = l + 1 < L ? P + h->l(l + 1, L_LN1B) : P + h->t(T_LNFB);
+      if (ln_fused) ep_set_ln(ep, g, be, l + 1 < L ? w.h1[l + 1] : w.yf, H, l + 1 < L ? w.mean1[l + 1] : w.meanf, l + 1 < L ? w.rstd1[l + 1] : w.rstdf, c.ln_eps);
+      DTB_TRY(gemm_fwd(st, w.fc[l], I, bfp(Pb, h->l(l, L_W2)), H, true, M, H, I, ep, ln_fused ? H : 0));
+      if (!ln_fused) DTB_TRY(ln_fwd(st, w.xs[l + 1], g, be, M, H, c.ln_eps, l + 1 < L ? w.h1[l + 1] : w.yf, l + 1 < L ? w.mean1[l + 1] : w.meanf,
+                                    l + 1 < L ? w.rstd1[l + 1] : w.rstdf));
     }
   }
-  // ---- ln_f + heads (A7) ----
-  DTB_TRY(ln_fwd(st, w.xs[L], P + h->t(T_LNFW), P + h->t(T_LNFB), M, H, c.ln_eps, w.yf, w.meanf, w.rstdf));
+  // ---- heads (A7; ln_f ran in the last c_proj epilogue / just above) ----
   DTB_TRY(heads_fwd(st, w.yf, P + h->t(T_WPA), P + h->t(T_BPA), P + h->t(T_WPS), P + h->t(T_BPS), P + h->t(T_WPR), P + h->t(T_BPR), BK, H,
                     sd, ad, c.action_tanh, w.ap, state_preds, return_preds));
   if (action_preds) DTB_CUDA(cudaMemcpyAsync(action_preds, w.ap, (size_t)BK * ad * sizeof(float), cudaMemcpyDeviceToDevice, st));
@@ -264,9 +286,10 @@ static int bwd_heads(const dtb_dt* h, cudaStream_t st, const float* P, const dtb
     DTB_CUDA(cudaMemsetAsync(G + h->t(T_WPS), 0, (pad8((long long)sd * H) + pad8(H)) * sizeof(float), ss));
     DTB_CUDA(cudaMemsetAsync(G + h->t(T_BPS), 0, (pad8(sd) + pad8(1)) * sizeof(float), ss));
   }
-  // the bf16 copy of every residual-stream gradient carries the dropout mask of the c_proj site that consumes it next
+  // the bf16 copy of every residual-stream gradient carries the dropout mask of the c_proj site that consumes it next; its column sums
+  // are that c_proj's bias gradient (here: mlp.c_proj.bias of the last block), reduced inside the same kernel
   DTB_TRY(ln_bwd(st, w.tmp_h, w.xs[L], w.meanf, w.rstdf, P + h->t(T_LNFW), nullptr, M, H, w.dX, w.dXb, G + h->t(T_LNFW), G + h->t(T_LNFB),
-                 w.ln_scratch, h->drop_resid(L - 1, 1)));
+                 w.ln_scratch, h->drop_resid(L - 1, 1), G + h->l(L - 1, L_B2)));
   return DTB_OK;
 }
 
@@ -291,8 +314,7 @@ static int bwd_layer(const dtb_dt* h, cudaStream_t st, const float* P, const voi
     DTB_TRY(gemm_fwd(st, X, H, bfp(Pb, h->l(l, L_W2)), H, false, M, I, H, ep));
   }
   DTB_TRY(sd.fork(st));
-  DTB_TRY(gemm_wgrad(ss, w.fc[l], I, X, H, I, H, M, G + h->l(l, L_W2), H, w.partial, w.partial_floats));
-  DTB_TRY(colsum_bf16(ss, X, M, H, H, G + h->l(l, L_B2), 0, w.cs_scratch));
+  DTB_TRY(gemm_wgrad(ss, w.fc[l], I, X, H, I, H, M, G + h->l(l, L_W2), H, w.partial, w.partial_floats));  // (c_proj.bias: by the ln_bwd that produced X)
   DTB_TRY(gemm_wgrad(ss, w.h2[l], H, T1, I, H, I, M, G + h->l(l, L_W1), I, w.partial, w.partial_floats));
   DTB_TRY(colsum_bf16(ss, T1, M, I, I, G + h->l(l, L_B1), 0, w.cs_scratch));
   DTB_TRY(sd.mark(sd.ev_a));
@@ -304,7 +326,7 @@ static int bwd_layer(const dtb_dt* h, cudaStream_t st, const float* P, const voi
   }
   if (attn_marked) DTB_TRY(sd.wait(st, sd.ev_b));  // the previous block's attention weight gradients still read Y / T2
   DTB_TRY(ln_bwd(st, w.tmp_h, w.xmid[l], w.mean2[l], w.rstd2[l], P + h->l(l, L_LN2W), w.dX, M, H, w.dX, Y, G + h->l(l, L_LN2W),
-                 G + h->l(l, L_LN2B), w.ln_scratch, h->drop_resid(l, 0)));
+                 G + h->l(l, L_LN2B), w.ln_scratch, h->drop_resid(l, 0), G + h->l(l, L_BO)));  // + attn.c_proj.bias gradient = colsum(Y)
   // ---- attention ----
   {  // do = dX Wo^T
     GemmEpilogue ep = ep_zero();
@@ -315,7 +337,6 @@ static int bwd_layer(const dtb_dt* h, cudaStream_t st, const float* P, const voi
   DTB_TRY(attn_bwd(st, w.qkv[l], b->attention_mask, w.o[l], w.tmp_h, w.lse[l], B, T, nh, d, T2, w.delta, h->drop_attn(l)));
   DTB_TRY(sd.fork(st));
   DTB_TRY(gemm_wgrad(ss, w.o[l], H, Y, H, H, H, M, G + h->l(l, L_WO), H, w.partial, w.partial_floats));
-  DTB_TRY(colsum_bf16(ss, Y, M, H, H, G + h->l(l, L_BO), 0, w.cs_scratch));
   DTB_TRY(gemm_wgrad(ss, w.h1[l], H, T2, 3 * H, H, 3 * H, M, G + h->l(l, L_WQKV), 3 * H, w.partial, w.partial_floats));
   DTB_TRY(colsum_bf16(ss, T2, M, 3 * H, 3 * H, G + h->l(l, L_BQKV), 0, w.cs_scratch));
   DTB_TRY(sd.mark(sd.ev_b));
@@ -328,7 +349,8 @@ static int bwd_layer(const dtb_dt* h, cudaStream_t st, const float* P, const voi
   }
   DTB_TRY(sd.wait(st, sd.ev_a));  // the MLP weight gradients read X and T1, which the next two kernels / the next block overwrite
   DTB_TRY(ln_bwd(st, w.tmp_h, w.xs[l], w.mean1[l], w.rstd1[l], P + h->l(l, L_LN1W), w.dX, M, H, w.dX, X, G + h->l(l, L_LN1W),
-                 G + h->l(l, L_LN1B), w.ln_scratch, l > 0 ? h->drop_resid(l - 1, 1) : h->drop_embd()));
+                 G + h->l(l, L_LN1B), w.ln_scratch, l > 0 ? h->drop_resid(l - 1, 1) : h->drop_embd(),
+                 l > 0 ? G + h->l(l - 1, L_B2) : nullptr));  // + the previous block's mlp.c_proj.bias gradient = colsum(X)
   return DTB_OK;
 }
 
@@ -343,7 +365,6 @@ static int bwd_embed(const dtb_dt* h, cudaStream_t st, const float* P, const voi
   SideStream& sside = h->side;
   DTB_TRY(sside.fork(st));
   cudaStream_t ss = sside.pick(st);  // parameter gradients on the side branch; d_states (towers' input) stays on the main chain
-  DTB_CUDA(cudaMemsetAsync(G + h->e(E_TABLE), 0, (size_t)E * H * sizeof(float), ss));
   DTB_TRY(embed_te_scatter(ss, w.tmp_h, b->timesteps, BK, H, E, G + h->e(E_TABLE)));
   DTB_TRY(gemm_wgrad(ss, w.tmp_h, 3 * H, w.U, h->P8, 3 * H, h->P8, BK, w.G, h->P8, w.partial, w.partial_floats));
   DTB_TRY(colsum_bf16(ss, w.tmp_h, BK, 3 * H, 3 * H, w.bsum, 0, w.cs_scratch));

@@ -116,4 +116,8 @@ class FusedClipAdamW:
         _lib.check(lib.dtb_clip_adamw_step(_lib.stream_ptr(), n, segs, C.byref(hp), _lib.ptr(st["step"]), _lib.ptr(st["scratch"])))
         for i, mod in enumerate(self.modules):
             # the library wrote the fp32 master behind torch's back: shadows it rewrote are current, the others must be re-staged
-            mod._staged_version = mod._version_now() if segs[i].params_bf16 else -1
+            if segs[i].params_bf16:
+                mod._staged_version = mod._version_now()
+            else:  # GEMM-ready bf16 copies in another order than the flat buffer (conv towers): re-staged here, as part of the optimizer
+                mod._staged_version = -1  # step, so that the forward / backward step itself launches no weight-staging kernels
+                mod._stage()

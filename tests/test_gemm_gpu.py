@@ -145,3 +145,52 @@ def test_gemm_cta_pair(cuda_device, a_mn, b_mn, M, N, K, split):
         _lib.gemm_bf16(A, B, M, N, K, a_mn_major=a_mn, b_mn_major=b_mn, out_f32=out, partial=part, split_k=split, bn=1000)
         torch.cuda.synchronize()
         assert rel_err(out, ref) < 2e-3
+
+
+@pytest.mark.parametrize("M,N,K,b_mn", [(5760, 128, 128, True), (5760, 128, 512, True), (90, 128, 128, True), (9600, 256, 1024, True),
+                                        (333, 64, 192, False), (1, 256, 256, True)])
+def test_gemm_fused_layernorm_epilogue(cuda_device, M, N, K, b_mn):
+    """c_proj + bias + residual + LayerNorm in one kernel (dtb_gemm_bf16_ln) vs addmm + layer_norm in fp32 on the same bf16 operands."""
+    from mtrl_b200 import _lib
+
+    dev = cuda_device
+    g = torch.Generator().manual_seed(M + N + K)
+    A = (torch.randn(M, K, generator=g) * 0.5).to(dev).to(torch.bfloat16)
+    W = (torch.randn(K, N, generator=g) * 0.1).to(dev).to(torch.bfloat16)  # Conv1D layout [in, out]
+    Wop = W if b_mn else W.t().contiguous()
+    bias = torch.randn(N, generator=g).to(dev)
+    res = (torch.randn(M, N, generator=g) * 2 + 0.3).to(dev)
+    gamma, beta = (torch.randn(N, generator=g) * 0.5 + 1).to(dev), torch.randn(N, generator=g).to(dev)
+    out = torch.full((M, N), float("nan"), device=dev)
+    y = torch.full((M, N), float("nan"), device=dev, dtype=torch.bfloat16)
+    mean, rstd = torch.empty(M, device=dev), torch.empty(M, device=dev)
+    _lib.gemm_bf16_ln(A, Wop, M, N, K, gamma, beta, 1e-5, y, b_mn_major=b_mn, bias=bias, residual=res, out_f32=out, mean=mean, rstd=rstd)
+    torch.cuda.synchronize()
+    ref = A.float() @ W.float() + bias + res
+    assert rel_err(out, ref) < 2e-3
+    ref_y = torch.nn.functional.layer_norm(out, (N,), gamma, beta, 1e-5)  # LN of the kernel's own fp32 rows: isolates the fused part
+    assert rel_err(y, ref_y) < 4e-3
+    assert rel_err(mean, out.mean(1)) < 1e-5
+    assert rel_err(rstd, 1.0 / torch.sqrt(out.var(1, unbiased=False) + 1e-5)) < 1e-5
+
+
+@pytest.mark.parametrize("Mtok,Kin,Nout,split", [(5760, 128, 384, 4), (5760, 512, 128, 8), (1920, 1024, 128, 3), (38400, 768, 768, 2)])
+def test_gemm_splitk_reduced_in_kernel_is_deterministic(cuda_device, Mtok, Kin, Nout, split):
+    """Split-K weight gradient with the reduction done by the last-arriving CTA of every tile: same bits on every run (fixed slice
+    order), equal to the fp32 reference, and the ticket counters return to zero (second call correct)."""
+    from mtrl_b200 import _lib
+
+    dev = cuda_device
+    g = torch.Generator().manual_seed(Mtok + Kin)
+    X = torch.randn(Mtok, Kin, generator=g).to(dev).to(torch.bfloat16)
+    dY = torch.randn(Mtok, Nout, generator=g).to(dev).to(torch.bfloat16)
+    ref = X.float().t() @ dY.float()
+    partial = torch.empty(split, Kin, Nout, device=dev)
+    outs = []
+    for _ in range(3):
+        out = torch.full((Kin, Nout), float("nan"), device=dev)
+        _lib.gemm_bf16(X, dY, Kin, Nout, Mtok, a_mn_major=True, b_mn_major=True, out_f32=out, partial=partial, split_k=split)
+        torch.cuda.synchronize()
+        assert rel_err(out, ref) < 2e-3
+        outs.append(out)
+    assert torch.equal(outs[0], outs[1]) and torch.equal(outs[1], outs[2])

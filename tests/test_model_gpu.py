@@ -235,3 +235,23 @@ def test_pad_left_bit_exact(cuda_device, t, K):
     for x, d in zip(srcs, dsts):
         assert torch.equal(d[K - t:], x) and (d[:K - t] == 0).all()
     assert torch.equal(mask, torch.cat([torch.zeros(K - t), torch.ones(t)]).to(dev))
+
+
+@pytest.mark.parametrize("name,B", [("c1", 64), ("c3", 4)])
+def test_gradients_are_bit_reproducible(cuda_device, name, B):
+    """SURVEY.md §8b "Determinism": fixed reduction orders everywhere (split-K slices and column partials summed in index order by the
+    last-arriving CTA, embedding-table rows accumulated in timestep order, no atomics on data) -> the whole flat gradient buffer, the
+    loss and the predictions are bitwise identical from run to run."""
+    _, model, K = build_pair(name, cuda_device, seed=13)
+    cfg = CONFIGS[name]
+    s, a, r, t, m = make_inputs(B, K, cfg["state_dim"], cfg["act_dim"], 1000, seed=5, onehot_actions=not cfg["action_tanh"])
+    t[:, :] = t[:1, :]  # every trajectory gathers the same embed_timestep rows: maximal collisions in the table gradient
+    dev = cuda_device
+    runs = []
+    for _ in range(3):
+        out = model.loss_and_backward(s.to(dev), a.to(dev), r.to(dev), t.to(dev), m.to(dev))
+        torch.cuda.synchronize()
+        runs.append((out.clone(), model.flat_grads.clone()))
+    for out, g in runs[1:]:
+        assert torch.equal(out, runs[0][0])
+        assert torch.equal(g, runs[0][1])
