@@ -292,7 +292,9 @@ int dtb_encoder_state_dim(const dtb_encoder* e);
 int dtb_encoder_param_entries(const dtb_encoder* e);
 long long dtb_encoder_param_layout(const dtb_encoder* e, long long* offsets, long long* numels);
 size_t dtb_encoder_workspace_bytes(const dtb_encoder* e, int N);
-/* fp32 master (PyTorch layouts) -> bf16 staged copy in tensor-core K order (same offsets). */
+/* fp32 master (PyTorch layouts) -> bf16 staged copy in tensor-core K order (same offsets), followed by the data-gradient weight
+ * matrices of the implicit-GEMM convolutions; the staged buffer has dtb_encoder_staged_elems() bf16 elements. */
+long long dtb_encoder_staged_elems(const dtb_encoder* e);
 int dtb_encoder_stage_params(const dtb_encoder* e, void* stream, const float* params, void* staged_bf16);
 int dtb_encoder_forward(const dtb_encoder* e, void* stream, const float* params, const void* staged_bf16, int N, const float* frames,
                         const float* audio, void* workspace, size_t workspace_bytes, void* states_bf16);

@@ -57,7 +57,8 @@ long long launch_count();
 
 // Optional live profiling (bench.py roofline): CUDA events recorded on the launching stream around each launch of a kernel family.
 enum ProfFamily { PF_GEMM = 0, PF_CONV1_FWD, PF_CONV1_WGRAD, PF_ATTN_FWD, PF_ATTN_BWD, PF_LN_FWD, PF_LN_BWD, PF_EMBED_FWD, PF_COLSUM,
-                  PF_IM2COL, PF_COL2IM, PF_GEMM_MEM /* GEMM shapes below the machine balance: work = algorithmic bytes */, PF_COUNT };
+                  PF_IM2COL, PF_COL2IM, PF_GEMM_MEM /* GEMM shapes below the machine balance: work = algorithmic bytes */, PF_CONVN_FWD, PF_CONVN_DGRAD,
+                  PF_CONVN_WGRAD /* implicit-GEMM conv2 / conv3: work = algorithmic bytes (input + output once) */, PF_COUNT };
 bool prof_on();
 int prof_begin(cudaStream_t stream, int family, double work);  // returns a slot (or -1)
 void prof_end(cudaStream_t stream, int slot);

@@ -26,6 +26,9 @@ struct Tower {
   int flat, feat;
   // flat-parameter offsets: conv w/b ..., fc w/b
   long long w_off[4], b_off[4];
+  // conv layers >= 1 that run as implicit GEMMs (convn.cu): offset of their data-gradient weights in the staged bf16 buffer
+  bool implicit[3];
+  long long dg_off[3];
 };
 
 static inline long long pad8l(long long n) { return (n + 7) & ~7LL; }
@@ -38,6 +41,7 @@ struct TowerWs {
   bf16* dP;     // patch-gradient scratch
   float* gstage;  // staged-order weight gradient scratch
   float* c1_partial;  // implicit conv1 wgrad per-CTA partials
+  float* cn_partial;  // implicit conv2 / conv3 wgrad per-CTA partials
 };
 
 struct EncWs {
@@ -58,6 +62,7 @@ struct dtb_encoder {
   Tower t[2];
   int state_dim;
   long long total;
+  long long staged_total;  // elements of the staged bf16 buffer: the flat layout + the data-gradient weights of the implicit convs
   int n_entries;
   std::vector<long long> off, num;
   mutable dtb::SideStream side;   // weight-gradient branch of the backward (and the audio tower in forward)
@@ -105,6 +110,18 @@ static void layout(dtb_encoder* e) {
   }
   e->total = o;
   e->n_entries = (int)e->off.size();
+  for (int ti = 0; ti < 2; ++ti) {
+    Tower& t = e->t[ti];
+    for (int i = 0; i < 3; ++i) { t.implicit[i] = false; t.dg_off[i] = 0; }
+    for (int i = 1; i < t.nconv; ++i) {
+      const ConvSpec& cs = t.conv[i];
+      if (!convn_supported(cs.cin, cs.cout, cs.k, cs.stride)) continue;
+      t.implicit[i] = true;
+      t.dg_off[i] = o;
+      o += pad8l((long long)convn_dgrad_weight_elems(cs.cin, cs.cout, cs.k));
+    }
+  }
+  e->staged_total = o;
 }
 
 template <typename T>
@@ -126,23 +143,26 @@ static void carve_ws(const dtb_encoder* e, int N, uint8_t* base, EncWs& w) {
     TowerWs& tw = w.t[ti];
     size_t max_dp = 0, max_g = (size_t)t.feat * t.flat;
     for (int i = 0; i < 3; ++i) tw.P[i] = tw.Y[i] = tw.dZ[i] = nullptr;
+    size_t cn_pf = 0;
     for (int i = 0; i < t.nconv; ++i) {
       const ConvSpec& cs = t.conv[i];
       const size_t rows = (size_t)N * cs.hout * cs.wout, kc = (size_t)cs.cin * cs.k * cs.k;
-      const bool implicit = i == 0 && conv1_implicit_supported(cs.cin, cs.win, cs.stride, cs.cout);
-      tw.P[i] = implicit ? nullptr : carve<bf16>(p, rows * kc);
+      const bool implicit = i == 0 ? conv1_implicit_supported(cs.cin, cs.win, cs.stride, cs.cout) : t.implicit[i];
+      tw.P[i] = implicit ? nullptr : carve<bf16>(p, rows * kc);  // patch matrices exist only on the explicit (im2col) path
       if (i == 0) tw.c1_partial = implicit ? carve<float>(p, conv1_wgrad_partial_floats(cs.cin, cs.cout)) : nullptr;
       tw.Y[i] = carve<bf16>(p, rows * cs.cout);
       tw.dZ[i] = carve<bf16>(p, rows * cs.cout);
-      if (i > 0 && rows * kc > max_dp) max_dp = rows * kc;
+      if (i > 0 && !implicit && rows * kc > max_dp) max_dp = rows * kc;
       if ((size_t)cs.cout * kc > max_g) max_g = (size_t)cs.cout * kc;
       if (!implicit) need(cs.cout, kc, rows);
+      if (i > 0 && implicit && convn_wgrad_partial_floats(cs.cin, cs.k) > cn_pf) cn_pf = convn_wgrad_partial_floats(cs.cin, cs.k);
       if ((size_t)cs.cout > maxn) maxn = cs.cout;
     }
     need(t.feat, t.flat, N);
     if ((size_t)t.feat > maxn) maxn = t.feat;
     tw.dP = carve<bf16>(p, max_dp);
     tw.gstage = carve<float>(p, max_g);
+    tw.cn_partial = carve<float>(p, cn_pf);
   }
   const bool sum = e->c.fusion == 1;
   w.feat[0] = sum ? carve<bf16>(p, (size_t)N * e->t[0].feat) : nullptr;
@@ -175,6 +195,10 @@ static int tower_forward(const dtb_encoder* e, int ti, cudaStream_t st, const fl
     const int rows = N * cs.hout * cs.wout, kc = cs.cin * cs.k * cs.k;
     if (i == 0 && tw.P[0] == nullptr) {  // implicit GEMM: patches gathered inside the kernel, never written to HBM
       DTB_TRY(conv1_fwd(st, x, x_u8, N, cs.cin, cs.hin, cs.win, cs.stride, e->c.input_scale, Ps + t.w_off[0], P + t.b_off[0], cs.cout, tw.Y[0]));
+      continue;
+    }
+    if (i > 0 && t.implicit[i]) {  // implicit GEMM over the previous layer's NHWC activation
+      DTB_TRY(convn_fwd(st, tw.Y[i - 1], N, cs.hin, cs.win, cs.cin, cs.k, cs.stride, Ps + t.w_off[i], P + t.b_off[i], cs.cout, tw.Y[i]));
       continue;
     }
     if (i == 0) DTB_REQUIRE(!x_u8, DTB_ERR_UNSUPPORTED, "uint8 pixel input needs the implicit-GEMM conv1 (W %% 4 == 0, stride 4, C <= 4)");
@@ -225,6 +249,14 @@ static int tower_backward(const dtb_encoder* e, int ti, cudaStream_t st, const b
     const ConvSpec& cs = t.conv[i];
     const int rows = N * cs.hout * cs.wout, kc = cs.cin * cs.k * cs.k;
     DTB_TRY(sd.fork(st));  // dZ[i] is complete on the main stream
+    if (i > 0 && t.implicit[i]) {
+      // weight + bias gradient (side branch): patches gathered again from Y[i-1]; written straight in PyTorch order
+      DTB_TRY(convn_wgrad(ss, tw.Y[i - 1], N, cs.hin, cs.win, cs.cin, cs.k, cs.stride, tw.dZ[i], cs.cout, tw.cn_partial, G + t.w_off[i],
+                          G + t.b_off[i]));
+      // data gradient (main chain): implicit transposed convolution with the ReLU mask of Y[i-1] in the epilogue
+      DTB_TRY(convn_dgrad(st, tw.dZ[i], N, cs.hin, cs.win, cs.cin, cs.k, cs.stride, Ps + t.dg_off[i], cs.cout, tw.Y[i - 1], tw.dZ[i - 1]));
+      continue;
+    }
     if (i == 0 && tw.P[0] == nullptr) {
       DTB_REQUIRE(x != nullptr, DTB_ERR_BAD_ARG, "encoder backward: frames / audio are needed again for the implicit conv1 weight gradient");
       DTB_TRY(conv1_wgrad(ss, x, x_u8, N, cs.cin, cs.hin, cs.win, cs.stride, e->c.input_scale, tw.dZ[0], cs.cout, tw.c1_partial, G + t.w_off[0]));
@@ -280,6 +312,7 @@ long long dtb_encoder_param_layout(const dtb_encoder* e, long long* offsets, lon
   }
   return e->total;
 }
+long long dtb_encoder_staged_elems(const dtb_encoder* e) { return e ? e->staged_total : DTB_ERR_BAD_ARG; }
 size_t dtb_encoder_workspace_bytes(const dtb_encoder* e, int N) {
   if (!e || N < 0) return 0;
   EncWs w;
@@ -297,6 +330,7 @@ int dtb_encoder_stage_params(const dtb_encoder* e, void* stream, const float* pa
       const ConvSpec& cs = t.conv[i];
       if (i == 0) DTB_TRY(cast_bf16(st, params + t.w_off[0], (size_t)cs.cout * cs.cin * cs.k * cs.k, S + t.w_off[0]));
       else DTB_TRY(permute_stage(st, params + t.w_off[i], cs.cout, cs.cin, cs.k * cs.k, S + t.w_off[i]));
+      if (i > 0 && t.implicit[i]) DTB_TRY(convn_stage_dgrad(st, params + t.w_off[i], cs.cin, cs.cout, cs.k, cs.stride, S + t.dg_off[i]));
     }
     const ConvSpec& cl = t.conv[t.nconv - 1];
     DTB_TRY(permute_stage(st, params + t.w_off[3], t.feat, cl.cout, cl.hout * cl.wout, S + t.w_off[3]));

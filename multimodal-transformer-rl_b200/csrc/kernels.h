@@ -145,6 +145,18 @@ size_t conv1_wgrad_partial_floats(int C, int cout);
 int conv1_wgrad(cudaStream_t stream, const void* x, int x_u8, int N, int C, int H, int W, int stride, float scale, const bf16* dz, int cout,
                 float* partial, float* dw);
 
+// ---- convn.cu (implicit-GEMM conv2 / conv3: forward, data gradient, weight + bias gradient) ---------------------
+bool convn_supported(int cin, int cout, int k, int stride);
+int convn_fwd(cudaStream_t stream, const bf16* x, int N, int hin, int win, int cin, int k, int stride, const bf16* w_staged, const float* bias,
+              int cout, bf16* y);
+size_t convn_dgrad_weight_elems(int cin, int cout, int k);
+int convn_stage_dgrad(cudaStream_t stream, const float* w, int cin, int cout, int k, int stride, bf16* dst);
+int convn_dgrad(cudaStream_t stream, const bf16* dz, int N, int hin, int win, int cin, int k, int stride, const bf16* wd_staged, int cout,
+                const bf16* act, bf16* dx);
+size_t convn_wgrad_partial_floats(int cin, int k);
+int convn_wgrad(cudaStream_t stream, const bf16* x, int N, int hin, int win, int cin, int k, int stride, const bf16* dz, int cout,
+                float* partial, float* dw, float* db);
+
 // ---- conv.cu -----------------------------------------------------------------------------------
 int im2col_nchw_k8(cudaStream_t stream, const float* x, int N, int C, int H, int W, int stride, float scale, bf16* p);
 int im2col_nhwc(cudaStream_t stream, const bf16* x, int N, int H, int W, int C, int k, int stride, bf16* p);

@@ -160,7 +160,8 @@ class MultimodalStateEncoder(nn.Module):
 
     def _stage(self):
         if self._staged is None or self._staged.device != self._flat.device:
-            self._staged = torch.zeros(self._total, dtype=torch.bfloat16, device=self._flat.device)
+            n = max(self._total, int(_lib.load().dtb_encoder_staged_elems(self._h)))  # + data-gradient weights of the implicit convs
+            self._staged = torch.zeros(n, dtype=torch.bfloat16, device=self._flat.device)
             self._staged_version = -1
         ver = self._version_now()
         if self._staged_version != ver:
