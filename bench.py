@@ -210,10 +210,14 @@ def run_ours(args, wl, rank, world, local_rank):
 
     def make_step_for(dev_in):
         raw_step = make_step(wl, model, parts, dev_in, reducer, 1.0 / world)
+        if not args.restage_each_step:
+            # bf16 weight staging is done by whoever changes the fp32 master (FusedClipAdamW.step() rewrites the DT shadow in its own pass
+            # and re-stages the towers): it is timed with the optimizer (`train_step_with_optimizer`), not with forward + backward
+            return raw_step
 
         def step():
             for p in parts:
-                p._staged_version = -1  # fp32 -> bf16 weight staging is part of every timed step
+                p._staged_version = -1  # round-1 semantics: fp32 -> bf16 weight staging inside every timed step
             return raw_step()
 
         return step
@@ -332,7 +336,9 @@ def run_ours(args, wl, rank, world, local_rank):
                    "parallelism": f"dp{world}", "cuda_graph": graphed, "dropout": args.dropout, "attn_type": ATTN_TYPE,
                    "l2": ("explicit 256 MiB flush between steps" if flush is not None else
                           f"no flush: per-step working set {ws_bytes / 1e6:.0f} MB > 126 MB L2"),
-                   "timed": "weight staging + forward + masked action MSE + backward" + (" + overlapped NCCL all-reduce" if world > 1 else "")},
+                   "timed": ("weight staging + " if args.restage_each_step else "") + "forward + masked action MSE + backward" +
+                            (" + overlapped NCCL all-reduce" if world > 1 else "") +
+                            ("" if args.restage_each_step else " (bf16 weight staging belongs to the optimizer step: train_step_with_optimizer)")},
         "e2e": {"value": tokens / e2e_ms * 1e3, "unit": "tokens/s", "ms_per_step": e2e_ms, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 8,
                 "host_format": "pinned host buffers in the reference's layouts (fp32; video frames as uint8 pixels, decoded in-kernel)",
                 "overlap": "H2D of batch i+1 on a copy stream while step i computes (double-buffered device slots)",
@@ -399,25 +405,51 @@ def run_cpu(wl, steps, warmup, budget_s=20.0, pdrop=0.0):
     b = make_batch(wl, Bs, seed=1234)
     for _ in range(warmup):
         oracle_step(wl, model, b)
-    t0 = time.perf_counter()
+    times = []
     for _ in range(steps):
+        t0 = time.perf_counter()
         loss = oracle_step(wl, model, b)
-    dt_s = (time.perf_counter() - t0) / steps
+        times.append(time.perf_counter() - t0)
+    dt_s = sum(times) / steps
     tokens = Bs * 3 * K
+    times.sort()
     return {"value": tokens / dt_s, "unit": "tokens/s", "cores": cores, "kind": "port", "ms_per_step": dt_s * 1e3,
+            "ms_per_step_min": times[0] * 1e3, "ms_per_step_median": times[len(times) // 2] * 1e3,
             "sample": f"fp32 PyTorch oracle (towers = reference conv_factory math), fwd+loss+bwd, batch {Bs} of {wl['B']} trajectories x K={K} "
                       f"({tokens} tokens/step), dropout {pdrop}, {steps} steps after {warmup} warm-up, {cores} threads", "loss": loss}
 
 
-# DRAM bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum, mean over the captured launches) of each workload's dominant
-# kernel, from the committed `ncu --set full` captures (a profiler pass cannot run inside the timed bench)
-NCU_TRAFFIC = {"c2": (12.87e6, "profiles/r01_ncu_gemm_c2_v2.txt (all 59 single-CTA GEMM launches of one c2 step: 759.6 MB DRAM read + write)"),
-               "c4": (186.2e6, "profiles/r01_ncu_gemm_pair_v2.txt (qkv GEMM at M=38400: 62.6 MB read + 123.6 MB written; tensor pipe 64 % active)")}
+def load_peaks():
+    """Roofline denominators: MEASURED_PEAKS.json (driver-written for this pool's B200s), else the fallback of B200_PROFILING.md."""
+    peaks = {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0, "source": "fallback (B200_PROFILING.md)"}
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as fh:
+            mp = json.load(fh)
+        peaks = {"hbm_gbs": float(mp["hbm_gbs"]), "bf16_tflops": float(mp["bf16_tflops"]),
+                 "bf16_tflops_sustained": float(mp.get("bf16_tflops_sustained", mp["bf16_tflops"])), "source": "measured (MEASURED_PEAKS.json)"}
+    except Exception:
+        pass
+    # machine balance: a GEMM shape with fewer flops per algorithmic byte than this cannot be tensor-bound (sustained peak / copy peak)
+    peaks["balance_flop_per_byte"] = peaks["bf16_tflops_sustained"] * 1e12 / (peaks["hbm_gbs"] * 1e9)
+    return peaks
 
-PROF_FAMILIES = [("gemm_tcgen05_kernel (+pair)", "tensor"), ("conv1_fwd_kernel", "hbm"), ("conv1_wgrad_kernel", "hbm"), ("attn_fwd_kernel", "tensor"),
-                 ("attn_bwd_dq+dkv_kernel", "tensor"), ("ln_fwd_kernel", "hbm"), ("ln_bwd_kernel(+finalize)", "hbm"), ("embed_fwd_kernel", "hbm"),
-                 ("colsum_stage1+2", "hbm"), ("im2col_nhwc_kernel", "hbm"), ("col2im_nhwc_relu_kernel", "hbm"),
-                 ("gemm_tcgen05_kernel, HBM-bound shapes (flops < 216 x bytes)", "hbm")]
+
+def load_traffic(workload):
+    """DRAM bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum) per kernel family, produced from the committed ncu CSV by
+    tools/ncu_traffic.py -> profiles/r02_traffic.json (a profiler pass cannot run inside the timed bench)."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "r02_traffic.json")) as fh:
+            return json.load(fh).get(workload, {})
+    except Exception:
+        return {}
+
+
+# order = the library's ProfFamily enum (csrc/common.cuh)
+PROF_FAMILIES = [("gemm_tcgen05_kernel (+pair)", "tensor"), ("conv1_fwd_kernel", "hbm"), ("conv1_wgrad_kernel", "hbm"), ("attn_fwd_tc_kernel", "tensor"),
+                 ("attn_bwd_dq+dkv_tc_kernel", "tensor"), ("ln_fwd_kernel", "hbm"), ("ln_bwd_kernel", "hbm"), ("embed_fwd_kernel", "hbm"),
+                 ("colsum_kernel", "hbm"), ("im2col_nhwc_kernel", "hbm"), ("col2im_nhwc_relu_kernel", "hbm"),
+                 ("gemm_tcgen05_kernel, HBM-bound shapes", "hbm"), ("convn_kernel<fwd>", "hbm"), ("convn_kernel<dgrad>", "hbm"),
+                 ("convn_wgrad_kernel", "hbm")]
 
 
 def measure_roofline(args, wl, ctx, reps=5):
@@ -429,13 +461,10 @@ def measure_roofline(args, wl, ctx, reps=5):
     from mtrl_b200 import _lib
 
     lib = _lib.load()
-    peaks = {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "source": "fallback (B200_PROFILING.md)"}
-    try:
-        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as fh:
-            mp = json.load(fh)
-        peaks = {"hbm_gbs": float(mp["hbm_gbs"]), "bf16_tflops": float(mp["bf16_tflops"]), "source": "measured (MEASURED_PEAKS.json, burst)"}
-    except Exception:
-        pass
+    peaks = load_peaks()
+    lib.dtb_profile_set_balance.argtypes = [C.c_double]
+    lib.dtb_profile_set_balance.restype = None
+    lib.dtb_profile_set_balance(peaks["balance_flop_per_byte"])
     step = ctx["step"]
     step()
     torch.cuda.synchronize()
@@ -472,6 +501,7 @@ def measure_roofline(args, wl, ctx, reps=5):
         for i, (ms, work, n) in report().items():
             acc[i] = [ms, work, n]
     lib.dtb_profile_enable(0)
+    traffic = load_traffic(args.workload)
     fams = []
     for i, (name, bound) in enumerate(PROF_FAMILIES):
         ms, work, n = acc[i]
@@ -487,13 +517,35 @@ def measure_roofline(args, wl, ctx, reps=5):
         else:
             f["achieved"], f["unit"], f["peak"] = f["work_per_step"] / f["ms_per_step"] / 1e6, "GB/s", peaks["hbm_gbs"]
         f["frac"] = f["achieved"] / f["peak"]
+        f["algorithmic_per_launch"] = f["work_per_step"] / max(1, f["launches_per_step"])
+        tr = traffic.get(f["kernel"])
+        f["traffic"] = tr["dram_bytes_per_launch"] if tr else None
+    if args.families_only:
+        return {"families": sorted(fams, key=lambda f: -f["ms_per_step"]), "profiled_ms_per_step": total, "how": mode}
     top = max(fams, key=lambda f: f["ms_per_step"])
-    return {"kernel": top["kernel"], "bound": top["bound"], "achieved": top["achieved"], "peak": top["peak"], "unit": top["unit"],
-            "frac": top["frac"], "traffic": (NCU_TRAFFIC.get(args.workload, (None, None))[0] if top["kernel"].startswith("gemm") else None),
-            "traffic_source": NCU_TRAFFIC.get(args.workload, (None, None))[1] if top["kernel"].startswith("gemm") else None, "peak_source": peaks["source"], "launches_per_step": top["launches_per_step"],
-            "avg_launch_us": top["ms_per_step"] / max(1, top["launches_per_step"]) * 1e3,
-            "how": f"CUDA events around every launch of the family on its own stream, {reps} steps, {mode}; algorithmic work per DESIGN.md §3",
-            "families": sorted(fams, key=lambda f: -f["ms_per_step"])}
+    tr = traffic.get(top["kernel"]) or {}
+    out = {"kernel": top["kernel"], "bound": top["bound"], "achieved": top["achieved"], "peak": top["peak"], "unit": top["unit"],
+           "frac": top["frac"], "traffic": tr.get("dram_bytes_per_launch"), "traffic_source": tr.get("source"),
+           "algorithmic_per_launch": top["algorithmic_per_launch"], "peak_source": peaks["source"],
+           "peaks": {k: peaks[k] for k in ("hbm_gbs", "bf16_tflops", "bf16_tflops_sustained", "balance_flop_per_byte")},
+           "launches_per_step": top["launches_per_step"], "avg_launch_us": top["ms_per_step"] / max(1, top["launches_per_step"]) * 1e3,
+           "how": f"CUDA events around every launch of the family on its own stream, {reps} steps, {mode}; algorithmic work per DESIGN.md §3; "
+                  "family spans on concurrent streams overlap, so their sum exceeds the step (see families_serialised)",
+           "families": sorted(fams, key=lambda f: -f["ms_per_step"])}
+    if ctx.get("world", 1) == 1 and not args.no_extras_serial:
+        # the same table with the library's side streams off (DTB_NO_SIDE_STREAM=1): every kernel alone on one stream, spans add up
+        try:
+            cmd = [sys.executable, os.path.abspath(__file__), "--workload", args.workload, "--steps", "5", "--warmup", "3", "--families-only",
+                   "--dropout", str(args.dropout)] + (["--batch", str(args.batch)] if args.batch else []) + (["--attn-type", ATTN_TYPE] if ATTN_TYPE else [])
+            r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=dict(os.environ, DTB_NO_SIDE_STREAM="1"))
+            ser = json.loads(r.stdout.strip().splitlines()[-1])
+            out["families_serialised"] = {"what": "DTB_NO_SIDE_STREAM=1: the whole step on one stream, family times add up to the step",
+                                          "ms_per_step": ser.get("ms_per_step"), "profiled_ms_per_step": ser["roofline"]["profiled_ms_per_step"],
+                                          "families": [{k: f.get(k) for k in ("kernel", "bound", "ms_per_step", "launches_per_step", "achieved", "unit", "frac")}
+                                                       for f in ser["roofline"]["families"]]}
+        except Exception as e:  # noqa: BLE001
+            out["families_serialised"] = {"error": str(e)[:200]}
+    return out
 
 
 def measure_get_action(wl, ctx, calls=300, warmup=50):
@@ -585,6 +637,9 @@ def main():
     ap.add_argument("--dropout", type=float, default=0.1, help="resid/attn/embd dropout of the training step (upstream default 0.1)")
     ap.add_argument("--no-optimizer-extra", action="store_true", help="skip the extra timing of the step + fused clip/AdamW")
     ap.add_argument("--attn-type", default=None, choices=["casl", "new"], help="modality attention of the encoders (reference --attn-type, src/utils.py:115); multimodal workloads only")
+    ap.add_argument("--restage-each-step", action="store_true", help="re-stage the bf16 weights inside every timed step (round-1 semantics)")
+    ap.add_argument("--families-only", action="store_true", help="print only the per-kernel-family table of one step (used for the serialised table)")
+    ap.add_argument("--no-extras-serial", action="store_true", help="skip the serialised (DTB_NO_SIDE_STREAM=1) family table sub-run")
     ap.add_argument("--no-extras", action="store_true", help="skip the other-workload summaries (c1 / c3 / c4) appended to the default line")
     args = ap.parse_args()
     global ATTN_TYPE
@@ -597,10 +652,10 @@ def main():
     if args.impl == "reference":
         if rank != 0:
             return
-        steps, warmup = min(args.steps, 10), min(args.warmup, 2)
-        r = run_cpu(wl, steps, max(warmup, 1), budget_s=60.0, pdrop=args.dropout)
+        steps, warmup = args.steps, args.warmup  # exactly what was asked for; the bounded sample (batch) is sized so that they fit ~2 minutes
+        r = run_cpu(wl, steps, warmup, budget_s=120.0, pdrop=args.dropout)
         line = {"impl": "reference", "metric": "DT train tokens/s (fwd+bwd)", "value": r["value"], "unit": "tokens/s", "n_gpus": args.gpus,
-                "steps": steps, "warmup": max(warmup, 1), "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak",
+                "steps": steps, "warmup": warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak",
                 "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": {"workload": wl["label"], "name": args.workload, "seq_len": 3 * wl["K"], "parallelism": "cpu", "dropout": args.dropout},
                 "cpu_baseline": r, "e2e": {"value": r["value"], "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},

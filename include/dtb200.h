@@ -43,6 +43,14 @@ long long dtb_launch_count(void);
  * 3 attention fwd (flops), 4 attention bwd (flops), 5 LN fwd (bytes), 6 LN bwd (bytes), 7 embed fwd (bytes), 8 colsum (bytes),
  * 9 im2col (bytes), 10 col2im (bytes).  report() synchronises the events and returns summed milliseconds, algorithmic work, launches. */
 void dtb_profile_enable(int on);
+/* machine balance (flop per byte: sustained bf16 peak / copy bandwidth of MEASURED_PEAKS.json) that splits GEMM launches into the
+ * tensor-bound family 0 and the HBM-bound family 11 */
+void dtb_profile_set_balance(double flop_per_byte);
+/* Runtime switches between kernel forms (A/B measurements and tests inside one process); unknown names are an error.
+ *   "splitk_inkernel" (default 0): split-K slices reduced by the last-arriving CTA inside the GEMM instead of a second launch
+ *   "ln_fused"        (default 1): LayerNorm in the c_proj GEMM epilogue when hidden <= 256
+ *   "conv_implicit"   (default 1): implicit-GEMM conv2 / conv3 (read when an encoder handle is created) */
+int dtb_set_option(const char* name, int value);
 int dtb_profile_report(int family, double* total_ms, double* work, long long* launches);
 /* timeline of the last profiled step: number of recorded launches, and launch i's family + [start, end] in ms from the first one */
 int dtb_profile_spans(void);

@@ -72,6 +72,9 @@ def _declare(lib):
     lib.dtb_last_error.restype = C.c_char_p
     lib.dtb_abi_version.restype = i
     lib.dtb_launch_count.restype = ll
+    lib.dtb_set_option.argtypes = [C.c_char_p, i]
+    lib.dtb_profile_set_balance.argtypes = [C.c_double]
+    lib.dtb_profile_set_balance.restype = None
     lib.dtb_profile_enable.argtypes = [i]
     lib.dtb_profile_enable.restype = None
     lib.dtb_profile_span.argtypes = [i, C.POINTER(i), C.POINTER(C.c_double), C.POINTER(C.c_double)]
@@ -216,6 +219,11 @@ def gemm_bf16_ln(A, B, M, N, K, gamma, beta, eps, ln_out, *, b_mn_major=False, b
     check(load().dtb_gemm_bf16_ln(stream_ptr(), ptr(A), C.c_int(A.stride(0)), 0, ptr(B), C.c_int(B.stride(0)), int(b_mn_major), M, N, K,
                                   C.byref(ep), ptr(gamma), ptr(beta), C.c_float(eps), ptr(ln_out), C.c_int(ln_out.stride(0)), ptr(mean),
                                   ptr(rstd)))
+
+
+def set_option(name: str, value: int):
+    """Runtime switch between kernel forms (see dtb_set_option in include/dtb200.h)."""
+    check(load().dtb_set_option(name.encode(), int(value)))
 
 
 # ---- thin op wrappers (used by tests and by the host-side model) ------------------------------------------------------

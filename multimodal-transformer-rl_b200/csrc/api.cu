@@ -22,6 +22,11 @@ int dtb_abi_version(void) { return DTB_ABI_VERSION; }
 const char* dtb_last_error(void) { return dtb::last_error(); }
 int dtb_check_device(void) { return dtb::require_sm100(); }
 long long dtb_launch_count(void) { return dtb::launch_count(); }
+int dtb_set_option(const char* name, int value) {
+  DTB_REQUIRE(name != nullptr, DTB_ERR_BAD_ARG, "dtb_set_option: null name");
+  return dtb::opt_set(name, value);
+}
+void dtb_profile_set_balance(double flop_per_byte) { dtb::opt_set_balance(flop_per_byte); }
 void dtb_profile_enable(int on) { dtb::prof_enable(on != 0); if (on) dtb::prof_reset(); }
 int dtb_profile_spans(void) { return dtb::prof_count(); }
 int dtb_profile_span(int i, int* family, double* start_ms, double* end_ms) { return dtb::prof_span(i, family, start_ms, end_ms); }

@@ -52,6 +52,13 @@ int cuda_fail(cudaError_t e, const char* what, const char* file, int line);
   } while (0)
 
 int num_sms();
+// runtime options (core.cu; C ABI: dtb_set_option / dtb_profile_set_balance)
+int opt_splitk_inkernel();
+int opt_ln_fused();
+int opt_conv_implicit();
+double opt_balance();
+void opt_set_balance(double flop_per_byte);
+int opt_set(const char* name, int value);
 void count_launch();
 long long launch_count();
 

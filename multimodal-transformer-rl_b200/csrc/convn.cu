@@ -433,12 +433,7 @@ __global__ void __launch_bounds__(256) convn_stage_dgrad_kernel(const float* __r
 
 // ---- host ------------------------------------------------------------------------------------------------------------------------
 bool convn_supported(int cin, int cout, int k, int stride) {
-  static int off = -1;
-  if (off < 0) {
-    const char* e = getenv("DTB_CONV_EXPLICIT");
-    off = (e && e[0] == '1') ? 1 : 0;
-  }
-  if (off) return false;
+  if (!opt_conv_implicit()) return false;  // dtb_set_option("conv_implicit", 0) / DTB_CONV_EXPLICIT=1: the im2col + GEMM + col2im path
   if (!(cin == 16 || cin == 32 || cin == 64) || !(cout == 32 || cout == 64)) return false;
   if ((k * k * cin) % 64 != 0 || k % (64 / cin) != 0 || stride < 1 || stride > 2 || k > 8) return false;
   // data gradient: every parity class must fill whole k-blocks

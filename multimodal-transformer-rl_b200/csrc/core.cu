@@ -32,6 +32,31 @@ bool pdl_enabled() {
   return on == 1;
 }
 
+// ---- runtime options (dtb_set_option): A/B switches between kernel forms inside one process; defaults from the environment ---------
+static int env_flag(const char* name, int dflt) {
+  const char* e = getenv(name);
+  return e ? (e[0] == '1' ? 1 : 0) : dflt;
+}
+struct Options {
+  int splitk_inkernel = env_flag("DTB_SPLITK_INKERNEL", 0);  // split-K slices reduced by the last-arriving CTA inside the GEMM
+  int ln_fused = !env_flag("DTB_LN_SEPARATE", 0);            // LayerNorm in the c_proj GEMM epilogue (H <= 256)
+  int conv_implicit = !env_flag("DTB_CONV_EXPLICIT", 0);     // implicit-GEMM conv2 / conv3 (read when an encoder is created)
+  double balance = 212.0;                                    // machine balance (flop / byte) that splits the GEMM profiling families
+};
+static Options& opts() { static Options o; return o; }
+int opt_splitk_inkernel() { return opts().splitk_inkernel; }
+int opt_ln_fused() { return opts().ln_fused; }
+int opt_conv_implicit() { return opts().conv_implicit; }
+double opt_balance() { return opts().balance; }
+void opt_set_balance(double b) { if (b > 0) opts().balance = b; }
+int opt_set(const char* name, int value) {
+  if (!strcmp(name, "splitk_inkernel")) opts().splitk_inkernel = value != 0;
+  else if (!strcmp(name, "ln_fused")) opts().ln_fused = value != 0;
+  else if (!strcmp(name, "conv_implicit")) opts().conv_implicit = value != 0;
+  else { set_error("dtb_set_option: unknown option '%s'", name); return DTB_ERR_BAD_ARG; }
+  return DTB_OK;
+}
+
 static long long g_launches = 0;
 void count_launch() { __atomic_add_fetch(&g_launches, 1, __ATOMIC_RELAXED); }
 long long launch_count() { return __atomic_load_n(&g_launches, __ATOMIC_RELAXED); }

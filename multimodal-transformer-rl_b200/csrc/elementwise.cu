@@ -64,14 +64,10 @@ int cast_bf16(cudaStream_t stream, const float* src, size_t n, bf16* dst) {
 constexpr int CS_SLABS_MAX = 1024;        // narrow matrices (conv bias grads, N = 32) need many row slabs to fill the GPU
 constexpr int CS_SCRATCH_MIN = 64 * 1024;  // floats
 
-// Column sums in ONE launch: grid (column groups, row slabs); every block writes its slab's partial row, takes a ticket on its column
-// group's counter, and the block that arrives last sums the group's slab partials in slab order (deterministic) into `out`.
-__global__ void __launch_bounds__(256) colsum_kernel(const bf16* __restrict__ x, int M, int N, int ld, float* __restrict__ scratch,
-                                                     unsigned int* __restrict__ counters, float* __restrict__ out, int accumulate) {
+__global__ void __launch_bounds__(256) colsum_stage1(const bf16* __restrict__ x, int M, int N, int ld, float* __restrict__ scratch) {
   pdl_trigger();
   pdl_wait();
   __shared__ float red[256][9];
-  __shared__ unsigned int s_last;
   const int cx = blockDim.x, ry = blockDim.y;
   const int col = (blockIdx.x * cx + threadIdx.x) * 8;
   const int slab = blockIdx.y, nslab = gridDim.y;
@@ -97,32 +93,23 @@ __global__ void __launch_bounds__(256) colsum_kernel(const bf16* __restrict__ x,
     *reinterpret_cast<float4*>(dst) = make_float4(acc[0], acc[1], acc[2], acc[3]);
     *reinterpret_cast<float4*>(dst + 4) = make_float4(acc[4], acc[5], acc[6], acc[7]);
   }
-  __threadfence();
+}
+
+__global__ void __launch_bounds__(256) colsum_stage2(const float* __restrict__ scratch, int nslab, int N, float* __restrict__ out,
+                                                     int accumulate) {
+  pdl_trigger();
+  pdl_wait();
+  __shared__ float red[8][33];
+  const int c = blockIdx.x * 32 + threadIdx.x;
+  float s = 0.f;
+  if (c < N)
+    for (int i = threadIdx.y; i < nslab; i += 8) s += scratch[(size_t)i * N + c];
+  red[threadIdx.y][threadIdx.x] = s;
   __syncthreads();
-  if (tid == 0) s_last = atomicAdd(counters + blockIdx.x, 1u) == (unsigned int)nslab - 1u ? 1u : 0u;
-  __syncthreads();
-  if (!s_last) return;
-  __threadfence();
-  // this column group's cx * 8 columns: thread (threadIdx.x, threadIdx.y) sums slabs threadIdx.y, + ry, ... of its 8 columns
-#pragma unroll
-  for (int e = 0; e < 8; ++e) acc[e] = 0.f;
-  if (col < N)
-    for (int i = threadIdx.y; i < nslab; i += ry) {
-      const float4 a = __ldcg(reinterpret_cast<const float4*>(scratch + (size_t)i * N + col));
-      const float4 b = __ldcg(reinterpret_cast<const float4*>(scratch + (size_t)i * N + col + 4));
-      acc[0] += a.x; acc[1] += a.y; acc[2] += a.z; acc[3] += a.w; acc[4] += b.x; acc[5] += b.y; acc[6] += b.z; acc[7] += b.w;
-    }
-#pragma unroll
-  for (int e = 0; e < 8; ++e) red[tid][e] = acc[e];
-  __syncthreads();
-  if (threadIdx.y == 0 && col < N) {
-    for (int i = 1; i < ry; ++i)
-#pragma unroll
-      for (int e = 0; e < 8; ++e) acc[e] += red[i * cx + threadIdx.x][e];
-#pragma unroll
-    for (int e = 0; e < 8; ++e) out[col + e] = accumulate ? out[col + e] + acc[e] : acc[e];
+  if (threadIdx.y == 0 && c < N) {
+    for (int i = 1; i < 8; ++i) s += red[i][threadIdx.x];
+    out[c] = accumulate ? out[c] + s : s;
   }
-  if (tid == 0) counters[blockIdx.x] = 0u;
 }
 
 size_t colsum_scratch_floats(int N) { return (size_t)64 * N > (size_t)CS_SCRATCH_MIN ? (size_t)64 * N : (size_t)CS_SCRATCH_MIN; }
@@ -141,11 +128,10 @@ int colsum_bf16(cudaStream_t stream, const bf16* x, int M, int N, int ld, float*
   if (nslab > CS_SLABS_MAX) nslab = CS_SLABS_MAX;
   if ((size_t)nslab * N > colsum_scratch_floats(N)) nslab = (int)(colsum_scratch_floats(N) / N);
   if (nslab < 1) nslab = 1;
-  unsigned int* counters = nullptr;
-  DTB_TRY(ticket_counters_take((unsigned int)colgroups, &counters));
-  DTB_REQUIRE(counters != nullptr, DTB_ERR_UNSUPPORTED, "colsum: too many column groups (%d)", colgroups);
   ProfScope prof(stream, PF_COLSUM, 2.0 * M * N);
-  DTB_LAUNCH(colsum_kernel, dim3(colgroups, nslab), dim3(cx, ry), 0, stream, x, M, N, ld, scratch, counters, out, accumulate);
+  DTB_LAUNCH(colsum_stage1, dim3(colgroups, nslab), dim3(cx, ry), 0, stream, x, M, N, ld, scratch);
+  DTB_CHECK_LAUNCH();
+  DTB_LAUNCH(colsum_stage2, (N + 31) / 32, dim3(32, 8), 0, stream, scratch, nslab, N, out, accumulate);
   DTB_CHECK_LAUNCH();
   return DTB_OK;
 }

@@ -116,14 +116,10 @@ int ticket_counters_take(unsigned int need, unsigned int** out) {
   g_sk_cursor += need;
   return DTB_OK;
 }
-static bool sk_inkernel_enabled() {
-  static int off = -1;
-  if (off < 0) {
-    const char* e = getenv("DTB_SPLITK_SEPARATE");
-    off = (e && e[0] == '1') ? 1 : 0;
-  }
-  return !off;
-}
+// Off by default: the slices of a tile are then summed by the few warps that own it (m_tiles x n_tiles x 4), a long chain of dependent
+// L2 round trips at the small-M/N, long-K weight-gradient shapes of c1-c3 (measured: c2 step 1.16 -> 2.0 ms), whereas the separate
+// splitk_reduce launch spreads the same sums over hundreds of blocks.  dtb_set_option("splitk_inkernel", 1) turns it on.
+static bool sk_inkernel_enabled() { return opt_splitk_inkernel() != 0; }
 
 size_t gemm_splitk_workspace_bytes(int M, int N, int K) {
   // upper bound used by callers that pre-size the workspace: split <= 32
@@ -237,14 +233,15 @@ int gemm_bf16(cudaStream_t stream, const bf16* A, int lda, int a_mn_major, const
     g_attr_set = true;
   }
   const int total = p.m_tiles * p.n_tiles * p.split_k;
-  // roofline family: a shape whose arithmetic intensity is below the machine balance (1 397 TFLOP/s / 6 457 GB/s = 216 flop/B,
-  // MEASURED_PEAKS.json) is HBM-bound; its work is counted in algorithmic bytes (operands once + every epilogue stream once)
+  // roofline family: a shape whose arithmetic intensity is below the machine balance (sustained bf16 peak / copy bandwidth of
+  // MEASURED_PEAKS.json, handed over by bench.py through dtb_profile_set_balance) is HBM-bound; its work is counted in algorithmic
+  // bytes (operands once + every epilogue stream once)
   const double flops = 2.0 * M * N * K, mn = (double)M * N;
   const double bytes = 2.0 * ((double)M * K + (double)K * N) +
                        (p.ep.partial ? 4.0 * mn * p.split_k
                                    : mn * ((p.ep.out_bf16 ? 2.0 : 0.0) + (p.ep.out_f32 ? 4.0 : 0.0) + (p.ep.out_preact ? 2.0 : 0.0) +
                                            (p.ep.residual ? 4.0 : 0.0) + (p.ep.dact ? 2.0 : 0.0)));
-  const bool mem_bound = flops < 216.0 * bytes;
+  const bool mem_bound = flops < opt_balance() * bytes;
   ProfScope prof(stream, mem_bound ? PF_GEMM_MEM : PF_GEMM, mem_bound ? bytes : flops);
   if (pair) {
     const int npairs = total < num_sms() / 2 ? total : num_sms() / 2;

@@ -153,14 +153,10 @@ static int gemm_fwd(cudaStream_t st, const bf16* A, int lda, const bf16* W, int 
   const int rc = gemm_bf16(st, A, lda, 0, W, ldw, w_mn_major ? 1 : 0, M, N, K, ep, 1, bn_override);
   return rc < 0 ? rc : DTB_OK;
 }
-// LayerNorm in the c_proj epilogue: the CTA must own whole rows (BN == H).  DTB_LN_SEPARATE=1 keeps the standalone ln_fwd launches.
+// LayerNorm in the c_proj epilogue: the CTA must own whole rows (BN == H).  dtb_set_option("ln_fused", 0) / DTB_LN_SEPARATE=1 keeps the
+// standalone ln_fwd launches.
 static bool dt_ln_fused(int H) {
-  static int off = -1;
-  if (off < 0) {
-    const char* e = getenv("DTB_LN_SEPARATE");
-    off = (e && e[0] == '1') ? 1 : 0;
-  }
-  return !off && H <= 256 && H % 64 == 0;  // BN == H must also be a legal MN-major B tile (multiple of 64)
+  return opt_ln_fused() && H <= 256 && H % 64 == 0;  // BN == H must also be a legal MN-major B tile (multiple of 64)
 }
 static void ep_set_ln(GemmEpilogue& ep, const float* gamma, const float* beta, bf16* out, int ld, float* mean, float* rstd, float eps) {
   ep.ln_gamma = gamma; ep.ln_beta = beta; ep.ln_out = out; ep.ld_ln = ld; ep.ln_mean = mean; ep.ln_rstd = rstd; ep.ln_eps = eps;

@@ -84,7 +84,9 @@ def test_encoder_forward_backward(cuda_device, frame_shape, audio_shape, conv_ty
 
 
 @pytest.mark.parametrize("cfg_name,frame_shape,audio_shape,B", [("c2", (3, 64, 64), (1, 64, 64), 4), ("c2", (1, 84, 84), (1, 84, 84), 2),
-                                                               ("c3", (3, 64, 64), (2, 64, 64), 2)])
+                                                               ("c3", (3, 64, 64), (2, 64, 64), 2),
+                                                               # the shapes bench.py times (BASELINE.json configs[1] / [2] at batch 64 per GPU)
+                                                               ("c2", (3, 64, 64), (1, 64, 64), 64), ("c3", (3, 64, 64), (2, 64, 64), 64)])
 def test_multimodal_dt_end_to_end(cuda_device, cfg_name, frame_shape, audio_shape, B):
     """frames + spectrograms -> towers -> state tokens -> DT -> masked action MSE; fused step vs the oracle's autograd."""
     from mtrl_b200.encoder import MultimodalDecisionTransformer

@@ -187,10 +187,18 @@ def test_gemm_splitk_reduced_in_kernel_is_deterministic(cuda_device, Mtok, Kin, 
     ref = X.float().t() @ dY.float()
     partial = torch.empty(split, Kin, Nout, device=dev)
     outs = []
-    for _ in range(3):
-        out = torch.full((Kin, Nout), float("nan"), device=dev)
-        _lib.gemm_bf16(X, dY, Kin, Nout, Mtok, a_mn_major=True, b_mn_major=True, out_f32=out, partial=partial, split_k=split)
-        torch.cuda.synchronize()
-        assert rel_err(out, ref) < 2e-3
-        outs.append(out)
+    _lib.set_option("splitk_inkernel", 1)
+    try:
+        for _ in range(3):
+            out = torch.full((Kin, Nout), float("nan"), device=dev)
+            _lib.gemm_bf16(X, dY, Kin, Nout, Mtok, a_mn_major=True, b_mn_major=True, out_f32=out, partial=partial, split_k=split)
+            torch.cuda.synchronize()
+            assert rel_err(out, ref) < 2e-3
+            outs.append(out)
+    finally:
+        _lib.set_option("splitk_inkernel", 0)
     assert torch.equal(outs[0], outs[1]) and torch.equal(outs[1], outs[2])
+    out = torch.full((Kin, Nout), float("nan"), device=dev)  # default: separate reduction launch (its own fixed summation order)
+    _lib.gemm_bf16(X, dY, Kin, Nout, Mtok, a_mn_major=True, b_mn_major=True, out_f32=out, partial=partial, split_k=split)
+    torch.cuda.synchronize()
+    assert rel_err(out, outs[0]) < 1e-6

@@ -25,7 +25,7 @@ def _oracle_step(oracle, s, a, r, t, m):
     return sp, ap, rp, loss
 
 
-@pytest.mark.parametrize("name,B", [("c1", 64), ("c2", 8), ("c3", 4), ("c4", 2)])
+@pytest.mark.parametrize("name,B", [("c1", 64), ("c2", 8), ("c3", 4), ("c4", 2), ("c2", 64), ("c3", 64), ("c4", 8)])
 def test_forward_loss_backward_fused(cuda_device, name, B):
     oracle, model, K = build_pair(name, cuda_device)
     cfg = CONFIGS[name]
