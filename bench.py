@@ -351,7 +351,8 @@ def run_ours(args, wl, rank, world, local_rank):
         "algorithmic_tflops_per_s": algorithmic_flops_per_step(wl, B * world) / ms / 1e9, "replicas_consistent": consistent,
         "train_step_with_optimizer": with_opt,
     }
-    return res, dict(model=model, parts=parts, dev=dev, dev_in=dev_in, step=step, world=world)
+    return res, dict(model=model, parts=parts, dev=dev, dev_in=dev_in, step=step, world=world, graph=slot["graph"] if graphed else None,
+                     graph_out=slot["out"])
 
 
 # ------------------------------------------------------------------------------------------------------------------------------
@@ -548,6 +549,148 @@ def measure_roofline(args, wl, ctx, reps=5):
     return out
 
 
+def measure_dp_parity(args, wl, ctx, rank, world):
+    """Correctness evidence for the N > 1 line (not only `replicas_consistent`): one un-timed step in eval mode (dropout off) on every
+    rank's own batch through the same GradAllReducer + grad_scale = 1/world path, then rank 0 compares its all-reduced flat gradients with
+    the uniformly averaged per-shard gradients of the fp32 oracle (the reference idiom, cleanrl/ppo_atari_multigpu.py:345-359), tensor
+    by tensor.  Every rank runs the step (it contains the collective); only rank 0 runs the oracle."""
+    from util import rel_err
+
+    model, parts, dev_in = ctx["model"], ctx["parts"], ctx["dev_in"]
+    from mtrl_b200.dp import GradAllReducer
+
+    was_training = [p.training for p in parts]
+    for p in parts:
+        p.eval()
+    red = GradAllReducer(bucket_bytes=args.bucket_mb << 20)
+    step = make_step(wl, model, parts, dev_in, red, 1.0 / world)
+    host = make_batch(wl, wl["B"], seed=1234 + rank)
+    for k, v in host.items():
+        dev_in[k].copy_(v)
+    out = step()
+    torch.cuda.synchronize()
+    res = None
+    if rank == 0:
+        oracle = build_oracle(wl, 0.0)
+        oracle.load_state_dict({k: v.detach().float().cpu() for k, v in model.state_dict().items()})
+        oracle.eval()
+        ref, losses = {}, []
+        for r in range(world):
+            losses.append(oracle_step(wl, oracle, make_batch(wl, wl["B"], seed=1234 + r)))
+            for n, p in oracle.named_parameters():
+                if p.grad is not None:
+                    ref[n] = ref.get(n, 0) + p.grad.detach() / world
+        errs = {n: rel_err(model.get_parameter(n).grad, g) for n, g in ref.items()}
+        worst = max(errs.items(), key=lambda kv: kv[1])
+        over = {n: round(e, 4) for n, e in errs.items() if e > 2e-2}
+        res = {"max_rel_err": worst[1], "worst_tensor": worst[0], "tensors": len(errs), "tensors_over_2e-2": over,
+               "loss_rank0": float(out[0]), "oracle_loss_rank0": losses[0],
+               "what": f"rank 0's all-reduced flat gradients vs the mean over {world} ranks of the fp32 oracle's per-shard gradients (dropout off, "
+                       "bf16 compute vs fp32: tensors behind a ReLU mask may exceed 2e-2 exactly as at N = 1, see BASELINE.md §4)"}
+    for p, t in zip(parts, was_training):
+        p.train(t)
+    return res
+
+
+def measure_library_bar(wl, dev, steps=10, warmup=3, pdrop=0.0):
+    """The 'library bar' of SURVEY.md §6 / §8d(ii): the fp32 oracle (plain PyTorch modules = cuBLAS / cuDNN / eager kernels) on the same
+    B200, fp32 and bf16 autocast, same batch, forward + loss + backward, CUDA-event timed."""
+    from oracle.trainer import masked_action_mse
+
+    out = {}
+    try:
+        model = build_oracle(wl, pdrop).to(dev)
+        model.train()
+        b = {k: v.to(dev) for k, v in make_batch(wl, wl["B"], seed=1234).items()}
+        if wl["enc"] is not None:
+            b["frames_f"] = b["frames"].float() * 2.0 / 255.0 - 1
+
+        def one(autocast):
+            model.zero_grad(set_to_none=True)
+            with torch.autocast("cuda", dtype=torch.bfloat16, enabled=autocast):
+                if wl["enc"] is None:
+                    _, ap, _ = model(b["states"], b["actions"], None, b["rtg"], b["timesteps"], b["mask"])
+                else:
+                    _, ap, _ = model(b["frames_f"], b["audio"], b["actions"], None, b["rtg"], b["timesteps"], b["mask"])
+                loss = masked_action_mse(ap.float(), b["actions"], b["mask"])
+            loss.backward()
+
+        tokens = wl["B"] * 3 * wl["K"]
+        for name, ac in (("eager_fp32", False), ("eager_bf16_autocast", True)):
+            for _ in range(warmup):
+                one(ac)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            torch.cuda.synchronize(dev)
+            e0.record()
+            for _ in range(steps):
+                one(ac)
+            e1.record()
+            torch.cuda.synchronize(dev)
+            ms = e0.elapsed_time(e1) / steps
+            out[name] = {"ms_per_step": ms, "value": tokens / ms * 1e3, "unit": "tokens/s"}
+        out["what"] = ("oracle/ (plain torch.nn modules: cuBLAS / cuDNN / eager elementwise kernels) on this B200, device-resident inputs, "
+                       f"fwd + masked MSE + bwd, {steps} steps after {warmup} warm-up, no CUDA graph (launch-bound like any eager loop)")
+    except Exception as e:  # noqa: BLE001
+        out["error"] = str(e)[:200]
+    return out
+
+
+def measure_e2e_resident(args, wl, ctx, steps):
+    """e2e with the trajectories RESIDENT in HBM (mtrl_b200.data.GpuTrajectoryStore): every step samples (trajectory,
+    start) pairs on the host with upstream's RNG calls, ships the 2 x B int64 indices, builds the batch with one dtb_get_batch launch
+    (raw uint8 frame rows and spectrogram rows included), runs the same captured step and reads the loss back."""
+    import numpy as np
+
+    from mtrl_b200.data import GpuTrajectoryStore
+
+    dev, dev_in, K, B = ctx["dev"], ctx["dev_in"], wl["K"], wl["B"]
+    rng = np.random.default_rng(99)
+    ad = wl["dt"]["act_dim"]
+    trajs = []
+    for _ in range(128):
+        T = int(rng.integers(K, 2 * K + 1))
+        t = {"actions": np.eye(ad, dtype=np.float32)[rng.integers(0, ad, T)] if not wl["dt"]["action_tanh"] else rng.uniform(-1, 1, (T, ad)).astype(np.float32),
+             "rewards": rng.uniform(-1, 1, T).astype(np.float32), "terminals": np.zeros(T, dtype=np.float32)}
+        if wl["enc"] is None:
+            t["observations"] = rng.standard_normal((T, wl["dt"]["state_dim"])).astype(np.float32)
+        else:
+            t["frames"] = rng.integers(0, 256, (T, *wl["enc"]["frame_shape"]), dtype=np.uint8)
+            t["audio"] = np.clip(rng.standard_normal((T, *wl["enc"]["audio_shape"])), -1, 1).astype(np.float32)
+        trajs.append(t)
+    store = GpuTrajectoryStore(trajs, raw_keys=() if wl["enc"] is None else ("frames", "audio"), device=dev)
+    get_batch = store.make_get_batch(K, MAX_EP_LEN, 1000.0, with_raw=True)
+    graph = ctx.get("graph")
+    loss_host = torch.empty(2, dtype=torch.float32).pin_memory()
+
+    def one():
+        (s, a, r, d, rtg, ts, m), raws = get_batch(B)
+        dev_in["actions"].copy_(a); dev_in["rtg"].copy_(rtg[:, :-1]); dev_in["timesteps"].copy_(ts); dev_in["mask"].copy_(m)
+        if wl["enc"] is None:
+            dev_in["states"].copy_(s)
+        else:
+            dev_in["frames"].copy_(raws["frames"]); dev_in["audio"].copy_(raws["audio"])
+        if graph is not None:
+            graph.replay()
+            out = ctx["graph_out"]
+        else:
+            out = ctx["step"]()
+        loss_host.copy_(out[:2], non_blocking=True)
+        torch.cuda.current_stream(dev).synchronize()
+        return float(loss_host[0])
+
+    for _ in range(3):
+        one()
+    torch.cuda.synchronize(dev)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        loss = one()
+    torch.cuda.synchronize(dev)
+    ms = (time.perf_counter() - t0) / steps * 1e3
+    return {"value": B * 3 * K / ms * 1e3, "unit": "tokens/s", "ms_per_step": ms, "h2d_bytes_per_step": 16 * B, "d2h_bytes_per_step": 8, "loss": loss,
+            "what": "trajectories (raw uint8 frames / spectrograms / actions / rewards) resident in HBM; per step: host RNG sampling, 2 x B int64 "
+                    "indices over PCIe, one dtb_get_batch launch, device-to-device hand-over to the captured step, loss read-back + sync"}
+
+
 def measure_get_action(wl, ctx, calls=300, warmup=50):
     """BASELINE.json's second metric: get_action latency at B = 1 with a full K-step history, through the public API
     (wall clock, one stream sync per call, p50 / p90 / p99 in microseconds)."""
@@ -639,6 +782,7 @@ def main():
     ap.add_argument("--attn-type", default=None, choices=["casl", "new"], help="modality attention of the encoders (reference --attn-type, src/utils.py:115); multimodal workloads only")
     ap.add_argument("--restage-each-step", action="store_true", help="re-stage the bf16 weights inside every timed step (round-1 semantics)")
     ap.add_argument("--families-only", action="store_true", help="print only the per-kernel-family table of one step (used for the serialised table)")
+    ap.add_argument("--no-dp-parity", action="store_true", help="N > 1: skip the gradient parity check against the oracle's averaged per-shard gradients")
     ap.add_argument("--no-extras-serial", action="store_true", help="skip the serialised (DTB_NO_SIDE_STREAM=1) family table sub-run")
     ap.add_argument("--no-extras", action="store_true", help="skip the other-workload summaries (c1 / c3 / c4) appended to the default line")
     args = ap.parse_args()
@@ -671,7 +815,12 @@ def main():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         torch.cuda.set_device(local_rank)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    if args.families_only:
+        args.no_optimizer_extra = True
     res, ctx = run_ours(args, wl, rank, world, local_rank)
+    if args.families_only:
+        print(json.dumps({"ms_per_step": res["ms_per_step"], "roofline": measure_roofline(args, wl, ctx)}), flush=True)
+        return
     if not args.no_roofline:
         # every rank runs it (the profiled steps contain the gradient all-reduce at N > 1: a collective on rank 0 alone would hang)
         try:
@@ -680,7 +829,20 @@ def main():
             roof = {"error": str(e)}
         if rank == 0:
             res["roofline"] = roof
+    if world > 1 and not args.no_dp_parity:
+        try:
+            dpp = measure_dp_parity(args, wl, ctx, rank, world)
+        except Exception as e:  # noqa: BLE001
+            dpp = {"error": str(e)[:300]}
+        if rank == 0:
+            res["dp_parity"] = dpp
     if rank == 0:
+        if world == 1 and not args.no_extras:
+            try:
+                res["e2e"]["resident"] = measure_e2e_resident(args, wl, ctx, args.steps)
+            except Exception as e:  # noqa: BLE001
+                res["e2e"]["resident"] = {"error": str(e)[:300]}
+            res["library_bar"] = measure_library_bar(wl, ctx["dev"], pdrop=args.dropout)
         if world == 1 and not args.no_get_action:
             try:
                 res["get_action"] = measure_get_action(wl, ctx)
