@@ -248,20 +248,27 @@ __global__ void __launch_bounds__(C1_THREADS, 1) conv1_wgrad_kernel(const __grid
   uint8_t* smP = smem;                                            // [stages][C][128 lines][128 B]
   uint8_t* smZ = smP + (size_t)p.stages * stage_bytes;            // [stages][128 lines][128 B]
   uint8_t* smZero = smZ + (size_t)p.stages * C1_KB_BYTES;         // [128 lines][128 B] zeros
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smZero + C1_KB_BYTES);
+  uint8_t* smOnes = smZero + C1_KB_BYTES;                         // [128 lines][128 B]: element (line, n = 0) = 1 -> D[C][:, 0] = db
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smOnes + C1_KB_BYTES);
   uint64_t* full_bar = bars;         // [stages] 128 producer arrivals + 1 TMA (expect_tx) arrival
   uint64_t* empty_bar = bars + 4;    // [stages]
   uint64_t* done_bar = bars + 8;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 9);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  for (int i = threadIdx.x; i < C1_KB_BYTES / 16; i += blockDim.x) reinterpret_cast<uint4*>(smZero)[i] = make_uint4(0, 0, 0, 0);
+  for (int i = threadIdx.x; i < 2 * C1_KB_BYTES / 16; i += blockDim.x) reinterpret_cast<uint4*>(smZero)[i] = make_uint4(0, 0, 0, 0);
+  __syncthreads();
+  if (threadIdx.x < 128) {  // n = 0 is the first bf16 of 16-byte unit 0, which the 128B swizzle places at unit (0 ^ (line & 7))
+    const int r = threadIdx.x;
+    *reinterpret_cast<uint16_t*>(smOnes + r * 128 + ((r & 7) << 4)) = 0x3F80;  // bf16 1.0
+  }
   if (threadIdx.x == 0) {
     for (int s = 0; s < p.stages; ++s) { mbar_init(&full_bar[s], C1_PRODUCERS + 1); mbar_init(&empty_bar[s], 1); }
     mbar_init(done_bar, 1);
     fence_mbar_init();
   }
-  if (warp == C1_MMA_WARP) { tmem_alloc(tmem_slot, 256); tmem_relinquish(); }
+  const uint32_t tmem_cols = (p.C + 1) * 64 <= 256 ? 256u : 512u;
+  if (warp == C1_MMA_WARP) { tmem_alloc(tmem_slot, tmem_cols); tmem_relinquish(); }
   fence_proxy_async();
   tc_fence_before();
   __syncthreads();
@@ -300,6 +307,11 @@ __global__ void __launch_bounds__(C1_THREADS, 1) conv1_wgrad_kernel(const __grid
           for (int ks = 0; ks < 8; ++ks)  // 16 patch rows per MMA
             umma_bf16(tmem_base + c * 64, make_smem_desc_sw128(z0 + ks * 2048, zero_addr - z0, 1024),
                       make_smem_desc_sw128(p0 + c * C1_KB_BYTES + ks * 2048, 16, 1024), idesc, (i > 0 || ks > 0) ? 1u : 0u);
+        // bias gradient: the same dZ^T tile against the constant ones chunk (column 0 of accumulator block C = sum over the patch rows)
+#pragma unroll
+        for (int ks = 0; ks < 8; ++ks)
+          umma_bf16(tmem_base + p.C * 64, make_smem_desc_sw128(z0 + ks * 2048, zero_addr - z0, 1024),
+                    make_smem_desc_sw128(smem_u32(smOnes) + ks * 2048, 16, 1024), idesc, (i > 0 || ks > 0) ? 1u : 0u);
         umma_commit(&empty_bar[stage]);
         if (++stage == (uint32_t)p.stages) { stage = 0; phase ^= 1; }
       }
@@ -309,9 +321,9 @@ __global__ void __launch_bounds__(C1_THREADS, 1) conv1_wgrad_kernel(const __grid
     // quadrant 0 holds output rows 0..31 = cout channels
     mbar_wait(done_bar, 0);
     tc_fence_after();
-    const int K = 64 * p.C;
+    const int K = 64 * (p.C + 1);  // + the ones block (only its column 0 is meaningful)
     float* dst = p.partial + ((size_t)blockIdx.x * p.cout + lane) * K;
-    for (int c = 0; c < p.C; ++c)
+    for (int c = 0; c <= p.C; ++c)
       for (int h = 0; h < 2; ++h) {
         uint32_t v[32];
         tmem_ld_32x32(tmem_base + c * 64 + h * 32, v);
@@ -327,7 +339,22 @@ __global__ void __launch_bounds__(C1_THREADS, 1) conv1_wgrad_kernel(const __grid
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == C1_MMA_WARP) { tc_fence_after(); tmem_dealloc(tmem_base, 256); }
+  if (warp == C1_MMA_WARP) { tc_fence_after(); tmem_dealloc(tmem_base, tmem_cols); }
+}
+
+// per-CTA partials [ncta][cout][64 (C + 1)] -> dw [cout][64 C] (PyTorch order) and db [cout] (column 64 C), CTAs added in index order
+__global__ void __launch_bounds__(256) conv1_wgrad_reduce_kernel(const float* __restrict__ partial, int ncta, int cout, int C,
+                                                                 float* __restrict__ dw, float* __restrict__ db) {
+  pdl_trigger();
+  pdl_wait();
+  const int Kp = 64 * (C + 1), K = 64 * C;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < cout * (K + 1); i += gridDim.x * blockDim.x) {
+    const int m = i / (K + 1), kk = i - m * (K + 1);
+    float s = 0.f;
+    for (int c = 0; c < ncta; ++c) s += __ldg(partial + ((size_t)c * cout + m) * Kp + kk);
+    if (kk < K) dw[(size_t)m * K + kk] = s;
+    else if (db) db[m] = s;
+  }
 }
 
 // ---- host ------------------------------------------------------------------------------------------------------------------------
@@ -369,18 +396,22 @@ int conv1_fwd(cudaStream_t stream, const void* x, int x_u8, int N, int C, int H,
   return DTB_OK;
 }
 
-size_t conv1_wgrad_partial_floats(int C, int cout) { return (size_t)DTB_NUM_SMS_FALLBACK * cout * 64 * C; }
+size_t conv1_wgrad_partial_floats(int C, int cout) { return (size_t)DTB_NUM_SMS_FALLBACK * cout * 64 * (C + 1); }
 
 int conv1_wgrad(cudaStream_t stream, const void* x, int x_u8, int N, int C, int H, int W, int stride, float scale, const bf16* dz, int cout,
-                float* partial, float* dw) {
+                float* partial, float* dw, float* db) {
   Conv1Params p;
   DTB_TRY(c1_params(p, x, x_u8, N, C, H, W, stride, scale, cout));
-  if (p.rows == 0) { DTB_CUDA(cudaMemsetAsync(dw, 0, (size_t)cout * 64 * C * sizeof(float), stream)); return DTB_OK; }
+  if (p.rows == 0) {
+    DTB_CUDA(cudaMemsetAsync(dw, 0, (size_t)cout * 64 * C * sizeof(float), stream));
+    if (db) DTB_CUDA(cudaMemsetAsync(db, 0, (size_t)cout * sizeof(float), stream));
+    return DTB_OK;
+  }
   p.partial = partial;
   p.stages = 2;
   CUtensorMap tmZ;
   DTB_TRY(make_tmap(&tmZ, dz, (uint64_t)cout, (uint64_t)p.rows, (uint64_t)cout, 64, 128));
-  const int smem = 1024 + p.stages * (C + 1) * C1_KB_BYTES + C1_KB_BYTES + 256 + 512;
+  const int smem = 1024 + p.stages * (C + 1) * C1_KB_BYTES + 2 * C1_KB_BYTES + 256 + 512;
   static bool attr = false;
   if (!attr) { DTB_CUDA(cudaFuncSetAttribute(conv1_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 225 * 1024)); attr = true; }
   int grid = p.tiles < num_sms() ? p.tiles : num_sms();
@@ -390,7 +421,10 @@ int conv1_wgrad(cudaStream_t stream, const void* x, int x_u8, int N, int C, int 
   DTB_CHECK_LAUNCH();
   prof.~ProfScope();
   prof.slot = -1;
-  return splitk_reduce(stream, partial, grid, cout, 64 * C, dw, 64 * C, 0, 1.f);
+  const int total = cout * (64 * C + 1);
+  DTB_LAUNCH(conv1_wgrad_reduce_kernel, (total + 255) / 256, 256, 0, stream, partial, grid, cout, C, dw, db);
+  DTB_CHECK_LAUNCH();
+  return DTB_OK;
 }
 
 }  // namespace dtb

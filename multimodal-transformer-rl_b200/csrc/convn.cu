@@ -49,8 +49,9 @@ __device__ __forceinline__ void cn_store_chunk(uint32_t tile_base, int r, int u,
 }
 
 // ================================================================================================================================
-// forward + data gradient share one kernel skeleton: 128-row tiles, one k-block (128 rows x 64 k) per pipeline stage, every producer
-// thread owns one tile row and four consecutive 16-byte chunks of it; the next k-block's loads are issued before the current one is stored.
+// forward + data gradient share one kernel skeleton: 128-row tiles, one k-block (128 rows x 64 k) per pipeline stage; producer lanes are
+// laid out so that every load instruction reads whole 128-byte lines (first version: one row per thread = 32 lines per instruction,
+// 256 mbarrier arrivals per k-block: 3.2 us per k-block at c2).
 // ================================================================================================================================
 template <bool DGRAD>
 __global__ void __launch_bounds__(CN_THREADS, 1) convn_kernel(const __grid_constant__ CUtensorMap tmW, const ConvNParams p) {
@@ -71,7 +72,7 @@ __global__ void __launch_bounds__(CN_THREADS, 1) convn_kernel(const __grid_const
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (threadIdx.x == 0) {
-    for (int s = 0; s < p.stages; ++s) { mbar_init(&full_bar[s], CN_PRODUCERS); mbar_init(&empty_bar[s], 1); }
+    for (int s = 0; s < p.stages; ++s) { mbar_init(&full_bar[s], CN_PRODUCERS / 32); mbar_init(&empty_bar[s], 1); }  // one arrival per producer warp
     for (int s = 0; s < 2; ++s) { mbar_init(&tfull_bar[s], 1); mbar_init(&tempty_bar[s], 4); }
     mbar_init(w_bar, 1);
     fence_mbar_init();
@@ -93,73 +94,78 @@ __global__ void __launch_bounds__(CN_THREADS, 1) convn_kernel(const __grid_const
 
   if (warp < CN_EPI_WARP0) {
     // ===== patch producers =====
-    const int r = threadIdx.x & 127, u0 = (threadIdx.x >> 7) * 4;
+    // Warp w owns rows 16 w .. 16 w + 15 of the tile; one load instruction covers 4 rows x 8 chunks = four whole 128-byte lines
+    // (lane = 8 * row + chunk), so a k-block costs every thread 4 loads (rows rq, rq + 4, rq + 8, rq + 12) and 4 conflict-free swizzled
+    // stores; loads run two k-blocks ahead of the stores; one mbarrier arrival per warp.
+    const int u = lane & 7, rq = warp * 16 + (lane >> 3);
     uint32_t stage = 0, phase = 0;
     for (int t = blockIdx.x; t < p.tiles; t += gridDim.x) {
       const int cls = tile_class(t);
-      // this thread's row of the tile
-      bool row_ok;
-      int n = 0, a = 0, b = 0;  // fwd: (n, oh, ow); dgrad: (n, ih / stride, iw / stride) within the class
-      int nkb, kb0 = 0;
-      if (!DGRAD) {
-        const long long m = (long long)t * 128 + r;
-        row_ok = m < p.rows;
-        const uint32_t mu = (uint32_t)(row_ok ? m : 0);
-        b = (int)(mu % (uint32_t)p.wo);
-        const uint32_t q = mu / (uint32_t)p.wo;
-        a = (int)(q % (uint32_t)p.ho);
-        n = (int)(q / (uint32_t)p.ho);
-        nkb = p.nkb;
-      } else {
-        const long long m = (long long)(t - p.cls_tile0[cls]) * 128 + r;
-        const int na = p.cls_na[cls], nb = p.cls_nb[cls];
-        row_ok = m < (long long)p.N * na * nb;
-        const uint32_t mu = (uint32_t)(row_ok ? m : 0);
-        b = (int)(mu % (uint32_t)nb);
-        const uint32_t q = mu / (uint32_t)nb;
-        a = (int)(q % (uint32_t)na);
-        n = (int)(q / (uint32_t)na);
-        nkb = p.cls_nkb[cls];
-        kb0 = p.cls_kb0[cls];
+      const int nkb = DGRAD ? p.cls_nkb[cls] : p.nkb;
+      // per row: element offset of the row's anchor in p.x (fwd: first patch element; dgrad: dZ pixel (n, a, b) channel 0), or -1
+      long long base[4];
+      int ra[4], rb[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int r = rq + 4 * j;
+        if (!DGRAD) {
+          const long long m = (long long)t * 128 + r;
+          const bool ok = m < p.rows;
+          const uint32_t mu = (uint32_t)(ok ? m : 0);
+          const int ow = (int)(mu % (uint32_t)p.wo);
+          const uint32_t q = mu / (uint32_t)p.wo;
+          const int oh = (int)(q % (uint32_t)p.ho), n = (int)(q / (uint32_t)p.ho);
+          base[j] = ok ? (((long long)n * p.hin + (long long)oh * p.stride) * p.win + (long long)ow * p.stride) * p.cin : -1;
+          ra[j] = rb[j] = 0;
+        } else {
+          const long long m = (long long)(t - p.cls_tile0[cls]) * 128 + r;
+          const int na = p.cls_na[cls], nb = p.cls_nb[cls];
+          const bool ok = m < (long long)p.N * na * nb;
+          const uint32_t mu = (uint32_t)(ok ? m : 0);
+          rb[j] = (int)(mu % (uint32_t)nb);
+          const uint32_t q = mu / (uint32_t)nb;
+          ra[j] = (int)(q % (uint32_t)na);
+          const int n = (int)(q / (uint32_t)na);
+          base[j] = ok ? (((long long)n * p.ho + ra[j]) * p.wo + rb[j]) * p.cout : -1;
+        }
       }
-      (void)kb0;
-      // source of this thread's four chunks of k-block kb (nullptr: structural zero / row beyond the tensor)
-      auto src_of = [&](int kb) -> const uint4* {
-        if (!row_ok) return nullptr;
+      auto load4 = [&](uint4 (&v)[4], int kb) {
         if (!DGRAD) {
           const int tap0 = kb * (64 / p.cin);  // the k-block's taps are consecutive kw of one kernel row: contiguous in NHWC
           const int kh = tap0 / p.k, kw0 = tap0 - kh * p.k;
-          const size_t off = (((size_t)n * p.hin + (size_t)a * p.stride + kh) * p.win + (size_t)b * p.stride + kw0) * p.cin + (size_t)u0 * 8;
-          return reinterpret_cast<const uint4*>(p.x + off);
+          const long long off = ((long long)kh * p.win + kw0) * p.cin + u * 8;
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            v[j] = base[j] >= 0 ? __ldg(reinterpret_cast<const uint4*>(p.x + base[j] + off)) : make_uint4(0, 0, 0, 0);
         } else {
-          const int e0 = kb * 64 + u0 * 8;           // first K index (tap, cout) of the four chunks: they never straddle a tap
+          const int e0 = kb * 64 + u * 8;  // K index (tap, cout) of this lane's chunk
           const int tt = e0 / p.cout, co = e0 - tt * p.cout;
           const int ntw = p.cls_ntw[cls];
-          const int dkh = tt / ntw, dkw = tt - dkh * ntw;
-          const int oh = a - dkh, ow = b - dkw;       // kh = ph + dkh * stride  ->  oh = (ih - kh) / stride = a - dkh
-          if (oh < 0 || oh >= p.ho || ow < 0 || ow >= p.wo) return nullptr;
-          const size_t off = (((size_t)n * p.ho + oh) * p.wo + ow) * p.cout + co;
-          return reinterpret_cast<const uint4*>(p.x + off);
+          const int dkh = tt / ntw, dkw = tt - dkh * ntw;  // kh = ph + dkh * stride  ->  oh = (ih - kh) / stride = a - dkh
+          const long long off = -((long long)dkh * p.wo + dkw) * p.cout + co;
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const int oh = ra[j] - dkh, ow = rb[j] - dkw;
+            const bool ok = base[j] >= 0 && oh >= 0 && ow >= 0 && oh < p.ho && ow < p.wo;  // else: the tap falls outside dZ (structural zero)
+            v[j] = ok ? __ldg(reinterpret_cast<const uint4*>(p.x + base[j] + off)) : make_uint4(0, 0, 0, 0);
+          }
         }
       };
-      uint4 cur[4], nxt[4];
-      auto load4 = [&](uint4 (&v)[4], int kb) {
-        const uint4* s = src_of(kb);
-#pragma unroll
-        for (int j = 0; j < 4; ++j) v[j] = s ? __ldg(s + j) : make_uint4(0, 0, 0, 0);
-      };
-      load4(cur, 0);
+      uint4 c0[4], c1[4], c2[4];
+      load4(c0, 0);
+      if (nkb > 1) load4(c1, 1);
       for (int kb = 0; kb < nkb; ++kb) {
-        if (kb + 1 < nkb) load4(nxt, kb + 1);
+        if (kb + 2 < nkb) load4(c2, kb + 2);
         mbar_wait(&empty_bar[stage], phase ^ 1);
         const uint32_t tile_base = smem_u32(smA + (size_t)stage * CN_KB128);
 #pragma unroll
-        for (int j = 0; j < 4; ++j) cn_store_chunk(tile_base, r, u0 + j, cur[j]);
+        for (int j = 0; j < 4; ++j) cn_store_chunk(tile_base, rq + 4 * j, u, c0[j]);
         fence_proxy_async();  // generic-proxy stores -> visible to the tensor core (async proxy)
-        mbar_arrive(&full_bar[stage]);
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&full_bar[stage]);
         if (++stage == (uint32_t)p.stages) { stage = 0; phase ^= 1; }
 #pragma unroll
-        for (int j = 0; j < 4; ++j) cur[j] = nxt[j];
+        for (int j = 0; j < 4; ++j) { c0[j] = c1[j]; c1[j] = c2[j]; }
       }
     }
   } else if (warp == CN_MMA_WARP) {
@@ -281,7 +287,7 @@ __global__ void __launch_bounds__(CN_THREADS, 1) convn_wgrad_kernel(const __grid
     *reinterpret_cast<uint16_t*>(smOnes + r * 128 + ((r & 7) << 4)) = 0x3F80;  // bf16 1.0
   }
   if (threadIdx.x == 0) {
-    for (int s = 0; s < 2; ++s) { mbar_init(&full_bar[s], CN_PRODUCERS + 1); mbar_init(&empty_bar[s], 1); }
+    for (int s = 0; s < 2; ++s) { mbar_init(&full_bar[s], CN_PRODUCERS / 32 + 1); mbar_init(&empty_bar[s], 1); }  // producer warps + the TMA's expect_tx arrival
     mbar_init(done_bar, 1);
     fence_mbar_init();
   }
@@ -296,22 +302,27 @@ __global__ void __launch_bounds__(CN_THREADS, 1) convn_wgrad_kernel(const __grid
   const int my_tiles = p.tiles > (int)blockIdx.x ? (p.tiles - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
 
   if (warp < CN_EPI_WARP0) {
-    const int r = threadIdx.x & 63, u0 = (threadIdx.x >> 6) * 2;  // one patch row, two 16-byte chunks of every k-block
+    // warp w owns patch rows 8 w .. 8 w + 7 of the 64-row tile; a load instruction covers 4 rows x 8 chunks (whole 128-byte lines)
+    const int u = lane & 7, rq = warp * 8 + (lane >> 3);
     uint32_t stage = 0, phase = 0;
     for (int t = blockIdx.x; t < p.tiles; t += gridDim.x) {
-      const long long m = (long long)t * 64 + r;
-      const bool row_ok = m < p.rows;
-      const uint32_t mu = (uint32_t)(row_ok ? m : 0);
-      const int ow = (int)(mu % (uint32_t)p.wo);
-      const uint32_t q = mu / (uint32_t)p.wo;
-      const int oh = (int)(q % (uint32_t)p.ho), n = (int)(q / (uint32_t)p.ho);
-      const bf16* base = p.x + (((size_t)n * p.hin + (size_t)oh * p.stride) * p.win + (size_t)ow * p.stride) * p.cin + (size_t)u0 * 8;
+      long long base[2];
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        const long long m = (long long)t * 64 + rq + 4 * j;
+        const bool ok = m < p.rows;
+        const uint32_t mu = (uint32_t)(ok ? m : 0);
+        const int ow = (int)(mu % (uint32_t)p.wo);
+        const uint32_t q = mu / (uint32_t)p.wo;
+        const int oh = (int)(q % (uint32_t)p.ho), n = (int)(q / (uint32_t)p.ho);
+        base[j] = ok ? (((long long)n * p.hin + (long long)oh * p.stride) * p.win + (long long)ow * p.stride) * p.cin + u * 8 : -1;
+      }
       auto load2 = [&](uint4 (&v)[2], int kb) {
         const int tap0 = kb * (64 / p.cin);
         const int kh = tap0 / p.k, kw0 = tap0 - kh * p.k;
-        const uint4* s = reinterpret_cast<const uint4*>(base + ((size_t)kh * p.win + kw0) * p.cin);
-        v[0] = row_ok ? __ldg(s) : make_uint4(0, 0, 0, 0);
-        v[1] = row_ok ? __ldg(s + 1) : make_uint4(0, 0, 0, 0);
+        const long long off = ((long long)kh * p.win + kw0) * p.cin;
+#pragma unroll
+        for (int j = 0; j < 2; ++j) v[j] = base[j] >= 0 ? __ldg(reinterpret_cast<const uint4*>(p.x + base[j] + off)) : make_uint4(0, 0, 0, 0);
       };
       mbar_wait(&empty_bar[stage], phase ^ 1);
       uint8_t* st = smS + (size_t)stage * stage_bytes;
@@ -319,17 +330,21 @@ __global__ void __launch_bounds__(CN_THREADS, 1) convn_wgrad_kernel(const __grid
         mbar_arrive_expect_tx(&full_bar[stage], CN_KB64);
         tma_load_2d(st + (size_t)p.nkb * CN_KB64, &tmZ, &full_bar[stage], 0, t * 64);
       }
-      uint4 cur[2], nxt[2];
-      load2(cur, 0);
+      uint4 c0[2], c1[2], c2[2], c3[2];
+      load2(c0, 0);
+      if (p.nkb > 1) load2(c1, 1);
+      if (p.nkb > 2) load2(c2, 2);
       for (int kb = 0; kb < p.nkb; ++kb) {
-        if (kb + 1 < p.nkb) load2(nxt, kb + 1);
+        if (kb + 3 < p.nkb) load2(c3, kb + 3);
         const uint32_t img = smem_u32(st + (size_t)kb * CN_KB64);
-        cn_store_chunk(img, r, u0, cur[0]);
-        cn_store_chunk(img, r, u0 + 1, cur[1]);
-        cur[0] = nxt[0]; cur[1] = nxt[1];
+        cn_store_chunk(img, rq, u, c0[0]);
+        cn_store_chunk(img, rq + 4, u, c0[1]);
+#pragma unroll
+        for (int j = 0; j < 2; ++j) { c0[j] = c1[j]; c1[j] = c2[j]; c2[j] = c3[j]; }
       }
       fence_proxy_async();
-      mbar_arrive(&full_bar[stage]);
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&full_bar[stage]);
       if (++stage == 2) { stage = 0; phase ^= 1; }
     }
   } else if (warp == CN_MMA_WARP) {

@@ -259,7 +259,9 @@ static int tower_backward(const dtb_encoder* e, int ti, cudaStream_t st, const b
     }
     if (i == 0 && tw.P[0] == nullptr) {
       DTB_REQUIRE(x != nullptr, DTB_ERR_BAD_ARG, "encoder backward: frames / audio are needed again for the implicit conv1 weight gradient");
-      DTB_TRY(conv1_wgrad(ss, x, x_u8, N, cs.cin, cs.hin, cs.win, cs.stride, e->c.input_scale, tw.dZ[0], cs.cout, tw.c1_partial, G + t.w_off[0]));
+      DTB_TRY(conv1_wgrad(ss, x, x_u8, N, cs.cin, cs.hin, cs.win, cs.stride, e->c.input_scale, tw.dZ[0], cs.cout, tw.c1_partial, G + t.w_off[0],
+                          G + t.b_off[0]));  // weight and bias gradient in one pass
+      continue;
     } else if (i == 0) {
       DTB_TRY(gemm_wgrad(ss, tw.dZ[0], cs.cout, tw.P[0], kc, cs.cout, kc, rows, G + t.w_off[0], kc, partial, w.partial_floats));
     } else {

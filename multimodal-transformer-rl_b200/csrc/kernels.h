@@ -143,7 +143,7 @@ int conv1_fwd(cudaStream_t stream, const void* x, int x_u8, int N, int C, int H,
               const float* bias, int cout, bf16* y);
 size_t conv1_wgrad_partial_floats(int C, int cout);
 int conv1_wgrad(cudaStream_t stream, const void* x, int x_u8, int N, int C, int H, int W, int stride, float scale, const bf16* dz, int cout,
-                float* partial, float* dw);
+                float* partial, float* dw, float* db /* bias gradient from the same pass (ones chunk); may be null */);
 
 // ---- convn.cu (implicit-GEMM conv2 / conv3: forward, data gradient, weight + bias gradient) ---------------------
 bool convn_supported(int cin, int cout, int k, int stride);
