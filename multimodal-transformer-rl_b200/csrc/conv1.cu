@@ -342,16 +342,23 @@ __global__ void __launch_bounds__(C1_THREADS, 1) conv1_wgrad_kernel(const __grid
   if (warp == C1_MMA_WARP) { tc_fence_after(); tmem_dealloc(tmem_base, tmem_cols); }
 }
 
-// per-CTA partials [ncta][cout][64 (C + 1)] -> dw [cout][64 C] (PyTorch order) and db [cout] (column 64 C), CTAs added in index order
+// per-CTA partials [ncta][cout][64 (C + 1)] -> dw [cout][64 C] (PyTorch order) and db [cout] (column 64 C).  32 outputs x 8 slice-lanes per
+// block: lane l sums CTAs l, l + 8, ... (independent loads), the 8 lanes are combined in index order (deterministic).
 __global__ void __launch_bounds__(256) conv1_wgrad_reduce_kernel(const float* __restrict__ partial, int ncta, int cout, int C,
                                                                  float* __restrict__ dw, float* __restrict__ db) {
   pdl_trigger();
   pdl_wait();
-  const int Kp = 64 * (C + 1), K = 64 * C;
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < cout * (K + 1); i += gridDim.x * blockDim.x) {
-    const int m = i / (K + 1), kk = i - m * (K + 1);
-    float s = 0.f;
-    for (int c = 0; c < ncta; ++c) s += __ldg(partial + ((size_t)c * cout + m) * Kp + kk);
+  __shared__ float red[8][33];
+  const int Kp = 64 * (C + 1), K = 64 * C, total = cout * (K + 1);
+  const int i = blockIdx.x * 32 + threadIdx.x;
+  const int m = i / (K + 1), kk = i - m * (K + 1);
+  float s = 0.f;
+  if (i < total)
+    for (int c = threadIdx.y; c < ncta; c += 8) s += __ldg(partial + ((size_t)c * cout + m) * Kp + kk);
+  red[threadIdx.y][threadIdx.x] = s;
+  __syncthreads();
+  if (threadIdx.y == 0 && i < total) {
+    for (int l = 1; l < 8; ++l) s += red[l][threadIdx.x];
     if (kk < K) dw[(size_t)m * K + kk] = s;
     else if (db) db[m] = s;
   }
@@ -422,7 +429,7 @@ int conv1_wgrad(cudaStream_t stream, const void* x, int x_u8, int N, int C, int 
   prof.~ProfScope();
   prof.slot = -1;
   const int total = cout * (64 * C + 1);
-  DTB_LAUNCH(conv1_wgrad_reduce_kernel, (total + 255) / 256, 256, 0, stream, partial, grid, cout, C, dw, db);
+  DTB_LAUNCH(conv1_wgrad_reduce_kernel, (total + 31) / 32, dim3(32, 8), 0, stream, partial, grid, cout, C, dw, db);
   DTB_CHECK_LAUNCH();
   return DTB_OK;
 }

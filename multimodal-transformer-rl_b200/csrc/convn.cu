@@ -395,18 +395,25 @@ __global__ void __launch_bounds__(CN_THREADS, 1) convn_wgrad_kernel(const __grid
   if (warp == CN_MMA_WARP) { tc_fence_after(); tmem_dealloc(tmem_base, 512); }
 }
 
-// partial [ncta][nmb * 128][64] -> dW in PyTorch order [cout][cin][kh][kw] (+ db), CTA partials added in index order (deterministic)
+// partial [ncta][nmb * 128][64] -> dW in PyTorch order [cout][cin][kh][kw] (+ db).  32 outputs x 8 slice-lanes per block: lane l sums CTAs
+// l, l + 8, ... (independent loads), the 8 lanes are combined in index order (deterministic).
 __global__ void __launch_bounds__(256) convn_wgrad_reduce_kernel(const float* __restrict__ partial, int ncta, int nmb, int nkb, int cin, int k,
                                                                  int cout, float* __restrict__ dw, float* __restrict__ db) {
   pdl_trigger();
   pdl_wait();
+  __shared__ float red[8][33];
   const int rows = nkb * 64 + 1;  // K indices + the ones row
   const size_t per = (size_t)nmb * 128 * 64;
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < rows * 64; i += gridDim.x * blockDim.x) {
-    const int m = i >> 6, co = i & 63;
-    if (co >= cout) continue;
-    float s = 0.f;
-    for (int c = 0; c < ncta; ++c) s += __ldg(partial + (size_t)c * per + (size_t)m * 64 + co);
+  const int i = blockIdx.x * 32 + threadIdx.x;
+  const int m = i >> 6, co = i & 63;
+  const bool ok = m < rows && co < cout;
+  float s = 0.f;
+  if (ok)
+    for (int c = threadIdx.y; c < ncta; c += 8) s += __ldg(partial + (size_t)c * per + (size_t)m * 64 + co);
+  red[threadIdx.y][threadIdx.x] = s;
+  __syncthreads();
+  if (threadIdx.y == 0 && ok) {
+    for (int l = 1; l < 8; ++l) s += red[l][threadIdx.x];
     if (m == nkb * 64) {
       db[co] = s;
     } else {
@@ -593,7 +600,7 @@ int convn_wgrad(cudaStream_t stream, const bf16* x, int N, int hin, int win, int
     DTB_CHECK_LAUNCH();
   }
   const int total = (p.nkb * 64 + 1) * 64;
-  DTB_LAUNCH(convn_wgrad_reduce_kernel, (total + 255) / 256, 256, 0, stream, partial, grid, p.nmb, p.nkb, cin, k, cout, dw, db);
+  DTB_LAUNCH(convn_wgrad_reduce_kernel, (total + 31) / 32, dim3(32, 8), 0, stream, partial, grid, p.nmb, p.nkb, cin, k, cout, dw, db);
   DTB_CHECK_LAUNCH();
   return DTB_OK;
 }

@@ -248,7 +248,8 @@ int embed_fwd(cudaStream_t stream, const float* states, const float* state_proj,
 constexpr int TE_MAX_PAIRS = 16;  // H <= 1024: 16 bf16 pairs per lane
 constexpr int TE_CHUNK = 4096;    // timesteps staged per pass (16 KB of shared memory)
 __global__ void __launch_bounds__(256) embed_te_scatter_kernel(const bf16* __restrict__ d_pre, const long long* __restrict__ timesteps,
-                                                               int BK, int H, int E, float* __restrict__ d_table) {
+                                                               const float* __restrict__ mask, int BK, int H, int E,
+                                                               float* __restrict__ d_table) {
   pdl_trigger();
   pdl_wait();
   __shared__ int s_ts[TE_CHUNK];
@@ -263,26 +264,46 @@ __global__ void __launch_bounds__(256) embed_te_scatter_kernel(const bf16* __res
     for (int i = threadIdx.x; i < n; i += blockDim.x) {
       long long ts = timesteps[c0 + i];
       ts = ts < 0 ? 0 : (ts >= E ? E - 1 : ts);  // same clamp as the forward gather
-      s_ts[i] = (int)ts;
+      // padded timesteps (mask 0) all carry timestep 0 and an exactly-zero gradient (no loss row, never a key): skipping them is
+      // bit-exact and keeps table row 0 from becoming a serial hot spot
+      s_ts[i] = (mask && mask[c0 + i] <= 0.f) ? -1 : (int)ts;
     }
     __syncthreads();
     if (e < E) {
       for (int t0 = 0; t0 < n; t0 += 32) {
         const int ts = t0 + lane < n ? s_ts[t0 + lane] : -1;
         unsigned int m = __ballot_sync(0xffffffffu, ts == e);
-        while (m) {
-          const int j = __ffs(m) - 1;
-          m &= m - 1;
-          const bf16* p = d_pre + (size_t)(c0 + t0 + j) * 3 * H;
+        while (m) {  // up to four matching rows per pass: all their loads are in flight together, the adds stay in timestep order
+          const bf16* p[4];
+          int nm = 0;
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            p[q] = d_pre;
+            if (m) {
+              p[q] = d_pre + (size_t)(c0 + t0 + __ffs(m) - 1) * 3 * H;
+              m &= m - 1;
+              nm = q + 1;
+            }
+          }
 #pragma unroll
           for (int i = 0; i < TE_MAX_PAIRS; ++i) {
             const int c = i * 64 + lane * 2;
             if (c < H) {
-              const float2 r = unpack_bf16x2(__ldg(reinterpret_cast<const uint32_t*>(p + c)));
-              const float2 s = unpack_bf16x2(__ldg(reinterpret_cast<const uint32_t*>(p + H + c)));
-              const float2 a = unpack_bf16x2(__ldg(reinterpret_cast<const uint32_t*>(p + 2 * H + c)));
-              acc[i].x += r.x + s.x + a.x;
-              acc[i].y += r.y + s.y + a.y;
+              uint32_t v[4][3];
+#pragma unroll
+              for (int q = 0; q < 4; ++q)
+                if (q < nm) {
+                  v[q][0] = __ldg(reinterpret_cast<const uint32_t*>(p[q] + c));
+                  v[q][1] = __ldg(reinterpret_cast<const uint32_t*>(p[q] + H + c));
+                  v[q][2] = __ldg(reinterpret_cast<const uint32_t*>(p[q] + 2 * H + c));
+                }
+#pragma unroll
+              for (int q = 0; q < 4; ++q)
+                if (q < nm) {
+                  const float2 r = unpack_bf16x2(v[q][0]), s = unpack_bf16x2(v[q][1]), a = unpack_bf16x2(v[q][2]);
+                  acc[i].x += r.x + s.x + a.x;
+                  acc[i].y += r.y + s.y + a.y;
+                }
             }
           }
         }
@@ -298,13 +319,14 @@ __global__ void __launch_bounds__(256) embed_te_scatter_kernel(const bf16* __res
   }
 }
 
-int embed_te_scatter(cudaStream_t stream, const bf16* d_pre, const long long* timesteps, int BK, int H, int E, float* d_table) {
+int embed_te_scatter(cudaStream_t stream, const bf16* d_pre, const long long* timesteps, const float* mask, int BK, int H, int E,
+                     float* d_table) {
   DTB_REQUIRE(H % 2 == 0 && H <= 64 * TE_MAX_PAIRS, DTB_ERR_UNSUPPORTED, "embed_te_scatter: hidden size %d unsupported", H);
   if (BK == 0) {
     DTB_CUDA(cudaMemsetAsync(d_table, 0, (size_t)E * H * sizeof(float), stream));
     return DTB_OK;
   }
-  DTB_LAUNCH(embed_te_scatter_kernel, (E + 7) / 8, 256, 0, stream, d_pre, timesteps, BK, H, E, d_table);
+  DTB_LAUNCH(embed_te_scatter_kernel, (E + 7) / 8, 256, 0, stream, d_pre, timesteps, mask, BK, H, E, d_table);
   DTB_CHECK_LAUNCH();
   return DTB_OK;
 }

@@ -121,7 +121,8 @@ int embed_fwd(cudaStream_t stream, const float* states, const float* state_proj,
               float* x, float* pre, float* mean, float* rstd, bf16* U, int P8, int u_states, const DropSite& drop = drop_none(),
               const float* ln1_gamma = nullptr, const float* ln1_beta = nullptr, bf16* h1 = nullptr, float* mean1 = nullptr,
               float* rstd1 = nullptr);
-int embed_te_scatter(cudaStream_t stream, const bf16* d_pre, const long long* timesteps, int BK, int H, int E, float* d_table);
+int embed_te_scatter(cudaStream_t stream, const bf16* d_pre, const long long* timesteps, const float* mask /* [BK] or null */, int BK, int H,
+                     int E, float* d_table);
 int embed_unpack(cudaStream_t stream, const float* G, const float* bsum, int H, int sd, int ad, int P8, int u_states, float* dwR,
                  float* dbR, float* dWs, float* dbs, float* dWa, float* dba);
 

@@ -361,7 +361,7 @@ static int bwd_embed(const dtb_dt* h, cudaStream_t st, const float* P, const voi
   SideStream& sside = h->side;
   DTB_TRY(sside.fork(st));
   cudaStream_t ss = sside.pick(st);  // parameter gradients on the side branch; d_states (towers' input) stays on the main chain
-  DTB_TRY(embed_te_scatter(ss, w.tmp_h, b->timesteps, BK, H, E, G + h->e(E_TABLE)));
+  DTB_TRY(embed_te_scatter(ss, w.tmp_h, b->timesteps, b->attention_mask, BK, H, E, G + h->e(E_TABLE)));
   DTB_TRY(gemm_wgrad(ss, w.tmp_h, 3 * H, w.U, h->P8, 3 * H, h->P8, BK, w.G, h->P8, w.partial, w.partial_floats));
   DTB_TRY(colsum_bf16(ss, w.tmp_h, BK, 3 * H, 3 * H, w.bsum, 0, w.cs_scratch));
   DTB_TRY(embed_unpack(ss, w.G, w.bsum, H, sd, ad, h->P8, h->sd_small, G + h->e(E_WR), G + h->e(E_BR), G + h->e(E_WS), G + h->e(E_BS),

@@ -47,14 +47,14 @@ def test_layernorm_fwd_bwd(cuda_device, M, H):
     assert rel_err(dxb, xr.grad + dres) < 5e-3
     assert rel_err(dg, gr.grad) < 1e-4
     assert rel_err(db, br.grad) < 1e-4
-    # same launch also reducing the column sums of dx (the bias gradient of the c_proj whose output gradient dx is); run twice: the
-    # ticket counter of the in-kernel "last block finishes" reduction must return to zero, and the result must be bit-reproducible
+    # same pass also reducing the column sums of dx (the bias gradient of the c_proj whose output gradient dx is); bit-reproducible
     outs = []
     for _ in range(2):
         dx2, dxb2, dg2, db2, dc = torch.empty_like(dx), torch.empty_like(dxb), torch.empty_like(dg), torch.empty_like(db), torch.empty(H, device=cuda_device)
         _lib.layernorm_bwd(dy, x, mean, rstd, gamma, dres, dx2, dxb2, dg2, db2, dcolsum=dc)
         torch.cuda.synchronize()
-        assert torch.equal(dx2, dx) and torch.equal(dxb2, dxb) and torch.equal(dg2, dg) and torch.equal(db2, db)
+        assert torch.equal(dx2, dx) and torch.equal(dxb2, dxb)
+        assert rel_err(dg2, dg) < 1e-5 and rel_err(db2, db) < 1e-5  # (the grid, hence the partial-sum grouping, may differ between the two forms)
         assert rel_err(dc, (xr.grad + dres).sum(0)) < 1e-4
         outs.append(dc)
     assert torch.equal(outs[0], outs[1])
