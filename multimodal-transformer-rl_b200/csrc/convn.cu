@@ -23,6 +23,7 @@ constexpr int CN_EPI_WARP0 = CN_PRODUCERS / 32, CN_MMA_WARP = CN_EPI_WARP0 + 4;
 constexpr int CN_KB128 = 128 * 128;  // one k-block image of a 128-row tile
 constexpr int CN_KB64 = 64 * 128;    // ... of a 64-row tile (wgrad)
 constexpr int CN_MAX_CLS = 4;
+constexpr int CN_STAGES = 6, CN_LAG = 4;  // fwd / dgrad k-block ring; stages announced LAG issues later
 
 struct ConvNParams {
   const bf16* x;   // fwd / wgrad: input activation NHWC [N, hin, win, cin];  dgrad: dZ of this layer [N, ho, wo, cout]
@@ -42,6 +43,15 @@ struct ConvNParams {
   int cls_ntw[CN_MAX_CLS];   // taps along kw in this class (taps of the class are ordered (dkh, dkw))
   int cls_kb0[CN_MAX_CLS], cls_nkb[CN_MAX_CLS];  // k-block range of the class inside the staged dgrad weights
 };
+
+// 16-byte asynchronous copy global -> shared (LDGSTS); src_bytes = 0 writes zeros (structural zeros / rows beyond the tensor)
+__device__ __forceinline__ void cn_cp_async16(uint32_t dst, const void* src, uint32_t src_bytes) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
+}
+__device__ __forceinline__ void cn_cp_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cn_cp_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+__device__ __forceinline__ uint32_t cn_chunk_addr(uint32_t tile_base, int r, int u) { return tile_base + r * 128 + ((u ^ (r & 7)) << 4); }
 
 __device__ __forceinline__ void cn_store_chunk(uint32_t tile_base, int r, int u, const uint4& v) {
   const uint32_t addr = tile_base + r * 128 + ((u ^ (r & 7)) << 4);
@@ -96,9 +106,10 @@ __global__ void __launch_bounds__(CN_THREADS, 1) convn_kernel(const __grid_const
     // ===== patch producers =====
     // Warp w owns rows 16 w .. 16 w + 15 of the tile; one load instruction covers 4 rows x 8 chunks = four whole 128-byte lines
     // (lane = 8 * row + chunk), so a k-block costs every thread 4 loads (rows rq, rq + 4, rq + 8, rq + 12) and 4 conflict-free swizzled
-    // stores; loads run two k-blocks ahead of the stores; one mbarrier arrival per warp.
+    // stores.  The copies are asynchronous (cp.async, zero-filled where the patch has no data): a stage is announced to the MMA warp
+    // CN_LAG stages after it was issued, so 4 x 4 x 16 B per thread (64 KB per SM) are in flight; one mbarrier arrival per warp.
     const int u = lane & 7, rq = warp * 16 + (lane >> 3);
-    uint32_t stage = 0, phase = 0;
+    uint32_t it = 0;  // k-block stages issued so far (runs straight through tile boundaries)
     for (int t = blockIdx.x; t < p.tiles; t += gridDim.x) {
       const int cls = tile_class(t);
       const int nkb = DGRAD ? p.cls_nkb[cls] : p.nkb;
@@ -129,14 +140,15 @@ __global__ void __launch_bounds__(CN_THREADS, 1) convn_kernel(const __grid_const
           base[j] = ok ? (((long long)n * p.ho + ra[j]) * p.wo + rb[j]) * p.cout : -1;
         }
       }
-      auto load4 = [&](uint4 (&v)[4], int kb) {
+      // k-block kb of this tile -> stage: four asynchronous 16-byte copies per thread, straight into the swizzled image
+      auto issue4 = [&](uint32_t tile_base, int kb) {
         if (!DGRAD) {
           const int tap0 = kb * (64 / p.cin);  // the k-block's taps are consecutive kw of one kernel row: contiguous in NHWC
           const int kh = tap0 / p.k, kw0 = tap0 - kh * p.k;
           const long long off = ((long long)kh * p.win + kw0) * p.cin + u * 8;
 #pragma unroll
           for (int j = 0; j < 4; ++j)
-            v[j] = base[j] >= 0 ? __ldg(reinterpret_cast<const uint4*>(p.x + base[j] + off)) : make_uint4(0, 0, 0, 0);
+            cn_cp_async16(cn_chunk_addr(tile_base, rq + 4 * j, u), base[j] >= 0 ? p.x + base[j] + off : p.x, base[j] >= 0 ? 16u : 0u);
         } else {
           const int e0 = kb * 64 + u * 8;  // K index (tap, cout) of this lane's chunk
           const int tt = e0 / p.cout, co = e0 - tt * p.cout;
@@ -147,27 +159,29 @@ __global__ void __launch_bounds__(CN_THREADS, 1) convn_kernel(const __grid_const
           for (int j = 0; j < 4; ++j) {
             const int oh = ra[j] - dkh, ow = rb[j] - dkw;
             const bool ok = base[j] >= 0 && oh >= 0 && ow >= 0 && oh < p.ho && ow < p.wo;  // else: the tap falls outside dZ (structural zero)
-            v[j] = ok ? __ldg(reinterpret_cast<const uint4*>(p.x + base[j] + off)) : make_uint4(0, 0, 0, 0);
+            cn_cp_async16(cn_chunk_addr(tile_base, rq + 4 * j, u), ok ? p.x + base[j] + off : p.x, ok ? 16u : 0u);
           }
         }
       };
-      uint4 c0[4], c1[4], c2[4];
-      load4(c0, 0);
-      if (nkb > 1) load4(c1, 1);
-      for (int kb = 0; kb < nkb; ++kb) {
-        if (kb + 2 < nkb) load4(c2, kb + 2);
+      for (int kb = 0; kb < nkb; ++kb, ++it) {
+        const uint32_t stage = it % CN_STAGES, phase = (it / CN_STAGES) & 1;
         mbar_wait(&empty_bar[stage], phase ^ 1);
-        const uint32_t tile_base = smem_u32(smA + (size_t)stage * CN_KB128);
-#pragma unroll
-        for (int j = 0; j < 4; ++j) cn_store_chunk(tile_base, rq + 4 * j, u, c0[j]);
-        fence_proxy_async();  // generic-proxy stores -> visible to the tensor core (async proxy)
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&full_bar[stage]);
-        if (++stage == (uint32_t)p.stages) { stage = 0; phase ^= 1; }
-#pragma unroll
-        for (int j = 0; j < 4; ++j) { c0[j] = c1[j]; c1[j] = c2[j]; }
+        issue4(smem_u32(smA + (size_t)stage * CN_KB128), kb);
+        cn_cp_commit();
+        if (it >= CN_LAG) {  // the copies of stage it - LAG have landed (at most LAG younger groups are still in flight)
+          cn_cp_wait<CN_LAG>();
+          fence_proxy_async();  // generic-proxy writes -> visible to the tensor core (async proxy)
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&full_bar[(it - CN_LAG) % CN_STAGES]);
+        }
       }
     }
+    // drain: the last LAG stages
+    cn_cp_wait<0>();
+    fence_proxy_async();
+    __syncwarp();
+    if (lane == 0)
+      for (uint32_t j = it > CN_LAG ? it - CN_LAG : 0; j < it; ++j) mbar_arrive(&full_bar[j % CN_STAGES]);
   } else if (warp == CN_MMA_WARP) {
     if (lane == 0) {
       tma_prefetch_desc(&tmW);
@@ -304,7 +318,7 @@ __global__ void __launch_bounds__(CN_THREADS, 1) convn_wgrad_kernel(const __grid
   if (warp < CN_EPI_WARP0) {
     // warp w owns patch rows 8 w .. 8 w + 7 of the 64-row tile; a load instruction covers 4 rows x 8 chunks (whole 128-byte lines)
     const int u = lane & 7, rq = warp * 8 + (lane >> 3);
-    uint32_t stage = 0, phase = 0;
+    uint32_t stage = 0, phase = 0, issued = 0;
     for (int t = blockIdx.x; t < p.tiles; t += gridDim.x) {
       long long base[2];
 #pragma unroll
@@ -317,35 +331,36 @@ __global__ void __launch_bounds__(CN_THREADS, 1) convn_wgrad_kernel(const __grid
         const int oh = (int)(q % (uint32_t)p.ho), n = (int)(q / (uint32_t)p.ho);
         base[j] = ok ? (((long long)n * p.hin + (long long)oh * p.stride) * p.win + (long long)ow * p.stride) * p.cin + u * 8 : -1;
       }
-      auto load2 = [&](uint4 (&v)[2], int kb) {
-        const int tap0 = kb * (64 / p.cin);
-        const int kh = tap0 / p.k, kw0 = tap0 - kh * p.k;
-        const long long off = ((long long)kh * p.win + kw0) * p.cin;
-#pragma unroll
-        for (int j = 0; j < 2; ++j) v[j] = base[j] >= 0 ? __ldg(reinterpret_cast<const uint4*>(p.x + base[j] + off)) : make_uint4(0, 0, 0, 0);
-      };
       mbar_wait(&empty_bar[stage], phase ^ 1);
       uint8_t* st = smS + (size_t)stage * stage_bytes;
       if (threadIdx.x == 0) {  // dZ rows of this tile: box [64 columns][64 rows]; columns >= cout and rows >= rows arrive as zeros
         mbar_arrive_expect_tx(&full_bar[stage], CN_KB64);
         tma_load_2d(st + (size_t)p.nkb * CN_KB64, &tmZ, &full_bar[stage], 0, t * 64);
       }
-      uint4 c0[2], c1[2], c2[2], c3[2];
-      load2(c0, 0);
-      if (p.nkb > 1) load2(c1, 1);
-      if (p.nkb > 2) load2(c2, 2);
-      for (int kb = 0; kb < p.nkb; ++kb) {
-        if (kb + 3 < p.nkb) load2(c3, kb + 3);
+      for (int kb = 0; kb < p.nkb; ++kb) {  // all k-blocks of the tile: 2 asynchronous 16-byte copies per thread and k-block
+        const int tap0 = kb * (64 / p.cin);
+        const int kh = tap0 / p.k, kw0 = tap0 - kh * p.k;
+        const long long off = ((long long)kh * p.win + kw0) * p.cin;
         const uint32_t img = smem_u32(st + (size_t)kb * CN_KB64);
-        cn_store_chunk(img, rq, u, c0[0]);
-        cn_store_chunk(img, rq + 4, u, c0[1]);
 #pragma unroll
-        for (int j = 0; j < 2; ++j) { c0[j] = c1[j]; c1[j] = c2[j]; c2[j] = c3[j]; }
+        for (int j = 0; j < 2; ++j)
+          cn_cp_async16(cn_chunk_addr(img, rq + 4 * j, u), base[j] >= 0 ? p.x + base[j] + off : p.x, base[j] >= 0 ? 16u : 0u);
       }
+      cn_cp_commit();
+      if (issued > 0) {  // announce the PREVIOUS tile's stage: its copies have landed once at most one younger group is pending
+        cn_cp_wait<1>();
+        fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&full_bar[stage ^ 1]);
+      }
+      ++issued;
+      if (++stage == 2) { stage = 0; phase ^= 1; }
+    }
+    if (issued > 0) {
+      cn_cp_wait<0>();
       fence_proxy_async();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&full_bar[stage]);
-      if (++stage == 2) { stage = 0; phase ^= 1; }
+      if (lane == 0) mbar_arrive(&full_bar[stage ^ 1]);
     }
   } else if (warp == CN_MMA_WARP) {
     if (lane == 0) {
@@ -496,9 +511,8 @@ int convn_fwd(cudaStream_t stream, const bf16* x, int N, int hin, int win, int c
   p.tiles = (int)((p.rows + 127) / 128);
   p.bias = bias; p.y = y;
   const int wbytes = (p.nkb * cout * 128 + 1023) & ~1023;
-  p.stages = (200 * 1024 - wbytes) / CN_KB128;
-  if (p.stages > 8) p.stages = 8;
-  DTB_REQUIRE(p.stages >= 2, DTB_ERR_UNSUPPORTED, "conv: weights too large for shared memory");
+  p.stages = CN_STAGES;
+  DTB_REQUIRE(wbytes + CN_STAGES * CN_KB128 <= 200 * 1024, DTB_ERR_UNSUPPORTED, "conv: weights too large for shared memory");
   CUtensorMap tmW;
   DTB_TRY(make_tmap(&tmW, w_staged, (uint64_t)k * k * cin, (uint64_t)cout, (uint64_t)k * k * cin, 64, (uint32_t)cout));
   DTB_TRY(cn_attr());
@@ -548,9 +562,8 @@ int convn_dgrad(cudaStream_t stream, const bf16* dz, int N, int hin, int win, in
   p.tiles = tile0;
   const int wkb_total = k * k * cout / 64;
   const int wbytes = (wkb_total * cin * 128 + 1023) & ~1023;
-  p.stages = (200 * 1024 - wbytes) / CN_KB128;
-  if (p.stages > 8) p.stages = 8;
-  DTB_REQUIRE(p.stages >= 2, DTB_ERR_UNSUPPORTED, "conv dgrad: weights too large for shared memory");
+  p.stages = CN_STAGES;
+  DTB_REQUIRE(wbytes + CN_STAGES * CN_KB128 <= 200 * 1024, DTB_ERR_UNSUPPORTED, "conv dgrad: weights too large for shared memory");
   CUtensorMap tmW;
   DTB_TRY(make_tmap(&tmW, wd_staged, (uint64_t)k * k * cout, (uint64_t)cin, (uint64_t)k * k * cout, 64, (uint32_t)cin));
   DTB_TRY(cn_attr());
