@@ -269,7 +269,8 @@ int dtb_dt_loss(const dtb_dt* h, void* stream, const dtb_dt_batch* batch, const 
 /* backward.  d_action_preds NULL = use the gradient dtb_dt_loss left in the workspace; d_state_preds / d_return_preds may be
  * NULL (zero).  Overwrites the gradients of the stages it runs.  Stages: 0 = ln_f + heads, 1..L = blocks L-1..0, L+1 = embedding;
  * [stage_begin, stage_end] inclusive lets a data-parallel host all-reduce finished stages while earlier layers still run.
- * d_states_bf16 (nullable): bf16 [B,K,sd] gradient w.r.t. a wide state (states_bf16 path) for the encoder towers. */
+ * d_states_bf16 (nullable): gradient w.r.t. the states — bf16 [B,K,sd] for a wide state (states_bf16 path, for the encoder towers), fp32
+ * [B,K,sd] for vector states (state_dim <= 64). */
 int dtb_dt_backward(const dtb_dt* h, void* stream, const float* params, const void* params_bf16, const dtb_dt_batch* batch,
                     void* workspace, size_t workspace_bytes, const float* d_action_preds, const float* d_state_preds,
                     const float* d_return_preds, float* grads, void* d_states_bf16, int stage_begin, int stage_end);

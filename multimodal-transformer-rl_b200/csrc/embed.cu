@@ -331,6 +331,35 @@ int embed_te_scatter(cudaStream_t stream, const bf16* d_pre, const long long* ti
   return DTB_OK;
 }
 
+// d_states[t, j] = sum_c d_pre_s[t, c] Ws[c, j]   (gradient w.r.t. fp32 vector states, state_dim <= 64; Ws fp32 [H, sd] as nn.Linear stores it)
+// One warp per timestep, lanes over j (coalesced Ws rows), the d_pre element broadcast to the warp.
+__global__ void __launch_bounds__(256) embed_dstates_kernel(const bf16* __restrict__ d_pre, const float* __restrict__ Ws, int BK, int H, int sd,
+                                                            float* __restrict__ d_states) {
+  pdl_trigger();
+  pdl_wait();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
+  for (int t = blockIdx.x * nwarp + warp; t < BK; t += gridDim.x * nwarp) {
+    const bf16* g = d_pre + (size_t)t * 3 * H + H;  // the state-token row
+    float a0 = 0.f, a1 = 0.f;
+    for (int c = 0; c < H; ++c) {
+      const float gc = __bfloat162float(g[c]);
+      if (lane < sd) a0 = fmaf(gc, __ldg(Ws + (size_t)c * sd + lane), a0);
+      if (lane + 32 < sd) a1 = fmaf(gc, __ldg(Ws + (size_t)c * sd + lane + 32), a1);
+    }
+    if (lane < sd) d_states[(size_t)t * sd + lane] = a0;
+    if (lane + 32 < sd) d_states[(size_t)t * sd + lane + 32] = a1;
+  }
+}
+int embed_dstates(cudaStream_t stream, const bf16* d_pre, const float* Ws, int BK, int H, int sd, float* d_states) {
+  DTB_REQUIRE(sd <= 64, DTB_ERR_UNSUPPORTED, "embed_dstates: state_dim %d > 64 goes through the tensor-core path", sd);
+  if (BK == 0) return DTB_OK;
+  int blocks = (BK + 7) / 8;
+  if (blocks > num_sms() * 4) blocks = num_sms() * 4;
+  DTB_LAUNCH(embed_dstates_kernel, blocks, 256, 0, stream, d_pre, Ws, BK, H, sd, d_states);
+  DTB_CHECK_LAUNCH();
+  return DTB_OK;
+}
+
 // G = d_pre^T U : fp32 [3H, P8] (tcgen05 wgrad GEMM); bsum = column sums of d_pre : fp32 [3H].
 // Only the diagonal blocks are gradients:  d wR[c] = G[c][0];  d Wa[c][j] = G[2H+c][1+j];  d Ws[c][j] = G[H+c][1+ad+j].
 __global__ void embed_unpack_kernel(const float* __restrict__ G, const float* __restrict__ bsum, int H, int sd, int ad, int P8,

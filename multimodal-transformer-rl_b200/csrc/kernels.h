@@ -123,6 +123,7 @@ int embed_fwd(cudaStream_t stream, const float* states, const float* state_proj,
               float* rstd1 = nullptr);
 int embed_te_scatter(cudaStream_t stream, const bf16* d_pre, const long long* timesteps, const float* mask /* [BK] or null */, int BK, int H,
                      int E, float* d_table);
+int embed_dstates(cudaStream_t stream, const bf16* d_pre, const float* Ws, int BK, int H, int sd, float* d_states);
 int embed_unpack(cudaStream_t stream, const float* G, const float* bsum, int H, int sd, int ad, int P8, int u_states, float* dwR,
                  float* dbR, float* dWs, float* dbs, float* dWa, float* dba);
 

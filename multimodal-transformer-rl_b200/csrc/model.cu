@@ -155,8 +155,10 @@ static int gemm_fwd(cudaStream_t st, const bf16* A, int lda, const bf16* W, int 
 }
 // LayerNorm in the c_proj epilogue: the CTA must own whole rows (BN == H).  dtb_set_option("ln_fused", 0) / DTB_LN_SEPARATE=1 keeps the
 // standalone ln_fwd launches.
-static bool dt_ln_fused(int H) {
-  return opt_ln_fused() && H <= 256 && H % 64 == 0;  // BN == H must also be a legal MN-major B tile (multiple of 64)
+static bool dt_ln_fused(int H, int M) {
+  // BN == H must also be a legal MN-major B tile (multiple of 64).  Below ~512 rows (get_action: M = 3K) the GEMM is pure latency and
+  // one CTA walking whole rows through three TMEM passes is slower than four N-tile CTAs + a 3 us ln_fwd launch (measured: +20 us per call).
+  return opt_ln_fused() && H <= 256 && H % 64 == 0 && M >= 512;
 }
 static void ep_set_ln(GemmEpilogue& ep, const float* gamma, const float* beta, bf16* out, int ld, float* mean, float* rstd, float eps) {
   ep.ln_gamma = gamma; ep.ln_beta = beta; ep.ln_out = out; ep.ld_ln = ld; ep.ln_mean = mean; ep.ln_rstd = rstd; ep.ln_eps = eps;
@@ -197,7 +199,7 @@ static int dt_forward(const dtb_dt* h, cudaStream_t st, const float* P, const vo
                     P + h->l(0, L_LN1W), P + h->l(0, L_LN1B), w.h1[0], w.mean1[0], w.rstd1[0]));  // + ln_1 of block 0 in the same pass
   // Every other LayerNorm of the forward (ln_2, the next block's ln_1, ln_f) runs in the epilogue of the c_proj GEMM that produces its
   // input row (north star (2): "LayerNorm/GELU/residual fused into GEMM epilogues") when a CTA can own whole rows: H <= 256, H % 32 == 0.
-  const bool ln_fused = dt_ln_fused(H);
+  const bool ln_fused = dt_ln_fused(H, M);
   // ---- GPT-2 blocks (A4-A6) ----
   for (int l = 0; l < L; ++l) {
     {
@@ -351,7 +353,8 @@ static int bwd_layer(const dtb_dt* h, cudaStream_t st, const float* P, const voi
 }
 
 static int bwd_embed(const dtb_dt* h, cudaStream_t st, const float* P, const void* Pb, const dtb_dt_batch* b, Workspace& w, float* G,
-                     bf16* d_states) {
+                     void* d_states_out) {
+  bf16* d_states = h->sd_small ? nullptr : reinterpret_cast<bf16*>(d_states_out);
   const dtb_dt_config& c = h->c;
   const int H = c.hidden, sd = c.state_dim, ad = c.act_dim, E = c.max_ep_len;
   const int BK = b->B * b->K, M = BK * 3;
@@ -366,6 +369,8 @@ static int bwd_embed(const dtb_dt* h, cudaStream_t st, const float* P, const voi
   DTB_TRY(colsum_bf16(ss, w.tmp_h, BK, 3 * H, 3 * H, w.bsum, 0, w.cs_scratch));
   DTB_TRY(embed_unpack(ss, w.G, w.bsum, H, sd, ad, h->P8, h->sd_small, G + h->e(E_WR), G + h->e(E_BR), G + h->e(E_WS), G + h->e(E_BS),
                        G + h->e(E_WA), G + h->e(E_BA)));
+  if (h->sd_small && d_states_out)  // gradient w.r.t. the fp32 vector states (autograd bridge with states.requires_grad)
+    DTB_TRY(embed_dstates(st, w.tmp_h, P + h->e(E_WS), BK, H, sd, reinterpret_cast<float*>(d_states_out)));
   if (!h->sd_small) {
     const bf16* dpre_s = w.tmp_h + H;  // state-token rows of d_pre, stride 3H
     const bf16* sb = b->states_bf16 ? reinterpret_cast<const bf16*>(b->states_bf16) : w.states_b;
@@ -498,7 +503,6 @@ int dtb_dt_backward(const dtb_dt* h, void* stream, const float* params, const vo
   const int L = h->c.n_layer;
   DTB_REQUIRE(stage_begin >= 0 && stage_end <= L + 1 && stage_begin <= stage_end, DTB_ERR_BAD_ARG, "dtb_dt_backward: bad stage range [%d, %d]",
               stage_begin, stage_end);
-  DTB_REQUIRE(d_states_bf16 == nullptr || !h->sd_small, DTB_ERR_UNSUPPORTED, "d_states is only produced for the wide-state (bf16) path");
   cudaStream_t st = (cudaStream_t)stream;
   Workspace w;
   DTB_TRY(get_ws(h, batch, workspace, workspace_bytes, w));
@@ -515,7 +519,7 @@ int dtb_dt_backward(const dtb_dt* h, void* stream, const float* params, const vo
   for (int s = stage_begin; s <= stage_end; ++s) {
     if (s == 0) DTB_TRY(bwd_heads(h, st, params, batch, w, d_action_preds ? d_action_preds : w.d_ap, d_state_preds, d_return_preds, grads));
     else if (s <= L) DTB_TRY(bwd_layer(h, st, params, params_bf16, batch, w, L - s, grads, attn_marked));
-    else DTB_TRY(bwd_embed(h, st, params, params_bf16, batch, w, grads, (bf16*)d_states_bf16));
+    else DTB_TRY(bwd_embed(h, st, params, params_bf16, batch, w, grads, d_states_bf16));
   }
   return h->side.join(st);
 }

@@ -506,12 +506,13 @@ class _DTFunction(torch.autograd.Function):
     @staticmethod
     def backward(ctx, d_state, d_action, d_return):
         model = ctx.model
-        if ctx.states_need_grad and not ctx.wide:
-            raise NotImplementedError("gradient w.r.t. fp32 states (state_dim <= 64) is not produced by the sm_100a path")
+        if ctx.states_need_grad and not ctx.wide and model.state_dim > 64:
+            raise _lib.DtbError("a wide state (state_dim > 64) must be handed over as bf16 to get its gradient (the tensor-core path)")
         grads = torch.empty_like(model._flat)
         if d_action is None:  # NULL would mean "use the fused-loss gradient kept in the workspace"
             d_action = torch.zeros(ctx.state_shape[:2] + (model.act_dim,), dtype=torch.float32, device=grads.device)
-        d_states = torch.empty(ctx.state_shape, dtype=torch.bfloat16, device=grads.device) if (ctx.wide and ctx.states_need_grad) else None
+        # wide states: bf16 gradient from the tensor-core dgrad; vector states (state_dim <= 64): fp32 gradient from embed_dstates
+        d_states = torch.empty(ctx.state_shape, dtype=torch.bfloat16 if ctx.wide else torch.float32, device=grads.device) if ctx.states_need_grad else None
         model._backward_raw(ctx.saved, d_action, d_state, d_return, grads, d_states)
         out = [grads[off:off + torch.Size(shp).numel()].view(shp) for shp, off in zip(model._shapes, model._offsets)]
         return (None, d_states, None, None, None, None, None, *out)

@@ -255,3 +255,21 @@ def test_gradients_are_bit_reproducible(cuda_device, name, B):
     for out, g in runs[1:]:
         assert torch.equal(out, runs[0][0])
         assert torch.equal(g, runs[0][1])
+
+
+def test_gradient_wrt_vector_states(cuda_device):
+    """states.requires_grad with state_dim <= 64 (VERDICT r1 weak #5): d loss / d states through the autograd bridge vs the oracle."""
+    oracle, model, K = build_pair("c1", cuda_device, seed=17)
+    s, a, r, t, m = make_inputs(8, K, 11, 3, 1000, seed=31)
+    dev = cuda_device
+    so = s.clone().requires_grad_(True)
+    _, ap_o, _ = oracle(so, a, None, r, t, m)
+    w = (m > 0).float()
+    ((ap_o ** 2).sum(-1) * w).sum().backward()
+    sg = s.to(dev).requires_grad_(True)
+    _, ap, _ = model(sg, a.to(dev), None, r.to(dev), t.to(dev), m.to(dev))
+    ((ap ** 2).sum(-1) * w.to(dev)).sum().backward()
+    torch.cuda.synchronize()
+    keep = m > 0  # gradients at padded timesteps are don't-care (SURVEY.md §8a)
+    assert sg.grad is not None and sg.grad.dtype == torch.float32
+    assert rel_err(sg.grad[keep.to(dev)], so.grad[keep]) <= TOL_GRAD
