@@ -235,3 +235,29 @@ def test_oracle_mfcc_reproduces_committed_golden():
     d = np.load(os.path.join(GOLD, "mfcc_ref.npz"))
     assert np.array_equal(O.psf_mfcc(d["wav"], int(d["samplerate"])), d["cepstra"])
     assert np.array_equal(O.wav_to_mfcc(int(d["samplerate"]), d["wav"]), d["image"])
+
+
+def test_oracle_mfcc_cross_checked_against_torchaudio_blocks():
+    """Second source for the unpinned MFCC restatement: torchaudio 2.11 building blocks, stage by
+    stage.  Power spectrum and DCT share their definition with python_speech_features and must agree to rounding; the mel filterbank
+    differs by design (floored FFT bins vs exact frequencies) — the residual on the reference's three assets is committed beside the
+    generator (oracle/check_mfcc_torchaudio.py -> tests/golden/mfcc_torchaudio_residual.json)."""
+    import json
+
+    import numpy as np
+
+    pytest.importorskip("torchaudio")
+    from oracle.check_mfcc_torchaudio import stages
+
+    rng = np.random.default_rng(3)
+    t = np.arange(24000) / 24000.0
+    sig = (3000 * np.sin(2 * np.pi * 440 * t) + 500 * rng.standard_normal(t.size)).astype(np.int16)
+    r = stages(sig, 24000)
+    assert r["powspec_vs_torch_stft_max_rel"] < 1e-12
+    assert r["dct_vs_torchaudio_create_dct_max_rel"] < 1e-5
+    assert 0.0 < r["filterbank_vs_torchaudio_melscale_fbanks_rel_l2"] < 0.1      # the documented design difference, bounded
+    assert r["cepstra_with_torchaudio_filterbank_rel_l2"] < 0.1
+    fx = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "mfcc_torchaudio_residual.json")))
+    for name in ("noise", "target_good", "target_bad"):
+        assert fx[name]["powspec_vs_torch_stft_max_rel"] < 1e-12 and fx[name]["dct_vs_torchaudio_create_dct_max_rel"] < 1e-5
+        assert fx[name]["cepstra_with_torchaudio_filterbank_rel_l2"] < 0.06
