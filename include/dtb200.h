@@ -275,6 +275,18 @@ int dtb_dt_backward(const dtb_dt* h, void* stream, const float* params, const vo
                     void* workspace, size_t workspace_bytes, const float* d_action_preds, const float* d_state_preds,
                     const float* d_return_preds, float* grads, void* d_states_bf16, int stage_begin, int stage_end);
 /* [begin, end) element range of the flat gradient buffer written by a backward stage. */
+/* ---- KV-cached incremental get_action: one kernel launch (a cluster of 8 CTAs) per rollout step -------------------
+ * Exact while the whole history fits the window (t <= K: no positional embedding, causal attention => the hidden states of earlier
+ * tokens never change).  `cache` (dtb_dt_decode_cache_bytes(h, K) bytes, caller-owned, device) holds the per-layer keys / values of the
+ * tokens of the first t_cached timesteps, written by earlier calls with the same history prefix; the call processes timesteps
+ * t_cached .. t-1 (normally t = t_cached + 1), (re)computing the action token of timestep t_cached - 1 whose action was a placeholder
+ * when it was cached, and writes action_out[act_dim] = prediction of the last state token.  History pointers: one row per timestep,
+ * t rows (states fp32 [t, sd] for state_dim <= 64, else states_bf16 [t, sd]).  t_cached = 0 starts a new episode. */
+int dtb_dt_decode_supported(const dtb_dt* h);
+size_t dtb_dt_decode_cache_bytes(const dtb_dt* h, int K);
+int dtb_dt_decode(const dtb_dt* h, void* stream, const float* params, const void* params_bf16, const float* states, const void* states_bf16,
+                  const float* actions, const float* returns_to_go, const long long* timesteps, int t, int t_cached, int K, void* cache,
+                  size_t cache_bytes, float* action_out);
 int dtb_dt_stage_grad_range(const dtb_dt* h, int stage, long long* begin, long long* end);
 
 /* ---- multimodal state encoder (REF src/agents.py:30-55 conv_factory, :118-119 towers, :133-134 /255, :137-143 fusion) ------

@@ -93,6 +93,10 @@ def _declare(lib):
     lib.dtb_dt_loss.argtypes = [vp, vp, C.POINTER(DtBatch), vp, f, vp, sz, vp]
     lib.dtb_dt_backward.argtypes = [vp, vp, vp, vp, C.POINTER(DtBatch), vp, sz, vp, vp, vp, vp, vp, i, i]
     lib.dtb_dt_stage_grad_range.argtypes = [vp, i, C.POINTER(ll), C.POINTER(ll)]
+    lib.dtb_dt_decode_supported.argtypes = [vp]
+    lib.dtb_dt_decode_cache_bytes.argtypes = [vp, i]
+    lib.dtb_dt_decode_cache_bytes.restype = sz
+    lib.dtb_dt_decode.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, vp, i, i, i, vp, sz, vp]
     lib.dtb_encoder_create.argtypes = [C.POINTER(EncoderConfig), C.POINTER(vp)]
     lib.dtb_encoder_destroy.argtypes = [vp]
     lib.dtb_encoder_state_dim.argtypes = [vp]

@@ -1,0 +1,437 @@
+// KV-cached incremental get_action as ONE kernel: a thread-block cluster of 8 CTAs walks the whole
+// B = 1 forward — embedding of the new tokens, every GPT-2 block, ln_f and the action head — for the 2-3 tokens a rollout step adds,
+// attending to the keys / values of all earlier tokens kept in a per-layer cache.
+//
+// Why it is exact: the trunk has no positional embedding (timestep embeddings are absolute), attention is causal, so the hidden states
+// of token j depend only on tokens <= j.  As long as the whole episode fits the window (t <= K: every Minecraft2d episode, Config.py:76)
+// the left-padded recompute of the reference (A9) and "append to the cache" are the same function.  Once the window slides the host
+// falls back to the recompute path (model.py).  One detail of the upstream call convention: the action of the newest timestep is a zero
+// placeholder that becomes the real action on the next call, so the action token of timestep t-1 is (re)computed together with R_t, s_t.
+//
+// Work split: every weight matrix is column-partitioned over the 8 CTAs (each reads 1/8 of it, 16-byte loads, k split over the
+// threads, partial sums combined in a fixed order: deterministic, and independent of how many tokens a call processes — a rollout that
+// appends step by step and a single call over the same history produce the same bits).  Activations of the <= 3 new tokens are
+// exchanged through a tiny L2-resident scratch between cluster barriers (5 per layer).  CUDA cores on purpose: M = 3 rows would waste
+// > 97 % of a 128-row tcgen05 tile, and the kernel is bound by streaming the weights from L2 (c1: 1.2 MB per call).
+#include "dt_handle.h"
+
+#include <new>
+#include <string.h>
+
+namespace dtb {
+int require_sm100();
+
+constexpr int DC_CTAS = 8;      // cluster size (portable maximum)
+constexpr int DC_THREADS = 256;
+constexpr int DC_NT = 3;        // tokens per launch: a_{t-1}, R_t, s_t
+constexpr int DC_MAXH = 1024;
+
+struct DecodeParams {
+  int H, I, L, nh, d, sd, ad, E, act, tanh_act, sd_small;
+  float eps;
+  const float* P;   // fp32 master (biases, LayerNorms, embeddings, heads)
+  const bf16* Pb;   // bf16 shadow (the GEMM weights, same offsets)
+  long long e_off[E_COUNT], l_off[L_COUNT], t_off[T_COUNT], layer_stride;
+  // history (device pointers, one row per timestep)
+  const float* states;      // [t, sd] fp32 (vector states) or null
+  const bf16* states_bf16;  // [t, sd] bf16 (wide states = tower features) or null
+  const float* actions;     // [t, ad]
+  const float* rtg;         // [t]
+  const long long* timesteps;
+  int p0, n;                // tokens [p0, p0 + n) of the interleaved stream are processed by this launch
+  bf16* kc;                 // key cache   [L][Tmax][H]
+  bf16* vc;                 // value cache [L][Tmax][H]
+  int Tmax;
+  float* scratch;           // exchange buffers, see dc_scratch_floats
+  float* action_out;        // [ad]: prediction of the last processed token (written when it is a state token)
+};
+
+// scratch layout (floats): sp [H] | q [NT][H] | o [NT][H] | x1 [NT][H] | x2 [NT][H] | fc [NT][I]
+__host__ __device__ inline size_t dc_scratch_floats(int H, int I) { return (size_t)H * (1 + 4 * DC_NT) + (size_t)DC_NT * I; }
+
+__device__ __forceinline__ void dc_cluster_sync() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t dc_cluster_rank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ float dc_round_bf16(float v) { return __bfloat162float(__float2bfloat16(v)); }
+__device__ __forceinline__ float dc_act(float v, int act) { return act == 1 ? fmaxf(v, 0.f) : gelu_new_f(v); }
+
+// LayerNorm of the n token rows x[t][0..H) (shared memory) -> y[t][0..H) rounded to bf16 (what the tensor-core path feeds its GEMMs);
+// warp t handles token t (two-pass statistics, as ln_fwd_kernel).
+__device__ __forceinline__ void dc_layernorm(const float* x, float* y, int n, int H, const float* gamma, const float* beta, float eps) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (warp < n) {
+    const float* xr = x + warp * H;
+    float s = 0.f;
+    for (int c = lane; c < H; c += 32) s += xr[c];
+    const float mean = warp_sum(s) / H;
+    float q = 0.f;
+    for (int c = lane; c < H; c += 32) { const float dlt = xr[c] - mean; q += dlt * dlt; }
+    const float rstd = rsqrtf(warp_sum(q) / H + eps);
+    for (int c = lane; c < H; c += 32) y[warp * H + c] = dc_round_bf16((xr[c] - mean) * rstd * __ldg(gamma + c) + __ldg(beta + c));
+  }
+  __syncthreads();
+}
+
+// Column slice [c0, c0 + ncols) of  out[t][c] = sum_k in[t][k] W[k][c]  for the n tokens; W bf16 [K][ldw] (Conv1D layout, columns
+// contiguous).  Thread (kg, cg): 8 adjacent columns (one 16-byte load per k), k = kg, kg + KG, ...; the KG partial sums of a column are
+// added in kg order.  `red` = shared scratch of KG * DC_NT * ncols floats.  Result left in red[t * ncols + j] (first NT * ncols floats).
+__device__ __forceinline__ void dc_gemv(const float* in, int K, const bf16* W, int ldw, int c0, int ncols, int n, float* red) {
+  const int CG = ncols >> 3;                 // 8-column groups of the slice
+  const int KG = DC_THREADS / CG;            // k-lanes
+  const int cg = threadIdx.x % CG, kg = threadIdx.x / CG;
+  float acc[DC_NT][8];
+#pragma unroll
+  for (int t = 0; t < DC_NT; ++t)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[t][j] = 0.f;
+  if (kg < KG) {
+    const bf16* wp = W + c0 + cg * 8;
+    int k = kg;
+    for (; k + 3 * KG < K; k += 4 * KG) {  // four independent 16-byte loads in flight
+      uint4 w[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) w[u] = __ldg(reinterpret_cast<const uint4*>(wp + (size_t)(k + u * KG) * ldw));
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const uint32_t ww[4] = {w[u].x, w[u].y, w[u].z, w[u].w};
+#pragma unroll
+        for (int t = 0; t < DC_NT; ++t)
+          if (t < n) {
+            const float a = in[t * K + k + u * KG];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const float2 f = unpack_bf16x2(ww[e]);
+              acc[t][2 * e] = fmaf(a, f.x, acc[t][2 * e]);
+              acc[t][2 * e + 1] = fmaf(a, f.y, acc[t][2 * e + 1]);
+            }
+          }
+      }
+    }
+    for (; k < K; k += KG) {
+      const uint4 w = __ldg(reinterpret_cast<const uint4*>(wp + (size_t)k * ldw));
+      const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+      for (int t = 0; t < DC_NT; ++t)
+        if (t < n) {
+          const float a = in[t * K + k];
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const float2 f = unpack_bf16x2(ww[e]);
+            acc[t][2 * e] = fmaf(a, f.x, acc[t][2 * e]);
+            acc[t][2 * e + 1] = fmaf(a, f.y, acc[t][2 * e + 1]);
+          }
+        }
+    }
+#pragma unroll
+    for (int t = 0; t < DC_NT; ++t)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) red[((size_t)kg * DC_NT + t) * ncols + cg * 8 + j] = acc[t][j];
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < n * ncols; i += DC_THREADS) {
+    const int t = i / ncols, j = i - t * ncols;
+    float s = red[(size_t)t * ncols + j];
+    for (int g = 1; g < KG; ++g) s += red[((size_t)g * DC_NT + t) * ncols + j];
+    red[(size_t)t * ncols + j] = s;  // slot (g = 0, t, j): read and written by this thread only
+  }
+  __syncthreads();
+}
+
+__global__ void __cluster_dims__(DC_CTAS, 1, 1) __launch_bounds__(DC_THREADS, 1) dt_decode_kernel(const DecodeParams p) {
+  extern __shared__ __align__(16) float dc_smem[];
+  const int H = p.H, I = p.I, n = p.n, d = p.d;
+  const int KI = H > I ? H : I;
+  float* x = dc_smem;                 // [NT][H]  residual stream of the new tokens (replicated in every CTA)
+  float* hb = x + DC_NT * H;          // [NT][KI] GEMV input (LayerNorm output / attention output / MLP hidden), bf16-rounded values
+  float* red = hb + DC_NT * KI;       // 6144 floats: GEMV partial sums, attention merge
+  const int rank = (int)dc_cluster_rank();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const float* P = p.P;
+  const bf16* Pb = p.Pb;
+  float* s_sp = p.scratch;                  // [H]      wide-state projection
+  float* s_q = s_sp + H;                    // [NT][H]
+  float* s_o = s_q + DC_NT * H;             // [NT][H]
+  float* s_x1 = s_o + DC_NT * H;            // [NT][H]
+  float* s_x2 = s_x1 + DC_NT * H;           // [NT][H]
+  float* s_fc = s_x2 + DC_NT * H;           // [NT][I]
+  pdl_trigger();
+  pdl_wait();
+
+  // ---- wide state (tower features, bf16): projection Ws[H][sd] . s, column slice per CTA, one warp per output --------------------
+  int wide_tok = -1;
+  if (!p.sd_small)
+    for (int t = 0; t < n; ++t)
+      if ((p.p0 + t) % 3 == 1) wide_tok = t;  // at most one state token among <= 3 consecutive tokens
+  if (wide_tok >= 0) {
+    const int k = (p.p0 + wide_tok) / 3, per = H / DC_CTAS;
+    const bf16* srow = p.states_bf16 + (size_t)k * p.sd;
+    for (int c = rank * per + warp; c < (rank + 1) * per; c += DC_THREADS / 32) {
+      const bf16* w = Pb + p.e_off[E_WS] + (size_t)c * p.sd;
+      float a = 0.f;
+      for (int j = lane * 8; j < p.sd; j += 256) {  // sd % 8 == 0 (checked at dtb_dt_create)
+        const uint4 wv = __ldg(reinterpret_cast<const uint4*>(w + j)), sv = __ldg(reinterpret_cast<const uint4*>(srow + j));
+        const uint32_t ww[4] = {wv.x, wv.y, wv.z, wv.w}, ss[4] = {sv.x, sv.y, sv.z, sv.w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const float2 f = unpack_bf16x2(ww[e]), g = unpack_bf16x2(ss[e]);
+          a = fmaf(f.x, g.x, a);
+          a = fmaf(f.y, g.y, a);
+        }
+      }
+      a = warp_sum(a);
+      if (lane == 0) s_sp[c] = a;
+    }
+    dc_cluster_sync();
+  }
+
+  // ---- embedding + embed_ln of the new tokens (HF:611-628), replicated in every CTA ------------------------------------------------
+  for (int t = 0; t < n; ++t) {
+    const int tok = p.p0 + t, k = tok / 3, type = tok - 3 * k;
+    long long ts = p.timesteps[k];
+    ts = ts < 0 ? 0 : (ts >= p.E ? p.E - 1 : ts);
+    const float* te = P + p.e_off[E_TABLE] + (size_t)ts * H;
+    for (int c = threadIdx.x; c < H; c += DC_THREADS) {
+      float v = __ldg(te + c);
+      if (type == 0) {
+        v += p.rtg[k] * __ldg(P + p.e_off[E_WR] + c) + __ldg(P + p.e_off[E_BR] + c);
+      } else if (type == 1) {
+        v += __ldg(P + p.e_off[E_BS] + c);
+        if (p.sd_small) {
+          const float* w = P + p.e_off[E_WS] + (size_t)c * p.sd;
+          for (int j = 0; j < p.sd; ++j) v = fmaf(__ldg(w + j), p.states[(size_t)k * p.sd + j], v);
+        } else {
+          v += __ldcg(s_sp + c);
+        }
+      } else {
+        v += __ldg(P + p.e_off[E_BA] + c);
+        const float* w = P + p.e_off[E_WA] + (size_t)c * p.ad;
+        for (int j = 0; j < p.ad; ++j) v = fmaf(__ldg(w + j), p.actions[(size_t)k * p.ad + j], v);
+      }
+      hb[t * H + c] = v;
+    }
+  }
+  __syncthreads();
+  if (warp < n) {  // embed_ln -> x (fp32, not rounded: the residual stream)
+    const float* xr = hb + warp * H;
+    float s = 0.f;
+    for (int c = lane; c < H; c += 32) s += xr[c];
+    const float mean = warp_sum(s) / H;
+    float q = 0.f;
+    for (int c = lane; c < H; c += 32) { const float dl = xr[c] - mean; q += dl * dl; }
+    const float rstd = rsqrtf(warp_sum(q) / H + p.eps);
+    for (int c = lane; c < H; c += 32)
+      x[warp * H + c] = (xr[c] - mean) * rstd * __ldg(P + p.e_off[E_LNW] + c) + __ldg(P + p.e_off[E_LNB] + c);
+  }
+  __syncthreads();
+
+  const float scale_log2 = 1.4426950408889634f * rsqrtf((float)d);
+  for (int l = 0; l < p.L; ++l) {
+    const long long lo = (long long)l * p.layer_stride;
+    bf16* kc = p.kc + (size_t)l * p.Tmax * H;
+    bf16* vc = p.vc + (size_t)l * p.Tmax * H;
+    // ---- A: ln_1 + this CTA's columns of q | k | v (HF:272, :179-185) ---------------------------------------------------------------
+    dc_layernorm(x, hb, n, H, P + p.l_off[L_LN1W] + lo, P + p.l_off[L_LN1B] + lo, p.eps);
+    {
+      const int ncols = 3 * H / DC_CTAS, c0 = rank * ncols;
+      dc_gemv(hb, H, Pb + p.l_off[L_WQKV] + lo, 3 * H, c0, ncols, n, red);
+      for (int i = threadIdx.x; i < n * ncols; i += DC_THREADS) {
+        const int t = i / ncols, c = c0 + (i - t * ncols);
+        const float v = red[i] + __ldg(P + p.l_off[L_BQKV] + lo + c);
+        if (c < H) s_q[t * H + c] = dc_round_bf16(v);
+        else if (c < 2 * H) kc[(size_t)(p.p0 + t) * H + (c - H)] = __float2bfloat16(v);
+        else vc[(size_t)(p.p0 + t) * H + (c - 2 * H)] = __float2bfloat16(v);
+      }
+    }
+    dc_cluster_sync();
+    // ---- B: causal attention of the new tokens over the cache (HF:47-65); heads rank, rank + 8, ... ---------------------------------
+    for (int hh = rank; hh < p.nh; hh += DC_CTAS) {
+      // warp w takes keys w, w + 8, ...; lane owns d / 32 dims; per (warp, token) online softmax, merged in warp order below
+      const int per = d >> 5;  // 1, 2 or 4
+      float qv[DC_NT][4], acc[DC_NT][4], m[DC_NT], lsum[DC_NT];
+#pragma unroll
+      for (int t = 0; t < DC_NT; ++t) {
+        m[t] = -INFINITY; lsum[t] = 0.f;
+#pragma unroll
+        for (int e = 0; e < 4; ++e) { acc[t][e] = 0.f; qv[t][e] = (t < n && e < per) ? __ldcg(s_q + t * H + hh * d + lane * per + e) : 0.f; }
+      }
+      const int last = p.p0 + n - 1;
+      for (int j = warp; j <= last; j += DC_THREADS / 32) {
+        float kv[4], vv[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          // ld.global.cg: the rows of this launch's tokens were written by other CTAs of the cluster a barrier ago
+          kv[e] = e < per ? __bfloat162float(__ushort_as_bfloat16(__ldcg(reinterpret_cast<const unsigned short*>(kc) + (size_t)j * H + hh * d + lane * per + e))) : 0.f;
+          vv[e] = e < per ? __bfloat162float(__ushort_as_bfloat16(__ldcg(reinterpret_cast<const unsigned short*>(vc) + (size_t)j * H + hh * d + lane * per + e))) : 0.f;
+        }
+#pragma unroll
+        for (int t = 0; t < DC_NT; ++t) {
+          if (t < n && j <= p.p0 + t) {  // warp-uniform
+            float s = 0.f;
+#pragma unroll
+            for (int e = 0; e < 4; ++e) s = fmaf(qv[t][e], kv[e], s);
+            s = warp_sum(s) * scale_log2;
+            const float mn = fmaxf(m[t], s), alpha = fast_exp2(m[t] - mn), pe = fast_exp2(s - mn);
+            lsum[t] = lsum[t] * alpha + pe;
+#pragma unroll
+            for (int e = 0; e < 4; ++e) acc[t][e] = acc[t][e] * alpha + pe * vv[e];
+            m[t] = mn;
+          }
+        }
+      }
+      // merge the 8 warps: red[(w * NT + t) * (d + 2)] = m, l, acc[d]
+      __syncthreads();
+#pragma unroll
+      for (int t = 0; t < DC_NT; ++t) {
+        float* r = red + ((size_t)warp * DC_NT + t) * (d + 2);
+        if (lane == 0) { r[0] = m[t]; r[1] = lsum[t]; }
+#pragma unroll
+        for (int e = 0; e < 4; ++e)
+          if (e < per) r[2 + lane * per + e] = acc[t][e];
+      }
+      __syncthreads();
+      for (int i = threadIdx.x; i < n * d; i += DC_THREADS) {
+        const int t = i / d, e = i - t * d;
+        float M = -INFINITY;
+        for (int w = 0; w < DC_THREADS / 32; ++w) M = fmaxf(M, red[((size_t)w * DC_NT + t) * (d + 2)]);
+        float L = 0.f, o = 0.f;
+        for (int w = 0; w < DC_THREADS / 32; ++w) {
+          const float* r = red + ((size_t)w * DC_NT + t) * (d + 2);
+          const float f = r[0] == -INFINITY ? 0.f : fast_exp2(r[0] - M);
+          L += r[1] * f;
+          o += r[2 + e] * f;
+        }
+        s_o[t * H + hh * d + e] = dc_round_bf16(L > 0.f ? o / L : 0.f);
+      }
+      __syncthreads();
+    }
+    dc_cluster_sync();
+    // ---- C: attn.c_proj + residual (HF:217-218, :281): this CTA's columns of x ---------------------------------------------------------
+    for (int i = threadIdx.x; i < n * H; i += DC_THREADS) hb[i] = __ldcg(s_o + i);
+    __syncthreads();
+    {
+      const int ncols = H / DC_CTAS, c0 = rank * ncols;
+      dc_gemv(hb, H, Pb + p.l_off[L_WO] + lo, H, c0, ncols, n, red);
+      for (int i = threadIdx.x; i < n * ncols; i += DC_THREADS) {
+        const int t = i / ncols, c = c0 + (i - t * ncols);
+        s_x1[t * H + c] = x[t * H + c] + red[i] + __ldg(P + p.l_off[L_BO] + lo + c);
+      }
+    }
+    dc_cluster_sync();
+    for (int i = threadIdx.x; i < n * H; i += DC_THREADS) x[i] = __ldcg(s_x1 + i);
+    __syncthreads();
+    // ---- D: ln_2 + mlp.c_fc + activation (HF:303, :234-235): this CTA's columns of the hidden layer ------------------------------------
+    dc_layernorm(x, hb, n, H, P + p.l_off[L_LN2W] + lo, P + p.l_off[L_LN2B] + lo, p.eps);
+    {
+      const int ncols = I / DC_CTAS, c0 = rank * ncols;
+      dc_gemv(hb, H, Pb + p.l_off[L_W1] + lo, I, c0, ncols, n, red);
+      for (int i = threadIdx.x; i < n * ncols; i += DC_THREADS) {
+        const int t = i / ncols, c = c0 + (i - t * ncols);
+        s_fc[t * I + c] = dc_round_bf16(dc_act(red[i] + __ldg(P + p.l_off[L_B1] + lo + c), p.act));
+      }
+    }
+    dc_cluster_sync();
+    // ---- F: mlp.c_proj + residual (HF:236-237, :306) -----------------------------------------------------------------------------------
+    for (int i = threadIdx.x; i < n * I; i += DC_THREADS) hb[i] = __ldcg(s_fc + i);
+    __syncthreads();
+    {
+      const int ncols = H / DC_CTAS, c0 = rank * ncols;
+      dc_gemv(hb, I, Pb + p.l_off[L_W2] + lo, H, c0, ncols, n, red);
+      for (int i = threadIdx.x; i < n * ncols; i += DC_THREADS) {
+        const int t = i / ncols, c = c0 + (i - t * ncols);
+        s_x2[t * H + c] = x[t * H + c] + red[i] + __ldg(P + p.l_off[L_B2] + lo + c);
+      }
+    }
+    dc_cluster_sync();
+    for (int i = threadIdx.x; i < n * H; i += DC_THREADS) x[i] = __ldcg(s_x2 + i);
+    __syncthreads();
+  }
+
+  // ---- ln_f + predict_action on the last token when it is a state token (HF:450, :652) ------------------------------------------------
+  const int last_tok = p.p0 + n - 1;
+  if (rank == 0 && last_tok % 3 == 1 && p.action_out) {
+    dc_layernorm(x + (n - 1) * H, hb, 1, H, P + p.t_off[T_LNFW], P + p.t_off[T_LNFB], p.eps);
+    for (int a = warp; a < p.ad; a += DC_THREADS / 32) {
+      const float* w = P + p.t_off[T_WPA] + (size_t)a * H;
+      float s = 0.f;
+      for (int c = lane; c < H; c += 32) s = fmaf(__ldg(w + c), hb[c], s);
+      s = warp_sum(s) + __ldg(P + p.t_off[T_BPA] + a);
+      if (lane == 0) p.action_out[a] = p.tanh_act ? tanhf(s) : s;
+    }
+  }
+  dc_cluster_sync();  // no CTA leaves while a peer may still be reading what it wrote (and: one completion point for the next launch)
+}
+
+}  // namespace dtb
+
+using namespace dtb;
+
+extern "C" {
+
+// H must split into 8-column groups per CTA for every weight matrix: H % 64 == 0 (then 3H / 8 and I / 8 = H / 2 are multiples of 8 too)
+int dtb_dt_decode_supported(const dtb_dt* h) {
+  if (!h) return 0;
+  const dtb_dt_config& c = h->c;
+  return c.hidden % 64 == 0 && c.hidden <= DC_MAXH && c.n_inner % 64 == 0 && (h->sd_small || c.state_dim % 8 == 0) ? 1 : 0;
+}
+
+// bytes of the decode state: key + value cache [L][3 K][H] bf16 each, then the exchange scratch
+size_t dtb_dt_decode_cache_bytes(const dtb_dt* h, int K) {
+  if (!h || K < 1) return 0;
+  const dtb_dt_config& c = h->c;
+  const size_t kv = (size_t)2 * c.n_layer * 3 * K * c.hidden * sizeof(bf16);
+  return ((kv + 255) & ~size_t(255)) + dc_scratch_floats(c.hidden, c.n_inner) * sizeof(float) + 256;
+}
+
+int dtb_dt_decode(const dtb_dt* h, void* stream, const float* params, const void* params_bf16, const float* states, const void* states_bf16,
+                  const float* actions, const float* returns_to_go, const long long* timesteps, int t, int t_cached, int K, void* cache,
+                  size_t cache_bytes, float* action_out) {
+  DTB_REQUIRE(h && params && params_bf16 && actions && returns_to_go && timesteps && cache && action_out, DTB_ERR_BAD_ARG, "dtb_dt_decode: null argument");
+  DTB_REQUIRE(dtb_dt_decode_supported(h), DTB_ERR_UNSUPPORTED, "dtb_dt_decode: hidden %d / n_inner %d unsupported (multiples of 64)", h->c.hidden, h->c.n_inner);
+  DTB_REQUIRE(t >= 1 && t <= K && t_cached >= 0 && t_cached < t, DTB_ERR_BAD_ARG, "dtb_dt_decode: need 0 <= t_cached (%d) < t (%d) <= K (%d)", t_cached, t, K);
+  DTB_REQUIRE(h->sd_small ? states != nullptr : states_bf16 != nullptr, DTB_ERR_BAD_ARG, "dtb_dt_decode: states (fp32, state_dim <= 64) or states_bf16 (wide) required");
+  DTB_REQUIRE(cache_bytes >= dtb_dt_decode_cache_bytes(h, K), DTB_ERR_WORKSPACE, "dtb_dt_decode: cache too small");
+  DTB_TRY(require_sm100());
+  const dtb_dt_config& c = h->c;
+  DecodeParams p;
+  memset(&p, 0, sizeof(p));
+  p.H = c.hidden; p.I = c.n_inner; p.L = c.n_layer; p.nh = c.n_head; p.d = c.hidden / c.n_head; p.sd = c.state_dim; p.ad = c.act_dim;
+  p.E = c.max_ep_len; p.act = c.activation; p.tanh_act = c.action_tanh; p.sd_small = h->sd_small; p.eps = c.ln_eps;
+  p.P = params; p.Pb = reinterpret_cast<const bf16*>(params_bf16);
+  for (int i = 0; i < E_COUNT; ++i) p.e_off[i] = h->e(i);
+  for (int i = 0; i < L_COUNT; ++i) p.l_off[i] = h->l(0, i);
+  for (int i = 0; i < T_COUNT; ++i) p.t_off[i] = h->t(i);
+  p.layer_stride = c.n_layer > 1 ? h->l(1, 0) - h->l(0, 0) : 0;
+  p.states = states; p.states_bf16 = reinterpret_cast<const bf16*>(states_bf16); p.actions = actions; p.rtg = returns_to_go; p.timesteps = timesteps;
+  uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(cache) + 255) & ~uintptr_t(255));
+  p.Tmax = 3 * K;
+  p.kc = reinterpret_cast<bf16*>(base);
+  p.vc = p.kc + (size_t)c.n_layer * p.Tmax * c.hidden;
+  const size_t kv = ((size_t)2 * c.n_layer * p.Tmax * c.hidden * sizeof(bf16) + 255) & ~size_t(255);
+  p.scratch = reinterpret_cast<float*>(base + kv);
+  p.action_out = action_out;
+  const int KI = c.hidden > c.n_inner ? c.hidden : c.n_inner;
+  const size_t smem = ((size_t)DC_NT * c.hidden + (size_t)DC_NT * KI + 6144) * sizeof(float);
+  static size_t attr = 0;
+  if (smem > attr) {
+    DTB_CUDA(cudaFuncSetAttribute(dt_decode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    attr = smem;
+  }
+  // tokens [p0, p1): the action token of the last cached timestep (its action was a placeholder when it was cached), then R, s of every
+  // new timestep; the newest timestep's own action token comes after its state token and is not needed for the prediction
+  const int p1 = 3 * t - 1;
+  for (int p0 = t_cached > 0 ? 3 * t_cached - 1 : 0; p0 < p1; p0 += DC_NT) {
+    p.p0 = p0;
+    p.n = p1 - p0 < DC_NT ? p1 - p0 : DC_NT;
+    DTB_LAUNCH(dt_decode_kernel, DC_CTAS, DC_THREADS, smem, (cudaStream_t)stream, p);
+    DTB_CHECK_LAUNCH();
+  }
+  return DTB_OK;
+}
+
+}  // extern "C"

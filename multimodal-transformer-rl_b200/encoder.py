@@ -309,6 +309,25 @@ class MultimodalDecisionTransformer(nn.Module):
         from .model import _ActionRunner
 
         dt, K = self.dt, self.dt.max_length
+        t = frames.shape[0]
+        if K is not None and t <= K and (dt.kv_cache if kwargs.get("use_cache") is None else kwargs["use_cache"]) and dt._decode_ready() \
+                and not self.encoder.attn_type:
+            # KV-cached step: the towers run on the NEW frames only, their features join a K-row history buffer, one decode kernel follows
+            hist = self.__dict__.get("_feat_hist")
+            if hist is None or hist.device != dt._flat.device:
+                hist = self.__dict__["_feat_hist"] = torch.zeros((K, self.encoder.state_dim), dtype=torch.bfloat16, device=dt._flat.device)
+            dc = dt._dc
+            self.encoder._stage()
+            dt._stage()
+            stale = dc is None or dc["ptr"] != dt._flat.data_ptr() or dc["stamp"] != dt._staged_version or t <= dc["t"] \
+                or self.__dict__.get("_feat_stamp") != self.encoder._staged_version
+            t0 = 0 if stale else dc["t"]
+            if stale and dc is not None:
+                dc["t"] = 0
+            self.__dict__["_feat_stamp"] = self.encoder._staged_version
+            hist[t0:t] = self.encoder.forward_raw(frames[t0:t].unsqueeze(0), audio[t0:t].unsqueeze(0))[0]
+            return dt._decode(None, hist, dt._rows(actions, dt.act_dim, torch.float32), dt._rows(returns_to_go, 0, torch.float32),
+                              dt._rows(timesteps, 0, torch.long), t)
         if K is None:
             states = self.encoder.forward_raw(frames.unsqueeze(0), audio.unsqueeze(0))[0].float()
             return dt.get_action(states, actions, rewards, returns_to_go, timesteps, **kwargs)

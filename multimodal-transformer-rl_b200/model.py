@@ -76,6 +76,8 @@ class DecisionTransformer(nn.Module):
         # nn.Dropout sites of the trunk (GPT2Model.drop / attn_dropout / resid_dropout); embd_pdrop follows resid_pdrop when not given
         self._p_resid, self._p_attn = float(resid_pdrop or 0.0), float(attn_pdrop or 0.0)
         self._p_embd = self._p_resid if embd_pdrop is None else float(embd_pdrop)
+        self.kv_cache = True          # get_action: append to a per-layer K/V cache while the history fits the window (exact, see _decode)
+        self._dc = None               # decode state: cache buffer, timesteps cached, parameter stamp, output buffer
         self._drop_state = None       # device int32 [3] = {seed_lo, seed_hi, step}, read by the kernels at run time
         self._drop_applied = None     # (p_embd, p_attn, p_resid, state ptr) last handed to the library
 
@@ -323,13 +325,58 @@ class DecisionTransformer(nn.Module):
         wide = self.state_dim > 64 and states.dtype == torch.bfloat16
         return _DTFunction.apply(self, states, actions, returns_to_go, timesteps, attention_mask, wide, *params)
 
+    # ---- KV-cached get_action ------------------------------------------------------------------------
+    def reset_kv_cache(self):
+        """Forget the cached keys / values (call when earlier entries of the history were edited in place; a shorter history, i.e. a
+        new episode, and a parameter update reset it automatically)."""
+        if self._dc is not None:
+            self._dc["t"] = 0
+
+    def _decode_ready(self) -> bool:
+        return bool(self.kv_cache and self.max_length is not None and not self.dropout_active()
+                    and _lib.load().dtb_dt_decode_supported(self._h))
+
+    def _decode(self, states, states_bf16, actions, returns_to_go, timesteps, t: int):
+        """One ``dtb_dt_decode`` call: the tokens of timesteps ``t_cached .. t-1`` go through a single cluster kernel that attends to the
+        cached keys / values of everything before.  Exact while ``t <= max_length``: without a positional embedding and with causal
+        attention the hidden states of earlier tokens never change, so appending equals the reference's left-padded recompute."""
+        lib, K = _lib.load(), self.max_length
+        dc = self._dc
+        if dc is None or dc["ptr"] != self._flat.data_ptr():
+            nbytes = int(lib.dtb_dt_decode_cache_bytes(self._h, K))
+            dc = self._dc = dict(cache=torch.zeros(nbytes, dtype=torch.uint8, device=self._flat.device), t=0, stamp=-1, ptr=self._flat.data_ptr(),
+                                 out=torch.zeros(self.act_dim, dtype=torch.float32, device=self._flat.device))
+        self._stage()
+        if dc["stamp"] != self._staged_version or t <= dc["t"]:  # weights changed, or a new episode / repeated call: start over
+            dc["t"], dc["stamp"] = 0, self._staged_version
+        _lib.check(lib.dtb_dt_decode(self._h, _lib.stream_ptr(), _lib.ptr(self._flat), _lib.ptr(self._flat_bf16), _lib.ptr(states),
+                                     _lib.ptr(states_bf16), _lib.ptr(actions), _lib.ptr(returns_to_go), _lib.ptr(timesteps), t, dc["t"], K,
+                                     _lib.ptr(dc["cache"]), dc["cache"].numel(), _lib.ptr(dc["out"])))
+        dc["t"] = t
+        return dc["out"].clone()
+
+    @staticmethod
+    def _rows(x, width, dtype):
+        x = x.detach()
+        if x.dtype != dtype:
+            x = x.to(dtype)
+        x = x.reshape(-1, width) if width else x.reshape(-1)
+        return x if x.is_contiguous() else x.contiguous()
+
     @torch.no_grad()
-    def get_action(self, states, actions, rewards, returns_to_go, timesteps, **kwargs):
+    def get_action(self, states, actions, rewards, returns_to_go, timesteps, use_cache=None, **kwargs):
         """Upstream evaluation entry point: last-K window, LEFT zero padding, action of the last state token.
 
-        With a fixed window (``max_length``) the call is one ``dtb_pad_left`` launch (window + padding + mask, integer-exact) plus the
-        replay of a CUDA graph of the B = 1 forward over static history buffers (``_ActionRunner``)."""
+        While the history fits the window (t <= ``max_length``) and ``kv_cache`` is on, the call appends to a per-layer key / value
+        cache: ONE kernel launch per rollout step (``_decode``).  Otherwise (sliding window, training-mode dropout, unsupported widths,
+        ``use_cache=False``) it is one ``dtb_pad_left`` launch (window + padding + mask, integer-exact) plus the replay of a CUDA graph
+        of the B = 1 forward over static history buffers (``_ActionRunner``)."""
         self._require_cuda(states)
+        if (self.kv_cache if use_cache is None else use_cache) and self.state_dim <= 64 and self._decode_ready():
+            s = self._rows(states, self.state_dim, torch.float32)
+            if s.shape[0] <= self.max_length:
+                return self._decode(s, None, self._rows(actions, self.act_dim, torch.float32), self._rows(returns_to_go, 0, torch.float32),
+                                    self._rows(timesteps, 0, torch.long), s.shape[0])
         if self.max_length is None:
             states = states.reshape(1, -1, self.state_dim)
             actions = actions.reshape(1, -1, self.act_dim)
