@@ -692,8 +692,13 @@ def measure_e2e_resident(args, wl, ctx, steps):
 
 
 def measure_get_action(wl, ctx, calls=300, warmup=50):
-    """BASELINE.json's second metric: get_action latency at B = 1 with a full K-step history, through the public API
-    (wall clock, one stream sync per call, p50 / p90 / p99 in microseconds)."""
+    """BASELINE.json's second metric: get_action latency at B = 1 with a full K-step history, through the public API (wall clock, one
+    stream sync per call, p50 / p90 / p99 in microseconds), model.eval().
+      * `p50_us` ...: the call a rollout makes at its last step (t = K): the K/V cache holds the first K - 1 timesteps, the call appends
+        one (towers on the newest frame only + ONE decode kernel).  Between timed calls the cache is rewound to K - 1 timesteps
+        (`_dc["t"] = K - 1`: its rows for the unchanged prefix stay valid), so every timed call does exactly a rollout step's work.
+      * `recompute`: the same call with use_cache=False (pad_left + CUDA graph of the whole B = 1 forward): what every call costs once the
+        window slides (t > K), and what round 1 reported as get_action."""
     model, dev, K = ctx["model"], ctx["dev"], wl["K"]
     model.eval()  # evaluation rollouts run without dropout (upstream evaluate_episode_rtg: model.eval())
     b = make_batch(wl, 1, seed=4321)
@@ -703,18 +708,36 @@ def measure_get_action(wl, ctx, calls=300, warmup=50):
     else:
         args += [b["frames"][0].to(dev), b["audio"][0].to(dev)]
     args += [b["actions"][0].to(dev), torch.zeros(K, device=dev), b["rtg"][0].to(dev), b["timesteps"][0].to(dev)]
-    lat = []
-    for i in range(warmup + calls):
-        torch.cuda.synchronize(dev)
-        t0 = time.perf_counter()
-        a = model.get_action(*args)
-        torch.cuda.current_stream(dev).synchronize()
-        if i >= warmup:
-            lat.append((time.perf_counter() - t0) * 1e6)
-    lat.sort()
-    pick = lambda q: lat[min(len(lat) - 1, int(q * len(lat)))]
-    return {"p50_us": pick(0.5), "p90_us": pick(0.9), "p99_us": pick(0.99), "calls": calls, "warmup": warmup, "history": K,
-            "action_dim": int(a.numel()), "how": "wall clock around model.get_action(...) + stream sync, inputs resident on the device, model.eval()"}
+    dt = ctx["parts"][0]
+
+    def run(use_cache):
+        lat, a = [], None
+        for i in range(warmup + calls):
+            if use_cache and dt._dc is not None and dt._dc["t"] == K:
+                dt._dc["t"] = K - 1  # rewind: the next call appends timestep K - 1 again
+            torch.cuda.synchronize(dev)
+            t0 = time.perf_counter()
+            a = model.get_action(*args, use_cache=use_cache)
+            torch.cuda.current_stream(dev).synchronize()
+            if i >= warmup:
+                lat.append((time.perf_counter() - t0) * 1e6)
+        lat.sort()
+        pick = lambda q: lat[min(len(lat) - 1, int(q * len(lat)))]
+        return {"p50_us": pick(0.5), "p90_us": pick(0.9), "p99_us": pick(0.99)}, a
+
+    cached_ok = bool(dt._decode_ready())
+    rec, a = run(False)
+    out = dict(rec)
+    if cached_ok:
+        out, a2 = run(True)
+        out["recompute"] = rec
+        out["cached_vs_recompute_max_abs_diff"] = float((a2 - a).abs().max())
+        out["path"] = "KV-cached append at t = K (dtb_dt_decode: one cluster kernel" + (" + towers on the newest frame" if wl["enc"] is not None else "") + ")"
+    else:
+        out["path"] = "recompute (pad_left + CUDA graph of the B = 1 forward)"
+    out.update({"calls": calls, "warmup": warmup, "history": K, "action_dim": int(a.numel()),
+                "how": "wall clock around model.get_action(...) + stream sync, inputs resident on the device, model.eval()"})
+    return out
 
 
 def other_workloads(args, skip):

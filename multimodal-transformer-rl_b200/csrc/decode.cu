@@ -1,4 +1,4 @@
-// KV-cached incremental get_action as ONE kernel: a thread-block cluster of 8 CTAs walks the whole
+// KV-cached incremental get_action as ONE kernel: a thread-block cluster of 1-16 CTAs walks the whole
 // B = 1 forward — embedding of the new tokens, every GPT-2 block, ln_f and the action head — for the 2-3 tokens a rollout step adds,
 // attending to the keys / values of all earlier tokens kept in a per-layer cache.
 //
@@ -8,7 +8,7 @@
 // falls back to the recompute path (model.py).  One detail of the upstream call convention: the action of the newest timestep is a zero
 // placeholder that becomes the real action on the next call, so the action token of timestep t-1 is (re)computed together with R_t, s_t.
 //
-// Work split: every weight matrix is column-partitioned over the 8 CTAs (each reads 1/8 of it, 16-byte loads, k split over the
+// Work split: every weight matrix is column-partitioned over the C CTAs (each reads 1/C of it, 16-byte loads, k split over the
 // threads, partial sums combined in a fixed order: deterministic, and independent of how many tokens a call processes — a rollout that
 // appends step by step and a single call over the same history produce the same bits).  Activations of the <= 3 new tokens are
 // exchanged through a tiny L2-resident scratch between cluster barriers (5 per layer).  CUDA cores on purpose: M = 3 rows would waste
@@ -21,10 +21,12 @@
 namespace dtb {
 int require_sm100();
 
-constexpr int DC_CTAS = 8;      // cluster size (portable maximum)
+constexpr int DC_MAX_CTAS = 16;  // cluster size: 1 .. 16, chosen per model so that one CTA streams at most ~1.5 MB of weights per layer
 constexpr int DC_THREADS = 256;
 constexpr int DC_NT = 3;        // tokens per launch: a_{t-1}, R_t, s_t
 constexpr int DC_MAXH = 1024;
+
+constexpr int DC_RED_FLOATS = 2048 * DC_NT + 2048 * DC_NT;  // level 1: KG * NT * ncols <= 256 * 8 * NT; level 2: RP * n * ncols (same bound)
 
 struct DecodeParams {
   int H, I, L, nh, d, sd, ad, E, act, tanh_act, sd_small;
@@ -39,6 +41,7 @@ struct DecodeParams {
   const float* rtg;         // [t]
   const long long* timesteps;
   int p0, n;                // tokens [p0, p0 + n) of the interleaved stream are processed by this launch
+  int C;                    // CTAs of the cluster (the grid is one cluster)
   bf16* kc;                 // key cache   [L][Tmax][H]
   bf16* vc;                 // value cache [L][Tmax][H]
   int Tmax;
@@ -93,12 +96,12 @@ __device__ __forceinline__ void dc_gemv(const float* in, int K, const bf16* W, i
   if (kg < KG) {
     const bf16* wp = W + c0 + cg * 8;
     int k = kg;
-    for (; k + 3 * KG < K; k += 4 * KG) {  // four independent 16-byte loads in flight
-      uint4 w[4];
+    for (; k + 7 * KG < K; k += 8 * KG) {  // eight independent 16-byte loads in flight per thread (the kernel is bound by weight streaming)
+      uint4 w[8];
 #pragma unroll
-      for (int u = 0; u < 4; ++u) w[u] = __ldg(reinterpret_cast<const uint4*>(wp + (size_t)(k + u * KG) * ldw));
+      for (int u = 0; u < 8; ++u) w[u] = __ldg(reinterpret_cast<const uint4*>(wp + (size_t)(k + u * KG) * ldw));
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
+      for (int u = 0; u < 8; ++u) {
         const uint32_t ww[4] = {w[u].x, w[u].y, w[u].z, w[u].w};
 #pragma unroll
         for (int t = 0; t < DC_NT; ++t)
@@ -134,22 +137,36 @@ __device__ __forceinline__ void dc_gemv(const float* in, int K, const bf16* W, i
       for (int j = 0; j < 8; ++j) red[((size_t)kg * DC_NT + t) * ncols + cg * 8 + j] = acc[t][j];
   }
   __syncthreads();
-  for (int i = threadIdx.x; i < n * ncols; i += DC_THREADS) {
-    const int t = i / ncols, j = i - t * ncols;
-    float s = red[(size_t)t * ncols + j];
-    for (int g = 1; g < KG; ++g) s += red[((size_t)g * DC_NT + t) * ncols + j];
-    red[(size_t)t * ncols + j] = s;  // slot (g = 0, t, j): read and written by this thread only
+  // the KG partial sums of every output are added in kg order, in two levels (fixed grouping: deterministic): RP threads per output sum
+  // contiguous kg ranges, then one thread adds the RP range sums
+  const int nout = n * ncols;
+  int RP = DC_THREADS / nout;
+  RP = RP < 1 ? 1 : (RP > KG ? KG : RP);
+  float* red2 = red + (size_t)KG * DC_NT * ncols;  // [RP][nout]
+  for (int i = threadIdx.x; i < nout * RP; i += DC_THREADS) {
+    const int r = i / nout, o = i - r * nout, t = o / ncols, j = o - t * ncols;
+    const int g0 = (int)((long long)r * KG / RP), g1 = (int)((long long)(r + 1) * KG / RP);
+    float s = 0.f;
+    for (int g = g0; g < g1; ++g) s += red[((size_t)g * DC_NT + t) * ncols + j];
+    red2[(size_t)r * nout + o] = s;
+  }
+  __syncthreads();
+  for (int o = threadIdx.x; o < nout; o += DC_THREADS) {
+    float s = red2[o];
+    for (int r = 1; r < RP; ++r) s += red2[(size_t)r * nout + o];
+    red[o] = s;  // result: red[t * ncols + j]
   }
   __syncthreads();
 }
 
-__global__ void __cluster_dims__(DC_CTAS, 1, 1) __launch_bounds__(DC_THREADS, 1) dt_decode_kernel(const DecodeParams p) {
+__global__ void __launch_bounds__(DC_THREADS, 1) dt_decode_kernel(const DecodeParams p) {
   extern __shared__ __align__(16) float dc_smem[];
   const int H = p.H, I = p.I, n = p.n, d = p.d;
   const int KI = H > I ? H : I;
   float* x = dc_smem;                 // [NT][H]  residual stream of the new tokens (replicated in every CTA)
   float* hb = x + DC_NT * H;          // [NT][KI] GEMV input (LayerNorm output / attention output / MLP hidden), bf16-rounded values
-  float* red = hb + DC_NT * KI;       // 6144 floats: GEMV partial sums, attention merge
+  float* red = hb + DC_NT * KI;       // DC_RED_FLOATS: GEMV partial sums (two levels), attention merge
+  const int DC_CTAS = p.C;
   const int rank = (int)dc_cluster_rank();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const float* P = p.P;
@@ -373,11 +390,20 @@ using namespace dtb;
 
 extern "C" {
 
-// H must split into 8-column groups per CTA for every weight matrix: H % 64 == 0 (then 3H / 8 and I / 8 = H / 2 are multiples of 8 too)
+// Cluster size: the largest power of two <= 16 such that a CTA streams at most ~0.5 MB of weights per layer, and every column slice
+// (H / C, 3H / C, I / C) is a whole number of 8-column groups.  c1 / c2 (H = 128): 1 CTA (no cluster barriers at all), c3: 4, c4: 16.
+static int dc_cluster_size(const dtb_dt_config& c) {
+  const double layer_bytes = 2.0 * (4.0 * c.hidden * c.hidden + 2.0 * c.hidden * c.n_inner);
+  int C = 1;
+  while (C < DC_MAX_CTAS && layer_bytes / C > 512.0 * 1024.0 && c.hidden % (16 * C) == 0 && c.n_inner % (16 * C) == 0) C *= 2;
+  return C;
+}
 int dtb_dt_decode_supported(const dtb_dt* h) {
   if (!h) return 0;
   const dtb_dt_config& c = h->c;
-  return c.hidden % 64 == 0 && c.hidden <= DC_MAXH && c.n_inner % 64 == 0 && (h->sd_small || c.state_dim % 8 == 0) ? 1 : 0;
+  const int C = dc_cluster_size(c);
+  const int widest = (3 * c.hidden > c.n_inner ? 3 * c.hidden : c.n_inner) / C;
+  return c.hidden % 8 == 0 && c.hidden <= DC_MAXH && c.n_inner % 8 == 0 && widest <= 2048 && (h->sd_small || (c.state_dim % 8 == 0 && c.hidden % C == 0)) ? 1 : 0;
 }
 
 // bytes of the decode state: key + value cache [L][3 K][H] bf16 each, then the exchange scratch
@@ -392,7 +418,7 @@ int dtb_dt_decode(const dtb_dt* h, void* stream, const float* params, const void
                   const float* actions, const float* returns_to_go, const long long* timesteps, int t, int t_cached, int K, void* cache,
                   size_t cache_bytes, float* action_out) {
   DTB_REQUIRE(h && params && params_bf16 && actions && returns_to_go && timesteps && cache && action_out, DTB_ERR_BAD_ARG, "dtb_dt_decode: null argument");
-  DTB_REQUIRE(dtb_dt_decode_supported(h), DTB_ERR_UNSUPPORTED, "dtb_dt_decode: hidden %d / n_inner %d unsupported (multiples of 64)", h->c.hidden, h->c.n_inner);
+  DTB_REQUIRE(dtb_dt_decode_supported(h), DTB_ERR_UNSUPPORTED, "dtb_dt_decode: hidden %d / n_inner %d unsupported", h->c.hidden, h->c.n_inner);
   DTB_REQUIRE(t >= 1 && t <= K && t_cached >= 0 && t_cached < t, DTB_ERR_BAD_ARG, "dtb_dt_decode: need 0 <= t_cached (%d) < t (%d) <= K (%d)", t_cached, t, K);
   DTB_REQUIRE(h->sd_small ? states != nullptr : states_bf16 != nullptr, DTB_ERR_BAD_ARG, "dtb_dt_decode: states (fp32, state_dim <= 64) or states_bf16 (wide) required");
   DTB_REQUIRE(cache_bytes >= dtb_dt_decode_cache_bytes(h, K), DTB_ERR_WORKSPACE, "dtb_dt_decode: cache too small");
@@ -416,19 +442,31 @@ int dtb_dt_decode(const dtb_dt* h, void* stream, const float* params, const void
   p.scratch = reinterpret_cast<float*>(base + kv);
   p.action_out = action_out;
   const int KI = c.hidden > c.n_inner ? c.hidden : c.n_inner;
-  const size_t smem = ((size_t)DC_NT * c.hidden + (size_t)DC_NT * KI + 6144) * sizeof(float);
+  const size_t smem = ((size_t)DC_NT * c.hidden + (size_t)DC_NT * KI + DC_RED_FLOATS) * sizeof(float);
   static size_t attr = 0;
   if (smem > attr) {
     DTB_CUDA(cudaFuncSetAttribute(dt_decode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    DTB_CUDA(cudaFuncSetAttribute(dt_decode_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
     attr = smem;
   }
+  p.C = dc_cluster_size(c);
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3(p.C); cfg.blockDim = dim3(DC_THREADS); cfg.dynamicSmemBytes = smem; cfg.stream = (cudaStream_t)stream;
+  cudaLaunchAttribute at[2];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = p.C; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+  at[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[1].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = pdl_enabled() ? 2 : 1;
   // tokens [p0, p1): the action token of the last cached timestep (its action was a placeholder when it was cached), then R, s of every
   // new timestep; the newest timestep's own action token comes after its state token and is not needed for the prediction
   const int p1 = 3 * t - 1;
   for (int p0 = t_cached > 0 ? 3 * t_cached - 1 : 0; p0 < p1; p0 += DC_NT) {
     p.p0 = p0;
     p.n = p1 - p0 < DC_NT ? p1 - p0 : DC_NT;
-    DTB_LAUNCH(dt_decode_kernel, DC_CTAS, DC_THREADS, smem, (cudaStream_t)stream, p);
+    DTB_CUDA(cudaLaunchKernelEx(&cfg, dt_decode_kernel, p));
     DTB_CHECK_LAUNCH();
   }
   return DTB_OK;
