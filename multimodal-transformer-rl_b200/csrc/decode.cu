@@ -81,10 +81,60 @@ __device__ __forceinline__ void dc_layernorm(const float* x, float* y, int n, in
   __syncthreads();
 }
 
-// Column slice [c0, c0 + ncols) of  out[t][c] = sum_k in[t][k] W[k][c]  for the n tokens; W bf16 [K][ldw] (Conv1D layout, columns
-// contiguous).  Thread (kg, cg): 8 adjacent columns (one 16-byte load per k), k = kg, kg + KG, ...; the KG partial sums of a column are
-// added in kg order.  `red` = shared scratch of KG * DC_NT * ncols floats.  Result left in red[t * ncols + j] (first NT * ncols floats).
-__device__ __forceinline__ void dc_gemv(const float* in, int K, const bf16* W, int ldw, int c0, int ncols, int n, float* red) {
+// ---- weight stream -------------------------------------------------------------------------------------------------------------------
+// The kernel is bound by streaming this CTA's column slices of the four weight matrices of every layer from L2.  They are walked as ONE
+// sequence of tiles (layer, matrix, k range): [rows][ncols] bf16, copied by all threads with cp.async (16 bytes each, no registers) into
+// a ring of DC_SLOTS shared-memory slots, DC_DEPTH tiles ahead of the tile being consumed.  The sequence runs straight through the phase
+// boundaries of the forward, so the next matrix (and the next layer) is already landing while a phase waits at a cluster barrier, runs
+// its LayerNorm or the attention.  (First version: __ldg in the GEMV loop — one dependent L2 round trip per 8 loads, 140 us at c1.)
+constexpr int DC_SLOT_BYTES = 24 * 1024, DC_SLOTS = 5, DC_DEPTH = 4;
+
+struct DcStream {
+  int K[4], N[4], ncols[4], rows[4], tiles[4], lid[4];  // per matrix: q|k|v, attn.c_proj, mlp.c_fc, mlp.c_proj
+  int per_layer, total;
+  int issued;  // tiles issued so far (identical in every thread)
+};
+__device__ __forceinline__ void dc_stream_init(DcStream& st, const DecodeParams& p) {
+  const int H = p.H, I = p.I;
+  const int K[4] = {H, H, H, I}, N[4] = {3 * H, H, I, H}, lid[4] = {L_WQKV, L_WO, L_W1, L_W2};
+  st.per_layer = 0;
+  for (int m = 0; m < 4; ++m) {
+    st.K[m] = K[m]; st.N[m] = N[m]; st.lid[m] = lid[m];
+    st.ncols[m] = N[m] / p.C;
+    int r = (DC_SLOT_BYTES / (st.ncols[m] * 2)) & ~7;
+    st.rows[m] = r > K[m] ? K[m] : r;
+    st.tiles[m] = (K[m] + st.rows[m] - 1) / st.rows[m];
+    st.per_layer += st.tiles[m];
+  }
+  st.total = st.per_layer * p.L;
+  st.issued = 0;
+}
+// issue the copies of tile g (or an empty group past the end, so that every thread always has the same number of groups pending)
+__device__ __forceinline__ void dc_stream_issue(DcStream& st, const DecodeParams& p, int rank, uint8_t* slots) {
+  const int g = st.issued++;
+  if (g < st.total) {
+    const int l = g / st.per_layer;
+    int r = g - l * st.per_layer, m = 0;
+    while (r >= st.tiles[m]) { r -= st.tiles[m]; ++m; }
+    const int k0 = r * st.rows[m], rows = min(st.rows[m], st.K[m] - k0), ncols = st.ncols[m], cg_n = ncols >> 3;
+    const bf16* W = p.Pb + p.l_off[st.lid[m]] + (long long)l * p.layer_stride + (size_t)k0 * st.N[m] + rank * ncols;
+    const uint32_t dst = smem_u32(slots + (size_t)(g % DC_SLOTS) * DC_SLOT_BYTES);
+    for (int i = threadIdx.x; i < rows * cg_n; i += DC_THREADS) {
+      const int row = i / cg_n, cg = i - row * cg_n;
+      asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + (uint32_t)(row * ncols + cg * 8) * 2u), "l"(W + (size_t)row * st.N[m] + cg * 8)
+                   : "memory");
+    }
+  }
+  asm volatile("cp.async.commit_group;" ::: "memory");
+}
+
+// Column slice of  out[t][c] = sum_k in[t][k] W[k][c]  for the n tokens, W = matrix m of the current layer, read from the tile ring.
+// Thread (kg, cg): 8 adjacent columns (one 16-byte shared-memory load per k), k = kg, kg + KG, ... inside every tile; the KG partial
+// sums of a column are added in a fixed order (two levels).  `consumed` = tiles consumed so far (the stream position of this gemv).
+// Result left in red[t * ncols + j].
+__device__ __forceinline__ void dc_gemv(DcStream& st, const DecodeParams& p, int rank, uint8_t* slots, int& consumed, int m, const float* in,
+                                        int n, float* red) {
+  const int K = st.K[m], ncols = st.ncols[m];
   const int CG = ncols >> 3;                 // 8-column groups of the slice
   const int KG = DC_THREADS / CG;            // k-lanes
   const int cg = threadIdx.x % CG, kg = threadIdx.x / CG;
@@ -93,20 +143,19 @@ __device__ __forceinline__ void dc_gemv(const float* in, int K, const bf16* W, i
   for (int t = 0; t < DC_NT; ++t)
 #pragma unroll
     for (int j = 0; j < 8; ++j) acc[t][j] = 0.f;
-  if (kg < KG) {
-    const bf16* wp = W + c0 + cg * 8;
-    int k = kg;
-    for (; k + 7 * KG < K; k += 8 * KG) {  // eight independent 16-byte loads in flight per thread (the kernel is bound by weight streaming)
-      uint4 w[8];
-#pragma unroll
-      for (int u = 0; u < 8; ++u) w[u] = __ldg(reinterpret_cast<const uint4*>(wp + (size_t)(k + u * KG) * ldw));
-#pragma unroll
-      for (int u = 0; u < 8; ++u) {
-        const uint32_t ww[4] = {w[u].x, w[u].y, w[u].z, w[u].w};
+  for (int tile = 0; tile < st.tiles[m]; ++tile, ++consumed) {
+    asm volatile("cp.async.wait_group %0;" ::"n"(DC_DEPTH - 1) : "memory");  // this thread's copies of tile `consumed` have landed
+    __syncthreads();                                                         // ... everybody's have; and the slot issued next is free
+    const uint8_t* slot = slots + (size_t)(consumed % DC_SLOTS) * DC_SLOT_BYTES;
+    const int k0 = tile * st.rows[m], rows = min(st.rows[m], K - k0);
+    if (kg < KG) {
+      for (int r = kg; r < rows; r += KG) {
+        const uint4 w = *reinterpret_cast<const uint4*>(slot + (size_t)(r * ncols + cg * 8) * 2);
+        const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
 #pragma unroll
         for (int t = 0; t < DC_NT; ++t)
           if (t < n) {
-            const float a = in[t * K + k + u * KG];
+            const float a = in[t * K + k0 + r];
 #pragma unroll
             for (int e = 0; e < 4; ++e) {
               const float2 f = unpack_bf16x2(ww[e]);
@@ -116,21 +165,9 @@ __device__ __forceinline__ void dc_gemv(const float* in, int K, const bf16* W, i
           }
       }
     }
-    for (; k < K; k += KG) {
-      const uint4 w = __ldg(reinterpret_cast<const uint4*>(wp + (size_t)k * ldw));
-      const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
-#pragma unroll
-      for (int t = 0; t < DC_NT; ++t)
-        if (t < n) {
-          const float a = in[t * K + k];
-#pragma unroll
-          for (int e = 0; e < 4; ++e) {
-            const float2 f = unpack_bf16x2(ww[e]);
-            acc[t][2 * e] = fmaf(a, f.x, acc[t][2 * e]);
-            acc[t][2 * e + 1] = fmaf(a, f.y, acc[t][2 * e + 1]);
-          }
-        }
-    }
+    dc_stream_issue(st, p, rank, slots);  // tile consumed + DEPTH goes into the slot tile consumed - 1 used (free since the barrier above)
+  }
+  if (kg < KG) {
 #pragma unroll
     for (int t = 0; t < DC_NT; ++t)
 #pragma unroll
@@ -166,6 +203,7 @@ __global__ void __launch_bounds__(DC_THREADS, 1) dt_decode_kernel(const DecodePa
   float* x = dc_smem;                 // [NT][H]  residual stream of the new tokens (replicated in every CTA)
   float* hb = x + DC_NT * H;          // [NT][KI] GEMV input (LayerNorm output / attention output / MLP hidden), bf16-rounded values
   float* red = hb + DC_NT * KI;       // DC_RED_FLOATS: GEMV partial sums (two levels), attention merge
+  uint8_t* slots = reinterpret_cast<uint8_t*>(red + DC_RED_FLOATS);  // weight tile ring (16-byte aligned: every region above is a multiple of 16 B)
   const int DC_CTAS = p.C;
   const int rank = (int)dc_cluster_rank();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -179,6 +217,11 @@ __global__ void __launch_bounds__(DC_THREADS, 1) dt_decode_kernel(const DecodePa
   float* s_fc = s_x2 + DC_NT * H;           // [NT][I]
   pdl_trigger();
   pdl_wait();
+  // start the weight stream: the first DEPTH tiles fly while the tokens are embedded
+  DcStream st;
+  dc_stream_init(st, p);
+  int consumed = 0;
+  for (int i = 0; i < DC_DEPTH; ++i) dc_stream_issue(st, p, rank, slots);
 
   // ---- wide state (tower features, bf16): projection Ws[H][sd] . s, column slice per CTA, one warp per output --------------------
   int wide_tok = -1;
@@ -256,7 +299,7 @@ __global__ void __launch_bounds__(DC_THREADS, 1) dt_decode_kernel(const DecodePa
     dc_layernorm(x, hb, n, H, P + p.l_off[L_LN1W] + lo, P + p.l_off[L_LN1B] + lo, p.eps);
     {
       const int ncols = 3 * H / DC_CTAS, c0 = rank * ncols;
-      dc_gemv(hb, H, Pb + p.l_off[L_WQKV] + lo, 3 * H, c0, ncols, n, red);
+      dc_gemv(st, p, rank, slots, consumed, 0, hb, n, red);
       for (int i = threadIdx.x; i < n * ncols; i += DC_THREADS) {
         const int t = i / ncols, c = c0 + (i - t * ncols);
         const float v = red[i] + __ldg(P + p.l_off[L_BQKV] + lo + c);
@@ -333,7 +376,7 @@ __global__ void __launch_bounds__(DC_THREADS, 1) dt_decode_kernel(const DecodePa
     __syncthreads();
     {
       const int ncols = H / DC_CTAS, c0 = rank * ncols;
-      dc_gemv(hb, H, Pb + p.l_off[L_WO] + lo, H, c0, ncols, n, red);
+      dc_gemv(st, p, rank, slots, consumed, 1, hb, n, red);
       for (int i = threadIdx.x; i < n * ncols; i += DC_THREADS) {
         const int t = i / ncols, c = c0 + (i - t * ncols);
         s_x1[t * H + c] = x[t * H + c] + red[i] + __ldg(P + p.l_off[L_BO] + lo + c);
@@ -346,7 +389,7 @@ __global__ void __launch_bounds__(DC_THREADS, 1) dt_decode_kernel(const DecodePa
     dc_layernorm(x, hb, n, H, P + p.l_off[L_LN2W] + lo, P + p.l_off[L_LN2B] + lo, p.eps);
     {
       const int ncols = I / DC_CTAS, c0 = rank * ncols;
-      dc_gemv(hb, H, Pb + p.l_off[L_W1] + lo, I, c0, ncols, n, red);
+      dc_gemv(st, p, rank, slots, consumed, 2, hb, n, red);
       for (int i = threadIdx.x; i < n * ncols; i += DC_THREADS) {
         const int t = i / ncols, c = c0 + (i - t * ncols);
         s_fc[t * I + c] = dc_round_bf16(dc_act(red[i] + __ldg(P + p.l_off[L_B1] + lo + c), p.act));
@@ -358,7 +401,7 @@ __global__ void __launch_bounds__(DC_THREADS, 1) dt_decode_kernel(const DecodePa
     __syncthreads();
     {
       const int ncols = H / DC_CTAS, c0 = rank * ncols;
-      dc_gemv(hb, I, Pb + p.l_off[L_W2] + lo, H, c0, ncols, n, red);
+      dc_gemv(st, p, rank, slots, consumed, 3, hb, n, red);
       for (int i = threadIdx.x; i < n * ncols; i += DC_THREADS) {
         const int t = i / ncols, c = c0 + (i - t * ncols);
         s_x2[t * H + c] = x[t * H + c] + red[i] + __ldg(P + p.l_off[L_B2] + lo + c);
@@ -395,7 +438,7 @@ extern "C" {
 static int dc_cluster_size(const dtb_dt_config& c) {
   const double layer_bytes = 2.0 * (4.0 * c.hidden * c.hidden + 2.0 * c.hidden * c.n_inner);
   int C = 1;
-  while (C < DC_MAX_CTAS && layer_bytes / C > 512.0 * 1024.0 && c.hidden % (16 * C) == 0 && c.n_inner % (16 * C) == 0) C *= 2;
+  while (C < DC_MAX_CTAS && layer_bytes / C > 256.0 * 1024.0 && c.hidden % (16 * C) == 0 && c.n_inner % (16 * C) == 0) C *= 2;
   return C;
 }
 int dtb_dt_decode_supported(const dtb_dt* h) {
@@ -403,7 +446,7 @@ int dtb_dt_decode_supported(const dtb_dt* h) {
   const dtb_dt_config& c = h->c;
   const int C = dc_cluster_size(c);
   const int widest = (3 * c.hidden > c.n_inner ? 3 * c.hidden : c.n_inner) / C;
-  return c.hidden % 8 == 0 && c.hidden <= DC_MAXH && c.n_inner % 8 == 0 && widest <= 2048 && (h->sd_small || (c.state_dim % 8 == 0 && c.hidden % C == 0)) ? 1 : 0;
+  return c.hidden % 8 == 0 && c.hidden <= DC_MAXH && c.n_inner % 8 == 0 && widest <= 1536 && (h->sd_small || (c.state_dim % 8 == 0 && c.hidden % C == 0)) ? 1 : 0;
 }
 
 // bytes of the decode state: key + value cache [L][3 K][H] bf16 each, then the exchange scratch
@@ -442,7 +485,7 @@ int dtb_dt_decode(const dtb_dt* h, void* stream, const float* params, const void
   p.scratch = reinterpret_cast<float*>(base + kv);
   p.action_out = action_out;
   const int KI = c.hidden > c.n_inner ? c.hidden : c.n_inner;
-  const size_t smem = ((size_t)DC_NT * c.hidden + (size_t)DC_NT * KI + DC_RED_FLOATS) * sizeof(float);
+  const size_t smem = ((size_t)DC_NT * c.hidden + (size_t)DC_NT * KI + DC_RED_FLOATS) * sizeof(float) + (size_t)DC_SLOTS * DC_SLOT_BYTES;
   static size_t attr = 0;
   if (smem > attr) {
     DTB_CUDA(cudaFuncSetAttribute(dt_decode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
