@@ -321,26 +321,45 @@ __global__ void __launch_bounds__(DC_THREADS, 1) dt_decode_kernel(const DecodePa
         for (int e = 0; e < 4; ++e) { acc[t][e] = 0.f; qv[t][e] = (t < n && e < per) ? __ldcg(s_q + t * H + hh * d + lane * per + e) : 0.f; }
       }
       const int last = p.p0 + n - 1;
-      for (int j = warp; j <= last; j += DC_THREADS / 32) {
-        float kv[4], vv[4];
+      // four keys per pass (j0, j0 + 8, j0 + 16, j0 + 24): their K / V rows (one vector load per lane and row) are all in flight before
+      // the first dot product.  ld.global.cg: the rows of this launch's tokens were written by other CTAs of the cluster a barrier ago.
+      auto load_row = [&](const bf16* base, int j, float (&out)[4]) {
+        const bf16* ptr = base + (size_t)j * H + hh * d + lane * per;
+        if (per == 4) {
+          const uint2 u = __ldcg(reinterpret_cast<const uint2*>(ptr));
+          const float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y);
+          out[0] = a.x; out[1] = a.y; out[2] = b.x; out[3] = b.y;
+        } else if (per == 2) {
+          const float2 a = unpack_bf16x2(__ldcg(reinterpret_cast<const uint32_t*>(ptr)));
+          out[0] = a.x; out[1] = a.y; out[2] = 0.f; out[3] = 0.f;
+        } else {
+          out[0] = __bfloat162float(__ushort_as_bfloat16(__ldcg(reinterpret_cast<const unsigned short*>(ptr))));
+          out[1] = out[2] = out[3] = 0.f;
+        }
+      };
+      for (int j0 = warp; j0 <= last; j0 += 4 * (DC_THREADS / 32)) {
+        float kv[4][4], vv[4][4];
 #pragma unroll
-        for (int e = 0; e < 4; ++e) {
-          // ld.global.cg: the rows of this launch's tokens were written by other CTAs of the cluster a barrier ago
-          kv[e] = e < per ? __bfloat162float(__ushort_as_bfloat16(__ldcg(reinterpret_cast<const unsigned short*>(kc) + (size_t)j * H + hh * d + lane * per + e))) : 0.f;
-          vv[e] = e < per ? __bfloat162float(__ushort_as_bfloat16(__ldcg(reinterpret_cast<const unsigned short*>(vc) + (size_t)j * H + hh * d + lane * per + e))) : 0.f;
+        for (int u = 0; u < 4; ++u) {
+          const int j = j0 + u * (DC_THREADS / 32);
+          if (j <= last) { load_row(kc, j, kv[u]); load_row(vc, j, vv[u]); }
         }
 #pragma unroll
-        for (int t = 0; t < DC_NT; ++t) {
-          if (t < n && j <= p.p0 + t) {  // warp-uniform
-            float s = 0.f;
+        for (int u = 0; u < 4; ++u) {
+          const int j = j0 + u * (DC_THREADS / 32);
 #pragma unroll
-            for (int e = 0; e < 4; ++e) s = fmaf(qv[t][e], kv[e], s);
-            s = warp_sum(s) * scale_log2;
-            const float mn = fmaxf(m[t], s), alpha = fast_exp2(m[t] - mn), pe = fast_exp2(s - mn);
-            lsum[t] = lsum[t] * alpha + pe;
+          for (int t = 0; t < DC_NT; ++t) {
+            if (t < n && j <= p.p0 + t) {  // warp-uniform (implies j <= last)
+              float sc = 0.f;
 #pragma unroll
-            for (int e = 0; e < 4; ++e) acc[t][e] = acc[t][e] * alpha + pe * vv[e];
-            m[t] = mn;
+              for (int e = 0; e < 4; ++e) sc = fmaf(qv[t][e], kv[u][e], sc);
+              sc = warp_sum(sc) * scale_log2;
+              const float mn = fmaxf(m[t], sc), alpha = fast_exp2(m[t] - mn), pe = fast_exp2(sc - mn);
+              lsum[t] = lsum[t] * alpha + pe;
+#pragma unroll
+              for (int e = 0; e < 4; ++e) acc[t][e] = acc[t][e] * alpha + pe * vv[u][e];
+              m[t] = mn;
+            }
           }
         }
       }
@@ -438,7 +457,7 @@ extern "C" {
 static int dc_cluster_size(const dtb_dt_config& c) {
   const double layer_bytes = 2.0 * (4.0 * c.hidden * c.hidden + 2.0 * c.hidden * c.n_inner);
   int C = 1;
-  while (C < DC_MAX_CTAS && layer_bytes / C > 256.0 * 1024.0 && c.hidden % (16 * C) == 0 && c.n_inner % (16 * C) == 0) C *= 2;
+  while (C < DC_MAX_CTAS && layer_bytes / C > 512.0 * 1024.0 && c.hidden % (16 * C) == 0 && c.n_inner % (16 * C) == 0) C *= 2;
   return C;
 }
 int dtb_dt_decode_supported(const dtb_dt* h) {
