@@ -22,11 +22,11 @@ namespace dtb {
 int require_sm100();
 
 constexpr int DC_MAX_CTAS = 16;  // cluster size: 1 .. 16, chosen per model so that one CTA streams at most ~1.5 MB of weights per layer
-constexpr int DC_THREADS = 256;
+constexpr int DC_THREADS = 512;  // 16 warps: the GEMV is issue / latency bound on few SMs (ncu: 28 % issue-active with 8 warps)
 constexpr int DC_NT = 3;        // tokens per launch: a_{t-1}, R_t, s_t
 constexpr int DC_MAXH = 1024;
 
-constexpr int DC_RED_FLOATS = 2048 * DC_NT + 2048 * DC_NT;  // level 1: KG * NT * ncols <= 256 * 8 * NT; level 2: RP * n * ncols (same bound)
+constexpr int DC_RED_FLOATS = 4096 * DC_NT + 1536 * DC_NT;  // level 1: KG * NT * ncols <= 512 * 8 * NT; level 2: RP * n * ncols <= max(512, NT * 1536)
 
 struct DecodeParams {
   int H, I, L, nh, d, sd, ad, E, act, tanh_act, sd_small;
@@ -87,7 +87,7 @@ __device__ __forceinline__ void dc_layernorm(const float* x, float* y, int n, in
 // a ring of DC_SLOTS shared-memory slots, DC_DEPTH tiles ahead of the tile being consumed.  The sequence runs straight through the phase
 // boundaries of the forward, so the next matrix (and the next layer) is already landing while a phase waits at a cluster barrier, runs
 // its LayerNorm or the attention.  (First version: __ldg in the GEMV loop — one dependent L2 round trip per 8 loads, 140 us at c1.)
-constexpr int DC_SLOT_BYTES = 24 * 1024, DC_SLOTS = 5, DC_DEPTH = 4;
+constexpr int DC_SLOT_BYTES = 24 * 1024, DC_SLOTS = 4, DC_DEPTH = 3;
 
 struct DcStream {
   int K[4], N[4], ncols[4], rows[4], tiles[4], lid[4];  // per matrix: q|k|v, attn.c_proj, mlp.c_fc, mlp.c_proj
@@ -119,10 +119,14 @@ __device__ __forceinline__ void dc_stream_issue(DcStream& st, const DecodeParams
     const int k0 = r * st.rows[m], rows = min(st.rows[m], st.K[m] - k0), ncols = st.ncols[m], cg_n = ncols >> 3;
     const bf16* W = p.Pb + p.l_off[st.lid[m]] + (long long)l * p.layer_stride + (size_t)k0 * st.N[m] + rank * ncols;
     const uint32_t dst = smem_u32(slots + (size_t)(g % DC_SLOTS) * DC_SLOT_BYTES);
-    for (int i = threadIdx.x; i < rows * cg_n; i += DC_THREADS) {
-      const int row = i / cg_n, cg = i - row * cg_n;
+    // chunk i = (row, cg) = (i / cg_n, i % cg_n), i = threadIdx.x, + DC_THREADS, ...: stepped without divisions
+    int row = threadIdx.x / cg_n, cg = threadIdx.x - row * cg_n;
+    const int drow = DC_THREADS / cg_n, dcg = DC_THREADS - drow * cg_n;
+    while (row < rows) {
       asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + (uint32_t)(row * ncols + cg * 8) * 2u), "l"(W + (size_t)row * st.N[m] + cg * 8)
                    : "memory");
+      row += drow; cg += dcg;
+      if (cg >= cg_n) { cg -= cg_n; ++row; }
     }
   }
   asm volatile("cp.async.commit_group;" ::: "memory");
@@ -149,20 +153,22 @@ __device__ __forceinline__ void dc_gemv(DcStream& st, const DecodeParams& p, int
     const uint8_t* slot = slots + (size_t)(consumed % DC_SLOTS) * DC_SLOT_BYTES;
     const int k0 = tile * st.rows[m], rows = min(st.rows[m], K - k0);
     if (kg < KG) {
-      for (int r = kg; r < rows; r += KG) {
-        const uint4 w = *reinterpret_cast<const uint4*>(slot + (size_t)(r * ncols + cg * 8) * 2);
+      // all DC_NT accumulator rows are always computed (rows >= n read whatever the input buffer holds and are never used): no branches,
+      // pointers stepped by constants — the loop is 1 LDS.128 + 3 LDS + 8 unpack + 24 FFMA
+      const uint8_t* wp = slot + (size_t)(kg * ncols + cg * 8) * 2;
+      const float* ip = in + k0 + kg;
+      const int wstep = KG * ncols * 2;
+      for (int r = kg; r < rows; r += KG, wp += wstep, ip += KG) {
+        const uint4 w = *reinterpret_cast<const uint4*>(wp);
         const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
+        const float a0 = ip[0], a1 = ip[K], a2 = ip[2 * K];
 #pragma unroll
-        for (int t = 0; t < DC_NT; ++t)
-          if (t < n) {
-            const float a = in[t * K + k0 + r];
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-              const float2 f = unpack_bf16x2(ww[e]);
-              acc[t][2 * e] = fmaf(a, f.x, acc[t][2 * e]);
-              acc[t][2 * e + 1] = fmaf(a, f.y, acc[t][2 * e + 1]);
-            }
-          }
+        for (int e = 0; e < 4; ++e) {
+          const float lo = __uint_as_float(ww[e] << 16), hi = __uint_as_float(ww[e] & 0xffff0000u);
+          acc[0][2 * e] = fmaf(a0, lo, acc[0][2 * e]); acc[0][2 * e + 1] = fmaf(a0, hi, acc[0][2 * e + 1]);
+          acc[1][2 * e] = fmaf(a1, lo, acc[1][2 * e]); acc[1][2 * e + 1] = fmaf(a1, hi, acc[1][2 * e + 1]);
+          acc[2][2 * e] = fmaf(a2, lo, acc[2][2 * e]); acc[2][2 * e + 1] = fmaf(a2, hi, acc[2][2 * e + 1]);
+        }
       }
     }
     dc_stream_issue(st, p, rank, slots);  // tile consumed + DEPTH goes into the slot tile consumed - 1 used (free since the barrier above)
