@@ -83,7 +83,7 @@ __device__ __forceinline__ void dc_layernorm(const float* x, float* y, int n, in
 
 // ---- weight stream -------------------------------------------------------------------------------------------------------------------
 // The kernel is bound by streaming this CTA's column slices of the four weight matrices of every layer from L2.  They are walked as ONE
-// sequence of tiles (layer, matrix, k range): [rows][ncols] bf16, copied by all threads with cp.async (16 bytes each, no registers) into
+// sequence of tiles (layer, matrix, k range): [rows][ncols] bf16, copied by TMA bulk copies (one per tile row, issued by warp 0) into
 // a ring of DC_SLOTS shared-memory slots, DC_DEPTH tiles ahead of the tile being consumed.  The sequence runs straight through the phase
 // boundaries of the forward, so the next matrix (and the next layer) is already landing while a phase waits at a cluster barrier, runs
 // its LayerNorm or the attention.  (First version: __ldg in the GEMV loop — one dependent L2 round trip per 8 loads, 140 us at c1.)
@@ -109,35 +109,34 @@ __device__ __forceinline__ void dc_stream_init(DcStream& st, const DecodeParams&
   st.total = st.per_layer * p.L;
   st.issued = 0;
 }
-// issue the copies of tile g (or an empty group past the end, so that every thread always has the same number of groups pending)
-__device__ __forceinline__ void dc_stream_issue(DcStream& st, const DecodeParams& p, int rank, uint8_t* slots) {
+// Warp 0 issues tile g: one bulk copy (TMA, cp.async.bulk) per tile row — ncols * 2 contiguous bytes of W — completing on the slot's
+// mbarrier.  (A first version used one 16-byte cp.async per thread and chunk: ncu showed 24 % of all instructions in that address
+// arithmetic, and the kernel issue-bound.)
+__device__ __forceinline__ void dc_stream_issue(DcStream& st, const DecodeParams& p, int rank, uint8_t* slots, uint64_t* full) {
   const int g = st.issued++;
-  if (g < st.total) {
-    const int l = g / st.per_layer;
-    int r = g - l * st.per_layer, m = 0;
-    while (r >= st.tiles[m]) { r -= st.tiles[m]; ++m; }
-    const int k0 = r * st.rows[m], rows = min(st.rows[m], st.K[m] - k0), ncols = st.ncols[m], cg_n = ncols >> 3;
-    const bf16* W = p.Pb + p.l_off[st.lid[m]] + (long long)l * p.layer_stride + (size_t)k0 * st.N[m] + rank * ncols;
-    const uint32_t dst = smem_u32(slots + (size_t)(g % DC_SLOTS) * DC_SLOT_BYTES);
-    // chunk i = (row, cg) = (i / cg_n, i % cg_n), i = threadIdx.x, + DC_THREADS, ...: stepped without divisions
-    int row = threadIdx.x / cg_n, cg = threadIdx.x - row * cg_n;
-    const int drow = DC_THREADS / cg_n, dcg = DC_THREADS - drow * cg_n;
-    while (row < rows) {
-      asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + (uint32_t)(row * ncols + cg * 8) * 2u), "l"(W + (size_t)row * st.N[m] + cg * 8)
-                   : "memory");
-      row += drow; cg += dcg;
-      if (cg >= cg_n) { cg -= cg_n; ++row; }
-    }
-  }
-  asm volatile("cp.async.commit_group;" ::: "memory");
+  if (g >= st.total || (threadIdx.x >> 5) != 0) return;
+  const int lane = threadIdx.x & 31;
+  const int l = g / st.per_layer;
+  int r = g - l * st.per_layer, m = 0;
+  while (r >= st.tiles[m]) { r -= st.tiles[m]; ++m; }
+  const int k0 = r * st.rows[m], rows = min(st.rows[m], st.K[m] - k0), ncols = st.ncols[m];
+  const bf16* W = p.Pb + p.l_off[st.lid[m]] + (long long)l * p.layer_stride + (size_t)k0 * st.N[m] + rank * ncols;
+  const int slot = g % DC_SLOTS;
+  const uint32_t dst = smem_u32(slots + (size_t)slot * DC_SLOT_BYTES), bar = smem_u32(&full[slot]), row_bytes = (uint32_t)ncols * 2u;
+  if (lane == 0) mbar_arrive_expect_tx(&full[slot], (uint32_t)rows * row_bytes);
+  __syncwarp();
+  for (int row = lane; row < rows; row += 32)
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst + (uint32_t)row * row_bytes),
+                 "l"(W + (size_t)row * st.N[m]), "r"(row_bytes), "r"(bar)
+                 : "memory");
 }
 
 // Column slice of  out[t][c] = sum_k in[t][k] W[k][c]  for the n tokens, W = matrix m of the current layer, read from the tile ring.
 // Thread (kg, cg): 8 adjacent columns (one 16-byte shared-memory load per k), k = kg, kg + KG, ... inside every tile; the KG partial
 // sums of a column are added in a fixed order (two levels).  `consumed` = tiles consumed so far (the stream position of this gemv).
 // Result left in red[t * ncols + j].
-__device__ __forceinline__ void dc_gemv(DcStream& st, const DecodeParams& p, int rank, uint8_t* slots, int& consumed, int m, const float* in,
-                                        int n, float* red) {
+__device__ __forceinline__ void dc_gemv(DcStream& st, const DecodeParams& p, int rank, uint8_t* slots, uint64_t* full, int& consumed, int m,
+                                        const float* in, int n, float* red) {
   const int K = st.K[m], ncols = st.ncols[m];
   const int CG = ncols >> 3;                 // 8-column groups of the slice
   const int KG = DC_THREADS / CG;            // k-lanes
@@ -148,8 +147,9 @@ __device__ __forceinline__ void dc_gemv(DcStream& st, const DecodeParams& p, int
 #pragma unroll
     for (int j = 0; j < 8; ++j) acc[t][j] = 0.f;
   for (int tile = 0; tile < st.tiles[m]; ++tile, ++consumed) {
-    asm volatile("cp.async.wait_group %0;" ::"n"(DC_DEPTH - 1) : "memory");  // this thread's copies of tile `consumed` have landed
-    __syncthreads();                                                         // ... everybody's have; and the slot issued next is free
+    __syncthreads();                           // everybody is done with tile consumed - 1: its slot is free for tile consumed + DEPTH
+    dc_stream_issue(st, p, rank, slots, full);
+    mbar_wait(&full[consumed % DC_SLOTS], (uint32_t)(consumed / DC_SLOTS) & 1u);  // tile `consumed` has landed
     const uint8_t* slot = slots + (size_t)(consumed % DC_SLOTS) * DC_SLOT_BYTES;
     const int k0 = tile * st.rows[m], rows = min(st.rows[m], K - k0);
     if (kg < KG) {
@@ -171,7 +171,6 @@ __device__ __forceinline__ void dc_gemv(DcStream& st, const DecodeParams& p, int
         }
       }
     }
-    dc_stream_issue(st, p, rank, slots);  // tile consumed + DEPTH goes into the slot tile consumed - 1 used (free since the barrier above)
   }
   if (kg < KG) {
 #pragma unroll
@@ -210,6 +209,7 @@ __global__ void __launch_bounds__(DC_THREADS, 1) dt_decode_kernel(const DecodePa
   float* hb = x + DC_NT * H;          // [NT][KI] GEMV input (LayerNorm output / attention output / MLP hidden), bf16-rounded values
   float* red = hb + DC_NT * KI;       // DC_RED_FLOATS: GEMV partial sums (two levels), attention merge
   uint8_t* slots = reinterpret_cast<uint8_t*>(red + DC_RED_FLOATS);  // weight tile ring (16-byte aligned: every region above is a multiple of 16 B)
+  uint64_t* full = reinterpret_cast<uint64_t*>(slots + (size_t)DC_SLOTS * DC_SLOT_BYTES);  // [DC_SLOTS] tile-landed barriers
   const int DC_CTAS = p.C;
   const int rank = (int)dc_cluster_rank();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -224,10 +224,15 @@ __global__ void __launch_bounds__(DC_THREADS, 1) dt_decode_kernel(const DecodePa
   pdl_trigger();
   pdl_wait();
   // start the weight stream: the first DEPTH tiles fly while the tokens are embedded
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < DC_SLOTS; ++i) mbar_init(&full[i], 1);
+    fence_mbar_init();
+  }
+  __syncthreads();
   DcStream st;
   dc_stream_init(st, p);
   int consumed = 0;
-  for (int i = 0; i < DC_DEPTH; ++i) dc_stream_issue(st, p, rank, slots);
+  for (int i = 0; i < DC_DEPTH; ++i) dc_stream_issue(st, p, rank, slots, full);
 
   // ---- wide state (tower features, bf16): projection Ws[H][sd] . s, column slice per CTA, one warp per output --------------------
   int wide_tok = -1;
@@ -305,7 +310,7 @@ __global__ void __launch_bounds__(DC_THREADS, 1) dt_decode_kernel(const DecodePa
     dc_layernorm(x, hb, n, H, P + p.l_off[L_LN1W] + lo, P + p.l_off[L_LN1B] + lo, p.eps);
     {
       const int ncols = 3 * H / DC_CTAS, c0 = rank * ncols;
-      dc_gemv(st, p, rank, slots, consumed, 0, hb, n, red);
+      dc_gemv(st, p, rank, slots, full, consumed, 0, hb, n, red);
       for (int i = threadIdx.x; i < n * ncols; i += DC_THREADS) {
         const int t = i / ncols, c = c0 + (i - t * ncols);
         const float v = red[i] + __ldg(P + p.l_off[L_BQKV] + lo + c);
@@ -401,7 +406,7 @@ __global__ void __launch_bounds__(DC_THREADS, 1) dt_decode_kernel(const DecodePa
     __syncthreads();
     {
       const int ncols = H / DC_CTAS, c0 = rank * ncols;
-      dc_gemv(st, p, rank, slots, consumed, 1, hb, n, red);
+      dc_gemv(st, p, rank, slots, full, consumed, 1, hb, n, red);
       for (int i = threadIdx.x; i < n * ncols; i += DC_THREADS) {
         const int t = i / ncols, c = c0 + (i - t * ncols);
         s_x1[t * H + c] = x[t * H + c] + red[i] + __ldg(P + p.l_off[L_BO] + lo + c);
@@ -414,7 +419,7 @@ __global__ void __launch_bounds__(DC_THREADS, 1) dt_decode_kernel(const DecodePa
     dc_layernorm(x, hb, n, H, P + p.l_off[L_LN2W] + lo, P + p.l_off[L_LN2B] + lo, p.eps);
     {
       const int ncols = I / DC_CTAS, c0 = rank * ncols;
-      dc_gemv(st, p, rank, slots, consumed, 2, hb, n, red);
+      dc_gemv(st, p, rank, slots, full, consumed, 2, hb, n, red);
       for (int i = threadIdx.x; i < n * ncols; i += DC_THREADS) {
         const int t = i / ncols, c = c0 + (i - t * ncols);
         s_fc[t * I + c] = dc_round_bf16(dc_act(red[i] + __ldg(P + p.l_off[L_B1] + lo + c), p.act));
@@ -426,7 +431,7 @@ __global__ void __launch_bounds__(DC_THREADS, 1) dt_decode_kernel(const DecodePa
     __syncthreads();
     {
       const int ncols = H / DC_CTAS, c0 = rank * ncols;
-      dc_gemv(st, p, rank, slots, consumed, 3, hb, n, red);
+      dc_gemv(st, p, rank, slots, full, consumed, 3, hb, n, red);
       for (int i = threadIdx.x; i < n * ncols; i += DC_THREADS) {
         const int t = i / ncols, c = c0 + (i - t * ncols);
         s_x2[t * H + c] = x[t * H + c] + red[i] + __ldg(P + p.l_off[L_B2] + lo + c);
@@ -510,7 +515,7 @@ int dtb_dt_decode(const dtb_dt* h, void* stream, const float* params, const void
   p.scratch = reinterpret_cast<float*>(base + kv);
   p.action_out = action_out;
   const int KI = c.hidden > c.n_inner ? c.hidden : c.n_inner;
-  const size_t smem = ((size_t)DC_NT * c.hidden + (size_t)DC_NT * KI + DC_RED_FLOATS) * sizeof(float) + (size_t)DC_SLOTS * DC_SLOT_BYTES;
+  const size_t smem = ((size_t)DC_NT * c.hidden + (size_t)DC_NT * KI + DC_RED_FLOATS) * sizeof(float) + (size_t)DC_SLOTS * DC_SLOT_BYTES + 64;
   static size_t attr = 0;
   if (smem > attr) {
     DTB_CUDA(cudaFuncSetAttribute(dt_decode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
