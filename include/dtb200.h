@@ -284,6 +284,10 @@ int dtb_dt_backward(const dtb_dt* h, void* stream, const float* params, const vo
  * t rows (states fp32 [t, sd] for state_dim <= 64, else states_bf16 [t, sd]).  t_cached = 0 starts a new episode. */
 int dtb_dt_decode_supported(const dtb_dt* h);
 size_t dtb_dt_decode_cache_bytes(const dtb_dt* h, int K);
+/* The kernel streams the weights by TMA bulk copies from a decode layout kept inside `cache` (per layer, matrix and CTA one contiguous
+ * [K][N / C] block): build it once with dtb_dt_decode_stage, and again after every parameter update (the cached keys / values are then
+ * stale too: restart with t_cached = 0). */
+int dtb_dt_decode_stage(const dtb_dt* h, void* stream, const void* params_bf16, int K, void* cache, size_t cache_bytes);
 int dtb_dt_decode(const dtb_dt* h, void* stream, const float* params, const void* params_bf16, const float* states, const void* states_bf16,
                   const float* actions, const float* returns_to_go, const long long* timesteps, int t, int t_cached, int K, void* cache,
                   size_t cache_bytes, float* action_out);

@@ -33,6 +33,8 @@ struct DecodeParams {
   float eps;
   const float* P;   // fp32 master (biases, LayerNorms, embeddings, heads)
   const bf16* Pb;   // bf16 shadow (the GEMM weights, same offsets)
+  const bf16* Wd;   // decode layout of the four weight matrices of every layer (dtb_dt_decode_stage)
+  bf16* Wd_out;     // (staging kernel only)
   long long e_off[E_COUNT], l_off[L_COUNT], t_off[T_COUNT], layer_stride;
   // history (device pointers, one row per timestep)
   const float* states;      // [t, sd] fp32 (vector states) or null
@@ -91,6 +93,7 @@ constexpr int DC_SLOT_BYTES = 24 * 1024, DC_SLOTS = 4, DC_DEPTH = 3;
 
 struct DcStream {
   int K[4], N[4], ncols[4], rows[4], tiles[4], lid[4];  // per matrix: q|k|v, attn.c_proj, mlp.c_fc, mlp.c_proj
+  size_t moff[4], layer_elems;                           // decode layout: element offset of matrix m inside a layer, elements per layer
   int per_layer, total;
   int issued;  // tiles issued so far (identical in every thread)
 };
@@ -98,7 +101,10 @@ __device__ __forceinline__ void dc_stream_init(DcStream& st, const DecodeParams&
   const int H = p.H, I = p.I;
   const int K[4] = {H, H, H, I}, N[4] = {3 * H, H, I, H}, lid[4] = {L_WQKV, L_WO, L_W1, L_W2};
   st.per_layer = 0;
+  st.layer_elems = 0;
   for (int m = 0; m < 4; ++m) {
+    st.moff[m] = st.layer_elems;
+    st.layer_elems += (size_t)K[m] * N[m];
     st.K[m] = K[m]; st.N[m] = N[m]; st.lid[m] = lid[m];
     st.ncols[m] = N[m] / p.C;
     int r = (DC_SLOT_BYTES / (st.ncols[m] * 2)) & ~7;
@@ -109,26 +115,48 @@ __device__ __forceinline__ void dc_stream_init(DcStream& st, const DecodeParams&
   st.total = st.per_layer * p.L;
   st.issued = 0;
 }
-// Warp 0 issues tile g: one bulk copy (TMA, cp.async.bulk) per tile row — ncols * 2 contiguous bytes of W — completing on the slot's
-// mbarrier.  (A first version used one 16-byte cp.async per thread and chunk: ncu showed 24 % of all instructions in that address
-// arithmetic, and the kernel issue-bound.)
+// Thread 0 issues tile g as ONE bulk copy (TMA, cp.async.bulk) completing on the slot's mbarrier: the weights are read from the decode
+// layout (dtb_dt_decode_stage), where the [K][ncols] column slice of every (layer, matrix, CTA rank) is one contiguous block, so a tile —
+// `rows` consecutive k of that block — is rows * ncols * 2 contiguous bytes.  (Earlier forms, measured: one 16-byte cp.async per thread
+// and chunk = 24 % of all instructions in address arithmetic and an issue-bound kernel; one bulk copy per 100-800 byte row of the
+// Conv1D-layout matrix = slower still, the copy engine pays per descriptor.)
 __device__ __forceinline__ void dc_stream_issue(DcStream& st, const DecodeParams& p, int rank, uint8_t* slots, uint64_t* full) {
   const int g = st.issued++;
-  if (g >= st.total || (threadIdx.x >> 5) != 0) return;
-  const int lane = threadIdx.x & 31;
+  if (g >= st.total || threadIdx.x != 0) return;
   const int l = g / st.per_layer;
   int r = g - l * st.per_layer, m = 0;
   while (r >= st.tiles[m]) { r -= st.tiles[m]; ++m; }
   const int k0 = r * st.rows[m], rows = min(st.rows[m], st.K[m] - k0), ncols = st.ncols[m];
-  const bf16* W = p.Pb + p.l_off[st.lid[m]] + (long long)l * p.layer_stride + (size_t)k0 * st.N[m] + rank * ncols;
+  const bf16* W = p.Wd + (size_t)l * st.layer_elems + st.moff[m] + ((size_t)rank * st.K[m] + k0) * ncols;
   const int slot = g % DC_SLOTS;
-  const uint32_t dst = smem_u32(slots + (size_t)slot * DC_SLOT_BYTES), bar = smem_u32(&full[slot]), row_bytes = (uint32_t)ncols * 2u;
-  if (lane == 0) mbar_arrive_expect_tx(&full[slot], (uint32_t)rows * row_bytes);
-  __syncwarp();
-  for (int row = lane; row < rows; row += 32)
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst + (uint32_t)row * row_bytes),
-                 "l"(W + (size_t)row * st.N[m]), "r"(row_bytes), "r"(bar)
-                 : "memory");
+  const uint32_t bytes = (uint32_t)rows * (uint32_t)ncols * 2u;
+  mbar_arrive_expect_tx(&full[slot], bytes);
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   smem_u32(slots + (size_t)slot * DC_SLOT_BYTES)),
+               "l"(W), "r"(bytes), "r"(smem_u32(&full[slot]))
+               : "memory");
+}
+
+// Conv1D-layout bf16 weights (the shadow the tensor-core path reads) -> decode layout: for every layer, matrix (q|k|v, attn.c_proj,
+// mlp.c_fc, mlp.c_proj) and CTA rank one contiguous [K][N / C] block.  One thread per 16-byte chunk.
+__global__ void __launch_bounds__(256) dt_decode_stage_kernel(const DecodeParams p, size_t layer_elems) {
+  pdl_trigger();
+  pdl_wait();
+  const int H = p.H, I = p.I;
+  const int K[4] = {H, H, H, I}, N[4] = {3 * H, H, I, H}, lid[4] = {L_WQKV, L_WO, L_W1, L_W2};
+  const size_t chunks_per_layer = layer_elems / 8, total = chunks_per_layer * p.L;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int l = (int)(i / chunks_per_layer);
+    size_t e = (i - (size_t)l * chunks_per_layer) * 8;  // element offset inside the layer (decode layout)
+    int m = 0;
+    while (e >= (size_t)K[m] * N[m]) { e -= (size_t)K[m] * N[m]; ++m; }
+    const int ncols = N[m] / p.C;
+    const int r = (int)(e / ((size_t)K[m] * ncols));
+    const size_t q = e - (size_t)r * K[m] * ncols;
+    const int k = (int)(q / ncols), c = (int)(q - (size_t)k * ncols);
+    const bf16* src = p.Pb + p.l_off[lid[m]] + (long long)l * p.layer_stride + (size_t)k * N[m] + r * ncols + c;
+    *reinterpret_cast<uint4*>(p.Wd_out + (size_t)l * layer_elems + (i - (size_t)l * chunks_per_layer) * 8) = __ldg(reinterpret_cast<const uint4*>(src));
+  }
 }
 
 // Column slice of  out[t][c] = sum_k in[t][k] W[k][c]  for the n tokens, W = matrix m of the current layer, read from the tile ring.
@@ -471,6 +499,12 @@ static int dc_cluster_size(const dtb_dt_config& c) {
   while (C < DC_MAX_CTAS && layer_bytes / C > 512.0 * 1024.0 && c.hidden % (16 * C) == 0 && c.n_inner % (16 * C) == 0) C *= 2;
   return C;
 }
+static size_t dc_layer_elems(const dtb_dt_config& c) { return (size_t)4 * c.hidden * c.hidden + (size_t)2 * c.hidden * c.n_inner; }
+// byte offset of the decode-layout weights inside the cache buffer: after the K/V cache and the exchange scratch
+static size_t dc_wd_offset(const dtb_dt_config& c, int K) {
+  const size_t kv = ((size_t)2 * c.n_layer * 3 * K * c.hidden * sizeof(bf16) + 255) & ~size_t(255);
+  return kv + ((dc_scratch_floats(c.hidden, c.n_inner) * sizeof(float) + 255) & ~size_t(255));
+}
 int dtb_dt_decode_supported(const dtb_dt* h) {
   if (!h) return 0;
   const dtb_dt_config& c = h->c;
@@ -483,8 +517,42 @@ int dtb_dt_decode_supported(const dtb_dt* h) {
 size_t dtb_dt_decode_cache_bytes(const dtb_dt* h, int K) {
   if (!h || K < 1) return 0;
   const dtb_dt_config& c = h->c;
-  const size_t kv = (size_t)2 * c.n_layer * 3 * K * c.hidden * sizeof(bf16);
-  return ((kv + 255) & ~size_t(255)) + dc_scratch_floats(c.hidden, c.n_inner) * sizeof(float) + 256;
+  return dc_wd_offset(c, K) + dc_layer_elems(c) * c.n_layer * sizeof(bf16) + 256;
+}
+
+static void dc_fill(const dtb_dt* h, DecodeParams& p, const float* params, const void* params_bf16, void* cache, int K) {
+  const dtb_dt_config& c = h->c;
+  memset(&p, 0, sizeof(p));
+  p.H = c.hidden; p.I = c.n_inner; p.L = c.n_layer; p.nh = c.n_head; p.d = c.hidden / c.n_head; p.sd = c.state_dim; p.ad = c.act_dim;
+  p.E = c.max_ep_len; p.act = c.activation; p.tanh_act = c.action_tanh; p.sd_small = h->sd_small; p.eps = c.ln_eps;
+  p.P = params; p.Pb = reinterpret_cast<const bf16*>(params_bf16);
+  for (int i = 0; i < E_COUNT; ++i) p.e_off[i] = h->e(i);
+  for (int i = 0; i < L_COUNT; ++i) p.l_off[i] = h->l(0, i);
+  for (int i = 0; i < T_COUNT; ++i) p.t_off[i] = h->t(i);
+  p.layer_stride = c.n_layer > 1 ? h->l(1, 0) - h->l(0, 0) : 0;
+  uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(cache) + 255) & ~uintptr_t(255));
+  p.Tmax = 3 * K;
+  p.kc = reinterpret_cast<bf16*>(base);
+  p.vc = p.kc + (size_t)c.n_layer * p.Tmax * c.hidden;
+  const size_t kv = ((size_t)2 * c.n_layer * p.Tmax * c.hidden * sizeof(bf16) + 255) & ~size_t(255);
+  p.scratch = reinterpret_cast<float*>(base + kv);
+  p.Wd = p.Wd_out = reinterpret_cast<bf16*>(base + dc_wd_offset(c, K));
+  p.C = dc_cluster_size(c);
+}
+
+// (Re)build the decode layout of the weights inside `cache` from the bf16 shadow: call once, and again whenever the parameters changed.
+int dtb_dt_decode_stage(const dtb_dt* h, void* stream, const void* params_bf16, int K, void* cache, size_t cache_bytes) {
+  DTB_REQUIRE(h && params_bf16 && cache, DTB_ERR_BAD_ARG, "dtb_dt_decode_stage: null argument");
+  DTB_REQUIRE(dtb_dt_decode_supported(h), DTB_ERR_UNSUPPORTED, "dtb_dt_decode_stage: hidden %d / n_inner %d unsupported", h->c.hidden, h->c.n_inner);
+  DTB_REQUIRE(cache_bytes >= dtb_dt_decode_cache_bytes(h, K), DTB_ERR_WORKSPACE, "dtb_dt_decode_stage: cache too small");
+  DecodeParams p;
+  dc_fill(h, p, nullptr, params_bf16, cache, K);
+  const size_t chunks = dc_layer_elems(h->c) * h->c.n_layer / 8;
+  size_t blocks = (chunks + 255) / 256;
+  if (blocks > (size_t)num_sms() * 8) blocks = (size_t)num_sms() * 8;
+  DTB_LAUNCH(dt_decode_stage_kernel, (unsigned)blocks, 256, 0, (cudaStream_t)stream, p, dc_layer_elems(h->c));
+  DTB_CHECK_LAUNCH();
+  return DTB_OK;
 }
 
 int dtb_dt_decode(const dtb_dt* h, void* stream, const float* params, const void* params_bf16, const float* states, const void* states_bf16,
@@ -498,21 +566,8 @@ int dtb_dt_decode(const dtb_dt* h, void* stream, const float* params, const void
   DTB_TRY(require_sm100());
   const dtb_dt_config& c = h->c;
   DecodeParams p;
-  memset(&p, 0, sizeof(p));
-  p.H = c.hidden; p.I = c.n_inner; p.L = c.n_layer; p.nh = c.n_head; p.d = c.hidden / c.n_head; p.sd = c.state_dim; p.ad = c.act_dim;
-  p.E = c.max_ep_len; p.act = c.activation; p.tanh_act = c.action_tanh; p.sd_small = h->sd_small; p.eps = c.ln_eps;
-  p.P = params; p.Pb = reinterpret_cast<const bf16*>(params_bf16);
-  for (int i = 0; i < E_COUNT; ++i) p.e_off[i] = h->e(i);
-  for (int i = 0; i < L_COUNT; ++i) p.l_off[i] = h->l(0, i);
-  for (int i = 0; i < T_COUNT; ++i) p.t_off[i] = h->t(i);
-  p.layer_stride = c.n_layer > 1 ? h->l(1, 0) - h->l(0, 0) : 0;
+  dc_fill(h, p, params, params_bf16, cache, K);
   p.states = states; p.states_bf16 = reinterpret_cast<const bf16*>(states_bf16); p.actions = actions; p.rtg = returns_to_go; p.timesteps = timesteps;
-  uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(cache) + 255) & ~uintptr_t(255));
-  p.Tmax = 3 * K;
-  p.kc = reinterpret_cast<bf16*>(base);
-  p.vc = p.kc + (size_t)c.n_layer * p.Tmax * c.hidden;
-  const size_t kv = ((size_t)2 * c.n_layer * p.Tmax * c.hidden * sizeof(bf16) + 255) & ~size_t(255);
-  p.scratch = reinterpret_cast<float*>(base + kv);
   p.action_out = action_out;
   const int KI = c.hidden > c.n_inner ? c.hidden : c.n_inner;
   const size_t smem = ((size_t)DC_NT * c.hidden + (size_t)DC_NT * KI + DC_RED_FLOATS) * sizeof(float) + (size_t)DC_SLOTS * DC_SLOT_BYTES + 64;
@@ -522,7 +577,6 @@ int dtb_dt_decode(const dtb_dt* h, void* stream, const float* params, const void
     DTB_CUDA(cudaFuncSetAttribute(dt_decode_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
     attr = smem;
   }
-  p.C = dc_cluster_size(c);
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));
   cfg.gridDim = dim3(p.C); cfg.blockDim = dim3(DC_THREADS); cfg.dynamicSmemBytes = smem; cfg.stream = (cudaStream_t)stream;

@@ -347,8 +347,11 @@ class DecisionTransformer(nn.Module):
             dc = self._dc = dict(cache=torch.zeros(nbytes, dtype=torch.uint8, device=self._flat.device), t=0, stamp=-1, ptr=self._flat.data_ptr(),
                                  out=torch.zeros(self.act_dim, dtype=torch.float32, device=self._flat.device))
         self._stage()
-        if dc["stamp"] != self._staged_version or t <= dc["t"]:  # weights changed, or a new episode / repeated call: start over
+        if dc["stamp"] != self._staged_version:  # weights changed: rebuild the decode layout, forget the cached keys / values
+            _lib.check(lib.dtb_dt_decode_stage(self._h, _lib.stream_ptr(), _lib.ptr(self._flat_bf16), K, _lib.ptr(dc["cache"]), dc["cache"].numel()))
             dc["t"], dc["stamp"] = 0, self._staged_version
+        if t <= dc["t"]:  # a new episode / repeated call: start over
+            dc["t"] = 0
         _lib.check(lib.dtb_dt_decode(self._h, _lib.stream_ptr(), _lib.ptr(self._flat), _lib.ptr(self._flat_bf16), _lib.ptr(states),
                                      _lib.ptr(states_bf16), _lib.ptr(actions), _lib.ptr(returns_to_go), _lib.ptr(timesteps), t, dc["t"], K,
                                      _lib.ptr(dc["cache"]), dc["cache"].numel(), _lib.ptr(dc["out"])))
