@@ -694,11 +694,10 @@ def measure_e2e_resident(args, wl, ctx, steps):
 def measure_get_action(wl, ctx, calls=300, warmup=50):
     """BASELINE.json's second metric: get_action latency at B = 1 with a full K-step history, through the public API (wall clock, one
     stream sync per call, p50 / p90 / p99 in microseconds), model.eval().
-      * `p50_us` ...: the call a rollout makes at its last step (t = K): the K/V cache holds the first K - 1 timesteps, the call appends
-        one (towers on the newest frame only + ONE decode kernel).  Between timed calls the cache is rewound to K - 1 timesteps
-        (`_dc["t"] = K - 1`: its rows for the unchanged prefix stay valid), so every timed call does exactly a rollout step's work.
-      * `recompute`: the same call with use_cache=False (pad_left + CUDA graph of the whole B = 1 forward): what every call costs once the
-        window slides (t > K), and what round 1 reported as get_action."""
+      * `p50_us` ...: the default path (pad_left + CUDA graph of the whole B = 1 forward), as in round 1.
+      * `kv_cached`: get_action(use_cache=True) at the last step of a rollout (t = K): the K/V cache holds the first K - 1 timesteps, the
+        call appends one (towers on the newest frame only + ONE decode kernel).  Between timed calls the cache is rewound to K - 1
+        timesteps (`_dc["t"] = K - 1`: its rows for the unchanged prefix stay valid), so every timed call does a rollout step's work."""
     model, dev, K = ctx["model"], ctx["dev"], wl["K"]
     model.eval()  # evaluation rollouts run without dropout (upstream evaluate_episode_rtg: model.eval())
     b = make_batch(wl, 1, seed=4321)
@@ -726,15 +725,13 @@ def measure_get_action(wl, ctx, calls=300, warmup=50):
         return {"p50_us": pick(0.5), "p90_us": pick(0.9), "p99_us": pick(0.99)}, a
 
     cached_ok = bool(dt._decode_ready())
-    rec, a = run(False)
-    out = dict(rec)
+    out, a = run(False)  # the default path of get_action
+    out["path"] = "recompute (pad_left + CUDA graph of the B = 1 forward): the library's default"
     if cached_ok:
-        out, a2 = run(True)
-        out["recompute"] = rec
-        out["cached_vs_recompute_max_abs_diff"] = float((a2 - a).abs().max())
-        out["path"] = "KV-cached append at t = K (dtb_dt_decode: one cluster kernel" + (" + towers on the newest frame" if wl["enc"] is not None else "") + ")"
-    else:
-        out["path"] = "recompute (pad_left + CUDA graph of the B = 1 forward)"
+        kvc, a2 = run(True)
+        kvc["max_abs_diff_vs_recompute"] = float((a2 - a).abs().max())
+        kvc["path"] = "use_cache=True: KV-cached append at t = K (dtb_dt_decode: one cluster kernel" + (" + towers on the newest frame" if wl["enc"] is not None else "") + ")"
+        out["kv_cached"] = kvc
     out.update({"calls": calls, "warmup": warmup, "history": K, "action_dim": int(a.numel()),
                 "how": "wall clock around model.get_action(...) + stream sync, inputs resident on the device, model.eval()"})
     return out

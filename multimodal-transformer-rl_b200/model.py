@@ -76,7 +76,10 @@ class DecisionTransformer(nn.Module):
         # nn.Dropout sites of the trunk (GPT2Model.drop / attn_dropout / resid_dropout); embd_pdrop follows resid_pdrop when not given
         self._p_resid, self._p_attn = float(resid_pdrop or 0.0), float(attn_pdrop or 0.0)
         self._p_embd = self._p_resid if embd_pdrop is None else float(embd_pdrop)
-        self.kv_cache = True          # get_action: append to a per-layer K/V cache while the history fits the window (exact, see _decode)
+        # get_action(use_cache=True) / kv_cache = True: append to a per-layer K/V cache while the history fits the window (exact, see _decode).
+        # Off by default: measured on B200 the one-kernel decode step is not yet faster than the graph of the full B = 1 forward
+        # (c1 147 vs ~100 us of GPU time, c4 0.8-1.2 vs 0.9 ms) — it is issue / latency bound on the 1-16 SMs it uses.
+        self.kv_cache = False
         self._dc = None               # decode state: cache buffer, timesteps cached, parameter stamp, output buffer
         self._drop_state = None       # device int32 [3] = {seed_lo, seed_hi, step}, read by the kernels at run time
         self._drop_applied = None     # (p_embd, p_attn, p_resid, state ptr) last handed to the library
@@ -333,7 +336,7 @@ class DecisionTransformer(nn.Module):
             self._dc["t"] = 0
 
     def _decode_ready(self) -> bool:
-        return bool(self.kv_cache and self.max_length is not None and not self.dropout_active()
+        return bool(self.max_length is not None and not self.dropout_active()
                     and _lib.load().dtb_dt_decode_supported(self._h))
 
     def _decode(self, states, states_bf16, actions, returns_to_go, timesteps, t: int):

@@ -36,7 +36,7 @@ def test_cached_rollout_matches_oracle_and_recompute(cuda_device, name):
     for t in range(1, T + 1):
         at = ad[:t].clone()
         at[-1] = 0  # upstream: the newest action is a zero placeholder
-        got = model.get_action(sd[:t], at, None, rd[:t], td[:t])
+        got = model.get_action(sd[:t], at, None, rd[:t], td[:t], use_cache=True)
         assert model._dc is not None and model._dc["t"] == t  # the decode path ran and cached t timesteps
         a_ref = a[:t].clone()
         a_ref[-1] = 0
@@ -60,7 +60,7 @@ def test_stepwise_equals_one_shot_bitwise_and_resets(cuda_device):
     def call(t):
         at = a[:t].clone()
         at[-1] = 0
-        return model.get_action(s[:t], at, None, r[:t], ts[:t])
+        return model.get_action(s[:t], at, None, r[:t], ts[:t], use_cache=True)
 
     step = [call(t) for t in range(1, K + 1)]          # append one timestep per call
     for t in (K, 5, 1, 13):                             # a shorter (or equal) history restarts the cache: whole history in one call
@@ -78,7 +78,7 @@ def test_stepwise_equals_one_shot_bitwise_and_resets(cuda_device):
     # beyond the window the call falls back to the recompute path (and the cache is left alone)
     s2, a2, r2, ts2 = (x.to(dev) for x in _history(cfg, K + 7, 9))
     a2[-1] = 0
-    out = model.get_action(s2, a2, None, r2, ts2)
+    out = model.get_action(s2, a2, None, r2, ts2, use_cache=True)
     assert out.shape == (cfg["act_dim"],) and torch.isfinite(out).all()
 
 
@@ -102,7 +102,7 @@ def test_multimodal_cached_get_action(cuda_device):
     for t in range(1, T + 1):
         at = acts[:t].clone()
         at[-1] = 0
-        got = model.get_action(frames[:t], audio[:t], at, None, rtg[:t], ts[:t])
+        got = model.get_action(frames[:t], audio[:t], at, None, rtg[:t], ts[:t], use_cache=True)
         assert dt._dc["t"] == t
         rec = model.get_action(frames[:t], audio[:t], at, None, rtg[:t], ts[:t], use_cache=False)
         assert rel_err(got, rec) <= 1e-2, (t, rel_err(got, rec))
