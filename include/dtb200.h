@@ -133,6 +133,15 @@ int dtb_cast_transpose(void* stream, const float* src, int R, int C, void* dst, 
 int dtb_pad_left(void* stream, int nseg, const void* const* srcs, void* const* dsts, const int* row_bytes, int t, int K, float* mask_out);
 size_t dtb_colsum_scratch_floats(int N);
 int dtb_colsum_bf16(void* stream, const void* x, int M, int N, int ld, float* out, int accumulate, float* scratch);
+/* Allocation-free variant of dtb_colsum_bf16.  NO counterpart in the reference: added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same kernels,
+ * same slab count and therefore bit-identical results; the slab partials live in a 256 KB file-scope `static __device__` array inside
+ * the library (held by every GPU that loads libdtb200.so until exit) instead of caller scratch.  Limit: N <= DTB_COLSUM_STATIC_MAX_N
+ * columns (larger N -> DTB_ERR_BAD_ARG with a message; use dtb_colsum_bf16).  Calls no cudaMalloc / cudaFree / allocating routine.
+ * Every call on a device shares the one array: calls that overlap on the GPU (different streams without ordering) race; calls on
+ * one stream, or ordered by events, are safe.  Nothing in the array has to start at zero (stage 1 overwrites what stage 2 reads). */
+#define DTB_COLSUM_STATIC_MAX_N 1024
+int dtb_colsum_bf16_static(void* stream, const void* x, int M, int N, int ld, float* out, int accumulate);
 
 /* ---- fused token embedding (HF:611-628): timestep gather + RTG/state/action projections + interleave + embed_ln -----
  * x fp32 [B*K*3, H] in token order R_k, s_k, a_k.  Exactly one of states (fp32 [BK, sd], sd <= 64) / state_proj

@@ -293,6 +293,12 @@ def colsum_bf16(x, out, accumulate=False):
     check(lib.dtb_colsum_bf16(stream_ptr(), ptr(x), M, N, x.stride(0), ptr(out), int(accumulate), ptr(scratch)))
 
 
+def colsum_bf16_static(x, out, accumulate=False):
+    """dtb_colsum_bf16_static: same result as colsum_bf16, scratch in the library's static device array; allocates nothing (N <= 1024)."""
+    M, N = x.shape
+    check(load().dtb_colsum_bf16_static(stream_ptr(), ptr(x), M, N, x.stride(0), ptr(out), int(accumulate)))
+
+
 def embed_fwd(states, state_proj, actions, rtg, timesteps, table, wR, bR, Ws, bs, Wa, ba, gamma, beta, eps, x, pre=None, mean=None,
               rstd=None, U=None, u_states=True):
     BK, ad = actions.shape

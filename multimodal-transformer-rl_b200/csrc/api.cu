@@ -158,6 +158,10 @@ int dtb_colsum_bf16(void* stream, const void* x, int M, int N, int ld, float* ou
   DTB_REQUIRE(x && out && scratch, DTB_ERR_BAD_ARG, "dtb_colsum_bf16: null pointer");
   return colsum_bf16((cudaStream_t)stream, (const bf16*)x, M, N, ld, out, accumulate, scratch);
 }
+int dtb_colsum_bf16_static(void* stream, const void* x, int M, int N, int ld, float* out, int accumulate) {
+  DTB_REQUIRE(x && out, DTB_ERR_BAD_ARG, "dtb_colsum_bf16_static: null pointer");
+  return colsum_bf16_static((cudaStream_t)stream, (const bf16*)x, M, N, ld, out, accumulate);
+}
 
 int dtb_embed_fwd(void* stream, const float* states, const float* state_proj, const float* actions, const float* rtg,
                   const long long* timesteps, const float* table, const float* wR, const float* bR, const float* Ws, const float* bs,

@@ -136,6 +136,54 @@ int colsum_bf16(cudaStream_t stream, const bf16* x, int M, int N, int ld, float*
   return DTB_OK;
 }
 
+// ---- allocation-free column sum (C ABI dtb_colsum_bf16_static; no counterpart in the reference) ----------------------------------
+// Same two kernels as colsum_bf16, with the slab partials in a file-scope device array instead of caller scratch, for callers that
+// cannot allocate (graph capture, serving loops).  The array costs CS_STATIC_FLOATS * 4 = 256 KB on every GPU that loads the library.
+// Its host-side name is only a handle: the device address is looked up once per device with cudaGetSymbolAddress (that device
+// current) and cached.  CS_STATIC_FLOATS == CS_SCRATCH_MIN == colsum_scratch_floats(N) for every N <= CS_STATIC_MAX_N, so the slab
+// count — and therefore every bit of the result — equals dtb_colsum_bf16's.  Stage 1 overwrites every partial stage 2 reads: nothing
+// has to start at zero.  All calls share the array: calls that overlap on the GPU (different streams, no ordering) race.
+constexpr int CS_STATIC_FLOATS = CS_SCRATCH_MIN;
+constexpr int CS_STATIC_MAX_N = CS_STATIC_FLOATS / 64;  // 1024 columns
+constexpr int CS_STATIC_MAX_DEVICES = 64;
+static __device__ __align__(256) float g_colsum_static[CS_STATIC_FLOATS];
+static float* g_colsum_static_ptr[CS_STATIC_MAX_DEVICES] = {};
+
+static_assert(CS_STATIC_MAX_N == DTB_COLSUM_STATIC_MAX_N, "include/dtb200.h states the limit");
+
+int colsum_bf16_static(cudaStream_t stream, const bf16* x, int M, int N, int ld, float* out, int accumulate) {
+  DTB_REQUIRE(M >= 1 && N >= 8 && N % 8 == 0 && ld % 8 == 0 && ld >= N && (reinterpret_cast<uintptr_t>(x) & 15) == 0, DTB_ERR_BAD_ARG,
+              "colsum_static: M >= 1, N and ld multiples of 8, ld >= N and x 16-byte aligned required (M=%d N=%d ld=%d)", M, N, ld);
+  DTB_REQUIRE(N <= CS_STATIC_MAX_N, DTB_ERR_BAD_ARG,
+              "colsum_static: N=%d exceeds the static scratch limit of %d columns (use dtb_colsum_bf16 with caller scratch)", N,
+              CS_STATIC_MAX_N);
+  int dev = -1;
+  DTB_CUDA(cudaGetDevice(&dev));
+  DTB_REQUIRE(dev >= 0 && dev < CS_STATIC_MAX_DEVICES, DTB_ERR_BAD_ARG, "colsum_static: device ordinal %d out of range", dev);
+  float* scratch = g_colsum_static_ptr[dev];
+  if (!scratch) {  // set-up, once per device, with that device current
+    DTB_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&scratch), g_colsum_static));
+    DTB_REQUIRE(scratch != nullptr, DTB_ERR_CUDA, "colsum_static: cudaGetSymbolAddress returned a null device address");
+    g_colsum_static_ptr[dev] = scratch;
+  }
+  const int n8 = N / 8;
+  int cx = 4;
+  while (cx < 32 && cx < n8) cx *= 2;
+  const int ry = 256 / cx;
+  const int colgroups = (n8 + cx - 1) / cx;
+  int nslab = (4 * num_sms() + colgroups - 1) / colgroups;
+  const int max_slab = (M + 4 * ry - 1) / (4 * ry);
+  if (nslab > max_slab) nslab = max_slab;
+  if (nslab > CS_SLABS_MAX) nslab = CS_SLABS_MAX;
+  if ((size_t)nslab * N > (size_t)CS_STATIC_FLOATS) nslab = CS_STATIC_FLOATS / N;
+  if (nslab < 1) nslab = 1;
+  DTB_LAUNCH(colsum_stage1, dim3(colgroups, nslab), dim3(cx, ry), 0, stream, x, M, N, ld, scratch);
+  DTB_CHECK_LAUNCH();
+  DTB_LAUNCH(colsum_stage2, (N + 31) / 32, dim3(32, 8), 0, stream, (const float*)scratch, nslab, N, out, accumulate);
+  DTB_CHECK_LAUNCH();
+  return DTB_OK;
+}
+
 // ---- get_action history packing: keep the t most recent rows, LEFT-pad with zeros to K rows, mask = [0]*(K-t)+[1]*t ----
 // One launch for all per-timestep tensors of the call (states / frames / audio / actions / rtg / timesteps): segment s has
 // row_words[s] 32-bit words per timestep; blockIdx.y = segment.  Padding and indexing are integer-exact copies.

@@ -75,6 +75,7 @@ int cast_bf16(cudaStream_t stream, const float* src, size_t n, bf16* dst);
 // column sums of a bf16 matrix [M, N] (ld) -> fp32 out[N] (+= if accumulate)
 int colsum_bf16(cudaStream_t stream, const bf16* x, int M, int N, int ld, float* out, int accumulate, float* scratch);
 size_t colsum_scratch_floats(int N);
+int colsum_bf16_static(cudaStream_t stream, const bf16* x, int M, int N, int ld, float* out, int accumulate);  // scratch = static device array
 
 // dropout plumbing: advance the device-resident step counter; export keep bits for the tests (groups = 0: no group folding)
 int dropout_advance(cudaStream_t stream, void* state);
