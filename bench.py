@@ -119,7 +119,7 @@ def make_step(wl, model, parts, dev_in, reducer, grad_scale):
     d = dev_in
     if wl["enc"] is None:
         dt = parts[0]
-        cb = None if reducer is None else (lambda stage, b, e: reducer.ready(dt.flat_grads, b, e))
+        cb = None if reducer is None else reducer.callback_for(model)
 
         def step():
             out = model.loss_and_backward(d["states"], d["actions"], d["rtg"], d["timesteps"], d["mask"], grad_scale=grad_scale, on_stage_done=cb)
@@ -128,7 +128,7 @@ def make_step(wl, model, parts, dev_in, reducer, grad_scale):
             return out
     else:
         dt, enc = parts
-        cb = None if reducer is None else (lambda stage, b, e: reducer.ready(enc.flat_grads if stage == "encoder" else dt.flat_grads, b, e))
+        cb = None if reducer is None else reducer.callback_for(model)  # trunk buckets + the towers' FC range overlap the backward
 
         def step():
             out = model.loss_and_backward(d["frames"], d["audio"], d["actions"], d["rtg"], d["timesteps"], d["mask"], grad_scale=grad_scale,
@@ -793,7 +793,7 @@ def main():
     ap.add_argument("--batch", type=int, default=0, help="per-GPU batch override (default: the workload's)")
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--flush-l2", action="store_true")
-    ap.add_argument("--bucket-mb", type=int, default=8)
+    ap.add_argument("--bucket-mb", type=int, default=2)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-roofline", action="store_true")
     ap.add_argument("--no-get-action", action="store_true", help="skip the get_action latency measurement (keeps ncu launch lists to the training step)")
@@ -877,8 +877,33 @@ def main():
             res["next_rows"] = next_rows()
         print(json.dumps(res), flush=True)
     if world > 1:
+        # The line is out; nothing below may keep the job alive.  Tear down in order (graphs holding captured NCCL kernels first, then the
+        # process group) under a watchdog: if any step of the teardown blocks, exit 0 after 30 s (stderr says where it stopped).
+        import gc
+
+        where = ["start"]
+
+        def _bail():
+            print(f"[bench] rank {rank}: teardown did not finish within 30 s (stuck after '{where[0]}'); exiting", file=sys.stderr, flush=True)
+            os._exit(0)
+
+        wd = threading.Timer(30.0, _bail)
+        wd.daemon = True
+        wd.start()
+        torch.cuda.synchronize()
+        where[0] = "synchronize"
         dist.barrier()
+        where[0] = "barrier"
+        ctx = None  # noqa: F841  (CUDA graphs with captured collectives, reducers, pipelines)
+        gc.collect()
+        torch.cuda.synchronize()
+        where[0] = "graphs released"
         dist.destroy_process_group()
+        where[0] = "destroy_process_group"
+        wd.cancel()
+        sys.stdout.flush()
+        sys.stderr.flush()
+        os._exit(0)  # skip interpreter-exit destructors of CUDA / NCCL objects: the results are printed, the group is destroyed
 
 
 if __name__ == "__main__":

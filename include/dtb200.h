@@ -306,9 +306,11 @@ int dtb_dt_stage_grad_range(const dtb_dt* h, int stage, long long* begin, long l
  * frames fp32 [N, Cv, H, W], audio fp32 [N, Ca, H, W] (N = B*K timesteps, NCHW as the reference's obs tensors) ->
  * states bf16 [N, state_dim] = [relu(video_fc) | relu(audio_fc)] (fusion 0, 'concat', per-sample dim=1 semantics) or their
  * sum (fusion 1).  Convolutions = patch gather + tcgen05 GEMM with bias+ReLU epilogue, NHWC bf16 activations.
- * Flat parameter order (PyTorch layouts, nn.Sequential indices of conv_factory): per tower (video, audio):
+ * Parameter ENTRY order (PyTorch layouts, nn.Sequential indices of conv_factory): per tower (video, audio):
  *   big  : 0.weight [32,C,8,8], 0.bias, 2.weight [64,32,4,4], 2.bias, 4.weight [64,64,3,3], 4.bias, 7.weight [512, 64*h*w], 7.bias
- *   small: 0.weight [16,C,8,8], 0.bias, 2.weight [32,16,4,4], 2.bias, 5.weight [256, 32*h*w], 5.bias */
+ *   small: 0.weight [16,C,8,8], 0.bias, 2.weight [32,16,4,4], 2.bias, 5.weight [256, 32*h*w], 5.bias
+ * The OFFSETS dtb_encoder_param_layout reports put both towers' conv tensors first and both FC tensors last (see
+ * dtb_encoder_fc_grad_range); always address a tensor through its reported offset. */
 typedef struct {
   int in_channels, in_h, in_w;
   int big; /* 1 = conv_factory('big'), 0 = 'small' */
@@ -338,6 +340,14 @@ int dtb_encoder_forward(const dtb_encoder* e, void* stream, const float* params,
 int dtb_encoder_backward(const dtb_encoder* e, void* stream, const float* params, const void* staged_bf16, int N, const float* frames,
                          const float* audio, const void* states_bf16,
                          const void* d_states_bf16, int d_states_masked, void* workspace, size_t workspace_bytes, float* grads);
+
+/* Data-parallel overlap (REF cleanrl/ppo_atari_multigpu.py:345-359 exchanges all gradients after backward): the two FC layers hold
+ * 7/8 of the towers' gradient bytes and are finished first in backward.  grads[begin, end) of dtb_encoder_fc_grad_range is that
+ * contiguous FC range ([0, begin) = the conv layers); dtb_encoder_wait_fc_grads makes `stream` wait (cudaStreamWaitEvent, capturable)
+ * until the FC gradients of the most recent dtb_encoder_backward call are final, so a communication stream can all-reduce them while
+ * the conv layers' backward is still running. */
+int dtb_encoder_fc_grad_range(const dtb_encoder* e, long long* begin, long long* end);
+int dtb_encoder_wait_fc_grads(const dtb_encoder* e, void* stream);
 
 /* Same, with the video frames as uint8 pixels [N, Cv, H, W]: the reference's pixel decode `img * 2. / 255. - 1` (fp32,
  * REF environments/Minecraft/Minecraft.py:333-335) runs inside the implicit-GEMM conv1 gather, bit-identical to passing the decoded

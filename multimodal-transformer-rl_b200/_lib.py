@@ -108,6 +108,8 @@ def _declare(lib):
     lib.dtb_encoder_workspace_bytes.restype = sz
     lib.dtb_encoder_stage_params.argtypes = [vp, vp, vp, vp]
     lib.dtb_encoder_staged_elems.argtypes = [vp]
+    lib.dtb_encoder_fc_grad_range.argtypes = [vp, C.POINTER(ll), C.POINTER(ll)]
+    lib.dtb_encoder_wait_fc_grads.argtypes = [vp, vp]
     lib.dtb_encoder_staged_elems.restype = ll
     lib.dtb_encoder_forward.argtypes = [vp, vp, vp, vp, i, vp, vp, vp, sz, vp]
     lib.dtb_encoder_backward.argtypes = [vp, vp, vp, vp, i, vp, vp, vp, vp, i, vp, sz, vp]

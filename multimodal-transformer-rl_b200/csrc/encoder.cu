@@ -62,12 +62,14 @@ struct dtb_encoder {
   Tower t[2];
   int state_dim;
   long long total;
+  long long fc_begin;  // flat offset where the two FC layers' tensors start (everything before it belongs to the conv layers)
   long long staged_total;  // elements of the staged bf16 buffer: the flat layout + the data-gradient weights of the implicit convs
   int n_entries;
   std::vector<long long> off, num;
   mutable dtb::SideStream side;   // weight-gradient branch of the backward (and the audio tower in forward)
   mutable dtb::SideStream side2;  // the audio tower's data-gradient chain in backward, concurrent with the video tower's
   mutable dtb::SideStream side3;  // the audio tower's weight-gradient branch (the video tower's uses `side`)
+  mutable cudaEvent_t fc_ev[2] = {nullptr, nullptr};  // recorded once a tower's FC weight + bias gradients are enqueued (backward)
 };
 
 namespace dtb {
@@ -94,19 +96,35 @@ static int build_tower(Tower& t, const dtb_tower_config& c) {
 }
 
 static void layout(dtb_encoder* e) {
+  // Offsets: the conv tensors of both towers first, then both FC tensors, so that the FC gradients (the bulk of the bytes, finished
+  // first in backward) are one contiguous range and the conv gradients (finished last) another: a data-parallel host exchanges the
+  // FC range while the conv layers are still running (dtb_encoder_fc_grad_range / dtb_encoder_wait_fc_grads).  The ENTRY order
+  // reported to the host stays the reference's module order (video_net.{0,2,4,7}, audio_net.{0,2,4,7}).
   long long o = 0;
   e->off.clear(); e->num.clear();
   for (int ti = 0; ti < 2; ++ti) {
     Tower& t = e->t[ti];
     for (int i = 0; i < t.nconv; ++i) {
       const ConvSpec& cs = t.conv[i];
-      const long long nw = (long long)cs.cout * cs.cin * cs.k * cs.k;
-      t.w_off[i] = o; e->off.push_back(o); e->num.push_back(nw); o += pad8l(nw);
-      t.b_off[i] = o; e->off.push_back(o); e->num.push_back(cs.cout); o += pad8l(cs.cout);
+      t.w_off[i] = o; o += pad8l((long long)cs.cout * cs.cin * cs.k * cs.k);
+      t.b_off[i] = o; o += pad8l(cs.cout);
     }
-    const long long nw = (long long)t.feat * t.flat;
-    t.w_off[3] = o; e->off.push_back(o); e->num.push_back(nw); o += pad8l(nw);
-    t.b_off[3] = o; e->off.push_back(o); e->num.push_back(t.feat); o += pad8l(t.feat);
+  }
+  e->fc_begin = o;
+  for (int ti = 0; ti < 2; ++ti) {
+    Tower& t = e->t[ti];
+    t.w_off[3] = o; o += pad8l((long long)t.feat * t.flat);
+    t.b_off[3] = o; o += pad8l(t.feat);
+  }
+  for (int ti = 0; ti < 2; ++ti) {
+    const Tower& t = e->t[ti];
+    for (int i = 0; i < t.nconv; ++i) {
+      const ConvSpec& cs = t.conv[i];
+      e->off.push_back(t.w_off[i]); e->num.push_back((long long)cs.cout * cs.cin * cs.k * cs.k);
+      e->off.push_back(t.b_off[i]); e->num.push_back(cs.cout);
+    }
+    e->off.push_back(t.w_off[3]); e->num.push_back((long long)t.feat * t.flat);
+    e->off.push_back(t.b_off[3]); e->num.push_back(t.feat);
   }
   e->total = o;
   e->n_entries = (int)e->off.size();
@@ -235,6 +253,7 @@ static int tower_backward(const dtb_encoder* e, int ti, cudaStream_t st, const b
   DTB_TRY(gemm_wgrad(ss, dF, ldf, tw.Y[last], t.flat, t.feat, t.flat, N, tw.gstage, t.flat, partial, w.partial_floats));
   DTB_TRY(permute_unstage(ss, tw.gstage, t.feat, cl.cout, hw, G + t.w_off[3]));  // staged (h,w,c) -> PyTorch flatten (c,h,w)
   DTB_TRY(colsum_bf16(ss, dF, N, t.feat, ldf, G + t.b_off[3], 0, cs_scratch));
+  DTB_CUDA(cudaEventRecord(e->fc_ev[ti], ss));  // this tower's FC gradients are final from here on (dtb_encoder_wait_fc_grads)
   {
     GemmEpilogue ep = epz();
     ep.dact = 1;
@@ -300,7 +319,11 @@ int dtb_encoder_create(const dtb_encoder_config* cfg, dtb_encoder** out) {
   return DTB_OK;
 }
 int dtb_encoder_destroy(dtb_encoder* e) {
-  if (e) { e->side.destroy(); e->side2.destroy(); e->side3.destroy(); }
+  if (e) {
+    e->side.destroy(); e->side2.destroy(); e->side3.destroy();
+    for (int ti = 0; ti < 2; ++ti)
+      if (e->fc_ev[ti]) cudaEventDestroy(e->fc_ev[ti]);
+  }
   delete e;
   return DTB_OK;
 }
@@ -313,6 +336,18 @@ long long dtb_encoder_param_layout(const dtb_encoder* e, long long* offsets, lon
     if (numels) numels[i] = e->num[i];
   }
   return e->total;
+}
+int dtb_encoder_fc_grad_range(const dtb_encoder* e, long long* begin, long long* end) {
+  DTB_REQUIRE(e && begin && end, DTB_ERR_BAD_ARG, "dtb_encoder_fc_grad_range: null argument");
+  *begin = e->fc_begin;
+  *end = e->total;
+  return DTB_OK;
+}
+int dtb_encoder_wait_fc_grads(const dtb_encoder* e, void* stream) {
+  DTB_REQUIRE(e, DTB_ERR_BAD_ARG, "dtb_encoder_wait_fc_grads: null handle");
+  DTB_REQUIRE(e->fc_ev[0] && e->fc_ev[1], DTB_ERR_BAD_ARG, "dtb_encoder_wait_fc_grads: no dtb_encoder_backward call has been made on this handle");
+  for (int ti = 0; ti < 2; ++ti) DTB_CUDA(cudaStreamWaitEvent((cudaStream_t)stream, e->fc_ev[ti], 0));
+  return DTB_OK;
 }
 long long dtb_encoder_staged_elems(const dtb_encoder* e) { return e ? e->staged_total : DTB_ERR_BAD_ARG; }
 size_t dtb_encoder_workspace_bytes(const dtb_encoder* e, int N) {
@@ -381,8 +416,11 @@ static int encoder_backward_impl(const dtb_encoder* e, void* stream, const float
                                  void* workspace, size_t workspace_bytes, float* grads) {
   DTB_REQUIRE(e && params && staged && d_states_bf16 && grads, DTB_ERR_BAD_ARG, "dtb_encoder_backward: null argument");
   cudaStream_t st = (cudaStream_t)stream;
+  for (int ti = 0; ti < 2; ++ti)
+    if (!e->fc_ev[ti]) DTB_CUDA(cudaEventCreateWithFlags(&e->fc_ev[ti], cudaEventDisableTiming));
   if (N == 0) {
     DTB_CUDA(cudaMemsetAsync(grads, 0, (size_t)e->total * sizeof(float), st));
+    for (int ti = 0; ti < 2; ++ti) DTB_CUDA(cudaEventRecord(e->fc_ev[ti], st));
     return DTB_OK;
   }
   EncWs w;

@@ -15,7 +15,7 @@ import torch.distributed as dist
 class GradAllReducer:
     """Coalesces finished gradient ranges of one flat buffer into buckets and all-reduces them on a communication stream."""
 
-    def __init__(self, bucket_bytes: int = 8 << 20, group=None):
+    def __init__(self, bucket_bytes: int = 2 << 20, group=None):
         self.group = group
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.bucket_elems = max(1, bucket_bytes // 4)
@@ -30,7 +30,7 @@ class GradAllReducer:
             self._comm = torch.cuda.Stream(device=device)
         return self._comm
 
-    def _flush(self, flat, lo, hi):
+    def _flush(self, flat, lo, hi, wait=None):
         if self.world == 1 or hi <= lo:
             return
         chunk = flat[lo:hi]
@@ -39,9 +39,46 @@ class GradAllReducer:
         if comm is None:
             dist.all_reduce(chunk, op=dist.ReduceOp.SUM, group=self.group)
             return
-        comm.wait_stream(torch.cuda.current_stream(flat.device))  # the stage's kernels are enqueued before this point
+        if wait is None:
+            comm.wait_stream(torch.cuda.current_stream(flat.device))  # the stage's kernels are enqueued before this point
+        else:
+            wait(comm)  # a narrower dependency than "everything enqueued so far" (e.g. the encoder's FC-gradient event)
         with torch.cuda.stream(comm):
             dist.all_reduce(chunk, op=dist.ReduceOp.SUM, group=self.group)
+
+    def flush(self, flat: torch.Tensor = None):
+        """Send what is pending (of ``flat``, or of every buffer) now instead of waiting for a full bucket."""
+        for key, cur in list(self._pending.items()):
+            if flat is None or cur[0] is flat:
+                self._flush(*cur)
+                del self._pending[key]
+
+    def ready_now(self, flat: torch.Tensor, begin: int, end: int, wait=None):
+        """All-reduce flat[begin:end] immediately; ``wait(comm_stream)`` replaces the default dependency on the current stream."""
+        self._flush(flat, begin, end, wait)
+
+    def callback_for(self, model):
+        """``on_stage_done`` callback for ``model.loss_and_backward`` (DecisionTransformer or MultimodalDecisionTransformer).
+
+        Trunk stages are coalesced into buckets and the last one flushes the rest, so the trunk's gradients travel while the towers'
+        backward runs; the encoder's FC range goes out as soon as the library's FC event fires (while the conv layers still run); only
+        the conv range (a few hundred KB) is exchanged after the last kernel."""
+        dt = getattr(model, "dt", model)
+        enc = getattr(model, "encoder", None)
+        last = dt.n_stages - 1
+
+        def cb(stage, begin, end):
+            if stage == "encoder_fc":
+                wait = enc.wait_fc_grads if enc.flat_grads.is_cuda else None
+                self.ready_now(enc.flat_grads, begin, end, wait)
+            elif stage == "encoder":
+                self.ready_now(enc.flat_grads, begin, end)
+            else:
+                self.ready(dt.flat_grads, begin, end)
+                if stage == last:
+                    self.flush(dt.flat_grads)
+
+        return cb
 
     def ready(self, flat: torch.Tensor, begin: int, end: int):
         """Mark flat[begin:end] as final for this step (its producing kernels are already enqueued on the current stream)."""

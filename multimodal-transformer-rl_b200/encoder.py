@@ -257,6 +257,17 @@ class MultimodalStateEncoder(nn.Module):
                        _lib.ptr(d_states), int(masked), _lib.ptr(ws), ws.numel(), _lib.ptr(grads)))
         return grads
 
+    def fc_grad_range(self):
+        """(begin, end) of the gradients that are final first in backward: the two FC layers (+ the modality-attention parameters, whose
+        backward runs before the towers'); [0, begin) are the conv layers' gradients, final only when backward_raw's kernels are done."""
+        b, e = C.c_longlong(), C.c_longlong()
+        _lib.check(_lib.load().dtb_encoder_fc_grad_range(self._h, C.byref(b), C.byref(e)))
+        return int(b.value), self._total
+
+    def wait_fc_grads(self, stream):
+        """Make ``stream`` (a torch.cuda.Stream) wait until the FC-range gradients of the last backward_raw call are final."""
+        _lib.check(_lib.load().dtb_encoder_wait_fc_grads(self._h, C.c_void_p(stream.cuda_stream)))
+
     def forward(self, frames, audio, hidden=None):
         params = [self.get_parameter(n) for n in self._names]
         return _EncoderFunction.apply(self, frames, audio, hidden, *params)
@@ -351,5 +362,9 @@ class MultimodalDecisionTransformer(nn.Module):
                                          on_stage_done=on_stage_done)
         self.encoder.backward_raw(d_states, masked=relu_out)
         if on_stage_done is not None:
-            on_stage_done("encoder", 0, self.encoder._total)
+            # two ranges of the encoder's flat gradients: the FC layers (final early: GradAllReducer.callback_for waits on the library's
+            # event instead of the whole backward) and the conv layers (final when everything enqueued so far is done)
+            fc_begin, fc_end = self.encoder.fc_grad_range()
+            on_stage_done("encoder_fc", fc_begin, fc_end)
+            on_stage_done("encoder", 0, fc_begin)
         return loss

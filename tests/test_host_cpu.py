@@ -129,6 +129,24 @@ assert replicas_consistent([params])
 if rank == 1:
     params[3] += 1e-3
 assert not replicas_consistent([params])
+# callback_for(model): trunk stages bucketed, the last trunk stage flushes the rest (so the trunk travels during the towers' backward),
+# the encoder's FC range and conv range go out as two immediate collectives
+g1, g2 = torch.full((1000,), float(rank + 1)) / world, torch.full((600,), float(2 * rank + 1)) / world
+class _DT: n_stages = 3; flat_grads = g1
+class _Enc:
+    flat_grads = g2
+    def wait_fc_grads(self, stream): raise AssertionError("CPU tensors: no stream to wait on")
+class _Model: dt = _DT(); encoder = _Enc()
+red2 = GradAllReducer(bucket_bytes=4 * 5000)
+cb = red2.callback_for(_Model())
+cb(0, 700, 1000); cb(1, 300, 700)
+assert red2.n_collectives == 0 and red2._pending
+cb(2, 0, 300)
+assert red2.n_collectives == 1 and not red2._pending
+cb("encoder_fc", 250, 600); cb("encoder", 0, 250)
+assert red2.n_collectives == 3
+red2.finish()
+assert torch.allclose(g1, torch.full((1000,), expect)) and torch.allclose(g2, torch.full((600,), sum(2 * r + 1 for r in range(world)) / world))
 dist.destroy_process_group()
 print("ok", rank)
 """
