@@ -16,8 +16,8 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 RULES = [(r"gemm_tcgen05", ["gemm_tcgen05_kernel (+pair)", "gemm_tcgen05_kernel, HBM-bound shapes"]), (r"conv1_fwd", ["conv1_fwd_kernel"]),
          (r"conv1_wgrad", ["conv1_wgrad_kernel"]), (r"attn_fwd", ["attn_fwd_tc_kernel"]), (r"attn_bwd", ["attn_bwd_dq+dkv_tc_kernel"]),
          (r"ln_fwd", ["ln_fwd_kernel"]), (r"ln_bwd_kernel", ["ln_bwd_kernel"]), (r"embed_fwd", ["embed_fwd_kernel"]), (r"colsum", ["colsum_kernel"]),
-         (r"im2col", ["im2col_nhwc_kernel"]), (r"col2im", ["col2im_nhwc_relu_kernel"]), (r"convn_kernel<\(bool\)0>|convn_kernel<false>", ["convn_kernel<fwd>"]),
-         (r"convn_kernel<\(bool\)1>|convn_kernel<true>", ["convn_kernel<dgrad>"]), (r"convn_wgrad_kernel", ["convn_wgrad_kernel"]),
+         (r"im2col", ["im2col_nhwc_kernel"]), (r"col2im", ["col2im_nhwc_relu_kernel"]), (r"convn_kernel<\(bool\)0>|convn_kernel<false>|convn_kernel<0>", ["convn_kernel<fwd>"]),
+         (r"convn_kernel<\(bool\)1>|convn_kernel<true>|convn_kernel<1>", ["convn_kernel<dgrad>"]), (r"convn_wgrad_kernel", ["convn_wgrad_kernel"]),
          (r"opt_adamw", ["opt_adamw"]), (r"heads_", ["heads"]), (r"get_batch", ["get_batch_kernel"])]
 
 
