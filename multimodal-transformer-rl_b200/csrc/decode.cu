@@ -16,6 +16,7 @@
 #include "dt_handle.h"
 
 #include <new>
+#include <stdlib.h>
 #include <string.h>
 
 namespace dtb {
@@ -49,7 +50,18 @@ struct DecodeParams {
   int Tmax;
   float* scratch;           // exchange buffers, see dc_scratch_floats
   float* action_out;        // [ad]: prediction of the last processed token (written when it is a state token)
+  int tc_slots, tc_red_floats;  // tensor-core path: ring slots that fit, length of `red`
+  unsigned long long* stamps;   // developer probe (DTB_DECODE_STAMP=1): %globaltimer at the phase boundaries, written by thread 0
 };
+
+__device__ __forceinline__ void dc_stamp(const DecodeParams& p, int& k) {
+  if (p.stamps && threadIdx.x == 0) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    p.stamps[k] = t;
+  }
+  ++k;
+}
 
 // scratch layout (floats): sp [H] | q [NT][H] | o [NT][H] | x1 [NT][H] | x2 [NT][H] | fc [NT][I]
 __host__ __device__ inline size_t dc_scratch_floats(int H, int I) { return (size_t)H * (1 + 4 * DC_NT) + (size_t)DC_NT * I; }
@@ -68,6 +80,7 @@ __device__ __forceinline__ float dc_act(float v, int act) { return act == 1 ? fm
 
 // LayerNorm of the n token rows x[t][0..H) (shared memory) -> y[t][0..H) rounded to bf16 (what the tensor-core path feeds its GEMMs);
 // warp t handles token t (two-pass statistics, as ln_fwd_kernel).
+template <bool SMEM_PARAMS = false>
 __device__ __forceinline__ void dc_layernorm(const float* x, float* y, int n, int H, const float* gamma, const float* beta, float eps) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (warp < n) {
@@ -78,7 +91,8 @@ __device__ __forceinline__ void dc_layernorm(const float* x, float* y, int n, in
     float q = 0.f;
     for (int c = lane; c < H; c += 32) { const float dlt = xr[c] - mean; q += dlt * dlt; }
     const float rstd = rsqrtf(warp_sum(q) / H + eps);
-    for (int c = lane; c < H; c += 32) y[warp * H + c] = dc_round_bf16((xr[c] - mean) * rstd * __ldg(gamma + c) + __ldg(beta + c));
+    for (int c = lane; c < H; c += 32)
+      y[warp * H + c] = dc_round_bf16((xr[c] - mean) * rstd * (SMEM_PARAMS ? gamma[c] : __ldg(gamma + c)) + (SMEM_PARAMS ? beta[c] : __ldg(beta + c)));
   }
   __syncthreads();
 }
@@ -229,6 +243,187 @@ __device__ __forceinline__ void dc_gemv(DcStream& st, const DecodeParams& p, int
   __syncthreads();
 }
 
+// ---- tensor-core GEMV (hidden % 128 == 0) -----------------------------------------------------------------------------------------------
+// The FFMA GEMV above is bound by instruction issue and by its per-tile block barriers on the one SM a small model uses (c1: 147 us for
+// 1.2 MB of weights).  Here the WEIGHTS are the A operand of tcgen05.mma (M = 128 output features per instruction, MN-major: the Conv1D
+// layout [k][feature] is read as it is) and the <= 3 new tokens are the B operand (N = 16 token slots, K-major, written by the threads into
+// the 128B-swizzled image): D[feature][token] accumulates in TMEM, one thread issues everything, and no thread ever touches a weight.
+// The weights are staged once per parameter update as a sequence of 16 KB blocks — [128 features][64 k], already in the swizzled
+// shared-memory image — so one plain bulk copy (cp.async.bulk) per block lands MMA-ready data; thread 0 keeps `depth` blocks in flight,
+// straight through the phase boundaries of the forward.  Columns of D are independent, so the bits of a token do not depend on which
+// slot it occupies or on how a history is chunked into launches.
+constexpr int DT_BLOCK_BYTES = 16384, DT_BLOCK_ELEMS = 8192, DT_MAX_SLOTS = 8, DT_TMEM_COLS = 64, DT_NTOK = 16;
+
+struct DcTc {
+  int K[4], ncols[4], ntile[4], nkb[4];  // per matrix: k extent, this CTA's columns, its 128-feature tiles, 64-wide k-blocks
+  size_t moff[4], layer_elems;
+  int per_layer, total;   // blocks per layer / in the whole forward (per CTA)
+  int slots, depth, sshift;  // ring slots (a power of two), blocks in flight, log2(slots)
+  // thread 0 only: stream position
+  int issued, consumed, is_l, is_m, is_b;
+  uint32_t acc_phase;     // every thread: parity of the accumulator barrier
+  uint32_t tmem;
+  uint8_t *ring, *bop;
+  uint64_t *full, *empty, *acc;
+};
+
+__device__ __forceinline__ void dt_init(DcTc& tc, const DecodeParams& p) {
+  const int H = p.H, I = p.I;
+  const int K[4] = {H, H, H, I}, N[4] = {3 * H, H, I, H};
+  tc.per_layer = 0;
+  tc.layer_elems = 0;
+  for (int m = 0; m < 4; ++m) {
+    tc.moff[m] = tc.layer_elems;
+    tc.layer_elems += (size_t)K[m] * N[m];
+    tc.K[m] = K[m];
+    tc.ncols[m] = N[m] / p.C;
+    tc.ntile[m] = tc.ncols[m] / 128;
+    tc.nkb[m] = K[m] / 64;
+    tc.per_layer += tc.ntile[m] * tc.nkb[m];
+  }
+  tc.total = tc.per_layer * p.L;
+  tc.issued = tc.consumed = tc.is_l = tc.is_m = tc.is_b = 0;
+  tc.acc_phase = 0;
+}
+// thread 0: issue the next weight block of this CTA's stream (if any) into its ring slot
+__device__ __forceinline__ void dt_issue(DcTc& tc, const DecodeParams& p, int rank) {
+  if (tc.issued >= tc.total) return;
+  const int g = tc.issued++;
+  const int slot = g % tc.slots;
+  if (g >= tc.slots) mbar_wait(&tc.empty[slot], (uint32_t)(g / tc.slots - 1) & 1u);  // the MMAs that read this slot have retired
+  const int m = tc.is_m;
+  const bf16* src = p.Wd + (size_t)tc.is_l * tc.layer_elems + tc.moff[m] + (size_t)rank * tc.K[m] * tc.ncols[m] + (size_t)tc.is_b * DT_BLOCK_ELEMS;
+  mbar_arrive_expect_tx(&tc.full[slot], DT_BLOCK_BYTES);
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   smem_u32(tc.ring + (size_t)slot * DT_BLOCK_BYTES)),
+               "l"(src), "r"((uint32_t)DT_BLOCK_BYTES), "r"(smem_u32(&tc.full[slot]))
+               : "memory");
+  if (++tc.is_b == tc.ntile[m] * tc.nkb[m]) {
+    tc.is_b = 0;
+    if (++tc.is_m == 4) { tc.is_m = 0; ++tc.is_l; }
+  }
+}
+__device__ __forceinline__ void dt_tmem_ld4(uint32_t taddr, uint32_t (&v)[4]) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]) : "r"(taddr) : "memory");
+}
+
+// Conv1D-layout bf16 weights -> the tensor-core decode layout: per layer, matrix and CTA rank the blocks (feature tile, k-block) in stream
+// order; inside a block two 64-feature halves of [64 k][64 features] rows (128 B each), 16-byte units XOR-swizzled by (k & 7) — exactly
+// what a TMA box {64 features, 64 k} with SWIZZLE_128B would have written.  One thread per 16-byte unit.
+__global__ void __launch_bounds__(256) dt_decode_stage_tc_kernel(const DecodeParams p, size_t layer_elems) {
+  pdl_trigger();
+  pdl_wait();
+  const int H = p.H, I = p.I;
+  const int K[4] = {H, H, H, I}, N[4] = {3 * H, H, I, H}, lid[4] = {L_WQKV, L_WO, L_W1, L_W2};
+  const size_t chunks_per_layer = layer_elems / 8, total = chunks_per_layer * p.L;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int l = (int)(i / chunks_per_layer);
+    size_t e = (i - (size_t)l * chunks_per_layer) * 8;  // element offset inside the layer (decode layout)
+    int m = 0;
+    while (e >= (size_t)K[m] * N[m]) { e -= (size_t)K[m] * N[m]; ++m; }
+    const int ncols = N[m] / p.C, nkb = K[m] / 64;
+    const size_t slice = (size_t)K[m] * ncols;
+    const int r = (int)(e / slice);
+    const size_t q = e - (size_t)r * slice;
+    const int blk = (int)(q / DT_BLOCK_ELEMS), w = (int)(q - (size_t)blk * DT_BLOCK_ELEMS);
+    const int ft = blk / nkb, kb = blk - ft * nkb;
+    const int j = w >> 12, rr = (w & 4095) >> 6, up = (w & 63) >> 3;
+    const int row = kb * 64 + rr, col = r * ncols + ft * 128 + j * 64 + ((up ^ (rr & 7)) << 3);
+    const bf16* src = p.Pb + p.l_off[lid[m]] + (long long)l * p.layer_stride + (size_t)row * N[m] + col;
+    *reinterpret_cast<uint4*>(p.Wd_out + (size_t)l * layer_elems + (i - (size_t)l * chunks_per_layer) * 8) = __ldg(reinterpret_cast<const uint4*>(src));
+  }
+}
+
+// out[t][c] = sum_k in[t][k] W[k][c] for this CTA's columns of matrix m, on the tensor core; result left in red[t * ncols + c].
+__device__ __forceinline__ void dt_gemv(DcTc& tc, const DecodeParams& p, int rank, int m, const float* in, int n, float* red) {
+  const int K = tc.K[m], ncols = tc.ncols[m], ku_per_row = K >> 3;
+  // B operand: token rows (bf16, the inputs are already bf16-rounded values) in the K-major 128B-swizzled image, one 2 KB region per k-block
+  for (int idx = threadIdx.x; idx < DC_NT * ku_per_row; idx += DC_THREADS) {
+    const int t = idx / ku_per_row, ku = idx - t * ku_per_row;
+    uint4 v = make_uint4(0u, 0u, 0u, 0u);
+    if (t < n) {
+      const float4 a = *reinterpret_cast<const float4*>(in + (size_t)t * K + ku * 8), b = *reinterpret_cast<const float4*>(in + (size_t)t * K + ku * 8 + 4);
+      v = make_uint4(pack_bf16x2(a.x, a.y), pack_bf16x2(a.z, a.w), pack_bf16x2(b.x, b.y), pack_bf16x2(b.z, b.w));
+    }
+    const uint32_t addr = smem_u32(tc.bop) + (uint32_t)(ku >> 3) * 2048u + (uint32_t)t * 128u + (uint32_t)(((ku & 7) ^ (t & 7)) << 4);
+    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+  }
+  fence_proxy_async();  // generic-proxy stores -> visible to the tensor core (async proxy)
+  __syncthreads();
+  // Jobs: the matrix is cut into <= 4 independent accumulations — its 128-feature tiles, and when there are fewer than 4 tiles also
+  // halves / quarters of k (partial sums in separate TMEM columns, added below in a fixed order: deterministic).  Lane 0 of warps 0-3
+  // (one per SM sub-partition) each walks the blocks of one job: wait for the block, 4 MMAs (K = 16 each), release the slot on
+  // retirement, and issue the load `depth` blocks further down the stream (every block is consumed by exactly one thread, so every
+  // load is issued exactly once).  The scalar chain per block (~0.5 us of waits, descriptor arithmetic and async-proxy instructions)
+  // is what paces this kernel, hence four chains side by side.  Job order = stream order (tile-major, then k).
+  const int ntile = tc.ntile[m], nkb = tc.nkb[m];
+  int ksplit = 1;
+  while (ntile * ksplit * 2 <= 4 && nkb % (ksplit * 2) == 0) ksplit *= 2;
+  const int njobs = ntile * ksplit, bpj = nkb / ksplit;
+  const uint32_t g_base = (uint32_t)tc.consumed;
+  if ((threadIdx.x & 31) == 0 && threadIdx.x < 128) {
+    const int j = threadIdx.x >> 5;
+    if (j < njobs) {
+      tc_fence_after();
+      const uint32_t idesc = make_idesc_bf16(128, DT_NTOK, 1, 0);
+      const uint32_t smask = (uint32_t)tc.slots - 1u, sshift = (uint32_t)tc.sshift, depth = (uint32_t)tc.depth, total = (uint32_t)tc.total;
+      const uint64_t adesc0 = make_smem_desc_sw128(smem_u32(tc.ring), 8192, 1024);  // MN-major: 16 k rows of 128 B per step, halves 8 KB apart
+      const uint64_t bdesc0 = make_smem_desc_sw128(smem_u32(tc.bop), 16, 1024);     // K-major: 32 B per step inside the 128 B row
+      const uint32_t ring0 = smem_u32(tc.ring), full0 = smem_u32(tc.full);
+      const uint32_t d_tmem = tc.tmem + (uint32_t)j * DT_NTOK;
+      uint32_t g = g_base + (uint32_t)(j * bpj);
+      int kb = (j % ksplit) * bpj;
+      for (int b = 0; b < bpj; ++b, ++g, ++kb) {
+        const uint32_t slot = g & smask;
+        mbar_wait(&tc.full[slot], (g >> sshift) & 1u);
+        tc_fence_after();
+        const uint64_t ad = adesc0 + (uint64_t)(slot * (DT_BLOCK_BYTES >> 4)), bd = bdesc0 + (uint64_t)(kb * (2048 >> 4));
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk) umma_bf16(d_tmem, ad + kk * (2048 >> 4), bd + kk * (32 >> 4), idesc, (b > 0 || kk > 0) ? 1u : 0u);
+        umma_commit(&tc.empty[slot]);  // frees the ring slot when these MMAs retire
+        const uint32_t g2 = g + depth;
+        if (g2 < total) {
+          const uint32_t s2 = g2 & smask;
+          if (g2 > smask) mbar_wait(&tc.empty[s2], ((g2 >> sshift) - 1u) & 1u);  // its previous block (g2 - slots) has retired
+          const bf16* src = p.Wd + (size_t)g2 * DT_BLOCK_ELEMS;                   // C = 1: the whole stream is one contiguous array
+          mbar_arrive_expect_tx(&tc.full[s2], DT_BLOCK_BYTES);
+          asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(ring0 + s2 * (uint32_t)DT_BLOCK_BYTES),
+                       "l"(src), "r"((uint32_t)DT_BLOCK_BYTES), "r"(full0 + s2 * 8u)
+                       : "memory");
+        }
+      }
+      umma_commit(tc.acc);  // this job's accumulator is final
+    } else {
+      mbar_arrive(tc.acc);
+    }
+  }
+  tc.consumed += ntile * nkb;
+  mbar_wait(tc.acc, tc.acc_phase);
+  tc.acc_phase ^= 1u;
+  tc_fence_after();
+  {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, q = warp & 3;
+    for (int ft = warp >> 2; ft < ntile; ft += DC_THREADS / 128) {
+      float o[DC_NT];
+#pragma unroll
+      for (int t = 0; t < DC_NT; ++t) o[t] = 0.f;
+      for (int ks = 0; ks < ksplit; ++ks) {  // partial sums of the k ranges, in k order
+        uint32_t v[4];
+        dt_tmem_ld4(tc.tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(ft * ksplit + ks) * DT_NTOK, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int t = 0; t < DC_NT; ++t) o[t] += __uint_as_float(v[t]);
+      }
+      const int f = ft * 128 + q * 32 + lane;
+#pragma unroll
+      for (int t = 0; t < DC_NT; ++t) red[t * ncols + f] = o[t];
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+}
+
+template <bool TC>
 __global__ void __launch_bounds__(DC_THREADS, 1) dt_decode_kernel(const DecodeParams p) {
   extern __shared__ __align__(16) float dc_smem[];
   const int H = p.H, I = p.I, n = p.n, d = p.d;
@@ -238,12 +433,28 @@ __global__ void __launch_bounds__(DC_THREADS, 1) dt_decode_kernel(const DecodePa
   float* red = hb + DC_NT * KI;       // DC_RED_FLOATS: GEMV partial sums (two levels), attention merge
   uint8_t* slots = reinterpret_cast<uint8_t*>(red + DC_RED_FLOATS);  // weight tile ring (16-byte aligned: every region above is a multiple of 16 B)
   uint64_t* full = reinterpret_cast<uint64_t*>(slots + (size_t)DC_SLOTS * DC_SLOT_BYTES);  // [DC_SLOTS] tile-landed barriers
+  DcTc tc;
+  float *lx = nullptr, *pl = nullptr;
+  if (TC) {  // tensor-core path (one CTA): red is tc_red_floats long, then the exchange buffers and this layer's small parameters (both in
+             // shared memory: no L2 round trip between the phases), then (1 KB aligned) the B-operand image, the block ring, the barriers
+    lx = red + p.tc_red_floats;          // sp [H] | q, o, x1, x2 [NT][H] | fc [NT][I]
+    pl = lx + 13 * H + DC_NT * I;        // ln_1.w, ln_1.b [H] | b_qkv [3H] | b_o [H] | ln_2.w, ln_2.b [H] | b_fc [I] | b_proj [H]
+    uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(pl + 9 * H + I) + 1023) & ~uintptr_t(1023));
+    tc.bop = base;
+    tc.ring = base + (size_t)(KI / 64) * 2048;
+    tc.slots = p.tc_slots;
+    tc.sshift = 31 - __clz(p.tc_slots);
+    tc.depth = p.tc_slots > 4 ? p.tc_slots - 3 : p.tc_slots - 1;  // a refilled slot was consumed >= 3 blocks ago: its MMAs have retired, thread 0 never waits for them
+    tc.full = reinterpret_cast<uint64_t*>(tc.ring + (size_t)tc.slots * DT_BLOCK_BYTES);
+    tc.empty = tc.full + DT_MAX_SLOTS;
+    tc.acc = tc.empty + DT_MAX_SLOTS;
+  }
   const int DC_CTAS = p.C;
   const int rank = (int)dc_cluster_rank();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const float* P = p.P;
   const bf16* Pb = p.Pb;
-  float* s_sp = p.scratch;                  // [H]      wide-state projection
+  float* s_sp = TC ? lx : p.scratch;        // [H]      wide-state projection
   float* s_q = s_sp + H;                    // [NT][H]
   float* s_o = s_q + DC_NT * H;             // [NT][H]
   float* s_x1 = s_o + DC_NT * H;            // [NT][H]
@@ -251,16 +462,41 @@ __global__ void __launch_bounds__(DC_THREADS, 1) dt_decode_kernel(const DecodePa
   float* s_fc = s_x2 + DC_NT * H;           // [NT][I]
   pdl_trigger();
   pdl_wait();
+  int sk = 0;
+  dc_stamp(p, sk);  // 0: start
   // start the weight stream: the first DEPTH tiles fly while the tokens are embedded
-  if (threadIdx.x == 0) {
-    for (int i = 0; i < DC_SLOTS; ++i) mbar_init(&full[i], 1);
-    fence_mbar_init();
-  }
-  __syncthreads();
   DcStream st;
-  dc_stream_init(st, p);
   int consumed = 0;
-  for (int i = 0; i < DC_DEPTH; ++i) dc_stream_issue(st, p, rank, slots, full);
+  if (TC) {
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tc.acc + 1);
+    if (threadIdx.x == 0) {
+      for (int i = 0; i < DT_MAX_SLOTS; ++i) { mbar_init(&tc.full[i], 1); mbar_init(&tc.empty[i], 1); }
+      mbar_init(tc.acc, 4);  // one arrival per issuing thread (lane 0 of warps 0-3)
+      fence_mbar_init();
+    }
+    if (warp == 2) {
+      tmem_alloc(tmem_slot, DT_TMEM_COLS);
+      tmem_relinquish();
+    }
+    // token slots n .. 15 of the B operand are never written again: zero them once (their D columns are never read, but keep them finite)
+    for (int i = threadIdx.x; i < (KI / 64) * 2048 / 16; i += DC_THREADS)
+      *reinterpret_cast<uint4*>(tc.bop + (size_t)i * 16) = make_uint4(0u, 0u, 0u, 0u);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    tc.tmem = *tmem_slot;
+    dt_init(tc, p);
+    if (threadIdx.x == 0)
+      for (int i = 0; i < tc.depth; ++i) dt_issue(tc, p, rank);
+  } else {
+    if (threadIdx.x == 0) {
+      for (int i = 0; i < DC_SLOTS; ++i) mbar_init(&full[i], 1);
+      fence_mbar_init();
+    }
+    __syncthreads();
+    dc_stream_init(st, p);
+    for (int i = 0; i < DC_DEPTH; ++i) dc_stream_issue(st, p, rank, slots, full);
+  }
 
   // ---- wide state (tower features, bf16): projection Ws[H][sd] . s, column slice per CTA, one warp per output --------------------
   int wide_tok = -1;
@@ -286,34 +522,35 @@ __global__ void __launch_bounds__(DC_THREADS, 1) dt_decode_kernel(const DecodePa
       a = warp_sum(a);
       if (lane == 0) s_sp[c] = a;
     }
-    dc_cluster_sync();
+    if (TC) __syncthreads(); else dc_cluster_sync();
   }
 
   // ---- embedding + embed_ln of the new tokens (HF:611-628), replicated in every CTA ------------------------------------------------
-  for (int t = 0; t < n; ++t) {
+  for (int idx = threadIdx.x; idx < n * H; idx += DC_THREADS) {  // all tokens at once: their dependent loads (timestep -> table row) overlap
+    const int t = idx / H, c = idx - t * H;
     const int tok = p.p0 + t, k = tok / 3, type = tok - 3 * k;
     long long ts = p.timesteps[k];
     ts = ts < 0 ? 0 : (ts >= p.E ? p.E - 1 : ts);
     const float* te = P + p.e_off[E_TABLE] + (size_t)ts * H;
-    for (int c = threadIdx.x; c < H; c += DC_THREADS) {
-      float v = __ldg(te + c);
-      if (type == 0) {
-        v += p.rtg[k] * __ldg(P + p.e_off[E_WR] + c) + __ldg(P + p.e_off[E_BR] + c);
-      } else if (type == 1) {
-        v += __ldg(P + p.e_off[E_BS] + c);
-        if (p.sd_small) {
-          const float* w = P + p.e_off[E_WS] + (size_t)c * p.sd;
-          for (int j = 0; j < p.sd; ++j) v = fmaf(__ldg(w + j), p.states[(size_t)k * p.sd + j], v);
-        } else {
-          v += __ldcg(s_sp + c);
-        }
+    float v = __ldg(te + c);
+    if (type == 0) {
+      v += p.rtg[k] * __ldg(P + p.e_off[E_WR] + c) + __ldg(P + p.e_off[E_BR] + c);
+    } else if (type == 1) {
+      v += __ldg(P + p.e_off[E_BS] + c);
+      if (p.sd_small) {
+        const float* w = P + p.e_off[E_WS] + (size_t)c * p.sd;
+        const float* srow = p.states + (size_t)k * p.sd;
+        for (int j = 0; j < p.sd; ++j) v = fmaf(__ldg(w + j), __ldg(srow + j), v);
       } else {
-        v += __ldg(P + p.e_off[E_BA] + c);
-        const float* w = P + p.e_off[E_WA] + (size_t)c * p.ad;
-        for (int j = 0; j < p.ad; ++j) v = fmaf(__ldg(w + j), p.actions[(size_t)k * p.ad + j], v);
+        v += (TC ? s_sp[c] : __ldcg(s_sp + c));
       }
-      hb[t * H + c] = v;
+    } else {
+      v += __ldg(P + p.e_off[E_BA] + c);
+      const float* w = P + p.e_off[E_WA] + (size_t)c * p.ad;
+      const float* arow = p.actions + (size_t)k * p.ad;
+      for (int j = 0; j < p.ad; ++j) v = fmaf(__ldg(w + j), __ldg(arow + j), v);
     }
+    hb[t * H + c] = v;
   }
   __syncthreads();
   if (warp < n) {  // embed_ln -> x (fp32, not rounded: the residual stream)
@@ -330,24 +567,40 @@ __global__ void __launch_bounds__(DC_THREADS, 1) dt_decode_kernel(const DecodePa
   __syncthreads();
 
   const float scale_log2 = 1.4426950408889634f * rsqrtf((float)d);
+  dc_stamp(p, sk);  // 1: embedded
   for (int l = 0; l < p.L; ++l) {
     const long long lo = (long long)l * p.layer_stride;
     bf16* kc = p.kc + (size_t)l * p.Tmax * H;
     bf16* vc = p.vc + (size_t)l * p.Tmax * H;
     // ---- A: ln_1 + this CTA's columns of q | k | v (HF:272, :179-185) ---------------------------------------------------------------
-    dc_layernorm(x, hb, n, H, P + p.l_off[L_LN1W] + lo, P + p.l_off[L_LN1B] + lo, p.eps);
+    if (TC) {
+      // this layer's LayerNorm vectors and biases -> shared memory, one float4 per thread and pass: a single L2 round trip per layer instead
+      // of one in front of every phase
+      const int seg_len[8] = {H, H, 3 * H, H, H, H, I, H};
+      const int seg_id[8] = {L_LN1W, L_LN1B, L_BQKV, L_BO, L_LN2W, L_LN2B, L_B1, L_B2};
+      for (int i = threadIdx.x * 4; i < 9 * H + I; i += DC_THREADS * 4) {
+        int sgm = 0, off = i;
+        while (off >= seg_len[sgm]) { off -= seg_len[sgm]; ++sgm; }
+        *reinterpret_cast<float4*>(pl + i) = __ldg(reinterpret_cast<const float4*>(P + p.l_off[seg_id[sgm]] + lo + off));
+      }
+      __syncthreads();
+      dc_layernorm<true>(x, hb, n, H, pl, pl + H, p.eps);
+    } else {
+      dc_layernorm(x, hb, n, H, P + p.l_off[L_LN1W] + lo, P + p.l_off[L_LN1B] + lo, p.eps);
+    }
     {
       const int ncols = 3 * H / DC_CTAS, c0 = rank * ncols;
-      dc_gemv(st, p, rank, slots, full, consumed, 0, hb, n, red);
+      if (TC) dt_gemv(tc, p, rank, 0, hb, n, red); else dc_gemv(st, p, rank, slots, full, consumed, 0, hb, n, red);
       for (int i = threadIdx.x; i < n * ncols; i += DC_THREADS) {
         const int t = i / ncols, c = c0 + (i - t * ncols);
-        const float v = red[i] + __ldg(P + p.l_off[L_BQKV] + lo + c);
+        const float v = red[i] + (TC ? pl[2 * H + c] : __ldg(P + p.l_off[L_BQKV] + lo + c));
         if (c < H) s_q[t * H + c] = dc_round_bf16(v);
         else if (c < 2 * H) kc[(size_t)(p.p0 + t) * H + (c - H)] = __float2bfloat16(v);
         else vc[(size_t)(p.p0 + t) * H + (c - 2 * H)] = __float2bfloat16(v);
       }
     }
-    dc_cluster_sync();
+    if (TC) __syncthreads(); else dc_cluster_sync();
+    dc_stamp(p, sk);  // +0: q | k | v done
     // ---- B: causal attention of the new tokens over the cache (HF:47-65); heads rank, rank + 8, ... ---------------------------------
     for (int hh = rank; hh < p.nh; hh += DC_CTAS) {
       // warp w takes keys w, w + 8, ...; lane owns d / 32 dims; per (warp, token) online softmax, merged in warp order below
@@ -357,7 +610,7 @@ __global__ void __launch_bounds__(DC_THREADS, 1) dt_decode_kernel(const DecodePa
       for (int t = 0; t < DC_NT; ++t) {
         m[t] = -INFINITY; lsum[t] = 0.f;
 #pragma unroll
-        for (int e = 0; e < 4; ++e) { acc[t][e] = 0.f; qv[t][e] = (t < n && e < per) ? __ldcg(s_q + t * H + hh * d + lane * per + e) : 0.f; }
+        for (int e = 0; e < 4; ++e) { acc[t][e] = 0.f; qv[t][e] = (t < n && e < per) ? (TC ? s_q[t * H + hh * d + lane * per + e] : __ldcg(s_q + t * H + hh * d + lane * per + e)) : 0.f; }
       }
       const int last = p.p0 + n - 1;
       // four keys per pass (j0, j0 + 8, j0 + 16, j0 + 24): their K / V rows (one vector load per lane and row) are all in flight before
@@ -428,48 +681,54 @@ __global__ void __launch_bounds__(DC_THREADS, 1) dt_decode_kernel(const DecodePa
       }
       __syncthreads();
     }
-    dc_cluster_sync();
+    if (TC) __syncthreads(); else dc_cluster_sync();
+    dc_stamp(p, sk);  // +1: attention done
     // ---- C: attn.c_proj + residual (HF:217-218, :281): this CTA's columns of x ---------------------------------------------------------
-    for (int i = threadIdx.x; i < n * H; i += DC_THREADS) hb[i] = __ldcg(s_o + i);
+    for (int i = threadIdx.x; i < n * H; i += DC_THREADS) hb[i] = (TC ? s_o[i] : __ldcg(s_o + i));
     __syncthreads();
     {
       const int ncols = H / DC_CTAS, c0 = rank * ncols;
-      dc_gemv(st, p, rank, slots, full, consumed, 1, hb, n, red);
+      if (TC) dt_gemv(tc, p, rank, 1, hb, n, red); else dc_gemv(st, p, rank, slots, full, consumed, 1, hb, n, red);
       for (int i = threadIdx.x; i < n * ncols; i += DC_THREADS) {
         const int t = i / ncols, c = c0 + (i - t * ncols);
-        s_x1[t * H + c] = x[t * H + c] + red[i] + __ldg(P + p.l_off[L_BO] + lo + c);
+        s_x1[t * H + c] = x[t * H + c] + red[i] + (TC ? pl[5 * H + c] : __ldg(P + p.l_off[L_BO] + lo + c));
       }
     }
-    dc_cluster_sync();
-    for (int i = threadIdx.x; i < n * H; i += DC_THREADS) x[i] = __ldcg(s_x1 + i);
+    if (TC) __syncthreads(); else dc_cluster_sync();
+    for (int i = threadIdx.x; i < n * H; i += DC_THREADS) x[i] = (TC ? s_x1[i] : __ldcg(s_x1 + i));
     __syncthreads();
+    dc_stamp(p, sk);  // +2: attn.c_proj done
     // ---- D: ln_2 + mlp.c_fc + activation (HF:303, :234-235): this CTA's columns of the hidden layer ------------------------------------
-    dc_layernorm(x, hb, n, H, P + p.l_off[L_LN2W] + lo, P + p.l_off[L_LN2B] + lo, p.eps);
+    if (TC) dc_layernorm<true>(x, hb, n, H, pl + 6 * H, pl + 7 * H, p.eps);
+    else dc_layernorm(x, hb, n, H, P + p.l_off[L_LN2W] + lo, P + p.l_off[L_LN2B] + lo, p.eps);
     {
       const int ncols = I / DC_CTAS, c0 = rank * ncols;
-      dc_gemv(st, p, rank, slots, full, consumed, 2, hb, n, red);
+      if (TC) dt_gemv(tc, p, rank, 2, hb, n, red); else dc_gemv(st, p, rank, slots, full, consumed, 2, hb, n, red);
       for (int i = threadIdx.x; i < n * ncols; i += DC_THREADS) {
         const int t = i / ncols, c = c0 + (i - t * ncols);
-        s_fc[t * I + c] = dc_round_bf16(dc_act(red[i] + __ldg(P + p.l_off[L_B1] + lo + c), p.act));
+        s_fc[t * I + c] = dc_round_bf16(dc_act(red[i] + (TC ? pl[8 * H + c] : __ldg(P + p.l_off[L_B1] + lo + c)), p.act));
       }
     }
-    dc_cluster_sync();
+    if (TC) __syncthreads(); else dc_cluster_sync();
+    dc_stamp(p, sk);  // +3: mlp.c_fc done
     // ---- F: mlp.c_proj + residual (HF:236-237, :306) -----------------------------------------------------------------------------------
-    for (int i = threadIdx.x; i < n * I; i += DC_THREADS) hb[i] = __ldcg(s_fc + i);
+    for (int i = threadIdx.x; i < n * I; i += DC_THREADS) hb[i] = (TC ? s_fc[i] : __ldcg(s_fc + i));
     __syncthreads();
     {
       const int ncols = H / DC_CTAS, c0 = rank * ncols;
-      dc_gemv(st, p, rank, slots, full, consumed, 3, hb, n, red);
+      if (TC) dt_gemv(tc, p, rank, 3, hb, n, red); else dc_gemv(st, p, rank, slots, full, consumed, 3, hb, n, red);
       for (int i = threadIdx.x; i < n * ncols; i += DC_THREADS) {
         const int t = i / ncols, c = c0 + (i - t * ncols);
-        s_x2[t * H + c] = x[t * H + c] + red[i] + __ldg(P + p.l_off[L_B2] + lo + c);
+        s_x2[t * H + c] = x[t * H + c] + red[i] + (TC ? pl[8 * H + I + c] : __ldg(P + p.l_off[L_B2] + lo + c));
       }
     }
-    dc_cluster_sync();
-    for (int i = threadIdx.x; i < n * H; i += DC_THREADS) x[i] = __ldcg(s_x2 + i);
+    if (TC) __syncthreads(); else dc_cluster_sync();
+    for (int i = threadIdx.x; i < n * H; i += DC_THREADS) x[i] = (TC ? s_x2[i] : __ldcg(s_x2 + i));
     __syncthreads();
+    dc_stamp(p, sk);  // +4: mlp.c_proj done
   }
 
+  dc_stamp(p, sk);  // after every layer's +4 below: all layers done
   // ---- ln_f + predict_action on the last token when it is a state token (HF:450, :652) ------------------------------------------------
   const int last_tok = p.p0 + n - 1;
   if (rank == 0 && last_tok % 3 == 1 && p.action_out) {
@@ -482,7 +741,16 @@ __global__ void __launch_bounds__(DC_THREADS, 1) dt_decode_kernel(const DecodePa
       if (lane == 0) p.action_out[a] = p.tanh_act ? tanhf(s) : s;
     }
   }
+  dc_stamp(p, sk);  // last: head done
   dc_cluster_sync();  // no CTA leaves while a peer may still be reading what it wrote (and: one completion point for the next launch)
+  if (TC) {
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2) {
+      tc_fence_after();
+      tmem_dealloc(tc.tmem, DT_TMEM_COLS);
+    }
+  }
 }
 
 }  // namespace dtb
@@ -491,13 +759,46 @@ using namespace dtb;
 
 extern "C" {
 
-// Cluster size: the largest power of two <= 16 such that a CTA streams at most ~0.5 MB of weights per layer, and every column slice
-// (H / C, 3H / C, I / C) is a whole number of 8-column groups.  c1 / c2 (H = 128): 1 CTA (no cluster barriers at all), c3: 4, c4: 16.
+// Tensor-core path (dt_gemv): hidden a multiple of 128, one CTA per 128 hidden columns — every CTA then owns 384 / 128 / (I / C) / 128 columns
+// of the four matrices, whole 128-feature MMA tiles.  DTB_DECODE_FFMA=1 forces the CUDA-core kernel (A/B measurements, tests).
+static bool dc_use_tc(const dtb_dt_config& c) {
+  static int force_ffma = -1;
+  if (force_ffma < 0) {
+    const char* e = getenv("DTB_DECODE_FFMA");
+    force_ffma = (e && e[0] == '1') ? 1 : 0;
+  }
+  if (force_ffma || c.hidden != 128) return false;  // one CTA (C = 1): the exchange between the phases stays in shared memory
+  const int C = c.hidden / 128;
+  return C <= DC_MAX_CTAS && c.n_inner % (128 * C) == 0 && c.n_inner / C <= 128 * (DT_TMEM_COLS / DT_NTOK) && c.hidden / c.n_head <= 128;
+}
+// Cluster size.  Tensor-core path: hidden / 128.  CUDA-core path: the largest power of two <= 16 such that a CTA streams at most ~0.5 MB
+// of weights per layer, and every column slice (H / C, 3H / C, I / C) is a whole number of 8-column groups.
 static int dc_cluster_size(const dtb_dt_config& c) {
+  if (dc_use_tc(c)) return c.hidden / 128;
   const double layer_bytes = 2.0 * (4.0 * c.hidden * c.hidden + 2.0 * c.hidden * c.n_inner);
   int C = 1;
   while (C < DC_MAX_CTAS && layer_bytes / C > 512.0 * 1024.0 && c.hidden % (16 * C) == 0 && c.n_inner % (16 * C) == 0) C *= 2;
   return C;
+}
+// tensor-core path: dynamic shared memory = x | hb | red (tc_red_floats) | pad to 1 KB | B-operand image | ring | barriers
+static int dc_tc_red_floats(const dtb_dt_config& c) {
+  const int C = c.hidden / 128, d = c.hidden / c.n_head;
+  int widest = 3 * c.hidden / C;
+  if (c.n_inner / C > widest) widest = c.n_inner / C;
+  int r = DC_NT * widest, a = (DC_THREADS / 32) * DC_NT * (d + 2);
+  return ((r > a ? r : a) + 63) & ~63;
+}
+static size_t dc_tc_smem(const dtb_dt_config& c, int* slots_out) {
+  const int KI = c.hidden > c.n_inner ? c.hidden : c.n_inner;
+  const size_t fixed = ((size_t)DC_NT * c.hidden + (size_t)DC_NT * KI + dc_tc_red_floats(c) + 13 * c.hidden + DC_NT * c.n_inner + 9 * c.hidden + c.n_inner) * sizeof(float) +
+                       1024 + (size_t)(KI / 64) * 2048 +
+                       (2 * DT_MAX_SLOTS + 1) * sizeof(uint64_t) + 64;
+  const size_t limit = 227 * 1024;
+  int slots = fixed + DT_BLOCK_BYTES <= limit ? (int)((limit - fixed) / DT_BLOCK_BYTES) : 0;
+  if (slots > DT_MAX_SLOTS) slots = DT_MAX_SLOTS;
+  while (slots & (slots - 1)) --slots;  // a power of two (the kernel masks instead of dividing)
+  if (slots_out) *slots_out = slots;
+  return fixed + (size_t)slots * DT_BLOCK_BYTES;
 }
 static size_t dc_layer_elems(const dtb_dt_config& c) { return (size_t)4 * c.hidden * c.hidden + (size_t)2 * c.hidden * c.n_inner; }
 // byte offset of the decode-layout weights inside the cache buffer: after the K/V cache and the exchange scratch
@@ -510,6 +811,11 @@ int dtb_dt_decode_supported(const dtb_dt* h) {
   const dtb_dt_config& c = h->c;
   const int C = dc_cluster_size(c);
   const int widest = (3 * c.hidden > c.n_inner ? 3 * c.hidden : c.n_inner) / C;
+  if (dc_use_tc(c)) {
+    int slots = 0;
+    dc_tc_smem(c, &slots);
+    return slots >= 2 && (h->sd_small || c.state_dim % 8 == 0) ? 1 : 0;
+  }
   return c.hidden % 8 == 0 && c.hidden <= DC_MAXH && c.n_inner % 8 == 0 && widest <= 1536 && (h->sd_small || (c.state_dim % 8 == 0 && c.hidden % C == 0)) ? 1 : 0;
 }
 
@@ -550,7 +856,8 @@ int dtb_dt_decode_stage(const dtb_dt* h, void* stream, const void* params_bf16, 
   const size_t chunks = dc_layer_elems(h->c) * h->c.n_layer / 8;
   size_t blocks = (chunks + 255) / 256;
   if (blocks > (size_t)num_sms() * 8) blocks = (size_t)num_sms() * 8;
-  DTB_LAUNCH(dt_decode_stage_kernel, (unsigned)blocks, 256, 0, (cudaStream_t)stream, p, dc_layer_elems(h->c));
+  if (dc_use_tc(h->c)) DTB_LAUNCH(dt_decode_stage_tc_kernel, (unsigned)blocks, 256, 0, (cudaStream_t)stream, p, dc_layer_elems(h->c));
+  else DTB_LAUNCH(dt_decode_stage_kernel, (unsigned)blocks, 256, 0, (cudaStream_t)stream, p, dc_layer_elems(h->c));
   DTB_CHECK_LAUNCH();
   return DTB_OK;
 }
@@ -569,13 +876,28 @@ int dtb_dt_decode(const dtb_dt* h, void* stream, const float* params, const void
   dc_fill(h, p, params, params_bf16, cache, K);
   p.states = states; p.states_bf16 = reinterpret_cast<const bf16*>(states_bf16); p.actions = actions; p.rtg = returns_to_go; p.timesteps = timesteps;
   p.action_out = action_out;
+  {
+    static int stamp = -1;
+    if (stamp < 0) { const char* e = getenv("DTB_DECODE_STAMP"); stamp = (e && e[0] == '1') ? 1 : 0; }
+    if (stamp && dc_use_tc(c)) p.stamps = reinterpret_cast<unsigned long long*>(p.scratch);  // the L2 exchange scratch is unused on this path
+  }
   const int KI = c.hidden > c.n_inner ? c.hidden : c.n_inner;
-  const size_t smem = ((size_t)DC_NT * c.hidden + (size_t)DC_NT * KI + DC_RED_FLOATS) * sizeof(float) + (size_t)DC_SLOTS * DC_SLOT_BYTES + 64;
-  static size_t attr = 0;
-  if (smem > attr) {
-    DTB_CUDA(cudaFuncSetAttribute(dt_decode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    DTB_CUDA(cudaFuncSetAttribute(dt_decode_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
-    attr = smem;
+  const bool tc = dc_use_tc(c);
+  size_t smem = ((size_t)DC_NT * c.hidden + (size_t)DC_NT * KI + DC_RED_FLOATS) * sizeof(float) + (size_t)DC_SLOTS * DC_SLOT_BYTES + 64;
+  if (tc) {
+    smem = dc_tc_smem(c, &p.tc_slots);
+    p.tc_red_floats = dc_tc_red_floats(c);
+  }
+  static size_t attr[2] = {0, 0};
+  if (smem > attr[tc ? 1 : 0]) {
+    if (tc) {
+      DTB_CUDA(cudaFuncSetAttribute(dt_decode_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      DTB_CUDA(cudaFuncSetAttribute(dt_decode_kernel<true>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+    } else {
+      DTB_CUDA(cudaFuncSetAttribute(dt_decode_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      DTB_CUDA(cudaFuncSetAttribute(dt_decode_kernel<false>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+    }
+    attr[tc ? 1 : 0] = smem;
   }
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));
@@ -593,7 +915,8 @@ int dtb_dt_decode(const dtb_dt* h, void* stream, const float* params, const void
   for (int p0 = t_cached > 0 ? 3 * t_cached - 1 : 0; p0 < p1; p0 += DC_NT) {
     p.p0 = p0;
     p.n = p1 - p0 < DC_NT ? p1 - p0 : DC_NT;
-    DTB_CUDA(cudaLaunchKernelEx(&cfg, dt_decode_kernel, p));
+    if (tc) DTB_CUDA(cudaLaunchKernelEx(&cfg, dt_decode_kernel<true>, p));
+    else DTB_CUDA(cudaLaunchKernelEx(&cfg, dt_decode_kernel<false>, p));
     DTB_CHECK_LAUNCH();
   }
   return DTB_OK;

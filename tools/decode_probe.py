@@ -46,4 +46,28 @@ for name in sys.argv[1:] or ["c1", "c3", "c4"]:
         wall.append((time.perf_counter() - t0) * 1e6)
         gpu.append(e0.elapsed_time(e1) * 1e3)
     gpu.sort(); wall.sort()
-    print(f"{name}: decode step GPU {gpu[n // 2]:.1f} us (event span incl. launch + clone), wall {wall[n // 2]:.1f} us", flush=True)
+    # the kernel alone: the same call captured in a CUDA graph and replayed back to back (no host time between launches)
+    dt._dc["t"] = K - 1
+    torch.cuda.synchronize()
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        call()
+    torch.cuda.synchronize()
+    reps = 200
+    e0.record()
+    for _ in range(reps):
+        graph.replay()
+    e1.record()
+    torch.cuda.synchronize()
+    kern = e0.elapsed_time(e1) * 1e3 / reps
+    if os.environ.get("DTB_DECODE_STAMP") == "1":
+        cfg = wl["dt"]
+        H, L = cfg["hidden_size"], cfg["n_layer"]
+        kv = (2 * L * 3 * K * H * 2 + 255) & ~255
+        base = (dt._dc["cache"].data_ptr() + 255) & ~255
+        off = base - dt._dc["cache"].data_ptr() + kv
+        st = dt._dc["cache"][off:off + 8 * (4 + 5 * L)].view(torch.int64).cpu().tolist()
+        names = ["start", "embedded"] + [f"L{l}.{ph}" for l in range(L) for ph in ("qkv", "attn", "proj", "fc", "proj2")] + ["layers", "head"]
+        print(name, "phase stamps (us since kernel start):", ", ".join(f"{nm} {(v - st[0]) / 1e3:.1f}" for nm, v in zip(names, st)), flush=True)
+    print(f"{name}: decode step kernel {kern:.1f} us (graph replays back to back), event span incl. launch + clone {gpu[n // 2]:.1f} us, wall {wall[n // 2]:.1f} us "
+          f"[{'FFMA' if os.environ.get('DTB_DECODE_FFMA') == '1' else 'tensor-core where supported'}]", flush=True)
