@@ -300,6 +300,14 @@ int dtb_dt_decode_stage(const dtb_dt* h, void* stream, const void* params_bf16, 
 int dtb_dt_decode(const dtb_dt* h, void* stream, const float* params, const void* params_bf16, const float* states, const void* states_bf16,
                   const float* actions, const float* returns_to_go, const long long* timesteps, int t, int t_cached, int K, void* cache,
                   size_t cache_bytes, float* action_out);
+/* One rollout step of the same kernel in a form a CUDA graph can replay: the step count t (1-based, the history length of THIS call) is read
+ * from device memory (*t_dev) and advanced to t + 1 by the kernel; the per-timestep inputs are 2-row windows holding timesteps t-2 and t-1
+ * (row 0 unused when t = 1; dtb_pad_left with K = 2 builds them): states2 fp32 [2, state_dim] (state_dim <= 64) or, for wide states, the
+ * newest timestep's features state_new_bf16 [state_dim]; actions2 [2, act_dim], returns_to_go2 [2], timesteps2 [2].  The cache must hold
+ * the keys / values of timesteps 0 .. t-2 (append-only use after dtb_dt_decode); the caller keeps t <= K. */
+int dtb_dt_decode_step(const dtb_dt* h, void* stream, const float* params, const void* params_bf16, const float* states2, const void* state_new_bf16,
+                       const float* actions2, const float* returns_to_go2, const long long* timesteps2, int* t_dev, int K, void* cache,
+                       size_t cache_bytes, float* action_out);
 int dtb_dt_stage_grad_range(const dtb_dt* h, int stage, long long* begin, long long* end);
 
 /* ---- multimodal state encoder (REF src/agents.py:30-55 conv_factory, :118-119 towers, :133-134 /255, :137-143 fusion) ------

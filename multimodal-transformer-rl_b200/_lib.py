@@ -98,6 +98,7 @@ def _declare(lib):
     lib.dtb_dt_decode_cache_bytes.restype = sz
     lib.dtb_dt_decode_stage.argtypes = [vp, vp, vp, i, vp, sz]
     lib.dtb_dt_decode.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, vp, i, i, i, vp, sz, vp]
+    lib.dtb_dt_decode_step.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i, vp, sz, vp]
     lib.dtb_encoder_create.argtypes = [C.POINTER(EncoderConfig), C.POINTER(vp)]
     lib.dtb_encoder_destroy.argtypes = [vp]
     lib.dtb_encoder_state_dim.argtypes = [vp]

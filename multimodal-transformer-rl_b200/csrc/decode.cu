@@ -51,6 +51,10 @@ struct DecodeParams {
   float* scratch;           // exchange buffers, see dc_scratch_floats
   float* action_out;        // [ad]: prediction of the last processed token (written when it is a state token)
   int tc_slots, tc_red_floats;  // tensor-core path: ring slots that fit, length of `red`
+  // step mode (dtb_dt_decode_step, CUDA-graph replayable): the timestep count t of this call is read from device memory (and advanced
+  // by the kernel), the per-timestep histories are 2-row windows [t - 2, t - 1], the wide state of the newest timestep is state_new
+  int* t_dev;
+  const bf16* state_new;
   unsigned long long* stamps;   // developer probe (DTB_DECODE_STAMP=1): %globaltimer at the phase boundaries, written by thread 0
 };
 
@@ -426,7 +430,8 @@ __device__ __forceinline__ void dt_gemv(DcTc& tc, const DecodeParams& p, int ran
 template <bool TC>
 __global__ void __launch_bounds__(DC_THREADS, 1) dt_decode_kernel(const DecodeParams p) {
   extern __shared__ __align__(16) float dc_smem[];
-  const int H = p.H, I = p.I, n = p.n, d = p.d;
+  const int H = p.H, I = p.I, d = p.d;
+  int p0 = p.p0, n = p.n, hbase = 0;
   const int KI = H > I ? H : I;
   float* x = dc_smem;                 // [NT][H]  residual stream of the new tokens (replicated in every CTA)
   float* hb = x + DC_NT * H;          // [NT][KI] GEMV input (LayerNorm output / attention output / MLP hidden), bf16-rounded values
@@ -464,6 +469,12 @@ __global__ void __launch_bounds__(DC_THREADS, 1) dt_decode_kernel(const DecodePa
   pdl_wait();
   int sk = 0;
   dc_stamp(p, sk);  // 0: start
+  if (p.t_dev) {  // step mode: tokens a_{t-2}, R_{t-1}, s_{t-1} (0-based timesteps) of the t-step history; rows of the 2-row windows = k - (t - 2)
+    const int t_now = *reinterpret_cast<volatile int*>(p.t_dev);
+    p0 = t_now > 1 ? 3 * (t_now - 1) - 1 : 0;
+    n = 3 * t_now - 1 - p0;
+    hbase = t_now - 2;
+  }
   // start the weight stream: the first DEPTH tiles fly while the tokens are embedded
   DcStream st;
   int consumed = 0;
@@ -502,10 +513,10 @@ __global__ void __launch_bounds__(DC_THREADS, 1) dt_decode_kernel(const DecodePa
   int wide_tok = -1;
   if (!p.sd_small)
     for (int t = 0; t < n; ++t)
-      if ((p.p0 + t) % 3 == 1) wide_tok = t;  // at most one state token among <= 3 consecutive tokens
+      if ((p0 + t) % 3 == 1) wide_tok = t;  // at most one state token among <= 3 consecutive tokens
   if (wide_tok >= 0) {
-    const int k = (p.p0 + wide_tok) / 3, per = H / DC_CTAS;
-    const bf16* srow = p.states_bf16 + (size_t)k * p.sd;
+    const int k = (p0 + wide_tok) / 3, per = H / DC_CTAS;
+    const bf16* srow = p.t_dev ? p.state_new : p.states_bf16 + (size_t)k * p.sd;
     for (int c = rank * per + warp; c < (rank + 1) * per; c += DC_THREADS / 32) {
       const bf16* w = Pb + p.e_off[E_WS] + (size_t)c * p.sd;
       float a = 0.f;
@@ -528,18 +539,18 @@ __global__ void __launch_bounds__(DC_THREADS, 1) dt_decode_kernel(const DecodePa
   // ---- embedding + embed_ln of the new tokens (HF:611-628), replicated in every CTA ------------------------------------------------
   for (int idx = threadIdx.x; idx < n * H; idx += DC_THREADS) {  // all tokens at once: their dependent loads (timestep -> table row) overlap
     const int t = idx / H, c = idx - t * H;
-    const int tok = p.p0 + t, k = tok / 3, type = tok - 3 * k;
-    long long ts = p.timesteps[k];
+    const int tok = p0 + t, k = tok / 3, type = tok - 3 * k;
+    long long ts = p.timesteps[k - hbase];
     ts = ts < 0 ? 0 : (ts >= p.E ? p.E - 1 : ts);
     const float* te = P + p.e_off[E_TABLE] + (size_t)ts * H;
     float v = __ldg(te + c);
     if (type == 0) {
-      v += p.rtg[k] * __ldg(P + p.e_off[E_WR] + c) + __ldg(P + p.e_off[E_BR] + c);
+      v += p.rtg[k - hbase] * __ldg(P + p.e_off[E_WR] + c) + __ldg(P + p.e_off[E_BR] + c);
     } else if (type == 1) {
       v += __ldg(P + p.e_off[E_BS] + c);
       if (p.sd_small) {
         const float* w = P + p.e_off[E_WS] + (size_t)c * p.sd;
-        const float* srow = p.states + (size_t)k * p.sd;
+        const float* srow = p.states + (size_t)(k - hbase) * p.sd;
         for (int j = 0; j < p.sd; ++j) v = fmaf(__ldg(w + j), __ldg(srow + j), v);
       } else {
         v += (TC ? s_sp[c] : __ldcg(s_sp + c));
@@ -547,7 +558,7 @@ __global__ void __launch_bounds__(DC_THREADS, 1) dt_decode_kernel(const DecodePa
     } else {
       v += __ldg(P + p.e_off[E_BA] + c);
       const float* w = P + p.e_off[E_WA] + (size_t)c * p.ad;
-      const float* arow = p.actions + (size_t)k * p.ad;
+      const float* arow = p.actions + (size_t)(k - hbase) * p.ad;
       for (int j = 0; j < p.ad; ++j) v = fmaf(__ldg(w + j), __ldg(arow + j), v);
     }
     hb[t * H + c] = v;
@@ -595,8 +606,8 @@ __global__ void __launch_bounds__(DC_THREADS, 1) dt_decode_kernel(const DecodePa
         const int t = i / ncols, c = c0 + (i - t * ncols);
         const float v = red[i] + (TC ? pl[2 * H + c] : __ldg(P + p.l_off[L_BQKV] + lo + c));
         if (c < H) s_q[t * H + c] = dc_round_bf16(v);
-        else if (c < 2 * H) kc[(size_t)(p.p0 + t) * H + (c - H)] = __float2bfloat16(v);
-        else vc[(size_t)(p.p0 + t) * H + (c - 2 * H)] = __float2bfloat16(v);
+        else if (c < 2 * H) kc[(size_t)(p0 + t) * H + (c - H)] = __float2bfloat16(v);
+        else vc[(size_t)(p0 + t) * H + (c - 2 * H)] = __float2bfloat16(v);
       }
     }
     if (TC) __syncthreads(); else dc_cluster_sync();
@@ -612,7 +623,7 @@ __global__ void __launch_bounds__(DC_THREADS, 1) dt_decode_kernel(const DecodePa
 #pragma unroll
         for (int e = 0; e < 4; ++e) { acc[t][e] = 0.f; qv[t][e] = (t < n && e < per) ? (TC ? s_q[t * H + hh * d + lane * per + e] : __ldcg(s_q + t * H + hh * d + lane * per + e)) : 0.f; }
       }
-      const int last = p.p0 + n - 1;
+      const int last = p0 + n - 1;
       // four keys per pass (j0, j0 + 8, j0 + 16, j0 + 24): their K / V rows (one vector load per lane and row) are all in flight before
       // the first dot product.  ld.global.cg: the rows of this launch's tokens were written by other CTAs of the cluster a barrier ago.
       auto load_row = [&](const bf16* base, int j, float (&out)[4]) {
@@ -641,7 +652,7 @@ __global__ void __launch_bounds__(DC_THREADS, 1) dt_decode_kernel(const DecodePa
           const int j = j0 + u * (DC_THREADS / 32);
 #pragma unroll
           for (int t = 0; t < DC_NT; ++t) {
-            if (t < n && j <= p.p0 + t) {  // warp-uniform (implies j <= last)
+            if (t < n && j <= p0 + t) {  // warp-uniform (implies j <= last)
               float sc = 0.f;
 #pragma unroll
               for (int e = 0; e < 4; ++e) sc = fmaf(qv[t][e], kv[u][e], sc);
@@ -730,7 +741,7 @@ __global__ void __launch_bounds__(DC_THREADS, 1) dt_decode_kernel(const DecodePa
 
   dc_stamp(p, sk);  // after every layer's +4 below: all layers done
   // ---- ln_f + predict_action on the last token when it is a state token (HF:450, :652) ------------------------------------------------
-  const int last_tok = p.p0 + n - 1;
+  const int last_tok = p0 + n - 1;
   if (rank == 0 && last_tok % 3 == 1 && p.action_out) {
     dc_layernorm(x + (n - 1) * H, hb, 1, H, P + p.t_off[T_LNFW], P + p.t_off[T_LNFB], p.eps);
     for (int a = warp; a < p.ad; a += DC_THREADS / 32) {
@@ -741,6 +752,7 @@ __global__ void __launch_bounds__(DC_THREADS, 1) dt_decode_kernel(const DecodePa
       if (lane == 0) p.action_out[a] = p.tanh_act ? tanhf(s) : s;
     }
   }
+  if (p.t_dev && rank == 0 && threadIdx.x == 0) *p.t_dev = hbase + 3;  // t + 1: the next step's count
   dc_stamp(p, sk);  // last: head done
   dc_cluster_sync();  // no CTA leaves while a peer may still be reading what it wrote (and: one completion point for the next launch)
   if (TC) {
@@ -814,7 +826,7 @@ int dtb_dt_decode_supported(const dtb_dt* h) {
   if (dc_use_tc(c)) {
     int slots = 0;
     dc_tc_smem(c, &slots);
-    return slots >= 2 && (h->sd_small || c.state_dim % 8 == 0) ? 1 : 0;
+    return slots >= 2 && (h->sd_small || c.state_dim % 8 == 0) ? 2 : 0;  // 2 = the tensor-core kernel (the host's automatic choice)
   }
   return c.hidden % 8 == 0 && c.hidden <= DC_MAXH && c.n_inner % 8 == 0 && widest <= 1536 && (h->sd_small || (c.state_dim % 8 == 0 && c.hidden % C == 0)) ? 1 : 0;
 }
@@ -862,20 +874,8 @@ int dtb_dt_decode_stage(const dtb_dt* h, void* stream, const void* params_bf16, 
   return DTB_OK;
 }
 
-int dtb_dt_decode(const dtb_dt* h, void* stream, const float* params, const void* params_bf16, const float* states, const void* states_bf16,
-                  const float* actions, const float* returns_to_go, const long long* timesteps, int t, int t_cached, int K, void* cache,
-                  size_t cache_bytes, float* action_out) {
-  DTB_REQUIRE(h && params && params_bf16 && actions && returns_to_go && timesteps && cache && action_out, DTB_ERR_BAD_ARG, "dtb_dt_decode: null argument");
-  DTB_REQUIRE(dtb_dt_decode_supported(h), DTB_ERR_UNSUPPORTED, "dtb_dt_decode: hidden %d / n_inner %d unsupported", h->c.hidden, h->c.n_inner);
-  DTB_REQUIRE(t >= 1 && t <= K && t_cached >= 0 && t_cached < t, DTB_ERR_BAD_ARG, "dtb_dt_decode: need 0 <= t_cached (%d) < t (%d) <= K (%d)", t_cached, t, K);
-  DTB_REQUIRE(h->sd_small ? states != nullptr : states_bf16 != nullptr, DTB_ERR_BAD_ARG, "dtb_dt_decode: states (fp32, state_dim <= 64) or states_bf16 (wide) required");
-  DTB_REQUIRE(cache_bytes >= dtb_dt_decode_cache_bytes(h, K), DTB_ERR_WORKSPACE, "dtb_dt_decode: cache too small");
-  DTB_TRY(require_sm100());
+static int dc_launch(const dtb_dt* h, cudaStream_t stream, DecodeParams& p, int t, int t_cached) {
   const dtb_dt_config& c = h->c;
-  DecodeParams p;
-  dc_fill(h, p, params, params_bf16, cache, K);
-  p.states = states; p.states_bf16 = reinterpret_cast<const bf16*>(states_bf16); p.actions = actions; p.rtg = returns_to_go; p.timesteps = timesteps;
-  p.action_out = action_out;
   {
     static int stamp = -1;
     if (stamp < 0) { const char* e = getenv("DTB_DECODE_STAMP"); stamp = (e && e[0] == '1') ? 1 : 0; }
@@ -901,7 +901,7 @@ int dtb_dt_decode(const dtb_dt* h, void* stream, const float* params, const void
   }
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));
-  cfg.gridDim = dim3(p.C); cfg.blockDim = dim3(DC_THREADS); cfg.dynamicSmemBytes = smem; cfg.stream = (cudaStream_t)stream;
+  cfg.gridDim = dim3(p.C); cfg.blockDim = dim3(DC_THREADS); cfg.dynamicSmemBytes = smem; cfg.stream = stream;
   cudaLaunchAttribute at[2];
   at[0].id = cudaLaunchAttributeClusterDimension;
   at[0].val.clusterDim.x = p.C; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
@@ -909,6 +909,13 @@ int dtb_dt_decode(const dtb_dt* h, void* stream, const float* params, const void
   at[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = at;
   cfg.numAttrs = pdl_enabled() ? 2 : 1;
+  if (p.t_dev) {  // step mode: one launch, the token range comes from the device-side count
+    p.p0 = 0; p.n = 0;
+    if (tc) DTB_CUDA(cudaLaunchKernelEx(&cfg, dt_decode_kernel<true>, p));
+    else DTB_CUDA(cudaLaunchKernelEx(&cfg, dt_decode_kernel<false>, p));
+    DTB_CHECK_LAUNCH();
+    return DTB_OK;
+  }
   // tokens [p0, p1): the action token of the last cached timestep (its action was a placeholder when it was cached), then R, s of every
   // new timestep; the newest timestep's own action token comes after its state token and is not needed for the prediction
   const int p1 = 3 * t - 1;
@@ -920,6 +927,40 @@ int dtb_dt_decode(const dtb_dt* h, void* stream, const float* params, const void
     DTB_CHECK_LAUNCH();
   }
   return DTB_OK;
+}
+
+int dtb_dt_decode(const dtb_dt* h, void* stream, const float* params, const void* params_bf16, const float* states, const void* states_bf16,
+                  const float* actions, const float* returns_to_go, const long long* timesteps, int t, int t_cached, int K, void* cache,
+                  size_t cache_bytes, float* action_out) {
+  DTB_REQUIRE(h && params && params_bf16 && actions && returns_to_go && timesteps && cache && action_out, DTB_ERR_BAD_ARG, "dtb_dt_decode: null argument");
+  DTB_REQUIRE(dtb_dt_decode_supported(h), DTB_ERR_UNSUPPORTED, "dtb_dt_decode: hidden %d / n_inner %d unsupported", h->c.hidden, h->c.n_inner);
+  DTB_REQUIRE(t >= 1 && t <= K && t_cached >= 0 && t_cached < t, DTB_ERR_BAD_ARG, "dtb_dt_decode: need 0 <= t_cached (%d) < t (%d) <= K (%d)", t_cached, t, K);
+  DTB_REQUIRE(h->sd_small ? states != nullptr : states_bf16 != nullptr, DTB_ERR_BAD_ARG, "dtb_dt_decode: states (fp32, state_dim <= 64) or states_bf16 (wide) required");
+  DTB_REQUIRE(cache_bytes >= dtb_dt_decode_cache_bytes(h, K), DTB_ERR_WORKSPACE, "dtb_dt_decode: cache too small");
+  DTB_TRY(require_sm100());
+  DecodeParams p;
+  dc_fill(h, p, params, params_bf16, cache, K);
+  p.states = states; p.states_bf16 = reinterpret_cast<const bf16*>(states_bf16); p.actions = actions; p.rtg = returns_to_go; p.timesteps = timesteps;
+  p.action_out = action_out;
+  return dc_launch(h, (cudaStream_t)stream, p, t, t_cached);
+}
+
+int dtb_dt_decode_step(const dtb_dt* h, void* stream, const float* params, const void* params_bf16, const float* states2, const void* state_new_bf16,
+                       const float* actions2, const float* returns_to_go2, const long long* timesteps2, int* t_dev, int K, void* cache,
+                       size_t cache_bytes, float* action_out) {
+  DTB_REQUIRE(h && params && params_bf16 && actions2 && returns_to_go2 && timesteps2 && t_dev && cache && action_out, DTB_ERR_BAD_ARG,
+              "dtb_dt_decode_step: null argument");
+  DTB_REQUIRE(dtb_dt_decode_supported(h), DTB_ERR_UNSUPPORTED, "dtb_dt_decode_step: hidden %d / n_inner %d unsupported", h->c.hidden, h->c.n_inner);
+  DTB_REQUIRE(h->sd_small ? states2 != nullptr : state_new_bf16 != nullptr, DTB_ERR_BAD_ARG,
+              "dtb_dt_decode_step: states2 (fp32 [2, state_dim], state_dim <= 64) or state_new_bf16 (wide, [state_dim]) required");
+  DTB_REQUIRE(cache_bytes >= dtb_dt_decode_cache_bytes(h, K), DTB_ERR_WORKSPACE, "dtb_dt_decode_step: cache too small");
+  DTB_TRY(require_sm100());
+  DecodeParams p;
+  dc_fill(h, p, params, params_bf16, cache, K);
+  p.states = states2; p.state_new = reinterpret_cast<const bf16*>(state_new_bf16); p.actions = actions2; p.rtg = returns_to_go2; p.timesteps = timesteps2;
+  p.t_dev = t_dev;
+  p.action_out = action_out;
+  return dc_launch(h, (cudaStream_t)stream, p, 0, 0);
 }
 
 }  // extern "C"

@@ -321,8 +321,7 @@ class MultimodalDecisionTransformer(nn.Module):
 
         dt, K = self.dt, self.dt.max_length
         t = frames.shape[0]
-        if K is not None and t <= K and (dt.kv_cache if kwargs.get("use_cache") is None else kwargs["use_cache"]) and dt._decode_ready() \
-                and not self.encoder.attn_type:
+        if K is not None and t <= K and not self.encoder.attn_type and dt._use_cache(kwargs.get("use_cache")):
             # KV-cached step: the towers run on the NEW frames only, their features join a K-row history buffer, one decode kernel follows
             hist = self.__dict__.get("_feat_hist")
             if hist is None or hist.device != dt._flat.device:
@@ -332,6 +331,11 @@ class MultimodalDecisionTransformer(nn.Module):
             dt._stage()
             stale = dc is None or dc["ptr"] != dt._flat.data_ptr() or dc["stamp"] != dt._staged_version or t <= dc["t"] \
                 or self.__dict__.get("_feat_stamp") != self.encoder._staged_version
+            if not stale and self.__dict__.get("_feat_stamp") == self.encoder._staged_version:
+                fdt = torch.uint8 if frames.dtype == torch.uint8 else torch.float32
+                r = dt._step_runner(t, self.encoder, fdt)
+                if r is not None:  # the next step of a cached rollout: one pad_left launch + one graph replay (towers on the new frame + decode)
+                    return r.step([(frames, r.frames), (audio, r.audio), (actions, r.actions), (returns_to_go, r.rtg), (timesteps, r.timesteps)], t)
             t0 = 0 if stale else dc["t"]
             if stale and dc is not None:
                 dc["t"] = 0

@@ -77,9 +77,9 @@ class DecisionTransformer(nn.Module):
         self._p_resid, self._p_attn = float(resid_pdrop or 0.0), float(attn_pdrop or 0.0)
         self._p_embd = self._p_resid if embd_pdrop is None else float(embd_pdrop)
         # get_action(use_cache=True) / kv_cache = True: append to a per-layer K/V cache while the history fits the window (exact, see _decode).
-        # Off by default: measured on B200 the one-kernel decode step is not yet faster than the graph of the full B = 1 forward
-        # (c1 147 vs ~100 us of GPU time, c4 0.8-1.2 vs 0.9 ms) — it is issue / latency bound on the 1-16 SMs it uses.
-        self.kv_cache = False
+        # None = automatic: on where the decode step runs on the tensor core (hidden_size 128: c1 / c2 — measured faster than the graph of
+        # the full B = 1 forward), off where only the CUDA-core kernel applies (c3 / c4: measured slower).
+        self.kv_cache = None
         self._dc = None               # decode state: cache buffer, timesteps cached, parameter stamp, output buffer
         self._drop_state = None       # device int32 [3] = {seed_lo, seed_hi, step}, read by the kernels at run time
         self._drop_applied = None     # (p_embd, p_attn, p_resid, state ptr) last handed to the library
@@ -339,6 +339,25 @@ class DecisionTransformer(nn.Module):
         return bool(self.max_length is not None and not self.dropout_active()
                     and _lib.load().dtb_dt_decode_supported(self._h))
 
+    def _use_cache(self, use_cache) -> bool:
+        """use_cache argument > kv_cache attribute > automatic (on where dtb_dt_decode_supported reports the tensor-core kernel: 2)."""
+        choice = self.kv_cache if use_cache is None else use_cache
+        if choice is None:
+            return bool(self.max_length is not None and not self.dropout_active() and _lib.load().dtb_dt_decode_supported(self._h) == 2)
+        return bool(choice) and self._decode_ready()
+
+    def _step_runner(self, t: int, encoder=None, frames_dtype=None):
+        """The graph-replay runner when this call is the next step of a rollout the cache already holds (t - 1 timesteps cached, weights
+        unchanged); None when the eager ``_decode`` path has to (re)build the cache first."""
+        dc = self._dc
+        if dc is None or dc["ptr"] != self._flat.data_ptr() or dc["stamp"] != self._staged_version or dc["t"] != t - 1 or t > self.max_length:
+            return None
+        r = self.__dict__.get("_step")
+        if r is None or r.dead(self) or r.enc is not encoder or (encoder is not None and r.frames.dtype != frames_dtype):
+            r = self.__dict__["_step"] = _StepRunner(self, encoder, frames_dtype)
+        r.arm(t)
+        return r
+
     def _decode(self, states, states_bf16, actions, returns_to_go, timesteps, t: int):
         """One ``dtb_dt_decode`` call: the tokens of timesteps ``t_cached .. t-1`` go through a single cluster kernel that attends to the
         cached keys / values of everything before.  Exact while ``t <= max_length``: without a positional embedding and with causal
@@ -378,9 +397,13 @@ class DecisionTransformer(nn.Module):
         ``use_cache=False``) it is one ``dtb_pad_left`` launch (window + padding + mask, integer-exact) plus the replay of a CUDA graph
         of the B = 1 forward over static history buffers (``_ActionRunner``)."""
         self._require_cuda(states)
-        if (self.kv_cache if use_cache is None else use_cache) and self.state_dim <= 64 and self._decode_ready():
+        if self.state_dim <= 64 and self._use_cache(use_cache):
             s = self._rows(states, self.state_dim, torch.float32)
             if s.shape[0] <= self.max_length:
+                self._stage()
+                r = self._step_runner(s.shape[0])
+                if r is not None:
+                    return r.step([(s, r.states), (actions, r.actions), (returns_to_go, r.rtg), (timesteps, r.timesteps)], s.shape[0])
                 return self._decode(s, None, self._rows(actions, self.act_dim, torch.float32), self._rows(returns_to_go, 0, torch.float32),
                                     self._rows(timesteps, 0, torch.long), s.shape[0])
         if self.max_length is None:
@@ -466,6 +489,83 @@ class DecisionTransformer(nn.Module):
                 self._h = None
         except Exception:
             pass
+
+
+class _StepRunner:
+    """Steady-state rollout step of the KV-cached get_action: ONE ``dtb_pad_left`` launch (the last two rows of every per-timestep
+    history -> static 2-row windows; the only launch that reads the caller's tensors) + the replay of ONE CUDA graph holding the towers
+    on the newest frame (multimodal model) and ``dtb_dt_decode_step`` (one kernel; the step count lives in device memory and is
+    advanced by the kernel, so the graph never changes).  Anything else — first call, new episode, changed weights, a skipped step —
+    goes through the eager ``_decode`` path, after which ``arm`` re-synchronises the device-side count."""
+
+    def __init__(self, dt, encoder=None, frames_dtype=None):
+        dev = dt._flat.device
+        self.dt, self.enc, self.dev = dt, encoder, dev
+        self.flat_ptr, self.cache_ptr = dt._flat.data_ptr(), dt._dc["cache"].data_ptr()
+        self.actions = torch.zeros((1, 2, dt.act_dim), dtype=torch.float32, device=dev)
+        self.rtg = torch.zeros((1, 2, 1), dtype=torch.float32, device=dev)
+        self.timesteps = torch.zeros((1, 2), dtype=torch.long, device=dev)
+        self.mask = torch.zeros((1, 2), dtype=torch.float32, device=dev)
+        self.states = self.frames = self.audio = None
+        if encoder is None:
+            self.states = torch.zeros((1, 2, dt.state_dim), dtype=torch.float32, device=dev)
+        else:
+            self.frames = torch.zeros((1, 2, *encoder.frame_shape), dtype=frames_dtype, device=dev)
+            self.audio = torch.zeros((1, 2, *encoder.audio_shape), dtype=torch.float32, device=dev)
+        self.t_dev = torch.zeros(1, dtype=torch.int32, device=dev)
+        self.t_next = -1  # host mirror of *t_dev (the history length the next step expects); -1 = unknown
+        self.graph, self._keep = None, None
+
+    def dead(self, dt):
+        return self.flat_ptr != dt._flat.data_ptr() or dt._dc is None or self.cache_ptr != dt._dc["cache"].data_ptr()
+
+    def arm(self, t_next: int):
+        if self.t_next != t_next:
+            self.t_dev.fill_(t_next)
+            self.t_next = t_next
+
+    def _body(self):
+        dt, lib = self.dt, _lib.load()
+        dc, feat = dt._dc, None
+        if self.enc is not None:
+            feat = self.enc.forward_raw(self.frames[:, 1:2], self.audio[:, 1:2])  # towers on the newest frame only
+        _lib.check(lib.dtb_dt_decode_step(dt._h, _lib.stream_ptr(), _lib.ptr(dt._flat), _lib.ptr(dt._flat_bf16), _lib.ptr(self.states),
+                                          _lib.ptr(feat), _lib.ptr(self.actions), _lib.ptr(self.rtg), _lib.ptr(self.timesteps),
+                                          _lib.ptr(self.t_dev), dt.max_length, _lib.ptr(dc["cache"]), dc["cache"].numel(), _lib.ptr(dc["out"])))
+        self._keep = (feat, None if self.enc is None else self.enc._last)
+
+    def step(self, hist, t: int):
+        """hist: [(source tensor with one row per timestep of the whole t-step history, static 2-row window)]; requires *t_dev == t."""
+        lib = _lib.load()
+        n = len(hist)
+        if "_dsts" not in self.__dict__:
+            self._dsts = (C.c_void_p * n)(*[d.data_ptr() for _, d in hist])
+            self._row_elems = [d[0, 0].numel() for _, d in hist]
+            self._rows = (C.c_int * n)(*[d[0, 0].numel() * d.element_size() for _, d in hist])
+            self._srcs = (C.c_void_p * n)()
+        srcs, keep = self._srcs, []
+        for i, (src, dst) in enumerate(hist):
+            if src.dtype != dst.dtype or not src.is_contiguous() or src.requires_grad:
+                src = src.detach().to(dst.dtype).contiguous()
+                keep.append(src)
+            if src.numel() // self._row_elems[i] != t:
+                raise ValueError("get_action: states / actions / returns_to_go / timesteps must have the same history length")
+            srcs[i] = src.data_ptr() + (max(0, t - 2) * self._rows[i])
+        _lib.check(lib.dtb_pad_left(_lib.stream_ptr(), n, srcs, self._dsts, self._rows, min(t, 2), 2, _lib.ptr(self.mask)))
+        if self.graph is None:
+            self._body()  # this call's step runs eagerly (it is also the warm-up: lazy allocations, tensor-map cache) ...
+            out = self.dt._dc["out"].clone()
+            torch.cuda.current_stream(self.dev).synchronize()
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):  # ... and is then captured (capture does not execute) for every later step
+                self._body()
+            self.graph = g
+        else:
+            self.graph.replay()
+            out = self.dt._dc["out"].clone()
+        self.t_next = t + 1
+        self.dt._dc["t"] = t
+        return out
 
 
 class _ActionRunner:
