@@ -517,21 +517,34 @@ __global__ void __launch_bounds__(DC_THREADS, 1) dt_decode_kernel(const DecodePa
   if (wide_tok >= 0) {
     const int k = (p0 + wide_tok) / 3, per = H / DC_CTAS;
     const bf16* srow = p.t_dev ? p.state_new : p.states_bf16 + (size_t)k * p.sd;
-    for (int c = rank * per + warp; c < (rank + 1) * per; c += DC_THREADS / 32) {
-      const bf16* w = Pb + p.e_off[E_WS] + (size_t)c * p.sd;
-      float a = 0.f;
-      for (int j = lane * 8; j < p.sd; j += 256) {  // sd % 8 == 0 (checked at dtb_dt_create)
-        const uint4 wv = __ldg(reinterpret_cast<const uint4*>(w + j)), sv = __ldg(reinterpret_cast<const uint4*>(srow + j));
-        const uint32_t ww[4] = {wv.x, wv.y, wv.z, wv.w}, ss[4] = {sv.x, sv.y, sv.z, sv.w};
+    // 8 consecutive outputs per warp and pass; per 256-wide k chunk the state row and the 8 weight rows are loaded before the first FMA
+    const int end = (rank + 1) * per;
+    for (int cb = rank * per + warp * 8; cb < end; cb += (DC_THREADS / 32) * 8) {
+      float a[8];
 #pragma unroll
-        for (int e = 0; e < 4; ++e) {
-          const float2 f = unpack_bf16x2(ww[e]), g = unpack_bf16x2(ss[e]);
-          a = fmaf(f.x, g.x, a);
-          a = fmaf(f.y, g.y, a);
+      for (int o = 0; o < 8; ++o) a[o] = 0.f;
+#pragma unroll 2
+      for (int j = lane * 8; j < p.sd; j += 256) {  // sd % 8 == 0 (checked at dtb_dt_create)
+        const uint4 sv = __ldg(reinterpret_cast<const uint4*>(srow + j));
+        uint4 wv[8];
+#pragma unroll
+        for (int o = 0; o < 8; ++o)
+          wv[o] = cb + o < end ? __ldg(reinterpret_cast<const uint4*>(Pb + p.e_off[E_WS] + (size_t)(cb + o) * p.sd + j)) : make_uint4(0u, 0u, 0u, 0u);
+        const float2 s0 = unpack_bf16x2(sv.x), s1 = unpack_bf16x2(sv.y), s2 = unpack_bf16x2(sv.z), s3 = unpack_bf16x2(sv.w);
+#pragma unroll
+        for (int o = 0; o < 8; ++o) {
+          const float2 w0 = unpack_bf16x2(wv[o].x), w1 = unpack_bf16x2(wv[o].y), w2 = unpack_bf16x2(wv[o].z), w3 = unpack_bf16x2(wv[o].w);
+          float v = a[o];
+          v = fmaf(w0.x, s0.x, v); v = fmaf(w0.y, s0.y, v); v = fmaf(w1.x, s1.x, v); v = fmaf(w1.y, s1.y, v);
+          v = fmaf(w2.x, s2.x, v); v = fmaf(w2.y, s2.y, v); v = fmaf(w3.x, s3.x, v); v = fmaf(w3.y, s3.y, v);
+          a[o] = v;
         }
       }
-      a = warp_sum(a);
-      if (lane == 0) s_sp[c] = a;
+#pragma unroll
+      for (int o = 0; o < 8; ++o) {
+        const float r = warp_sum(a[o]);
+        if (lane == 0 && cb + o < end) s_sp[cb + o] = r;
+      }
     }
     if (TC) __syncthreads(); else dc_cluster_sync();
   }
@@ -613,6 +626,8 @@ __global__ void __launch_bounds__(DC_THREADS, 1) dt_decode_kernel(const DecodePa
     if (TC) __syncthreads(); else dc_cluster_sync();
     dc_stamp(p, sk);  // +0: q | k | v done
     // ---- B: causal attention of the new tokens over the cache (HF:47-65); heads rank, rank + 8, ... ---------------------------------
+    // (Tried and dropped: one warp per (token, head) with lanes owning whole keys — 16.6 us instead of 4.7 us per layer at c1: with three
+    // busy warps the scattered K rows and the in-order P.V walk are pure load latency.  Keys spread over all 16 warps it stays.)
     for (int hh = rank; hh < p.nh; hh += DC_CTAS) {
       // warp w takes keys w, w + 8, ...; lane owns d / 32 dims; per (warp, token) online softmax, merged in warp order below
       const int per = d >> 5;  // 1, 2 or 4
