@@ -339,8 +339,11 @@ __global__ void __launch_bounds__(256) dt_decode_stage_tc_kernel(const DecodePar
 }
 
 // out[t][c] = sum_k in[t][k] W[k][c] for this CTA's columns of matrix m, on the tensor core; result left in red[t * ncols + c].
-__device__ __forceinline__ void dt_gemv(DcTc& tc, const DecodeParams& p, int rank, int m, const float* in, int n, float* red) {
-  const int K = tc.K[m], ncols = tc.ncols[m], ku_per_row = K >> 3;
+// epi(f, o): called by the thread that owns output feature f of this CTA's slice with the DC_NT token values o[] (bias, activation, residual
+// and the store happen there: the accumulators never take a detour through shared memory).
+template <typename Epi>
+__device__ __forceinline__ void dt_gemv(DcTc& tc, const DecodeParams& p, int rank, int m, const float* in, int n, Epi epi) {
+  const int K = tc.K[m], ku_per_row = K >> 3;
   // B operand: token rows (bf16, the inputs are already bf16-rounded values) in the K-major 128B-swizzled image, one 2 KB region per k-block
   for (int idx = threadIdx.x; idx < DC_NT * ku_per_row; idx += DC_THREADS) {
     const int t = idx / ku_per_row, ku = idx - t * ku_per_row;
@@ -418,9 +421,7 @@ __device__ __forceinline__ void dt_gemv(DcTc& tc, const DecodeParams& p, int ran
 #pragma unroll
         for (int t = 0; t < DC_NT; ++t) o[t] += __uint_as_float(v[t]);
       }
-      const int f = ft * 128 + q * 32 + lane;
-#pragma unroll
-      for (int t = 0; t < DC_NT; ++t) red[t * ncols + f] = o[t];
+      epi(ft * 128 + q * 32 + lane, o);
     }
   }
   tc_fence_before();
@@ -461,7 +462,7 @@ __global__ void __launch_bounds__(DC_THREADS, 1) dt_decode_kernel(const DecodePa
   const bf16* Pb = p.Pb;
   float* s_sp = TC ? lx : p.scratch;        // [H]      wide-state projection
   float* s_q = s_sp + H;                    // [NT][H]
-  float* s_o = s_q + DC_NT * H;             // [NT][H]
+  float* s_o = TC ? hb : s_q + DC_NT * H;   // [NT][H]  (tensor-core path: the attention output IS the next GEMV input)
   float* s_x1 = s_o + DC_NT * H;            // [NT][H]
   float* s_x2 = s_x1 + DC_NT * H;           // [NT][H]
   float* s_fc = s_x2 + DC_NT * H;           // [NT][I]
@@ -614,16 +615,28 @@ __global__ void __launch_bounds__(DC_THREADS, 1) dt_decode_kernel(const DecodePa
     }
     {
       const int ncols = 3 * H / DC_CTAS, c0 = rank * ncols;
-      if (TC) dt_gemv(tc, p, rank, 0, hb, n, red); else dc_gemv(st, p, rank, slots, full, consumed, 0, hb, n, red);
-      for (int i = threadIdx.x; i < n * ncols; i += DC_THREADS) {
+      if (TC) {
+        dt_gemv(tc, p, rank, 0, hb, n, [&](int c, const float (&o)[DC_NT]) {
+          const float b = pl[2 * H + c];
+          for (int t = 0; t < n; ++t) {
+            const float v = o[t] + b;
+            if (c < H) s_q[t * H + c] = dc_round_bf16(v);
+            else if (c < 2 * H) kc[(size_t)(p0 + t) * H + (c - H)] = __float2bfloat16(v);
+            else vc[(size_t)(p0 + t) * H + (c - 2 * H)] = __float2bfloat16(v);
+          }
+        });
+      } else {
+        dc_gemv(st, p, rank, slots, full, consumed, 0, hb, n, red);
+      }
+      for (int i = threadIdx.x; i < n * ncols && !TC; i += DC_THREADS) {
         const int t = i / ncols, c = c0 + (i - t * ncols);
-        const float v = red[i] + (TC ? pl[2 * H + c] : __ldg(P + p.l_off[L_BQKV] + lo + c));
+        const float v = red[i] + __ldg(P + p.l_off[L_BQKV] + lo + c);
         if (c < H) s_q[t * H + c] = dc_round_bf16(v);
         else if (c < 2 * H) kc[(size_t)(p0 + t) * H + (c - H)] = __float2bfloat16(v);
         else vc[(size_t)(p0 + t) * H + (c - 2 * H)] = __float2bfloat16(v);
       }
     }
-    if (TC) __syncthreads(); else dc_cluster_sync();
+    if (!TC) dc_cluster_sync();  // (tensor-core path: dt_gemv ends with a block barrier and there is no peer CTA)
     dc_stamp(p, sk);  // +0: q | k | v done
     // ---- B: causal attention of the new tokens over the cache (HF:47-65); heads rank, rank + 8, ... ---------------------------------
     // (Tried and dropped: one warp per (token, head) with lanes owning whole keys — 16.6 us instead of 4.7 us per layer at c1: with three
@@ -707,50 +720,67 @@ __global__ void __launch_bounds__(DC_THREADS, 1) dt_decode_kernel(const DecodePa
       }
       __syncthreads();
     }
-    if (TC) __syncthreads(); else dc_cluster_sync();
+    if (!TC) dc_cluster_sync();
     dc_stamp(p, sk);  // +1: attention done
     // ---- C: attn.c_proj + residual (HF:217-218, :281): this CTA's columns of x ---------------------------------------------------------
-    for (int i = threadIdx.x; i < n * H; i += DC_THREADS) hb[i] = (TC ? s_o[i] : __ldcg(s_o + i));
-    __syncthreads();
-    {
+    if (TC) {
+      dt_gemv(tc, p, rank, 1, hb, n, [&](int c, const float (&o)[DC_NT]) {
+        const float b = pl[5 * H + c];
+        for (int t = 0; t < n; ++t) x[t * H + c] += o[t] + b;  // residual stream updated in place by the owner of column c
+      });
+    } else {
+      for (int i = threadIdx.x; i < n * H; i += DC_THREADS) hb[i] = __ldcg(s_o + i);
+      __syncthreads();
       const int ncols = H / DC_CTAS, c0 = rank * ncols;
-      if (TC) dt_gemv(tc, p, rank, 1, hb, n, red); else dc_gemv(st, p, rank, slots, full, consumed, 1, hb, n, red);
+      dc_gemv(st, p, rank, slots, full, consumed, 1, hb, n, red);
       for (int i = threadIdx.x; i < n * ncols; i += DC_THREADS) {
         const int t = i / ncols, c = c0 + (i - t * ncols);
-        s_x1[t * H + c] = x[t * H + c] + red[i] + (TC ? pl[5 * H + c] : __ldg(P + p.l_off[L_BO] + lo + c));
+        s_x1[t * H + c] = x[t * H + c] + red[i] + __ldg(P + p.l_off[L_BO] + lo + c);
       }
+      dc_cluster_sync();
+      for (int i = threadIdx.x; i < n * H; i += DC_THREADS) x[i] = __ldcg(s_x1 + i);
+      __syncthreads();
     }
-    if (TC) __syncthreads(); else dc_cluster_sync();
-    for (int i = threadIdx.x; i < n * H; i += DC_THREADS) x[i] = (TC ? s_x1[i] : __ldcg(s_x1 + i));
-    __syncthreads();
     dc_stamp(p, sk);  // +2: attn.c_proj done
     // ---- D: ln_2 + mlp.c_fc + activation (HF:303, :234-235): this CTA's columns of the hidden layer ------------------------------------
-    if (TC) dc_layernorm<true>(x, hb, n, H, pl + 6 * H, pl + 7 * H, p.eps);
-    else dc_layernorm(x, hb, n, H, P + p.l_off[L_LN2W] + lo, P + p.l_off[L_LN2B] + lo, p.eps);
-    {
-      const int ncols = I / DC_CTAS, c0 = rank * ncols;
-      if (TC) dt_gemv(tc, p, rank, 2, hb, n, red); else dc_gemv(st, p, rank, slots, full, consumed, 2, hb, n, red);
-      for (int i = threadIdx.x; i < n * ncols; i += DC_THREADS) {
-        const int t = i / ncols, c = c0 + (i - t * ncols);
-        s_fc[t * I + c] = dc_round_bf16(dc_act(red[i] + (TC ? pl[8 * H + c] : __ldg(P + p.l_off[L_B1] + lo + c)), p.act));
-      }
-    }
-    if (TC) __syncthreads(); else dc_cluster_sync();
-    dc_stamp(p, sk);  // +3: mlp.c_fc done
     // ---- F: mlp.c_proj + residual (HF:236-237, :306) -----------------------------------------------------------------------------------
-    for (int i = threadIdx.x; i < n * I; i += DC_THREADS) hb[i] = (TC ? s_fc[i] : __ldcg(s_fc + i));
-    __syncthreads();
-    {
-      const int ncols = H / DC_CTAS, c0 = rank * ncols;
-      if (TC) dt_gemv(tc, p, rank, 3, hb, n, red); else dc_gemv(st, p, rank, slots, full, consumed, 3, hb, n, red);
-      for (int i = threadIdx.x; i < n * ncols; i += DC_THREADS) {
-        const int t = i / ncols, c = c0 + (i - t * ncols);
-        s_x2[t * H + c] = x[t * H + c] + red[i] + (TC ? pl[8 * H + I + c] : __ldg(P + p.l_off[L_B2] + lo + c));
+    if (TC) {
+      dc_layernorm<true>(x, hb, n, H, pl + 6 * H, pl + 7 * H, p.eps);
+      dt_gemv(tc, p, rank, 2, hb, n, [&](int c, const float (&o)[DC_NT]) {  // hb (the LayerNorm output) is free again: dt_gemv works on its operand image
+        const float b = pl[8 * H + c];
+        for (int t = 0; t < n; ++t) hb[t * I + c] = dc_round_bf16(dc_act(o[t] + b, p.act));
+      });
+      dc_stamp(p, sk);  // +3: mlp.c_fc done
+      dt_gemv(tc, p, rank, 3, hb, n, [&](int c, const float (&o)[DC_NT]) {
+        const float b = pl[8 * H + I + c];
+        for (int t = 0; t < n; ++t) x[t * H + c] += o[t] + b;
+      });
+    } else {
+      dc_layernorm(x, hb, n, H, P + p.l_off[L_LN2W] + lo, P + p.l_off[L_LN2B] + lo, p.eps);
+      {
+        const int ncols = I / DC_CTAS, c0 = rank * ncols;
+        dc_gemv(st, p, rank, slots, full, consumed, 2, hb, n, red);
+        for (int i = threadIdx.x; i < n * ncols; i += DC_THREADS) {
+          const int t = i / ncols, c = c0 + (i - t * ncols);
+          s_fc[t * I + c] = dc_round_bf16(dc_act(red[i] + __ldg(P + p.l_off[L_B1] + lo + c), p.act));
+        }
       }
+      dc_cluster_sync();
+      dc_stamp(p, sk);  // +3: mlp.c_fc done
+      for (int i = threadIdx.x; i < n * I; i += DC_THREADS) hb[i] = __ldcg(s_fc + i);
+      __syncthreads();
+      {
+        const int ncols = H / DC_CTAS, c0 = rank * ncols;
+        dc_gemv(st, p, rank, slots, full, consumed, 3, hb, n, red);
+        for (int i = threadIdx.x; i < n * ncols; i += DC_THREADS) {
+          const int t = i / ncols, c = c0 + (i - t * ncols);
+          s_x2[t * H + c] = x[t * H + c] + red[i] + __ldg(P + p.l_off[L_B2] + lo + c);
+        }
+      }
+      dc_cluster_sync();
+      for (int i = threadIdx.x; i < n * H; i += DC_THREADS) x[i] = __ldcg(s_x2 + i);
+      __syncthreads();
     }
-    if (TC) __syncthreads(); else dc_cluster_sync();
-    for (int i = threadIdx.x; i < n * H; i += DC_THREADS) x[i] = (TC ? s_x2[i] : __ldcg(s_x2 + i));
-    __syncthreads();
     dc_stamp(p, sk);  // +4: mlp.c_proj done
   }
 
