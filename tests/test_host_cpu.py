@@ -69,6 +69,20 @@ def test_encoder_layout_and_state_dict_roundtrip():
         assert set(o.state_dict()) == set(e.state_dict()) and o.state_dim == e.state_dim
         e.load_state_dict(o.state_dict())
         assert all(torch.equal(e.state_dict()[k], v) for k, v in o.state_dict().items())
+        # flat layout for the data-parallel exchange: both towers' conv tensors first, both FC tensors last (one contiguous FC range), the
+        # entries never overlap, and the names keep the reference's module order
+        fc_begin, fc_end = e.fc_grad_range()
+        assert 0 < fc_begin < fc_end == e._total
+        fc_idx = "7" if args[2] == "big" else "5"
+        spans = []
+        for name, shp, off in zip(e._names, e._shapes, e._offsets):
+            n = int(torch.Size(shp).numel())
+            is_fc = name.split(".")[1] == fc_idx
+            assert (off >= fc_begin) == is_fc, (name, off, fc_begin)
+            spans.append((off, off + n))
+        spans.sort()
+        assert all(a[1] <= b[0] for a, b in zip(spans, spans[1:]))
+        assert [n.split(".")[0] for n in e._names[:2]] == ["video_net", "video_net"] and e._names[-1].startswith("audio_net")
 
 
 def test_no_cpu_fallback():
