@@ -320,3 +320,26 @@ def test_reset_parameters_follows_upstream_init_split():
     assert abs(float(sd["transformer.h.1.mlp.c_proj.weight"].std()) - 0.02 / 2.0) < 2e-3   # scaled by 1 / sqrt(2 L)
     assert float(sd["transformer.h.0.mlp.c_fc.bias"].abs().sum()) == 0.0
     assert torch.equal(sd["embed_ln.weight"], torch.ones(128)) and torch.equal(sd["transformer.ln_f.weight"], torch.ones(128))
+
+
+def test_argument_validation_of_the_round2_entry_points_needs_no_gpu():
+    """dtb_colsum_bf16_static / dtb_dt_decode_step / dtb_encoder_wait_fc_grads reject bad arguments before any CUDA call."""
+    import ctypes as C
+
+    from mtrl_b200 import _lib
+    from mtrl_b200.model import DecisionTransformer
+
+    lib = _lib.load()
+    fake_x, fake_out = C.c_void_p(0x10000), C.c_void_p(0x20000)  # never dereferenced: the calls below are rejected first
+    assert lib.dtb_colsum_bf16_static(None, fake_x, 16, 1032, 1032, fake_out, 0) == -1
+    assert b"exceeds the static scratch limit" in lib.dtb_last_error()
+    assert lib.dtb_colsum_bf16_static(None, fake_x, 16, 12, 16, fake_out, 0) == -1      # N not a multiple of 8
+    assert lib.dtb_colsum_bf16_static(None, None, 16, 8, 8, fake_out, 0) == -1           # null input
+    dt = DecisionTransformer(11, 3, 128, max_length=20, max_ep_len=100, device="cpu")
+    assert lib.dtb_dt_decode_supported(dt._h) == 2                                          # hidden 128: the tensor-core decode kernel
+    assert lib.dtb_dt_decode_step(dt._h, None, None, None, None, None, None, None, None, None, 20, None, 0, None) == -1
+    wide = DecisionTransformer(11, 3, 64, max_length=20, max_ep_len=100, n_head=2, device="cpu")
+    assert lib.dtb_dt_decode_supported(wide._h) == 1                                        # other widths: the CUDA-core cluster kernel
+    assert dt._use_cache(None) is False      # training mode (dropout 0.1 active): never cached
+    dt.eval(); wide.eval()
+    assert dt._use_cache(None) is True and wide._use_cache(None) is False and wide._use_cache(True) is True  # automatic choice = tensor-core kernel only
