@@ -39,8 +39,11 @@ WORKLOADS = {
 MAX_EP_LEN = 1000
 
 
-def make_batch(wl, B, seed):
-    """Seeded synthetic trajectories of SURVEY.md §8d, on the host."""
+def make_batch(wl, B, seed, with_index=False):
+    """Seeded synthetic trajectories of SURVEY.md §8d, on the host.  Mono-audio workloads (Minecraft2d: c2 / c5) draw every timestep's
+    spectrogram from a table of three images, as the reference environment does (Minecraft.py:145-159: mfcc_target_good / _bad /
+    _no_listen, built once by _init_mfcc :222-225); `audio` is always the expanded fp32 tensor, with_index=True adds `audio_index`
+    (int64 [B, K]) and `audio_table` (fp32 [3, 1, H, W]) for feeders that ship indices instead of images."""
     from util import make_inputs
 
     dt = wl["dt"]
@@ -55,7 +58,15 @@ def make_batch(wl, B, seed):
         # uint8 pixels, the format the frames exist in before the reference's decode img * 2 / 255 - 1 (Minecraft.py:333-335); our arm
         # ships the pixels and decodes in-kernel (bit-identical, tests/test_encoder_gpu.py), the CPU arm decodes on the host
         out["frames"] = torch.randint(0, 256, (B, K, *wl["enc"]["frame_shape"]), generator=g, dtype=torch.uint8)
-        out["audio"] = torch.randn(B, K, *wl["enc"]["audio_shape"], generator=g).clamp_(-1, 1)
+        ashape = tuple(wl["enc"]["audio_shape"])
+        if ashape[0] == 1:
+            table = torch.rand(3, *ashape, generator=g) * 2 - 1  # min-max normalised MFCC images in [-1, 1] (Minecraft.py:239-243)
+            idx = torch.randint(0, 3, (B, K), generator=g)
+            out["audio"] = table[idx]
+            if with_index:
+                out["audio_index"], out["audio_table"] = idx, table
+        else:  # stereo spectrograms (Skeleton+): arbitrary per-timestep images
+            out["audio"] = torch.randn(B, K, *ashape, generator=g).clamp_(-1, 1)
     return out
 
 
@@ -204,8 +215,16 @@ def run_ours(args, wl, rank, world, local_rank):
     B, K = wl["B"], wl["K"]
     model, parts = build_ours(wl, dev, args.dropout, rank)
     broadcast_parameters([p.flat_params for p in parts])
-    host = make_batch(wl, B, seed=1234 + rank)  # per-rank data seeds (ppo_atari_multigpu.py:197-199); weak scaling: B per GPU fixed
-    pinned = {k: v.contiguous().pin_memory() for k, v in host.items()}
+    host = make_batch(wl, B, seed=1234 + rank, with_index=True)  # per-rank data seeds (ppo_atari_multigpu.py:197-199); weak scaling: B per GPU fixed
+    # `pinned`: every input as a full tensor (what the step reads; the reference's layouts).  `feed`: what the e2e loop ships per step — the
+    # same, except that a table-drawn input (Minecraft2d's audio channel: one of three MFCC images per timestep) travels as its indices
+    # and is gathered from the device-resident table on the copy stream (HostBatchPipeline(indexed=...): lossless, the step sees `audio`)
+    pinned = {k: v.contiguous().pin_memory() for k, v in host.items() if k not in ("audio_index", "audio_table")}
+    indexed, feed = None, pinned
+    if "audio_index" in host:
+        indexed = {"audio": ("audio_index", host["audio_table"].to(dev))}
+        feed = {k: v for k, v in pinned.items() if k != "audio"}
+        feed["audio_index"] = host["audio_index"].contiguous().pin_memory()
     reducer = GradAllReducer(bucket_bytes=args.bucket_mb << 20) if world > 1 else None
 
     def make_step_for(dev_in):
@@ -226,14 +245,14 @@ def run_ours(args, wl, rank, world, local_rank):
 
     graphed = not args.no_graph  # NCCL all-reduces on the communication stream are captured into the step's graph too
     try:
-        pipe = HostBatchPipeline(make_step_for, pinned, dev, use_graph=graphed, warmup=max(args.warmup, 3))
+        pipe = HostBatchPipeline(make_step_for, pinned, dev, use_graph=graphed, warmup=max(args.warmup, 3), indexed=indexed)
     except Exception as e:  # noqa: BLE001
         if not graphed:
             raise
         print(f"[bench] CUDA graph capture failed ({e}); timing plain launches", file=sys.stderr)
         torch.cuda.synchronize(dev)
         graphed = False
-        pipe = HostBatchPipeline(make_step_for, pinned, dev, use_graph=False, warmup=max(args.warmup, 3))
+        pipe = HostBatchPipeline(make_step_for, pinned, dev, use_graph=False, warmup=max(args.warmup, 3), indexed=indexed)
     slot = pipe.slots[0]
     dev_in, step = slot["dev"], slot["step"]
     h2d = pipe.bytes_per_batch
@@ -258,41 +277,46 @@ def run_ours(args, wl, rank, world, local_rank):
 
     # ---- e2e: pinned host buffers -> H2D (copy stream, double-buffered: batch i+1 copies while step i computes) -> step -> loss D2H + sync,
     # every step, through the package's own feeder (mtrl_b200.pipeline.HostBatchPipeline) ----
-    pipe.prefetch(pinned)
-    for _ in range(3):
-        pipe.step(pinned)
-    if world > 1:
-        dist.barrier()
-    torch.cuda.synchronize(dev)
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        loss_val = pipe.step(pinned)
-    torch.cuda.synchronize(dev)
-    e2e_ms = (time.perf_counter() - t0) / args.steps * 1e3
-    if world > 1:
-        t = torch.tensor([e2e_ms], device=dev, dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e_ms = float(t.item())
+    def e2e_loop(batch, deferred=False):
+        pipe.deferred_loss = deferred
+        pipe.prefetch(batch)
+        for _ in range(3):
+            pipe.step(batch)
+        if deferred:
+            pipe.flush()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+        t0 = time.perf_counter()
+        last = None
+        for _ in range(args.steps):
+            last = pipe.step(batch)
+        if deferred:
+            last = pipe.flush()
+        torch.cuda.synchronize(dev)
+        ms_ = (time.perf_counter() - t0) / args.steps * 1e3
+        pipe.step(None)  # drain the prefetched slot so that the next loop starts clean
+        if deferred:
+            pipe.flush()
+        torch.cuda.synchronize(dev)
+        pipe.deferred_loss = False
+        if world > 1:
+            t = torch.tensor([ms_], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms_ = float(t.item())
+        return ms_, last
+
+    e2e_ms, loss_val = e2e_loop(feed)
     # the same loop with the loss read deferred by one step (HostBatchPipeline(deferred_loss=True) semantics): every loss still crosses to the
     # host inside the timed region, but the host enqueues step i + 1 before it waits for loss i
-    pipe.deferred_loss = True
-    for _ in range(3):
-        pipe.step(pinned)
-    pipe.flush()
-    if world > 1:
-        dist.barrier()
-    torch.cuda.synchronize(dev)
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        pipe.step(pinned)
-    loss_deferred = pipe.flush()
-    torch.cuda.synchronize(dev)
-    e2e_def_ms = (time.perf_counter() - t0) / args.steps * 1e3
-    pipe.deferred_loss = False
-    if world > 1:
-        t = torch.tensor([e2e_def_ms], device=dev, dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e_def_ms = float(t.item())
+    e2e_def_ms, loss_deferred = e2e_loop(feed, deferred=True)
+    # round 1 / 2 comparison: every input as a full tensor in the reference's layouts (the audio channel as fp32 images)
+    e2e_full_ms = None
+    if indexed:
+        order, pipe._copy_first = pipe._copy_first, True  # 55 MB per step: the copy is the longer pole, enqueue it first (as rounds 1-2 did)
+        e2e_full_ms = e2e_loop(pinned)[0]
+        pipe._copy_first = order
+    h2d_full = sum(v.numel() * v.element_size() for v in pinned.values())
     clock_info = clocks.stop() if rank == 0 else None
     consistent = replicas_consistent([p.flat_params for p in parts])
 
@@ -340,7 +364,14 @@ def run_ours(args, wl, rank, world, local_rank):
                             (" + overlapped NCCL all-reduce" if world > 1 else "") +
                             ("" if args.restage_each_step else " (bf16 weight staging belongs to the optimizer step: train_step_with_optimizer)")},
         "e2e": {"value": tokens / e2e_ms * 1e3, "unit": "tokens/s", "ms_per_step": e2e_ms, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 8,
-                "host_format": "pinned host buffers in the reference's layouts (fp32; video frames as uint8 pixels, decoded in-kernel)",
+                "host_format": ("pinned host buffers: video frames as uint8 pixels (decoded in-kernel), the audio channel as indices into the environment's "
+                                "table of three MFCC images (REF Minecraft.py:145-159, 222-225; gathered on the device, lossless), everything else fp32 / int64 "
+                                "in the reference's layouts" if indexed else
+                                "pinned host buffers in the reference's layouts (fp32; video frames as uint8 pixels, decoded in-kernel)"),
+                "full_tensor_inputs": (None if e2e_full_ms is None else
+                                       {"value": tokens / e2e_full_ms * 1e3, "unit": "tokens/s", "ms_per_step": e2e_full_ms, "h2d_bytes_per_step": h2d_full,
+                                        "what": "same loop with the audio channel shipped as fp32 images every step (the e2e format of rounds 1-2): bound by the "
+                                                "PCIe link, not by the kernels"}),
                 "overlap": "H2D of batch i+1 on a copy stream while step i computes (double-buffered device slots)",
                 "loss_read": "the step's own loss, one stream sync per step (upstream train_step semantics)",
                 "deferred_loss_read": {"value": tokens / e2e_def_ms * 1e3, "unit": "tokens/s", "ms_per_step": e2e_def_ms, "last_loss": loss_deferred,

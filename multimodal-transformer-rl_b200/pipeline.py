@@ -15,24 +15,40 @@ import torch
 
 class HostBatchPipeline:
     def __init__(self, make_step: Callable[[Dict[str, torch.Tensor]], Callable[[], torch.Tensor]], example: Dict[str, torch.Tensor],
-                 device: torch.device, use_graph: bool = True, warmup: int = 3, deferred_loss: bool = False):
+                 device: torch.device, use_graph: bool = True, warmup: int = 3, deferred_loss: bool = False,
+                 indexed: Dict[str, tuple] | None = None):
         """make_step(device_batch) -> step() returning a device tensor whose element 0 is the loss; `example` fixes shapes/dtypes.
+        indexed: {name: (index_key, table)} — input `name` of the step is a gather ``table[index]`` of a small device-resident table
+        (table [n, *row_shape] on `device`, index int64 with the leading dims of the input): host batches then carry `index_key` instead
+        of `name`, only the indices cross PCIe, and the rows are expanded into the slot's device tensor on the copy stream (lossless;
+        the step sees the same tensor).  The reference's Minecraft2d audio channel is such an input: every timestep's spectrogram is one
+        of three precomputed MFCC images (REF environments/Minecraft/Minecraft.py:145-159, 222-225).
         deferred_loss: ``step()`` returns the loss of the PREVIOUS step (nan on the first call; ``flush()`` returns the last one): every
         step's loss is still copied to the host, but the host no longer waits for step i before enqueueing step i + 1, so the GPU never
         idles for a host round trip.  Default False = upstream ``train_step()`` semantics (the step's own loss, one sync per step)."""
         self.device = device
         self.copy_stream = torch.cuda.Stream(device=device)
         self.slots = []
+        self.indexed = dict(indexed or {})
+        self._index_of = {ik: (name, table) for name, (ik, table) in self.indexed.items()}
+        for name, (ik, table) in self.indexed.items():
+            if name not in example or table.device != torch.device(device) or tuple(example[name].shape[-(table.dim() - 1):]) != tuple(table.shape[1:]):
+                raise ValueError(f"indexed input {name!r}: table must live on {device} and its rows must match the input's trailing dims")
         for _ in range(2):
             dev = {k: torch.empty(v.shape, dtype=v.dtype, device=device) for k, v in example.items()}
-            self.slots.append(dict(dev=dev, step=make_step(dev), graph=None, out=None, copied=torch.cuda.Event(), consumed=torch.cuda.Event()))
+            idx = {ik: torch.empty(example[name].shape[:example[name].dim() - (table.dim() - 1)], dtype=torch.long, device=device)
+                   for name, (ik, table) in self.indexed.items()}
+            self.slots.append(dict(dev=dev, idx=idx, step=make_step(dev), graph=None, out=None, copied=torch.cuda.Event(), consumed=torch.cuda.Event()))
         self.loss_host = torch.empty(2, dtype=torch.float32).pin_memory()
         self.deferred_loss = bool(deferred_loss)
         self._loss_hosts = [torch.empty(2, dtype=torch.float32).pin_memory() for _ in range(2)]
         self._loss_events = [torch.cuda.Event() for _ in range(2)]
         self._pending, self._parity = None, 0
-        self.bytes_per_batch = sum(v.numel() * v.element_size() for v in example.values())
+        # bytes that cross PCIe per batch: the full tensors, except indexed inputs (8 bytes per gathered row)
+        self.bytes_per_batch = sum(v.numel() * v.element_size() for k, v in example.items() if k not in self.indexed) + \
+            sum(8 * s_idx.numel() for s_idx in self.slots[0]["idx"].values())
         self._cur, self._filled = 0, False
+        self._copy_first = self.bytes_per_batch > (32 << 20)
         # warm-up on real data, then capture one graph per slot
         for s in self.slots:
             for k, v in example.items():
@@ -56,7 +72,12 @@ class HostBatchPipeline:
         self.copy_stream.wait_event(s["consumed"])  # the step that last read this slot has finished
         with torch.cuda.stream(self.copy_stream):
             for k, v in host_batch.items():
-                s["dev"][k].copy_(v, non_blocking=True)
+                if k in self._index_of:  # indices cross PCIe, the rows are gathered from the resident table on the copy stream
+                    name, table = self._index_of[k]
+                    s["idx"][k].copy_(v, non_blocking=True)
+                    torch.index_select(table, 0, s["idx"][k].view(-1), out=s["dev"][name].view(-1, *table.shape[1:]))
+                else:
+                    s["dev"][k].copy_(v, non_blocking=True)
             s["copied"].record(self.copy_stream)
         self._filled = True
 
@@ -67,7 +88,10 @@ class HostBatchPipeline:
         s = self.slots[self._cur]
         main = torch.cuda.current_stream(self.device)
         main.wait_event(s["copied"])
-        if next_host_batch is not None:
+        # Large batches (the copy takes about as long as the step): start the next copy first, it is the longer pole.  Small ones (indices,
+        # uint8 frames): launch the step first — the host time of enqueueing the copies (tens of microseconds) would otherwise sit between
+        # the previous step's sync and this step's first kernel.
+        if next_host_batch is not None and self._copy_first:
             self.prefetch(next_host_batch)  # overlaps with the kernels enqueued next
         if s["graph"] is not None:
             s["graph"].replay()
@@ -75,6 +99,8 @@ class HostBatchPipeline:
         else:
             out = s["step"]()
         s["consumed"].record(main)
+        if next_host_batch is not None and not self._copy_first:
+            self.prefetch(next_host_batch)  # overlaps with the kernels just enqueued
         if next_host_batch is not None:
             self._cur = 1 - self._cur
         else:

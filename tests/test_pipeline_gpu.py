@@ -45,3 +45,33 @@ def test_pipeline_losses_match_direct_steps(cuda_device, use_graph):
     assert math.isnan(lagged[0]) and lagged[1:] == direct[:-1]
     assert pipe.flush() == direct[-1]
     assert math.isnan(pipe.flush())  # nothing pending any more
+
+
+def test_indexed_input_equals_full_tensor_input(cuda_device):
+    """An input drawn from a small table (the reference's Minecraft2d audio channel: one of three MFCC images per timestep) may travel as
+    its indices: the rows are gathered on the copy stream and the step sees the same tensor, so the losses are bit-identical and only
+    8 bytes per row cross PCIe; a batch that carries the full tensor instead still works on the same pipeline."""
+    from mtrl_b200.pipeline import HostBatchPipeline
+    from util import make_inputs
+
+    dev = cuda_device
+    _, model, batches, make_step = (None, *_setup(dev))
+    K, sd = batches[0]["states"].shape[1], batches[0]["states"].shape[2]
+    g = torch.Generator().manual_seed(3)
+    table = torch.randn(3, sd, generator=g)
+    full, feed = [], []
+    for b in batches:
+        idx = torch.randint(0, 3, b["states"].shape[:2], generator=g)
+        fb = dict(b, states=table[idx].contiguous().pin_memory())
+        full.append(fb)
+        feed.append({**{k: v for k, v in fb.items() if k != "states"}, "state_index": idx.pin_memory()})
+    direct = [float(make_step({k: v.to(dev) for k, v in b.items()})()[0]) for b in full]
+    pipe = HostBatchPipeline(make_step, full[0], dev, indexed={"states": ("state_index", table.to(dev))})
+    assert pipe.bytes_per_batch == sum(v.numel() * v.element_size() for k, v in full[0].items() if k != "states") + 8 * full[0]["states"].shape[0] * K
+    pipe.prefetch(feed[0])
+    got = [pipe.step(feed[i + 1] if i + 1 < len(feed) else None) for i in range(len(feed))]
+    assert got == direct
+    pipe.prefetch(full[1])  # the full tensor is still accepted
+    assert pipe.step(None) == direct[1]
+    with pytest.raises(ValueError):
+        HostBatchPipeline(make_step, full[0], dev, indexed={"states": ("state_index", table[:, :4].to(dev))})
