@@ -11,7 +11,7 @@ Follows /root/reference/src/agents.py:
 Generalisation (SURVEY.md F4): the reference hard-codes in_channels=1 and an 84x84 input (flatten 64*7*7 / 32*9*9);
 BASELINE.json names 3x64x64 frames and 1- or 2-channel 64x64 spectrograms, so C_in/H/W are parameters here and the
 flatten size is derived.  At (1, 84, 84) this module is numerically the reference's conv_factory
-(pinned by oracle/check_vs_reference.py and tests/golden/encoder_ref_*.pt).
+(pinned by tests/golden/make_golden.py, which imports the reference classes, and its fixtures tests/golden/encoder_ref_*.pt).
 Fusion quirk: agents.py:138 concatenates along dim 0 and relies on the reshape at :146, which equals the intended
 per-sample [video | audio] only for batch 1; sibling scripts use dim=1 explicitly (src/minecraft_lstm_google.py:83).
 The oracle implements the per-sample (dim=1) semantics.
