@@ -343,3 +343,44 @@ def test_argument_validation_of_the_round2_entry_points_needs_no_gpu():
     assert dt._use_cache(None) is False      # training mode (dropout 0.1 active): never cached
     dt.eval(); wide.eval()
     assert dt._use_cache(None) is True and wide._use_cache(None) is False and wide._use_cache(True) is True  # automatic choice = tensor-core kernel only
+
+
+def test_traffic_table_is_reproducible_from_the_committed_csv(tmp_path):
+    """bench.py's roofline.traffic comes from profiles/r02_traffic.json; that file must be exactly what tools/ncu_traffic.py makes of the
+    committed ncu CSV ('recomputable by running one committed script on one committed CSV')."""
+    import importlib.util
+    import json
+    import shutil
+
+    committed = json.load(open(os.path.join(ROOT, "profiles", "r02_traffic.json")))
+    work = tmp_path / "repo"
+    (work / "profiles").mkdir(parents=True)
+    (work / "tools").mkdir()
+    shutil.copy(os.path.join(ROOT, "tools", "ncu_traffic.py"), work / "tools" / "ncu_traffic.py")
+    shutil.copy(os.path.join(ROOT, "profiles", "r02_c2_traffic_v3.csv"), work / "profiles" / "r02_c2_traffic_v3.csv")
+    r = subprocess.run([sys.executable, str(work / "tools" / "ncu_traffic.py"), "c2", str(work / "profiles" / "r02_c2_traffic_v3.csv")],
+                       capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stderr[-2000:]
+    again = json.load(open(work / "profiles" / "r02_traffic.json"))
+    assert set(again["c2"]) == set(committed["c2"])
+    for fam, row in committed["c2"].items():
+        for k in ("dram_bytes_per_launch", "dram_read_per_launch", "dram_write_per_launch", "launches_in_capture"):
+            assert again["c2"][fam][k] == pytest.approx(row[k], rel=1e-12), (fam, k)
+    gemm = committed["c2"]["gemm_tcgen05_kernel, HBM-bound shapes"]
+    assert 4e6 < gemm["dram_bytes_per_launch"] < 6e6  # 4.97 MB per launch: below the 7.70 MB algorithmic bytes (no re-reads)
+
+
+def test_bench_minecraft_audio_is_drawn_from_a_three_image_table():
+    """bench.make_batch mirrors the reference environment: every timestep's spectrogram of a mono-audio workload is one of three images
+    (REF environments/Minecraft/Minecraft.py:145-159); the index form expands to exactly the full tensor, stereo workloads stay free-form."""
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import bench
+
+    wl = dict(bench.WORKLOADS["c2"])
+    a, b = bench.make_batch(wl, 4, seed=5), bench.make_batch(wl, 4, seed=5, with_index=True)
+    assert set(b) - set(a) == {"audio_index", "audio_table"} and all(torch.equal(a[k], b[k]) for k in a)
+    assert b["audio_table"].shape == (3, 1, 64, 64) and b["audio_index"].dtype == torch.long and int(b["audio_index"].max()) <= 2
+    assert torch.equal(b["audio_table"][b["audio_index"]], b["audio"])
+    assert float(b["audio"].min()) >= -1.0 and float(b["audio"].max()) <= 1.0
+    assert "audio_index" not in bench.make_batch(dict(bench.WORKLOADS["c3"]), 2, seed=5, with_index=True)
