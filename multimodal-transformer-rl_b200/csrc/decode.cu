@@ -8,11 +8,17 @@
 // falls back to the recompute path (model.py).  One detail of the upstream call convention: the action of the newest timestep is a zero
 // placeholder that becomes the real action on the next call, so the action token of timestep t-1 is (re)computed together with R_t, s_t.
 //
-// Work split: every weight matrix is column-partitioned over the C CTAs (each reads 1/C of it, 16-byte loads, k split over the
-// threads, partial sums combined in a fixed order: deterministic, and independent of how many tokens a call processes — a rollout that
-// appends step by step and a single call over the same history produce the same bits).  Activations of the <= 3 new tokens are
-// exchanged through a tiny L2-resident scratch between cluster barriers (5 per layer).  CUDA cores on purpose: M = 3 rows would waste
-// > 97 % of a 128-row tcgen05 tile, and the kernel is bound by streaming the weights from L2 (c1: 1.2 MB per call).
+// Two forms of the kernel (template parameter TC; dc_use_tc picks):
+//  * TC = true, hidden 128 (c1 / c2 / c5), one CTA: the GEMVs run on the tensor core with the WEIGHTS as the A operand (128 output features
+//    per tcgen05.mma, the <= 3 new tokens padded to 16 columns as the B operand) — M = 3 token rows as the A operand would waste > 97 % of
+//    a 128-row tile, features-as-rows wastes nothing but columns.  Weights stream from L2 as pre-swizzled 16 KB blocks (see dt_gemv);
+//    everything between the phases stays in shared memory.  Measured 72 us per step at c1 (the CUDA-core form: 127 us, issue / barrier bound).
+//  * TC = false, any other width: every weight matrix is column-partitioned over the C CTAs of a cluster (each reads 1/C of it through a
+//    cp.async.bulk tile ring, k split over the threads, partial sums combined in a fixed order), activations of the new tokens exchanged
+//    through a tiny L2-resident scratch between cluster barriers (5 per layer).
+// Both are deterministic and independent of how many tokens a call processes: a rollout that appends step by step and a single call over
+// the same history produce the same bits.  Step mode (dtb_dt_decode_step): the step count comes from device memory, so one captured CUDA
+// graph serves every step of a rollout.
 #include "dt_handle.h"
 
 #include <new>
