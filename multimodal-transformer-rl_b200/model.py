@@ -336,14 +336,20 @@ class DecisionTransformer(nn.Module):
             self._dc["t"] = 0
 
     def _decode_ready(self) -> bool:
-        return bool(self.max_length is not None and not self.dropout_active()
-                    and _lib.load().dtb_dt_decode_supported(self._h))
+        return bool(self.max_length is not None and not self.dropout_active() and self._decode_support())
+
+    def _decode_support(self) -> int:
+        """dtb_dt_decode_supported of this configuration (0 no, 1 CUDA-core kernel, 2 tensor-core kernel); a property of the config: asked once."""
+        v = self.__dict__.get("_dc_support")
+        if v is None:
+            v = self.__dict__["_dc_support"] = int(_lib.load().dtb_dt_decode_supported(self._h))
+        return v
 
     def _use_cache(self, use_cache) -> bool:
         """use_cache argument > kv_cache attribute > automatic (on where dtb_dt_decode_supported reports the tensor-core kernel: 2)."""
         choice = self.kv_cache if use_cache is None else use_cache
         if choice is None:
-            return bool(self.max_length is not None and not self.dropout_active() and _lib.load().dtb_dt_decode_supported(self._h) == 2)
+            return bool(self.max_length is not None and not self.dropout_active() and self._decode_support() == 2)
         return bool(choice) and self._decode_ready()
 
     def _step_runner(self, t: int, encoder=None, frames_dtype=None):
@@ -398,12 +404,13 @@ class DecisionTransformer(nn.Module):
         of the B = 1 forward over static history buffers (``_ActionRunner``)."""
         self._require_cuda(states)
         if self.state_dim <= 64 and self._use_cache(use_cache):
-            s = self._rows(states, self.state_dim, torch.float32)
-            if s.shape[0] <= self.max_length:
+            t = states.numel() // self.state_dim
+            if t <= self.max_length:
                 self._stage()
-                r = self._step_runner(s.shape[0])
-                if r is not None:
-                    return r.step([(s, r.states), (actions, r.actions), (returns_to_go, r.rtg), (timesteps, r.timesteps)], s.shape[0])
+                r = self._step_runner(t)
+                if r is not None:  # (the runner converts dtype / layout only when it has to: no per-call views on the host)
+                    return r.step([(states, r.states), (actions, r.actions), (returns_to_go, r.rtg), (timesteps, r.timesteps)], t)
+                s = self._rows(states, self.state_dim, torch.float32)
                 return self._decode(s, None, self._rows(actions, self.act_dim, torch.float32), self._rows(returns_to_go, 0, torch.float32),
                                     self._rows(timesteps, 0, torch.long), s.shape[0])
         if self.max_length is None:
